@@ -1,0 +1,186 @@
+/* seacurrent_b200.h — C ABI of the B200-native sea-current planning hot path.
+ *
+ * Drop-in boundary for the path  waypoints -> Bezier spline (reference cubic, or Lau09 quintic +
+ * curvature/arc-length optimiser) -> toppra time parameterisation -> sampled trajectory,
+ * batched over P independent planning problems.  Everything behind these entry points is
+ * hand-written sm_100a CUDA; there is no CPU fallback: every entry point returns
+ * SCB_E_NO_DEVICE / SCB_E_CUDA when no B200-class device can be used.
+ *
+ * Reference interfaces replaced (paths relative to the sea-current tree; "sc:" =
+ * sea_current.hpp, "tp:" = third-party/toppra/cpp/src/toppra/):
+ *   bezier_spline::from_path            sc:402, sc:599-683   -> ctrl_x / ctrl_y
+ *   bezier_spline::arclength            sc:413, sc:767-896   -> arclen_total / arclen_table
+ *   gen_vel_prof<1>                     sc:1191-1265         -> status, K_lo/K_hi, x, t, s_* streams
+ *     TOPPRA::computePathParametrization tp:algorithm.cpp:14-26 (ReturnCode tp:algorithm.hpp:13-32)
+ *     parametrizer::Spline              tp:parametrizer/spline.cpp:10-45
+ *   bezier_spline::resample             sc:419, sc:898-1005  -> px / py, s_px / s_py
+ *   bezier_spline::angular_velocity     sc:416, sc:1055-1067 -> omega, s_omega
+ *   serialize_path_to_json              sc:1423-1457         -> host side, include/sea_current_b200.hpp
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no C++/torch types cross the ABI; nothing throws.
+ *   - return value: 0 = OK, < 0 = API / CUDA error (scb_strerror).  A per-problem planning
+ *     failure never fails the batch: it is reported in status[p] with toppra's ReturnCode
+ *     numbering and fail_stage[p] = the gridpoint index at which the LP became infeasible.
+ *   - "real" buffers hold double when the context precision is SCB_FP64 and float when it is
+ *     SCB_FP32.
+ *   - layouts: per-path arrays are problem-major  [P][n]  (one path's data contiguous: the
+ *     spline kernels run one warp per path); per-gridpoint and per-sample arrays are
+ *     gridpoint-major  [G][P]  (problem index fastest: the toppra kernels run one thread per
+ *     problem, so adjacent threads touch adjacent addresses).
+ *   - any output pointer may be NULL: that array is then not produced.
+ *   - one scb_ctx per host thread and GPU; calls on a ctx are serialised on its stream.
+ */
+#ifndef SEACURRENT_B200_H
+#define SEACURRENT_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SCB_VERSION 100 /* 0.1.0 */
+
+/* API-level error codes (function return values) */
+enum {
+  SCB_OK = 0,
+  SCB_E_INVALID = -1,   /* bad argument (NULL, P/W/G out of range, capacity exceeded) */
+  SCB_E_NO_DEVICE = -2, /* no CUDA device / not an sm_100 part */
+  SCB_E_CUDA = -3,      /* CUDA runtime error; see scb_last_cuda_error */
+  SCB_E_NOMEM = -4
+};
+
+/* per-problem status[p].  0-5 are toppra's ReturnCode (tp:algorithm.hpp:13-32). */
+enum {
+  SCB_ST_OK = 0,
+  SCB_ST_ERR_UNKNOWN = 1,
+  SCB_ST_ERR_FAIL_CONTROLLABLE = 2,
+  SCB_ST_ERR_FAIL_FORWARD_PASS = 3,
+  SCB_ST_ERR_UNINITIALIZED = 4,
+  SCB_ST_ERR_FAIL_FEASIBLE = 5,
+  /* conditions the reference asserts on or throws for (sc:34-52 SC_ASSERT; tp:constraint/
+   * linear_joint_velocity.cpp:54; tp:solver.cpp:36-37) */
+  SCB_ST_ERR_BAD_PATH = 16,     /* non-finite waypoint, zero-length leg, or arclength <= 0 */
+  SCB_ST_ERR_BAD_LIMITS = 17,   /* velocity box excludes 0 where q'(s) = 0, or lo > hi */
+  SCB_ST_ERR_TIME_KNOTS = 18    /* a knot interval < 1e-8 s (the reference drops such knots,
+                                   tp:parametrizer/spline.cpp:25-33; unreachable for x_cap = 100) */
+};
+
+enum { SCB_FP64 = 0, SCB_FP32 = 1 };
+enum { SCB_REF_CUBIC = 0,    /* the reference's construction, sc:599-683 */
+       SCB_LAU_QUINTIC = 1 };/* Lau et al. IROS'09 sec. III-A quintic + optimiser */
+
+#define SCB_ARCLEN_SUBDIV 100 /* sub-intervals per segment (precision 0.01, sc:767) */
+#define SCB_ARCLEN_TABLE (SCB_ARCLEN_SUBDIV + 1)
+
+typedef struct scb_ctx scb_ctx;
+
+typedef struct scb_config {
+  int32_t device;         /* CUDA ordinal */
+  int32_t precision;      /* SCB_FP64 | SCB_FP32 */
+  int32_t spline_mode;    /* SCB_REF_CUBIC | SCB_LAU_QUINTIC */
+  int32_t max_problems;   /* capacities used to size device scratch and staging buffers */
+  int32_t max_waypoints;
+  int32_t max_gridpoints;
+  int32_t max_samples;    /* S_cap of the uniform-dt stream; 0 = stream never requested */
+} scb_config;
+
+/* Optimiser options (LAU_QUINTIC only; DESIGN.md "A6/A7").  iters = 0 disables it. */
+typedef struct scb_opt {
+  int32_t iters;            /* K: fixed RPROP iteration budget */
+  int32_t move_waypoints;   /* 1: inner waypoints are parameters too; 0: elongations only */
+  double lambda;            /* weight of the arc-length term */
+  double e_init, e_min, e_max; /* tangent elongation factor: start value and clamp */
+  double step_e, step_w;    /* initial RPROP steps (elongation; waypoint, as a fraction of the
+                               tangent magnitude) */
+  double w_radius;          /* inner waypoints may move at most this far from their input */
+} scb_opt;
+
+/* stages of the path one call runs (scb_batch_in.stages; 0 = all three) */
+enum {
+  SCB_STAGE_SPLINE = 1,   /* from_path (+ optimiser) + arclength: wx/wy -> ctrl, arclen_*, cost */
+  SCB_STAGE_TIMING = 2,   /* gen_vel_prof: L -> status, K, x, t, v, a, T_total, s_time/pos/vel/acc.
+                             Without SCB_STAGE_SPLINE the path length is read from path_len. */
+  SCB_STAGE_GEOMETRY = 4  /* resample + angular_velocity: arc length -> px, py, omega and
+                             s_px, s_py, s_omega.  Needs SCB_STAGE_SPLINE in the same call.
+                             Without SCB_STAGE_TIMING, out->n_samples / s_pos (and s_vel, if
+                             s_omega is wanted) are INPUTS: the positions to resample at. */
+};
+
+typedef struct scb_batch_in {
+  int32_t P, W, G;          /* problems, waypoints per problem (>= 2), toppra gridpoints (>= 2;
+                               the reference's default is 101, tp:algorithm.hpp:140) */
+  const void* wx;           /* real [P][W]  waypoint x */
+  const void* wy;           /* real [P][W]  waypoint y */
+  const void* start_angle;  /* real [P] or NULL; NaN = atan2 of the first leg (sc:606-609) */
+  const void* vel_lo;       /* real [P]  velocity box (vel_lim_func, sc:1175) ... */
+  const void* vel_hi;       /* real [P] */
+  const void* vel_lo_grid;  /* real [G][P] or NULL: per-gridpoint limits replace vel_lo/vel_hi */
+  const void* vel_hi_grid;  /* real [G][P] or NULL */
+  const void* acc_lo;       /* real [P]  acc_min */
+  const void* acc_hi;       /* real [P]  acc_max */
+  const void* vel_start;    /* real [P] or NULL (= 0): q'(0) of the Hermite path (sc:1213-1222) */
+  const void* vel_end;      /* real [P] or NULL (= 0) */
+  const void* path_len;     /* real [P]: pos_end - pos_start, read only when SCB_STAGE_SPLINE is off */
+  int32_t stages;           /* SCB_STAGE_* bitmask; 0 = all */
+  double x_cap;             /* upper bound of sdot^2 in the backward pass; 0 = reference's 100
+                               (tp:algorithm.hpp:152 m_initXBound) */
+  double dt;                /* uniform-dt stream period; 0 = reference's 0.02 (sc:1199) */
+  scb_opt opt;
+} scb_batch_in;
+
+typedef struct scb_batch_out {
+  int32_t* status;          /* [P] */
+  int32_t* fail_stage;      /* [P]  -1 when status is OK */
+  void* ctrl_x;             /* real [P][(W-1)*(d+1)]  d = 3 (REF_CUBIC) or 5 (LAU_QUINTIC) */
+  void* ctrl_y;
+  void* arclen_total;       /* real [P]  L */
+  void* arclen_table;       /* real [P][(W-1)*SCB_ARCLEN_TABLE] cumulative length per segment */
+  void* T_total;            /* real [P]  duration */
+  void* cost;               /* real [P]  J after the optimiser (quintic) / J of the cubic */
+  /* one record per toppra gridpoint, [G][P] each */
+  void* K_lo; void* K_hi;   /* controllable sets */
+  void* x;                  /* parametrization sdot^2 */
+  void* t;                  /* knot times (trapezoid rule) */
+  void* px; void* py;       /* curve point at arc length q(s_i) */
+  void* v; void* a;         /* dq/dt, d2q/dt2 of the parametrizer spline at t_i */
+  void* omega;              /* v * curvature */
+  /* uniform-dt stream (what gen_vel_prof + resample + angular_velocity return), [S_cap][P] */
+  int32_t S_cap;
+  int32_t* n_samples;       /* [P]  ceil(T/dt) (sc:1237); entries beyond S_cap are not written */
+  void* s_time; void* s_pos; void* s_vel; void* s_acc; void* s_px; void* s_py; void* s_omega;
+} scb_batch_out;
+
+/* per-stage device time of the last scb_plan_batch* call on this ctx, milliseconds */
+typedef struct scb_timing {
+  float h2d_ms, spline_ms, toppra_ms, param_ms, sample_ms, d2h_ms, total_ms;
+  int32_t launches;         /* kernels launched by that call */
+} scb_timing;
+
+int scb_version(void);
+const char* scb_strerror(int code);
+void scb_default_opt(scb_opt* opt);
+
+int scb_create(scb_ctx** out, const scb_config* cfg);
+int scb_destroy(scb_ctx* ctx);
+
+/* Host buffers in, host buffers out: H2D copy, kernels, D2H copy, synchronous. */
+int scb_plan_batch(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out);
+
+/* Device buffers in and out (already resident in HBM); enqueued on the ctx stream and
+ * synchronised before returning unless `async` is non-zero. */
+int scb_plan_batch_device(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, int async);
+int scb_synchronize(scb_ctx* ctx);
+
+int scb_get_timing(scb_ctx* ctx, scb_timing* out);
+const char* scb_last_cuda_error(scb_ctx* ctx);
+/* the cudaStream_t the ctx launches on (so a caller can order its own work / CUDA events) */
+void* scb_stream(scb_ctx* ctx);
+/* algorithmic bytes one launch over this batch must move (SURVEY 8-D4 formula) */
+int64_t scb_algorithmic_bytes(int32_t precision, int32_t spline_mode, int32_t P, int32_t W, int32_t G);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SEACURRENT_B200_H */

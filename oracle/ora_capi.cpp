@@ -1,0 +1,288 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY.  C entry points over the header-only oracle so that
+// tests/ (ctypes), __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs
+// can call it.  Never linked into libseacurrent_b200.so.
+#include <chrono>
+#include <cstring>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+#include "../include/seacurrent_b200.h"
+#include "ora_plan.hpp"
+
+using namespace ora;
+
+extern "C" {
+
+int ora_num_threads(void) {
+#ifdef _OPENMP
+  return omp_get_max_threads();
+#else
+  return 1;
+#endif
+}
+
+// ---------------------------------------------------------------- Seidel (test_solver.cpp)
+int ora_lp1d(double v0, double v1, const double* A, int n, double* optvar) {
+  std::vector<std::array<double, 2>> a(n);
+  for (int i = 0; i < n; ++i) a[i] = {A[2 * i], A[2 * i + 1]};
+  tp::LpSol1d s = tp::solve_lp1d(v0, v1, a, n);
+  *optvar = s.optvar;
+  return s.feasible ? 1 : 0;
+}
+
+int ora_lp2d(const double* v, const double* A, int n, const double* low, const double* high, double* optvar,
+             int* active) {
+  std::vector<std::array<double, 3>> a(n);
+  for (int i = 0; i < n; ++i) a[i] = {A[3 * i], A[3 * i + 1], A[3 * i + 2]};
+  tp::LpSol s = tp::solve_lp2d(v, a, low, high);
+  optvar[0] = s.optvar[0]; optvar[1] = s.optvar[1];
+  if (active) { active[0] = s.active_c[0]; active[1] = s.active_c[1]; }
+  return s.feasible ? 1 : 0;
+}
+
+// ---------------------------------------------------------------- generic toppra problem
+// coeffs: [nseg][4][dof] (row 0 multiplies ds^3), breaks [nseg+1].  Constant velocity and
+// acceleration boxes.  Outputs K [G][2], x [G], feas [G][2] (any may be null).
+// Returns the ReturnCode of computePathParametrization; *feas_rc that of computeFeasibleSets.
+int ora_toppra_ppoly(int nseg, int dof, const double* coeffs, const double* breaks, int G, const double* vel_lo,
+                     const double* vel_hi, const double* acc_lo, const double* acc_hi, int interpolation,
+                     double sd_start, double sd_end, double* K, double* x, double* feas, int* feas_rc) {
+  tp::Problem pb;
+  pb.path.breaks.assign(breaks, breaks + nseg + 1);
+  for (int s = 0; s < nseg; ++s) {
+    std::vector<tp::Vec> c(4, tp::Vec(dof));
+    for (int r = 0; r < 4; ++r) for (int k = 0; k < dof; ++k) c[r][k] = coeffs[((size_t)s * 4 + r) * dof + k];
+    pb.path.c0.push_back(c);
+  }
+  pb.path.finish();
+  pb.gridpoints = tp::linspaced(G, breaks[0], breaks[nseg]);
+  tp::Vec vl(vel_lo, vel_lo + dof), vh(vel_hi, vel_hi + dof);
+  pb.vel_lim = [vl, vh](double, tp::Vec& lo, tp::Vec& hi) { lo = vl; hi = vh; };
+  pb.acc_lo.assign(acc_lo, acc_lo + dof); pb.acc_hi.assign(acc_hi, acc_hi + dof);
+  pb.interpolation = interpolation != 0;
+  tp::ParamData d = tp::compute_path_parametrization(pb, sd_start, sd_end);
+  for (int i = 0; i < G; ++i) {
+    if (K && i < (int)d.controllable_sets.size()) { K[2 * i] = d.controllable_sets[i][0]; K[2 * i + 1] = d.controllable_sets[i][1]; }
+    if (x && i < (int)d.parametrization.size()) x[i] = d.parametrization[i];
+  }
+  if (feas) {
+    tp::Stages st = tp::build_stages(pb);
+    tp::ParamData f;
+    const int rc = tp::compute_feasible_sets(st, f);
+    if (feas_rc) *feas_rc = rc;
+    for (int i = 0; i < G; ++i) { feas[2 * i] = f.feasible_sets[i][0]; feas[2 * i + 1] = f.feasible_sets[i][1]; }
+  }
+  return d.ret_code;
+}
+
+// Spline parametrizer over a generic ppoly path (test_spline_parametrizer.cpp): returns the
+// knot times ts [G] and evaluates q(t), q'(t) at `n_eval` times.  solve_mode 0 dense QR, 1 Thomas.
+int ora_spline_param(int nseg, int dof, const double* coeffs, const double* breaks, int G, const double* gridpoints,
+                     const double* vsq, int solve_mode, double* ts, int n_eval, const double* t_eval, double* q,
+                     double* qd, double* qdd) {
+  tp::PPoly path;
+  path.breaks.assign(breaks, breaks + nseg + 1);
+  for (int s = 0; s < nseg; ++s) {
+    std::vector<tp::Vec> c(4, tp::Vec(dof));
+    for (int r = 0; r < 4; ++r) for (int k = 0; k < dof; ++k) c[r][k] = coeffs[((size_t)s * 4 + r) * dof + k];
+    path.c0.push_back(c);
+  }
+  path.finish();
+  tp::Vec gp(gridpoints, gridpoints + G), v(vsq, vsq + G);
+  tp::SplineParam sp = tp::spline_parametrizer(path, gp, v, solve_mode);
+  for (size_t i = 0; i < sp.ts.size(); ++i) ts[i] = sp.ts[i];
+  for (int i = 0; i < n_eval; ++i) {
+    tp::Vec a = sp.traj.eval_single(t_eval[i], 0), b = sp.traj.eval_single(t_eval[i], 1), c = sp.traj.eval_single(t_eval[i], 2);
+    for (int k = 0; k < dof; ++k) { q[i * dof + k] = a[k]; qd[i * dof + k] = b[k]; if (qdd) qdd[i * dof + k] = c[k]; }
+  }
+  return (int)sp.ts.size();
+}
+
+// Clamped cubic spline through (t_i, y_i) with end slopes (test_cubic_spline*.cpp vs scipy).
+void ora_cubic_spline(int n, const double* t, const double* y, double bc0, double bc1, int solve_mode, int n_eval,
+                      const double* t_eval, double* out) {
+  std::vector<tp::Vec> pos(n);
+  for (int i = 0; i < n; ++i) pos[i] = {y[i]};
+  tp::PPoly p = tp::cubic_spline_clamped(pos, tp::Vec(t, t + n), {bc0}, {bc1}, solve_mode);
+  for (int i = 0; i < n_eval; ++i) out[i] = p.eval_single(t_eval[i], 0)[0];
+}
+
+// Hermite path eval (test_hermite_spline.cpp)
+void ora_hermite_eval(int n, int dof, const double* pos, const double* vel, const double* times, int n_eval,
+                      const double* s_eval, int order, double* out) {
+  std::vector<tp::Vec> P(n), V(n);
+  for (int i = 0; i < n; ++i) { P[i].assign(pos + i * dof, pos + (i + 1) * dof); V[i].assign(vel + i * dof, vel + (i + 1) * dof); }
+  tp::PPoly p = tp::PPoly::hermite(P, V, tp::Vec(times, times + n));
+  for (int i = 0; i < n_eval; ++i) { tp::Vec r = p.eval_single(s_eval[i], order); for (int k = 0; k < dof; ++k) out[i * dof + k] = r[k]; }
+}
+
+// ---------------------------------------------------------------- reference-faithful E1 (float32 spline side)
+// examples/json_test.cpp:28-58 / zmq_test.cpp:64-92 body: from_path -> arclength ->
+// gen_vel_prof<1> -> resample -> angular_velocity, with the reference's arithmetic types.
+// mode bit 0: dense 10,001-point preview sampling of every segment (sc:679);
+// mode bit 1: Bernstein-Fourier evaluation with complex pow (sc:721-748), else de Casteljau;
+// mode bit 2: dense column-pivoted QR in the parametrizer (tp:...piecewise_poly_path.cpp:162),
+//             else Thomas ("restated-fast").
+struct E1Out {
+  Spline<float> sp; ArclengthData<float> ad; tp::VelocityProfile prof; Resampled<float> rs; std::vector<float> angvel;
+};
+static E1Out e1_reference(const float* wx, const float* wy, int W, float start_angle, double vel_lo, double vel_hi,
+                          double acc_lo, double acc_hi, int N, float dt, int mode) {
+  E1Out o;
+  std::vector<V2<float>> path(W);
+  for (int i = 0; i < W; ++i) path[i] = {wx[i], wy[i]};
+  const int ev = (mode & 2) ? EVAL_BF : EVAL_DC;
+  o.sp = from_path(path, start_angle, (mode & 1) != 0, ev);
+  o.ad = arclength(o.sp, 0.01f, ev);
+  tp::VelLimFn lim = [vel_lo, vel_hi](double, tp::Vec& lo, tp::Vec& hi) { lo[0] = vel_lo; hi[0] = vel_hi; };
+  o.prof = tp::gen_vel_prof((double)o.ad.arclength, 0.0, 0.0, 0.0, lim, acc_lo, acc_hi, dt, N,
+                            (mode & 4) ? tp::SOLVE_DENSE_QR : tp::SOLVE_THOMAS);
+  if (o.prof.pd.ret_code != tp::OK) return o;
+  std::vector<float> pos = o.prof.pos;
+  o.rs = resample(o.sp, pos, o.ad, true, ev);
+  std::vector<float> curv = curvature(o.sp, o.rs, ev);
+  std::vector<float> vel(o.prof.vel.begin(), o.prof.vel.begin() + std::min(o.prof.vel.size(), curv.size()));
+  curv.resize(vel.size());
+  o.angvel = angular_velocity(curv, vel);
+  return o;
+}
+
+// Single problem, all outputs (fixture test).  Buffers sized by the caller: ctrl 8*(W-1)
+// floats (x,y interleaved per control point), tables (W-1)*101, streams cap entries.
+int ora_e1_single(const float* wx, const float* wy, int W, float start_angle, double vel_lo, double vel_hi,
+                  double acc_lo, double acc_hi, int N, float dt, int mode, float* ctrl, float* tables, float* total,
+                  int cap, int* n_samples, double* time, float* pos, float* vel, float* acc, float* px, float* py,
+                  float* angvel, int* n_resampled) {
+  E1Out o = e1_reference(wx, wy, W, start_angle, vel_lo, vel_hi, acc_lo, acc_hi, N, dt, mode);
+  for (int s = 0; s + 1 < W; ++s) for (int j = 0; j < 4; ++j) { ctrl[(s * 4 + j) * 2] = o.sp.ctrl[s][j].x; ctrl[(s * 4 + j) * 2 + 1] = o.sp.ctrl[s][j].y; }
+  for (int s = 0; s + 1 < W; ++s) for (int k = 0; k < 101; ++k) tables[s * 101 + k] = o.ad.segments[s][k];
+  *total = o.ad.arclength;
+  const int S = (int)o.prof.time.size();
+  *n_samples = S;
+  for (int i = 0; i < std::min(S, cap); ++i) { time[i] = o.prof.time[i]; pos[i] = o.prof.pos[i]; vel[i] = o.prof.vel[i]; acc[i] = o.prof.acc[i]; }
+  const int Rn = (int)o.rs.pts.size();
+  *n_resampled = Rn;
+  for (int i = 0; i < std::min(Rn, cap); ++i) { px[i] = o.rs.pts[i].x; py[i] = o.rs.pts[i].y; angvel[i] = i < (int)o.angvel.size() ? o.angvel[i] : 0.f; }
+  return o.prof.pd.ret_code;
+}
+
+// Timed CPU baseline ("port" of the reference's E1 body), OpenMP over problems.
+// wx/wy [P][W] float; limits [P] double.  Returns elapsed seconds; *checksum defeats DCE.
+double ora_e1_batch_time(int P, int W, const float* wx, const float* wy, const double* vel_lo, const double* vel_hi,
+                         const double* acc_lo, const double* acc_hi, int N, float dt, int mode, int nthreads,
+                         double* checksum) {
+  double sum = 0;
+  auto t0 = std::chrono::steady_clock::now();
+#ifdef _OPENMP
+  if (nthreads > 0) omp_set_num_threads(nthreads);
+#endif
+#pragma omp parallel for schedule(dynamic) reduction(+ : sum)
+  for (int p = 0; p < P; ++p) {
+    E1Out o = e1_reference(wx + (size_t)p * W, wy + (size_t)p * W, W, NAN, vel_lo[p], vel_hi[p], acc_lo[p], acc_hi[p], N, dt, mode);
+    sum += o.ad.arclength + (o.prof.time.empty() ? 0.0 : o.prof.time.back()) + (o.angvel.empty() ? 0.f : o.angvel[o.angvel.size() / 2]);
+  }
+  auto t1 = std::chrono::steady_clock::now();
+  if (checksum) *checksum = sum;
+  return std::chrono::duration<double>(t1 - t0).count();
+}
+
+// ---------------------------------------------------------------- Lau stages (property tests)
+// Evaluate the quintic built from (Wp, e) over the model frozen at `path`: control points
+// [(W-1)*6*2], cost J, gradients ge [W], gW [W*2].
+double ora_lau_eval(const double* path_xy, int W, double start_angle, const double* Wp_xy, const double* e, double lambda,
+                    double* ctrl, double* ge, double* gW) {
+  std::vector<V2<double>> path(W), Wp(W);
+  for (int i = 0; i < W; ++i) { path[i] = {path_xy[2 * i], path_xy[2 * i + 1]}; Wp[i] = {Wp_xy[2 * i], Wp_xy[2 * i + 1]}; }
+  LauModel<double> m = lau_model(path, start_angle);
+  std::vector<double> ev(e, e + W);
+  Spline<double> sp = lau_build(m, Wp, ev);
+  std::vector<std::vector<V2<double>>> g;
+  const double J = lau_cost_grad(sp, lambda, &g);
+  std::vector<V2<double>> gw; std::vector<double> gee;
+  lau_backprop(m, g, gw, gee);
+  for (int s = 0; s + 1 < W; ++s) for (int j = 0; j < 6; ++j) { if (ctrl) { ctrl[(s * 6 + j) * 2] = sp.ctrl[s][j].x; ctrl[(s * 6 + j) * 2 + 1] = sp.ctrl[s][j].y; } }
+  for (int i = 0; i < W; ++i) { if (ge) ge[i] = gee[i]; if (gW) { gW[2 * i] = gw[i].x; gW[2 * i + 1] = gw[i].y; } }
+  return J;
+}
+
+// Run the optimiser; history gets iters+1 costs.  Returns the best cost.
+double ora_lau_optimise(const double* path_xy, int W, double start_angle, const scb_opt* opt, double* ctrl, double* e_out,
+                        double* history) {
+  std::vector<V2<double>> path(W);
+  for (int i = 0; i < W; ++i) path[i] = {path_xy[2 * i], path_xy[2 * i + 1]};
+  LauOpt o;
+  o.iters = opt->iters; o.move_waypoints = opt->move_waypoints; o.lambda = opt->lambda; o.e_init = opt->e_init;
+  o.e_min = opt->e_min; o.e_max = opt->e_max; o.step_e = opt->step_e; o.step_w = opt->step_w; o.w_radius = opt->w_radius;
+  LauResult<double> r = lau_optimise(lau_model(path, start_angle), o);
+  for (int s = 0; s + 1 < W; ++s) for (int j = 0; j < 6; ++j) { ctrl[(s * 6 + j) * 2] = r.spline.ctrl[s][j].x; ctrl[(s * 6 + j) * 2 + 1] = r.spline.ctrl[s][j].y; }
+  for (int i = 0; i < W; ++i) if (e_out) e_out[i] = r.e[i];
+  for (size_t i = 0; i < r.history.size(); ++i) if (history) history[i] = r.history[i];
+  return r.cost;
+}
+
+// ---------------------------------------------------------------- the product's batch, on the CPU
+// Same structs and layouts as scb_plan_batch (FP64 host buffers).  solve_mode: 0 dense QR
+// (reference), 1 Thomas.  Returns elapsed seconds through *seconds.
+int ora_plan_batch(const scb_batch_in* in, const scb_batch_out* out, int spline_mode, int solve_mode, int nthreads,
+                   double* seconds) {
+  const int P = in->P, W = in->W, G = in->G;
+  const double *wx = (const double*)in->wx, *wy = (const double*)in->wy, *sa = (const double*)in->start_angle;
+  const double *vlo = (const double*)in->vel_lo, *vhi = (const double*)in->vel_hi;
+  const double *vlg = (const double*)in->vel_lo_grid, *vhg = (const double*)in->vel_hi_grid;
+  const double *alo = (const double*)in->acc_lo, *ahi = (const double*)in->acc_hi;
+  const double *vs = (const double*)in->vel_start, *ve = (const double*)in->vel_end;
+  const int d = spline_mode == 0 ? 3 : 5, nc = (W - 1) * (d + 1), S_cap = out->S_cap;
+  auto t0 = std::chrono::steady_clock::now();
+#ifdef _OPENMP
+  if (nthreads > 0) omp_set_num_threads(nthreads);
+#endif
+#pragma omp parallel for schedule(dynamic)
+  for (int p = 0; p < P; ++p) {
+    PlanIn pi;
+    pi.path.resize(W);
+    for (int i = 0; i < W; ++i) pi.path[i] = {wx[(size_t)p * W + i], wy[(size_t)p * W + i]};
+    pi.start_angle = sa ? sa[p] : NAN;
+    std::vector<double> gl, gh;
+    if (vlg && vhg) {
+      gl.resize(G); gh.resize(G);
+      for (int i = 0; i < G; ++i) { gl[i] = vlg[(size_t)i * P + p]; gh[i] = vhg[(size_t)i * P + p]; }
+      pi.vel_lo_grid = gl.data(); pi.vel_hi_grid = gh.data();
+    } else { pi.vel_lo = vlo[p]; pi.vel_hi = vhi[p]; }
+    pi.acc_lo = alo[p]; pi.acc_hi = ahi[p];
+    pi.vel_start = vs ? vs[p] : 0.0; pi.vel_end = ve ? ve[p] : 0.0;
+    pi.G = G;
+    pi.x_cap = in->x_cap > 0 ? in->x_cap : 100.0;
+    pi.dt = in->dt > 0 ? in->dt : (double)0.02f;
+    pi.spline_mode = spline_mode;
+    pi.opt.iters = in->opt.iters; pi.opt.move_waypoints = in->opt.move_waypoints; pi.opt.lambda = in->opt.lambda;
+    pi.opt.e_init = in->opt.e_init; pi.opt.e_min = in->opt.e_min; pi.opt.e_max = in->opt.e_max;
+    pi.opt.step_e = in->opt.step_e; pi.opt.step_w = in->opt.step_w; pi.opt.w_radius = in->opt.w_radius;
+    pi.solve_mode = solve_mode;
+    pi.S_cap = S_cap;
+    PlanOut o = plan_one(pi);
+    if (out->status) out->status[p] = o.status;
+    if (out->fail_stage) out->fail_stage[p] = o.fail_stage;
+    auto put = [&](void* dst, size_t idx, double v) { if (dst) ((double*)dst)[idx] = v; };
+    for (int k = 0; k < nc; ++k) {
+      put(out->ctrl_x, (size_t)p * nc + k, k < (int)o.ctrl_x.size() ? o.ctrl_x[k] : 0.0);
+      put(out->ctrl_y, (size_t)p * nc + k, k < (int)o.ctrl_y.size() ? o.ctrl_y[k] : 0.0);
+    }
+    put(out->arclen_total, p, o.L); put(out->T_total, p, o.T); put(out->cost, p, o.cost);
+    const int nt = (W - 1) * SCB_ARCLEN_TABLE;
+    for (int k = 0; k < nt; ++k) put(out->arclen_table, (size_t)p * nt + k, k < (int)o.table.size() ? o.table[k] : 0.0);
+    auto grid = [&](void* dst, const std::vector<double>& v) { if (dst) for (int i = 0; i < G; ++i) ((double*)dst)[(size_t)i * P + p] = i < (int)v.size() ? v[i] : 0.0; };
+    grid(out->K_lo, o.K_lo); grid(out->K_hi, o.K_hi); grid(out->x, o.x); grid(out->t, o.t);
+    grid(out->px, o.px); grid(out->py, o.py); grid(out->v, o.v); grid(out->a, o.a); grid(out->omega, o.omega);
+    if (S_cap > 0) {
+      if (out->n_samples) out->n_samples[p] = o.n_samples;
+      auto strm = [&](void* dst, const std::vector<double>& v) { if (dst) for (int i = 0; i < S_cap; ++i) ((double*)dst)[(size_t)i * P + p] = i < (int)v.size() ? v[i] : 0.0; };
+      strm(out->s_time, o.s_time); strm(out->s_pos, o.s_pos); strm(out->s_vel, o.s_vel); strm(out->s_acc, o.s_acc);
+      strm(out->s_px, o.s_px); strm(out->s_py, o.s_py); strm(out->s_omega, o.s_omega);
+    }
+  }
+  auto t1 = std::chrono::steady_clock::now();
+  if (seconds) *seconds = std::chrono::duration<double>(t1 - t0).count();
+  return 0;
+}
+
+}  // extern "C"

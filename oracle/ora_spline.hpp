@@ -154,7 +154,25 @@ template <class R> struct Spline {
   int n_segments() const { return (int)ctrl.size(); }
 };
 
-enum EvalMode { EVAL_BF = 0, EVAL_DC = 1 };
+enum EvalMode { EVAL_BF = 0, EVAL_DC = 1, EVAL_POW = 2 };
+
+// Power-basis form of the same polynomial, a_k = C(n,k) * (k-th forward difference of P at 0),
+// evaluated by Horner.  This is the arithmetic the CUDA kernels use.
+template <class R> inline void bezier_power_coeffs(const V2<R>* ctrl, int degree, V2<R>* a) {
+  V2<R> d[8];
+  for (int i = 0; i <= degree; ++i) d[i] = ctrl[i];
+  R binom = 1;
+  for (int k = 0; k <= degree; ++k) {
+    a[k] = binom * d[0];
+    for (int j = 0; j + k < degree; ++j) d[j] = d[j + 1] - d[j];
+    binom = binom * (R)(degree - k) / (R)(k + 1);
+  }
+}
+template <class R> inline V2<R> horner(const V2<R>* a, int degree, R u) {
+  V2<R> v = a[degree];
+  for (int k = degree - 1; k >= 0; --k) v = {v.x * u + a[k].x, v.y * u + a[k].y};
+  return v;
+}
 
 template <class R>
 inline void eval_curve(const std::vector<V2<R>>& ctrl, const std::vector<R>& pos, int mode,
@@ -166,6 +184,10 @@ inline void eval_curve(const std::vector<V2<R>>& ctrl, const std::vector<R>& pos
     bf_coefficients(ctrl, Qx, Qy);
     auto om = omega_table<R>(deg);
     for (size_t i = 0; i < pos.size(); ++i) out[i] = bezier_point_bf(Qx, Qy, om, deg, pos[i]);
+  } else if (mode == EVAL_POW) {
+    V2<R> a[8];
+    bezier_power_coeffs(ctrl.data(), deg, a);
+    for (size_t i = 0; i < pos.size(); ++i) out[i] = horner(a, deg, pos[i]);
   } else {
     for (size_t i = 0; i < pos.size(); ++i) out[i] = bezier_point_dc(ctrl.data(), deg, pos[i]);
   }

@@ -1,0 +1,334 @@
+// Parametrizer + geometry on the GPU, one thread per planning problem (sm_100a).
+//
+// param_kernel   parametrizer::Spline  (tp:parametrizer/spline.cpp:10-45, tp:parametrizer.cpp:6-21):
+//                knot times by the trapezoid rule, clamped cubic spline q(t) through (t_i, q(s_i))
+//                (tp:geometric_path/piecewise_poly_path.cpp:102-187) — solved as the tridiagonal
+//                system it is (Thomas) instead of the reference's dense column-pivoted QR —
+//                then the per-gridpoint record: v, a (spline derivatives at the knots), the curve
+//                point at arc length q(s_i) and omega = v * kappa (sea_current.hpp:1017-1067).
+// sample_kernel  the uniform-dt stream of gen_vel_prof (sea_current.hpp:1235-1262), resample
+//                (sc:898-1005) and angular_velocity (sc:1055-1067).
+//
+// Arc length -> curve parameter is an exact inversion of the arc-length table (search + Newton
+// on a 4-point Gauss-Legendre integral of |B'|), not the reference's float Chebyshev fit
+// (DESIGN.md "Deviations").  All gridpoint / sample arrays are [n][P], problem index fastest.
+#include "scb_common.cuh"
+
+namespace scb {
+
+__device__ __constant__ double kGL4X[4] = {-0.8611363115940525752, -0.3399810435848562648, 0.3399810435848562648,
+                                           0.8611363115940525752};
+__device__ __constant__ double kGL4W[4] = {0.3478548451374538574, 0.6521451548625461426, 0.6521451548625461426,
+                                           0.3478548451374538574};
+
+// Power-basis form of one Bezier segment: a_k = C(d,k) * (k-th forward difference of P at 0).
+template <class R, int DEG> struct SegPoly {
+  R ax[DEG + 1], ay[DEG + 1];
+  __device__ __forceinline__ void load(const R* __restrict__ cx, const R* __restrict__ cy) {
+    R dx[DEG + 1], dy[DEG + 1];
+#pragma unroll
+    for (int i = 0; i <= DEG; ++i) { dx[i] = cx[i]; dy[i] = cy[i]; }
+    R binom = 1;
+#pragma unroll
+    for (int k = 0; k <= DEG; ++k) {
+      ax[k] = binom * dx[0]; ay[k] = binom * dy[0];
+#pragma unroll
+      for (int j = 0; j + k < DEG; ++j) { dx[j] = dx[j + 1] - dx[j]; dy[j] = dy[j + 1] - dy[j]; }
+      binom = binom * (R)(DEG - k) / (R)(k + 1);
+    }
+  }
+  __device__ __forceinline__ void d1(R u, R& x, R& y) const {
+    x = (R)DEG * ax[DEG]; y = (R)DEG * ay[DEG];
+#pragma unroll
+    for (int k = DEG - 2; k >= 0; --k) { x = x * u + (R)(k + 1) * ax[k + 1]; y = y * u + (R)(k + 1) * ay[k + 1]; }
+  }
+  __device__ __forceinline__ R speed(R u) const { R x, y; d1(u, x, y); return sqrt(x * x + y * y); }
+  __device__ __forceinline__ void eval(R u, R& px, R& py, R& kappa) const {
+    px = ax[DEG]; py = ay[DEG];
+#pragma unroll
+    for (int k = DEG - 1; k >= 0; --k) { px = px * u + ax[k]; py = py * u + ay[k]; }
+    R x1, y1; d1(u, x1, y1);
+    // B'' coefficients: (k+1) * [(k+2) a_{k+2}]
+    R x2 = (R)(DEG - 1) * ((R)DEG * ax[DEG]), y2 = (R)(DEG - 1) * ((R)DEG * ay[DEG]);
+#pragma unroll
+    for (int k = DEG - 3; k >= 0; --k) {
+      x2 = x2 * u + (R)(k + 1) * ((R)(k + 2) * ax[k + 2]);
+      y2 = y2 * u + (R)(k + 1) * ((R)(k + 2) * ay[k + 2]);
+    }
+    const R n2 = x1 * x1 + y1 * y1;
+    kappa = (x1 * y2 - y1 * x2) / (n2 * sqrt(n2));  // sc:1029
+  }
+};
+
+// Walks the arc-length table of one problem: arc length q -> (segment, u) -> point, curvature.
+template <class R, int DEG> struct ArcWalker {
+  const R* cx; const R* cy; const R* table;  // this problem's rows
+  int nseg, seg, k;
+  R seg_start, seg_end, total;
+  SegPoly<R, DEG> poly;
+  __device__ __forceinline__ void set_segment(int s) {
+    seg = s;
+    R acc = 0;
+    for (int j = 0; j < s; ++j) acc += table[j * kTable + kSub];
+    seg_start = acc; seg_end = acc + table[s * kTable + kSub];
+    poly.load(cx + s * (DEG + 1), cy + s * (DEG + 1));
+    k = 0;
+  }
+  __device__ __forceinline__ void init(const R* cx_, const R* cy_, const R* table_, int nseg_) {
+    cx = cx_; cy = cy_; table = table_; nseg = nseg_;
+    R acc = 0;
+    for (int j = 0; j < nseg; ++j) acc += table[j * kTable + kSub];
+    total = acc;
+    set_segment(0);
+  }
+  __device__ __forceinline__ void locate(R q, R& px, R& py, R& kappa) {
+    q = fmin(fmax(q, (R)0), total);
+    if (q > seg_end) {
+      while (seg < nseg - 1 && q > seg_end) {  // forward: cumulative sums continue exactly
+        ++seg; seg_start = seg_end; seg_end = seg_start + table[seg * kTable + kSub];
+      }
+      poly.load(cx + seg * (DEG + 1), cy + seg * (DEG + 1)); k = 0;
+    } else if (seg > 0 && q <= seg_start) {
+      int s = seg;
+      R st = seg_start;
+      // backward: recompute the prefix so it equals the forward cumulative sum bit for bit
+      while (s > 0 && q <= st) { --s; st = 0; for (int j = 0; j < s; ++j) st += table[j * kTable + kSub]; }
+      set_segment(s);
+    }
+    const R r = q - seg_start;
+    const R* c = table + seg * kTable;
+    while (k < kSub - 1 && c[k + 1] <= r) ++k;
+    while (k > 0 && c[k] > r) --k;
+    const R h = (R)0.01, a = fmin((R)k * h, (R)1);
+    const R ck = c[k], target = r - ck;
+    R du = h * target / (c[k + 1] - ck);
+    du = fmin(fmax(du, (R)0), h);
+#pragma unroll 1
+    for (int it = 0; it < kInvNewton; ++it) {
+      const R half = (R)0.5 * du, mid = a + half;
+      R F = 0;
+#pragma unroll
+      for (int gq = 0; gq < 4; ++gq) F += (R)kGL4W[gq] * poly.speed(mid + half * (R)kGL4X[gq]);
+      F *= half;
+      du = du - (F - target) / poly.speed(a + du);
+      du = fmin(fmax(du, (R)0), h);
+    }
+    poly.eval(fmin(a + du, (R)1), px, py, kappa);
+  }
+};
+
+template <class R> struct Hermite1 {
+  R c0, c1, c2, step; int N;
+  __device__ __forceinline__ void init(R L, R vs, R ve, int N_) {
+    c2 = vs; c0 = (ve - (R)2 * L + vs); c1 = (ve - vs - (R)3 * c0) / (R)2; N = N_; step = (R)1 / (R)N_;
+  }
+  __device__ __forceinline__ R s_at(int i) const { return i == N ? (R)1 : (R)i * step; }
+  __device__ __forceinline__ R q(R s) const { return c0 * (s * s * s) + c1 * (s * s) + c2 * s; }
+  __device__ __forceinline__ R qd(R s) const { return ((R)3 * c0) * (s * s) + ((R)2 * c1) * s + c2; }
+};
+
+template <class R, int DEG>
+__global__ void __launch_bounds__(64) param_kernel(ParamArgs g) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= g.P) return;
+  const int P = g.P, G = g.G, N = G - 1;
+  const R* X2 = (const R*)g.x;  // sdot^2
+  R* tb = (R*)g.t_buf; R* Xb = (R*)g.X_buf; R* cpb = (R*)g.cp_buf;
+  R* o_t = (R*)g.t; R* o_v = (R*)g.v; R* o_a = (R*)g.a; R* o_px = (R*)g.px; R* o_py = (R*)g.py; R* o_om = (R*)g.omega;
+  int status = g.status[p];
+  Hermite1<R> hp;
+  if (status == SCB_ST_OK) {
+    hp.init(((const R*)g.L)[p], g.vel_start ? ((const R*)g.vel_start)[p] : (R)0,
+            g.vel_end ? ((const R*)g.vel_end)[p] : (R)0, N);
+    // ---- pass 1: knot times + Thomas forward elimination
+    const R sd0 = sqrt(X2[p]);
+    R sd_prev = sd0, t = 0, t_prev = 0, t_pp = 0;
+    R q_pp = 0, q_prev = hp.q(hp.s_at(0)), s_prev = hp.s_at(0);
+    R cp_prev = 0, b_prev = 0;
+    const R bc0 = hp.qd(hp.s_at(0)) * sd0;
+    tb[p] = 0;
+    for (int i = 1; i <= N; ++i) {
+      const R s = hp.s_at(i), sd = sqrt(X2[(size_t)i * P + p]);
+      const R avg = (sd_prev + sd) / 2;
+      const R dt = avg > (R)1e-8 ? (s - s_prev) / avg : (R)5;
+      if (dt < (R)1e-8) status = SCB_ST_ERR_TIME_KNOTS;
+      t = t_prev + dt;
+      tb[(size_t)i * P + p] = t;
+      const R qi = hp.q(s);
+      const R h = t - t_prev;  // h_{i-1}
+      // row j = i - 1
+      R lo, di, up, B;
+      if (i == 1) { lo = 0; di = 2 * h; up = h; B = 3 * (qi - q_prev) / h - 3 * bc0; }
+      else {
+        const R hm = t_prev - t_pp;  // h_{i-2}
+        lo = hm; di = 2 * (hm + h); up = h;
+        B = 3 * (qi - q_prev) / h - 3 * (q_prev - q_pp) / hm;
+      }
+      R cpj, bj;
+      if (i == 1) { cpj = up / di; bj = B / di; }
+      else { const R m = di - lo * cp_prev; cpj = up / m; bj = (B - lo * b_prev) / m; }
+      cpb[(size_t)(i - 1) * P + p] = cpj; Xb[(size_t)(i - 1) * P + p] = bj;
+      cp_prev = cpj; b_prev = bj;
+      if (i == N) {  // last row j = N
+        const R bc1 = hp.qd(s) * sd;
+        const R lo2 = h, di2 = 2 * h, B2 = 3 * bc1 - 3 * (qi - q_prev) / h;
+        const R m = di2 - lo2 * cp_prev;
+        Xb[(size_t)N * P + p] = (B2 - lo2 * b_prev) / m;  // = X_N
+      }
+      t_pp = t_prev; t_prev = t; q_pp = q_prev; q_prev = qi; s_prev = s; sd_prev = sd;
+    }
+  }
+  if (status != SCB_ST_OK) {
+    if (g.status[p] == SCB_ST_OK) g.status[p] = status;
+    for (int i = 0; i < G; ++i) {
+      const size_t o = (size_t)i * P + p;
+      tb[o] = 0; Xb[o] = 0;
+      if (o_t) o_t[o] = 0; if (o_v) o_v[o] = 0; if (o_a) o_a[o] = 0;
+      if (o_px) o_px[o] = 0; if (o_py) o_py[o] = 0; if (o_om) o_om[o] = 0;
+    }
+    if (g.T_total) ((R*)g.T_total)[p] = 0;
+    return;
+  }
+  // ---- pass 2 (backward): back substitution, knot derivatives, geometry
+  ArcWalker<R, DEG> walk;
+  const bool geo = g.geometry != 0;
+  if (geo) {
+    const int nseg = g.W - 1;
+    walk.init((const R*)g.ctrl_x + (size_t)p * nseg * (DEG + 1), (const R*)g.ctrl_y + (size_t)p * nseg * (DEG + 1),
+              (const R*)g.table + (size_t)p * nseg * kTable, nseg);
+  }
+  R X_next = Xb[(size_t)N * P + p];
+  R t_next = tb[(size_t)N * P + p];
+  R q_next = hp.q(hp.s_at(N));
+  if (g.T_total) ((R*)g.T_total)[p] = t_next - tb[p];
+  for (int i = N; i >= 0; --i) {
+    const size_t o = (size_t)i * P + p;
+    R vi, ai, qi;
+    if (i == N) {
+      // knot N is evaluated on the last segment at ds = h (piecewise_poly_path.cpp:240-252)
+      const R Xi = Xb[(size_t)(N - 1) * P + p] - cpb[(size_t)(N - 1) * P + p] * X_next;
+      const R ti = tb[(size_t)(N - 1) * P + p];
+      const R qm = hp.q(hp.s_at(N - 1));
+      const R h = t_next - ti;
+      const R k0 = (X_next - Xi) / (3 * h), k1 = Xi, k2 = (q_next - qm) / h - h / 3 * (2 * Xi + X_next);
+      vi = (k0 * 3) * (h * h) + (k1 * 2) * h + k2;
+      ai = ((k0 * 3) * 2) * h + k1 * 2;
+      qi = q_next;
+    } else {
+      const R Xi = Xb[o] - cpb[o] * X_next;
+      Xb[o] = Xi;
+      const R ti = tb[o], qv = hp.q(hp.s_at(i));
+      const R h = t_next - ti;
+      vi = (q_next - qv) / h - h / 3 * (2 * Xi + X_next);
+      ai = Xi * 2;
+      qi = qv;
+      X_next = Xi; t_next = ti; q_next = qv;
+    }
+    if (o_t) o_t[o] = tb[o];
+    if (o_v) o_v[o] = vi;
+    if (o_a) o_a[o] = ai;
+    if (geo) {
+      R px, py, kap;
+      walk.locate(qi, px, py, kap);
+      if (o_px) o_px[o] = px;
+      if (o_py) o_py[o] = py;
+      if (o_om) o_om[o] = vi * kap;
+    }
+  }
+}
+
+template <class R, int DEG>
+__global__ void __launch_bounds__(64) sample_kernel(SampleArgs g) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= g.P) return;
+  const int P = g.P, N = g.G - 1, S_cap = g.S_cap;
+  R* o_time = (R*)g.s_time; R* o_pos = (R*)g.s_pos; R* o_vel = (R*)g.s_vel; R* o_acc = (R*)g.s_acc;
+  R* o_px = (R*)g.s_px; R* o_py = (R*)g.s_py; R* o_om = (R*)g.s_omega;
+  const bool ok = g.status[p] == SCB_ST_OK;
+  int n = 0;
+  if (ok) {
+    ArcWalker<R, DEG> walk;
+    const bool geo = g.geometry != 0;
+    if (geo) {
+      const int nseg = g.W - 1;
+      walk.init((const R*)g.ctrl_x + (size_t)p * nseg * (DEG + 1), (const R*)g.ctrl_y + (size_t)p * nseg * (DEG + 1),
+                (const R*)g.table + (size_t)p * nseg * kTable, nseg);
+    }
+    if (g.timing) {
+      const R* tb = (const R*)g.t_buf; const R* Xb = (const R*)g.X_buf;
+      Hermite1<R> hp;
+      hp.init(((const R*)g.L)[p], g.vel_start ? ((const R*)g.vel_start)[p] : (R)0,
+              g.vel_end ? ((const R*)g.vel_end)[p] : (R)0, N);
+      const R t0 = tb[p], T = tb[(size_t)N * P + p];
+      const int S = (int)ceil((double)(T - t0) / g.dt);  // sc:1237
+      g.n_samples[p] = S;
+      n = S < S_cap ? S : S_cap;
+      const R stp = S > 1 ? (T - t0) / (R)(S - 1) : (R)0;
+      int j = -1;
+      R tj = 0, k0 = 0, k1 = 0, k2 = 0, k3 = 0, t_up = t0;
+      for (int i = 0; i < n; ++i) {
+        const R time = (i == S - 1) ? T : t0 + (R)i * stp;  // Eigen LinSpaced
+        if (j < 0 || (j < N - 1 && t_up <= time)) {
+          if (j < 0) j = 0;
+          while (j < N - 1 && tb[(size_t)(j + 1) * P + p] <= time) ++j;
+          tj = tb[(size_t)j * P + p]; t_up = tb[(size_t)(j + 1) * P + p];
+          const R Xj = Xb[(size_t)j * P + p], Xn = Xb[(size_t)(j + 1) * P + p];
+          const R qj = hp.q(hp.s_at(j)), qn = hp.q(hp.s_at(j + 1));
+          const R h = t_up - tj;
+          k0 = (Xn - Xj) / (3 * h); k1 = Xj; k2 = (qn - qj) / h - h / 3 * (2 * Xj + Xn); k3 = qj;
+        }
+        const R ds = time - tj;
+        const R pos = k0 * (ds * ds * ds) + k1 * (ds * ds) + k2 * ds + k3;
+        const R vel = (k0 * 3) * (ds * ds) + (k1 * 2) * ds + k2;
+        const R acc = ((k0 * 3) * 2) * ds + k1 * 2;
+        const size_t o = (size_t)i * P + p;
+        if (o_time) o_time[o] = time;
+        if (o_pos) o_pos[o] = pos;
+        if (o_vel) o_vel[o] = vel;
+        if (o_acc) o_acc[o] = acc;
+        if (geo) {
+          R px, py, kap;
+          walk.locate(pos, px, py, kap);
+          if (o_px) o_px[o] = px;
+          if (o_py) o_py[o] = py;
+          if (o_om) o_om[o] = vel * kap;
+        }
+      }
+    } else if (geo) {  // resample / angular_velocity of caller-supplied positions
+      const int S = g.n_samples[p];
+      n = S < S_cap ? S : S_cap;
+      for (int i = 0; i < n; ++i) {
+        const size_t o = (size_t)i * P + p;
+        R px, py, kap;
+        walk.locate(o_pos[o], px, py, kap);
+        if (o_px) o_px[o] = px;
+        if (o_py) o_py[o] = py;
+        if (o_om) o_om[o] = (o_vel ? o_vel[o] : (R)1) * kap;
+      }
+    }
+  } else if (g.timing) {
+    g.n_samples[p] = 0;
+  }
+  for (int i = n; i < S_cap; ++i) {
+    const size_t o = (size_t)i * P + p;
+    if (g.timing) { if (o_time) o_time[o] = 0; if (o_pos) o_pos[o] = 0; if (o_vel) o_vel[o] = 0; if (o_acc) o_acc[o] = 0; }
+    if (o_px) o_px[o] = 0; if (o_py) o_py[o] = 0; if (o_om) o_om[o] = 0;
+  }
+}
+
+template <class R> void launch_param(const ParamArgs& a, cudaStream_t st) {
+  const int block = 64, grid = (a.P + block - 1) / block;
+  if (a.deg == 3) param_kernel<R, 3><<<grid, block, 0, st>>>(a);
+  else param_kernel<R, 5><<<grid, block, 0, st>>>(a);
+}
+template <class R> void launch_sample(const SampleArgs& a, cudaStream_t st) {
+  const int block = 64, grid = (a.P + block - 1) / block;
+  if (a.deg == 3) sample_kernel<R, 3><<<grid, block, 0, st>>>(a);
+  else sample_kernel<R, 5><<<grid, block, 0, st>>>(a);
+}
+template void launch_param<double>(const ParamArgs&, cudaStream_t);
+template void launch_param<float>(const ParamArgs&, cudaStream_t);
+template void launch_sample<double>(const SampleArgs&, cudaStream_t);
+template void launch_sample<float>(const SampleArgs&, cudaStream_t);
+
+}  // namespace scb

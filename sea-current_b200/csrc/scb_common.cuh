@@ -1,0 +1,85 @@
+// Shared device helpers for the sea-current B200 kernels (sm_100a).
+#pragma once
+#include <cuda_runtime.h>
+#include <math_constants.h>
+#include <stdint.h>
+
+#include "../../include/seacurrent_b200.h"
+
+namespace scb {
+
+constexpr int kWarp = 32;
+constexpr int kTable = SCB_ARCLEN_TABLE;   // 101 cumulative entries per segment
+constexpr int kSub = SCB_ARCLEN_SUBDIV;    // 100 sub-intervals per segment (sc:767, precision 0.01)
+constexpr int kInvNewton = 3;              // Newton steps of the arc-length inversion
+
+template <class R> struct Num;
+template <> struct Num<double> {
+  static __device__ __forceinline__ double inf() { return CUDART_INF; }
+  static __device__ __forceinline__ double nan() { return CUDART_NAN; }
+};
+template <> struct Num<float> {
+  static __device__ __forceinline__ float inf() { return CUDART_INF_F; }
+  static __device__ __forceinline__ float nan() { return CUDART_NAN_F; }
+};
+
+template <class R> struct V2 { R x, y; };
+
+template <class R> __device__ __forceinline__ R rsqrt_(R v);
+template <> __device__ __forceinline__ double rsqrt_(double v) { return rsqrt(v); }
+template <> __device__ __forceinline__ float rsqrt_(float v) { return rsqrtf(v); }
+
+// Kernel-argument bundles (plain pointers; R-typed buffers passed as void* and cast inside).
+struct SplineArgs {
+  int P, W;
+  const void *wx, *wy, *start_angle;  // [P][W], [P][W], [P] or null
+  void *ctrl_x, *ctrl_y;              // [P][(W-1)*(d+1)]
+  void *table;                        // [P][(W-1)*101]
+  void *L, *cost;                     // [P]
+  int32_t* status;                    // [P]  written: SCB_ST_OK or SCB_ST_ERR_BAD_PATH
+  scb_opt opt;
+};
+
+struct ToppraArgs {
+  int P, G;
+  const void *L;                       // [P] path length
+  const void *vel_lo, *vel_hi;         // [P]
+  const void *vel_lo_grid, *vel_hi_grid;  // [G][P] or null
+  const void *acc_lo, *acc_hi;         // [P]
+  const void *vel_start, *vel_end;     // [P] or null
+  double x_cap;
+  void *K_lo, *K_hi, *x;               // [G][P]
+  int32_t *status, *fail_stage;        // [P]; status is read (skip if already failed) and written
+};
+
+struct ParamArgs {
+  int P, G, W, deg;
+  const void *L, *vel_start, *vel_end; // [P]
+  const void *x;                       // [G][P]
+  const void *ctrl_x, *ctrl_y, *table; // spline data (null when geometry is off)
+  void *t, *v, *a, *px, *py, *omega;   // [G][P] outputs (any may be null, t/X scratch never null)
+  void *t_buf, *X_buf, *cp_buf;        // [G][P] scratch: knot times, spline unknowns, Thomas c'
+  void *T_total;                       // [P]
+  int32_t* status;
+  int geometry;
+};
+
+struct SampleArgs {
+  int P, G, W, deg, S_cap;
+  double dt;
+  const void *L, *vel_start, *vel_end;
+  const void *t_buf, *X_buf;           // [G][P]
+  const void *ctrl_x, *ctrl_y, *table;
+  int32_t* n_samples;                  // [P]
+  void *s_time, *s_pos, *s_vel, *s_acc, *s_px, *s_py, *s_omega;  // [S_cap][P]
+  const int32_t* status;
+  int timing, geometry;                // timing off: s_pos / s_vel / n_samples are inputs
+};
+
+template <class R> void launch_spline(const SplineArgs& a, int spline_mode, cudaStream_t st);
+template <class R> void launch_toppra(const ToppraArgs& a, cudaStream_t st);
+template <class R> void launch_param(const ParamArgs& a, cudaStream_t st);
+template <class R> void launch_sample(const SampleArgs& a, cudaStream_t st);
+size_t spline_smem_bytes(int W, int spline_mode, int real_size, int warps);
+
+}  // namespace scb
