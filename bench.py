@@ -1,0 +1,296 @@
+#!/usr/bin/env python3
+"""bench.py — smoothed+timed trajectories/s of the planning hot path on N B200s.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--config C3|C2|C4|C5]
+
+A step = one pass of the whole path (Lau quintic spline + optimiser -> arc-length tables ->
+toppra backward/forward -> parametrizer -> per-gridpoint trajectory record) over one batch of
+synthetic planning problems.  N=1 workload = BASELINE.json configs[2] ("65,536 MPC candidate
+rollouts, 1,000 gridpoints"), the batch the north_star's roofline target is quoted on; N>1 = the
+same batch per rank (weak scaling), per-problem summary records all-gathered over NCCL.
+
+value      whole-job trajectories/s, inputs and outputs resident in HBM (CUDA events on the ctx stream,
+           max over ranks)
+e2e        same metric through scb_plan_batch with pinned HOST buffers (H2D + kernels + D2H timed)
+roofline   dominant kernel: its own algorithmic bytes / its mean launch duration vs measured HBM peak
+cpu_baseline  the oracle's reference-faithful port of the E1 body timed on this box's host cores
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "smoothed+timed trajectories/sec"
+UNIT = "trajectories/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="C3", choices=["C2", "C3", "C4", "C5"])
+    ap.add_argument("--precision", default="fp64", choices=["fp64", "fp32"])
+    ap.add_argument("--problems", type=int, default=0, help="override the per-rank batch size")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
+    return ap.parse_args()
+
+
+def workload(name, rank, world, problems=0):
+    import seacurrent_b200 as scb
+    P0, W, G = scb.workloads.CONFIGS[name]
+    if name == "C4":  # fixed global batch, sharded (strong)
+        P = problems or P0
+        lo, hi = scb.shard_range(P, rank, world)
+        w = scb.workloads.config_c4(P=P, lo=lo, hi=hi)
+        return w, dict(workload="C4: %d randomized problems sharded over %d ranks" % (P, world), P_global=P, W=W, G=G), "strong"
+    P = problems or P0
+    w = scb.workloads.by_name(name, P=P)
+    if name == "C3" and world > 1:  # each rank perturbs the nominal path with its own stream
+        rng = np.random.Generator(np.random.PCG64([scb.workloads.SEED, 3, 1000 + rank]))
+        w["wx"][:, 1:-1] += rng.normal(0, 0.05, size=(P, W - 2))
+    desc = {"C2": "C2: batch of %d independent 20-waypoint paths, 500 gridpoints",
+            "C3": "C3: %d MPC candidate rollouts (perturbed 10-waypoint path), 1,000 gridpoints, vel/accel limits",
+            "C5": "C5: %d long-horizon 200-waypoint paths, 10,000 gridpoints"}[name] % P
+    if world > 1:
+        desc += " per rank x %d ranks" % world
+    return w, dict(workload=desc, P_global=P * world, W=W, G=G), "weak"
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.stop_flag, self.th = index, [], False, None
+
+    def _run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.check_output(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                               "--format=csv,noheader,nounits"], timeout=5).decode().strip()
+                self.rows.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.05)
+
+    def start(self):
+        self.th = threading.Thread(target=self._run, daemon=True)
+        self.th.start()
+
+    def stop(self):
+        self.stop_flag = True
+        if self.th:
+            self.th.join(timeout=10)
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 6 for i in range(4) if r[2 + i].lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def cpu_baseline_run(w, G, seconds, nthreads):
+    """The oracle's reference-faithful port of the E1 body (float32 spline side with the 10,001-point
+    preview sampling, Bernstein-Fourier evaluation, FP64 toppra with the dense column-pivoted QR
+    parametrizer; 'port'), on a bounded sample of the same workload."""
+    from oracle import oracle as ora
+    ora.build()
+    cores = nthreads or ora.num_threads()
+    P = w["wx"].shape[0]
+    n = min(P, cores)
+    sel = slice(0, n)
+    args = lambda s: (w["wx"][s], w["wy"][s], w["vel_lo"][s], w["vel_hi"][s], w["acc_lo"][s], w["acc_hi"][s])
+    t, _ = ora.e1_batch_time(*args(sel), N=G - 1, mode=7, nthreads=cores)
+    per_wave = max(t, 1e-6)
+    waves = int(max(1, min(seconds / per_wave, P // n)))
+    m = n * waves
+    if waves > 1:
+        t, _ = ora.e1_batch_time(*args(slice(0, m)), N=G - 1, mode=7, nthreads=cores)
+    faithful = m / t
+    # 'restated-fast': same port with the tridiagonal parametrizer and no preview sampling
+    m2 = min(P, max(cores * 8, 64))
+    t2, _ = ora.e1_batch_time(*args(slice(0, m2)), N=G - 1, mode=0, nthreads=cores)
+    return {"value": faithful, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": "first %d problems of the workload, oracle E1 port mode 7 (preview sampling + Bernstein-Fourier + "
+                      "dense col-piv QR parametrizer, as the reference), %.1f s" % (m, t),
+            "restated_fast": {"value": m2 / t2, "sample": "first %d problems, de Casteljau + Thomas parametrizer, no preview, %.2f s" % (m2, t2)}}
+
+
+def reference_arm(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    w, cfg, scaling = workload(a.config, 0, 1, a.problems)
+    G = cfg["G"]
+    from oracle import oracle as ora
+    ora.build()
+    cores = ora.num_threads()
+    n = min(w["wx"].shape[0], cores)
+    args = (w["wx"][:n], w["wy"][:n], w["vel_lo"][:n], w["vel_hi"][:n], w["acc_lo"][:n], w["acc_hi"][:n])
+    for _ in range(a.warmup):
+        ora.e1_batch_time(*args, N=G - 1, mode=7, nthreads=cores)
+    t0 = time.perf_counter()
+    for _ in range(a.steps):
+        ora.e1_batch_time(*args, N=G - 1, mode=7, nthreads=cores)
+    dt = time.perf_counter() - t0
+    v = n * a.steps / dt
+    sample = "each step = the first %d problems of the workload (one per host thread), oracle E1 port mode 7" % n
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
+            "warmup": a.warmup, "ms_per_step": 1e3 * dt / a.steps, "higher_is_better": True, "scaling": scaling,
+            "vs_baseline": None, "dtype": "f32 spline / f64 toppra (reference arithmetic)", "data": "synthetic",
+            "config": dict(cfg, sample=sample),
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+def main():
+    a = parse()
+    if a.impl == "reference":
+        return reference_arm(a)
+    import torch
+    import torch.distributed as dist
+    import seacurrent_b200 as scb
+
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    w, cfg, scaling = workload(a.config, rank, world, a.problems)
+    P, W = w["wx"].shape
+    G = w["G"]
+    mode = "lau_quintic"
+    pl = scb.BatchPlanner(local, a.precision, mode, max_problems=P, max_waypoints=W, max_gridpoints=G)
+    tdt = torch.float64 if a.precision == "fp64" else torch.float32
+    opt = scb.default_opt(move_waypoints=1)
+    inputs = {k: torch.from_numpy(np.ascontiguousarray(v)).to(dev, dtype=tdt) for k, v in w.items() if k != "G"}
+    bi, bo, res = pl.make_device_batch(inputs, G=G, opt=opt)
+    stream = torch.cuda.ExternalStream(pl.stream(), device=dev)
+    nrec = P * 32
+
+    def step():
+        pl.run_device(bi, bo, sync=False)
+        rec = pl.pack_summary(P, res)
+        if world > 1:
+            with torch.cuda.stream(stream):
+                rec = scb.gather_summaries(rec, world)
+        return rec
+
+    for _ in range(max(a.warmup, 3)):
+        rec = step()
+    pl.synchronize(); torch.cuda.synchronize()
+    ok_frac = float((res["status"] == 0).float().mean().item())
+    # ---- device-resident timing: K steps, one event pair on the ctx stream
+    sampler = ClockSampler(local)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(a.steps):
+        rec = step()
+    e1.record(stream)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    clocks = sampler.stop()
+    ms = e0.elapsed_time(e1)
+    launches_per_step = pl.timing()["launches"] + 1
+    if world > 1:
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    ms_per_step = ms / a.steps
+    value = cfg["P_global"] / (ms_per_step * 1e-3) if scaling == "weak" else cfg["P_global"] / (ms_per_step * 1e-3)
+
+    # ---- per-kernel durations (CUDA events recorded by the ctx around every stage, one step at a time)
+    stage_ms = {"spline_ms": [], "toppra_ms": [], "param_ms": [], "sample_ms": []}
+    for _ in range(min(a.steps, 5)):
+        pl.run_device(bi, bo, sync=True)
+        tm = pl.timing()
+        for k in stage_ms:
+            stage_ms[k].append(tm[k])
+    stage_ms = {k: float(np.mean(v)) for k, v in stage_ms.items()}
+    rs = 8 if a.precision == "fp64" else 4
+    d = 5
+    # algorithmic bytes of each kernel: its mandatory inputs + outputs (DESIGN.md "Kernels")
+    kbytes = {"spline_ms": P * rs * (2 * W + 1 + 2 * (d + 1) * (W - 1) + 2),                # waypoints, angle -> ctrl, L, J
+              "toppra_ms": P * (rs * (1 + 6 + 3 * G) + 8),                                    # L, limits -> K_lo, K_hi, x, status
+              "param_ms": P * rs * (G + 2 + 2 * (d + 1) * (W - 1) + 6 * G + 1)}                # x, ctrl -> t, px, py, v, a, omega, T
+    dom = max(kbytes, key=lambda k: stage_ms[k])
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    ach = kbytes[dom] / (stage_ms[dom] * 1e-3) / 1e9
+    path_bytes = pl.algorithmic_bytes(P, W, G)
+    roof = {"bound": "hbm", "kernel": dom.replace("_ms", "_kernel"), "achieved": ach, "peak": peak, "unit": "GB/s",
+            "frac": ach / peak, "traffic": None, "peak_source": "measured" if peaks else "fallback",
+            "kernel_ms": stage_ms[dom], "algorithmic_bytes_per_launch": kbytes[dom],
+            "path": {"algorithmic_bytes_per_step": path_bytes, "achieved": path_bytes / (ms_per_step * 1e-3) / 1e9,
+                     "frac": path_bytes / (ms_per_step * 1e-3) / 1e9 / peak}}
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": scaling, "vs_baseline": None,
+            "dtype": "f64" if a.precision == "fp64" else "f32", "data": "synthetic",
+            "config": dict(cfg, P_per_rank=P, spline="lau_quintic, optimiser K=%d move_waypoints=1" % opt.iters,
+                           l2="outputs streamed per step (%.2f GB) exceed the 126 MB L2; no flush" % (path_bytes / 1e9),
+                           ok_fraction=ok_frac),
+            "stage_ms": stage_ms, "roofline": roof, "clocks": clocks, "gpu_launches": launches_per_step * a.steps}
+
+    # ---- e2e: host buffers in pinned memory through scb_plan_batch
+    if not a.no_e2e:
+        names = scb.TRAJECTORY_OUTPUTS
+        host_in = {k: torch.from_numpy(np.ascontiguousarray(v, dtype=pl.real)).pin_memory().numpy() for k, v in w.items() if k != "G"}
+        bufs = {"status": torch.empty(P, dtype=torch.int32).pin_memory().numpy(),
+                "fail_stage": torch.empty(P, dtype=torch.int32).pin_memory().numpy()}
+        for n in names:
+            bufs[n] = torch.empty(pl.out_shape(n, P, W, G, 0), dtype=tdt).pin_memory().numpy()
+        h2d = sum(v.nbytes for v in host_in.values()); d2h = sum(v.nbytes for v in bufs.values())
+        k2 = max(2, min(a.steps, 5))
+        for _ in range(2):
+            pl.plan(G=G, outputs=names, out_buffers=bufs, opt=opt, **host_in)
+        if world > 1:
+            dist.barrier()
+        t0 = time.perf_counter()
+        for _ in range(k2):
+            pl.plan(G=G, outputs=names, out_buffers=bufs, opt=opt, **host_in)
+        dt = time.perf_counter() - t0
+        if world > 1:
+            t = torch.tensor([dt], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dt = float(t.item())
+        tm = pl.timing()
+        line["e2e"] = {"value": cfg["P_global"] * k2 / dt if scaling == "weak" else cfg["P_global"] * k2 / dt, "unit": UNIT,
+                       "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": k2,
+                       "last_step_ms": {k: tm[k] for k in ("h2d_ms", "d2h_ms", "total_ms")},
+                       "outputs": list(names)}
+    if rank == 0 and not a.no_cpu:
+        line["cpu_baseline"] = cpu_baseline_run(w, G, a.cpu_seconds, 0)
+    if rank == 0:
+        print(json.dumps(line))
+    pl.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -180,6 +180,19 @@ void* scb_stream(scb_ctx* ctx);
 /* algorithmic bytes one launch over this batch must move (SURVEY 8-D4 formula) */
 int64_t scb_algorithmic_bytes(int32_t precision, int32_t spline_mode, int32_t P, int32_t W, int32_t G);
 
+/* Fixed-size per-problem summary: what an MPC outer loop needs to rank rollouts, and the only
+ * payload the multi-GPU path exchanges (NCCL all-gather of P_local records per rank; full
+ * trajectories stay sharded on the GPU that planned them). */
+typedef struct scb_summary {
+  int32_t status, fail_stage;
+  double T_total, arclen_total, cost;   /* always double, whatever the ctx precision */
+} scb_summary;
+/* Device pointers (outputs of a previous scb_plan_batch_device on this ctx; any of fail_stage /
+ * T_total / arclen_total / cost may be NULL = 0) -> dst[P] on the device.  Enqueued on the ctx
+ * stream; not synchronised. */
+int scb_pack_summary_device(scb_ctx* ctx, int32_t P, const int32_t* status, const int32_t* fail_stage,
+                            const void* T_total, const void* arclen_total, const void* cost, scb_summary* dst);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,207 @@
+"""ORACLE — TEST INFRASTRUCTURE ONLY.  ctypes view of oracle/liboracle.so (ora_capi.cpp).
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
+import this module.  The product (sea-current_b200/) never does.
+"""
+import ctypes as C
+import importlib.util
+import os
+import subprocess
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+LIB = os.path.join(HERE, "liboracle.so")
+
+
+def _abi():
+    if "seacurrent_b200" not in sys.modules:
+        spec = importlib.util.spec_from_file_location("seacurrent_b200_shim", os.path.join(ROOT, "seacurrent_b200.py"))
+        m = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(m)
+    return sys.modules["seacurrent_b200"].abi
+
+
+def build(force=False):
+    srcs = [os.path.join(HERE, f) for f in os.listdir(HERE) if f.endswith((".hpp", ".cpp", ".h"))]
+    srcs.append(os.path.join(ROOT, "include", "seacurrent_b200.h"))
+    if force or not os.path.exists(LIB) or any(os.path.getmtime(s) > os.path.getmtime(LIB) for s in srcs):
+        subprocess.check_call(["make", "-C", HERE, "-s"] + (["-B"] if force else []))
+    return LIB
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB):
+            build()
+        _lib = C.CDLL(LIB)
+        _lib.ora_e1_batch_time.restype = C.c_double
+        _lib.ora_lau_eval.restype = C.c_double
+        _lib.ora_lau_optimise.restype = C.c_double
+    return _lib
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def _d(a):
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+def num_threads():
+    return lib().ora_num_threads()
+
+
+def lp1d(v, A):
+    A = _d(A).reshape(-1, 2)
+    opt = C.c_double()
+    ok = lib().ora_lp1d(C.c_double(v[0]), C.c_double(v[1]), _p(A), len(A), C.byref(opt))
+    return bool(ok), opt.value
+
+
+def lp2d(v, A, low, high):
+    A = _d(A).reshape(-1, 3); v = _d(v); low = _d(low); high = _d(high)
+    opt = np.zeros(2); act = np.zeros(2, dtype=np.int32)
+    ok = lib().ora_lp2d(_p(v), _p(A), len(A), _p(low), _p(high), _p(opt), _p(act))
+    return bool(ok), opt, act
+
+
+def toppra_ppoly(coeffs, breaks, G, vel_lo, vel_hi, acc_lo, acc_hi, interpolation, sd_start=0.0, sd_end=0.0,
+                 feasible=False):
+    """coeffs [nseg][4][dof] (row 0 multiplies ds^3)."""
+    coeffs = _d(coeffs); nseg, _, dof = coeffs.shape
+    breaks = _d(breaks)
+    K = np.zeros((G, 2)); x = np.zeros(G); feas = np.zeros((G, 2)) if feasible else None
+    frc = C.c_int(0)
+    rc = lib().ora_toppra_ppoly(nseg, dof, _p(coeffs), _p(breaks), G, _p(_d(vel_lo)), _p(_d(vel_hi)), _p(_d(acc_lo)),
+                                _p(_d(acc_hi)), int(interpolation), C.c_double(sd_start), C.c_double(sd_end), _p(K),
+                                _p(x), _p(feas), C.byref(frc))
+    return rc, K, x, feas, frc.value
+
+
+def spline_param(coeffs, breaks, gridpoints, vsq, t_eval_fn=None, solve_mode=0, t_eval=None):
+    coeffs = _d(coeffs); nseg, _, dof = coeffs.shape
+    gp = _d(gridpoints); G = len(gp)
+    ts = np.zeros(G)
+    te = _d(t_eval if t_eval is not None else [0.0])
+    q = np.zeros((len(te), dof)); qd = np.zeros((len(te), dof)); qdd = np.zeros((len(te), dof))
+    n = lib().ora_spline_param(nseg, dof, _p(coeffs), _p(_d(breaks)), G, _p(gp), _p(_d(vsq)), solve_mode, _p(ts), len(te),
+                               _p(te), _p(q), _p(qd), _p(qdd))
+    return ts[:n], q, qd, qdd
+
+
+def cubic_spline(t, y, bc0, bc1, t_eval, solve_mode=0):
+    t = _d(t); y = _d(y); te = _d(t_eval)
+    out = np.zeros(len(te))
+    lib().ora_cubic_spline(len(t), _p(t), _p(y), C.c_double(bc0), C.c_double(bc1), solve_mode, len(te), _p(te), _p(out))
+    return out
+
+
+def hermite_eval(pos, vel, times, s_eval, order):
+    pos = _d(pos); vel = _d(vel); n, dof = pos.shape
+    se = _d(s_eval)
+    out = np.zeros((len(se), dof))
+    lib().ora_hermite_eval(n, dof, _p(pos), _p(vel), _p(_d(times)), len(se), _p(se), order, _p(out))
+    return out
+
+
+def e1_single(wx, wy, vel_lo, vel_hi, acc_lo, acc_hi, N=100, dt=0.02, mode=6, start_angle=float("nan"), cap=8192):
+    """Reference-faithful (float32 spline side) E1 body for one problem."""
+    wx = np.ascontiguousarray(wx, dtype=np.float32); wy = np.ascontiguousarray(wy, dtype=np.float32)
+    W = len(wx)
+    ctrl = np.zeros(8 * (W - 1), dtype=np.float32); tables = np.zeros((W - 1) * 101, dtype=np.float32)
+    total = C.c_float(); ns = C.c_int(); nr = C.c_int()
+    time = np.zeros(cap); f = lambda: np.zeros(cap, dtype=np.float32)
+    pos, vel, acc, px, py, av = f(), f(), f(), f(), f(), f()
+    rc = lib().ora_e1_single(_p(wx), _p(wy), W, C.c_float(start_angle), C.c_double(vel_lo), C.c_double(vel_hi),
+                             C.c_double(acc_lo), C.c_double(acc_hi), N, C.c_float(dt), mode, _p(ctrl), _p(tables),
+                             C.byref(total), cap, C.byref(ns), _p(time), _p(pos), _p(vel), _p(acc), _p(px), _p(py), _p(av),
+                             C.byref(nr))
+    S, Rn = min(ns.value, cap), min(nr.value, cap)
+    return dict(rc=rc, ctrl=ctrl.reshape(W - 1, 4, 2), tables=tables.reshape(W - 1, 101), total=total.value,
+                n_samples=ns.value, time=time[:S], pos=pos[:S], vel=vel[:S], acc=acc[:S], px=px[:Rn], py=py[:Rn],
+                ang_vel=av[:Rn], n_resampled=nr.value)
+
+
+def e1_batch_time(wx, wy, vel_lo, vel_hi, acc_lo, acc_hi, N=100, dt=0.02, mode=7, nthreads=0):
+    """Timed CPU baseline: the reference's E1 body (float32 spline side, FP64 toppra) over a batch,
+    OpenMP over problems.  Returns (seconds, checksum)."""
+    wx = np.ascontiguousarray(wx, dtype=np.float32); wy = np.ascontiguousarray(wy, dtype=np.float32)
+    P, W = wx.shape
+    cs = C.c_double()
+    bc = lambda a: _d(np.broadcast_to(a, (P,)))
+    s = lib().ora_e1_batch_time(P, W, _p(wx), _p(wy), _p(bc(vel_lo)), _p(bc(vel_hi)), _p(bc(acc_lo)), _p(bc(acc_hi)), N,
+                                C.c_float(dt), mode, nthreads, C.byref(cs))
+    return s, cs.value
+
+
+def lau_eval(path_xy, Wp_xy, e, lam, start_angle=float("nan")):
+    path = _d(path_xy); Wp = _d(Wp_xy); e = _d(e); W = len(path)
+    ctrl = np.zeros(((W - 1), 6, 2)); ge = np.zeros(W); gW = np.zeros((W, 2))
+    J = lib().ora_lau_eval(_p(path), W, C.c_double(start_angle), _p(Wp), _p(e), C.c_double(lam), _p(ctrl), _p(ge), _p(gW))
+    return J, ctrl, ge, gW
+
+
+def lau_optimise(path_xy, opt, start_angle=float("nan")):
+    path = _d(path_xy); W = len(path)
+    ctrl = np.zeros(((W - 1), 6, 2)); e = np.zeros(W); hist = np.zeros(opt.iters + 1)
+    J = lib().ora_lau_optimise(_p(path), W, C.c_double(start_angle), C.byref(opt), _p(ctrl), _p(e), _p(hist))
+    return J, ctrl, e, hist
+
+
+def plan_batch(wx=None, wy=None, vel_lo=None, vel_hi=None, acc_lo=None, acc_hi=None, G=101, start_angle=None,
+               vel_lo_grid=None, vel_hi_grid=None, vel_start=None, vel_end=None, spline_mode=0, solve_mode=1,
+               S_cap=0, x_cap=0.0, dt=0.0, opt=None, nthreads=0, outputs=None):
+    """The product's batch on the CPU (FP64), same layouts as scb_plan_batch.  Returns (dict, seconds)."""
+    abi = _abi()
+    keep = []
+
+    def arr(a, shape):
+        if a is None:
+            return None
+        a = np.ascontiguousarray(np.broadcast_to(_d(a), shape))
+        keep.append(a)
+        return a.ctypes.data
+
+    wx = _d(wx); P, W = wx.shape
+    bi = abi.ScbBatchIn()
+    bi.P, bi.W, bi.G = P, W, G
+    bi.wx, bi.wy = arr(wx, (P, W)), arr(wy, (P, W))
+    bi.start_angle = arr(start_angle, (P,))
+    bi.vel_lo, bi.vel_hi = arr(vel_lo, (P,)), arr(vel_hi, (P,))
+    bi.vel_lo_grid, bi.vel_hi_grid = arr(vel_lo_grid, (G, P)), arr(vel_hi_grid, (G, P))
+    bi.acc_lo, bi.acc_hi = arr(acc_lo, (P,)), arr(acc_hi, (P,))
+    bi.vel_start, bi.vel_end = arr(vel_start, (P,)), arr(vel_end, (P,))
+    bi.x_cap, bi.dt = x_cap, dt
+    if opt is None:
+        opt = abi.ScbOpt(32, 0, 0.05, 1.0, 0.25, 4.0, 0.1, 0.05, 0.25)
+    bi.opt = opt
+    d = 3 if spline_mode == 0 else 5
+    shapes = {"ctrl_x": (P, (W - 1) * (d + 1)), "ctrl_y": (P, (W - 1) * (d + 1)), "arclen_table": (P, (W - 1) * 101),
+              "arclen_total": (P,), "T_total": (P,), "cost": (P,)}
+    for n in ("K_lo", "K_hi", "x", "t", "px", "py", "v", "a", "omega"):
+        shapes[n] = (G, P)
+    if S_cap > 0:
+        for n in ("s_time", "s_pos", "s_vel", "s_acc", "s_px", "s_py", "s_omega"):
+            shapes[n] = (S_cap, P)
+    res = {"status": np.zeros(P, dtype=np.int32), "fail_stage": np.zeros(P, dtype=np.int32)}
+    bo = abi.ScbBatchOut()
+    bo.status, bo.fail_stage, bo.S_cap = res["status"].ctypes.data, res["fail_stage"].ctypes.data, S_cap
+    if S_cap > 0:
+        res["n_samples"] = np.zeros(P, dtype=np.int32)
+        bo.n_samples = res["n_samples"].ctypes.data
+    for n, shp in shapes.items():
+        if outputs is not None and n not in outputs:
+            continue
+        res[n] = np.zeros(shp)
+        setattr(bo, n, res[n].ctypes.data)
+    sec = C.c_double()
+    lib().ora_plan_batch(C.byref(bi), C.byref(bo), spline_mode, solve_mode, nthreads, C.byref(sec))
+    return res, sec.value

@@ -2,7 +2,11 @@
 
 The directory name carries a hyphen (it mirrors the reference's name), so import it through
 the root-level shim:  `import seacurrent_b200 as scb`.
+
+Only what the path needs lives here: csrc/ (CUDA kernels + the C ABI, libseacurrent_b200.so)
+and scb/ (ctypes marshalling for tests and bench, synthetic workloads).  The C++ drop-in for
+sea_current.hpp callers is include/sea_current_b200.hpp.
 """
-from .scb import abi  # noqa: F401
-from .scb.planner import (BatchPlanner, BatchResult, bezier_spline, gen_vel_prof, planning_space,  # noqa: F401
-                          serialize_path_to_json, velocity_profile, arclength_data, default_opt)
+from .scb import abi, workloads  # noqa: F401
+from .scb.planner import (ALL_OUTPUTS, TRAJECTORY_OUTPUTS, SUMMARY_DTYPE, BatchPlanner, BatchResult, ScbError,  # noqa: F401
+                          default_opt, gather_summaries, shard_range)

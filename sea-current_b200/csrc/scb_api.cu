@@ -1,0 +1,410 @@
+// C ABI of the B200-native sea-current planning path (include/seacurrent_b200.h).
+//
+// Host side of the drop-in boundary: owns the CUDA stream, the device scratch that the fused
+// kernels need between stages (arc-length tables, controllable sets, Thomas scratch) and, for
+// the host-buffer entry point, the device mirrors of the caller's arrays.  No planning
+// arithmetic happens on the host: every stage is a kernel launch (spline_kernel.cu,
+// toppra_kernel.cu, param_kernel.cu).  There is no CPU fallback — without an sm_100 device
+// scb_create fails with SCB_E_NO_DEVICE.
+//
+// Reference call sequence replaced (examples/json_test.cpp:28-58):
+//   from_path -> arclength -> gen_vel_prof<1> -> resample -> angular_velocity.
+#include <cstdio>
+#include <cstring>
+#include <new>
+
+#include "scb_common.cuh"
+
+namespace {
+
+struct Slot { void* p = nullptr; size_t bytes = 0; };
+
+enum SlotId {
+  // scratch used when the caller did not ask for the corresponding output
+  SL_L, SL_TABLE, SL_CTRL_X, SL_CTRL_Y, SL_K_LO, SL_K_HI, SL_X, SL_T, SL_XB, SL_CP, SL_STATUS, SL_FAIL, SL_NS,
+  // device mirrors of host inputs
+  SL_IN_WX, SL_IN_WY, SL_IN_SA, SL_IN_VLO, SL_IN_VHI, SL_IN_VLG, SL_IN_VHG, SL_IN_ALO, SL_IN_AHI, SL_IN_VS,
+  SL_IN_VE, SL_IN_PL,
+  // device mirrors of host outputs
+  SL_O_STATUS, SL_O_FAIL, SL_O_CTRL_X, SL_O_CTRL_Y, SL_O_L, SL_O_TABLE, SL_O_T_TOTAL, SL_O_COST, SL_O_K_LO,
+  SL_O_K_HI, SL_O_X, SL_O_T, SL_O_PX, SL_O_PY, SL_O_V, SL_O_A, SL_O_OMEGA, SL_O_NS, SL_O_STIME, SL_O_SPOS,
+  SL_O_SVEL, SL_O_SACC, SL_O_SPX, SL_O_SPY, SL_O_SOMEGA,
+  SL_COUNT
+};
+
+}  // namespace
+
+struct scb_ctx {
+  scb_config cfg;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev[8] = {};
+  Slot slot[SL_COUNT];
+  scb_timing timing = {};
+  bool timing_pending = false, host_call = false;
+  char err[256] = {0};
+};
+
+namespace {
+
+using namespace scb;
+
+int fail_cuda(scb_ctx* c, cudaError_t e, const char* where) {
+  snprintf(c->err, sizeof(c->err), "%s: %s", where, cudaGetErrorString(e));
+  return SCB_E_CUDA;
+}
+#define SCB_CUDA(call)                                         \
+  do {                                                         \
+    cudaError_t e_ = (call);                                   \
+    if (e_ != cudaSuccess) return fail_cuda(ctx, e_, #call);   \
+  } while (0)
+
+// grow-only device buffer
+int ensure(scb_ctx* ctx, int id, size_t bytes, void** out) {
+  Slot& s = ctx->slot[id];
+  if (bytes == 0) bytes = 16;
+  if (s.bytes < bytes) {
+    if (s.p) { cudaFree(s.p); s.p = nullptr; s.bytes = 0; }
+    cudaError_t e = cudaMalloc(&s.p, bytes);
+    if (e != cudaSuccess) { fail_cuda(ctx, e, "cudaMalloc"); return e == cudaErrorMemoryAllocation ? SCB_E_NOMEM : SCB_E_CUDA; }
+    s.bytes = bytes;
+  }
+  *out = s.p;
+  return SCB_OK;
+}
+
+size_t real_size(const scb_ctx* c) { return c->cfg.precision == SCB_FP64 ? 8 : 4; }
+int degree_of(const scb_ctx* c) { return c->cfg.spline_mode == SCB_REF_CUBIC ? 3 : 5; }
+
+int validate(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, int& stages) {
+  if (!ctx || !in || !out) return SCB_E_INVALID;
+  stages = in->stages ? in->stages : (SCB_STAGE_SPLINE | SCB_STAGE_TIMING | SCB_STAGE_GEOMETRY);
+  if (in->P < 0 || in->P > ctx->cfg.max_problems) return SCB_E_INVALID;
+  if ((stages & SCB_STAGE_SPLINE) && (in->W < 2 || in->W > ctx->cfg.max_waypoints || !in->wx || !in->wy)) return SCB_E_INVALID;
+  if ((stages & SCB_STAGE_TIMING) && (in->G < 2 || in->G > ctx->cfg.max_gridpoints)) return SCB_E_INVALID;
+  if ((stages & SCB_STAGE_TIMING) && (!in->acc_lo || !in->acc_hi)) return SCB_E_INVALID;
+  if ((stages & SCB_STAGE_TIMING) && !((in->vel_lo && in->vel_hi) || (in->vel_lo_grid && in->vel_hi_grid))) return SCB_E_INVALID;
+  if ((stages & SCB_STAGE_TIMING) && !(stages & SCB_STAGE_SPLINE) && !in->path_len) return SCB_E_INVALID;
+  if ((stages & SCB_STAGE_GEOMETRY) && !(stages & SCB_STAGE_SPLINE)) return SCB_E_INVALID;
+  if (out->S_cap < 0 || out->S_cap > ctx->cfg.max_samples) return SCB_E_INVALID;
+  if ((stages & SCB_STAGE_GEOMETRY) && !(stages & SCB_STAGE_TIMING) && (out->S_cap <= 0 || !out->n_samples || !out->s_pos)) return SCB_E_INVALID;
+  if (!out->status) return SCB_E_INVALID;
+  // a spline kernel needs its per-warp state in shared memory
+  if ((stages & SCB_STAGE_SPLINE) &&
+      spline_smem_bytes(in->W, ctx->cfg.spline_mode, (int)real_size(ctx), 1) > 200 * 1024) return SCB_E_INVALID;
+  return SCB_OK;
+}
+
+// Enqueue every stage on the ctx stream.  All pointers are device pointers.
+template <class R>
+int run_device(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, int stages) {
+  const int P = in->P, W = in->W, G = in->G, deg = degree_of(ctx);
+  const size_t rs = sizeof(R);
+  cudaStream_t st = ctx->stream;
+  int launches = 0;
+  if (P == 0) return SCB_OK;
+  const bool do_spline = stages & SCB_STAGE_SPLINE, do_timing = stages & SCB_STAGE_TIMING,
+             do_geo = stages & SCB_STAGE_GEOMETRY;
+  int rc;
+  void *dL = out->arclen_total, *dTab = out->arclen_table, *dCx = out->ctrl_x, *dCy = out->ctrl_y;
+  int32_t* dFail = out->fail_stage;
+  if (!dFail && (rc = ensure(ctx, SL_FAIL, (size_t)P * 4, (void**)&dFail))) return rc;
+  SCB_CUDA(cudaEventRecord(ctx->ev[1], st));
+  if (do_spline) {
+    const size_t nseg = W - 1;
+    if (!dL && (rc = ensure(ctx, SL_L, P * rs, &dL))) return rc;
+    if (!dTab && (rc = ensure(ctx, SL_TABLE, (size_t)P * nseg * kTable * rs, &dTab))) return rc;
+    if (do_geo) {
+      if (!dCx && (rc = ensure(ctx, SL_CTRL_X, (size_t)P * nseg * (deg + 1) * rs, &dCx))) return rc;
+      if (!dCy && (rc = ensure(ctx, SL_CTRL_Y, (size_t)P * nseg * (deg + 1) * rs, &dCy))) return rc;
+    }
+    SplineArgs a{};
+    a.P = P; a.W = W; a.wx = in->wx; a.wy = in->wy; a.start_angle = in->start_angle;
+    a.ctrl_x = dCx; a.ctrl_y = dCy; a.table = dTab; a.L = dL; a.cost = out->cost; a.status = out->status;
+    a.opt = in->opt;
+    launch_spline<R>(a, ctx->cfg.spline_mode, st);
+    ++launches;
+  } else {
+    SCB_CUDA(cudaMemsetAsync(out->status, 0, (size_t)P * 4, st));
+    dL = (void*)in->path_len;
+  }
+  SCB_CUDA(cudaEventRecord(ctx->ev[2], st));
+  void *dT = out->t, *dXb = nullptr, *dCp = nullptr;
+  if (do_timing) {
+    void *dKlo = out->K_lo, *dKhi = out->K_hi, *dX = out->x;
+    const size_t gp = (size_t)G * P * rs;
+    if (!dKlo && (rc = ensure(ctx, SL_K_LO, gp, &dKlo))) return rc;
+    if (!dKhi && (rc = ensure(ctx, SL_K_HI, gp, &dKhi))) return rc;
+    if (!dX && (rc = ensure(ctx, SL_X, gp, &dX))) return rc;
+    if (!dT && (rc = ensure(ctx, SL_T, gp, &dT))) return rc;
+    if ((rc = ensure(ctx, SL_XB, gp, &dXb))) return rc;
+    if ((rc = ensure(ctx, SL_CP, gp, &dCp))) return rc;
+    ToppraArgs t{};
+    t.P = P; t.G = G; t.L = dL; t.vel_lo = in->vel_lo; t.vel_hi = in->vel_hi;
+    t.vel_lo_grid = in->vel_lo_grid; t.vel_hi_grid = in->vel_hi_grid;
+    t.acc_lo = in->acc_lo; t.acc_hi = in->acc_hi; t.vel_start = in->vel_start; t.vel_end = in->vel_end;
+    t.x_cap = in->x_cap > 0 ? in->x_cap : 100.0;
+    t.K_lo = dKlo; t.K_hi = dKhi; t.x = dX; t.status = out->status; t.fail_stage = dFail;
+    launch_toppra<R>(t, st);
+    ++launches;
+    SCB_CUDA(cudaEventRecord(ctx->ev[3], st));
+    ParamArgs q{};
+    q.P = P; q.G = G; q.W = W; q.deg = deg; q.L = dL; q.vel_start = in->vel_start; q.vel_end = in->vel_end;
+    q.x = dX; q.ctrl_x = dCx; q.ctrl_y = dCy; q.table = dTab;
+    q.t = nullptr; q.v = out->v; q.a = out->a; q.px = out->px; q.py = out->py; q.omega = out->omega;
+    q.t_buf = dT; q.X_buf = dXb; q.cp_buf = dCp; q.T_total = out->T_total; q.status = out->status;
+    q.geometry = do_geo ? 1 : 0;
+    launch_param<R>(q, st);
+    ++launches;
+  } else {
+    SCB_CUDA(cudaMemsetAsync(dFail, 0xff, (size_t)P * 4, st));
+    SCB_CUDA(cudaEventRecord(ctx->ev[3], st));
+  }
+  SCB_CUDA(cudaEventRecord(ctx->ev[4], st));
+  const bool want_stream = out->S_cap > 0 && (out->s_time || out->s_pos || out->s_vel || out->s_acc || out->s_px ||
+                                              out->s_py || out->s_omega || out->n_samples);
+  if (want_stream && (do_timing || do_geo)) {
+    int32_t* dNs = out->n_samples;
+    if (!dNs && (rc = ensure(ctx, SL_NS, (size_t)P * 4, (void**)&dNs))) return rc;
+    SampleArgs s{};
+    s.P = P; s.G = G; s.W = W; s.deg = deg; s.S_cap = out->S_cap;
+    s.dt = in->dt > 0 ? in->dt : (double)0.02f;
+    s.L = dL; s.vel_start = in->vel_start; s.vel_end = in->vel_end; s.t_buf = dT; s.X_buf = dXb;
+    s.ctrl_x = dCx; s.ctrl_y = dCy; s.table = dTab; s.n_samples = dNs;
+    s.s_time = out->s_time; s.s_pos = out->s_pos; s.s_vel = out->s_vel; s.s_acc = out->s_acc;
+    s.s_px = out->s_px; s.s_py = out->s_py; s.s_omega = out->s_omega; s.status = out->status;
+    s.timing = do_timing ? 1 : 0; s.geometry = do_geo ? 1 : 0;
+    launch_sample<R>(s, st);
+    ++launches;
+  }
+  SCB_CUDA(cudaEventRecord(ctx->ev[5], st));
+  SCB_CUDA(cudaGetLastError());
+  ctx->timing.launches = launches;
+  ctx->timing_pending = true;
+  return SCB_OK;
+}
+
+template <class R>
+__global__ void pack_summary_kernel(int P, const int32_t* status, const int32_t* fail, const R* T, const R* L, const R* J,
+                                    scb_summary* dst) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= P) return;
+  scb_summary s;
+  s.status = status[p]; s.fail_stage = fail ? fail[p] : -1;
+  s.T_total = T ? (double)T[p] : 0.0; s.arclen_total = L ? (double)L[p] : 0.0; s.cost = J ? (double)J[p] : 0.0;
+  dst[p] = s;
+}
+
+int run_device_any(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, int stages) {
+  return ctx->cfg.precision == SCB_FP64 ? run_device<double>(ctx, in, out, stages) : run_device<float>(ctx, in, out, stages);
+}
+
+void collect_timing(scb_ctx* ctx) {
+  if (!ctx->timing_pending) return;
+  scb_timing& t = ctx->timing;
+  auto el = [&](int a, int b) { float ms = 0; cudaEventElapsedTime(&ms, ctx->ev[a], ctx->ev[b]); return ms; };
+  t.spline_ms = el(1, 2); t.toppra_ms = el(2, 3); t.param_ms = el(3, 4); t.sample_ms = el(4, 5);
+  if (ctx->host_call) { t.h2d_ms = el(0, 1); t.d2h_ms = el(5, 6); t.total_ms = el(0, 6); }
+  else { t.h2d_ms = 0; t.d2h_ms = 0; t.total_ms = el(1, 5); }
+  ctx->timing_pending = false;
+}
+
+}  // namespace
+
+extern "C" {
+
+int scb_version(void) { return SCB_VERSION; }
+
+const char* scb_strerror(int code) {
+  switch (code) {
+    case SCB_OK: return "ok";
+    case SCB_E_INVALID: return "invalid argument";
+    case SCB_E_NO_DEVICE: return "no usable sm_100 CUDA device (there is no CPU fallback)";
+    case SCB_E_CUDA: return "CUDA runtime error (see scb_last_cuda_error)";
+    case SCB_E_NOMEM: return "out of device memory";
+    default: return "unknown error";
+  }
+}
+
+void scb_default_opt(scb_opt* o) {
+  if (!o) return;
+  o->iters = 32; o->move_waypoints = 0; o->lambda = 0.05;
+  o->e_init = 1.0; o->e_min = 0.25; o->e_max = 4.0;
+  o->step_e = 0.1; o->step_w = 0.05; o->w_radius = 0.25;
+}
+
+int64_t scb_algorithmic_bytes(int32_t precision, int32_t spline_mode, int32_t P, int32_t W, int32_t G) {
+  // b*[(2W+8) + 2(d+1)(W-1) + 9G + 3] + 4 bytes per trajectory
+  const int64_t b = precision == SCB_FP64 ? 8 : 4, d = spline_mode == SCB_REF_CUBIC ? 3 : 5;
+  const int64_t per = b * ((2 * (int64_t)W + 8) + 2 * (d + 1) * ((int64_t)W - 1) + 9 * (int64_t)G + 3) + 4;
+  return per * P;
+}
+
+int scb_create(scb_ctx** out, const scb_config* cfg) {
+  if (!out || !cfg) return SCB_E_INVALID;
+  *out = nullptr;
+  if (cfg->precision != SCB_FP64 && cfg->precision != SCB_FP32) return SCB_E_INVALID;
+  if (cfg->spline_mode != SCB_REF_CUBIC && cfg->spline_mode != SCB_LAU_QUINTIC) return SCB_E_INVALID;
+  if (cfg->max_problems < 1 || cfg->max_waypoints < 2 || cfg->max_gridpoints < 2 || cfg->max_samples < 0) return SCB_E_INVALID;
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0 || cfg->device < 0 || cfg->device >= n) { cudaGetLastError(); return SCB_E_NO_DEVICE; }
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, cfg->device) != cudaSuccess) return SCB_E_NO_DEVICE;
+  if (prop.major != 10) return SCB_E_NO_DEVICE;  // kernels are built for sm_100a only
+  scb_ctx* ctx = new (std::nothrow) scb_ctx();
+  if (!ctx) return SCB_E_NOMEM;
+  ctx->cfg = *cfg;
+  if (cudaSetDevice(cfg->device) != cudaSuccess || cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) {
+    delete ctx; return SCB_E_CUDA;
+  }
+  for (auto& e : ctx->ev) if (cudaEventCreate(&e) != cudaSuccess) { scb_destroy(ctx); return SCB_E_CUDA; }
+  *out = ctx;
+  return SCB_OK;
+}
+
+int scb_destroy(scb_ctx* ctx) {
+  if (!ctx) return SCB_E_INVALID;
+  cudaSetDevice(ctx->cfg.device);
+  if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+  for (auto& s : ctx->slot) if (s.p) cudaFree(s.p);
+  for (auto& e : ctx->ev) if (e) cudaEventDestroy(e);
+  if (ctx->stream) cudaStreamDestroy(ctx->stream);
+  delete ctx;
+  return SCB_OK;
+}
+
+int scb_plan_batch_device(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, int async) {
+  int stages;
+  int rc = validate(ctx, in, out, stages);
+  if (rc) return rc;
+  SCB_CUDA(cudaSetDevice(ctx->cfg.device));
+  ctx->host_call = false;
+  rc = run_device_any(ctx, in, out, stages);
+  if (rc) return rc;
+  if (!async) { SCB_CUDA(cudaStreamSynchronize(ctx->stream)); collect_timing(ctx); }
+  return SCB_OK;
+}
+
+int scb_synchronize(scb_ctx* ctx) {
+  if (!ctx) return SCB_E_INVALID;
+  SCB_CUDA(cudaSetDevice(ctx->cfg.device));
+  SCB_CUDA(cudaStreamSynchronize(ctx->stream));
+  collect_timing(ctx);
+  return SCB_OK;
+}
+
+int scb_plan_batch(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out) {
+  int stages;
+  int rc = validate(ctx, in, out, stages);
+  if (rc) return rc;
+  SCB_CUDA(cudaSetDevice(ctx->cfg.device));
+  const int P = in->P, W = in->W, G = in->G, deg = degree_of(ctx), S = out->S_cap;
+  if (P == 0) return SCB_OK;
+  const size_t rs = real_size(ctx);
+  cudaStream_t st = ctx->stream;
+  scb_batch_in din = *in;
+  scb_batch_out dout = *out;
+  SCB_CUDA(cudaEventRecord(ctx->ev[0], st));
+  // ---- H2D: one cudaMemcpyAsync per input array (full speed when the caller's memory is pinned)
+  auto up = [&](int id, const void* src, size_t bytes, const void** dst) -> int {
+    if (!src) { *dst = nullptr; return SCB_OK; }
+    void* d;
+    int r = ensure(ctx, id, bytes, &d);
+    if (r) return r;
+    cudaError_t e = cudaMemcpyAsync(d, src, bytes, cudaMemcpyHostToDevice, st);
+    if (e != cudaSuccess) return fail_cuda(ctx, e, "cudaMemcpyAsync H2D");
+    *dst = d;
+    return SCB_OK;
+  };
+  const bool do_spline = stages & SCB_STAGE_SPLINE, do_timing = stages & SCB_STAGE_TIMING;
+  if (do_spline) {
+    if ((rc = up(SL_IN_WX, in->wx, (size_t)P * W * rs, &din.wx))) return rc;
+    if ((rc = up(SL_IN_WY, in->wy, (size_t)P * W * rs, &din.wy))) return rc;
+    if ((rc = up(SL_IN_SA, in->start_angle, P * rs, &din.start_angle))) return rc;
+  }
+  if (do_timing) {
+    if ((rc = up(SL_IN_VLO, in->vel_lo, P * rs, &din.vel_lo))) return rc;
+    if ((rc = up(SL_IN_VHI, in->vel_hi, P * rs, &din.vel_hi))) return rc;
+    if ((rc = up(SL_IN_VLG, in->vel_lo_grid, (size_t)G * P * rs, &din.vel_lo_grid))) return rc;
+    if ((rc = up(SL_IN_VHG, in->vel_hi_grid, (size_t)G * P * rs, &din.vel_hi_grid))) return rc;
+    if ((rc = up(SL_IN_ALO, in->acc_lo, P * rs, &din.acc_lo))) return rc;
+    if ((rc = up(SL_IN_AHI, in->acc_hi, P * rs, &din.acc_hi))) return rc;
+    if ((rc = up(SL_IN_VS, in->vel_start, P * rs, &din.vel_start))) return rc;
+    if ((rc = up(SL_IN_VE, in->vel_end, P * rs, &din.vel_end))) return rc;
+    if (!do_spline && (rc = up(SL_IN_PL, in->path_len, P * rs, &din.path_len))) return rc;
+  }
+  // ---- device mirrors of the requested outputs
+  struct Down { void* host; void* dev; size_t bytes; };
+  Down downs[32];
+  int nd = 0;
+  auto mirror = [&](int id, void* host, size_t bytes, void** dev) -> int {
+    if (!host) { *dev = nullptr; return SCB_OK; }
+    void* d;
+    int r = ensure(ctx, id, bytes, &d);
+    if (r) return r;
+    *dev = d;
+    downs[nd++] = {host, d, bytes};
+    return SCB_OK;
+  };
+  const size_t nc = (size_t)(W > 1 ? W - 1 : 0) * (deg + 1), nt = (size_t)(W > 1 ? W - 1 : 0) * kTable;
+  const size_t gp = (size_t)G * P * rs, sp = (size_t)S * P * rs;
+#define MIR(id, field, bytes) if ((rc = mirror(id, out->field, bytes, (void**)&dout.field))) return rc
+  MIR(SL_O_STATUS, status, (size_t)P * 4); MIR(SL_O_FAIL, fail_stage, (size_t)P * 4);
+  if (do_spline) {
+    MIR(SL_O_CTRL_X, ctrl_x, P * nc * rs); MIR(SL_O_CTRL_Y, ctrl_y, P * nc * rs);
+    MIR(SL_O_L, arclen_total, P * rs); MIR(SL_O_TABLE, arclen_table, P * nt * rs); MIR(SL_O_COST, cost, P * rs);
+  } else { dout.ctrl_x = dout.ctrl_y = dout.arclen_total = dout.arclen_table = dout.cost = nullptr; }
+  if (do_timing) {
+    MIR(SL_O_T_TOTAL, T_total, P * rs);
+    MIR(SL_O_K_LO, K_lo, gp); MIR(SL_O_K_HI, K_hi, gp); MIR(SL_O_X, x, gp); MIR(SL_O_T, t, gp);
+    MIR(SL_O_V, v, gp); MIR(SL_O_A, a, gp);
+    if (stages & SCB_STAGE_GEOMETRY) { MIR(SL_O_PX, px, gp); MIR(SL_O_PY, py, gp); MIR(SL_O_OMEGA, omega, gp); }
+    else { dout.px = dout.py = dout.omega = nullptr; }
+  } else { dout.T_total = dout.K_lo = dout.K_hi = dout.x = dout.t = dout.v = dout.a = dout.px = dout.py = dout.omega = nullptr; }
+  if (S > 0) {
+    MIR(SL_O_NS, n_samples, (size_t)P * 4);
+    MIR(SL_O_STIME, s_time, sp); MIR(SL_O_SPOS, s_pos, sp); MIR(SL_O_SVEL, s_vel, sp); MIR(SL_O_SACC, s_acc, sp);
+    MIR(SL_O_SPX, s_px, sp); MIR(SL_O_SPY, s_py, sp); MIR(SL_O_SOMEGA, s_omega, sp);
+    if (!do_timing) {  // positions (and velocities) to resample at are inputs
+      SCB_CUDA(cudaMemcpyAsync(dout.n_samples, out->n_samples, (size_t)P * 4, cudaMemcpyHostToDevice, st));
+      SCB_CUDA(cudaMemcpyAsync(dout.s_pos, out->s_pos, sp, cudaMemcpyHostToDevice, st));
+      if (out->s_vel) SCB_CUDA(cudaMemcpyAsync(dout.s_vel, out->s_vel, sp, cudaMemcpyHostToDevice, st));
+    }
+  }
+#undef MIR
+  ctx->host_call = true;
+  rc = run_device_any(ctx, &din, &dout, stages);
+  if (rc) return rc;
+  for (int i = 0; i < nd; ++i)
+    SCB_CUDA(cudaMemcpyAsync(downs[i].host, downs[i].dev, downs[i].bytes, cudaMemcpyDeviceToHost, st));
+  SCB_CUDA(cudaEventRecord(ctx->ev[6], st));
+  SCB_CUDA(cudaStreamSynchronize(st));
+  collect_timing(ctx);
+  return SCB_OK;
+}
+
+int scb_pack_summary_device(scb_ctx* ctx, int32_t P, const int32_t* status, const int32_t* fail_stage, const void* T_total,
+                            const void* arclen_total, const void* cost, scb_summary* dst) {
+  if (!ctx || P < 0 || !status || !dst) return SCB_E_INVALID;
+  if (P == 0) return SCB_OK;
+  SCB_CUDA(cudaSetDevice(ctx->cfg.device));
+  const int block = 256, grid = (P + block - 1) / block;
+  if (ctx->cfg.precision == SCB_FP64)
+    pack_summary_kernel<double><<<grid, block, 0, ctx->stream>>>(P, status, fail_stage, (const double*)T_total,
+                                                                 (const double*)arclen_total, (const double*)cost, dst);
+  else
+    pack_summary_kernel<float><<<grid, block, 0, ctx->stream>>>(P, status, fail_stage, (const float*)T_total,
+                                                                (const float*)arclen_total, (const float*)cost, dst);
+  SCB_CUDA(cudaGetLastError());
+  return SCB_OK;
+}
+
+int scb_get_timing(scb_ctx* ctx, scb_timing* out) {
+  if (!ctx || !out) return SCB_E_INVALID;
+  *out = ctx->timing;
+  return SCB_OK;
+}
+
+const char* scb_last_cuda_error(scb_ctx* ctx) { return ctx ? ctx->err : ""; }
+void* scb_stream(scb_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+
+}  // extern "C"

@@ -162,6 +162,7 @@ __global__ void __launch_bounds__(64) toppra_kernel(ToppraArgs g) {
   const R INF = Num<R>::inf();
   if (g.status[p] != SCB_ST_OK) {  // spline stage already failed this problem
     for (int i = 0; i < G; ++i) { K_lo[(size_t)i * P + p] = 0; K_hi[(size_t)i * P + p] = 0; X[(size_t)i * P + p] = 0; }
+    g.fail_stage[p] = -1;
     return;
   }
   PathK<R> pk;
@@ -212,7 +213,7 @@ __global__ void __launch_bounds__(64) toppra_kernel(ToppraArgs g) {
     for (int i = 0; i < G && status == SCB_ST_OK; ++i) {
       R lo = pk.vlo, hi = pk.vhi;
       if (grid_lim) { lo = vlg[(size_t)i * P + p]; hi = vhg[(size_t)i * P + p]; }
-      if (!vel_xbound(pk.qd(pk.s_at(i)), lo, hi, xl, xh)) { status = SCB_ST_ERR_BAD_LIMITS; fail_stage = i; }
+      if (!vel_xbound(pk.qd(pk.s_at(i)), lo, hi, xl, xh)) status = SCB_ST_ERR_BAD_LIMITS;
     }
   }
 

@@ -51,6 +51,11 @@ class ScbBatchOut(C.Structure):
                 ("s_px", C.c_void_p), ("s_py", C.c_void_p), ("s_omega", C.c_void_p)]
 
 
+class ScbSummary(C.Structure):
+    _fields_ = [("status", C.c_int32), ("fail_stage", C.c_int32), ("T_total", C.c_double),
+                ("arclen_total", C.c_double), ("cost", C.c_double)]
+
+
 class ScbTiming(C.Structure):
     _fields_ = [("h2d_ms", C.c_float), ("spline_ms", C.c_float), ("toppra_ms", C.c_float),
                 ("param_ms", C.c_float), ("sample_ms", C.c_float), ("d2h_ms", C.c_float),
@@ -71,6 +76,8 @@ SYMBOLS = {
     "scb_last_cuda_error": (C.c_char_p, [C.c_void_p]),
     "scb_stream": (C.c_void_p, [C.c_void_p]),
     "scb_algorithmic_bytes": (C.c_int64, [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32]),
+    "scb_pack_summary_device": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                          C.c_void_p, C.c_void_p]),
 }
 
 _lib = None

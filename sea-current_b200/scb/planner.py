@@ -1,0 +1,240 @@
+"""Batched planner over the C ABI (include/seacurrent_b200.h) — test / bench harness side.
+
+The product's host layer for C++ callers is include/sea_current_b200.hpp (namespace turtle::sc,
+the reference's signatures).  This module is the thin ctypes equivalent used by tests/ and
+bench.py: it only marshals numpy / torch buffers into scb_batch_in / scb_batch_out and calls
+scb_plan_batch (host buffers) or scb_plan_batch_device (HBM-resident torch tensors).  There is
+no planning arithmetic here and no fallback: if the library cannot be loaded or no sm_100
+device exists, construction raises.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import abi
+
+PER_PROBLEM = ("arclen_total", "T_total", "cost")
+PER_GRID = ("K_lo", "K_hi", "x", "t", "px", "py", "v", "a", "omega")
+PER_SAMPLE = ("s_time", "s_pos", "s_vel", "s_acc", "s_px", "s_py", "s_omega")
+ALL_OUTPUTS = ("ctrl_x", "ctrl_y", "arclen_table") + PER_PROBLEM + PER_GRID
+# what the reference's E1 call sequence hands back to its caller (gen_vel_prof + resample +
+# angular_velocity, examples/json_test.cpp:28-58), one record per toppra gridpoint
+TRAJECTORY_OUTPUTS = ("arclen_total", "T_total", "t", "px", "py", "v", "a", "omega")
+
+
+class ScbError(RuntimeError):
+    pass
+
+
+def default_opt(**kw):
+    o = abi.ScbOpt()
+    abi.load_library().scb_default_opt(C.byref(o))
+    for k, v in kw.items():
+        setattr(o, "lambda_" if k == "lambda" else k, v)
+    return o
+
+
+class BatchResult(dict):
+    """dict of output arrays (+ 'status', 'fail_stage', optionally 'n_samples') with attribute access."""
+    __getattr__ = dict.__getitem__
+
+
+class BatchPlanner:
+    def __init__(self, device=0, precision="fp64", spline_mode="ref_cubic", max_problems=65536, max_waypoints=32,
+                 max_gridpoints=1001, max_samples=0):
+        self.lib = abi.load_library()
+        self.precision = {"fp64": abi.SCB_FP64, "fp32": abi.SCB_FP32}[precision]
+        self.spline_mode = {"ref_cubic": abi.SCB_REF_CUBIC, "lau_quintic": abi.SCB_LAU_QUINTIC}[spline_mode]
+        self.real = np.float64 if self.precision == abi.SCB_FP64 else np.float32
+        self.degree = 3 if self.spline_mode == abi.SCB_REF_CUBIC else 5
+        self.device = device
+        cfg = abi.ScbConfig(device, self.precision, self.spline_mode, max_problems, max_waypoints, max_gridpoints,
+                            max_samples)
+        h = C.c_void_p()
+        rc = self.lib.scb_create(C.byref(h), C.byref(cfg))
+        if rc != 0:
+            raise ScbError("scb_create: %s" % self.lib.scb_strerror(rc).decode())
+        self.ctx = h
+
+    def close(self):
+        if getattr(self, "ctx", None):
+            self.lib.scb_destroy(self.ctx)
+            self.ctx = None
+
+    __del__ = close
+
+    def _check(self, rc, what):
+        if rc != 0:
+            raise ScbError("%s: %s [%s]" % (what, self.lib.scb_strerror(rc).decode(),
+                                            self.lib.scb_last_cuda_error(self.ctx).decode()))
+
+    def timing(self):
+        t = abi.ScbTiming()
+        self.lib.scb_get_timing(self.ctx, C.byref(t))
+        return {k: getattr(t, k) for k, _ in abi.ScbTiming._fields_}
+
+    def stream(self):
+        return self.lib.scb_stream(self.ctx)
+
+    def synchronize(self):
+        self._check(self.lib.scb_synchronize(self.ctx), "scb_synchronize")
+
+    def algorithmic_bytes(self, P, W, G):
+        return self.lib.scb_algorithmic_bytes(self.precision, self.spline_mode, P, W, G)
+
+    def out_shape(self, name, P, W, G, S_cap):
+        nseg = W - 1
+        if name in ("ctrl_x", "ctrl_y"):
+            return (P, nseg * (self.degree + 1))
+        if name == "arclen_table":
+            return (P, nseg * abi.ARCLEN_TABLE)
+        if name in PER_PROBLEM:
+            return (P,)
+        if name in PER_GRID:
+            return (G, P)
+        if name in PER_SAMPLE:
+            return (S_cap, P)
+        raise KeyError(name)
+
+    # ------------------------------------------------------------------ host buffers
+    def plan(self, wx=None, wy=None, vel_lo=None, vel_hi=None, acc_lo=None, acc_hi=None, G=101, start_angle=None,
+             vel_lo_grid=None, vel_hi_grid=None, vel_start=None, vel_end=None, path_len=None, stages=0,
+             outputs=ALL_OUTPUTS, S_cap=0, x_cap=0.0, dt=0.0, opt=None, out_buffers=None, resample_at=None):
+        """Host arrays in, host arrays out (scb_plan_batch).  `out_buffers` lets a caller pass
+        preallocated (e.g. pinned) numpy arrays keyed by output name."""
+        R = self.real
+        keep = []
+
+        def arr(a, shape=None):
+            if a is None:
+                return None
+            a = np.ascontiguousarray(a, dtype=R)
+            if shape is not None and a.shape != shape:
+                a = np.ascontiguousarray(np.broadcast_to(a, shape))
+            keep.append(a)
+            return a.ctypes.data
+
+        if wx is not None:
+            wx = np.ascontiguousarray(wx, dtype=R)
+            P, W = wx.shape
+        else:
+            P, W = len(np.atleast_1d(path_len)), 2
+        bi = abi.ScbBatchIn()
+        bi.P, bi.W, bi.G = P, W, G
+        bi.wx, bi.wy = arr(wx), arr(wy, (P, W) if wx is not None else None)
+        bi.start_angle = arr(start_angle, (P,))
+        bi.vel_lo, bi.vel_hi = arr(vel_lo, (P,)), arr(vel_hi, (P,))
+        bi.vel_lo_grid, bi.vel_hi_grid = arr(vel_lo_grid, (G, P)), arr(vel_hi_grid, (G, P))
+        bi.acc_lo, bi.acc_hi = arr(acc_lo, (P,)), arr(acc_hi, (P,))
+        bi.vel_start, bi.vel_end = arr(vel_start, (P,)), arr(vel_end, (P,))
+        bi.path_len = arr(path_len, (P,))
+        bi.stages, bi.x_cap, bi.dt = stages, x_cap, dt
+        bi.opt = opt if opt is not None else default_opt()
+        res = BatchResult()
+        bo = abi.ScbBatchOut()
+        ob = out_buffers or {}
+
+        def outbuf(name, shape, dtype):
+            a = ob.get(name)
+            if a is None:
+                a = np.empty(shape, dtype=dtype)
+            assert a.shape == tuple(shape) and a.dtype == dtype and a.flags.c_contiguous, name
+            res[name] = a
+            return a.ctypes.data
+
+        bo.status = outbuf("status", (P,), np.int32)
+        bo.fail_stage = outbuf("fail_stage", (P,), np.int32)
+        bo.S_cap = S_cap
+        names = list(outputs)
+        if S_cap > 0:
+            names += [n for n in PER_SAMPLE if n not in names]
+            bo.n_samples = outbuf("n_samples", (P,), np.int32)
+            if resample_at is not None:  # geometry only: positions (and velocities) are inputs
+                pos, vel, ns = resample_at
+                res["s_pos"] = np.ascontiguousarray(pos, dtype=R)
+                res["s_vel"] = np.ascontiguousarray(vel, dtype=R) if vel is not None else None
+                res["n_samples"][:] = ns
+                ob = dict(ob, s_pos=res["s_pos"])
+                if res["s_vel"] is not None:
+                    ob["s_vel"] = res["s_vel"]
+                else:
+                    names.remove("s_vel")
+                    del res["s_vel"]
+        for n in names:
+            setattr(bo, n, outbuf(n, self.out_shape(n, P, W, G, S_cap), R))
+        self._check(self.lib.scb_plan_batch(self.ctx, C.byref(bi), C.byref(bo)), "scb_plan_batch")
+        return res
+
+    # ------------------------------------------------------------------ HBM-resident buffers
+    def make_device_batch(self, inputs, G, outputs=ALL_OUTPUTS, S_cap=0, stages=0, x_cap=0.0, dt=0.0, opt=None):
+        """inputs: dict name -> torch CUDA tensor (dtype = ctx precision, contiguous).  Allocates
+        the output tensors once and returns (batch_in, batch_out, result_tensors): the structs can be
+        passed to run_device() any number of times without further allocation."""
+        import torch
+        tdt = torch.float64 if self.precision == abi.SCB_FP64 else torch.float32
+        dev = torch.device("cuda", self.device)
+        bi = abi.ScbBatchIn()
+        wx = inputs.get("wx")
+        if wx is not None:
+            P, W = wx.shape
+        else:
+            P, W = inputs["path_len"].shape[0], 2
+        bi.P, bi.W, bi.G = P, W, G
+        for name in ("wx", "wy", "start_angle", "vel_lo", "vel_hi", "vel_lo_grid", "vel_hi_grid", "acc_lo", "acc_hi",
+                     "vel_start", "vel_end", "path_len"):
+            t = inputs.get(name)
+            if t is not None:
+                assert t.is_cuda and t.dtype == tdt and t.is_contiguous(), name
+                setattr(bi, name, t.data_ptr())
+        bi.stages, bi.x_cap, bi.dt = stages, x_cap, dt
+        bi.opt = opt if opt is not None else default_opt()
+        res = {"status": torch.empty(P, dtype=torch.int32, device=dev),
+               "fail_stage": torch.empty(P, dtype=torch.int32, device=dev)}
+        bo = abi.ScbBatchOut()
+        bo.status, bo.fail_stage, bo.S_cap = res["status"].data_ptr(), res["fail_stage"].data_ptr(), S_cap
+        names = list(outputs)
+        if S_cap > 0:
+            names += [n for n in PER_SAMPLE if n not in names]
+            res["n_samples"] = torch.empty(P, dtype=torch.int32, device=dev)
+            bo.n_samples = res["n_samples"].data_ptr()
+        for n in names:
+            res[n] = torch.empty(self.out_shape(n, P, W, G, S_cap), dtype=tdt, device=dev)
+            setattr(bo, n, res[n].data_ptr())
+        return bi, bo, res
+
+    def run_device(self, bi, bo, sync=True):
+        self._check(self.lib.scb_plan_batch_device(self.ctx, C.byref(bi), C.byref(bo), 0 if sync else 1),
+                    "scb_plan_batch_device")
+
+    def pack_summary(self, P, res):
+        """Device-side pack of the 32-byte per-problem summary records (what the multi-GPU path gathers)."""
+        import torch
+        dst = torch.empty(P * C.sizeof(abi.ScbSummary), dtype=torch.uint8, device=res["status"].device)
+        ptr = lambda n: res[n].data_ptr() if n in res else None
+        self._check(self.lib.scb_pack_summary_device(self.ctx, P, ptr("status"), ptr("fail_stage"), ptr("T_total"),
+                                                     ptr("arclen_total"), ptr("cost"), dst.data_ptr()),
+                    "scb_pack_summary_device")
+        return dst
+
+
+SUMMARY_DTYPE = np.dtype([("status", np.int32), ("fail_stage", np.int32), ("T_total", np.float64),
+                          ("arclen_total", np.float64), ("cost", np.float64)])
+
+
+def shard_range(P, rank, world):
+    """Contiguous block of problems owned by `rank`: [lo, hi)."""
+    per = (P + world - 1) // world
+    lo = min(P, rank * per)
+    return lo, min(P, lo + per)
+
+
+def gather_summaries(local_bytes, world, group=None):
+    """all-gather of per-rank summary-record buffers (uint8 torch tensors of equal length) — the one
+    collective of the multi-GPU path.  NCCL when the tensors are CUDA, gloo on CPU."""
+    import torch
+    import torch.distributed as dist
+    if world == 1:
+        return local_bytes
+    out = torch.empty(world * local_bytes.numel(), dtype=torch.uint8, device=local_bytes.device)
+    dist.all_gather_into_tensor(out, local_bytes, group=group)
+    return out
