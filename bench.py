@@ -231,9 +231,9 @@ def main():
     rs = 8 if a.precision == "fp64" else 4
     d = 5
     # algorithmic bytes of each kernel: its mandatory inputs + outputs (DESIGN.md "Kernels")
-    kbytes = {"spline_ms": P * rs * (2 * W + 1 + 2 * (d + 1) * (W - 1) + 2),                # waypoints, angle -> ctrl, L, J
-              "toppra_ms": P * (rs * (1 + 6 + 3 * G) + 8),                                    # L, limits -> K_lo, K_hi, x, status
-              "param_ms": P * rs * (G + 2 + 2 * (d + 1) * (W - 1) + 6 * G + 1)}                # x, ctrl -> t, px, py, v, a, omega, T
+    kbytes = {"spline_ms": P * rs * (2 * W + 3 + 2 * (d + 1) * (W - 1) + 2 + 3 * G),   # waypoints, angle, end slopes -> ctrl, L, J, px, py, kappa
+              "toppra_ms": P * (rs * (1 + 6 + 3 * G) + 8),                              # L, limits -> K_lo, K_hi, x, status
+              "param_ms": P * rs * (2 * G + 3 + 4 * G + 1)}                             # x, kappa, L -> t, v, a, omega, T
     dom = max(kbytes, key=lambda k: stage_ms[k])
     peaks = {}
     try:
@@ -243,7 +243,7 @@ def main():
     peak = float(peaks.get("hbm_gbs", 6650.0))
     ach = kbytes[dom] / (stage_ms[dom] * 1e-3) / 1e9
     path_bytes = pl.algorithmic_bytes(P, W, G)
-    roof = {"bound": "hbm", "kernel": dom.replace("_ms", "_kernel"), "achieved": ach, "peak": peak, "unit": "GB/s",
+    roof = {"bound": "hbm", "kernel": {"spline_ms": "path_kernel", "toppra_ms": "toppra_kernel", "param_ms": "param_kernel"}[dom], "achieved": ach, "peak": peak, "unit": "GB/s",
             "frac": ach / peak, "traffic": None, "peak_source": "measured" if peaks else "fallback",
             "kernel_ms": stage_ms[dom], "algorithmic_bytes_per_launch": kbytes[dom],
             "path": {"algorithmic_bytes_per_step": path_bytes, "achieved": path_bytes / (ms_per_step * 1e-3) / 1e9,

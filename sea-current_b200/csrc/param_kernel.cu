@@ -4,8 +4,9 @@
 //                knot times by the trapezoid rule, clamped cubic spline q(t) through (t_i, q(s_i))
 //                (tp:geometric_path/piecewise_poly_path.cpp:102-187) — solved as the tridiagonal
 //                system it is (Thomas) instead of the reference's dense column-pivoted QR —
-//                then the per-gridpoint record: v, a (spline derivatives at the knots), the curve
-//                point at arc length q(s_i) and omega = v * kappa (sea_current.hpp:1017-1067).
+//                then the per-gridpoint record: v, a (spline derivatives at the knots) and
+//                omega = v * kappa (sea_current.hpp:1055-1067) with kappa at arc length q(s_i) as
+//                written by path_kernel.
 // sample_kernel  the uniform-dt stream of gen_vel_prof (sea_current.hpp:1235-1262), resample
 //                (sc:898-1005) and angular_velocity (sc:1055-1067).
 //
@@ -127,14 +128,15 @@ template <class R> struct Hermite1 {
   __device__ __forceinline__ R qd(R s) const { return ((R)3 * c0) * (s * s) + ((R)2 * c1) * s + c2; }
 };
 
-template <class R, int DEG>
+template <class R>
 __global__ void __launch_bounds__(64) param_kernel(ParamArgs g) {
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
   if (p >= g.P) return;
   const int P = g.P, G = g.G, N = G - 1;
   const R* X2 = (const R*)g.x;  // sdot^2
   R* tb = (R*)g.t_buf; R* Xb = (R*)g.X_buf; R* cpb = (R*)g.cp_buf;
-  R* o_t = (R*)g.t; R* o_v = (R*)g.v; R* o_a = (R*)g.a; R* o_px = (R*)g.px; R* o_py = (R*)g.py; R* o_om = (R*)g.omega;
+  R* o_t = (R*)g.t; R* o_v = (R*)g.v; R* o_a = (R*)g.a; R* o_om = (R*)g.omega;
+  const R* kap = (const R*)g.kappa;
   int status = g.status[p];
   Hermite1<R> hp;
   if (status == SCB_ST_OK) {
@@ -184,19 +186,12 @@ __global__ void __launch_bounds__(64) param_kernel(ParamArgs g) {
       const size_t o = (size_t)i * P + p;
       tb[o] = 0; Xb[o] = 0;
       if (o_t) o_t[o] = 0; if (o_v) o_v[o] = 0; if (o_a) o_a[o] = 0;
-      if (o_px) o_px[o] = 0; if (o_py) o_py[o] = 0; if (o_om) o_om[o] = 0;
+      if (o_om) o_om[o] = 0;
     }
     if (g.T_total) ((R*)g.T_total)[p] = 0;
     return;
   }
-  // ---- pass 2 (backward): back substitution, knot derivatives, geometry
-  ArcWalker<R, DEG> walk;
-  const bool geo = g.geometry != 0;
-  if (geo) {
-    const int nseg = g.W - 1;
-    walk.init((const R*)g.ctrl_x + (size_t)p * nseg * (DEG + 1), (const R*)g.ctrl_y + (size_t)p * nseg * (DEG + 1),
-              (const R*)g.table + (size_t)p * nseg * kTable, nseg);
-  }
+  // ---- pass 2 (backward): back substitution, knot derivatives, angular velocity
   R X_next = Xb[(size_t)N * P + p];
   R t_next = tb[(size_t)N * P + p];
   R q_next = hp.q(hp.s_at(N));
@@ -227,13 +222,7 @@ __global__ void __launch_bounds__(64) param_kernel(ParamArgs g) {
     if (o_t) o_t[o] = tb[o];
     if (o_v) o_v[o] = vi;
     if (o_a) o_a[o] = ai;
-    if (geo) {
-      R px, py, kap;
-      walk.locate(qi, px, py, kap);
-      if (o_px) o_px[o] = px;
-      if (o_py) o_py[o] = py;
-      if (o_om) o_om[o] = vi * kap;
-    }
+    if (o_om) o_om[o] = kap ? vi * kap[o] : (R)0;
   }
 }
 
@@ -318,8 +307,7 @@ __global__ void __launch_bounds__(64) sample_kernel(SampleArgs g) {
 
 template <class R> void launch_param(const ParamArgs& a, cudaStream_t st) {
   const int block = 64, grid = (a.P + block - 1) / block;
-  if (a.deg == 3) param_kernel<R, 3><<<grid, block, 0, st>>>(a);
-  else param_kernel<R, 5><<<grid, block, 0, st>>>(a);
+  param_kernel<R><<<grid, block, 0, st>>>(a);
 }
 template <class R> void launch_sample(const SampleArgs& a, cudaStream_t st) {
   const int block = 64, grid = (a.P + block - 1) / block;

@@ -21,7 +21,7 @@ struct Slot { void* p = nullptr; size_t bytes = 0; };
 
 enum SlotId {
   // scratch used when the caller did not ask for the corresponding output
-  SL_L, SL_TABLE, SL_CTRL_X, SL_CTRL_Y, SL_K_LO, SL_K_HI, SL_X, SL_T, SL_XB, SL_CP, SL_STATUS, SL_FAIL, SL_NS,
+  SL_L, SL_TABLE, SL_CTRL_X, SL_CTRL_Y, SL_K_LO, SL_K_HI, SL_X, SL_T, SL_XB, SL_CP, SL_KAPPA, SL_STATUS, SL_FAIL, SL_NS,
   // device mirrors of host inputs
   SL_IN_WX, SL_IN_WY, SL_IN_SA, SL_IN_VLO, SL_IN_VHI, SL_IN_VLG, SL_IN_VHG, SL_IN_ALO, SL_IN_AHI, SL_IN_VS,
   SL_IN_VE, SL_IN_PL,
@@ -88,9 +88,11 @@ int validate(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, int
   if (out->S_cap < 0 || out->S_cap > ctx->cfg.max_samples) return SCB_E_INVALID;
   if ((stages & SCB_STAGE_GEOMETRY) && !(stages & SCB_STAGE_TIMING) && (out->S_cap <= 0 || !out->n_samples || !out->s_pos)) return SCB_E_INVALID;
   if (!out->status) return SCB_E_INVALID;
-  // a spline kernel needs its per-warp state in shared memory
-  if ((stages & SCB_STAGE_SPLINE) &&
-      spline_smem_bytes(in->W, ctx->cfg.spline_mode, (int)real_size(ctx), 1) > 200 * 1024) return SCB_E_INVALID;
+  // the path kernel keeps one path's state in shared memory
+  if (stages & SCB_STAGE_SPLINE) {
+    int pb, th; bool tab; size_t sm;
+    if (!path_launch_shape(in->W, ctx->cfg.spline_mode, (int)real_size(ctx), pb, th, tab, sm)) return SCB_E_INVALID;
+  }
   return SCB_OK;
 }
 
@@ -109,19 +111,30 @@ int run_device(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, i
   int32_t* dFail = out->fail_stage;
   if (!dFail && (rc = ensure(ctx, SL_FAIL, (size_t)P * 4, (void**)&dFail))) return rc;
   SCB_CUDA(cudaEventRecord(ctx->ev[1], st));
+  const bool want_stream = out->S_cap > 0 && (out->s_time || out->s_pos || out->s_vel || out->s_acc || out->s_px ||
+                                              out->s_py || out->s_omega || out->n_samples);
+  void* dKappa = nullptr;
   if (do_spline) {
     const size_t nseg = W - 1;
+    int pb, th; bool tab_smem; size_t smb;
+    path_launch_shape(W, ctx->cfg.spline_mode, (int)rs, pb, th, tab_smem, smb);
+    const bool geo_stream = do_geo && want_stream;  // the uniform-dt sampler walks the tables in HBM
     if (!dL && (rc = ensure(ctx, SL_L, P * rs, &dL))) return rc;
-    if (!dTab && (rc = ensure(ctx, SL_TABLE, (size_t)P * nseg * kTable * rs, &dTab))) return rc;
-    if (do_geo) {
+    if (!dTab && (!tab_smem || geo_stream) && (rc = ensure(ctx, SL_TABLE, (size_t)P * nseg * kTable * rs, &dTab))) return rc;
+    if (geo_stream) {
       if (!dCx && (rc = ensure(ctx, SL_CTRL_X, (size_t)P * nseg * (deg + 1) * rs, &dCx))) return rc;
       if (!dCy && (rc = ensure(ctx, SL_CTRL_Y, (size_t)P * nseg * (deg + 1) * rs, &dCy))) return rc;
     }
-    SplineArgs a{};
-    a.P = P; a.W = W; a.wx = in->wx; a.wy = in->wy; a.start_angle = in->start_angle;
+    PathArgs a{};
+    a.P = P; a.W = W; a.G = G; a.wx = in->wx; a.wy = in->wy; a.start_angle = in->start_angle;
+    a.vel_start = in->vel_start; a.vel_end = in->vel_end;
     a.ctrl_x = dCx; a.ctrl_y = dCy; a.table = dTab; a.L = dL; a.cost = out->cost; a.status = out->status;
+    if (do_geo && do_timing) {
+      a.px = out->px; a.py = out->py;
+      if (out->omega) { if ((rc = ensure(ctx, SL_KAPPA, (size_t)G * P * rs, &dKappa))) return rc; a.kappa = dKappa; }
+    }
     a.opt = in->opt;
-    launch_spline<R>(a, ctx->cfg.spline_mode, st);
+    launch_path<R>(a, ctx->cfg.spline_mode, st);
     ++launches;
   } else {
     SCB_CUDA(cudaMemsetAsync(out->status, 0, (size_t)P * 4, st));
@@ -148,11 +161,10 @@ int run_device(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, i
     ++launches;
     SCB_CUDA(cudaEventRecord(ctx->ev[3], st));
     ParamArgs q{};
-    q.P = P; q.G = G; q.W = W; q.deg = deg; q.L = dL; q.vel_start = in->vel_start; q.vel_end = in->vel_end;
-    q.x = dX; q.ctrl_x = dCx; q.ctrl_y = dCy; q.table = dTab;
-    q.t = nullptr; q.v = out->v; q.a = out->a; q.px = out->px; q.py = out->py; q.omega = out->omega;
+    q.P = P; q.G = G; q.L = dL; q.vel_start = in->vel_start; q.vel_end = in->vel_end;
+    q.x = dX; q.kappa = dKappa;
+    q.t = nullptr; q.v = out->v; q.a = out->a; q.omega = out->omega;
     q.t_buf = dT; q.X_buf = dXb; q.cp_buf = dCp; q.T_total = out->T_total; q.status = out->status;
-    q.geometry = do_geo ? 1 : 0;
     launch_param<R>(q, st);
     ++launches;
   } else {
@@ -160,8 +172,6 @@ int run_device(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, i
     SCB_CUDA(cudaEventRecord(ctx->ev[3], st));
   }
   SCB_CUDA(cudaEventRecord(ctx->ev[4], st));
-  const bool want_stream = out->S_cap > 0 && (out->s_time || out->s_pos || out->s_vel || out->s_acc || out->s_px ||
-                                              out->s_py || out->s_omega || out->n_samples);
   if (want_stream && (do_timing || do_geo)) {
     int32_t* dNs = out->n_samples;
     if (!dNs && (rc = ensure(ctx, SL_NS, (size_t)P * 4, (void**)&dNs))) return rc;

@@ -30,13 +30,16 @@ template <> __device__ __forceinline__ double rsqrt_(double v) { return rsqrt(v)
 template <> __device__ __forceinline__ float rsqrt_(float v) { return rsqrtf(v); }
 
 // Kernel-argument bundles (plain pointers; R-typed buffers passed as void* and cast inside).
-struct SplineArgs {
-  int P, W;
+struct PathArgs {
+  int P, W, G, PB;                    // PB (paths per CTA) and table_in_smem are filled in by launch_path
   const void *wx, *wy, *start_angle;  // [P][W], [P][W], [P] or null
-  void *ctrl_x, *ctrl_y;              // [P][(W-1)*(d+1)]
-  void *table;                        // [P][(W-1)*101]
+  const void *vel_start, *vel_end;    // [P] or null: end slopes of the Hermite path q(s)
+  void *ctrl_x, *ctrl_y;              // [P][(W-1)*(d+1)] or null
+  void *table;                        // [P][(W-1)*101]; may be null only when the table fits in shared memory
   void *L, *cost;                     // [P]
+  void *px, *py, *kappa;              // [G][P] or null: curve point / curvature at arc length q(s_i)
   int32_t* status;                    // [P]  written: SCB_ST_OK or SCB_ST_ERR_BAD_PATH
+  int table_in_smem;
   scb_opt opt;
 };
 
@@ -53,15 +56,14 @@ struct ToppraArgs {
 };
 
 struct ParamArgs {
-  int P, G, W, deg;
+  int P, G;
   const void *L, *vel_start, *vel_end; // [P]
   const void *x;                       // [G][P]
-  const void *ctrl_x, *ctrl_y, *table; // spline data (null when geometry is off)
-  void *t, *v, *a, *px, *py, *omega;   // [G][P] outputs (any may be null, t/X scratch never null)
+  const void *kappa;                   // [G][P] or null
+  void *t, *v, *a, *omega;             // [G][P] outputs (any may be null)
   void *t_buf, *X_buf, *cp_buf;        // [G][P] scratch: knot times, spline unknowns, Thomas c'
   void *T_total;                       // [P]
   int32_t* status;
-  int geometry;
 };
 
 struct SampleArgs {
@@ -76,10 +78,10 @@ struct SampleArgs {
   int timing, geometry;                // timing off: s_pos / s_vel / n_samples are inputs
 };
 
-template <class R> void launch_spline(const SplineArgs& a, int spline_mode, cudaStream_t st);
+template <class R> void launch_path(const PathArgs& a, int spline_mode, cudaStream_t st);
 template <class R> void launch_toppra(const ToppraArgs& a, cudaStream_t st);
 template <class R> void launch_param(const ParamArgs& a, cudaStream_t st);
 template <class R> void launch_sample(const SampleArgs& a, cudaStream_t st);
-size_t spline_smem_bytes(int W, int spline_mode, int real_size, int warps);
+bool path_launch_shape(int W, int spline_mode, int real_size, int& PB, int& threads, bool& table_in_smem, size_t& smem);
 
 }  // namespace scb
