@@ -52,7 +52,10 @@ def _scales(ref, ok):
     # their condition number w.r.t. the knot data is ~ L / h_min^2 (measured: a 1e-16 relative input
     # perturbation moves `a` by ~30 eps L / h^2 in the oracle itself), so `a` gets that absolute term.
     cond_a = 2000 * np.finfo(np.float64).eps * L / h_min ** 2
-    return sc, cond_a
+    # ... and the knot velocities inherit it through v_i = dq/h - h/3 (2 X_i + X_{i+1}): h_i * cond_a
+    h = np.diff(t, axis=0) if t.shape[0] > 1 else T[None, :]
+    cond_v = np.vstack([h, h[-1:]]) * cond_a[None, :]
+    return sc, cond_a, cond_v
 
 
 def _check(res, ref, rtol, names):
@@ -62,13 +65,15 @@ def _check(res, ref, rtol, names):
     ok = ref["status"] == 0
     if not ok.any():
         return
-    sc, cond_a = _scales(ref, ok)
+    sc, cond_a, cond_v = _scales(ref, ok)
     for n in names:
         if n in GRID:
             g, w = res[n][:, ok], ref[n][:, ok]
             tol = rtol * np.maximum(np.abs(w), 1e-3 * sc[n][None, :])
             if n == "a":
                 tol = tol + cond_a[None, :]
+            if n == "v":
+                tol = tol + cond_v
             if n == "omega":  # curvature at arc length q: q is resolved to eps * L, i.e. eps * (#segments) of a segment
                 tol = tol * max(1.0, (res["ctrl_x"].shape[1] / 4) / 20.0)
         elif n in ("T_total", "cost", "arclen_total"):
