@@ -108,6 +108,15 @@ enum {
                              s_omega is wanted) are INPUTS: the positions to resample at. */
 };
 
+/* Stage-LP back ends of the toppra passes (tp:solver/seidel.cpp:265-347).  Both return the same
+ * optimum (it is unique) and the same feasibility verdicts; tests compare them LP by LP. */
+enum {
+  SCB_LP_DEFAULT = 0,      /* = SCB_LP_CLOSED_FORM */
+  SCB_LP_SEIDEL = 1,       /* the reference's incremental sequence, operation for operation: given the
+                              same path length, bit-identical to the reference's FP64 results; ~6x slower */
+  SCB_LP_CLOSED_FORM = 2   /* eliminate u: three determinants and six quotients per stage */
+};
+
 typedef struct scb_batch_in {
   int32_t P, W, G;          /* problems, waypoints per problem (>= 2), toppra gridpoints (>= 2;
                                the reference's default is 101, tp:algorithm.hpp:140) */
@@ -124,6 +133,7 @@ typedef struct scb_batch_in {
   const void* vel_end;      /* real [P] or NULL (= 0) */
   const void* path_len;     /* real [P]: pos_end - pos_start, read only when SCB_STAGE_SPLINE is off */
   int32_t stages;           /* SCB_STAGE_* bitmask; 0 = all */
+  int32_t lp_mode;          /* SCB_LP_*: how the stage LPs of toppra are solved; 0 = default */
   double x_cap;             /* upper bound of sdot^2 in the backward pass; 0 = reference's 100
                                (tp:algorithm.hpp:152 m_initXBound) */
   double dt;                /* uniform-dt stream period; 0 = reference's 0.02 (sc:1199) */

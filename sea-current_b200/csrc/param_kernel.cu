@@ -118,42 +118,45 @@ template <class R, int DEG> struct ArcWalker {
   }
 };
 
-template <class R> struct Hermite1 {
-  R c0, c1, c2, step; int N;
-  __device__ __forceinline__ void init(R L, R vs, R ve, int N_) {
-    c2 = vs; c0 = (ve - (R)2 * L + vs); c1 = (ve - vs - (R)3 * c0) / (R)2; N = N_; step = (R)1 / (R)N_;
+struct Hermite1 {  // FP64 in both precision modes, like the toppra kernel
+  double c0, c1, c2, step; int N;
+  __device__ __forceinline__ void init(double L, double vs, double ve, int N_) {
+    c2 = vs; c0 = (ve - 2.0 * L + vs); c1 = (ve - vs - 3.0 * c0) / 2.0; N = N_; step = 1.0 / (double)N_;
   }
-  __device__ __forceinline__ R s_at(int i) const { return i == N ? (R)1 : (R)i * step; }
-  __device__ __forceinline__ R q(R s) const { return c0 * (s * s * s) + c1 * (s * s) + c2 * s; }
-  __device__ __forceinline__ R qd(R s) const { return ((R)3 * c0) * (s * s) + ((R)2 * c1) * s + c2; }
+  __device__ __forceinline__ double s_at(int i) const { return i == N ? 1.0 : (double)i * step; }
+  __device__ __forceinline__ double q(double s) const { return c0 * (s * s * s) + c1 * (s * s) + c2 * s; }
+  __device__ __forceinline__ double qd(double s) const { return (3.0 * c0) * (s * s) + (2.0 * c1) * s + c2; }
 };
 
-template <class R>
+// `S` is the storage type of the caller's arrays; the recurrences (knot times, Thomas) run in FP64
+// and their scratch (t_buf, X_buf, cp_buf) is always double.
+template <class S>
 __global__ void __launch_bounds__(64) param_kernel(ParamArgs g) {
+  typedef double R;
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
   if (p >= g.P) return;
   const int P = g.P, G = g.G, N = G - 1;
-  const R* X2 = (const R*)g.x;  // sdot^2
+  const S* X2 = (const S*)g.x;  // sdot^2
   R* tb = (R*)g.t_buf; R* Xb = (R*)g.X_buf; R* cpb = (R*)g.cp_buf;
-  R* o_t = (R*)g.t; R* o_v = (R*)g.v; R* o_a = (R*)g.a; R* o_om = (R*)g.omega;
-  const R* kap = (const R*)g.kappa;
+  S* o_t = (S*)g.t; S* o_v = (S*)g.v; S* o_a = (S*)g.a; S* o_om = (S*)g.omega;
+  const S* kap = (const S*)g.kappa;
   int status = g.status[p];
-  Hermite1<R> hp;
+  Hermite1 hp;
   if (status == SCB_ST_OK) {
-    hp.init(((const R*)g.L)[p], g.vel_start ? ((const R*)g.vel_start)[p] : (R)0,
-            g.vel_end ? ((const R*)g.vel_end)[p] : (R)0, N);
+    hp.init((R)((const S*)g.L)[p], g.vel_start ? (R)((const S*)g.vel_start)[p] : 0.0,
+            g.vel_end ? (R)((const S*)g.vel_end)[p] : 0.0, N);
     // ---- pass 1: knot times + Thomas forward elimination
-    const R sd0 = sqrt(X2[p]);
+    const R sd0 = sqrt((R)X2[p]);
     R sd_prev = sd0, t = 0, t_prev = 0, t_pp = 0;
     R q_pp = 0, q_prev = hp.q(hp.s_at(0)), s_prev = hp.s_at(0);
     R cp_prev = 0, b_prev = 0;
     const R bc0 = hp.qd(hp.s_at(0)) * sd0;
     tb[p] = 0;
     for (int i = 1; i <= N; ++i) {
-      const R s = hp.s_at(i), sd = sqrt(X2[(size_t)i * P + p]);
+      const R s = hp.s_at(i), sd = sqrt((R)X2[(size_t)i * P + p]);
       const R avg = (sd_prev + sd) / 2;
-      const R dt = avg > (R)1e-8 ? (s - s_prev) / avg : (R)5;
-      if (dt < (R)1e-8) status = SCB_ST_ERR_TIME_KNOTS;
+      const R dt = avg > 1e-8 ? (s - s_prev) / avg : 5.0;
+      if (dt < 1e-8) status = SCB_ST_ERR_TIME_KNOTS;
       t = t_prev + dt;
       tb[(size_t)i * P + p] = t;
       const R qi = hp.q(s);
@@ -185,20 +188,19 @@ __global__ void __launch_bounds__(64) param_kernel(ParamArgs g) {
     for (int i = 0; i < G; ++i) {
       const size_t o = (size_t)i * P + p;
       tb[o] = 0; Xb[o] = 0;
-      if (o_t) o_t[o] = 0; if (o_v) o_v[o] = 0; if (o_a) o_a[o] = 0;
-      if (o_om) o_om[o] = 0;
+      if (o_t) o_t[o] = 0; if (o_v) o_v[o] = 0; if (o_a) o_a[o] = 0; if (o_om) o_om[o] = 0;
     }
-    if (g.T_total) ((R*)g.T_total)[p] = 0;
+    if (g.T_total) ((S*)g.T_total)[p] = 0;
     return;
   }
   // ---- pass 2 (backward): back substitution, knot derivatives, angular velocity
   R X_next = Xb[(size_t)N * P + p];
   R t_next = tb[(size_t)N * P + p];
   R q_next = hp.q(hp.s_at(N));
-  if (g.T_total) ((R*)g.T_total)[p] = t_next - tb[p];
+  if (g.T_total) ((S*)g.T_total)[p] = (S)(t_next - tb[p]);
   for (int i = N; i >= 0; --i) {
     const size_t o = (size_t)i * P + p;
-    R vi, ai, qi;
+    R vi, ai;
     if (i == N) {
       // knot N is evaluated on the last segment at ds = h (piecewise_poly_path.cpp:240-252)
       const R Xi = Xb[(size_t)(N - 1) * P + p] - cpb[(size_t)(N - 1) * P + p] * X_next;
@@ -208,7 +210,6 @@ __global__ void __launch_bounds__(64) param_kernel(ParamArgs g) {
       const R k0 = (X_next - Xi) / (3 * h), k1 = Xi, k2 = (q_next - qm) / h - h / 3 * (2 * Xi + X_next);
       vi = (k0 * 3) * (h * h) + (k1 * 2) * h + k2;
       ai = ((k0 * 3) * 2) * h + k1 * 2;
-      qi = q_next;
     } else {
       const R Xi = Xb[o] - cpb[o] * X_next;
       Xb[o] = Xi;
@@ -216,13 +217,12 @@ __global__ void __launch_bounds__(64) param_kernel(ParamArgs g) {
       const R h = t_next - ti;
       vi = (q_next - qv) / h - h / 3 * (2 * Xi + X_next);
       ai = Xi * 2;
-      qi = qv;
       X_next = Xi; t_next = ti; q_next = qv;
     }
-    if (o_t) o_t[o] = tb[o];
-    if (o_v) o_v[o] = vi;
-    if (o_a) o_a[o] = ai;
-    if (o_om) o_om[o] = kap ? vi * kap[o] : (R)0;
+    if (o_t) o_t[o] = (S)tb[o];
+    if (o_v) o_v[o] = (S)vi;
+    if (o_a) o_a[o] = (S)ai;
+    if (o_om) o_om[o] = kap ? (S)(vi * (R)kap[o]) : (S)0;
   }
 }
 
@@ -244,43 +244,43 @@ __global__ void __launch_bounds__(64) sample_kernel(SampleArgs g) {
                 (const R*)g.table + (size_t)p * nseg * kTable, nseg);
     }
     if (g.timing) {
-      const R* tb = (const R*)g.t_buf; const R* Xb = (const R*)g.X_buf;
-      Hermite1<R> hp;
-      hp.init(((const R*)g.L)[p], g.vel_start ? ((const R*)g.vel_start)[p] : (R)0,
-              g.vel_end ? ((const R*)g.vel_end)[p] : (R)0, N);
-      const R t0 = tb[p], T = tb[(size_t)N * P + p];
-      const int S = (int)ceil((double)(T - t0) / g.dt);  // sc:1237
+      const double* tb = (const double*)g.t_buf; const double* Xb = (const double*)g.X_buf;
+      Hermite1 hp;
+      hp.init((double)((const R*)g.L)[p], g.vel_start ? (double)((const R*)g.vel_start)[p] : 0.0,
+              g.vel_end ? (double)((const R*)g.vel_end)[p] : 0.0, N);
+      const double t0 = tb[p], T = tb[(size_t)N * P + p];
+      const int S = (int)ceil((T - t0) / g.dt);  // sc:1237
       g.n_samples[p] = S;
       n = S < S_cap ? S : S_cap;
-      const R stp = S > 1 ? (T - t0) / (R)(S - 1) : (R)0;
+      const double stp = S > 1 ? (T - t0) / (double)(S - 1) : 0.0;
       int j = -1;
-      R tj = 0, k0 = 0, k1 = 0, k2 = 0, k3 = 0, t_up = t0;
+      double tj = 0, k0 = 0, k1 = 0, k2 = 0, k3 = 0, t_up = t0;
       for (int i = 0; i < n; ++i) {
-        const R time = (i == S - 1) ? T : t0 + (R)i * stp;  // Eigen LinSpaced
+        const double time = (i == S - 1) ? T : t0 + (double)i * stp;  // Eigen LinSpaced
         if (j < 0 || (j < N - 1 && t_up <= time)) {
           if (j < 0) j = 0;
           while (j < N - 1 && tb[(size_t)(j + 1) * P + p] <= time) ++j;
           tj = tb[(size_t)j * P + p]; t_up = tb[(size_t)(j + 1) * P + p];
-          const R Xj = Xb[(size_t)j * P + p], Xn = Xb[(size_t)(j + 1) * P + p];
-          const R qj = hp.q(hp.s_at(j)), qn = hp.q(hp.s_at(j + 1));
-          const R h = t_up - tj;
+          const double Xj = Xb[(size_t)j * P + p], Xn = Xb[(size_t)(j + 1) * P + p];
+          const double qj = hp.q(hp.s_at(j)), qn = hp.q(hp.s_at(j + 1));
+          const double h = t_up - tj;
           k0 = (Xn - Xj) / (3 * h); k1 = Xj; k2 = (qn - qj) / h - h / 3 * (2 * Xj + Xn); k3 = qj;
         }
-        const R ds = time - tj;
-        const R pos = k0 * (ds * ds * ds) + k1 * (ds * ds) + k2 * ds + k3;
-        const R vel = (k0 * 3) * (ds * ds) + (k1 * 2) * ds + k2;
-        const R acc = ((k0 * 3) * 2) * ds + k1 * 2;
+        const double ds = time - tj;
+        const double pos = k0 * (ds * ds * ds) + k1 * (ds * ds) + k2 * ds + k3;
+        const double vel = (k0 * 3) * (ds * ds) + (k1 * 2) * ds + k2;
+        const double acc = ((k0 * 3) * 2) * ds + k1 * 2;
         const size_t o = (size_t)i * P + p;
-        if (o_time) o_time[o] = time;
-        if (o_pos) o_pos[o] = pos;
-        if (o_vel) o_vel[o] = vel;
-        if (o_acc) o_acc[o] = acc;
+        if (o_time) o_time[o] = (R)time;
+        if (o_pos) o_pos[o] = (R)pos;
+        if (o_vel) o_vel[o] = (R)vel;
+        if (o_acc) o_acc[o] = (R)acc;
         if (geo) {
           R px, py, kap;
-          walk.locate(pos, px, py, kap);
+          walk.locate((R)pos, px, py, kap);
           if (o_px) o_px[o] = px;
           if (o_py) o_py[o] = py;
-          if (o_om) o_om[o] = vel * kap;
+          if (o_om) o_om[o] = (R)(vel * (double)kap);
         }
       }
     } else if (geo) {  // resample / angular_velocity of caller-supplied positions
@@ -307,7 +307,7 @@ __global__ void __launch_bounds__(64) sample_kernel(SampleArgs g) {
 
 template <class R> void launch_param(const ParamArgs& a, cudaStream_t st) {
   const int block = 64, grid = (a.P + block - 1) / block;
-  param_kernel<R><<<grid, block, 0, st>>>(a);
+  param_kernel<R><<<grid, block, 0, st>>>(a);  // R = storage type
 }
 template <class R> void launch_sample(const SampleArgs& a, cudaStream_t st) {
   const int block = 64, grid = (a.P + block - 1) / block;

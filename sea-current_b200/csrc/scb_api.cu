@@ -79,6 +79,7 @@ int validate(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, int
   if (!ctx || !in || !out) return SCB_E_INVALID;
   stages = in->stages ? in->stages : (SCB_STAGE_SPLINE | SCB_STAGE_TIMING | SCB_STAGE_GEOMETRY);
   if (in->P < 0 || in->P > ctx->cfg.max_problems) return SCB_E_INVALID;
+  if (in->lp_mode < SCB_LP_DEFAULT || in->lp_mode > SCB_LP_CLOSED_FORM) return SCB_E_INVALID;
   if ((stages & SCB_STAGE_SPLINE) && (in->W < 2 || in->W > ctx->cfg.max_waypoints || !in->wx || !in->wy)) return SCB_E_INVALID;
   if ((stages & SCB_STAGE_TIMING) && (in->G < 2 || in->G > ctx->cfg.max_gridpoints)) return SCB_E_INVALID;
   if ((stages & SCB_STAGE_TIMING) && (!in->acc_lo || !in->acc_hi)) return SCB_E_INVALID;
@@ -141,29 +142,34 @@ int run_device(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, i
     dL = (void*)in->path_len;
   }
   SCB_CUDA(cudaEventRecord(ctx->ev[2], st));
-  void *dT = out->t, *dXb = nullptr, *dCp = nullptr;
+  // internal state of the recurrences is FP64 in both precision modes: in FP64 mode the caller's
+  // K_lo / K_hi / t arrays double as that state, in FP32 mode it lives in scratch
+  const bool f64 = sizeof(R) == 8;
+  void *dT = f64 ? out->t : nullptr, *dXb = nullptr, *dCp = nullptr;
   if (do_timing) {
-    void *dKlo = out->K_lo, *dKhi = out->K_hi, *dX = out->x;
-    const size_t gp = (size_t)G * P * rs;
-    if (!dKlo && (rc = ensure(ctx, SL_K_LO, gp, &dKlo))) return rc;
-    if (!dKhi && (rc = ensure(ctx, SL_K_HI, gp, &dKhi))) return rc;
+    void *dKlo = f64 ? out->K_lo : nullptr, *dKhi = f64 ? out->K_hi : nullptr, *dX = out->x;
+    const size_t gp = (size_t)G * P * rs, gp8 = (size_t)G * P * 8;
+    if (!dKlo && (rc = ensure(ctx, SL_K_LO, gp8, &dKlo))) return rc;
+    if (!dKhi && (rc = ensure(ctx, SL_K_HI, gp8, &dKhi))) return rc;
     if (!dX && (rc = ensure(ctx, SL_X, gp, &dX))) return rc;
-    if (!dT && (rc = ensure(ctx, SL_T, gp, &dT))) return rc;
-    if ((rc = ensure(ctx, SL_XB, gp, &dXb))) return rc;
-    if ((rc = ensure(ctx, SL_CP, gp, &dCp))) return rc;
+    if (!dT && (rc = ensure(ctx, SL_T, gp8, &dT))) return rc;
+    if ((rc = ensure(ctx, SL_XB, gp8, &dXb))) return rc;
+    if ((rc = ensure(ctx, SL_CP, gp8, &dCp))) return rc;
     ToppraArgs t{};
     t.P = P; t.G = G; t.L = dL; t.vel_lo = in->vel_lo; t.vel_hi = in->vel_hi;
     t.vel_lo_grid = in->vel_lo_grid; t.vel_hi_grid = in->vel_hi_grid;
     t.acc_lo = in->acc_lo; t.acc_hi = in->acc_hi; t.vel_start = in->vel_start; t.vel_end = in->vel_end;
     t.x_cap = in->x_cap > 0 ? in->x_cap : 100.0;
     t.K_lo = dKlo; t.K_hi = dKhi; t.x = dX; t.status = out->status; t.fail_stage = dFail;
-    launch_toppra<R>(t, st);
+    if (!f64) { t.K_lo_out = out->K_lo; t.K_hi_out = out->K_hi; }
+    if (in->lp_mode == SCB_LP_SEIDEL) launch_toppra<R>(t, st);
+    else launch_toppra_fast<R>(t, st);
     ++launches;
     SCB_CUDA(cudaEventRecord(ctx->ev[3], st));
     ParamArgs q{};
     q.P = P; q.G = G; q.L = dL; q.vel_start = in->vel_start; q.vel_end = in->vel_end;
     q.x = dX; q.kappa = dKappa;
-    q.t = nullptr; q.v = out->v; q.a = out->a; q.omega = out->omega;
+    q.t = f64 ? nullptr : out->t; q.v = out->v; q.a = out->a; q.omega = out->omega;
     q.t_buf = dT; q.X_buf = dXb; q.cp_buf = dCp; q.T_total = out->T_total; q.status = out->status;
     launch_param<R>(q, st);
     ++launches;

@@ -51,7 +51,9 @@ struct ToppraArgs {
   const void *acc_lo, *acc_hi;         // [P]
   const void *vel_start, *vel_end;     // [P] or null
   double x_cap;
-  void *K_lo, *K_hi, *x;               // [G][P]
+  void *K_lo, *K_hi;                   // double [G][P], always (internal state; the FP64 outputs themselves)
+  void *K_lo_out, *K_hi_out;           // S [G][P] or null: FP32-mode copies for the caller
+  void *x;                             // S [G][P]
   int32_t *status, *fail_stage;        // [P]; status is read (skip if already failed) and written
 };
 
@@ -80,6 +82,7 @@ struct SampleArgs {
 
 template <class R> void launch_path(const PathArgs& a, int spline_mode, cudaStream_t st);
 template <class R> void launch_toppra(const ToppraArgs& a, cudaStream_t st);
+template <class R> void launch_toppra_fast(const ToppraArgs& a, cudaStream_t st);
 template <class R> void launch_param(const ParamArgs& a, cudaStream_t st);
 template <class R> void launch_sample(const SampleArgs& a, cudaStream_t st);
 bool path_launch_shape(int W, int spline_mode, int real_size, int& PB, int& threads, bool& table_in_smem, size_t& smem);

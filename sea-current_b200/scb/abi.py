@@ -9,6 +9,7 @@ SCB_FP64, SCB_FP32 = 0, 1
 SCB_REF_CUBIC, SCB_LAU_QUINTIC = 0, 1
 ARCLEN_TABLE = 101
 STAGE_SPLINE, STAGE_TIMING, STAGE_GEOMETRY = 1, 2, 4
+LP_DEFAULT, LP_SEIDEL, LP_CLOSED_FORM = 0, 1, 2
 
 ST_OK, ST_ERR_UNKNOWN, ST_ERR_FAIL_CONTROLLABLE, ST_ERR_FAIL_FORWARD_PASS = 0, 1, 2, 3
 ST_ERR_UNINITIALIZED, ST_ERR_FAIL_FEASIBLE = 4, 5
@@ -34,7 +35,7 @@ class ScbBatchIn(C.Structure):
                 ("vel_lo_grid", C.c_void_p), ("vel_hi_grid", C.c_void_p),
                 ("acc_lo", C.c_void_p), ("acc_hi", C.c_void_p),
                 ("vel_start", C.c_void_p), ("vel_end", C.c_void_p),
-                ("path_len", C.c_void_p), ("stages", C.c_int32),
+                ("path_len", C.c_void_p), ("stages", C.c_int32), ("lp_mode", C.c_int32),
                 ("x_cap", C.c_double), ("dt", C.c_double), ("opt", ScbOpt)]
 
 

@@ -99,7 +99,7 @@ class BatchPlanner:
     # ------------------------------------------------------------------ host buffers
     def plan(self, wx=None, wy=None, vel_lo=None, vel_hi=None, acc_lo=None, acc_hi=None, G=101, start_angle=None,
              vel_lo_grid=None, vel_hi_grid=None, vel_start=None, vel_end=None, path_len=None, stages=0,
-             outputs=ALL_OUTPUTS, S_cap=0, x_cap=0.0, dt=0.0, opt=None, out_buffers=None, resample_at=None):
+             outputs=ALL_OUTPUTS, S_cap=0, x_cap=0.0, dt=0.0, opt=None, out_buffers=None, resample_at=None, lp_mode=0):
         """Host arrays in, host arrays out (scb_plan_batch).  `out_buffers` lets a caller pass
         preallocated (e.g. pinned) numpy arrays keyed by output name."""
         R = self.real
@@ -128,7 +128,7 @@ class BatchPlanner:
         bi.acc_lo, bi.acc_hi = arr(acc_lo, (P,)), arr(acc_hi, (P,))
         bi.vel_start, bi.vel_end = arr(vel_start, (P,)), arr(vel_end, (P,))
         bi.path_len = arr(path_len, (P,))
-        bi.stages, bi.x_cap, bi.dt = stages, x_cap, dt
+        bi.stages, bi.x_cap, bi.dt, bi.lp_mode = stages, x_cap, dt, lp_mode
         bi.opt = opt if opt is not None else default_opt()
         res = BatchResult()
         bo = abi.ScbBatchOut()
@@ -166,7 +166,7 @@ class BatchPlanner:
         return res
 
     # ------------------------------------------------------------------ HBM-resident buffers
-    def make_device_batch(self, inputs, G, outputs=ALL_OUTPUTS, S_cap=0, stages=0, x_cap=0.0, dt=0.0, opt=None):
+    def make_device_batch(self, inputs, G, outputs=ALL_OUTPUTS, S_cap=0, stages=0, x_cap=0.0, dt=0.0, opt=None, lp_mode=0):
         """inputs: dict name -> torch CUDA tensor (dtype = ctx precision, contiguous).  Allocates
         the output tensors once and returns (batch_in, batch_out, result_tensors): the structs can be
         passed to run_device() any number of times without further allocation."""
@@ -186,7 +186,7 @@ class BatchPlanner:
             if t is not None:
                 assert t.is_cuda and t.dtype == tdt and t.is_contiguous(), name
                 setattr(bi, name, t.data_ptr())
-        bi.stages, bi.x_cap, bi.dt = stages, x_cap, dt
+        bi.stages, bi.x_cap, bi.dt, bi.lp_mode = stages, x_cap, dt, lp_mode
         bi.opt = opt if opt is not None else default_opt()
         res = {"status": torch.empty(P, dtype=torch.int32, device=dev),
                "fail_stage": torch.empty(P, dtype=torch.int32, device=dev)}
