@@ -56,7 +56,7 @@ __device__ __forceinline__ void calc_tangent(R w0x, R w0y, R w1x, R w1y, R w2x, 
 __host__ __device__ inline size_t path_smem_reals(int W, int deg, int PB, bool table_in_smem) {
   const size_t nseg = W - 1;
   size_t per = (size_t)(deg == 5 ? 29 : 4) * W                       // per-waypoint arrays
-               + nseg * (size_t)(2 * (deg + 1) + 2 * deg + 2 * (deg + 1) + 2 + (deg == 5 ? 13 : 0))
+               + nseg * (size_t)(2 * (deg + 1) + 2 * deg + 2 * (deg + 1) + 3 + (deg == 5 ? 13 : 0))
                + 8;                                                   // per-path scalars
   if (table_in_smem) per += nseg * kTable;
   return per * PB + (deg == 5 ? 32 * 13 : 0);
@@ -91,11 +91,14 @@ __global__ void __launch_bounds__(512, 1) path_kernel(PathArgs g) {
   int* bad = (int*)smem_raw;        // [PB]
   int* improve = bad + 32;          // [PB]
   Carve<R> sm((R*)(smem_raw + kPathSmemIntBytes));
+  // cumulative segment ends are FP64 in both precision modes (first carve: 8-byte aligned): the arc
+  // position of a gridpoint is resolved against them before it is narrowed to a segment-local R
+  double* segend = (double*)sm.take((size_t)PB * nseg * (sizeof(double) / sizeof(R)));
   R* wx = sm.take(PB * W); R* wy = sm.take(PB * W); R* tx = sm.take(PB * W); R* ty = sm.take(PB * W);
   R* cx = sm.take(PB * nseg * NC); R* cy = sm.take(PB * nseg * NC);
   R* hx = sm.take(PB * nseg * DEG); R* hy = sm.take(PB * nseg * DEG);
   R* ax = sm.take(PB * nseg * NC); R* ay = sm.take(PB * nseg * NC);
-  R* segtot = sm.take(PB * nseg); R* segend = sm.take(PB * nseg);
+  R* segtot = sm.take(PB * nseg);
   R* scal = sm.take(PB * 8);  // per path: 0 J, 1 bestJ, 2 gemax, 3 gwmax, 4 L, 5 vel_start, 6 vel_end
 
   // ---- P0: load waypoints (coalesced: the CTA's slice of [P][W] is contiguous), validate

@@ -70,14 +70,14 @@
   __syncthreads();
   if (tid < PBa) {
     const int p = p0 + tid;
-    R acc = 0;
-    for (int s = 0; s < nseg; ++s) { acc += segtot[tid * nseg + s]; segend[tid * nseg + s] = acc; }
+    double acc = 0;
+    for (int s = 0; s < nseg; ++s) { acc += (double)segtot[tid * nseg + s]; segend[tid * nseg + s] = acc; }
     const bool ok = !bad[tid] && acc > 0 && isfinite(acc);
     if (!ok) bad[tid] = 1;
-    scal[tid * 8 + 4] = acc;
+    scal[tid * 8 + 4] = (R)acc;
     scal[tid * 8 + 5] = g.vel_start ? ((const R*)g.vel_start)[p] : (R)0;
     scal[tid * 8 + 6] = g.vel_end ? ((const R*)g.vel_end)[p] : (R)0;
-    ((R*)g.L)[p] = ok ? acc : (R)0;
+    ((R*)g.L)[p] = ok ? (R)acc : (R)0;
     if (g.cost) ((R*)g.cost)[p] = ok ? scal[tid * 8 + 1] : (R)0;
     g.status[p] = ok ? SCB_ST_OK : SCB_ST_ERR_BAD_PATH;
   }
@@ -95,7 +95,7 @@
   //      [G][P] arrays are PB-contiguous.
   if (g.px || g.py || g.kappa) {
     const int G = g.G, N = G - 1;
-    const R step = (R)1 / (R)N;
+    const double step = 1.0 / (double)N;
     R* o_px = (R*)g.px; R* o_py = (R*)g.py; R* o_k = (R*)g.kappa;
     for (int it = tid; it < PBa * G; it += T) {
       const int i = it / PBa, pl = it - i * PBa;
@@ -104,17 +104,18 @@
         if (o_px) o_px[o] = 0; if (o_py) o_py[o] = 0; if (o_k) o_k[o] = 0;
         continue;
       }
-      HermiteQ<R> hq;
-      const R Ltot = scal[pl * 8 + 4];
-      hq.init(Ltot, scal[pl * 8 + 5], scal[pl * 8 + 6]);
-      R q = hq.q(i == N ? (R)1 : (R)i * step);
-      q = fmin(fmax(q, (R)0), Ltot);
+      // q(s_i) in FP64 against the FP64 segment ends, whatever R is (three DFMAs per gridpoint)
+      HermiteQ<double> hq;
+      const double* se_ = segend + pl * nseg;
+      const double Ltot = se_[nseg - 1];
+      hq.init(Ltot, (double)scal[pl * 8 + 5], (double)scal[pl * 8 + 6]);
+      double q = hq.q(i == N ? 1.0 : (double)i * step);
+      q = fmin(fmax(q, 0.0), Ltot);
       // segment: first j with q <= segend[j]
-      const R* se_ = segend + pl * nseg;
       int lo = 0, hi = nseg - 1;
       while (lo < hi) { const int m = (lo + hi) >> 1; if (q <= se_[m]) hi = m; else lo = m + 1; }
       const int sgl = lo, sg = pl * nseg + sgl;
-      const R r = q - (sgl > 0 ? se_[sgl - 1] : (R)0);
+      const R r = (R)(q - (sgl > 0 ? se_[sgl - 1] : 0.0));
       const R* c = tab + sg * kTable;
       int kl = 0, kh = kSub;
       while (kh - kl > 1) { const int m = (kl + kh) >> 1; if (c[m] <= r) kl = m; else kh = m; }
