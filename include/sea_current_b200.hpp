@@ -1,0 +1,458 @@
+// sea_current_b200.hpp — host-side drop-in for the planning hot path of sea_current.hpp.
+//
+// Keeps namespace turtle::sc and the call sequence a sea-current caller writes
+// (examples/json_test.cpp:28-65, examples/zmq_test.cpp:64-92):
+//
+//     bezier_spline pad = bezier_spline::from_path(path, space);      // sc:402, sc:599-683
+//     arclength_data ad = pad.arclength();                            // sc:413, sc:767-896
+//     velocity_profile prof = gen_vel_prof<1>(pos_end, pos_start, vel_end, vel_start,
+//                                             vel_lim, acc_min, acc_max);   // sc:1191-1265
+//     bezier_spline re = pad.resample(prof.pos[0], ad, true);         // sc:419, sc:898-1005
+//     std::vector<float> w = re.angular_velocity(prof);               // sc:416, sc:1055-1067
+//     json j = serialize_path_to_json(re, prof, ad, w);               // sc:1423-1457
+//
+// Every numeric step is a batch-of-1 call into the C ABI of include/seacurrent_b200.h, i.e. a
+// CUDA kernel launch on a B200; nothing is computed on the host and there is no CPU fallback:
+// without libseacurrent_b200.so and an sm_100 device every entry point throws.  Batched callers
+// should use turtle::sc::b200::batch_planner (or the C ABI directly) instead: one call plans
+// thousands of paths.
+//
+// The reference's value types come from Eigen (Vector2f, VectorXf, Eigen::Vector<T, N>) and
+// toppra (toppra::Vector).  Eigen is not part of this image, so this header carries small
+// stand-ins with the members the call sequence uses; when <Eigen/Core> has been included first
+// they are not defined and the real ones are used.
+//
+// Deliberate differences from the reference (DESIGN.md "Deviations"):
+//   * bezier_spline::pts / positions are empty after from_path: the 10,001-point-per-segment
+//     preview (sc:679) feeds nothing downstream.  resample() fills pts as in the reference.
+//   * resample() inverts the arc-length table exactly instead of through the float Chebyshev
+//     least-squares fit (sc:1109-1170); it does not print (sc:946-947, 999-1002).
+//   * gen_vel_prof throws planning_error when toppra's verdict is not OK; the reference fetches
+//     the ReturnCode and ignores it in Release builds (sc:1225-1227).
+//   * serialize_path_to_json writes velocity[i] / acceleration[i] of sample i; the reference's
+//     format_vec_vecx (sc:1410-1420) repeats element 0 (index slip).
+//   * the header's free functions are inline (the reference's are not: ODR).
+#ifndef SEA_CURRENT_B200_HPP
+#define SEA_CURRENT_B200_HPP
+
+#include <array>
+#include <charconv>
+#include <cmath>
+#include <cstdint>
+#include <cstdlib>
+#include <functional>
+#include <initializer_list>
+#include <limits>
+#include <ostream>
+#include <sstream>
+#include <stdexcept>
+#include <string>
+#include <tuple>
+#include <vector>
+
+#include "seacurrent_b200.h"
+
+// ------------------------------------------------------------------ Eigen / toppra stand-ins
+#ifndef EIGEN_CORE_H
+namespace Eigen {
+struct Vector2f {
+  float v[2];
+  Vector2f(float x = 0, float y = 0) : v{x, y} {}
+  float x() const { return v[0]; }
+  float y() const { return v[1]; }
+  float& operator()(int i) { return v[i]; }
+  float operator()(int i) const { return v[i]; }
+  float& operator[](int i) { return v[i]; }
+  float operator[](int i) const { return v[i]; }
+};
+template <class T> struct VectorX {
+  std::vector<T> d;
+  VectorX() = default;
+  explicit VectorX(long n) : d((size_t)n, T(0)) {}
+  VectorX(const T* b, const T* e) : d(b, e) {}
+  static VectorX Zero(long n) { return VectorX(n); }
+  long rows() const { return (long)d.size(); }
+  long size() const { return (long)d.size(); }
+  T* data() { return d.data(); }
+  const T* data() const { return d.data(); }
+  T& operator()(long i, long = 0) { return d[(size_t)i]; }
+  T operator()(long i, long = 0) const { return d[(size_t)i]; }
+  T& operator[](long i) { return d[(size_t)i]; }
+  T operator[](long i) const { return d[(size_t)i]; }
+};
+using VectorXf = VectorX<float>;
+using VectorXd = VectorX<double>;
+template <class T, int N> struct Vector {
+  std::array<T, N> v{};
+  Vector() = default;
+  Vector(std::initializer_list<T> l) { int i = 0; for (T x : l) if (i < N) v[i++] = x; }
+  int rows() const { return N; }
+  T& operator()(int i) { return v[i]; }
+  T operator()(int i) const { return v[i]; }
+};
+struct MatrixX2f {  // Matrix<float, Dynamic, 2>
+  std::vector<float> cx, cy;
+  long rows() const { return (long)cx.size(); }
+  float operator()(long i, int j) const { return j == 0 ? cx[(size_t)i] : cy[(size_t)i]; }
+};
+}  // namespace Eigen
+namespace toppra {
+typedef double value_type;
+typedef Eigen::VectorXd Vector;
+}  // namespace toppra
+#define SEA_CURRENT_B200_OWN_EIGEN 1
+#endif
+
+namespace turtle::sc {
+
+using Eigen::Vector2f;
+using Eigen::VectorXf;
+using toppra::value_type;
+#ifdef SEA_CURRENT_B200_OWN_EIGEN
+using Eigen::MatrixX2f;
+#else
+struct MatrixX2f {
+  std::vector<float> cx, cy;
+  long rows() const { return (long)cx.size(); }
+  float operator()(long i, int j) const { return j == 0 ? cx[(size_t)i] : cy[(size_t)i]; }
+};
+#endif
+
+// toppra::ReturnCode of the failed plan (tp:algorithm.hpp:13-32) + the gridpoint it failed at
+struct planning_error : std::runtime_error {
+  int status, fail_stage;
+  planning_error(int st, int fs, const std::string& what) : std::runtime_error(what), status(st), fail_stage(fs) {}
+};
+
+struct bounding_rect {  // sc:61-84
+  float x_max, x_min, y_max, y_min;
+  bounding_rect(float x_max, float x_min, float y_max, float y_min) : x_max(x_max), x_min(x_min), y_max(y_max), y_min(y_min) {}
+};
+struct obstacle {};  // sc:193-284: the path reads ps.obstacles only when it is non-empty (shrink_tangent, sc:575-596)
+struct planning_space {  // sc:298-319; only what from_path touches
+  std::vector<obstacle> obstacles;
+  bounding_rect bound_rect;
+  planning_space(const bounding_rect& br) : bound_rect(br) {}
+};
+
+struct arclength_data {  // sc:322-326
+  float arclength = 0;
+  std::vector<VectorXf> segments;
+  std::vector<VectorXf> positions;
+};
+
+struct velocity_profile {  // sc:379-386
+  std::vector<VectorXf> pos, vel, acc;
+  toppra::Vector time;
+  velocity_profile(std::vector<VectorXf> pos, std::vector<VectorXf> vel, std::vector<VectorXf> acc, toppra::Vector time)
+      : pos(std::move(pos)), vel(std::move(vel)), acc(std::move(acc)), time(std::move(time)) {}
+};
+
+using vel_lim_func = std::function<std::tuple<toppra::Vector, toppra::Vector>(value_type time)>;  // sc:1175
+
+namespace b200 {
+
+// Spline construction used by the drop-in calls: the reference's cubic (default) or the Lau09
+// quintic + optimiser.  Also settable with SEA_CURRENT_B200_SPLINE=lau in the environment.
+inline int& spline_mode() {
+  static int m = [] { const char* e = std::getenv("SEA_CURRENT_B200_SPLINE"); return (e && (e[0] == 'l' || e[0] == 'L')) ? SCB_LAU_QUINTIC : SCB_REF_CUBIC; }();
+  return m;
+}
+inline int& device() { static int d = 0; return d; }
+
+inline void check(int rc, scb_ctx* ctx, const char* what) {
+  if (rc == SCB_OK) return;
+  std::string msg = std::string(what) + ": " + scb_strerror(rc);
+  if (ctx && rc == SCB_E_CUDA) msg += std::string(" [") + scb_last_cuda_error(ctx) + "]";
+  throw std::runtime_error(msg);
+}
+
+// RAII owner of one scb_ctx (FP64).  One per host thread and GPU.
+class batch_planner {
+ public:
+  batch_planner(int device, int precision, int spline_mode, int max_problems, int max_waypoints, int max_gridpoints, int max_samples)
+      : precision_(precision), mode_(spline_mode) {
+    scb_config cfg{device, precision, spline_mode, max_problems, max_waypoints, max_gridpoints, max_samples};
+    check(scb_create(&ctx_, &cfg), nullptr, "scb_create");
+  }
+  ~batch_planner() { if (ctx_) scb_destroy(ctx_); }
+  batch_planner(const batch_planner&) = delete;
+  batch_planner& operator=(const batch_planner&) = delete;
+  scb_ctx* ctx() const { return ctx_; }
+  int degree() const { return mode_ == SCB_REF_CUBIC ? 3 : 5; }
+  // host buffers in, host buffers out; see seacurrent_b200.h for the layouts
+  void plan(const scb_batch_in& in, const scb_batch_out& out) { check(scb_plan_batch(ctx_, &in, &out), ctx_, "scb_plan_batch"); }
+  scb_timing timing() const { scb_timing t{}; scb_get_timing(ctx_, &t); return t; }
+
+ private:
+  scb_ctx* ctx_ = nullptr;
+  int precision_, mode_;
+};
+
+constexpr int kDropInMaxWaypoints = 4096, kDropInGrid = 101 /* tp:algorithm.hpp:140 */, kDropInMaxSamples = 1 << 17;
+
+inline batch_planner& drop_in_planner() {  // batch-of-1 context behind the reference-shaped calls
+  static thread_local batch_planner pl(device(), SCB_FP64, spline_mode(), 1, kDropInMaxWaypoints, kDropInGrid, kDropInMaxSamples);
+  return pl;
+}
+
+}  // namespace b200
+
+class bezier_spline {  // sc:388-431
+ public:
+  std::vector<std::vector<Vector2f>> ctrl_pts;
+  MatrixX2f pts;
+  std::vector<VectorXf> positions;
+
+  bezier_spline() = default;
+
+  inline int n_pts() const { return (int)pts.rows(); }
+  inline int n_segments() const { return (int)ctrl_pts.size(); }
+  inline int degree() const { return ctrl_pts.empty() ? 0 : (int)ctrl_pts[0].size() - 1; }
+
+  // sc:599-683 (tangent heuristics sc:343-377).  ps.obstacles must be empty.
+  static bezier_spline from_path(const std::vector<Vector2f>& path, const planning_space& ps,
+                                 float start_angle = std::numeric_limits<float>::quiet_NaN()) {
+    if (!ps.obstacles.empty()) throw std::invalid_argument("sea_current_b200: obstacle-aware tangent clipping is not built yet");
+    if (path.size() < 2) throw std::invalid_argument("sea_current_b200: a path needs at least two waypoints");
+    bezier_spline s;
+    s.wx_.resize(path.size()); s.wy_.resize(path.size());
+    for (size_t i = 0; i < path.size(); ++i) { s.wx_[i] = path[i].x(); s.wy_[i] = path[i].y(); }
+    s.start_angle_ = start_angle;
+    s.build();
+    return s;
+  }
+
+  // sc:767-896.  Only the reference's default precision exists on the device (100 sub-intervals).
+  arclength_data arclength(const float precision = 0.01f) const {
+    if (std::fabs(precision - 0.01f) > 1e-9f) throw std::invalid_argument("sea_current_b200: arclength precision is fixed at 0.01");
+    return ad_;
+  }
+
+  // sc:898-1005.  Mutates profile_pos when nudge_positions is set, as the reference does.
+  bezier_spline resample(VectorXf& profile_pos, arclength_data /*ad*/, bool nudge_positions = false) const {
+    if (profile_pos.rows() <= 0) throw std::invalid_argument("The vector of positions to be sampled must not be empty");
+    bezier_spline r = *this;
+    r.arc_.assign(profile_pos.data(), profile_pos.data() + profile_pos.rows());
+    r.geometry(nullptr, nudge_positions);
+    for (long i = 0; i < profile_pos.rows(); ++i) profile_pos(i) = (float)r.arc_[(size_t)i];
+    return r;
+  }
+
+  // sc:1017-1039: curvature at every resampled point
+  std::vector<float> curvature() const { return std::vector<float>(kappa_.begin(), kappa_.end()); }
+
+  // sc:1055-1067: omega_i = v_i * kappa_i
+  std::vector<float> angular_velocity(const velocity_profile& vel_prof) const {
+    if (vel_prof.vel.empty() || (size_t)vel_prof.vel[0].size() != arc_.size())
+      throw std::invalid_argument("curvature and velocity vectors must be the same size");
+    bezier_spline r = *this;
+    std::vector<double> v(arc_.size());
+    for (size_t i = 0; i < v.size(); ++i) v[i] = vel_prof.vel[0][(long)i];
+    r.geometry(v.data(), false);
+    return std::vector<float>(r.kappa_.begin(), r.kappa_.end());
+  }
+
+ private:
+  std::vector<double> wx_, wy_, arc_, kappa_;
+  float start_angle_ = std::numeric_limits<float>::quiet_NaN();
+  arclength_data ad_;
+
+  void build() {  // SCB_STAGE_SPLINE: control points + arc-length tables
+    b200::batch_planner& pl = b200::drop_in_planner();
+    const int W = (int)wx_.size(), nseg = W - 1, nc = pl.degree() + 1;
+    std::vector<double> cx((size_t)nseg * nc), cy((size_t)nseg * nc), tab((size_t)nseg * SCB_ARCLEN_TABLE);
+    double L = 0, sa = start_angle_;
+    int32_t status = 0;
+    scb_batch_in in{};
+    in.P = 1; in.W = W; in.G = b200::kDropInGrid; in.wx = wx_.data(); in.wy = wy_.data(); in.start_angle = &sa;
+    in.stages = SCB_STAGE_SPLINE;
+    scb_default_opt(&in.opt);
+    scb_batch_out out{};
+    out.status = &status; out.ctrl_x = cx.data(); out.ctrl_y = cy.data(); out.arclen_total = &L; out.arclen_table = tab.data();
+    pl.plan(in, out);
+    if (status != SCB_ST_OK) throw planning_error(status, -1, "sea_current_b200: bad path (non-finite waypoint or zero-length leg)");
+    ctrl_pts.assign((size_t)nseg, std::vector<Vector2f>((size_t)nc));
+    ad_ = arclength_data();
+    ad_.arclength = (float)L;
+    for (int s = 0; s < nseg; ++s) {
+      for (int j = 0; j < nc; ++j) ctrl_pts[(size_t)s][(size_t)j] = Vector2f((float)cx[(size_t)s * nc + j], (float)cy[(size_t)s * nc + j]);
+      VectorXf seg(SCB_ARCLEN_TABLE), pos(SCB_ARCLEN_TABLE);
+      for (int k = 0; k < SCB_ARCLEN_TABLE; ++k) { seg(k) = (float)tab[(size_t)s * SCB_ARCLEN_TABLE + k]; pos(k) = std::fmin((float)k * 0.01f, 1.0f); }
+      ad_.segments.push_back(seg); ad_.positions.push_back(pos);
+    }
+  }
+
+  void geometry(const double* vel, bool nudge) {  // SCB_STAGE_SPLINE | SCB_STAGE_GEOMETRY at arc_
+    b200::batch_planner& pl = b200::drop_in_planner();
+    const int S = (int)arc_.size();
+    if (S > b200::kDropInMaxSamples) throw std::invalid_argument("sea_current_b200: too many samples for the drop-in context");
+    std::vector<double> px((size_t)S), py((size_t)S), om((size_t)S), vv;
+    double sa = start_angle_;
+    int32_t status = 0, ns = S;
+    scb_batch_in in{};
+    in.P = 1; in.W = (int)wx_.size(); in.G = b200::kDropInGrid; in.wx = wx_.data(); in.wy = wy_.data(); in.start_angle = &sa;
+    in.stages = SCB_STAGE_SPLINE | SCB_STAGE_GEOMETRY; in.nudge_positions = nudge ? 1 : 0;
+    scb_default_opt(&in.opt);
+    scb_batch_out out{};
+    out.status = &status; out.S_cap = S; out.n_samples = &ns; out.s_pos = arc_.data();
+    if (vel) { vv.assign(vel, vel + S); out.s_vel = vv.data(); }
+    out.s_px = px.data(); out.s_py = py.data(); out.s_omega = om.data();
+    pl.plan(in, out);
+    if (status != SCB_ST_OK) throw planning_error(status, -1, "sea_current_b200: bad path");
+    pts.cx.assign(px.begin(), px.end()); pts.cy.assign(py.begin(), py.end());
+    kappa_ = om;  // s_vel absent: v = 1, i.e. curvature; present: angular velocity
+  }
+};
+
+// sc:1191-1265.  N = 1 is the only instantiation sea-current uses (arc length is the one DOF).
+template <int N>
+inline velocity_profile gen_vel_prof(const Eigen::Vector<value_type, N>& pos_end, const Eigen::Vector<value_type, N>& pos_start,
+                                     const Eigen::Vector<value_type, N>& vel_end, const Eigen::Vector<value_type, N>& vel_start,
+                                     const vel_lim_func& vel_lim, const Eigen::Vector<value_type, N>& acc_min,
+                                     const Eigen::Vector<value_type, N>& acc_max, const float dt = 0.02f) {
+  static_assert(N == 1, "sea_current_b200: gen_vel_prof is built for the 1-DOF arc-length path (N = 1)");
+  b200::batch_planner& pl = b200::drop_in_planner();
+  const int G = b200::kDropInGrid, S_cap = b200::kDropInMaxSamples;
+  // vel_lim_func of the path position s (sc:1177-1188), tabulated at toppra's gridpoints
+  std::vector<double> vlo((size_t)G), vhi((size_t)G);
+  for (int i = 0; i < G; ++i) {
+    const double s = i == G - 1 ? 1.0 : (double)i * (1.0 / (double)(G - 1));
+    auto lim = vel_lim(s);
+    vlo[(size_t)i] = std::get<0>(lim)(0); vhi[(size_t)i] = std::get<1>(lim)(0);
+  }
+  const double L = pos_end(0) - pos_start(0), vs = vel_start(0), ve = vel_end(0), alo = acc_min(0), ahi = acc_max(0);
+  int32_t status = 0, fail = -1, ns = 0;
+  std::vector<double> st((size_t)S_cap), sp((size_t)S_cap), sv((size_t)S_cap), sa((size_t)S_cap);
+  scb_batch_in in{};
+  in.P = 1; in.W = 2; in.G = G; in.path_len = &L; in.vel_lo_grid = vlo.data(); in.vel_hi_grid = vhi.data();
+  in.acc_lo = &alo; in.acc_hi = &ahi; in.vel_start = &vs; in.vel_end = &ve;
+  in.stages = SCB_STAGE_TIMING; in.lp_mode = SCB_LP_SEIDEL; in.dt = (double)dt;
+  scb_default_opt(&in.opt);
+  scb_batch_out out{};
+  out.status = &status; out.fail_stage = &fail; out.S_cap = S_cap; out.n_samples = &ns;
+  out.s_time = st.data(); out.s_pos = sp.data(); out.s_vel = sv.data(); out.s_acc = sa.data();
+  pl.plan(in, out);
+  if (status != SCB_ST_OK) {
+    std::ostringstream m;
+    m << "sea_current_b200: toppra verdict " << status << " at gridpoint " << fail;
+    throw planning_error(status, fail, m.str());
+  }
+  if (ns > S_cap) throw std::runtime_error("sea_current_b200: trajectory longer than the drop-in sample capacity");
+  const double p0 = pos_start(0);
+  VectorXf pos(ns), vel(ns), acc(ns);
+  toppra::Vector time(ns);
+  for (int i = 0; i < ns; ++i) { pos(i) = (float)(sp[(size_t)i] + p0); vel(i) = (float)sv[(size_t)i]; acc(i) = (float)sa[(size_t)i]; time(i) = st[(size_t)i]; }
+  return velocity_profile({pos}, {vel}, {acc}, time);
+}
+
+// Minimal JSON value for the one document the path emits (an array of flat sample objects):
+// `o << std::setw(4) << j` and j.dump(4) print what nlohmann::json prints for sc:1439-1454
+// (keys in alphabetical order, 4-space indent).
+class json {
+ public:
+  struct sample { double time, velocity, acceleration, angularVelocity, x, y; };
+  std::vector<sample> samples;
+  size_t size() const { return samples.size(); }
+  std::string dump(int indent = -1) const {
+    std::string o;
+    const bool pretty = indent >= 0;
+    auto nl = [&](int depth) { if (pretty) { o += '\n'; o.append((size_t)(depth * indent), ' '); } };
+    auto num = [&](double v) {  // shortest round-trip digits, laid out as nlohmann's dtoa (fixed for 1e-4 <= |v| < 1e15)
+      if (!std::isfinite(v)) { o += "null"; return; }
+      if (v == 0) { o += std::signbit(v) ? "-0.0" : "0.0"; return; }
+      char buf[40];
+      auto r = std::to_chars(buf, buf + sizeof buf, std::fabs(v), std::chars_format::scientific);
+      std::string sci(buf, r.ptr), dig;
+      const size_t epos = sci.find('e');
+      for (size_t i = 0; i < epos; ++i) if (sci[i] != '.') dig += sci[i];
+      const int k = (int)dig.size(), n = std::atoi(sci.c_str() + epos + 1) + 1;  // value = 0.dig * 10^n
+      if (v < 0) o += '-';
+      if (k <= n && n <= 15) { o += dig; o.append((size_t)(n - k), '0'); o += ".0"; }
+      else if (0 < n && n <= 15) { o.append(dig, 0, (size_t)n); o += '.'; o.append(dig, (size_t)n, std::string::npos); }
+      else if (-4 < n && n <= 0) { o += "0."; o.append((size_t)(-n), '0'); o += dig; }
+      else {
+        o += dig[0];
+        if (k > 1) { o += '.'; o.append(dig, 1, std::string::npos); }
+        const int e = n - 1;
+        o += 'e'; o += e < 0 ? '-' : '+';
+        const int ae = e < 0 ? -e : e;
+        if (ae < 10) o += '0';
+        o += std::to_string(ae);
+      }
+    };
+    auto key = [&](const char* k, int depth) { nl(depth); o += '"'; o += k; o += pretty ? "\": " : "\":"; };
+    if (samples.empty()) return "[]";
+    o += '[';
+    for (size_t i = 0; i < samples.size(); ++i) {
+      const sample& s = samples[i];
+      nl(1); o += '{';
+      key("acceleration", 2); num(s.acceleration); o += ',';
+      key("angularVelocity", 2); num(s.angularVelocity); o += ',';
+      key("holonomicAngularVelocity", 2); num(0.0); o += ',';
+      key("holonomicRotation", 2); num(0.0); o += ',';
+      key("pose", 2); o += '{';
+      key("translation", 3); o += '{';
+      key("x", 4); num(s.x); o += ',';
+      key("y", 4); num(s.y);
+      nl(3); o += '}';
+      nl(2); o += "},";
+      key("time", 2); num(s.time); o += ',';
+      key("velocity", 2); num(s.velocity);
+      nl(1); o += '}';
+      if (i + 1 < samples.size()) o += ',';
+    }
+    nl(0); o += ']';
+    return o;
+  }
+  friend std::ostream& operator<<(std::ostream& os, const json& j) {
+    const int w = (int)os.width();
+    os.width(0);
+    return os << j.dump(w > 0 ? w : -1);
+  }
+};
+
+// sc:1423-1457
+inline json serialize_path_to_json(const bezier_spline& spline, const velocity_profile& vel_prof, const arclength_data& /*arclens*/,
+                                   const std::vector<float>& ang_vel) {
+  json j;
+  const long n = spline.pts.rows();
+  if (vel_prof.vel.empty() || vel_prof.vel[0].size() < n || vel_prof.time.size() < n || (long)ang_vel.size() < n)
+    throw std::invalid_argument("serialize_path_to_json: profile shorter than the resampled spline");
+  j.samples.resize((size_t)n);
+  for (long i = 0; i < n; ++i)
+    j.samples[(size_t)i] = {(double)(float)vel_prof.time(i), (double)vel_prof.vel[0](i), (double)vel_prof.acc[0](i), (double)ang_vel[(size_t)i],
+                            (double)spline.pts(i, 0), (double)spline.pts(i, 1)};
+  return j;
+}
+
+namespace b200 {
+
+// The request/response body of examples/zmq_test.cpp:26-101 without the socket: text
+//   "acc_min acc_max vel_min vel_max\n x0 y0\n x1 y1 ..."  ->  pretty-printed JSON (setw(4)).
+inline std::string handle_text_request(const std::string& req) {
+  std::istringstream ss(req);
+  float acc_min_val, acc_max_val, vel_min_val, vel_max_val;
+  if (!(ss >> acc_min_val >> acc_max_val >> vel_min_val >> vel_max_val)) throw std::invalid_argument("request: four limits expected");
+  std::vector<Vector2f> path;
+  float x, y, max_x = 0, max_y = 0;
+  while (ss >> x >> y) { path.emplace_back(x, y); max_x = std::fmax(max_x, std::fabs(x)); max_y = std::fmax(max_y, std::fabs(y)); }
+  planning_space space(bounding_rect(max_x, -max_x, max_y, -max_y));
+  bezier_spline pad = bezier_spline::from_path(path, space);
+  const arclength_data ad = pad.arclength();
+  const Eigen::Vector<value_type, 1> pos_end{ad.arclength}, zero{0.0}, amin{acc_min_val}, amax{acc_max_val};
+  auto vel_lim = [&](value_type) {
+    toppra::Vector lo(1), hi(1);
+    lo(0) = vel_min_val; hi(0) = vel_max_val;
+    return std::make_tuple(lo, hi);
+  };
+  velocity_profile prof = gen_vel_prof<1>(pos_end, zero, zero, zero, vel_lim, amin, amax);
+  bezier_spline re = pad.resample(prof.pos[0], ad, true);
+  const std::vector<float> ang_vel = re.angular_velocity(prof);
+  return serialize_path_to_json(re, prof, ad, ang_vel).dump(4) + "\n";
+}
+
+}  // namespace b200
+}  // namespace turtle::sc
+
+#endif  // SEA_CURRENT_B200_HPP

@@ -134,6 +134,9 @@ typedef struct scb_batch_in {
   const void* path_len;     /* real [P]: pos_end - pos_start, read only when SCB_STAGE_SPLINE is off */
   int32_t stages;           /* SCB_STAGE_* bitmask; 0 = all */
   int32_t lp_mode;          /* SCB_LP_*: how the stage LPs of toppra are solved; 0 = default */
+  int32_t nudge_positions;  /* geometry-only calls: 1 = repair the caller's s_pos in place before resampling
+                               (ends pinned to 0 / L, non-monotone entries averaged, clamp; sc:902-912) */
+  int32_t reserved0;
   double x_cap;             /* upper bound of sdot^2 in the backward pass; 0 = reference's 100
                                (tp:algorithm.hpp:152 m_initXBound) */
   double dt;                /* uniform-dt stream period; 0 = reference's 0.02 (sc:1199) */

@@ -286,6 +286,22 @@ __global__ void __launch_bounds__(64) sample_kernel(SampleArgs g) {
     } else if (geo) {  // resample / angular_velocity of caller-supplied positions
       const int S = g.n_samples[p];
       n = S < S_cap ? S : S_cap;
+      if (g.nudge && n > 0) {  // sc:902-912, in place like the reference (it takes profile_pos by reference)
+        const R Ltot = walk.total;
+        o_pos[p] = 0;
+        o_pos[(size_t)(n - 1) * P + p] = Ltot;
+        R prev = 0;
+        for (int i = 1; i + 1 < n; ++i) {
+          const size_t o = (size_t)i * P + p;
+          R cur = o_pos[o];
+          const R nxt = o_pos[o + P];
+          if (cur < prev || cur > nxt) cur = (prev + nxt) / 2;
+          if (cur < 0) cur = 0;
+          if (cur > Ltot) cur = Ltot;
+          o_pos[o] = cur;
+          prev = cur;
+        }
+      }
       for (int i = 0; i < n; ++i) {
         const size_t o = (size_t)i * P + p;
         R px, py, kap;

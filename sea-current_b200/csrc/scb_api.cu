@@ -188,7 +188,7 @@ int run_device(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, i
     s.ctrl_x = dCx; s.ctrl_y = dCy; s.table = dTab; s.n_samples = dNs;
     s.s_time = out->s_time; s.s_pos = out->s_pos; s.s_vel = out->s_vel; s.s_acc = out->s_acc;
     s.s_px = out->s_px; s.s_py = out->s_py; s.s_omega = out->s_omega; s.status = out->status;
-    s.timing = do_timing ? 1 : 0; s.geometry = do_geo ? 1 : 0;
+    s.timing = do_timing ? 1 : 0; s.geometry = do_geo ? 1 : 0; s.nudge = in->nudge_positions ? 1 : 0;
     launch_sample<R>(s, st);
     ++launches;
   }

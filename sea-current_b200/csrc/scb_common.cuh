@@ -78,6 +78,7 @@ struct SampleArgs {
   void *s_time, *s_pos, *s_vel, *s_acc, *s_px, *s_py, *s_omega;  // [S_cap][P]
   const int32_t* status;
   int timing, geometry;                // timing off: s_pos / s_vel / n_samples are inputs
+  int nudge;                           // geometry-only: repair s_pos in place first (sc:902-912)
 };
 
 template <class R> void launch_path(const PathArgs& a, int spline_mode, cudaStream_t st);

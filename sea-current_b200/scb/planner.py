@@ -99,7 +99,8 @@ class BatchPlanner:
     # ------------------------------------------------------------------ host buffers
     def plan(self, wx=None, wy=None, vel_lo=None, vel_hi=None, acc_lo=None, acc_hi=None, G=101, start_angle=None,
              vel_lo_grid=None, vel_hi_grid=None, vel_start=None, vel_end=None, path_len=None, stages=0,
-             outputs=ALL_OUTPUTS, S_cap=0, x_cap=0.0, dt=0.0, opt=None, out_buffers=None, resample_at=None, lp_mode=0):
+             outputs=ALL_OUTPUTS, S_cap=0, x_cap=0.0, dt=0.0, opt=None, out_buffers=None, resample_at=None, lp_mode=0,
+             nudge=False):
         """Host arrays in, host arrays out (scb_plan_batch).  `out_buffers` lets a caller pass
         preallocated (e.g. pinned) numpy arrays keyed by output name."""
         R = self.real
@@ -129,6 +130,7 @@ class BatchPlanner:
         bi.vel_start, bi.vel_end = arr(vel_start, (P,)), arr(vel_end, (P,))
         bi.path_len = arr(path_len, (P,))
         bi.stages, bi.x_cap, bi.dt, bi.lp_mode = stages, x_cap, dt, lp_mode
+        bi.nudge_positions = 1 if nudge else 0
         bi.opt = opt if opt is not None else default_opt()
         res = BatchResult()
         bo = abi.ScbBatchOut()

@@ -1,0 +1,56 @@
+// Drop-in check: the call sequence a sea-current user writes (examples/json_test.cpp:28-65 and the
+// request body of examples/zmq_test.cpp:26-101), compiled against include/sea_current_b200.hpp
+// instead of sea_current.hpp.  tests/test_drop_in.py builds it with g++, runs it on the GPU box and
+// compares what it prints with the oracle.
+//
+//   drop_in_e1 json <out.json>      the six-waypoint case of examples/json_test.cpp
+//   drop_in_e1 text <out.json>      the request of examples/zmq_test.py:7-10 through handle_text_request
+#include <cstring>
+#include <fstream>
+#include <iomanip>
+#include <iostream>
+
+#include "sea_current_b200.hpp"
+
+using namespace Eigen;
+using namespace turtle::sc;
+
+static int run_json_case(const char* out_path) {
+  planning_space space(bounding_rect{1, -1, 1, -1});
+  const std::vector<Vector2f> path = {Vector2f(0, 0), Vector2f(10, 0), Vector2f(10, 10), Vector2f(10, 20), Vector2f(30, 50), Vector2f(0, 0)};
+  bezier_spline pad = bezier_spline::from_path(path, space);
+  const arclength_data ad = pad.arclength();
+  const Eigen::Vector<value_type, 1> pos_end{ad.arclength}, pos_start{0}, vel_end{0}, vel_start{0}, acc_min{-0.25}, acc_max{0.25};
+  auto vel_lim = [](toppra::value_type) {
+    toppra::Vector lower{1}, upper{1};
+    lower(0, 0) = 0;
+    upper(0, 0) = 1;
+    return std::make_tuple(lower, upper);
+  };
+  velocity_profile prof = gen_vel_prof<1>(pos_end, pos_start, vel_end, vel_start, vel_lim, acc_min, acc_max);
+  bezier_spline re = pad.resample(prof.pos[0], ad, true);
+  const std::vector<float> ang_vel = re.angular_velocity(prof);
+  json j = serialize_path_to_json(re, prof, ad, ang_vel);
+  std::ofstream o(out_path);
+  o << std::setw(4) << j << std::endl;
+  // one summary line for the test: arclength, sample count, first table entries, a control point
+  std::cout << std::setprecision(9) << "{\"arclength\": " << ad.arclength << ", \"n_samples\": " << re.n_pts()
+            << ", \"n_segments\": " << pad.n_segments() << ", \"degree\": " << pad.degree() << ", \"seg0_1\": " << ad.segments[0](1)
+            << ", \"ctrl_1_x\": " << pad.ctrl_pts[0][1].x() << ", \"ctrl_1_y\": " << pad.ctrl_pts[0][1].y() << "}" << std::endl;
+  return 0;
+}
+
+int main(int argc, char** argv) {
+  if (argc < 3) { std::cerr << "usage: drop_in_e1 json|text <out.json>" << std::endl; return 2; }
+  try {
+    if (!std::strcmp(argv[1], "json")) return run_json_case(argv[2]);
+    const std::string req = "-0.5 0.5 -0.25 0.25\n0 0\n10 0\n10 10";
+    std::ofstream o(argv[2]);
+    o << b200::handle_text_request(req);
+    std::cout << "{\"ok\": true}" << std::endl;
+    return 0;
+  } catch (const std::exception& e) {
+    std::cerr << "drop_in_e1: " << e.what() << std::endl;
+    return 3;
+  }
+}

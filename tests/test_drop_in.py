@@ -1,0 +1,116 @@
+"""The C++ drop-in (include/sea_current_b200.hpp): the reference's call sequence compiled against
+the shim header, linked to libseacurrent_b200.so.
+
+CPU: the header compiles as C++17 and C++20, the JSON writer prints what nlohmann's dump(4) prints
+(= Python's json.dumps(indent=4, sort_keys=True)), and the program fails loudly without a GPU.
+GPU: what it produces equals the oracle / the reference's fixture."""
+import json
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+CSRC = os.path.join(ROOT, "sea-current_b200", "csrc")
+LIB = os.path.join(CSRC, "libseacurrent_b200.so")
+
+
+def _cxx():
+    return "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
+
+
+def _build(tmp, src, std="c++20", link=True):
+    exe = os.path.join(str(tmp), os.path.basename(src).replace(".cpp", "_" + std.replace("+", "p")))
+    cmd = [_cxx(), "-std=" + std, "-O1", "-Wall", "-Werror", "-I" + os.path.join(ROOT, "include"), os.path.join(ROOT, "tests", "cpp", src),
+           "-o", exe]
+    if link:
+        cmd += ["-L" + CSRC, "-lseacurrent_b200", "-Wl,-rpath," + CSRC]
+    subprocess.check_call(cmd)
+    return exe
+
+
+@pytest.fixture(scope="module")
+def built(tmp_path_factory):
+    if not os.path.exists(LIB):
+        pytest.fail("libseacurrent_b200.so is not built; run __graft_entry__.build()")
+    return _build(tmp_path_factory.mktemp("dropin"), "drop_in_e1.cpp")
+
+
+def test_header_compiles_as_cxx17_and_cxx20(tmp_path):
+    _build(tmp_path, "drop_in_e1.cpp", "c++17")
+    _build(tmp_path, "drop_in_e1.cpp", "c++20")
+
+
+def test_json_writer_matches_nlohmann_layout(tmp_path):
+    exe = _build(tmp_path, "json_writer.cpp")
+    pretty, compact, empty = subprocess.check_output([exe]).decode().split("====\n")
+    doc = json.loads(pretty)
+    assert len(doc) == 3 and doc == json.loads(compact)
+    # nlohmann::json::dump(4) == Python's indent=4 with sorted keys (objects are std::map) and shortest round-trip floats
+    assert pretty.rstrip("\n") == json.dumps(doc, indent=4, sort_keys=True)
+    assert compact.rstrip("\n") == json.dumps(doc, separators=(",", ":"), sort_keys=True)
+    assert set(doc[1]) == {"time", "velocity", "acceleration", "angularVelocity", "pose", "holonomicRotation", "holonomicAngularVelocity"}
+    assert doc[1]["pose"]["translation"] == {"x": 10.5, "y": -3.0} and doc[1]["time"] == float(np.float32(0.02))
+    assert empty.strip() == "[]"
+
+
+def test_fails_loudly_without_a_device(built, tmp_path):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    r = subprocess.run([built, "json", str(tmp_path / "o.json")], capture_output=True)
+    assert r.returncode == 3 and b"no CPU fallback" in r.stderr
+
+
+@pytest.mark.gpu
+def test_json_case_matches_oracle(built, tmp_path, oracle):
+    """examples/json_test.cpp's body through the shim vs the oracle's FP64 plan of the same problem."""
+    import seacurrent_b200 as scb
+    out = tmp_path / "o.json"
+    head = json.loads(subprocess.check_output([built, "json", str(out)]).decode())
+    doc = json.load(open(out))
+    a, _ = scb.workloads.config_c1()
+    ref, _ = oracle.plan_batch(spline_mode=0, S_cap=8192, **a)
+    n = int(ref["n_samples"][0])
+    assert head["n_samples"] == n == len(doc) and head["n_segments"] == 5 and head["degree"] == 3
+    assert abs(head["arclength"] - ref["arclen_total"][0]) <= 1e-6 * ref["arclen_total"][0]
+    assert abs(head["seg0_1"] - ref["arclen_table"][0, 1]) <= 1e-6
+    assert abs(head["ctrl_1_x"] - ref["ctrl_x"][0, 1]) <= 1e-5 and abs(head["ctrl_1_y"] - ref["ctrl_y"][0, 1]) <= 1e-5
+    col = lambda *k: np.array([_get(d, k) for d in doc])
+    f32 = lambda x: x.astype(np.float32).astype(np.float64)
+    np.testing.assert_allclose(col("time"), f32(ref["s_time"][:n, 0]), rtol=1e-6)
+    # the drop-in carries positions as float32 (VectorXf, as the reference): arc positions are good to eps32 * L
+    L = ref["arclen_total"][0]
+    np.testing.assert_allclose(col("velocity"), ref["s_vel"][:n, 0], atol=1e-6)
+    np.testing.assert_allclose(col("acceleration"), ref["s_acc"][:n, 0], atol=2e-6)
+    np.testing.assert_allclose(col("pose", "translation", "x"), ref["s_px"][:n, 0], atol=2e-6 * L)
+    np.testing.assert_allclose(col("pose", "translation", "y"), ref["s_py"][:n, 0], atol=2e-6 * L)
+    np.testing.assert_allclose(col("angularVelocity"), ref["s_omega"][:n, 0], atol=2e-3 * np.abs(ref["s_omega"][:n, 0]).max())
+    assert all(d["holonomicRotation"] == 0.0 and d["holonomicAngularVelocity"] == 0.0 for d in doc)
+
+
+def _get(d, keys):
+    for k in keys:
+        d = d[k]
+    return d
+
+
+@pytest.mark.gpu
+def test_text_request_matches_reference_fixture(built, tmp_path, golden_dir):
+    """The zmq request of examples/zmq_test.py:7-10 -> JSON, against examples/output.json (the
+    reference's own float32 output, older dict-of-arrays schema)."""
+    out = tmp_path / "o.json"
+    subprocess.check_call([built, "text", str(out)])
+    doc = json.load(open(out))
+    fix = json.load(open(os.path.join(golden_dir, "output_json_fixture.json")))
+    n, st = fix["n_samples"], fix["stride"]
+    assert len(doc) == n
+    t = np.array([d["time"] for d in doc]); v = np.array([d["velocity"] for d in doc]); a = np.array([d["acceleration"] for d in doc])
+    x = np.array([d["pose"]["translation"]["x"] for d in doc]); y = np.array([d["pose"]["translation"]["y"] for d in doc])
+    np.testing.assert_allclose(t[::st], fix["time"], rtol=1e-5, atol=1e-5)
+    np.testing.assert_allclose(v[::st], fix["vel"], atol=2e-5)
+    np.testing.assert_allclose(a[::st], fix["acc"], atol=2e-4)
+    m = len(fix["pos_x"])
+    np.testing.assert_allclose(x[::st][:m], fix["pos_x"], atol=5e-3)
+    np.testing.assert_allclose(y[::st][:m], fix["pos_y"], atol=5e-3)

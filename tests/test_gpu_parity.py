@@ -349,3 +349,21 @@ def test_geometry_only_resample(planners, oracle):
     d = np.hypot(np.diff(res["s_px"], axis=0), np.diff(res["s_py"], axis=0))
     assert np.all(d <= (L / (S - 1))[None, :] * (1 + 1e-9))
     assert np.all(d >= (L / (S - 1))[None, :] * 0.5)
+
+
+def test_python_toppra_fixture(planners, golden_dir):
+    """The timing stage against vectors produced by the reference's in-tree Python toppra in gen_vel_prof's
+    configuration (tests/golden/gen_pytoppra_fixtures.py); both stage-LP back ends."""
+    g = json.load(open(os.path.join(golden_dir, "pytoppra_hermite_golden.json")))
+    cs = g["cases"]
+    pl = planners("fp64", "ref_cubic")
+    for lp in (scb.abi.LP_SEIDEL, scb.abi.LP_CLOSED_FORM):
+        res = pl.plan(path_len=[c["L"] for c in cs], G=g["G"], stages=scb.abi.STAGE_TIMING, lp_mode=lp,
+                      vel_lo=[c["vel"][0] for c in cs], vel_hi=[c["vel"][1] for c in cs], acc_lo=[c["acc"][0] for c in cs],
+                      acc_hi=[c["acc"][1] for c in cs], outputs=("K_lo", "K_hi", "x", "T_total"))
+        assert np.all(res["status"] == 0)
+        for p, c in enumerate(cs):
+            np.testing.assert_allclose(res["x"][:, p], c["x"], rtol=3e-7, atol=3e-10 * max(c["x"]), err_msg=c["name"])
+            np.testing.assert_allclose(res["K_hi"][:, p], c["K_hi"], rtol=3e-7, atol=3e-10 * max(c["x"]), err_msg=c["name"])
+            np.testing.assert_allclose(res["K_lo"][:, p], c["K_lo"], rtol=3e-7, atol=3e-10 * max(c["x"]), err_msg=c["name"])
+            assert abs(res["T_total"][p] - c["T"]) <= 1e-6 * c["T"]

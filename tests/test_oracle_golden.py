@@ -189,3 +189,20 @@ def test_gl32_table_matches_reference(oracle):
         ref_x, ref_w = sorted(nums[32:]), sorted(nums[:32])
     np.testing.assert_allclose(sorted(ours[:32]), ref_x, atol=1e-15)
     np.testing.assert_allclose(sorted(ours[32:]), ref_w, atol=1e-15)
+
+
+# ---- in-tree Python toppra, gen_vel_prof's own configuration (tests/golden/gen_pytoppra_fixtures.py)
+def test_hermite_interpolation_vs_python_toppra(oracle, golden_dir):
+    """1-DOF Hermite path, Interpolation discretisation, 101 gridpoints: controllable sets, parametrization
+    and duration against the reference's Python implementation (its Cython Seidel
+    uses looser thresholds: agreement is 1.5e-7 relative where the velocity box binds, 1e-15 where it does not)."""
+    g = json.load(open(os.path.join(golden_dir, "pytoppra_hermite_golden.json")))
+    for c in g["cases"]:
+        L, vs, ve = c["L"], c["vel_start"], c["vel_end"]
+        co = np.zeros((1, 4, 1))
+        co[0, 0, 0] = ve - 2 * L + vs; co[0, 1, 0] = 3 * L - 2 * vs - ve; co[0, 2, 0] = vs  # tp:piecewise_poly_path.cpp:364-375
+        rc, K, x, _, _ = oracle.toppra_ppoly(co, [0, 1], g["G"], [c["vel"][0]], [c["vel"][1]], [c["acc"][0]], [c["acc"][1]], 1)
+        assert rc == 0, c["name"]
+        np.testing.assert_allclose(x, c["x"], rtol=3e-7, atol=3e-10 * max(c["x"]), err_msg=c["name"])
+        np.testing.assert_allclose(K[:, 1], c["K_hi"], rtol=3e-7, atol=3e-10 * max(c["x"]), err_msg=c["name"])
+        np.testing.assert_allclose(K[:, 0], c["K_lo"], rtol=3e-7, atol=3e-10 * max(c["x"]), err_msg=c["name"])
