@@ -1,0 +1,199 @@
+// Arc stage on the GPU (sm_100a): everything between the control points and the toppra kernels.
+//   arc-length tables    sea_current.hpp:767-896 (100 sub-intervals per segment, cumulative table of
+//                        101 entries), path length, final path status
+//   geometry             curve point and curvature at the arc length q(s_i) of every toppra gridpoint
+//                        (resample sc:898-1005 + curvature sc:1017-1039; exact table inversion instead
+//                        of the float Chebyshev fit, DESIGN.md "Deviations")
+// Input: the control points the path kernels wrote ([P][(W-1)(d+1)], one path contiguous).
+//
+// Split from the path kernels because the two halves want different machines (profiles/r1c_*, r1d_*):
+// the optimiser needs 128 registers per thread (16 warps per SM); these phases are embarrassingly
+// parallel, need ~80, and run here with 24 warps per SM and no per-path serial sections.
+//
+// One CTA owns PB consecutive paths; its threads are re-mapped per phase:
+//   (path, segment)                 power basis of the segment and of its hodograph -> shared memory
+//   warp per (path, segment)        lanes 0..24 integrate 4 consecutive sub-intervals each; a warp scan
+//                                   of the lane totals gives the cumulative table, stored 32 B per lane
+//   (gridpoint, path), path fastest geometry; stores to the [G][P] arrays are PB-contiguous
+//
+// Arc-length pieces: the reference integrates |B'| over every 0.01-wide sub-interval with a 32-point
+// Gauss-Legendre rule.  The integrand is analytic there and the 6-point rule agrees with the 32-point
+// one to ~1e-15 unless the speed has a (near-)zero within a few interval widths.  A lane evaluates the
+// 4- and 6-point rules (10 nodes) and keeps the 6-point value when the two agree to 1e-11 relative
+// (FP32: 2e-6); otherwise it runs the reference's 32 nodes in the reference's order.  On C2/C3 0.1 % of
+// the pieces take the long way; accepted pieces are within 1e-11 of the 32-point value
+// (DESIGN.md "Arc length").
+#include "path_device.cuh"
+
+namespace scb {
+
+constexpr int kArcThreads = 256;
+constexpr int kPiecesPerLane = 4, kScanLanes = kSub / kPiecesPerLane;  // 25 lanes x 4 pieces = 100
+
+__host__ __device__ inline size_t arc_smem_bytes(int W, int deg, int PB, int real_size) {
+  const size_t nseg = W - 1;
+  const size_t reals = (size_t)PB * nseg * (2 * (deg + 1) + 2 * deg + 1) + (size_t)PB * 2;
+  return 64 + sizeof(double) * PB * nseg + (reals * real_size + 15) / 16 * 16;
+}
+
+template <class R, int DEG>
+__global__ void __launch_bounds__(kArcThreads, 3) arc_kernel(PathArgs g) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  constexpr int NC = DEG + 1;
+  constexpr unsigned kFullMask = 0xffffffffu;
+  const int tid = threadIdx.x, T = blockDim.x, lane = tid & 31, warp = tid >> 5, nwarps = T >> 5;
+  const int W = g.W, nseg = W - 1, PB = g.PB, P = g.P;
+  const int p0 = blockIdx.x * PB;
+  const int PBa = min(PB, P - p0);
+  int* bad = (int*)smem_raw;                         // [PB] (PB <= 16)
+  double* segend = (double*)(smem_raw + 64);         // [PB * nseg] cumulative segment ends, FP64 in both modes
+  Carve<R> sm((R*)(smem_raw + 64 + sizeof(double) * (size_t)PB * nseg));
+  R* ax = sm.take((size_t)PB * nseg * NC); R* ay = sm.take((size_t)PB * nseg * NC);
+  R* hx = sm.take((size_t)PB * nseg * DEG); R* hy = sm.take((size_t)PB * nseg * DEG);
+  R* segtot = sm.take((size_t)PB * nseg);
+  R* vse = sm.take((size_t)PB * 2);                  // vel_start, vel_end per path
+  const int nS = PBa * nseg, nc = nseg * NC, nt = nseg * kTable;
+
+  // ---- status of the path kernel, power basis of every segment
+  if (tid < PBa) bad[tid] = g.status[p0 + tid] != SCB_ST_OK;
+  for (int it = tid; it < nS; it += T) {
+    const R* cx = (const R*)g.ctrl_x + (size_t)p0 * nc + (size_t)it * NC;
+    const R* cy = (const R*)g.ctrl_y + (size_t)p0 * nc + (size_t)it * NC;
+    power_basis<R, DEG>(cx, cy, ax + NC * it, ay + NC * it, hx + DEG * it, hy + DEG * it);
+  }
+  __syncthreads();
+
+  // ---- A4: cumulative arc-length table, one warp per (path, segment)
+  R* tab = (R*)g.table + (size_t)p0 * nt;
+  for (int sg = warp; sg < nS; sg += nwarps) {
+    R kx[DEG], ky[DEG];
+#pragma unroll
+    for (int j = 0; j < DEG; ++j) { kx[j] = hx[DEG * sg + j]; ky[j] = hy[DEG * sg + j]; }
+    auto speed = [&](R u) {
+      R dx = kx[DEG - 1], dy = ky[DEG - 1];
+#pragma unroll
+      for (int j = DEG - 2; j >= 0; --j) { dx = dx * u + kx[j]; dy = dy * u + ky[j]; }
+      const R n2 = dx * dx + dy * dy;
+      return n2 > 0 ? n2 * fast_rsqrt<R>(n2) : (R)0;
+    };
+    R piece[kPiecesPerLane];
+    const bool live = lane < kScanLanes;
+    bool redo_any = false;
+#pragma unroll
+    for (int j = 0; j < kPiecesPerLane; ++j) {
+      const int k = min(lane, kScanLanes - 1) * kPiecesPerLane + j;
+      const R a = fmin((R)k * (R)0.01, (R)1), b = fmin((R)(k + 1) * (R)0.01, (R)1);  // sc:851
+      const R half = (b - a) / 2, mid = (b + a) / 2;
+      R s4 = 0, s6 = 0;
+#pragma unroll
+      for (int i = 0; i < 2; ++i) s4 += (R)kG4W[i] * (speed(mid - half * (R)kG4X[i]) + speed(mid + half * (R)kG4X[i]));
+#pragma unroll
+      for (int i = 0; i < 3; ++i) s6 += (R)kG6W[i] * (speed(mid - half * (R)kG6X[i]) + speed(mid + half * (R)kG6X[i]));
+      piece[j] = s6 * half;
+      const R tol = sizeof(R) == 8 ? (R)1e-11 : (R)2e-6;
+      const bool redo = live && !(fabs(s4 - s6) <= tol * s6);
+      if (redo) {  // the reference's 32 nodes in table order (sc:854-880); rare, so the divergence is cheap
+        R acc = 0;
+#pragma unroll 4
+        for (int i = 0; i < 32; ++i) acc += (R)GL32_W[i] * speed(half * (R)GL32_X[i] + mid);
+        piece[j] = acc * half;
+      }
+      redo_any |= redo;
+    }
+    (void)redo_any;
+    // lane-local running sums, then an inclusive warp scan of the lane totals (sc:882-886 adds the
+    // pieces one after the other; this order differs from it by rounding only)
+    R run[kPiecesPerLane];
+    run[0] = piece[0];
+#pragma unroll
+    for (int j = 1; j < kPiecesPerLane; ++j) run[j] = run[j - 1] + piece[j];
+    R tot = live ? run[kPiecesPerLane - 1] : (R)0, incl = tot;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      const R up = __shfl_up_sync(kFullMask, incl, off);
+      if (lane >= off) incl += up;
+    }
+    const R base = incl - tot;
+    R* c = tab + (size_t)sg * kTable;
+    if (live) {
+#pragma unroll
+      for (int j = 0; j < kPiecesPerLane; ++j) c[lane * kPiecesPerLane + j + 1] = base + run[j];
+    }
+    if (lane == 0) c[0] = 0;
+    if (lane == kScanLanes - 1) segtot[sg] = incl;
+  }
+  __syncthreads();
+
+  // ---- path length, final status
+  if (tid < PBa) {
+    const int p = p0 + tid;
+    double acc = 0;
+    for (int s = 0; s < nseg; ++s) { acc += (double)segtot[tid * nseg + s]; segend[tid * nseg + s] = acc; }
+    const bool ok = !bad[tid] && acc > 0 && isfinite(acc);
+    if (!ok) bad[tid] = 1;
+    vse[tid * 2] = g.vel_start ? ((const R*)g.vel_start)[p] : (R)0;
+    vse[tid * 2 + 1] = g.vel_end ? ((const R*)g.vel_end)[p] : (R)0;
+    ((R*)g.L)[p] = ok ? (R)acc : (R)0;
+    if (!ok && g.cost) ((R*)g.cost)[p] = 0;
+    g.status[p] = ok ? SCB_ST_OK : SCB_ST_ERR_BAD_PATH;
+  }
+  __syncthreads();
+  for (int it = tid; it < PBa * nt; it += T) if (bad[it / nt]) tab[it] = 0;
+  if (g.ctrl_x && g.ctrl_y) {
+    for (int it = tid; it < PBa * nc; it += T) {
+      if (bad[it / nc]) { ((R*)g.ctrl_x)[(size_t)p0 * nc + it] = 0; ((R*)g.ctrl_y)[(size_t)p0 * nc + it] = 0; }
+    }
+  }
+  __syncthreads();  // the tables written above are read below by other threads of this CTA
+
+  // ---- geometry at the toppra gridpoints: q(s_i) -> (segment, u) -> point, curvature
+  if (g.px || g.py || g.kappa) {
+    const int G = g.G, N = G - 1;
+    const double step = 1.0 / (double)N;
+    R* o_px = (R*)g.px; R* o_py = (R*)g.py; R* o_k = (R*)g.kappa;
+    for (int it = tid; it < PBa * G; it += T) {
+      const int i = it / PBa, pl = it - i * PBa;
+      const size_t oo = (size_t)i * P + p0 + pl;
+      if (bad[pl]) {
+        if (o_px) o_px[oo] = 0; if (o_py) o_py[oo] = 0; if (o_k) o_k[oo] = 0;
+        continue;
+      }
+      R bx, by, kap;
+      gridpoint_geometry<R, DEG>(i, N, step, segend + pl * nseg, nseg, (double)vse[pl * 2], (double)vse[pl * 2 + 1],
+                                 tab + (size_t)pl * nt, ax + (size_t)pl * nseg * NC, ay + (size_t)pl * nseg * NC, bx, by, kap);
+      if (o_px) o_px[oo] = bx;
+      if (o_py) o_py[oo] = by;
+      if (o_k) o_k[oo] = kap;
+    }
+  }
+}
+
+// paths per CTA: 8 when the power bases fit ~40 KB (3+ CTAs per SM), fewer for long paths; 0 = too long
+int arc_paths_per_cta(int W, int spline_mode, int real_size, size_t& smem) {
+  const int deg = spline_mode == SCB_REF_CUBIC ? 3 : 5;
+  for (int pb = 8; pb >= 1; pb >>= 1) {
+    smem = arc_smem_bytes(W, deg, pb, real_size);
+    if (smem <= (pb > 1 ? 40 * 1024 : 200 * 1024)) return pb;
+  }
+  return 0;
+}
+
+template <class R> void launch_arc(const PathArgs& a0, int spline_mode, cudaStream_t st) {
+  PathArgs a = a0;
+  size_t smem;
+  const int PB = arc_paths_per_cta(a.W, spline_mode, (int)sizeof(R), smem);
+  if (!PB) return;
+  a.PB = PB;
+  const int grid = (a.P + PB - 1) / PB;
+  if (spline_mode == SCB_REF_CUBIC) {
+    cudaFuncSetAttribute(arc_kernel<R, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    arc_kernel<R, 3><<<grid, kArcThreads, smem, st>>>(a);
+  } else {
+    cudaFuncSetAttribute(arc_kernel<R, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    arc_kernel<R, 5><<<grid, kArcThreads, smem, st>>>(a);
+  }
+}
+template void launch_arc<double>(const PathArgs&, int, cudaStream_t);
+template void launch_arc<float>(const PathArgs&, int, cudaStream_t);
+
+}  // namespace scb

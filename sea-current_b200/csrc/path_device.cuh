@@ -1,0 +1,209 @@
+// Device helpers shared by the two path kernels (path_kernel.cu: CTA team, path_warp_kernel.cu:
+// warp team).  Reference lines are sea_current.hpp ("sc:").
+#pragma once
+#include "gl32_device.h"
+#include "scb_common.cuh"
+
+namespace scb {
+
+template <class R> __device__ __forceinline__ R dist2(R ax, R ay, R bx, R by) {  // sc:86-88 pt_dist
+  const R dx = bx - ax, dy = by - ay;
+  return sqrt(dx * dx + dy * dy);
+}
+
+// 1/sqrt(x) for a positive normal x.  FP64: MUFU.RSQ64H seed (2^-22) and one third-order step
+// y (1 + e/2 + 3 e^2/8), e = 1 - x y^2 -> full double precision in 5 FP64 instructions, no special-
+// case branches (CUDA's rsqrt() costs 16 instructions, 7 of them FP64: profiles/r1b_*.lines.txt).
+template <class R> __device__ __forceinline__ R fast_rsqrt(R x);
+template <> __device__ __forceinline__ float fast_rsqrt<float>(float x) { return rsqrtf(x); }
+template <> __device__ __forceinline__ double fast_rsqrt<double>(double x) {
+  double y;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+  const double e = fma(-x * y, y, 1.0);
+  const double p = fma(0.375, e, 0.5);
+  return fma(y * e, p, y);
+}
+
+// sc:347-369 (acos argument clamped: the one conscious fix, DESIGN.md "Deviations")
+template <class R>
+__device__ __forceinline__ void calc_tangent(R w0x, R w0y, R w1x, R w1y, R w2x, R w2y, R& tx, R& ty) {
+  const R ux = w0x - w1x, uy = w0y - w1y, vx = w2x - w1x, vy = w2y - w1y;
+  const R udv = ux * vx + uy * vy;
+  const R du = dist2<R>(ux, uy, 0, 0), dv = dist2<R>(vx, vy, 0, 0);
+  R arg = udv / (du * dv);
+  arg = fmax((R)-1, fmin((R)1, arg));
+  const R theta = acos(arg) / 2;
+  const R offset = atan2(uy, ux), test_offset = atan2(vy, vx);
+  const R mult = (test_offset - offset < 0) ? (R)-1 : (R)1;  // no angle wrapping, as the reference
+  R sn, cs;
+  sincos(offset + mult * theta, &sn, &cs);
+  R lx = sn, ly = -cs;
+  const R n2 = lx * lx + ly * ly;
+  if (n2 > 0) { const R n = sqrt(n2); lx = lx / n; ly = ly / n; }
+  const R m2 = dist2<R>(w1x + lx, w1y + ly, w2x, w2y) < dist2<R>(w1x - lx, w1y - ly, w2x, w2y) ? (R)1 : (R)-1;
+  const R mag = (R)0.5 * fmin(du, dv);  // sc:343-345: |W0W1| = |u|, |W1W2| = |v|
+  tx = mag * (m2 * lx); ty = mag * (m2 * ly);
+}
+
+// Tangent of waypoint i of one path (x, y: its W waypoints).  sc:371-377, 606-638.
+template <class R>
+__device__ __forceinline__ void waypoint_tangent(const R* x, const R* y, int W, int i, R start_angle, R& ox, R& oy) {
+  if (i == 0) {  // sc:371-373, 606-609
+    R ang = start_angle;
+    if (isnan(ang)) ang = atan2(y[1] - y[0], x[1] - x[0]);
+    const R mag = (R)0.5 * dist2<R>(x[0], y[0], x[1], y[1]);
+    R sn, cs; sincos(ang, &sn, &cs);
+    ox = mag * cs; oy = mag * sn;
+  } else if (i == W - 1) {  // sc:375-377
+    const R dx = x[i] - x[i - 1], dy = y[i] - y[i - 1];
+    const R mag = (R)0.5 * dist2<R>(x[i - 1], y[i - 1], x[i], y[i]);
+    const R n = sqrt(dx * dx + dy * dy);
+    ox = mag * (dx / n); oy = mag * (dy / n);
+  } else {
+    calc_tangent<R>(x[i - 1], y[i - 1], x[i], y[i], x[i + 1], y[i + 1], ox, oy);
+  }
+}
+
+template <class R> struct Carve {
+  R* base; size_t off;
+  __device__ __forceinline__ Carve(R* b) : base(b), off(0) {}
+  __device__ __forceinline__ R* take(size_t n) { R* p = base + off; off += n; return p; }
+};
+
+template <class R> struct HermiteQ {  // q(s) of gen_vel_prof's 1-DOF path (piecewise_poly_path.cpp:364-375)
+  R c0, c1, c2;
+  __device__ __forceinline__ void init(R L, R vs, R ve) { c2 = vs; c0 = (ve - (R)2 * L + vs); c1 = (ve - vs - (R)3 * c0) / (R)2; }
+  __device__ __forceinline__ R q(R s) const { return c0 * (s * s * s) + c1 * (s * s) + c2 * s; }
+};
+
+// Gauss-Legendre rules on [-1, 1] (positive halves)
+static __constant__ double kG4X[2] = {0.3399810435848562648, 0.8611363115940525752};
+static __constant__ double kG4W[2] = {0.6521451548625461426, 0.3478548451374538574};
+static __constant__ double kG6X[3] = {0.2386191860831969086, 0.6612093864662645137, 0.9324695142031520278};
+static __constant__ double kG6W[3] = {0.4679139345726910473, 0.3607615730481386076, 0.1713244923791703450};
+// 4-point rule in the node order the arc-length inversion uses (DESIGN.md "Arc-length inversion")
+static __constant__ double kPGL4X[4] = {-0.8611363115940525752, -0.3399810435848562648, 0.3399810435848562648,
+                                            0.8611363115940525752};
+static __constant__ double kPGL4W[4] = {0.3478548451374538574, 0.6521451548625461426, 0.6521451548625461426,
+                                            0.3478548451374538574};
+
+// iRPROP- update of one parameter (DESIGN.md "New stages")
+template <class R> __device__ __forceinline__ R rprop_step(R gv, R& gprev, R& step, R smin, R smax) {
+  const R s = gv * gprev;
+  if (s > 0) step = fmin(step * (R)1.2, smax);
+  else if (s < 0) { step = fmax(step * (R)0.5, smin); gv = 0; }
+  gprev = gv;
+  return gv > 0 ? -step : (gv < 0 ? step : (R)0);
+}
+
+// Power basis of one segment: a_k = C(d,k) Delta^k P_0 (curve) and h_k likewise for the hodograph
+// control points d (P[j+1] - P[j])  (sc:1041-1053).
+template <class R, int DEG>
+__device__ __forceinline__ void power_basis(const R* cx, const R* cy, R* ax, R* ay, R* hx, R* hy) {
+  constexpr int NC = DEG + 1;
+  R dx[NC], dy[NC];
+#pragma unroll
+  for (int j = 0; j < NC; ++j) { dx[j] = cx[j]; dy[j] = cy[j]; }
+  R hdx[DEG], hdy[DEG];
+#pragma unroll
+  for (int j = 0; j < DEG; ++j) { hdx[j] = (R)DEG * (dx[j + 1] - dx[j]); hdy[j] = (R)DEG * (dy[j + 1] - dy[j]); }
+  R binom = 1;
+#pragma unroll
+  for (int k = 0; k <= DEG; ++k) {
+    ax[k] = binom * dx[0]; ay[k] = binom * dy[0];
+#pragma unroll
+    for (int j = 0; j + k < DEG; ++j) { dx[j] = dx[j + 1] - dx[j]; dy[j] = dy[j + 1] - dy[j]; }
+    binom = binom * (R)(DEG - k) / (R)(k + 1);
+  }
+  binom = 1;
+#pragma unroll
+  for (int k = 0; k < DEG; ++k) {
+    hx[k] = binom * hdx[0]; hy[k] = binom * hdy[0];
+#pragma unroll
+    for (int j = 0; j + k < DEG - 1; ++j) { hdx[j] = hdx[j + 1] - hdx[j]; hdy[j] = hdy[j + 1] - hdy[j]; }
+    binom = binom * (R)(DEG - 1 - k) / (R)(k + 1);
+  }
+}
+
+// Basis values of B' and B'' of a quintic at cost node `node` of the 32-point rule mapped to [0,1]:
+// out[0..5] = dB'/dP_j, out[6..11] = dB''/dP_j, out[12] = quadrature weight (DESIGN.md "New stages").
+template <class R> __device__ __forceinline__ void lau_node_basis(R* out, int node) {
+  const double t = 0.5 * GL32_X[node] + 0.5, s = 1 - t;
+  const double b4[5] = {s * s * s * s, 4 * t * s * s * s, 6 * t * t * s * s, 4 * t * t * t * s, t * t * t * t};
+  const double b3[4] = {s * s * s, 3 * t * s * s, 3 * t * t * s, t * t * t};
+#pragma unroll
+  for (int j = 0; j < 6; ++j) {
+    const double lo = j > 0 ? b4[j - 1] : 0, hi = j < 5 ? b4[j] : 0;
+    out[j] = (R)(5 * (lo - hi));
+    const double a = j >= 2 ? b3[j - 2] : 0, b = (j >= 1 && j <= 4) ? b3[j - 1] : 0, c = j <= 3 ? b3[j] : 0;
+    out[6 + j] = (R)(20 * (a - 2 * b + c));
+  }
+  out[12] = (R)(0.5 * GL32_W[node]);
+}
+
+// Geometry at toppra gridpoint i of one path: arc length q(s_i) (FP64, Hermite path of gen_vel_prof)
+// -> segment (first j with q <= segend[j]) -> table sub-interval -> Newton on a 4-point Gauss-Legendre
+// integral of |B'| (kInvNewton steps, DESIGN.md "Arc-length inversion") -> curve point and curvature (sc:1029).
+//   segend: cumulative segment ends of this path (FP64); tab: its [nseg][101] cumulative table;
+//   ax, ay: its [nseg][DEG+1] power-basis coefficients.
+template <class R, int DEG>
+__device__ __forceinline__ void gridpoint_geometry(int i, int N, double step, const double* segend, int nseg, double vs, double ve,
+                                                   const R* tab, const R* ax, const R* ay, R& bx, R& by, R& kap) {
+  constexpr int NC = DEG + 1;
+  HermiteQ<double> hq;
+  const double Ltot = segend[nseg - 1];
+  hq.init(Ltot, vs, ve);
+  double q = hq.q(i == N ? 1.0 : (double)i * step);
+  q = fmin(fmax(q, 0.0), Ltot);
+  int lo = 0, hi = nseg - 1;
+  while (lo < hi) { const int m = (lo + hi) >> 1; if (q <= segend[m]) hi = m; else lo = m + 1; }
+  const int sg = lo;
+  const R r = (R)(q - (sg > 0 ? segend[sg - 1] : 0.0));
+  const R* c = tab + (size_t)sg * kTable;
+  const R seg_len = (R)(segend[sg] - (sg > 0 ? segend[sg - 1] : 0.0));
+  // largest kl in [0, 99] with c[kl] <= r: the table is close to linear, so start from the proportional
+  // guess and walk (two independent loads, then rarely more) instead of seven dependent bisection loads
+  int kl = (int)((R)kSub * r / seg_len);
+  kl = max(0, min(kSub - 1, kl));
+  while (kl > 0 && c[kl] > r) --kl;
+  while (kl < kSub - 1 && c[kl + 1] <= r) ++kl;
+  const R h = (R)0.01, a0 = fmin((R)kl * h, (R)1);
+  const R ck = c[kl], target = r - ck;
+  R du = h * target / (c[kl + 1] - ck);
+  du = fmin(fmax(du, (R)0), h);
+  const R* sax = ax + NC * sg; const R* say = ay + NC * sg;
+  R kx[DEG], ky[DEG];  // B' in power basis: (k+1) a_{k+1}
+#pragma unroll
+  for (int j = 0; j < DEG; ++j) { kx[j] = (R)(j + 1) * sax[j + 1]; ky[j] = (R)(j + 1) * say[j + 1]; }
+  auto speed = [&](R u) {
+    R dx = kx[DEG - 1], dy = ky[DEG - 1];
+#pragma unroll
+    for (int j = DEG - 2; j >= 0; --j) { dx = dx * u + kx[j]; dy = dy * u + ky[j]; }
+    const R n2 = dx * dx + dy * dy;
+    return n2 > 0 ? n2 * fast_rsqrt<R>(n2) : (R)0;
+  };
+#pragma unroll 1
+  for (int nit = 0; nit < kInvNewton; ++nit) {
+    const R half = (R)0.5 * du, mid = a0 + half;
+    R F = 0;
+#pragma unroll
+    for (int gq = 0; gq < 4; ++gq) F += (R)kPGL4W[gq] * speed(mid + half * (R)kPGL4X[gq]);
+    F *= half;
+    du = du - (F - target) / speed(a0 + du);
+    du = fmin(fmax(du, (R)0), h);
+  }
+  const R u = fmin(a0 + du, (R)1);
+  bx = sax[DEG]; by = say[DEG];
+#pragma unroll
+  for (int j = DEG - 1; j >= 0; --j) { bx = bx * u + sax[j]; by = by * u + say[j]; }
+  R x1 = kx[DEG - 1], y1 = ky[DEG - 1];
+#pragma unroll
+  for (int j = DEG - 2; j >= 0; --j) { x1 = x1 * u + kx[j]; y1 = y1 * u + ky[j]; }
+  R x2 = (R)(DEG - 1) * kx[DEG - 1], y2 = (R)(DEG - 1) * ky[DEG - 1];
+#pragma unroll
+  for (int j = DEG - 3; j >= 0; --j) { x2 = x2 * u + (R)(j + 1) * kx[j + 1]; y2 = y2 * u + (R)(j + 1) * ky[j + 1]; }
+  const R n2 = x1 * x1 + y1 * y1, rn = fast_rsqrt<R>(n2);
+  kap = (x1 * y2 - y1 * x2) * (rn * rn * rn);
+}
+
+}  // namespace scb

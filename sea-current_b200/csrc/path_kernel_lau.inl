@@ -1,7 +1,7 @@
 // Body of path_kernel<R, 5>: Lau09 quintic builder (A5), curvature/arc-length cost with analytic
 // gradient (A6) and the iRPROP- loop (A7).  Included inside the kernel; see path_kernel.cu for the
 // names in scope.  tx/ty hold the frozen base tangents Bt.  No reference code exists for these
-// stages: the frozen definition is oracle/ora_lau.hpp (DESIGN.md "New stages").
+// stages: the frozen definition is DESIGN.md "New stages" (DESIGN.md "New stages").
     R* w0x = sm.take(PB * W); R* w0y = sm.take(PB * W); R* mag = sm.take(PB * W); R* alpha = sm.take(PB * W);
     R* e = sm.take(PB * W); R* se = sm.take(PB * W); R* pe = sm.take(PB * W);
     R* swx = sm.take(PB * W); R* swy = sm.take(PB * W); R* pwx = sm.take(PB * W); R* pwy = sm.take(PB * W);

@@ -3,8 +3,8 @@
 // Host side of the drop-in boundary: owns the CUDA stream, the device scratch that the fused
 // kernels need between stages (arc-length tables, controllable sets, Thomas scratch) and, for
 // the host-buffer entry point, the device mirrors of the caller's arrays.  No planning
-// arithmetic happens on the host: every stage is a kernel launch (spline_kernel.cu,
-// toppra_kernel.cu, param_kernel.cu).  There is no CPU fallback — without an sm_100 device
+// arithmetic happens on the host: every stage is a kernel launch (path_warp_kernel.cu / path_kernel.cu,
+// arc_kernel.cu, toppra_fast_kernel.cu / toppra_kernel.cu, param_kernel.cu).  There is no CPU fallback — without an sm_100 device
 // scb_create fails with SCB_E_NO_DEVICE.
 //
 // Reference call sequence replaced (examples/json_test.cpp:28-58):
@@ -117,15 +117,12 @@ int run_device(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, i
   void* dKappa = nullptr;
   if (do_spline) {
     const size_t nseg = W - 1;
-    int pb, th; bool tab_smem; size_t smb;
-    path_launch_shape(W, ctx->cfg.spline_mode, (int)rs, pb, th, tab_smem, smb);
-    const bool geo_stream = do_geo && want_stream;  // the uniform-dt sampler walks the tables in HBM
+    // the control points and the arc-length tables are the hand-over between the path kernel and the
+    // arc kernel (and the uniform-dt sampler): scratch when the caller did not ask for them
     if (!dL && (rc = ensure(ctx, SL_L, P * rs, &dL))) return rc;
-    if (!dTab && (!tab_smem || geo_stream) && (rc = ensure(ctx, SL_TABLE, (size_t)P * nseg * kTable * rs, &dTab))) return rc;
-    if (geo_stream) {
-      if (!dCx && (rc = ensure(ctx, SL_CTRL_X, (size_t)P * nseg * (deg + 1) * rs, &dCx))) return rc;
-      if (!dCy && (rc = ensure(ctx, SL_CTRL_Y, (size_t)P * nseg * (deg + 1) * rs, &dCy))) return rc;
-    }
+    if (!dTab && (rc = ensure(ctx, SL_TABLE, (size_t)P * nseg * kTable * rs, &dTab))) return rc;
+    if (!dCx && (rc = ensure(ctx, SL_CTRL_X, (size_t)P * nseg * (deg + 1) * rs, &dCx))) return rc;
+    if (!dCy && (rc = ensure(ctx, SL_CTRL_Y, (size_t)P * nseg * (deg + 1) * rs, &dCy))) return rc;
     PathArgs a{};
     a.P = P; a.W = W; a.G = G; a.wx = in->wx; a.wy = in->wy; a.start_angle = in->start_angle;
     a.vel_start = in->vel_start; a.vel_end = in->vel_end;
@@ -136,7 +133,7 @@ int run_device(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, i
     }
     a.opt = in->opt;
     launch_path<R>(a, ctx->cfg.spline_mode, st);
-    ++launches;
+    launches += 2;  // path kernel + arc kernel
   } else {
     SCB_CUDA(cudaMemsetAsync(out->status, 0, (size_t)P * 4, st));
     dL = (void*)in->path_len;

@@ -84,6 +84,6 @@ def test_product_never_imports_oracle():
     for sub in ("sea-current_b200", "include"):
         for dp, _, fs in os.walk(os.path.join(ROOT, sub)):
             for f in fs:
-                if f.endswith((".py", ".cu", ".cuh", ".h", ".hpp")) or f == "Makefile":
+                if f.endswith((".py", ".cu", ".cuh", ".inl", ".h", ".hpp")) or f == "Makefile":
                     m = pat.search(open(os.path.join(dp, f)).read())
                     assert m is None, (dp, f, m.group(0))

@@ -248,13 +248,23 @@ def test_fp32_mode_within_1e4(planners, oracle):
         ref, _ = oracle.plan_batch(wx=wx, wy=wy, G=G, spline_mode=0 if mode == "ref_cubic" else 1, **lim)
         np.testing.assert_array_equal(res["status"], ref["status"])
         ok = ref["status"] == 0
-        for n in ("arclen_total", "T_total", "ctrl_x", "ctrl_y", "x", "K_hi", "K_lo", "t", "px", "py", "v", "omega"):
+        for n in ("arclen_total", "T_total", "ctrl_x", "ctrl_y", "x", "K_hi", "K_lo", "t", "px", "py", "v"):
             g, w = (res[n][:, ok], ref[n][:, ok]) if n in GRID else (res[n][ok], ref[n][ok])
             # positions are judged against the extent of the path, everything else against 1 % of its range
-            # (omega = v * kappa is spiky: arc positions carry float eps * L, which moves narrow curvature peaks)
-            frac = 1.0 if n in ("ctrl_x", "ctrl_y", "px", "py") else 1e-1 if n == "omega" else 1e-2
+            frac = 1.0 if n in ("ctrl_x", "ctrl_y", "px", "py") else 1e-2
             e = rel_err(g, w, floor=frac * float(np.max(np.abs(ref["K_hi" if n == "K_lo" else n]))))
             assert e <= RTOL32, (mode, n, e)
+        # omega = v * kappa(u): the curve parameter u of a gridpoint comes out of float tables, i.e. with an
+        # uncertainty of ~4 eps32 of a segment; where the curvature has a narrow peak that moves omega by
+        # |d omega / d u| * 4 eps32.  The slope is taken from the oracle's own omega (finite differences
+        # over the gridpoint index i; du/di = (W-1) * 6 s (1-s) / N for q = L (3 s^2 - 2 s^3)).
+        w = ref["omega"][:, ok]; g = res["omega"][:, ok]
+        sg = np.linspace(0.0, 1.0, G)[:, None]
+        du_di = (W - 1) * 6.0 * sg * (1.0 - sg) / (G - 1)
+        di = np.minimum(4 * np.finfo(np.float32).eps / np.maximum(du_di, 1e-300), 1.0)
+        cond = np.abs(np.gradient(w, axis=0)) * di
+        tol = RTOL32 * np.maximum(np.abs(w), 1e-1 * np.abs(w).max(axis=0, keepdims=True)) + cond
+        assert np.all(np.abs(g - w) <= tol), (mode, "omega", float(np.max(np.abs(g - w) / tol)))
 
 
 # ------------------------------------------------------------------ size-independent properties at full size
@@ -360,7 +370,8 @@ def test_python_toppra_fixture(planners, golden_dir):
     for lp in (scb.abi.LP_SEIDEL, scb.abi.LP_CLOSED_FORM):
         res = pl.plan(path_len=[c["L"] for c in cs], G=g["G"], stages=scb.abi.STAGE_TIMING, lp_mode=lp,
                       vel_lo=[c["vel"][0] for c in cs], vel_hi=[c["vel"][1] for c in cs], acc_lo=[c["acc"][0] for c in cs],
-                      acc_hi=[c["acc"][1] for c in cs], outputs=("K_lo", "K_hi", "x", "T_total"))
+                      acc_hi=[c["acc"][1] for c in cs], vel_start=[c["vel_start"] for c in cs], vel_end=[c["vel_end"] for c in cs],
+                      outputs=("K_lo", "K_hi", "x", "T_total"))
         assert np.all(res["status"] == 0)
         for p, c in enumerate(cs):
             np.testing.assert_allclose(res["x"][:, p], c["x"], rtol=3e-7, atol=3e-10 * max(c["x"]), err_msg=c["name"])
