@@ -129,58 +129,68 @@ struct Hermite1 {  // FP64 in both precision modes, like the toppra kernel
 };
 
 // `S` is the storage type of the caller's arrays; the recurrences (knot times, Thomas) run in FP64
-// and their scratch (t_buf, X_buf, cp_buf) is always double.
+// and their scratch (t_buf, X_buf, cp_buf) is always double.  Both sweeps are sequential per problem,
+// so the kernel lives on memory-level parallelism: every thread fetches kPU gridpoints of each input
+// array before it touches the dependent arithmetic (a warp's 32 problems = 256 contiguous bytes per
+// gridpoint), and quotients go through fast_rcp / fast_sqrt (no IEEE division sequences).
+constexpr int kPU = 8;
+
 template <class S>
-__global__ void __launch_bounds__(64) param_kernel(ParamArgs g) {
+__global__ void __launch_bounds__(32) param_kernel(ParamArgs g) {
   typedef double R;
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
   if (p >= g.P) return;
   const int P = g.P, G = g.G, N = G - 1;
-  const S* X2 = (const S*)g.x;  // sdot^2
-  R* tb = (R*)g.t_buf; R* Xb = (R*)g.X_buf; R* cpb = (R*)g.cp_buf;
-  S* o_t = (S*)g.t; S* o_v = (S*)g.v; S* o_a = (S*)g.a; S* o_om = (S*)g.omega;
-  const S* kap = (const S*)g.kappa;
+  const S* __restrict__ X2 = (const S*)g.x;  // sdot^2
+  R* __restrict__ tb = (R*)g.t_buf; R* __restrict__ Xb = (R*)g.X_buf; R* __restrict__ cpb = (R*)g.cp_buf;
+  S* __restrict__ o_t = (S*)g.t; S* __restrict__ o_v = (S*)g.v; S* __restrict__ o_a = (S*)g.a; S* __restrict__ o_om = (S*)g.omega;
+  const S* __restrict__ kap = (const S*)g.kappa;
   int status = g.status[p];
   Hermite1 hp;
   if (status == SCB_ST_OK) {
     hp.init((R)((const S*)g.L)[p], g.vel_start ? (R)((const S*)g.vel_start)[p] : 0.0,
             g.vel_end ? (R)((const S*)g.vel_end)[p] : 0.0, N);
-    // ---- pass 1: knot times + Thomas forward elimination
-    const R sd0 = sqrt((R)X2[p]);
-    R sd_prev = sd0, t = 0, t_prev = 0, t_pp = 0;
-    R q_pp = 0, q_prev = hp.q(hp.s_at(0)), s_prev = hp.s_at(0);
+    // ---- pass 1: knot times (trapezoid rule, spline.cpp:14-24) + Thomas forward elimination of the
+    //      clamped cubic spline through (t_i, q(s_i))  (piecewise_poly_path.cpp:102-176)
+    const R sd0 = fast_sqrt((R)X2[p]);
+    R sd_prev = sd0, t_prev = 0, h_prev = 0, slope_prev = 0;
+    R q_prev = hp.q(hp.s_at(0)), s_prev = hp.s_at(0);
     R cp_prev = 0, b_prev = 0;
     const R bc0 = hp.qd(hp.s_at(0)) * sd0;
     tb[p] = 0;
-    for (int i = 1; i <= N; ++i) {
-      const R s = hp.s_at(i), sd = sqrt((R)X2[(size_t)i * P + p]);
-      const R avg = (sd_prev + sd) / 2;
-      const R dt = avg > 1e-8 ? (s - s_prev) / avg : 5.0;
-      if (dt < 1e-8) status = SCB_ST_ERR_TIME_KNOTS;
-      t = t_prev + dt;
-      tb[(size_t)i * P + p] = t;
-      const R qi = hp.q(s);
-      const R h = t - t_prev;  // h_{i-1}
-      // row j = i - 1
-      R lo, di, up, B;
-      if (i == 1) { lo = 0; di = 2 * h; up = h; B = 3 * (qi - q_prev) / h - 3 * bc0; }
-      else {
-        const R hm = t_prev - t_pp;  // h_{i-2}
-        lo = hm; di = 2 * (hm + h); up = h;
-        B = 3 * (qi - q_prev) / h - 3 * (q_prev - q_pp) / hm;
+    for (int i0 = 1; i0 <= N; i0 += kPU) {
+      R xs[kPU];
+#pragma unroll
+      for (int u = 0; u < kPU; ++u) xs[u] = (R)X2[(size_t)min(i0 + u, N) * P + p];
+#pragma unroll
+      for (int u = 0; u < kPU; ++u) {
+        const int i = i0 + u;
+        if (i <= N) {
+          const R s = hp.s_at(i), sd = fast_sqrt(xs[u]);
+          const R avg = (sd_prev + sd) * 0.5;
+          const R dt = avg > 1e-8 ? (s - s_prev) * fast_rcp<R>(avg) : 5.0;
+          if (dt < 1e-8) status = SCB_ST_ERR_TIME_KNOTS;
+          const R t = t_prev + dt;
+          tb[(size_t)i * P + p] = t;
+          const R qi = hp.q(s);
+          const R h = t - t_prev;                          // h_{i-1}
+          const R slope = (qi - q_prev) * fast_rcp<R>(h);  // (q_i - q_{i-1}) / h_{i-1}
+          // row j = i - 1 of the tridiagonal system
+          R lo, di, B;
+          if (i == 1) { lo = 0; di = 2 * h; B = 3 * slope - 3 * bc0; }
+          else { lo = h_prev; di = 2 * (h_prev + h); B = 3 * slope - 3 * slope_prev; }
+          const R rm = fast_rcp<R>(di - lo * cp_prev);
+          const R cpj = h * rm, bj = (B - lo * b_prev) * rm;
+          cpb[(size_t)(i - 1) * P + p] = cpj; Xb[(size_t)(i - 1) * P + p] = bj;
+          cp_prev = cpj; b_prev = bj;
+          if (i == N) {  // last row j = N
+            const R bc1 = hp.qd(s) * sd;
+            const R B2 = 3 * bc1 - 3 * slope;
+            Xb[(size_t)N * P + p] = (B2 - h * b_prev) * fast_rcp<R>(2 * h - h * cp_prev);  // = X_N
+          }
+          t_prev = t; h_prev = h; slope_prev = slope; q_prev = qi; s_prev = s; sd_prev = sd;
+        }
       }
-      R cpj, bj;
-      if (i == 1) { cpj = up / di; bj = B / di; }
-      else { const R m = di - lo * cp_prev; cpj = up / m; bj = (B - lo * b_prev) / m; }
-      cpb[(size_t)(i - 1) * P + p] = cpj; Xb[(size_t)(i - 1) * P + p] = bj;
-      cp_prev = cpj; b_prev = bj;
-      if (i == N) {  // last row j = N
-        const R bc1 = hp.qd(s) * sd;
-        const R lo2 = h, di2 = 2 * h, B2 = 3 * bc1 - 3 * (qi - q_prev) / h;
-        const R m = di2 - lo2 * cp_prev;
-        Xb[(size_t)N * P + p] = (B2 - lo2 * b_prev) / m;  // = X_N
-      }
-      t_pp = t_prev; t_prev = t; q_pp = q_prev; q_prev = qi; s_prev = s; sd_prev = sd;
     }
   }
   if (status != SCB_ST_OK) {
@@ -198,31 +208,42 @@ __global__ void __launch_bounds__(64) param_kernel(ParamArgs g) {
   R t_next = tb[(size_t)N * P + p];
   R q_next = hp.q(hp.s_at(N));
   if (g.T_total) ((S*)g.T_total)[p] = (S)(t_next - tb[p]);
-  for (int i = N; i >= 0; --i) {
-    const size_t o = (size_t)i * P + p;
-    R vi, ai;
-    if (i == N) {
-      // knot N is evaluated on the last segment at ds = h (piecewise_poly_path.cpp:240-252)
-      const R Xi = Xb[(size_t)(N - 1) * P + p] - cpb[(size_t)(N - 1) * P + p] * X_next;
-      const R ti = tb[(size_t)(N - 1) * P + p];
-      const R qm = hp.q(hp.s_at(N - 1));
-      const R h = t_next - ti;
-      const R k0 = (X_next - Xi) / (3 * h), k1 = Xi, k2 = (q_next - qm) / h - h / 3 * (2 * Xi + X_next);
-      vi = (k0 * 3) * (h * h) + (k1 * 2) * h + k2;
-      ai = ((k0 * 3) * 2) * h + k1 * 2;
-    } else {
-      const R Xi = Xb[o] - cpb[o] * X_next;
-      Xb[o] = Xi;
-      const R ti = tb[o], qv = hp.q(hp.s_at(i));
-      const R h = t_next - ti;
-      vi = (q_next - qv) / h - h / 3 * (2 * Xi + X_next);
-      ai = Xi * 2;
-      X_next = Xi; t_next = ti; q_next = qv;
+  const R kapN = kap ? (R)kap[(size_t)N * P + p] : 0.0;
+  const R X_N = X_next, t_N = t_next;
+  for (int i0 = N - 1; i0 >= 0; i0 -= kPU) {
+    R xb[kPU], cb[kPU], tt[kPU], kk[kPU];
+#pragma unroll
+    for (int u = 0; u < kPU; ++u) {
+      const size_t o = (size_t)max(i0 - u, 0) * P + p;
+      xb[u] = Xb[o]; cb[u] = cpb[o]; tt[u] = tb[o]; kk[u] = kap ? (R)kap[o] : 0.0;
     }
-    if (o_t) o_t[o] = (S)tb[o];
-    if (o_v) o_v[o] = (S)vi;
-    if (o_a) o_a[o] = (S)ai;
-    if (o_om) o_om[o] = kap ? (S)(vi * (R)kap[o]) : (S)0;
+#pragma unroll
+    for (int u = 0; u < kPU; ++u) {
+      const int i = i0 - u;
+      if (i >= 0) {
+        const size_t o = (size_t)i * P + p;
+        const R Xi = xb[u] - cb[u] * X_next;
+        if (g.keep_X) Xb[o] = Xi;
+        const R ti = tt[u], qv = hp.q(hp.s_at(i));
+        const R h = t_next - ti;
+        const R vi = (q_next - qv) * fast_rcp<R>(h) - h * (1.0 / 3.0) * (2 * Xi + X_next);
+        if (i == N - 1) {
+          // knot N is evaluated on the last segment at ds = h (piecewise_poly_path.cpp:240-252)
+          const R k0 = (X_N - Xi) * fast_rcp<R>(3 * h), k1 = Xi;
+          const R vN = (k0 * 3) * (h * h) + (k1 * 2) * h + vi, aN = ((k0 * 3) * 2) * h + k1 * 2;
+          const size_t oN = (size_t)N * P + p;
+          if (o_t) o_t[oN] = (S)t_N;
+          if (o_v) o_v[oN] = (S)vN;
+          if (o_a) o_a[oN] = (S)aN;
+          if (o_om) o_om[oN] = (S)(vN * kapN);
+        }
+        if (o_t) o_t[o] = (S)ti;
+        if (o_v) o_v[o] = (S)vi;
+        if (o_a) o_a[o] = (S)(Xi * 2);
+        if (o_om) o_om[o] = (S)(vi * kk[u]);
+        X_next = Xi; t_next = ti; q_next = qv;
+      }
+    }
   }
 }
 
@@ -322,7 +343,7 @@ __global__ void __launch_bounds__(64) sample_kernel(SampleArgs g) {
 }
 
 template <class R> void launch_param(const ParamArgs& a, cudaStream_t st) {
-  const int block = 64, grid = (a.P + block - 1) / block;
+  const int block = 32, grid = (a.P + block - 1) / block;
   param_kernel<R><<<grid, block, 0, st>>>(a);  // R = storage type
 }
 template <class R> void launch_sample(const SampleArgs& a, cudaStream_t st) {

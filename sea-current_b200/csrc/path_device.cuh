@@ -11,19 +11,6 @@ template <class R> __device__ __forceinline__ R dist2(R ax, R ay, R bx, R by) { 
   return sqrt(dx * dx + dy * dy);
 }
 
-// 1/sqrt(x) for a positive normal x.  FP64: MUFU.RSQ64H seed (2^-22) and one third-order step
-// y (1 + e/2 + 3 e^2/8), e = 1 - x y^2 -> full double precision in 5 FP64 instructions, no special-
-// case branches (CUDA's rsqrt() costs 16 instructions, 7 of them FP64: profiles/r1b_*.lines.txt).
-template <class R> __device__ __forceinline__ R fast_rsqrt(R x);
-template <> __device__ __forceinline__ float fast_rsqrt<float>(float x) { return rsqrtf(x); }
-template <> __device__ __forceinline__ double fast_rsqrt<double>(double x) {
-  double y;
-  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
-  const double e = fma(-x * y, y, 1.0);
-  const double p = fma(0.375, e, 0.5);
-  return fma(y * e, p, y);
-}
-
 // sc:347-369 (acos argument clamped: the one conscious fix, DESIGN.md "Deviations")
 template <class R>
 __device__ __forceinline__ void calc_tangent(R w0x, R w0y, R w1x, R w1y, R w2x, R w2y, R& tx, R& ty) {

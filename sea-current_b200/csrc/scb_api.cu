@@ -168,6 +168,7 @@ int run_device(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, i
     q.x = dX; q.kappa = dKappa;
     q.t = f64 ? nullptr : out->t; q.v = out->v; q.a = out->a; q.omega = out->omega;
     q.t_buf = dT; q.X_buf = dXb; q.cp_buf = dCp; q.T_total = out->T_total; q.status = out->status;
+    q.keep_X = want_stream ? 1 : 0;
     launch_param<R>(q, st);
     ++launches;
   } else {

@@ -29,6 +29,35 @@ template <class R> __device__ __forceinline__ R rsqrt_(R v);
 template <> __device__ __forceinline__ double rsqrt_(double v) { return rsqrt(v); }
 template <> __device__ __forceinline__ float rsqrt_(float v) { return rsqrtf(v); }
 
+// 1/sqrt(x) for a positive normal x.  FP64: MUFU.RSQ64H seed (2^-22) and one third-order step
+// y (1 + e/2 + 3 e^2/8), e = 1 - x y^2 -> full double precision in 5 FP64 instructions, no special-
+// case branches (CUDA's rsqrt() costs 16 instructions, 7 of them FP64: profiles/r1b_*.lines.txt).
+template <class R> __device__ __forceinline__ R fast_rsqrt(R x);
+template <> __device__ __forceinline__ float fast_rsqrt<float>(float x) { return rsqrtf(x); }
+template <> __device__ __forceinline__ double fast_rsqrt<double>(double x) {
+  double y;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+  const double e = fma(-x * y, y, 1.0);
+  const double p = fma(0.375, e, 0.5);
+  return fma(y * e, p, y);
+}
+
+// 1/x for a normal x.  FP64: MUFU.RCP64H seed and two Newton steps (4 FMAs) instead of the ~20-instruction
+// IEEE division sequence; relative error <= ~1 ulp.  Used where the result feeds a 1e-9 tolerance, never in the
+// bit-exact Seidel kernel.
+template <class R> __device__ __forceinline__ R fast_rcp(R x);
+template <> __device__ __forceinline__ float fast_rcp<float>(float x) { return __frcp_rn(x); }
+template <> __device__ __forceinline__ double fast_rcp<double>(double x) {
+  double y;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+  double e = fma(-x, y, 1.0);
+  y = fma(y, e, y);
+  e = fma(-x, y, 1.0);
+  return fma(y, e, y);
+}
+// sqrt(x) for x >= 0 through fast_rsqrt
+__device__ __forceinline__ double fast_sqrt(double x) { return x > 0 ? x * fast_rsqrt<double>(x) : 0.0; }
+
 // Kernel-argument bundles (plain pointers; R-typed buffers passed as void* and cast inside).
 struct PathArgs {
   int P, W, G, PB;                    // PB (paths per CTA) and table_in_smem are filled in by launch_path
@@ -66,6 +95,7 @@ struct ParamArgs {
   void *t_buf, *X_buf, *cp_buf;        // [G][P] scratch: knot times, spline unknowns, Thomas c'
   void *T_total;                       // [P]
   int32_t* status;
+  int keep_X;                          // 1: X_buf must hold the solved unknowns afterwards (the uniform-dt sampler reads them)
 };
 
 struct SampleArgs {

@@ -255,13 +255,13 @@ def test_fp32_mode_within_1e4(planners, oracle):
             e = rel_err(g, w, floor=frac * float(np.max(np.abs(ref["K_hi" if n == "K_lo" else n]))))
             assert e <= RTOL32, (mode, n, e)
         # omega = v * kappa(u): the curve parameter u of a gridpoint comes out of float tables, i.e. with an
-        # uncertainty of ~4 eps32 of a segment; where the curvature has a narrow peak that moves omega by
-        # |d omega / d u| * 4 eps32.  The slope is taken from the oracle's own omega (finite differences
+        # uncertainty of ~16 eps32 of a segment (cumulative float sums over 100 table entries); where the curvature has a narrow peak that moves omega by
+        # |d omega / d u| * 16 eps32.  The slope is taken from the oracle's own omega (finite differences
         # over the gridpoint index i; du/di = (W-1) * 6 s (1-s) / N for q = L (3 s^2 - 2 s^3)).
         w = ref["omega"][:, ok]; g = res["omega"][:, ok]
         sg = np.linspace(0.0, 1.0, G)[:, None]
         du_di = (W - 1) * 6.0 * sg * (1.0 - sg) / (G - 1)
-        di = np.minimum(4 * np.finfo(np.float32).eps / np.maximum(du_di, 1e-300), 1.0)
+        di = np.minimum(16 * np.finfo(np.float32).eps / np.maximum(du_di, 1e-300), 1.0)
         cond = np.abs(np.gradient(w, axis=0)) * di
         tol = RTOL32 * np.maximum(np.abs(w), 1e-1 * np.abs(w).max(axis=0, keepdims=True)) + cond
         assert np.all(np.abs(g - w) <= tol), (mode, "omega", float(np.max(np.abs(g - w) / tol)))
