@@ -12,7 +12,9 @@ same batch per rank (weak scaling), per-problem summary records all-gathered ove
 value      whole-job trajectories/s, inputs and outputs resident in HBM (CUDA events on the ctx stream,
            max over ranks)
 e2e        same metric through scb_plan_batch with pinned HOST buffers (H2D + kernels + D2H timed)
-roofline   dominant kernel: its own algorithmic bytes / its mean launch duration vs measured HBM peak
+roofline   dominant kernel (by duration): algorithmic flops (or bytes) / its mean launch duration against the pipe
+           that binds it -- the FP64/FP32 vector pipe (measured FMA peak, profiles/r1_fp_peak.json) or HBM
+           (MEASURED_PEAKS.json); `kernels` lists every kernel of the step against both, `path` the whole step
 cpu_baseline  the oracle's reference-faithful port of the E1 body timed on this box's host cores
 """
 import argparse
@@ -220,34 +222,67 @@ def main():
     ms_per_step = ms / a.steps
     value = cfg["P_global"] / (ms_per_step * 1e-3) if scaling == "weak" else cfg["P_global"] / (ms_per_step * 1e-3)
 
-    # ---- per-kernel durations (CUDA events recorded by the ctx around every stage, one step at a time)
-    stage_ms = {"spline_ms": [], "toppra_ms": [], "param_ms": [], "sample_ms": []}
+    # ---- per-kernel durations (CUDA events recorded by the ctx around every kernel, one step at a time)
+    keys = ("path_ms", "arc_ms", "toppra_ms", "param_ms", "sample_ms")
+    stage_ms = {k: [] for k in keys}
     for _ in range(min(a.steps, 5)):
         pl.run_device(bi, bo, sync=True)
         tm = pl.timing()
-        for k in stage_ms:
+        for k in keys:
             stage_ms[k].append(tm[k])
     stage_ms = {k: float(np.mean(v)) for k, v in stage_ms.items()}
     rs = 8 if a.precision == "fp64" else 4
-    d = 5
-    # algorithmic bytes of each kernel: its mandatory inputs + outputs (DESIGN.md "Kernels")
-    kbytes = {"spline_ms": P * rs * (2 * W + 3 + 2 * (d + 1) * (W - 1) + 2 + 3 * G),   # waypoints, angle, end slopes -> ctrl, L, J, px, py, kappa
-              "toppra_ms": P * (rs * (1 + 6 + 3 * G) + 8),                              # L, limits -> K_lo, K_hi, x, status
-              "param_ms": P * rs * (2 * G + 3 + 4 * G + 1)}                             # x, kappa, L -> t, v, a, omega, T
-    dom = max(kbytes, key=lambda k: stage_ms[k])
+    d, K_it, Q = 5, opt.iters, 32
+    # algorithmic bytes of each kernel = its mandatory inputs + outputs; algorithmic flops = SURVEY 8-D5's model,
+    # F_par's 160 G split 100 G (arc-length inversion, curve, curvature: arc kernel) + 60 G (parametrizer)
+    kern = {
+        "path_ms": ("path_warp_kernel", P * rs * (2 * W + 1 + 2 * (d + 1) * (W - 1) + 1), P * K_it * (W - 1) * Q * 120.0),
+        "arc_ms": ("arc_kernel", P * rs * (2 * (d + 1) * (W - 1) + 1 + 3 * G), P * ((W - 1) * 3200 * 24.0 + 100.0 * G)),
+        "toppra_ms": ("toppra_fast_kernel", P * (rs * (1 + 6 + 3 * G) + 8), P * 640.0 * G),
+        "param_ms": ("param_kernel", P * rs * (2 * G + 3 + 4 * G + 1), P * 60.0 * G),
+    }
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
     except Exception:
         pass
-    peak = float(peaks.get("hbm_gbs", 6650.0))
-    ach = kbytes[dom] / (stage_ms[dom] * 1e-3) / 1e9
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    # FP-pipe peaks: FMA microbenchmark on this pool's B200 (tools/fp_peak.cu -> profiles/r1_fp_peak.json)
+    fp_peak, fp_src = (37.07, "nominal-equivalent") if a.precision == "fp64" else (70.48, "nominal-equivalent")
+    try:
+        fpj = json.load(open(os.path.join(ROOT, "profiles", "r1_fp_peak.json")))
+        fp_peak = float(fpj["fp64_peak_tflops" if a.precision == "fp64" else "fp32_peak_tflops"]); fp_src = "measured (tools/fp_peak.cu)"
+    except Exception:
+        pass
+    traffic = {}
+    try:  # dram__bytes_read+write per launch from the committed ncu --set full capture of this command (C3, fp64)
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json"))).get("%s_%s" % (a.config, a.precision), {})
+    except Exception:
+        pass
+    kernels = []
+    for k, (name, nbytes, nflops) in kern.items():
+        ms_k = max(stage_ms[k], 1e-6)
+        gbs, tfs = nbytes / (ms_k * 1e-3) / 1e9, nflops / (ms_k * 1e-3) / 1e12
+        kernels.append({"kernel": name, "ms": stage_ms[k], "algorithmic_bytes": int(nbytes), "algorithmic_flops": nflops,
+                        "hbm_gbs": gbs, "hbm_frac": gbs / hbm_peak, "fp_tflops": tfs, "fp_frac": tfs / fp_peak,
+                        "bound": "fp_pipe" if tfs / fp_peak >= gbs / hbm_peak else "hbm", "traffic": traffic.get(name)})
+    dom = max(kernels, key=lambda r: r["ms"])
     path_bytes = pl.algorithmic_bytes(P, W, G)
-    roof = {"bound": "hbm", "kernel": {"spline_ms": "path_kernel", "toppra_ms": "toppra_kernel", "param_ms": "param_kernel"}[dom], "achieved": ach, "peak": peak, "unit": "GB/s",
-            "frac": ach / peak, "traffic": None, "peak_source": "measured" if peaks else "fallback",
-            "kernel_ms": stage_ms[dom], "algorithmic_bytes_per_launch": kbytes[dom],
-            "path": {"algorithmic_bytes_per_step": path_bytes, "achieved": path_bytes / (ms_per_step * 1e-3) / 1e9,
-                     "frac": path_bytes / (ms_per_step * 1e-3) / 1e9 / peak}}
+    path_flops = sum(r["algorithmic_flops"] for r in kernels)
+    step_s = ms_per_step * 1e-3
+    if dom["bound"] == "hbm":
+        roof = {"bound": "hbm", "kernel": dom["kernel"], "achieved": dom["hbm_gbs"], "peak": hbm_peak, "unit": "GB/s",
+                "frac": dom["hbm_frac"], "peak_source": "measured (MEASURED_PEAKS.json)" if peaks else "fallback"}
+    else:  # no stage is a dense contraction: the binding pipe is the FP64 (FP32) vector pipe, not the tensor cores
+        roof = {"bound": "fp_pipe", "kernel": dom["kernel"], "achieved": dom["fp_tflops"], "peak": fp_peak, "unit": "TFLOP/s",
+                "frac": dom["fp_frac"], "peak_source": fp_src}
+    roof.update({"traffic": dom["traffic"], "kernel_ms": dom["ms"], "algorithmic_bytes_per_launch": dom["algorithmic_bytes"],
+                 "algorithmic_flops_per_launch": dom["algorithmic_flops"],
+                 "hbm": {"achieved": dom["hbm_gbs"], "peak": hbm_peak, "unit": "GB/s", "frac": dom["hbm_frac"]},
+                 "kernels": kernels,
+                 "path": {"algorithmic_bytes_per_step": path_bytes, "hbm_gbs": path_bytes / step_s / 1e9,
+                          "hbm_frac": path_bytes / step_s / 1e9 / hbm_peak, "algorithmic_flops_per_step": path_flops,
+                          "fp_tflops": path_flops / step_s / 1e12, "fp_frac": path_flops / step_s / 1e12 / fp_peak}})
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": scaling, "vs_baseline": None,
             "dtype": "f64" if a.precision == "fp64" else "f32", "data": "synthetic",

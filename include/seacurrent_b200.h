@@ -169,6 +169,7 @@ typedef struct scb_batch_out {
 typedef struct scb_timing {
   float h2d_ms, spline_ms, toppra_ms, param_ms, sample_ms, d2h_ms, total_ms;
   int32_t launches;         /* kernels launched by that call */
+  float path_ms, arc_ms;    /* spline_ms split into its two kernels (waypoints -> control points; tables + geometry) */
 } scb_timing;
 
 int scb_version(void);

@@ -151,7 +151,7 @@ bool path_launch_shape(int W, int spline_mode, int real_size, int& PB, int& thre
 }
 
 // path stage = control points (this file or path_warp_kernel.cu) + arc stage (arc_kernel.cu): 2 launches
-template <class R> void launch_path(const PathArgs& a0, int spline_mode, cudaStream_t st) {
+template <class R> void launch_path(const PathArgs& a0, int spline_mode, cudaStream_t st, cudaEvent_t between) {
   PathArgs a = a0;
   int PB, threads; bool tab; size_t smem;
   if (!path_launch_shape(a.W, spline_mode, (int)sizeof(R), PB, threads, tab, smem)) return;
@@ -170,9 +170,10 @@ template <class R> void launch_path(const PathArgs& a0, int spline_mode, cudaStr
       path_kernel<R, 5><<<grid, threads, smem, st>>>(a);
     }
   }
+  if (between) cudaEventRecord(between, st);  // splits spline_ms into path_ms + arc_ms
   launch_arc<R>(a0, spline_mode, st);
 }
-template void launch_path<double>(const PathArgs&, int, cudaStream_t);
-template void launch_path<float>(const PathArgs&, int, cudaStream_t);
+template void launch_path<double>(const PathArgs&, int, cudaStream_t, cudaEvent_t);
+template void launch_path<float>(const PathArgs&, int, cudaStream_t, cudaEvent_t);
 
 }  // namespace scb

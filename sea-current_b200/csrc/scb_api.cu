@@ -40,7 +40,7 @@ struct scb_ctx {
   cudaEvent_t ev[8] = {};
   Slot slot[SL_COUNT];
   scb_timing timing = {};
-  bool timing_pending = false, host_call = false;
+  bool timing_pending = false, host_call = false, split_spline = false;
   char err[256] = {0};
 };
 
@@ -132,11 +132,13 @@ int run_device(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, i
       if (out->omega) { if ((rc = ensure(ctx, SL_KAPPA, (size_t)G * P * rs, &dKappa))) return rc; a.kappa = dKappa; }
     }
     a.opt = in->opt;
-    launch_path<R>(a, ctx->cfg.spline_mode, st);
+    launch_path<R>(a, ctx->cfg.spline_mode, st, ctx->ev[7]);
     launches += 2;  // path kernel + arc kernel
+    ctx->split_spline = true;
   } else {
     SCB_CUDA(cudaMemsetAsync(out->status, 0, (size_t)P * 4, st));
     dL = (void*)in->path_len;
+    ctx->split_spline = false;
   }
   SCB_CUDA(cudaEventRecord(ctx->ev[2], st));
   // internal state of the recurrences is FP64 in both precision modes: in FP64 mode the caller's
@@ -217,6 +219,7 @@ void collect_timing(scb_ctx* ctx) {
   scb_timing& t = ctx->timing;
   auto el = [&](int a, int b) { float ms = 0; cudaEventElapsedTime(&ms, ctx->ev[a], ctx->ev[b]); return ms; };
   t.spline_ms = el(1, 2); t.toppra_ms = el(2, 3); t.param_ms = el(3, 4); t.sample_ms = el(4, 5);
+  t.path_ms = ctx->split_spline ? el(1, 7) : 0; t.arc_ms = ctx->split_spline ? el(7, 2) : 0;
   if (ctx->host_call) { t.h2d_ms = el(0, 1); t.d2h_ms = el(5, 6); t.total_ms = el(0, 6); }
   else { t.h2d_ms = 0; t.d2h_ms = 0; t.total_ms = el(1, 5); }
   ctx->timing_pending = false;

@@ -111,7 +111,7 @@ struct SampleArgs {
   int nudge;                           // geometry-only: repair s_pos in place first (sc:902-912)
 };
 
-template <class R> void launch_path(const PathArgs& a, int spline_mode, cudaStream_t st);
+template <class R> void launch_path(const PathArgs& a, int spline_mode, cudaStream_t st, cudaEvent_t between = nullptr);
 template <class R> void launch_toppra(const ToppraArgs& a, cudaStream_t st);
 template <class R> void launch_toppra_fast(const ToppraArgs& a, cudaStream_t st);
 template <class R> void launch_param(const ParamArgs& a, cudaStream_t st);

@@ -61,7 +61,7 @@ class ScbSummary(C.Structure):
 class ScbTiming(C.Structure):
     _fields_ = [("h2d_ms", C.c_float), ("spline_ms", C.c_float), ("toppra_ms", C.c_float),
                 ("param_ms", C.c_float), ("sample_ms", C.c_float), ("d2h_ms", C.c_float),
-                ("total_ms", C.c_float), ("launches", C.c_int32)]
+                ("total_ms", C.c_float), ("launches", C.c_int32), ("path_ms", C.c_float), ("arc_ms", C.c_float)]
 
 
 # every symbol include/seacurrent_b200.h declares: (restype, argtypes)
