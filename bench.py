@@ -236,7 +236,7 @@ def main():
     # algorithmic bytes of each kernel = its mandatory inputs + outputs; algorithmic flops = SURVEY 8-D5's model,
     # F_par's 160 G split 100 G (arc-length inversion, curve, curvature: arc kernel) + 60 G (parametrizer)
     kern = {
-        "path_ms": ("path_warp_kernel", P * rs * (2 * W + 1 + 2 * (d + 1) * (W - 1) + 1), P * K_it * (W - 1) * Q * 120.0),
+        "path_ms": ("path_lane_kernel" if W <= 32 else "path_kernel", P * rs * (2 * W + 1 + 2 * (d + 1) * (W - 1) + 1), P * K_it * (W - 1) * Q * 120.0),
         "arc_ms": ("arc_kernel", P * rs * (2 * (d + 1) * (W - 1) + 1 + 3 * G), P * ((W - 1) * 3200 * 24.0 + 100.0 * G)),
         "toppra_ms": ("toppra_fast_kernel", P * (rs * (1 + 6 + 3 * G) + 8), P * 640.0 * G),
         "param_ms": ("param_kernel", P * rs * (2 * G + 3 + 4 * G + 1), P * 60.0 * G),

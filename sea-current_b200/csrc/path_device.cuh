@@ -1,5 +1,5 @@
-// Device helpers shared by the two path kernels (path_kernel.cu: CTA team, path_warp_kernel.cu:
-// warp team).  Reference lines are sea_current.hpp ("sc:").
+// Device helpers shared by the two path kernels (path_kernel.cu: CTA team, path_lane_kernel.cu:
+// lane per waypoint).  Reference lines are sea_current.hpp ("sc:").
 #pragma once
 #include "gl32_device.h"
 #include "scb_common.cuh"

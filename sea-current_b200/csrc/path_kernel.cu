@@ -7,7 +7,7 @@
 // Arc-length tables and the geometry at the toppra gridpoints follow in arc_kernel.cu.
 //
 // This is the variant for paths whose optimiser state does not fit a warp's slice of shared memory
-// (long paths, e.g. C5's 200 waypoints); shorter paths run path_warp_kernel.cu.  One CTA owns PB
+// (long paths, e.g. C5's 200 waypoints); paths of up to 32 waypoints run path_lane_kernel.cu.  One CTA owns PB
 // consecutive paths, all per-path state lives in shared memory, and the CTA's threads are re-mapped
 // phase by phase onto the items of that phase: (path, waypoint), (path, segment), (path, segment,
 // node group).  Per-path arrays are [P][n] in HBM (a CTA's slice is contiguous).
@@ -32,7 +32,8 @@ __host__ __device__ inline size_t path_smem_reals(int W, int deg, int PB, bool t
 }
 constexpr int kPathSmemIntBytes = 256;  // flags in front of the reals
 
-template <class R, int DEG>
+// R: arithmetic and shared-memory type (always double, see path_lane_kernel.cu "Arithmetic"); S: storage type in HBM
+template <class R, int DEG, class S>
 __global__ void __launch_bounds__(512, 1) path_kernel(PathArgs g) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   constexpr int NC = DEG + 1;
@@ -51,7 +52,7 @@ __global__ void __launch_bounds__(512, 1) path_kernel(PathArgs g) {
   if (tid < 32) { bad[tid] = 0; improve[tid] = 0; }
   __syncthreads();
   for (int it = tid; it < PBa * W; it += T) {
-    const R x = ((const R*)g.wx)[(size_t)p0 * W + it], y = ((const R*)g.wy)[(size_t)p0 * W + it];
+    const R x = (R)((const S*)g.wx)[(size_t)p0 * W + it], y = (R)((const S*)g.wy)[(size_t)p0 * W + it];
     wx[it] = x; wy[it] = y;
     if (!isfinite(x) || !isfinite(y)) bad[it / W] = 1;
   }
@@ -66,7 +67,7 @@ __global__ void __launch_bounds__(512, 1) path_kernel(PathArgs g) {
     const R* x = wx + pl * W; const R* y = wy + pl * W;
     R ox, oy;
     if (i == 0) {  // sc:371-373, 606-609
-      R ang = g.start_angle ? ((const R*)g.start_angle)[p0 + pl] : Num<R>::nan();
+      R ang = g.start_angle ? (R)((const S*)g.start_angle)[p0 + pl] : Num<R>::nan();
       if (isnan(ang)) ang = atan2(y[1] - y[0], x[1] - x[0]);
       const R mag = (R)0.5 * dist2<R>(x[0], y[0], x[1], y[1]);
       R sn, cs; sincos(ang, &sn, &cs);
@@ -103,12 +104,12 @@ __global__ void __launch_bounds__(512, 1) path_kernel(PathArgs g) {
     const int nc = nseg * NC;
     for (int it = tid; it < PBa * nc; it += T) {
       const bool b = bad[it / nc] != 0;
-      ((R*)g.ctrl_x)[(size_t)p0 * nc + it] = b ? (R)0 : cx[it];
-      ((R*)g.ctrl_y)[(size_t)p0 * nc + it] = b ? (R)0 : cy[it];
+      ((S*)g.ctrl_x)[(size_t)p0 * nc + it] = b ? (S)0 : (S)cx[it];
+      ((S*)g.ctrl_y)[(size_t)p0 * nc + it] = b ? (S)0 : (S)cy[it];
     }
     if (tid < PBa) {
       const int p = p0 + tid;
-      if (g.cost) ((R*)g.cost)[p] = bad[tid] ? (R)0 : scal[tid * 8 + 1];
+      if (g.cost) ((S*)g.cost)[p] = bad[tid] ? (S)0 : (S)scal[tid * 8 + 1];
       g.status[p] = bad[tid] ? SCB_ST_ERR_BAD_PATH : SCB_ST_OK;
     }
   }
@@ -118,23 +119,24 @@ size_t path_smem_bytes(int W, int spline_mode, int real_size, int PB) {
   return kPathSmemIntBytes + path_smem_reals(W, spline_mode == SCB_REF_CUBIC ? 3 : 5, PB, false) * real_size;
 }
 
-static bool use_warp_team() {  // SCB_PATH_TEAM=cta forces the CTA-team kernel (A/B measurements)
-  static const bool v = [] { const char* e = getenv("SCB_PATH_TEAM"); return !(e && e[0] == 'c'); }();
-  return v;
+static bool use_lane_kernel() {  // SCB_PATH_TEAM=cta forces the CTA-team kernel (A/B measurements, tests)
+  const char* e = getenv("SCB_PATH_TEAM");
+  return !(e && e[0] == 'c');
 }
 
-// Launch geometry of the path stage (warp-team kernel when a path fits a warp's slice, else the
-// CTA-team kernel: PB paths per CTA so that two CTAs fit one SM when possible).  False = the path is
-// too long for either kernel or for arc_kernel's shared-memory power bases.  The arc-length tables
-// always live in global memory (table_in_smem is kept for the ABI of this helper only).
+// Launch geometry of the path stage: the lane-per-waypoint kernel (threads = 128) for W <= 32, else the
+// CTA-team kernel: PB paths per CTA so that two CTAs fit one SM when possible.  False = the path is too
+// long for the CTA kernel or for arc_kernel's shared-memory power bases.  `real_size` is the STORAGE size
+// (arc kernel); the path kernels compute in FP64 in both modes.  The arc-length tables always live in
+// global memory (table_in_smem is kept for the ABI of this helper only).
 bool path_launch_shape(int W, int spline_mode, int real_size, int& PB, int& threads, bool& table_in_smem, size_t& smem) {
   table_in_smem = false;
   size_t arc_smem;
   if (!arc_paths_per_cta(W, spline_mode, real_size, arc_smem)) return false;
-  if (use_warp_team() && path_warp_shape(W, spline_mode, real_size, PB, smem)) { threads = 128; return true; }
+  if (use_lane_kernel() && path_lane_shape(W, PB, smem, spline_mode)) { threads = 128; return true; }
   const size_t budget2 = 111 * 1024, budget1 = 224 * 1024;
   const int deg = spline_mode == SCB_REF_CUBIC ? 3 : 5;
-  auto bytes = [&](int pb) { return path_smem_bytes(W, spline_mode, real_size, pb); };
+  auto bytes = [&](int pb) { return path_smem_bytes(W, spline_mode, 8, pb); };
   if (bytes(1) > budget1) return false;
   const int lanes_per_path = (W - 1) * (deg == 5 ? kNG : 8);  // items of the widest compute phase
   if (bytes(1) <= budget2) {
@@ -150,24 +152,25 @@ bool path_launch_shape(int W, int spline_mode, int real_size, int& PB, int& thre
   return true;
 }
 
-// path stage = control points (this file or path_warp_kernel.cu) + arc stage (arc_kernel.cu): 2 launches
+// path stage = control points (this file or path_lane_kernel.cu) + arc stage (arc_kernel.cu): 2 launches.
+// R is the storage type of the mode; the control-point kernels compute in FP64.
 template <class R> void launch_path(const PathArgs& a0, int spline_mode, cudaStream_t st, cudaEvent_t between) {
   PathArgs a = a0;
   int PB, threads; bool tab; size_t smem;
   if (!path_launch_shape(a.W, spline_mode, (int)sizeof(R), PB, threads, tab, smem)) return;
   if (threads == 128) {
-    launch_path_warp<R>(a0, spline_mode, PB, smem, st);
+    launch_path_lane<R>(a0, spline_mode, PB, smem, st);
   } else {
     a.PB = PB; a.table_in_smem = 0;
     const int grid = (a.P + PB - 1) / PB;
     if (spline_mode == SCB_REF_CUBIC) {
-      cudaFuncSetAttribute(path_kernel<R, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      cudaFuncSetAttribute(path_kernel<R, 3>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-      path_kernel<R, 3><<<grid, threads, smem, st>>>(a);
+      cudaFuncSetAttribute(path_kernel<double, 3, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      cudaFuncSetAttribute(path_kernel<double, 3, R>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+      path_kernel<double, 3, R><<<grid, threads, smem, st>>>(a);
     } else {
-      cudaFuncSetAttribute(path_kernel<R, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      cudaFuncSetAttribute(path_kernel<R, 5>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-      path_kernel<R, 5><<<grid, threads, smem, st>>>(a);
+      cudaFuncSetAttribute(path_kernel<double, 5, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      cudaFuncSetAttribute(path_kernel<double, 5, R>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+      path_kernel<double, 5, R><<<grid, threads, smem, st>>>(a);
     }
   }
   if (between) cudaEventRecord(between, st);  // splits spline_ms into path_ms + arc_ms

@@ -1,0 +1,303 @@
+// Path stage, lane-per-waypoint variant (sm_100a): the default for paths of up to 32 waypoints.
+//   tangent heuristics sc:343-377, segment builder sc:599-683 (cubic), Lau09 quintic builder + cost /
+//   analytic gradient + iRPROP- (DESIGN.md "New stages" is the frozen definition).
+//
+// Mapping.  A warp owns PB = floor(32 / W) consecutive paths.  Lane l owns waypoint i = l % W of path
+// l / W for the whole kernel AND segment i (waypoints i, i+1) when i < W-1.  Everything a waypoint needs
+// from its neighbours travels by __shfl_up/down(1): there is no shared-memory hand-over, no __syncwarp
+// and no lane re-mapping between the phases of an optimiser iteration (the predecessor,
+// path_warp_kernel.cu, spent half of its issue slots and stall samples in those phases:
+// profiles/r1f_path_warp_kernel_f64.lines.txt).  Shared memory only holds per-lane private optimiser
+// state (a register spill area the owner alone touches).
+//
+// Cost + gradient of a segment run on ONE lane, all 32 Gauss-Legendre nodes in sequence, so node
+// constants are warp-uniform constant-bank operands (LAU_NODE) and partial sums never leave
+// registers.  The hodograph is evaluated in the power basis,
+//     B'(u) = sum_m c_m u^m,  c_m = C(4,m) Delta^m D_0,  D_j = 5 (P_{j+1} - P_j),
+// by Horner (7 FMAs per axis for B', B'' instead of 12 in the Bernstein form), and the gradient is
+// accumulated against the powers of u (G_m = sum f1 u^m, H_m = sum f2 u^m: 9 per axis instead of 12)
+// and mapped back to (T, A, W) once per iteration.  D_j are formed from (W, T, A) directly,
+//     D0 = T_i, D1 = T_i + A_i/4, D2 = 5 (W_{i+1} - W_i) - 2 (T_i + T_{i+1}) + (A_{i+1} - A_i)/4,
+//     D3 = T_{i+1} - A_{i+1}/4, D4 = T_{i+1},
+// which is the frozen control-point construction with the O(|W|) terms cancelled analytically.
+// 63 FP64 instructions per node (was ~95).
+//
+// Arithmetic is FP64 for both storage types S: iRPROP- acts on gradient SIGNS, so its iterates are
+// only reproducible where the gradient is resolved far below the decision threshold (1e-9 of the
+// largest component) -- like toppra's feasibility tolerances this does not exist in FP32
+// (DESIGN.md "Precision modes").  S = float only changes what is loaded and stored.
+#include "lau_nodes_device.h"
+#include "path_device.cuh"
+
+namespace scb {
+
+namespace {
+
+constexpr unsigned kAll = 0xffffffffu;
+constexpr int kLaneWarps = 4;     // warps per CTA
+constexpr int kLaneSlots = 15;    // private FP64 slots per lane in shared memory:
+enum { kSe, kPe, kSwx, kSwy, kPwx, kPwy, kW0x, kW0y, kMag, kBe, kBwx, kBwy, kAlpha, kAnPrev, kApNext };
+
+__device__ __forceinline__ double up1(double v) { return __shfl_up_sync(kAll, v, 1); }
+__device__ __forceinline__ double dn1(double v) { return __shfl_down_sync(kAll, v, 1); }
+__device__ __forceinline__ double from(double v, int src) { return __shfl_sync(kAll, v, src & 31); }
+
+// Cost of one quintic segment and, if GRAD, its gradient with respect to the power-basis coefficients of
+// the hodograph (gc?[m] = dJ/dc_m).  cx, cy: c_0..c_4.  32 nodes in the reference's table order.
+template <bool GRAD>
+__device__ __forceinline__ double segment_cost(const double (&cx)[5], const double (&cy)[5], double lambda,
+                                               double (&gcx)[5], double (&gcy)[5]) {
+  const double dx2 = 2.0 * cx[2], dx3 = 3.0 * cx[3], dx4 = 4.0 * cx[4];
+  const double dy2 = 2.0 * cy[2], dy3 = 3.0 * cy[3], dy4 = 4.0 * cy[4];
+  double J = 0;
+  double Gx[5] = {0, 0, 0, 0, 0}, Gy[5] = {0, 0, 0, 0, 0}, Hx[4] = {0, 0, 0, 0}, Hy[4] = {0, 0, 0, 0};
+#pragma unroll 4
+  for (int q = 0; q < 32; ++q) {
+    const double u = LAU_NODE[q][0], u2 = LAU_NODE[q][1], u3 = LAU_NODE[q][2], u4 = LAU_NODE[q][3];
+    const double wq = LAU_NODE[q][4], w2 = LAU_NODE[q][5];
+    const double x1 = fma(fma(fma(fma(cx[4], u, cx[3]), u, cx[2]), u, cx[1]), u, cx[0]);
+    const double y1 = fma(fma(fma(fma(cy[4], u, cy[3]), u, cy[2]), u, cy[1]), u, cy[0]);
+    const double x2 = fma(fma(fma(dx4, u, dx3), u, dx2), u, cx[1]);
+    const double y2 = fma(fma(fma(dy4, u, dy3), u, dy2), u, cy[1]);
+    // n = |B'|; every power of 1/n comes from one rsqrt
+    const double n2 = fma(x1, x1, y1 * y1), rn = fast_rsqrt<double>(n2), n = n2 * rn, rn2 = rn * rn;
+    const double c = fma(x1, y2, -(y1 * x2));
+    const double in5 = (rn2 * rn2) * rn;
+    const double t = c * in5, cc5 = t * c;                  // c / n^5, c^2 / n^5
+    J = fma(wq, fma(lambda, n, cc5), J);
+    if (GRAD) {
+      // d/dB' = k1 (y2, -x2) + (k3 - k2) B',  d/dB'' = k1 (-y1, x1);  k1 = 2c/n^5, k2 = 5c^2/n^7, k3 = lambda/n
+      const double wk1 = w2 * t;
+      const double wk32 = wq * fma(-5.0, cc5 * rn2, lambda * rn);
+      const double fx1 = fma(wk1, y2, wk32 * x1), fy1 = fma(-wk1, x2, wk32 * y1);
+      const double fx2 = -(wk1 * y1), fy2 = wk1 * x1;
+      Gx[0] += fx1; Gx[1] = fma(fx1, u, Gx[1]); Gx[2] = fma(fx1, u2, Gx[2]); Gx[3] = fma(fx1, u3, Gx[3]); Gx[4] = fma(fx1, u4, Gx[4]);
+      Gy[0] += fy1; Gy[1] = fma(fy1, u, Gy[1]); Gy[2] = fma(fy1, u2, Gy[2]); Gy[3] = fma(fy1, u3, Gy[3]); Gy[4] = fma(fy1, u4, Gy[4]);
+      Hx[0] += fx2; Hx[1] = fma(fx2, u, Hx[1]); Hx[2] = fma(fx2, u2, Hx[2]); Hx[3] = fma(fx2, u3, Hx[3]);
+      Hy[0] += fy2; Hy[1] = fma(fy2, u, Hy[1]); Hy[2] = fma(fy2, u2, Hy[2]); Hy[3] = fma(fy2, u3, Hy[3]);
+    }
+  }
+  if (GRAD) {  // B'' = sum_m m c_m u^(m-1)
+    gcx[0] = Gx[0]; gcy[0] = Gy[0];
+#pragma unroll
+    for (int m = 1; m < 5; ++m) { gcx[m] = fma((double)m, Hx[m - 1], Gx[m]); gcy[m] = fma((double)m, Hy[m - 1], Gy[m]); }
+  }
+  return J;
+}
+
+// c_m = C(4,m) Delta^m D_0
+__device__ __forceinline__ void hodograph_power(double d0, double d1, double d2, double d3, double d4, double (&c)[5]) {
+  const double a0 = d1 - d0, a1 = d2 - d1, a2 = d3 - d2, a3 = d4 - d3;
+  const double b0 = a1 - a0, b1 = a2 - a1, b2 = a3 - a2;
+  const double e0 = b1 - b0, e1 = b2 - b1;
+  c[0] = d0; c[1] = 4.0 * a0; c[2] = 6.0 * b0; c[3] = 4.0 * e0; c[4] = e1 - e0;
+}
+// transpose of hodograph_power: gradient with respect to D_0..D_4
+__device__ __forceinline__ void hodograph_power_T(const double (&g)[5], double (&gd)[5]) {
+  gd[0] = g[0] - 4.0 * g[1] + 6.0 * g[2] - 4.0 * g[3] + g[4];
+  gd[1] = 4.0 * g[1] - 12.0 * g[2] + 12.0 * g[3] - 4.0 * g[4];
+  gd[2] = 6.0 * g[2] - 12.0 * g[3] + 6.0 * g[4];
+  gd[3] = 4.0 * g[3] - 4.0 * g[4];
+  gd[4] = g[4];
+}
+
+}  // namespace
+
+template <class S, int DEG>
+__global__ void __launch_bounds__(kLaneWarps * 32, 4) path_lane_kernel(PathArgs g) {
+  extern __shared__ __align__(16) unsigned char lane_smem_raw[];
+  constexpr int NC = DEG + 1;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int W = g.W, nseg = W - 1, PB = g.PB, P = g.P;
+  const int team = blockIdx.x * kLaneWarps + warp;
+  const int p0 = team * PB;
+  if (p0 >= P) return;  // the whole warp leaves together
+  const int pl = lane / W, i = lane - pl * W;
+  const int p = p0 + pl, base = pl * W;
+  const bool own = pl < PB && p < P;
+  const bool first = i == 0, last = i == nseg;
+  const bool seg = own && !last;          // this lane also owns segment i
+  const bool inner = own && !first && !last;
+
+  // ---- waypoints in (a warp's slice of [P][W] is contiguous), neighbours, validation
+  double wx = own ? (double)((const S*)g.wx)[(size_t)p * W + i] : (double)lane;
+  double wy = own ? (double)((const S*)g.wy)[(size_t)p * W + i] : 0.0;
+  const double xm = up1(wx), ym = up1(wy), xp = dn1(wx), yp = dn1(wy);
+  const double dprev = dist2<double>(xm, ym, wx, wy), dnext = dist2<double>(wx, wy, xp, yp);
+  const bool lane_bad = own && (!isfinite(wx) || !isfinite(wy) || (seg && !(dnext > 0)));
+  const unsigned bad_mask = __ballot_sync(kAll, lane_bad);
+  const unsigned path_mask = (W >= 32 ? kAll : ((1u << W) - 1u)) << (base & 31);
+  const bool bad = (bad_mask & path_mask) != 0;
+
+  // ---- tangents (sc:343-377, 606-638)
+  double btx, bty;
+  if (first) {
+    double ang = g.start_angle && own ? (double)((const S*)g.start_angle)[p] : CUDART_NAN;
+    if (isnan(ang)) ang = atan2(yp - wy, xp - wx);
+    double sn, cs; sincos(ang, &sn, &cs);
+    btx = (0.5 * dnext) * cs; bty = (0.5 * dnext) * sn;
+  } else if (last) {
+    const double dx = wx - xm, dy = wy - ym, n = sqrt(dx * dx + dy * dy);
+    btx = (0.5 * dprev) * (dx / n); bty = (0.5 * dprev) * (dy / n);
+  } else {
+    calc_tangent<double>(xm, ym, wx, wy, xp, yp, btx, bty);
+  }
+
+  double cost = 0;
+  double e = 1.0;
+  if constexpr (DEG == 5) {
+    // ================= Lau09 quintic builder (A5), cost + gradient (A6), iRPROP- (A7) =================
+    double* st = (double*)lane_smem_raw + (size_t)warp * kLaneSlots * 32 + lane;  // st[k * 32]: private slot k
+    const scb_opt& o = g.opt;
+    const double lambda = o.lambda;
+    {
+      const double mag = sqrt(btx * btx + bty * bty);
+      const double alpha = inner ? dnext / (dprev + dnext) : 0.0;
+      // weights of the "previous" / "next" cubic in A_i (one-sided at the ends)
+      const double ap = first ? 0.0 : (last ? 1.0 : alpha), an = last ? 0.0 : (first ? 1.0 : 1.0 - alpha);
+      st[kSe * 32] = o.step_e; st[kPe * 32] = 0;
+      st[kSwx * 32] = o.step_w * mag; st[kSwy * 32] = o.step_w * mag; st[kPwx * 32] = 0; st[kPwy * 32] = 0;
+      st[kW0x * 32] = wx; st[kW0y * 32] = wy; st[kMag * 32] = mag;
+      st[kBe * 32] = o.e_init; st[kBwx * 32] = wx; st[kBwy * 32] = wy;
+      st[kAlpha * 32] = alpha; st[kAnPrev * 32] = up1(an); st[kApNext * 32] = dn1(ap);
+      e = o.e_init;
+    }
+    const int K = o.iters;
+    for (int iter = 0; iter <= K; ++iter) {
+      // ---- A5: T, A per waypoint; hodograph control points D of the lane's segment
+      const double alpha = st[kAlpha * 32];
+      const double Tx = e * btx, Ty = e * bty;
+      const double Txm = up1(Tx), Tym = up1(Ty), Txp = dn1(Tx), Typ = dn1(Ty);
+      const double wxm = up1(wx), wym = up1(wy), wxp = dn1(wx), wyp = dn1(wy);
+      const double pvx = 6.0 * (wxm - wx) + 4.0 * Tx + 2.0 * Txm, pvy = 6.0 * (wym - wy) + 4.0 * Ty + 2.0 * Tym;
+      const double nxx = 6.0 * (wxp - wx) - 4.0 * Tx - 2.0 * Txp, nxy = 6.0 * (wyp - wy) - 4.0 * Ty - 2.0 * Typ;
+      const double Ax = first ? nxx : (last ? pvx : alpha * pvx + (1.0 - alpha) * nxx);
+      const double Ay = first ? nxy : (last ? pvy : alpha * pvy + (1.0 - alpha) * nxy);
+      const double Axp = dn1(Ax), Ayp = dn1(Ay);
+      double cx[5], cy[5];
+      hodograph_power(Tx, fma(0.25, Ax, Tx), fma(0.25, Axp - Ax, fma(5.0, wxp - wx, -2.0 * (Tx + Txp))), fma(-0.25, Axp, Txp), Txp, cx);
+      hodograph_power(Ty, fma(0.25, Ay, Ty), fma(0.25, Ayp - Ay, fma(5.0, wyp - wy, -2.0 * (Ty + Typ))), fma(-0.25, Ayp, Typ), Typ, cy);
+      // ---- A6
+      double gcx[5], gcy[5], Js;
+      if (iter < K) Js = segment_cost<true>(cx, cy, lambda, gcx, gcy);
+      else Js = segment_cost<false>(cx, cy, lambda, gcx, gcy);
+      if (!seg) Js = 0;
+      // J of the path: segments in order (DESIGN.md "New stages", A6)
+      double J = 0;
+      for (int s = 0; s < nseg; ++s) J += from(Js, base + s);
+      const bool better = iter == 0 || J < cost;
+      if (better) { cost = J; st[kBe * 32] = e; st[kBwx * 32] = wx; st[kBwy * 32] = wy; }
+      if (iter == K) break;
+      // ---- chain rule: D -> (T, A, W) of the segment's two waypoints, then A -> (T, W) of the neighbours
+      double gdx[5], gdy[5];
+      hodograph_power_T(gcx, gdx); hodograph_power_T(gcy, gdy);
+      if (!seg) {
+#pragma unroll
+        for (int m = 0; m < 5; ++m) { gdx[m] = 0; gdy[m] = 0; }
+      }
+      // end side of the segment (waypoint i+1) is picked up by the next lane
+      const double eTx = up1(gdx[3] + gdx[4] - 2.0 * gdx[2]), eTy = up1(gdy[3] + gdy[4] - 2.0 * gdy[2]);
+      const double eAx = up1(0.25 * (gdx[2] - gdx[3])), eAy = up1(0.25 * (gdy[2] - gdy[3]));
+      const double eWx = up1(5.0 * gdx[2]), eWy = up1(5.0 * gdy[2]);
+      double gTx = gdx[0] + gdx[1] - 2.0 * gdx[2], gTy = gdy[0] + gdy[1] - 2.0 * gdy[2];
+      double gAx = 0.25 * (gdx[1] - gdx[2]), gAy = 0.25 * (gdy[1] - gdy[2]);
+      double gWx = -5.0 * gdx[2], gWy = -5.0 * gdy[2];
+      if (!first) { gTx += eTx; gTy += eTy; gAx += eAx; gAy += eAy; gWx += eWx; gWy += eWy; }
+      {
+        const double ap = first ? 0.0 : (last ? 1.0 : alpha), an = last ? 0.0 : (first ? 1.0 : 1.0 - alpha);
+        const double gAxm = up1(gAx), gAym = up1(gAy), gAxp = dn1(gAx), gAyp = dn1(gAy);
+        const double k6 = 6.0 * (ap + an), k4 = 4.0 * (ap - an);
+        gWx = fma(-k6, gAx, gWx); gWy = fma(-k6, gAy, gWy); gTx = fma(k4, gAx, gTx); gTy = fma(k4, gAy, gTy);
+        if (!first) {  // waypoint i is the "next" of i-1
+          const double a = st[kAnPrev * 32];
+          gWx = fma(6.0 * a, gAxm, gWx); gWy = fma(6.0 * a, gAym, gWy); gTx = fma(-2.0 * a, gAxm, gTx); gTy = fma(-2.0 * a, gAym, gTy);
+        }
+        if (!last) {   // waypoint i is the "previous" of i+1
+          const double a = st[kApNext * 32];
+          gWx = fma(6.0 * a, gAxp, gWx); gWy = fma(6.0 * a, gAyp, gWy); gTx = fma(2.0 * a, gAxp, gTx); gTy = fma(2.0 * a, gAyp, gTy);
+        }
+      }
+      const double ge = gTx * btx + gTy * bty;
+      // largest gradient component of each class over the path (components below 1e-9 of it count as zero)
+      double gemax = 0, gwmax = 0;
+      {
+        const double mine = own ? fabs(ge) : 0.0, minw = inner ? fmax(fabs(gWx), fabs(gWy)) : 0.0;
+        for (int k = 0; k < W; ++k) { gemax = fmax(gemax, from(mine, base + k)); gwmax = fmax(gwmax, from(minw, base + k)); }
+      }
+      // ---- A7: iRPROP-
+      {
+        const double te = 1e-9 * gemax, tw = 1e-9 * gwmax;
+        double se = st[kSe * 32], pe = st[kPe * 32];
+        const double gi = fabs(ge) <= te ? 0.0 : ge;
+        const double ei = e + rprop_step<double>(gi, pe, se, 1e-6, 1.0);
+        e = fmin((double)o.e_max, fmax((double)o.e_min, ei));
+        st[kSe * 32] = se; st[kPe * 32] = pe;
+        if (o.move_waypoints && inner) {
+          const double mag = st[kMag * 32], w0x = st[kW0x * 32], w0y = st[kW0y * 32];
+          double swx = st[kSwx * 32], swy = st[kSwy * 32], pwx = st[kPwx * 32], pwy = st[kPwy * 32];
+          const double gvx = fabs(gWx) <= tw ? 0.0 : gWx, gvy = fabs(gWy) <= tw ? 0.0 : gWy;
+          const double smin = 1e-6 * mag, smax = 0.5 * mag, rr = o.w_radius;
+          const double nx = wx + rprop_step<double>(gvx, pwx, swx, smin, smax);
+          const double ny = wy + rprop_step<double>(gvy, pwy, swy, smin, smax);
+          wx = fmin(w0x + rr, fmax(w0x - rr, nx));
+          wy = fmin(w0y + rr, fmax(w0y - rr, ny));
+          st[kSwx * 32] = swx; st[kSwy * 32] = swy; st[kPwx * 32] = pwx; st[kPwy * 32] = pwy;
+        }
+      }
+    }
+    e = st[kBe * 32]; wx = st[kBwx * 32]; wy = st[kBwy * 32];
+  }
+
+  // ---- control points of the lane's segment (the frozen construction), cost and the path verdict -> global
+  {
+    const double Tx = e * btx, Ty = e * bty;
+    const double Txp = dn1(Tx), Typ = dn1(Ty), wxp = dn1(wx), wyp = dn1(wy);
+    double ox[NC], oy[NC];
+    if constexpr (DEG == 3) {  // sc:661-681
+      ox[0] = wx; oy[0] = wy; ox[1] = wx + Tx; oy[1] = wy + Ty;
+      ox[2] = wxp - Txp; oy[2] = wyp - Typ; ox[3] = wxp; oy[3] = wyp;
+    } else {
+      const double alpha = ((double*)lane_smem_raw + (size_t)warp * kLaneSlots * 32 + lane)[kAlpha * 32];
+      const double Txm = up1(Tx), Tym = up1(Ty), wxm = up1(wx), wym = up1(wy);
+      const double pvx = 6.0 * (wxm - wx) + 4.0 * Tx + 2.0 * Txm, pvy = 6.0 * (wym - wy) + 4.0 * Ty + 2.0 * Tym;
+      const double nxx = 6.0 * (wxp - wx) - 4.0 * Tx - 2.0 * Txp, nxy = 6.0 * (wyp - wy) - 4.0 * Ty - 2.0 * Typ;
+      const double Ax = first ? nxx : (last ? pvx : alpha * pvx + (1.0 - alpha) * nxx);
+      const double Ay = first ? nxy : (last ? pvy : alpha * pvy + (1.0 - alpha) * nxy);
+      const double Axp = dn1(Ax), Ayp = dn1(Ay);
+      const double fifth = 1.0 / 5.0, twentieth = 1.0 / 20.0;
+      const double p1x = wx + fifth * Tx, p1y = wy + fifth * Ty, p4x = wxp - fifth * Txp, p4y = wyp - fifth * Typ;
+      ox[0] = wx; oy[0] = wy; ox[1] = p1x; oy[1] = p1y;
+      ox[2] = twentieth * Ax + 2.0 * p1x - wx; oy[2] = twentieth * Ay + 2.0 * p1y - wy;
+      ox[3] = twentieth * Axp + 2.0 * p4x - wxp; oy[3] = twentieth * Ayp + 2.0 * p4y - wyp;
+      ox[4] = p4x; oy[4] = p4y; ox[5] = wxp; oy[5] = wyp;
+    }
+    if (seg) {
+      S* dx = (S*)g.ctrl_x + ((size_t)p * nseg + i) * NC; S* dy = (S*)g.ctrl_y + ((size_t)p * nseg + i) * NC;
+#pragma unroll
+      for (int j = 0; j < NC; ++j) { dx[j] = bad ? (S)0 : (S)ox[j]; dy[j] = bad ? (S)0 : (S)oy[j]; }
+    }
+    if (own && first) {
+      if (g.cost) ((S*)g.cost)[p] = bad ? (S)0 : (S)cost;
+      g.status[p] = bad ? SCB_ST_ERR_BAD_PATH : SCB_ST_OK;
+    }
+  }
+}
+
+bool path_lane_shape(int W, int& PB, size_t& smem, int spline_mode) {
+  if (W < 2 || W > 32) return false;
+  PB = 32 / W;
+  smem = spline_mode == SCB_REF_CUBIC ? 0 : (size_t)kLaneWarps * kLaneSlots * 32 * sizeof(double);
+  return true;
+}
+
+template <class S> void launch_path_lane(const PathArgs& a0, int spline_mode, int PB, size_t smem, cudaStream_t st) {
+  PathArgs a = a0;
+  a.PB = PB; a.table_in_smem = 0;
+  const int per_cta = PB * kLaneWarps, grid = (a.P + per_cta - 1) / per_cta;
+  if (spline_mode == SCB_REF_CUBIC) path_lane_kernel<S, 3><<<grid, kLaneWarps * 32, smem, st>>>(a);
+  else path_lane_kernel<S, 5><<<grid, kLaneWarps * 32, smem, st>>>(a);
+}
+template void launch_path_lane<double>(const PathArgs&, int, int, size_t, cudaStream_t);
+template void launch_path_lane<float>(const PathArgs&, int, int, size_t, cudaStream_t);
+
+}  // namespace scb

@@ -3,7 +3,7 @@
 // Host side of the drop-in boundary: owns the CUDA stream, the device scratch that the fused
 // kernels need between stages (arc-length tables, controllable sets, Thomas scratch) and, for
 // the host-buffer entry point, the device mirrors of the caller's arrays.  No planning
-// arithmetic happens on the host: every stage is a kernel launch (path_warp_kernel.cu / path_kernel.cu,
+// arithmetic happens on the host: every stage is a kernel launch (path_lane_kernel.cu / path_kernel.cu,
 // arc_kernel.cu, toppra_fast_kernel.cu / toppra_kernel.cu, param_kernel.cu).  There is no CPU fallback — without an sm_100 device
 // scb_create fails with SCB_E_NO_DEVICE.
 //

@@ -116,9 +116,9 @@ template <class R> void launch_toppra(const ToppraArgs& a, cudaStream_t st);
 template <class R> void launch_toppra_fast(const ToppraArgs& a, cudaStream_t st);
 template <class R> void launch_param(const ParamArgs& a, cudaStream_t st);
 template <class R> void launch_sample(const SampleArgs& a, cudaStream_t st);
-// warp-team variant of the path kernel (path_warp_kernel.cu); false = the path does not fit a warp's slice
-bool path_warp_shape(int W, int spline_mode, int real_size, int& PB, size_t& smem);
-template <class R> void launch_path_warp(const PathArgs& a, int spline_mode, int PB, size_t smem, cudaStream_t st);
+// lane-per-waypoint variant of the path kernel (path_lane_kernel.cu); false = more than 32 waypoints
+bool path_lane_shape(int W, int& PB, size_t& smem, int spline_mode);
+template <class S> void launch_path_lane(const PathArgs& a, int spline_mode, int PB, size_t smem, cudaStream_t st);
 // arc stage (arc_kernel.cu): tables, length, geometry at the gridpoints; paths per CTA (0 = path too long)
 int arc_paths_per_cta(int W, int spline_mode, int real_size, size_t& smem);
 template <class R> void launch_arc(const PathArgs& a, int spline_mode, cudaStream_t st);

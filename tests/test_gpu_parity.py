@@ -246,13 +246,13 @@ def fp32_omega_tol(oracle, ref, wx, wy, G, lim, mode, n_probe=3):
     differently).  Both are measured rather than modelled: the FP64 oracle is re-run on waypoints perturbed by
     2 eps32 relative (a backward-error statement: FP32 mode must agree with the exact result of inputs perturbed
     at float rounding level), and the spread of its omega enters the tolerance with a factor 4; the arc position of
-    a gridpoint additionally moves by ~16 eps32 of a segment (cumulative float table sums), which is the slope
-    term."""
+    a gridpoint additionally moves by up to ~64 eps32 of a segment (a cumulative float table of 100 entries: 50 eps32
+    worst case, plus the float Newton inversion), which is the slope term."""
     W = wx.shape[1]
     w = ref["omega"]
     sg = np.linspace(0.0, 1.0, G)[:, None]
     du_di = (W - 1) * 6.0 * sg * (1.0 - sg) / (G - 1)
-    di = np.minimum(16 * np.finfo(np.float32).eps / np.maximum(du_di, 1e-300), 1.0)
+    di = np.minimum(64 * np.finfo(np.float32).eps / np.maximum(du_di, 1e-300), 1.0)
     cond = np.abs(np.gradient(w, axis=0)) * di
     spread = np.zeros_like(w)
     rng = np.random.default_rng(4242)
@@ -269,6 +269,8 @@ def test_fp32_mode_within_1e4(planners, oracle):
     rng = np.random.default_rng(21)
     P, W, G = 256, 10, 500
     wx, wy = scb.workloads.random_walk_paths(rng, P, W)
+    # identical inputs on both sides: the waypoints the FP32 mode can represent
+    wx = wx.astype(np.float32).astype(np.float64); wy = wy.astype(np.float32).astype(np.float64)
     lim = scb.workloads.random_limits(rng, P, slow_fraction=0.0)
     for mode in ("ref_cubic", "lau_quintic"):
         pl = planners("fp32", mode)

@@ -10,6 +10,7 @@ import test_gpu_parity as T
 rng = np.random.default_rng(21)
 P, W, G = 256, 10, 500
 wx, wy = scb.workloads.random_walk_paths(rng, P, W)
+wx = wx.astype(np.float32).astype(np.float64); wy = wy.astype(np.float32).astype(np.float64)
 lim = scb.workloads.random_limits(rng, P, slow_fraction=0.0)
 for mode in ("ref_cubic", "lau_quintic"):
     pl = scb.BatchPlanner(0, "fp32", mode, max_problems=4096, max_waypoints=64, max_gridpoints=1001, max_samples=0)
