@@ -9,7 +9,7 @@
 // Two steps deviate from the reference ON PURPOSE (DESIGN.md "Deviations"):
 //   * arc length -> curve parameter: the reference fits a degree-9 Chebyshev polynomial per
 //     segment in float (resample/chebfit, sc:898-1005, 1109-1170; ~1e-4 L error).  The
-//     product inverts the table exactly: table search + 3 Newton steps on a 4-point
+//     product inverts the table exactly: table search + Newton steps to convergence on a 4-point
 //     Gauss–Legendre integral of |B'| (arclen_invert below).  The reference variant is kept
 //     in ora_arclen.hpp (resample) and compared against the fixture separately.
 //   * the clamped cubic spline of the parametrizer is solved by the Thomas algorithm instead
@@ -23,7 +23,7 @@
 namespace ora {
 
 enum { ST_BAD_PATH = 16, ST_BAD_LIMITS = 17, ST_TIME_KNOTS = 18 };
-static const int INV_NEWTON_ITERS = 3;
+static const int INV_NEWTON_ITERS = 40;       // cap; the iteration stops when it has converged (|step| <= 1e-12 h)
 static const double GL4_X[4] = {-0.8611363115940525752, -0.3399810435848562648, 0.3399810435848562648, 0.8611363115940525752};
 static const double GL4_W[4] = {0.3478548451374538574, 0.6521451548625461426, 0.6521451548625461426, 0.3478548451374538574};
 
@@ -90,8 +90,9 @@ inline void arclen_invert(const std::vector<SegPoly>& polys, const std::vector<d
     double F = 0;
     for (int g = 0; g < 4; ++g) F += GL4_W[g] * sp.speed(mid + half * GL4_X[g]);
     F *= half;
-    du = du - (F - target) / sp.speed(a + du);
-    du = std::min(std::max(du, 0.0), h);
+    const double delta = (F - target) / sp.speed(a + du);
+    du = std::min(std::max(du - delta, 0.0), h);
+    if (std::fabs(delta) <= 1e-12 * h) break;  // converged: the next correction is ~delta^2
   }
   u = std::min(a + du, 1.0);
 }

@@ -12,17 +12,18 @@
 //
 // One CTA owns PB consecutive paths; its threads are re-mapped per phase:
 //   (path, segment)                 power basis of the segment and of its hodograph -> shared memory
-//   warp per (path, segment)        lanes 0..24 integrate 4 consecutive sub-intervals each; a warp scan
-//                                   of the lane totals gives the cumulative table, stored 32 B per lane
+//   (path, segment, piece)          one 0.01-wide piece per thread and turn -> raw piece lengths in the table
+//   warp per (path, segment)        lanes 0..24 re-read 4 consecutive pieces each; a warp scan of the lane
+//                                   totals gives the cumulative table, stored 32 B per lane
 //   (gridpoint, path), path fastest geometry; stores to the [G][P] arrays are PB-contiguous
 //
 // Arc-length pieces: the reference integrates |B'| over every 0.01-wide sub-interval with a 32-point
-// Gauss-Legendre rule.  The integrand is analytic there and the 6-point rule agrees with the 32-point
-// one to ~1e-15 unless the speed has a (near-)zero within a few interval widths.  A lane evaluates the
-// 4- and 6-point rules (10 nodes) and keeps the 6-point value when the two agree to 1e-11 relative
-// (FP32: 2e-6); otherwise it runs the reference's 32 nodes in the reference's order.  On C2/C3 0.1 % of
-// the pieces take the long way; accepted pieces are within 1e-11 of the 32-point value
-// (DESIGN.md "Arc length").
+// Gauss-Legendre rule.  The integrand is analytic there; a thread evaluates the 7-point Kronrod extension
+// of the 3-point Gauss rule (7 nodes, exact to degree 11 like the 6-point Gauss rule) and keeps it when
+// the embedded Gauss value agrees to 1e-9 relative (FP32: 1e-5) -- K7's own error is then ~the square of
+// that -- and otherwise runs the reference's 32 nodes in the reference's order.  Measured on the C2/C3
+// control points (numpy): 0.27 % / 0.01 % of the pieces take the long way, accepted pieces are within
+// 2.4e-14 relative of the 32-point value (DESIGN.md "Arc length").
 #include "path_device.cuh"
 
 namespace scb {
@@ -63,9 +64,11 @@ __global__ void __launch_bounds__(kArcThreads, 3) arc_kernel(PathArgs g) {
   }
   __syncthreads();
 
-  // ---- A4: cumulative arc-length table, one warp per (path, segment)
+  // ---- A4, step 1: every 0.01-wide piece of every segment, one piece per thread and turn (all lanes busy;
+  // the warp-per-segment form kept 25 of 32).  Raw piece lengths go to the table's own slots [k + 1].
   R* tab = (R*)g.table + (size_t)p0 * nt;
-  for (int sg = warp; sg < nS; sg += nwarps) {
+  for (int it = tid; it < nS * kSub; it += T) {
+    const int sg = it / kSub, k = it - sg * kSub;
     R kx[DEG], ky[DEG];
 #pragma unroll
     for (int j = 0; j < DEG; ++j) { kx[j] = hx[DEG * sg + j]; ky[j] = hy[DEG * sg + j]; }
@@ -76,37 +79,38 @@ __global__ void __launch_bounds__(kArcThreads, 3) arc_kernel(PathArgs g) {
       const R n2 = dx * dx + dy * dy;
       return n2 > 0 ? n2 * fast_rsqrt<R>(n2) : (R)0;
     };
-    R piece[kPiecesPerLane];
-    const bool live = lane < kScanLanes;
-    bool redo_any = false;
-#pragma unroll
-    for (int j = 0; j < kPiecesPerLane; ++j) {
-      const int k = min(lane, kScanLanes - 1) * kPiecesPerLane + j;
-      const R a = fmin((R)k * (R)0.01, (R)1), b = fmin((R)(k + 1) * (R)0.01, (R)1);  // sc:851
-      const R half = (b - a) / 2, mid = (b + a) / 2;
-      R s4 = 0, s6 = 0;
-#pragma unroll
-      for (int i = 0; i < 2; ++i) s4 += (R)kG4W[i] * (speed(mid - half * (R)kG4X[i]) + speed(mid + half * (R)kG4X[i]));
-#pragma unroll
-      for (int i = 0; i < 3; ++i) s6 += (R)kG6W[i] * (speed(mid - half * (R)kG6X[i]) + speed(mid + half * (R)kG6X[i]));
-      piece[j] = s6 * half;
-      const R tol = sizeof(R) == 8 ? (R)1e-11 : (R)2e-6;
-      const bool redo = live && !(fabs(s4 - s6) <= tol * s6);
-      if (redo) {  // the reference's 32 nodes in table order (sc:854-880); rare, so the divergence is cheap
-        R acc = 0;
+    const R a = fmin((R)k * (R)0.01, (R)1), b = fmin((R)(k + 1) * (R)0.01, (R)1);  // sc:851
+    const R half = (b - a) / 2, mid = (b + a) / 2;
+    // Gauss 3 inside Kronrod 7 (7 nodes, K7 exact to degree 11 like the 6-point Gauss rule)
+    const R f0 = speed(mid);
+    const R f1 = speed(mid - half * (R)kK7X[0]) + speed(mid + half * (R)kK7X[0]);
+    const R f2 = speed(mid - half * (R)kK7X[1]) + speed(mid + half * (R)kK7X[1]);
+    const R f3 = speed(mid - half * (R)kK7X[2]) + speed(mid + half * (R)kK7X[2]);
+    const R s3 = (R)(8.0 / 9.0) * f0 + (R)(5.0 / 9.0) * f2;
+    const R s7 = (R)kK7W[0] * f0 + (R)kK7W[1] * f1 + (R)kK7W[2] * f2 + (R)kK7W[3] * f3;
+    R piece = s7 * half;
+    const R tol = sizeof(R) == 8 ? (R)1e-9 : (R)1e-5;
+    if (!(fabs(s3 - s7) <= tol * s7)) {  // the reference's 32 nodes in table order (sc:854-880); rare
+      R acc = 0;
 #pragma unroll 4
-        for (int i = 0; i < 32; ++i) acc += (R)GL32_W[i] * speed(half * (R)GL32_X[i] + mid);
-        piece[j] = acc * half;
-      }
-      redo_any |= redo;
+      for (int i = 0; i < 32; ++i) acc += (R)GL32_W[i] * speed(half * (R)GL32_X[i] + mid);
+      piece = acc * half;
     }
-    (void)redo_any;
+    tab[(size_t)sg * kTable + k + 1] = piece;
+  }
+  __syncthreads();  // pieces (global) are read back by another thread of this CTA
+
+  // ---- A4, step 2: cumulative table, one warp per (path, segment): lanes 0..24 own 4 consecutive pieces
+  for (int sg = warp; sg < nS; sg += nwarps) {
+    R* c = tab + (size_t)sg * kTable;
+    const bool live = lane < kScanLanes;
+    R run[kPiecesPerLane];
+#pragma unroll
+    for (int j = 0; j < kPiecesPerLane; ++j) run[j] = live ? c[lane * kPiecesPerLane + j + 1] : (R)0;
     // lane-local running sums, then an inclusive warp scan of the lane totals (sc:882-886 adds the
     // pieces one after the other; this order differs from it by rounding only)
-    R run[kPiecesPerLane];
-    run[0] = piece[0];
 #pragma unroll
-    for (int j = 1; j < kPiecesPerLane; ++j) run[j] = run[j - 1] + piece[j];
+    for (int j = 1; j < kPiecesPerLane; ++j) run[j] = run[j - 1] + run[j];
     R tot = live ? run[kPiecesPerLane - 1] : (R)0, incl = tot;
 #pragma unroll
     for (int off = 1; off < 32; off <<= 1) {
@@ -114,7 +118,6 @@ __global__ void __launch_bounds__(kArcThreads, 3) arc_kernel(PathArgs g) {
       if (lane >= off) incl += up;
     }
     const R base = incl - tot;
-    R* c = tab + (size_t)sg * kTable;
     if (live) {
 #pragma unroll
       for (int j = 0; j < kPiecesPerLane; ++j) c[lane * kPiecesPerLane + j + 1] = base + run[j];

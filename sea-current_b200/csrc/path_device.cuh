@@ -68,6 +68,10 @@ static __constant__ double kG4X[2] = {0.3399810435848562648, 0.86113631159405257
 static __constant__ double kG4W[2] = {0.6521451548625461426, 0.3478548451374538574};
 static __constant__ double kG6X[3] = {0.2386191860831969086, 0.6612093864662645137, 0.9324695142031520278};
 static __constant__ double kG6W[3] = {0.4679139345726910473, 0.3607615730481386076, 0.1713244923791703450};
+// Kronrod extension of the 3-point Gauss rule: nodes x1 < x2 (= sqrt(3/5), the Gauss node) < x3 are the roots of
+// P3(x) (x^4 - 10/9 x^2 + 155/891); weights for {0, x1, x2, x3} from exactness on 1, x^2, x^4, x^6
+static __constant__ double kK7X[3] = {0.43424374934680265, 0.7745966692414834, 0.96049126870802026};
+static __constant__ double kK7W[4] = {0.4509165386584757, 0.40139741477596125, 0.26848808986833372, 0.10465622602646719};
 // 4-point rule in the node order the arc-length inversion uses (DESIGN.md "Arc-length inversion")
 static __constant__ double kPGL4X[4] = {-0.8611363115940525752, -0.3399810435848562648, 0.3399810435848562648,
                                             0.8611363115940525752};
@@ -130,7 +134,7 @@ template <class R> __device__ __forceinline__ void lau_node_basis(R* out, int no
 
 // Geometry at toppra gridpoint i of one path: arc length q(s_i) (FP64, Hermite path of gen_vel_prof)
 // -> segment (first j with q <= segend[j]) -> table sub-interval -> Newton on a 4-point Gauss-Legendre
-// integral of |B'| (kInvNewton steps, DESIGN.md "Arc-length inversion") -> curve point and curvature (sc:1029).
+// integral of |B'| from a cubic-Hermite start (DESIGN.md "Arc-length inversion") -> curve point and curvature (sc:1029).
 //   segend: cumulative segment ends of this path (FP64); tab: its [nseg][101] cumulative table;
 //   ax, ay: its [nseg][DEG+1] power-basis coefficients.
 template <class R, int DEG>
@@ -151,33 +155,79 @@ __device__ __forceinline__ void gridpoint_geometry(int i, int N, double step, co
   // largest kl in [0, 99] with c[kl] <= r: the table is close to linear, so start from the proportional
   // guess and walk (two independent loads, then rarely more) instead of seven dependent bisection loads
   int kl = (int)((R)kSub * r / seg_len);
-  kl = max(0, min(kSub - 1, kl));
-  while (kl > 0 && c[kl] > r) --kl;
-  while (kl < kSub - 1 && c[kl + 1] <= r) ++kl;
+  kl = max(1, min(kSub - 2, kl));
+  // four independent loads around the guess decide almost every gridpoint in one memory round trip
+  // (the dependent walk that follows was 21 % of this kernel's stall samples, profiles/r1h_arc_kernel_f64.lines.txt)
+  R ck, ck1;
+  {
+    const R cm = c[kl - 1], c0 = c[kl], c1 = c[kl + 1], c2 = c[kl + 2];
+    if (r < c0) { --kl; ck = cm; ck1 = c0; }
+    else if (r >= c1) { ++kl; ck = c1; ck1 = c2; }
+    else { ck = c0; ck1 = c1; }
+    if (ck > r || (ck1 <= r && kl < kSub - 1)) {  // the guess was off by more than one piece: walk
+      while (kl > 0 && c[kl] > r) --kl;
+      while (kl < kSub - 1 && c[kl + 1] <= r) ++kl;
+      ck = c[kl]; ck1 = c[kl + 1];
+    }
+  }
   const R h = (R)0.01, a0 = fmin((R)kl * h, (R)1);
-  const R ck = c[kl], target = r - ck;
-  R du = h * target / (c[kl + 1] - ck);
-  du = fmin(fmax(du, (R)0), h);
+  const R target = r - ck, ds = ck1 - ck;
   const R* sax = ax + NC * sg; const R* say = ay + NC * sg;
   R kx[DEG], ky[DEG];  // B' in power basis: (k+1) a_{k+1}
 #pragma unroll
   for (int j = 0; j < DEG; ++j) { kx[j] = (R)(j + 1) * sax[j + 1]; ky[j] = (R)(j + 1) * say[j + 1]; }
-  auto speed = [&](R u) {
+  auto speed2 = [&](R u) {
     R dx = kx[DEG - 1], dy = ky[DEG - 1];
 #pragma unroll
     for (int j = DEG - 2; j >= 0; --j) { dx = dx * u + kx[j]; dy = dy * u + ky[j]; }
-    const R n2 = dx * dx + dy * dy;
-    return n2 > 0 ? n2 * fast_rsqrt<R>(n2) : (R)0;
+    return dx * dx + dy * dy;
   };
+  auto speed = [&](R u) { const R n2 = speed2(u); return n2 > 0 ? n2 * fast_rsqrt<R>(n2) : (R)0; };
+  auto inv_speed = [&](R u) { const R n2 = speed2(u); return n2 > 0 ? fast_rsqrt<R>(n2) : (R)0; };
+  // Start: the cubic Hermite inverse u(s) on [c_k, c_k+1] (end values 0 and h, end slopes 1/|B'|): its error
+  // is ~ds^4 |d4u/ds4| / 384, i.e. ~1e-8 h for a smooth piece against ~1e-3 h for linear interpolation, so
+  // that ONE Newton step on the quadrature normally reaches the root; near a cusp the clamps keep the
+  // iterate inside the piece.
+  R du;
+  bool smooth;
+  {
+    const R tau = fmin(fmax(target * fast_rcp<R>(ds), (R)0), (R)1), om = (R)1 - tau;
+    const R r0 = inv_speed(a0), r1 = inv_speed(fmin(a0 + h, (R)1));
+    du = (tau * om) * ds * (om * r0 - tau * r1) + h * (tau * tau) * ((R)3 - (R)2 * tau);
+    du = fmin(fmax(du, (R)0), h);
+    const R m0 = r0 * ds, m1 = r1 * ds;  // mean speed / end speed
+    smooth = m0 >= (R)0.8 * h && m0 <= (R)1.25 * h && m1 >= (R)0.8 * h && m1 <= (R)1.25 * h;
+  }
+  // One step is accepted only where the iteration is known to be quadratic and the step small:
+  //   (a) the piece is smooth (end speeds within 25 % of the mean speed ds/h: |B'| has no dip inside, so the
+  //       4-point quadrature F and its Newton derivative |B'| are consistent to ~1e-8),
+  //   (b) the correction was small, and (c) the predicted next correction C delta^2 is below tolerance,
+  //       C = |d|B'|/du| / (2 |B'|) = |B'.B''| / (2 |B'|^2) where the step lands.
+  // Otherwise (near a cusp F is a poor quadrature, its derivative is not |B'| and Newton converges only
+  // linearly) the loop runs to |delta| <= tolS like the restated definition does.
+  const bool f64 = sizeof(R) == 8;
+  const R tolS = (f64 ? (R)1e-12 : (R)2e-5) * h, tolB = (f64 ? (R)1e-5 : (R)1e-2) * h, tolC = (f64 ? (R)1e-12 : (R)1e-5) * h;
 #pragma unroll 1
-  for (int nit = 0; nit < kInvNewton; ++nit) {
+  for (int nit = 0; nit < kInvNewtonMax; ++nit) {
     const R half = (R)0.5 * du, mid = a0 + half;
     R F = 0;
 #pragma unroll
     for (int gq = 0; gq < 4; ++gq) F += (R)kPGL4W[gq] * speed(mid + half * (R)kPGL4X[gq]);
     F *= half;
-    du = du - (F - target) / speed(a0 + du);
-    du = fmin(fmax(du, (R)0), h);
+    const R ue = a0 + du;
+    R x1 = kx[DEG - 1], y1 = ky[DEG - 1];
+#pragma unroll
+    for (int j = DEG - 2; j >= 0; --j) { x1 = x1 * ue + kx[j]; y1 = y1 * ue + ky[j]; }
+    R x2 = (R)(DEG - 1) * kx[DEG - 1], y2 = (R)(DEG - 1) * ky[DEG - 1];
+#pragma unroll
+    for (int j = DEG - 3; j >= 0; --j) { x2 = x2 * ue + (R)(j + 1) * kx[j + 1]; y2 = y2 * ue + (R)(j + 1) * ky[j + 1]; }
+    const R n2 = x1 * x1 + y1 * y1, rn = n2 > 0 ? fast_rsqrt<R>(n2) : (R)0;
+    const R delta = (F - target) * rn;
+    du = fmin(fmax(du - delta, (R)0), h);
+    const R ad = fabs(delta);
+    if (ad <= tolS) break;
+    const R C = (R)0.5 * fabs(x1 * x2 + y1 * y2) * (rn * rn);
+    if (smooth && ad <= tolB && C * ad * ad <= tolC) break;
   }
   const R u = fmin(a0 + du, (R)1);
   bx = sax[DEG]; by = say[DEG];

@@ -11,7 +11,8 @@ namespace scb {
 constexpr int kWarp = 32;
 constexpr int kTable = SCB_ARCLEN_TABLE;   // 101 cumulative entries per segment
 constexpr int kSub = SCB_ARCLEN_SUBDIV;    // 100 sub-intervals per segment (sc:767, precision 0.01)
-constexpr int kInvNewton = 3;              // Newton steps of the arc-length inversion
+constexpr int kInvNewton = 3;              // Newton steps of the arc-length inversion, fixed-count form (sampler)
+constexpr int kInvNewtonMax = 40;          // ... and the cap of the adaptive form (arc kernel; 1 step is the rule)
 
 template <class R> struct Num;
 template <> struct Num<double> {
