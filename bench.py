@@ -104,13 +104,21 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(sm)}
 
 
+def host_cores():
+    """Host threads this process may use (torchrun exports OMP_NUM_THREADS=1; the CPU arm must not inherit that)."""
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
 def cpu_baseline_run(w, G, seconds, nthreads):
     """The oracle's reference-faithful port of the E1 body (float32 spline side with the 10,001-point
     preview sampling, Bernstein-Fourier evaluation, FP64 toppra with the dense column-pivoted QR
     parametrizer; 'port'), on a bounded sample of the same workload."""
     from oracle import oracle as ora
     ora.build()
-    cores = nthreads or ora.num_threads()
+    cores = nthreads or host_cores()
     P = w["wx"].shape[0]
     n = min(P, cores)
     sel = slice(0, n)
@@ -139,7 +147,7 @@ def reference_arm(a):
     G = cfg["G"]
     from oracle import oracle as ora
     ora.build()
-    cores = ora.num_threads()
+    cores = host_cores()
     n = min(w["wx"].shape[0], cores)
     args = (w["wx"][:n], w["wy"][:n], w["vel_lo"][:n], w["vel_hi"][:n], w["acc_lo"][:n], w["acc_hi"][:n])
     for _ in range(a.warmup):
@@ -173,6 +181,7 @@ def main():
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # stdout carries the one JSON line only
         dist.init_process_group("nccl", device_id=dev)
     w, cfg, scaling = workload(a.config, rank, world, a.problems)
     P, W = w["wx"].shape
@@ -318,7 +327,7 @@ def main():
                        "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": k2,
                        "last_step_ms": {k: tm[k] for k in ("h2d_ms", "d2h_ms", "total_ms")},
                        "outputs": list(names)}
-    if rank == 0 and not a.no_cpu:
+    if rank == 0 and world == 1 and not a.no_cpu:  # N=1 only (torchrun pins OMP_NUM_THREADS=1 per rank)
         line["cpu_baseline"] = cpu_baseline_run(w, G, a.cpu_seconds, 0)
     if rank == 0:
         print(json.dumps(line))
