@@ -37,6 +37,10 @@ constexpr double abs_tol = 1e-13, rel_tol = 1e-10, maxsd = 1e8;
 
 namespace {
 
+// min / max of two non-NaN doubles: compare + two selects (fmin / fmax cost a fourth instruction for NaN quieting)
+__device__ __forceinline__ double dmin(double a, double b) { return a < b ? a : b; }
+__device__ __forceinline__ double dmax(double a, double b) { return a > b ? a : b; }
+
 // lo <= al u + be x <= hi with al >= 0 (a slab with al < 0 is its own mirror image)
 struct Slab { double al, be, lo, hi; };
 
@@ -55,13 +59,13 @@ __device__ __forceinline__ bool pair_apply(double D, double rD, double E1, doubl
   const double q1 = E1 * rD, q2 = E2 * rD;
   const bool pos = D > 0, zero = D == 0;
   const double hc = pos ? q1 : q2, lc = pos ? q2 : q1;
-  xh = fmin(xh, zero ? CUDART_INF : hc);
-  xl = fmax(xl, zero ? -CUDART_INF : lc);
+  xh = dmin(xh, zero ? CUDART_INF : hc);
+  xl = dmax(xl, zero ? -CUDART_INF : lc);
   return !(zero && (E1 < -ftol::abs_tol || E2 > ftol::abs_tol));
 }
 
 __device__ __forceinline__ bool incoherent(double lo, double hi) {
-  return lo - hi > fmax(ftol::abs_tol, fmax(fabs(lo), fabs(hi)) * ftol::rel_tol);
+  return lo - hi > dmax(ftol::abs_tol, dmax(fabs(lo), fabs(hi)) * ftol::rel_tol);
 }
 
 // linear_joint_velocity.cpp:24-61: x-box of a gridpoint from the velocity limits [lo, hi] and q' = v
@@ -69,8 +73,8 @@ __device__ __forceinline__ bool vel_xbound(double v, double lo, double hi, doubl
   const double vinv = fast_rcp<double>(v);  // unused when v == 0
   const double p = hi * vinv, m = lo * vinv;
   const bool pos = v > 0, zero = v == 0;
-  const double sdmax = zero ? ftol::maxsd : fmin(pos ? p : m, ftol::maxsd);
-  const double sdmin = zero ? -ftol::maxsd : fmax(pos ? m : p, -ftol::maxsd);
+  const double sdmax = zero ? ftol::maxsd : dmin(pos ? p : m, ftol::maxsd);
+  const double sdmin = zero ? -ftol::maxsd : dmax(pos ? m : p, -ftol::maxsd);
   xlo = sdmin > 0 ? sdmin * sdmin : 0.0;
   xhi = sdmax * sdmax;
   return !(zero && (hi < 0 || lo > 0));
@@ -143,14 +147,14 @@ __global__ void __launch_bounds__(64) toppra_fast_kernel(ToppraArgs g) {
     // slab 0 is K[i+1] seen through x_next = x + 2 delta u: (al, be, lo, hi) = (2 delta, 1, nlo, nhi)
     const double D01 = fma(-twod, s1.be, s1.al), D02 = fma(-twod, s2.be, s2.al), D12 = fma(s1.be, s2.al, -(s2.be * s1.al));
     const double r01 = fast_rcp<double>(D01), r02 = fast_rcp<double>(D02), r12 = fast_rcp<double>(D12);
-    double xl = fmax(xlo, 0.0), xh = fmin(xhi, x_cap);
+    double xl = dmax(xlo, 0.0), xh = dmin(xhi, x_cap);
     bool ok = !incoherent(xl, xh);
     ok = pair_apply(D12, r12, fma(s1.hi, s2.al, -(s2.lo * s1.al)), fma(s1.lo, s2.al, -(s2.hi * s1.al)), xl, xh) && ok;
     ok = pair_apply(D01, r01, fma(nhi, s1.al, -(s1.lo * twod)), fma(nlo, s1.al, -(s1.hi * twod)), xl, xh) && ok;
     ok = pair_apply(D02, r02, fma(nhi, s2.al, -(s2.lo * twod)), fma(nlo, s2.al, -(s2.hi * twod)), xl, xh) && ok;
     ok = ok && !incoherent(xl, xh) && acc_ok;
     if (!ok) { first_fail = i; alive = false; put_K(o, 0.0, 0.0); continue; }
-    nhi = xh; nlo = fmax(0.0, xl);
+    nhi = xh; nlo = dmax(0.0, xl);
     put_K(o, nlo, nhi);
   }
   if (status == SCB_ST_ERR_BAD_LIMITS) {
@@ -191,15 +195,15 @@ __global__ void __launch_bounds__(64) toppra_fast_kernel(ToppraArgs g) {
           const double r0 = fast_rcp<double>(twod), r1 = fast_rcp<double>(s1.al), r2 = fast_rcp<double>(s2.al);
           const double klo = kl[u], khi = kh[u];
           // a box that misses x_i by more than the tolerance is infeasible (seidel.cpp:73-76)
-          const double lo1 = fmax(xlo, xi), hi1 = fmin(xhi, xi);
-          bool ok = !(lo1 > hi1 && (lo1 - hi1 > fmax(fabs(lo1), fabs(hi1)) * ftol::rel_tol));
+          const double lo1 = dmax(xlo, xi), hi1 = dmin(xhi, xi);
+          bool ok = !(lo1 > hi1 && (lo1 - hi1 > dmax(fabs(lo1), fabs(hi1)) * ftol::rel_tol));
           const double xf = lo1 > hi1 ? (lo1 + hi1) / 2 : xi;
           // slabs without u (al = 0) only constrain x
           const double u0 = (khi - xf) * r0;
           const double u1 = s1.al > 0 ? fma(-s1.be, xf, s1.hi) * r1 : CUDART_INF;
           const double u2 = s2.al > 0 ? fma(-s2.be, xf, s2.hi) * r2 : CUDART_INF;
-          const double uu = fmin(u0, fmin(u1, u2));
-          const double slack = fmax(ftol::abs_tol, fabs(uu) * ftol::rel_tol);
+          const double uu = dmin(u0, dmin(u1, u2));
+          const double slack = dmax(ftol::abs_tol, fabs(uu) * ftol::rel_tol);
           ok = ok && (klo - xf - twod * uu) <= twod * slack + ftol::abs_tol;
           ok = ok && (s1.lo - s1.be * xf - s1.al * uu) <= s1.al * slack + ftol::abs_tol;
           ok = ok && (s2.lo - s2.be * xf - s2.al * uu) <= s2.al * slack + ftol::abs_tol;
@@ -208,7 +212,7 @@ __global__ void __launch_bounds__(64) toppra_fast_kernel(ToppraArgs g) {
           ox += P;
           if (!ok) { status = SCB_ST_ERR_FAIL_FORWARD_PASS; fail_stage = i; go = false; }
           else {
-            xi = fmin(khi, fmax(klo, fma(twod, uu, xi)));
+            xi = dmin(khi, dmax(klo, fma(twod, uu, xi)));
             X[ox] = (S)xi;
             done = i + 1;
           }
