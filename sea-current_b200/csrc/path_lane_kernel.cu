@@ -11,7 +11,7 @@
 // state (a register spill area the owner alone touches).
 //
 // Cost + gradient of a segment run on ONE lane, all 32 Gauss-Legendre nodes in sequence, so node
-// constants are warp-uniform constant-bank operands (LAU_NODE) and partial sums never leave
+// constants are warp-uniform constant-bank operands (LAU_PAIR) and partial sums never leave
 // registers.  The hodograph is evaluated in the power basis,
 //     B'(u) = sum_m c_m u^m,  c_m = C(4,m) Delta^m D_0,  D_j = 5 (P_{j+1} - P_j),
 // by Horner (7 FMAs per axis for B', B'' instead of 12 in the Bernstein form), and the gradient is
@@ -20,7 +20,8 @@
 //     D0 = T_i, D1 = T_i + A_i/4, D2 = 5 (W_{i+1} - W_i) - 2 (T_i + T_{i+1}) + (A_{i+1} - A_i)/4,
 //     D3 = T_{i+1} - A_{i+1}/4, D4 = T_{i+1},
 // which is the frozen control-point construction with the O(|W|) terms cancelled analytically.
-// 63 FP64 instructions per node (was ~95).
+// Nodes are taken in symmetric pairs about u = 1/2 (segment_cost below): ~53 FP64 instructions per node
+// (the Bernstein-form predecessor needed ~95).
 //
 // Arithmetic is FP64 for both storage types S: iRPROP- acts on gradient SIGNS, so its iterates are
 // only reproducible where the gradient is resolved far below the decision threshold (1e-9 of the
@@ -42,45 +43,78 @@ __device__ __forceinline__ double up1(double v) { return __shfl_up_sync(kAll, v,
 __device__ __forceinline__ double dn1(double v) { return __shfl_down_sync(kAll, v, 1); }
 __device__ __forceinline__ double from(double v, int src) { return __shfl_sync(kAll, v, src & 31); }
 
+// What one cost node contributes, given B' = (x1, y1) and B'' = (x2, y2) there: the weighted integrand (returned)
+// and, if GRAD, the weighted forces f1 = dJ/dB', f2 = dJ/dB''.
+//   d/dB' = k1 (y2, -x2) + (k3 - k2) B',  d/dB'' = k1 (-y1, x1);  k1 = 2c/n^5, k2 = 5c^2/n^7, k3 = lambda/n
+template <bool GRAD>
+__device__ __forceinline__ double node_terms(double x1, double y1, double x2, double y2, double lambda, double wq, double w2,
+                                             double& fx1, double& fy1, double& fx2, double& fy2) {
+  // n = |B'|; every power of 1/n comes from one rsqrt
+  const double n2 = fma(x1, x1, y1 * y1), rn = fast_rsqrt<double>(n2), n = n2 * rn, rn2 = rn * rn;
+  const double c = fma(x1, y2, -(y1 * x2));
+  const double in5 = (rn2 * rn2) * rn;
+  const double t = c * in5, cc5 = t * c;  // c / n^5, c^2 / n^5
+  if (GRAD) {
+    const double wk1 = w2 * t;
+    const double wk32 = wq * fma(-5.0, cc5 * rn2, lambda * rn);
+    fx1 = fma(wk1, y2, wk32 * x1); fy1 = fma(-wk1, x2, wk32 * y1);
+    fx2 = -(wk1 * y1); fy2 = wk1 * x1;
+  }
+  return fma(lambda, n, cc5);
+}
+
 // Cost of one quintic segment and, if GRAD, its gradient with respect to the power-basis coefficients of
-// the hodograph (gc?[m] = dJ/dc_m).  cx, cy: c_0..c_4.  32 nodes in the reference's table order.
+// the hodograph (gc?[m] = dJ/dc_m).  cx, cy: c_0..c_4.  The 32 nodes are 16 pairs u = 1/2 -+ h with equal
+// weights: with B'(1/2 + v) = sum_m e_m v^m the two values of a pair are E(h^2) -+ h O(h^2) (even and odd
+// parts: 11 instructions per axis for B' and B'' at BOTH nodes instead of 14), and the moments
+// G_m = sum f1 v^m, H_m = sum f2 v^m take the pair's sum (even m) or difference (odd m): 13 instead of 18.
 template <bool GRAD>
 __device__ __forceinline__ double segment_cost(const double (&cx)[5], const double (&cy)[5], double lambda,
                                                double (&gcx)[5], double (&gcy)[5]) {
-  const double dx2 = 2.0 * cx[2], dx3 = 3.0 * cx[3], dx4 = 4.0 * cx[4];
-  const double dy2 = 2.0 * cy[2], dy3 = 3.0 * cy[3], dy4 = 4.0 * cy[4];
+  // Taylor shift to u = 1/2: e_m = sum_k c_k C(k,m) 2^(m-k)
+  const double ex0 = cx[0] + 0.5 * cx[1] + 0.25 * cx[2] + 0.125 * cx[3] + 0.0625 * cx[4];
+  const double ex1 = cx[1] + cx[2] + 0.75 * cx[3] + 0.5 * cx[4];
+  const double ex2 = cx[2] + 1.5 * cx[3] + 1.5 * cx[4], ex3 = cx[3] + 2.0 * cx[4], ex4 = cx[4];
+  const double ey0 = cy[0] + 0.5 * cy[1] + 0.25 * cy[2] + 0.125 * cy[3] + 0.0625 * cy[4];
+  const double ey1 = cy[1] + cy[2] + 0.75 * cy[3] + 0.5 * cy[4];
+  const double ey2 = cy[2] + 1.5 * cy[3] + 1.5 * cy[4], ey3 = cy[3] + 2.0 * cy[4], ey4 = cy[4];
+  // B''(1/2 + v) = e1 + 2 e2 v + 3 e3 v^2 + 4 e4 v^3
+  const double tx2 = 2.0 * ex2, tx3 = 3.0 * ex3, tx4 = 4.0 * ex4, ty2 = 2.0 * ey2, ty3 = 3.0 * ey3, ty4 = 4.0 * ey4;
   double J = 0;
   double Gx[5] = {0, 0, 0, 0, 0}, Gy[5] = {0, 0, 0, 0, 0}, Hx[4] = {0, 0, 0, 0}, Hy[4] = {0, 0, 0, 0};
-#pragma unroll 4
-  for (int q = 0; q < 32; ++q) {
-    const double u = LAU_NODE[q][0], u2 = LAU_NODE[q][1], u3 = LAU_NODE[q][2], u4 = LAU_NODE[q][3];
-    const double wq = LAU_NODE[q][4], w2 = LAU_NODE[q][5];
-    const double x1 = fma(fma(fma(fma(cx[4], u, cx[3]), u, cx[2]), u, cx[1]), u, cx[0]);
-    const double y1 = fma(fma(fma(fma(cy[4], u, cy[3]), u, cy[2]), u, cy[1]), u, cy[0]);
-    const double x2 = fma(fma(fma(dx4, u, dx3), u, dx2), u, cx[1]);
-    const double y2 = fma(fma(fma(dy4, u, dy3), u, dy2), u, cy[1]);
-    // n = |B'|; every power of 1/n comes from one rsqrt
-    const double n2 = fma(x1, x1, y1 * y1), rn = fast_rsqrt<double>(n2), n = n2 * rn, rn2 = rn * rn;
-    const double c = fma(x1, y2, -(y1 * x2));
-    const double in5 = (rn2 * rn2) * rn;
-    const double t = c * in5, cc5 = t * c;                  // c / n^5, c^2 / n^5
-    J = fma(wq, fma(lambda, n, cc5), J);
+#pragma unroll 2
+  for (int q = 0; q < 16; ++q) {
+    const double h = LAU_PAIR[q][0], w = LAU_PAIR[q][1], ww = LAU_PAIR[q][2], h3 = LAU_PAIR[q][3];
+    const double wq = LAU_PAIR[q][4], w2 = LAU_PAIR[q][5];
+    const double Ex = fma(fma(ex4, w, ex2), w, ex0), Ox = h * fma(ex3, w, ex1);
+    const double Ey = fma(fma(ey4, w, ey2), w, ey0), Oy = h * fma(ey3, w, ey1);
+    const double Ax = fma(tx3, w, ex1), Bx = h * fma(tx4, w, tx2);
+    const double Ay = fma(ty3, w, ey1), By = h * fma(ty4, w, ty2);
+    double fx1p, fy1p, fx2p, fy2p, fx1m, fy1m, fx2m, fy2m;
+    const double jm = node_terms<GRAD>(Ex - Ox, Ey - Oy, Ax - Bx, Ay - By, lambda, wq, w2, fx1m, fy1m, fx2m, fy2m);
+    const double jp = node_terms<GRAD>(Ex + Ox, Ey + Oy, Ax + Bx, Ay + By, lambda, wq, w2, fx1p, fy1p, fx2p, fy2p);
+    J = fma(wq, jm + jp, J);
     if (GRAD) {
-      // d/dB' = k1 (y2, -x2) + (k3 - k2) B',  d/dB'' = k1 (-y1, x1);  k1 = 2c/n^5, k2 = 5c^2/n^7, k3 = lambda/n
-      const double wk1 = w2 * t;
-      const double wk32 = wq * fma(-5.0, cc5 * rn2, lambda * rn);
-      const double fx1 = fma(wk1, y2, wk32 * x1), fy1 = fma(-wk1, x2, wk32 * y1);
-      const double fx2 = -(wk1 * y1), fy2 = wk1 * x1;
-      Gx[0] += fx1; Gx[1] = fma(fx1, u, Gx[1]); Gx[2] = fma(fx1, u2, Gx[2]); Gx[3] = fma(fx1, u3, Gx[3]); Gx[4] = fma(fx1, u4, Gx[4]);
-      Gy[0] += fy1; Gy[1] = fma(fy1, u, Gy[1]); Gy[2] = fma(fy1, u2, Gy[2]); Gy[3] = fma(fy1, u3, Gy[3]); Gy[4] = fma(fy1, u4, Gy[4]);
-      Hx[0] += fx2; Hx[1] = fma(fx2, u, Hx[1]); Hx[2] = fma(fx2, u2, Hx[2]); Hx[3] = fma(fx2, u3, Hx[3]);
-      Hy[0] += fy2; Hy[1] = fma(fy2, u, Hy[1]); Hy[2] = fma(fy2, u2, Hy[2]); Hy[3] = fma(fy2, u3, Hy[3]);
+      const double sx1 = fx1p + fx1m, dx1 = fx1p - fx1m, sy1 = fy1p + fy1m, dy1 = fy1p - fy1m;
+      const double sx2 = fx2p + fx2m, dx2 = fx2p - fx2m, sy2 = fy2p + fy2m, dy2 = fy2p - fy2m;
+      Gx[0] += sx1; Gx[2] = fma(sx1, w, Gx[2]); Gx[4] = fma(sx1, ww, Gx[4]); Gx[1] = fma(dx1, h, Gx[1]); Gx[3] = fma(dx1, h3, Gx[3]);
+      Gy[0] += sy1; Gy[2] = fma(sy1, w, Gy[2]); Gy[4] = fma(sy1, ww, Gy[4]); Gy[1] = fma(dy1, h, Gy[1]); Gy[3] = fma(dy1, h3, Gy[3]);
+      Hx[0] += sx2; Hx[2] = fma(sx2, w, Hx[2]); Hx[1] = fma(dx2, h, Hx[1]); Hx[3] = fma(dx2, h3, Hx[3]);
+      Hy[0] += sy2; Hy[2] = fma(sy2, w, Hy[2]); Hy[1] = fma(dy2, h, Hy[1]); Hy[3] = fma(dy2, h3, Hy[3]);
     }
   }
-  if (GRAD) {  // B'' = sum_m m c_m u^(m-1)
-    gcx[0] = Gx[0]; gcy[0] = Gy[0];
+  if (GRAD) {
+    // gradient with respect to e_m (B'' = sum_m m e_m v^(m-1)), then the transposed Taylor shift
+    double gex[5], gey[5];
+    gex[0] = Gx[0]; gey[0] = Gy[0];
 #pragma unroll
-    for (int m = 1; m < 5; ++m) { gcx[m] = fma((double)m, Hx[m - 1], Gx[m]); gcy[m] = fma((double)m, Hy[m - 1], Gy[m]); }
+    for (int m = 1; m < 5; ++m) { gex[m] = fma((double)m, Hx[m - 1], Gx[m]); gey[m] = fma((double)m, Hy[m - 1], Gy[m]); }
+    gcx[0] = gex[0]; gcy[0] = gey[0];
+    gcx[1] = 0.5 * gex[0] + gex[1]; gcy[1] = 0.5 * gey[0] + gey[1];
+    gcx[2] = 0.25 * gex[0] + gex[1] + gex[2]; gcy[2] = 0.25 * gey[0] + gey[1] + gey[2];
+    gcx[3] = 0.125 * gex[0] + 0.75 * gex[1] + 1.5 * gex[2] + gex[3]; gcy[3] = 0.125 * gey[0] + 0.75 * gey[1] + 1.5 * gey[2] + gey[3];
+    gcx[4] = 0.0625 * gex[0] + 0.5 * gex[1] + 1.5 * gex[2] + 2.0 * gex[3] + gex[4];
+    gcy[4] = 0.0625 * gey[0] + 0.5 * gey[1] + 1.5 * gey[2] + 2.0 * gey[3] + gey[4];
   }
   return J;
 }
