@@ -31,13 +31,15 @@ namespace scb {
 constexpr int kArcThreads = 256;
 constexpr int kPiecesPerLane = 4, kScanLanes = kSub / kPiecesPerLane;  // 25 lanes x 4 pieces = 100
 
-__host__ __device__ inline size_t arc_smem_bytes(int W, int deg, int PB, int real_size) {
+__host__ __device__ inline size_t arc_smem_bytes(int W, int deg, int PB, int real_size, bool table_in_smem) {
   const size_t nseg = W - 1;
-  const size_t reals = (size_t)PB * nseg * (2 * (deg + 1) + 2 * deg + 1) + (size_t)PB * 2;
+  const size_t reals = (size_t)PB * nseg * (2 * (deg + 1) + 2 * deg + 1 + (table_in_smem ? kTable : 0)) + (size_t)PB * 2;
   return 64 + sizeof(double) * PB * nseg + (reals * real_size + 15) / 16 * 16;
 }
 
-template <class R, int DEG>
+// TS: the CTA's arc-length tables also live in shared memory (the geometry phase reads them from there; the
+// table lookups out of L1/L2 were a third of this kernel's stall samples, profiles/r1i_arc_kernel_f64.lines.txt)
+template <class R, int DEG, bool TS>
 __global__ void __launch_bounds__(kArcThreads, 3) arc_kernel(PathArgs g) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   constexpr int NC = DEG + 1;
@@ -53,6 +55,7 @@ __global__ void __launch_bounds__(kArcThreads, 3) arc_kernel(PathArgs g) {
   R* hx = sm.take((size_t)PB * nseg * DEG); R* hy = sm.take((size_t)PB * nseg * DEG);
   R* segtot = sm.take((size_t)PB * nseg);
   R* vse = sm.take((size_t)PB * 2);                  // vel_start, vel_end per path
+  R* stab = TS ? sm.take((size_t)PB * nseg * kTable) : nullptr;
   const int nS = PBa * nseg, nc = nseg * NC, nt = nseg * kTable;
 
   // ---- status of the path kernel, power basis of every segment
@@ -67,6 +70,7 @@ __global__ void __launch_bounds__(kArcThreads, 3) arc_kernel(PathArgs g) {
   // ---- A4, step 1: every 0.01-wide piece of every segment, one piece per thread and turn (all lanes busy;
   // the warp-per-segment form kept 25 of 32).  Raw piece lengths go to the table's own slots [k + 1].
   R* tab = (R*)g.table + (size_t)p0 * nt;
+  R* wtab = TS ? stab : tab;  // where the pieces and the lookups live
   for (int it = tid; it < nS * kSub; it += T) {
     const int sg = it / kSub, k = it - sg * kSub;
     R kx[DEG], ky[DEG];
@@ -96,17 +100,18 @@ __global__ void __launch_bounds__(kArcThreads, 3) arc_kernel(PathArgs g) {
       for (int i = 0; i < 32; ++i) acc += (R)GL32_W[i] * speed(half * (R)GL32_X[i] + mid);
       piece = acc * half;
     }
-    tab[(size_t)sg * kTable + k + 1] = piece;
+    wtab[(size_t)sg * kTable + k + 1] = piece;
   }
-  __syncthreads();  // pieces (global) are read back by another thread of this CTA
+  __syncthreads();  // pieces are read back by another thread of this CTA
 
   // ---- A4, step 2: cumulative table, one warp per (path, segment): lanes 0..24 own 4 consecutive pieces
   for (int sg = warp; sg < nS; sg += nwarps) {
     R* c = tab + (size_t)sg * kTable;
+    R* cs = wtab + (size_t)sg * kTable;
     const bool live = lane < kScanLanes;
     R run[kPiecesPerLane];
 #pragma unroll
-    for (int j = 0; j < kPiecesPerLane; ++j) run[j] = live ? c[lane * kPiecesPerLane + j + 1] : (R)0;
+    for (int j = 0; j < kPiecesPerLane; ++j) run[j] = live ? cs[lane * kPiecesPerLane + j + 1] : (R)0;
     // lane-local running sums, then an inclusive warp scan of the lane totals (sc:882-886 adds the
     // pieces one after the other; this order differs from it by rounding only)
 #pragma unroll
@@ -120,9 +125,13 @@ __global__ void __launch_bounds__(kArcThreads, 3) arc_kernel(PathArgs g) {
     const R base = incl - tot;
     if (live) {
 #pragma unroll
-      for (int j = 0; j < kPiecesPerLane; ++j) c[lane * kPiecesPerLane + j + 1] = base + run[j];
+      for (int j = 0; j < kPiecesPerLane; ++j) {
+        const R v = base + run[j];
+        c[lane * kPiecesPerLane + j + 1] = v;
+        if (TS) cs[lane * kPiecesPerLane + j + 1] = v;
+      }
     }
-    if (lane == 0) c[0] = 0;
+    if (lane == 0) { c[0] = 0; if (TS) cs[0] = 0; }
     if (lane == kScanLanes - 1) segtot[sg] = incl;
   }
   __syncthreads();
@@ -163,7 +172,7 @@ __global__ void __launch_bounds__(kArcThreads, 3) arc_kernel(PathArgs g) {
       }
       R bx, by, kap;
       gridpoint_geometry<R, DEG>(i, N, step, segend + pl * nseg, nseg, (double)vse[pl * 2], (double)vse[pl * 2 + 1],
-                                 tab + (size_t)pl * nt, ax + (size_t)pl * nseg * NC, ay + (size_t)pl * nseg * NC, bx, by, kap);
+                                 wtab + (size_t)pl * nt, ax + (size_t)pl * nseg * NC, ay + (size_t)pl * nseg * NC, bx, by, kap);
       if (o_px) o_px[oo] = bx;
       if (o_py) o_py[oo] = by;
       if (o_k) o_k[oo] = kap;
@@ -171,30 +180,37 @@ __global__ void __launch_bounds__(kArcThreads, 3) arc_kernel(PathArgs g) {
   }
 }
 
-// paths per CTA: 8 when the power bases fit ~40 KB (3+ CTAs per SM), fewer for long paths; 0 = too long
-int arc_paths_per_cta(int W, int spline_mode, int real_size, size_t& smem) {
+// paths per CTA: as many (up to 8) as keep three CTAs on an SM with the tables in shared memory; long paths
+// keep their tables in global memory (8, 4, 2 or 1 paths per CTA by the size of the power bases); 0 = too long
+int arc_paths_per_cta(int W, int spline_mode, int real_size, size_t& smem, bool* table_in_smem) {
   const int deg = spline_mode == SCB_REF_CUBIC ? 3 : 5;
+  for (int pb = 8; pb >= 1; --pb) {
+    smem = arc_smem_bytes(W, deg, pb, real_size, true);
+    if (smem <= 74 * 1024) { if (table_in_smem) *table_in_smem = true; return pb; }
+  }
+  if (table_in_smem) *table_in_smem = false;
   for (int pb = 8; pb >= 1; pb >>= 1) {
-    smem = arc_smem_bytes(W, deg, pb, real_size);
+    smem = arc_smem_bytes(W, deg, pb, real_size, false);
     if (smem <= (pb > 1 ? 40 * 1024 : 200 * 1024)) return pb;
   }
   return 0;
 }
 
+template <class R, int DEG, bool TS> static void launch_arc_t(const PathArgs& a, int grid, size_t smem, cudaStream_t st) {
+  cudaFuncSetAttribute(arc_kernel<R, DEG, TS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (TS) cudaFuncSetAttribute(arc_kernel<R, DEG, TS>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+  arc_kernel<R, DEG, TS><<<grid, kArcThreads, smem, st>>>(a);
+}
+
 template <class R> void launch_arc(const PathArgs& a0, int spline_mode, cudaStream_t st) {
   PathArgs a = a0;
-  size_t smem;
-  const int PB = arc_paths_per_cta(a.W, spline_mode, (int)sizeof(R), smem);
+  size_t smem; bool ts;
+  const int PB = arc_paths_per_cta(a.W, spline_mode, (int)sizeof(R), smem, &ts);
   if (!PB) return;
   a.PB = PB;
   const int grid = (a.P + PB - 1) / PB;
-  if (spline_mode == SCB_REF_CUBIC) {
-    cudaFuncSetAttribute(arc_kernel<R, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    arc_kernel<R, 3><<<grid, kArcThreads, smem, st>>>(a);
-  } else {
-    cudaFuncSetAttribute(arc_kernel<R, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    arc_kernel<R, 5><<<grid, kArcThreads, smem, st>>>(a);
-  }
+  if (spline_mode == SCB_REF_CUBIC) { if (ts) launch_arc_t<R, 3, true>(a, grid, smem, st); else launch_arc_t<R, 3, false>(a, grid, smem, st); }
+  else { if (ts) launch_arc_t<R, 5, true>(a, grid, smem, st); else launch_arc_t<R, 5, false>(a, grid, smem, st); }
 }
 template void launch_arc<double>(const PathArgs&, int, cudaStream_t);
 template void launch_arc<float>(const PathArgs&, int, cudaStream_t);

@@ -121,7 +121,7 @@ template <class R> void launch_sample(const SampleArgs& a, cudaStream_t st);
 bool path_lane_shape(int W, int& PB, size_t& smem, int spline_mode);
 template <class S> void launch_path_lane(const PathArgs& a, int spline_mode, int PB, size_t smem, cudaStream_t st);
 // arc stage (arc_kernel.cu): tables, length, geometry at the gridpoints; paths per CTA (0 = path too long)
-int arc_paths_per_cta(int W, int spline_mode, int real_size, size_t& smem);
+int arc_paths_per_cta(int W, int spline_mode, int real_size, size_t& smem, bool* table_in_smem = nullptr);
 template <class R> void launch_arc(const PathArgs& a, int spline_mode, cudaStream_t st);
 bool path_launch_shape(int W, int spline_mode, int real_size, int& PB, int& threads, bool& table_in_smem, size_t& smem);
 
