@@ -33,8 +33,8 @@ constexpr int kPiecesPerLane = 4, kScanLanes = kSub / kPiecesPerLane;  // 25 lan
 
 __host__ __device__ inline size_t arc_smem_bytes(int W, int deg, int PB, int real_size, bool table_in_smem) {
   const size_t nseg = W - 1;
-  const size_t reals = (size_t)PB * nseg * (2 * (deg + 1) + 2 * deg + 1 + (table_in_smem ? kTable : 0)) + (size_t)PB * 2;
-  return 64 + sizeof(double) * PB * nseg + (reals * real_size + 15) / 16 * 16;
+  const size_t reals = (size_t)PB * nseg * (2 * (deg + 1) + 2 * deg + 2 + (table_in_smem ? kTable : 0));
+  return 64 + sizeof(double) * PB * (nseg + 4) + (reals * real_size + 15) / 16 * 16;
 }
 
 // TS: the CTA's arc-length tables also live in shared memory (the geometry phase reads them from there; the
@@ -50,11 +50,12 @@ __global__ void __launch_bounds__(kArcThreads, 3) arc_kernel(PathArgs g) {
   const int PBa = min(PB, P - p0);
   int* bad = (int*)smem_raw;                         // [PB] (PB <= 16)
   double* segend = (double*)(smem_raw + 64);         // [PB * nseg] cumulative segment ends, FP64 in both modes
-  Carve<R> sm((R*)(smem_raw + 64 + sizeof(double) * (size_t)PB * nseg));
+  double* hqc = segend + (size_t)PB * nseg;          // [PB][4]: c0, c1, c2 of q(s) (gen_vel_prof's Hermite path)
+  Carve<R> sm((R*)(smem_raw + 64 + sizeof(double) * (size_t)PB * (nseg + 4)));
   R* ax = sm.take((size_t)PB * nseg * NC); R* ay = sm.take((size_t)PB * nseg * NC);
   R* hx = sm.take((size_t)PB * nseg * DEG); R* hy = sm.take((size_t)PB * nseg * DEG);
   R* segtot = sm.take((size_t)PB * nseg);
-  R* vse = sm.take((size_t)PB * 2);                  // vel_start, vel_end per path
+  R* invlen = sm.take((size_t)PB * nseg);            // 100 / segment length
   R* stab = TS ? sm.take((size_t)PB * nseg * kTable) : nullptr;
   const int nS = PBa * nseg, nc = nseg * NC, nt = nseg * kTable;
 
@@ -140,11 +141,17 @@ __global__ void __launch_bounds__(kArcThreads, 3) arc_kernel(PathArgs g) {
   if (tid < PBa) {
     const int p = p0 + tid;
     double acc = 0;
-    for (int s = 0; s < nseg; ++s) { acc += (double)segtot[tid * nseg + s]; segend[tid * nseg + s] = acc; }
+    for (int s = 0; s < nseg; ++s) {
+      const R len = segtot[tid * nseg + s];
+      acc += (double)len; segend[tid * nseg + s] = acc; invlen[tid * nseg + s] = (R)kSub / len;
+    }
     const bool ok = !bad[tid] && acc > 0 && isfinite(acc);
     if (!ok) bad[tid] = 1;
-    vse[tid * 2] = g.vel_start ? ((const R*)g.vel_start)[p] : (R)0;
-    vse[tid * 2 + 1] = g.vel_end ? ((const R*)g.vel_end)[p] : (R)0;
+    {
+      HermiteQ<double> hq;
+      hq.init(acc, g.vel_start ? (double)((const R*)g.vel_start)[p] : 0.0, g.vel_end ? (double)((const R*)g.vel_end)[p] : 0.0);
+      hqc[tid * 4] = hq.c0; hqc[tid * 4 + 1] = hq.c1; hqc[tid * 4 + 2] = hq.c2;
+    }
     ((R*)g.L)[p] = ok ? (R)acc : (R)0;
     if (!ok && g.cost) ((R*)g.cost)[p] = 0;
     g.status[p] = ok ? SCB_ST_OK : SCB_ST_ERR_BAD_PATH;
@@ -163,6 +170,7 @@ __global__ void __launch_bounds__(kArcThreads, 3) arc_kernel(PathArgs g) {
     const int G = g.G, N = G - 1;
     const double step = 1.0 / (double)N;
     R* o_px = (R*)g.px; R* o_py = (R*)g.py; R* o_k = (R*)g.kappa;
+    int sg = 0;
     for (int it = tid; it < PBa * G; it += T) {
       const int i = it / PBa, pl = it - i * PBa;
       const size_t oo = (size_t)i * P + p0 + pl;
@@ -171,8 +179,9 @@ __global__ void __launch_bounds__(kArcThreads, 3) arc_kernel(PathArgs g) {
         continue;
       }
       R bx, by, kap;
-      gridpoint_geometry<R, DEG>(i, N, step, segend + pl * nseg, nseg, (double)vse[pl * 2], (double)vse[pl * 2 + 1],
-                                 wtab + (size_t)pl * nt, ax + (size_t)pl * nseg * NC, ay + (size_t)pl * nseg * NC, bx, by, kap);
+      gridpoint_geometry<R, DEG>(i, N, step, segend + pl * nseg, nseg, hqc + pl * 4, invlen + pl * nseg, sg, wtab + (size_t)pl * nt,
+                                 ax + (size_t)pl * nseg * NC, ay + (size_t)pl * nseg * NC, hx + (size_t)pl * nseg * DEG,
+                                 hy + (size_t)pl * nseg * DEG, bx, by, kap);
       if (o_px) o_px[oo] = bx;
       if (o_py) o_py[oo] = by;
       if (o_k) o_k[oo] = kap;

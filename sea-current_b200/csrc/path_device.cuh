@@ -138,23 +138,24 @@ template <class R> __device__ __forceinline__ void lau_node_basis(R* out, int no
 //   segend: cumulative segment ends of this path (FP64); tab: its [nseg][101] cumulative table;
 //   ax, ay: its [nseg][DEG+1] power-basis coefficients.
 template <class R, int DEG>
-__device__ __forceinline__ void gridpoint_geometry(int i, int N, double step, const double* segend, int nseg, double vs, double ve,
-                                                   const R* tab, const R* ax, const R* ay, R& bx, R& by, R& kap) {
+__device__ __forceinline__ void gridpoint_geometry(int i, int N, double step, const double* segend, int nseg, const double* hqc,
+                                                   const R* inv_len, int& sg, const R* tab, const R* ax, const R* ay,
+                                                   const R* hx, const R* hy, R& bx, R& by, R& kap) {
+  // hqc: {c0, c1, c2} of q(s) = c0 s^3 + c1 s^2 + c2 s; inv_len[j] = 100 / length of segment j; sg: the caller's
+  // guess of the segment (its previous gridpoint's), updated
   constexpr int NC = DEG + 1;
-  HermiteQ<double> hq;
   const double Ltot = segend[nseg - 1];
-  hq.init(Ltot, vs, ve);
-  double q = hq.q(i == N ? 1.0 : (double)i * step);
+  const double sq = i == N ? 1.0 : (double)i * step;
+  double q = hqc[0] * (sq * sq * sq) + hqc[1] * (sq * sq) + hqc[2] * sq;
   q = fmin(fmax(q, 0.0), Ltot);
-  int lo = 0, hi = nseg - 1;
-  while (lo < hi) { const int m = (lo + hi) >> 1; if (q <= segend[m]) hi = m; else lo = m + 1; }
-  const int sg = lo;
+  // first j with q <= segend[j]: a thread's gridpoints advance along the path, so walk from the last answer
+  while (sg > 0 && q <= segend[sg - 1]) --sg;
+  while (sg < nseg - 1 && q > segend[sg]) ++sg;
   const R r = (R)(q - (sg > 0 ? segend[sg - 1] : 0.0));
   const R* c = tab + (size_t)sg * kTable;
-  const R seg_len = (R)(segend[sg] - (sg > 0 ? segend[sg - 1] : 0.0));
   // largest kl in [0, 99] with c[kl] <= r: the table is close to linear, so start from the proportional
   // guess and walk (two independent loads, then rarely more) instead of seven dependent bisection loads
-  int kl = (int)((R)kSub * r / seg_len);
+  int kl = (int)(r * inv_len[sg]);
   kl = max(1, min(kSub - 2, kl));
   // four independent loads around the guess decide almost every gridpoint in one memory round trip
   // (the dependent walk that follows was 21 % of this kernel's stall samples, profiles/r1h_arc_kernel_f64.lines.txt)
@@ -173,9 +174,9 @@ __device__ __forceinline__ void gridpoint_geometry(int i, int N, double step, co
   const R h = (R)0.01, a0 = fmin((R)kl * h, (R)1);
   const R target = r - ck, ds = ck1 - ck;
   const R* sax = ax + NC * sg; const R* say = ay + NC * sg;
-  R kx[DEG], ky[DEG];  // B' in power basis: (k+1) a_{k+1}
+  R kx[DEG], ky[DEG];  // B' in power basis (the hodograph coefficients the table was integrated with)
 #pragma unroll
-  for (int j = 0; j < DEG; ++j) { kx[j] = (R)(j + 1) * sax[j + 1]; ky[j] = (R)(j + 1) * say[j + 1]; }
+  for (int j = 0; j < DEG; ++j) { kx[j] = hx[DEG * sg + j]; ky[j] = hy[DEG * sg + j]; }
   auto speed2 = [&](R u) {
     R dx = kx[DEG - 1], dy = ky[DEG - 1];
 #pragma unroll
