@@ -184,7 +184,11 @@ def test_infeasible_and_bad_inputs_verdicts(planners, oracle, lp_mode):
 @pytest.mark.parametrize("lp_mode", [scb.abi.LP_CLOSED_FORM, scb.abi.LP_SEIDEL])
 @pytest.mark.parametrize("mode,W,G,P", [("ref_cubic", 20, 500, 256), ("lau_quintic", 20, 500, 256),
                                         ("lau_quintic", 10, 1000, 256), ("ref_cubic", 2, 2, 33),
-                                        ("lau_quintic", 3, 17, 65), ("ref_cubic", 200, 2001, 16)])
+                                        ("lau_quintic", 3, 17, 65), ("ref_cubic", 200, 2001, 16),
+                                        # more than 32 waypoints: the CTA-team path kernel (shared-memory optimiser)
+                                        ("lau_quintic", 40, 300, 24), ("lau_quintic", 200, 501, 6),
+                                        # 17..32 waypoints: one path per warp in the lane kernel
+                                        ("lau_quintic", 32, 200, 40), ("ref_cubic", 17, 100, 70)])
 def test_batch_matches_oracle_fp64(planners, oracle, mode, W, G, P, lp_mode):
     rng = np.random.default_rng(100 + W + G)
     wx, wy = scb.workloads.random_walk_paths(rng, P, W)
@@ -193,6 +197,28 @@ def test_batch_matches_oracle_fp64(planners, oracle, mode, W, G, P, lp_mode):
     res = pl.plan(wx=wx, wy=wy, G=G, lp_mode=lp_mode, **lim)
     ref, _ = oracle.plan_batch(wx=wx, wy=wy, G=G, spline_mode=0 if mode == "ref_cubic" else 1, **lim)
     _check(res, ref, RTOL64, ("ctrl_x", "ctrl_y", "arclen_total", "arclen_table", "T_total", "cost") + GRID)
+
+
+def test_cta_team_kernel_matches_lane_kernel(oracle, monkeypatch):
+    """SCB_PATH_TEAM=cta forces the CTA-team path kernel on short paths: same control points and cost as the
+    lane-per-waypoint kernel (1e-9: the two evaluate the cost in different polynomial bases) and as the oracle."""
+    rng = np.random.default_rng(5)
+    P, W, G = 96, 10, 64
+    wx, wy = scb.workloads.random_walk_paths(rng, P, W)
+    lim = scb.workloads.random_limits(rng, P, slow_fraction=0.0)
+    out = {}
+    for team in ("lane", "cta"):
+        monkeypatch.setenv("SCB_PATH_TEAM", team)
+        for prec in ("fp64", "fp32"):
+            pl = scb.BatchPlanner(0, prec, "lau_quintic", max_problems=P, max_waypoints=W, max_gridpoints=G)
+            out[team, prec] = pl.plan(wx=wx, wy=wy, G=G, **lim)
+            pl.close()
+    ref, _ = oracle.plan_batch(wx=wx, wy=wy, G=G, spline_mode=1, **lim)
+    for n in ("ctrl_x", "ctrl_y", "cost", "arclen_total"):
+        for team in ("lane", "cta"):
+            assert rel_err(out[team, "fp64"][n], ref[n], floor=float(np.max(np.abs(ref[n])))) <= RTOL64, (team, n)
+        # FP32 mode: the optimiser still runs in FP64 on the float waypoints; both kernels agree to float rounding
+        assert rel_err(out["cta", "fp32"][n], out["lane", "fp32"][n], floor=float(np.max(np.abs(ref[n])))) <= 1e-6, n
 
 
 def test_c3_rollouts_match_oracle(planners, oracle):
