@@ -140,6 +140,13 @@ typedef struct scb_batch_in {
   double x_cap;             /* upper bound of sdot^2 in the backward pass; 0 = reference's 100
                                (tp:algorithm.hpp:152 m_initXBound) */
   double dt;                /* uniform-dt stream period; 0 = reference's 0.02 (sc:1199) */
+  /* Curvature-aware velocity limits (Lau09 III-B "isolated constraints"; the reference's hook for them is the
+   * position-dependent vel_lim_func, sc:1175-1188, examples/test.cpp:194-209).  With kappa_i the curvature at
+   * the arc length of gridpoint i, the velocity box of that gridpoint is intersected with [-c_i, c_i],
+   *   c_i = min(omega_max / |kappa_i|, sqrt(acc_lat_max / |kappa_i|));  0 switches a term off.
+   * Needs SCB_STAGE_SPLINE | SCB_STAGE_TIMING | SCB_STAGE_GEOMETRY in the same call. */
+  double omega_max;         /* |angular velocity| <= omega_max  */
+  double acc_lat_max;       /* centripetal acceleration v^2 |kappa| <= acc_lat_max */
   scb_opt opt;
 } scb_batch_in;
 

@@ -38,6 +38,7 @@ struct PlanIn {
   int G = 101;
   double x_cap = 100.0;
   double dt = (double)0.02f;
+  double omega_max = 0, acc_lat_max = 0;  // curvature-aware velocity caps (0 = off), see scb_batch_in
   int spline_mode = 0;  // 0 REF_CUBIC, 1 LAU_QUINTIC
   LauOpt opt;
   int solve_mode = tp::SOLVE_THOMAS;
@@ -141,6 +142,29 @@ inline PlanOut plan_one(const PlanIn& in) {
   const double *vlg = in.vel_lo_grid, *vhg = in.vel_hi_grid;
   const double vlo = in.vel_lo, vhi = in.vel_hi;
   const tp::Vec& gp = pb.gridpoints;
+  // Curvature-aware limits (Lau09 III-B; the reference's hook is the position-dependent vel_lim_func,
+  // sc:1175-1188): the box of gridpoint i is intersected with [-c_i, c_i],
+  // c_i = min(omega_max / |kappa_i|, sqrt(acc_lat_max / |kappa_i|)), kappa_i = curvature at arc length q(s_i).
+  std::vector<double> cl, ch;
+  if (in.omega_max > 0 || in.acc_lat_max > 0) {
+    cl.resize(G); ch.resize(G);
+    for (int i = 0; i < G; ++i) {
+      const double q = pb.path.eval_single(gp[i], 0)[0];
+      int seg; double u, bx, by, kap;
+      arclen_invert(polys, o.table, seg_end, q, seg, u);
+      curve_at(polys[seg], u, bx, by, kap);
+      double lo = vlg && vhg ? vlg[i] : vlo, hi = vlg && vhg ? vhg[i] : vhi;
+      const double k = std::fabs(kap);
+      if (k > 0) {
+        double c = INFINITY;
+        if (in.omega_max > 0) c = in.omega_max / k;
+        if (in.acc_lat_max > 0) c = std::min(c, std::sqrt(in.acc_lat_max / k));
+        hi = std::min(hi, c); lo = std::max(lo, -c);
+      }
+      cl[i] = lo; ch[i] = hi;
+    }
+    vlg = cl.data(); vhg = ch.data();
+  }
   pb.vel_lim = [&](double s, tp::Vec& lo, tp::Vec& hi) {
     if (vlg && vhg) {
       size_t i = std::lower_bound(gp.begin(), gp.end(), s) - gp.begin();

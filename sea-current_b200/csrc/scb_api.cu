@@ -86,6 +86,10 @@ int validate(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, int
   if ((stages & SCB_STAGE_TIMING) && !((in->vel_lo && in->vel_hi) || (in->vel_lo_grid && in->vel_hi_grid))) return SCB_E_INVALID;
   if ((stages & SCB_STAGE_TIMING) && !(stages & SCB_STAGE_SPLINE) && !in->path_len) return SCB_E_INVALID;
   if ((stages & SCB_STAGE_GEOMETRY) && !(stages & SCB_STAGE_SPLINE)) return SCB_E_INVALID;
+  if (!(in->omega_max >= 0) || !(in->acc_lat_max >= 0)) return SCB_E_INVALID;
+  if ((in->omega_max > 0 || in->acc_lat_max > 0) &&
+      (stages & (SCB_STAGE_SPLINE | SCB_STAGE_TIMING | SCB_STAGE_GEOMETRY)) != (SCB_STAGE_SPLINE | SCB_STAGE_TIMING | SCB_STAGE_GEOMETRY))
+    return SCB_E_INVALID;  // the caps need the curvature at the gridpoints
   if (out->S_cap < 0 || out->S_cap > ctx->cfg.max_samples) return SCB_E_INVALID;
   if ((stages & SCB_STAGE_GEOMETRY) && !(stages & SCB_STAGE_TIMING) && (out->S_cap <= 0 || !out->n_samples || !out->s_pos)) return SCB_E_INVALID;
   if (!out->status) return SCB_E_INVALID;
@@ -115,6 +119,7 @@ int run_device(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, i
   const bool want_stream = out->S_cap > 0 && (out->s_time || out->s_pos || out->s_vel || out->s_acc || out->s_px ||
                                               out->s_py || out->s_omega || out->n_samples);
   void* dKappa = nullptr;
+  const bool curv = in->omega_max > 0 || in->acc_lat_max > 0;  // validate(): needs all three stages
   if (do_spline) {
     const size_t nseg = W - 1;
     // the control points and the arc-length tables are the hand-over between the path kernel and the
@@ -129,7 +134,7 @@ int run_device(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, i
     a.ctrl_x = dCx; a.ctrl_y = dCy; a.table = dTab; a.L = dL; a.cost = out->cost; a.status = out->status;
     if (do_geo && do_timing) {
       a.px = out->px; a.py = out->py;
-      if (out->omega) { if ((rc = ensure(ctx, SL_KAPPA, (size_t)G * P * rs, &dKappa))) return rc; a.kappa = dKappa; }
+      if (out->omega || curv) { if ((rc = ensure(ctx, SL_KAPPA, (size_t)G * P * rs, &dKappa))) return rc; a.kappa = dKappa; }
     }
     a.opt = in->opt;
     launch_path<R>(a, ctx->cfg.spline_mode, st, ctx->ev[7]);
@@ -159,6 +164,7 @@ int run_device(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, i
     t.vel_lo_grid = in->vel_lo_grid; t.vel_hi_grid = in->vel_hi_grid;
     t.acc_lo = in->acc_lo; t.acc_hi = in->acc_hi; t.vel_start = in->vel_start; t.vel_end = in->vel_end;
     t.x_cap = in->x_cap > 0 ? in->x_cap : 100.0;
+    if (curv) { t.kappa = dKappa; t.omega_max = in->omega_max; t.acc_lat_max = in->acc_lat_max; }
     t.K_lo = dKlo; t.K_hi = dKhi; t.x = dX; t.status = out->status; t.fail_stage = dFail;
     if (!f64) { t.K_lo_out = out->K_lo; t.K_hi_out = out->K_hi; }
     if (in->lp_mode == SCB_LP_SEIDEL) launch_toppra<R>(t, st);

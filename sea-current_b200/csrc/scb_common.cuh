@@ -59,6 +59,19 @@ template <> __device__ __forceinline__ double fast_rcp<double>(double x) {
 // sqrt(x) for x >= 0 through fast_rsqrt
 __device__ __forceinline__ double fast_sqrt(double x) { return x > 0 ? x * fast_rsqrt<double>(x) : 0.0; }
 
+// Curvature-aware velocity cap of one gridpoint (scb_batch_in.omega_max / acc_lat_max): intersects [lo, hi] with
+// [-c, c], c = min(omega_max / |kappa|, sqrt(acc_lat_max / |kappa|)).
+__device__ __forceinline__ void curvature_cap(double kappa, double omega_max, double acc_lat_max, double& lo, double& hi) {
+  const double k = fabs(kappa);
+  if (k > 0) {
+    const double rk = fast_rcp<double>(k);
+    double c = CUDART_INF;
+    if (omega_max > 0) c = omega_max * rk;
+    if (acc_lat_max > 0) c = fmin(c, fast_sqrt(acc_lat_max * rk));
+    hi = fmin(hi, c); lo = fmax(lo, -c);
+  }
+}
+
 // Kernel-argument bundles (plain pointers; R-typed buffers passed as void* and cast inside).
 struct PathArgs {
   int P, W, G, PB;                    // PB (paths per CTA) and table_in_smem are filled in by launch_path
@@ -81,6 +94,8 @@ struct ToppraArgs {
   const void *acc_lo, *acc_hi;         // [P]
   const void *vel_start, *vel_end;     // [P] or null
   double x_cap;
+  const void *kappa;                   // S [G][P] or null: curvature at the gridpoints, for the two caps below
+  double omega_max, acc_lat_max;       // scb_batch_in: 0 = off
   void *K_lo, *K_hi;                   // double [G][P], always (internal state; the FP64 outputs themselves)
   void *K_lo_out, *K_hi_out;           // S [G][P] or null: FP32-mode copies for the caller
   void *x;                             // S [G][P]

@@ -84,7 +84,7 @@ constexpr int kTU = 8;  // forward pass: controllable sets of kTU stages are fet
 
 }  // namespace
 
-template <class S, bool GRID>
+template <class S, bool GRID, bool CURV>
 __global__ void __launch_bounds__(64) toppra_fast_kernel(ToppraArgs g) {
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
   if (p >= g.P) return;
@@ -115,6 +115,8 @@ __global__ void __launch_bounds__(64) toppra_fast_kernel(ToppraArgs g) {
   auto qd = [&](double s) { return c0_3 * (s * s) + c1_2 * s + c2; };
   auto qdd = [&](double s) { return c0_6 * s + c1_2; };
   const S* __restrict__ vlg = (const S*)g.vel_lo_grid; const S* __restrict__ vhg = (const S*)g.vel_hi_grid;
+  const S* __restrict__ kap = (const S*)g.kappa;
+  const double om_max = g.omega_max, al_max = g.acc_lat_max;
 
   // ---- backward pass: controllable sets.  The velocity box of every gridpoint is validated on
   // the way (the reference throws before its passes, solver.cpp:26-63: same verdict; gridpoint N
@@ -126,6 +128,7 @@ __global__ void __launch_bounds__(64) toppra_fast_kernel(ToppraArgs g) {
   if (!pre_failed) {
     double lo = vlo, hi = vhi, xl, xh;
     if (GRID) { lo = (double)vlg[o]; hi = (double)vhg[o]; }
+    if (CURV) curvature_cap((double)kap[o], om_max, al_max, lo, hi);
     if (!vel_xbound(an, lo, hi, xl, xh)) status = SCB_ST_ERR_BAD_LIMITS;
   }
   bool alive = status == SCB_ST_OK;
@@ -137,6 +140,7 @@ __global__ void __launch_bounds__(64) toppra_fast_kernel(ToppraArgs g) {
     const double s = (double)i * step, delta = sn - s, twod = 2.0 * delta, a = qd(s), b = qdd(s);
     double lo = vlo, hi = vhi, xlo, xhi;
     if (GRID) { lo = (double)vlg[o]; hi = (double)vhg[o]; }
+    if (CURV) curvature_cap((double)kap[o], om_max, al_max, lo, hi);
     const bool vel_ok = vel_xbound(a, lo, hi, xlo, xhi);
     // rows of the stage (tp:constraint.cpp:100-162): acceleration at s_i and, interpolated, at s_{i+1}
     const Slab s1 = orient(a, b, Al, Ah, nAl, nAh);
@@ -188,6 +192,7 @@ __global__ void __launch_bounds__(64) toppra_fast_kernel(ToppraArgs g) {
           const double an2 = qd(sn2), bn2 = qdd(sn2);
           double lo = vlo, hi = vhi, xlo, xhi;
           if (GRID) { lo = (double)vlg[ox]; hi = (double)vhg[ox]; }
+          if (CURV) curvature_cap((double)kap[ox], om_max, al_max, lo, hi);
           vel_xbound(a, lo, hi, xlo, xhi);  // validated by the backward pass
           const Slab s1 = orient(a, b, Al, Ah, nAl, nAh);
           const Slab s2 = orient(fma(twod, bn2, an2), bn2, Al, Ah, nAl, nAh);
@@ -227,8 +232,11 @@ __global__ void __launch_bounds__(64) toppra_fast_kernel(ToppraArgs g) {
 
 template <class S> void launch_toppra_fast(const ToppraArgs& a, cudaStream_t st) {
   const int block = 64, grid = (a.P + block - 1) / block;
-  if (a.vel_lo_grid && a.vel_hi_grid) toppra_fast_kernel<S, true><<<grid, block, 0, st>>>(a);
-  else toppra_fast_kernel<S, false><<<grid, block, 0, st>>>(a);
+  const bool gl = a.vel_lo_grid && a.vel_hi_grid, cv = a.kappa && (a.omega_max > 0 || a.acc_lat_max > 0);
+  if (gl && cv) toppra_fast_kernel<S, true, true><<<grid, block, 0, st>>>(a);
+  else if (gl) toppra_fast_kernel<S, true, false><<<grid, block, 0, st>>>(a);
+  else if (cv) toppra_fast_kernel<S, false, true><<<grid, block, 0, st>>>(a);
+  else toppra_fast_kernel<S, false, false><<<grid, block, 0, st>>>(a);
 }
 template void launch_toppra_fast<double>(const ToppraArgs&, cudaStream_t);
 template void launch_toppra_fast<float>(const ToppraArgs&, cudaStream_t);

@@ -180,6 +180,8 @@ __global__ void __launch_bounds__(64) toppra_kernel(ToppraArgs g) {
   }
   const S* vlg = (const S*)g.vel_lo_grid; const S* vhg = (const S*)g.vel_hi_grid;
   const bool grid_lim = vlg && vhg;
+  const S* __restrict__ kap = (const S*)g.kappa;
+  const bool curv = kap && (g.omega_max > 0 || g.acc_lat_max > 0);
   const double x_cap = g.x_cap;
 
   // stage rows 2..5 and x box of stage i (rows 0,1 are the x_next coupling, filled per LP)
@@ -196,6 +198,7 @@ __global__ void __launch_bounds__(64) toppra_kernel(ToppraArgs g) {
     A[5][0] = -a2; A[5][1] = -b2; A[5][2] = pk.acc_lo;
     double lo = pk.vlo, hi = pk.vhi;
     if (grid_lim) { lo = (double)vlg[(size_t)i * P + p]; hi = (double)vhg[(size_t)i * P + p]; }
+    if (curv) curvature_cap((double)kap[(size_t)i * P + p], g.omega_max, g.acc_lat_max, lo, hi);
     vel_xbound(a, lo, hi, xlo, xhi);
   };
   auto couple = [&](double (&A)[6][3], double delta, double nlo, double nhi) {
@@ -212,6 +215,7 @@ __global__ void __launch_bounds__(64) toppra_kernel(ToppraArgs g) {
     for (int i = 0; i < G && status == SCB_ST_OK; ++i) {
       double lo = pk.vlo, hi = pk.vhi;
       if (grid_lim) { lo = (double)vlg[(size_t)i * P + p]; hi = (double)vhg[(size_t)i * P + p]; }
+    if (curv) curvature_cap((double)kap[(size_t)i * P + p], g.omega_max, g.acc_lat_max, lo, hi);
       if (!vel_xbound(pk.qd(pk.s_at(i)), lo, hi, xl, xh)) status = SCB_ST_ERR_BAD_LIMITS;
     }
   }

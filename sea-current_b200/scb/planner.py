@@ -100,7 +100,7 @@ class BatchPlanner:
     def plan(self, wx=None, wy=None, vel_lo=None, vel_hi=None, acc_lo=None, acc_hi=None, G=101, start_angle=None,
              vel_lo_grid=None, vel_hi_grid=None, vel_start=None, vel_end=None, path_len=None, stages=0,
              outputs=ALL_OUTPUTS, S_cap=0, x_cap=0.0, dt=0.0, opt=None, out_buffers=None, resample_at=None, lp_mode=0,
-             nudge=False):
+             nudge=False, omega_max=0.0, acc_lat_max=0.0):
         """Host arrays in, host arrays out (scb_plan_batch).  `out_buffers` lets a caller pass
         preallocated (e.g. pinned) numpy arrays keyed by output name."""
         R = self.real
@@ -130,6 +130,7 @@ class BatchPlanner:
         bi.vel_start, bi.vel_end = arr(vel_start, (P,)), arr(vel_end, (P,))
         bi.path_len = arr(path_len, (P,))
         bi.stages, bi.x_cap, bi.dt, bi.lp_mode = stages, x_cap, dt, lp_mode
+        bi.omega_max, bi.acc_lat_max = omega_max, acc_lat_max
         bi.nudge_positions = 1 if nudge else 0
         bi.opt = opt if opt is not None else default_opt()
         res = BatchResult()
@@ -168,7 +169,8 @@ class BatchPlanner:
         return res
 
     # ------------------------------------------------------------------ HBM-resident buffers
-    def make_device_batch(self, inputs, G, outputs=ALL_OUTPUTS, S_cap=0, stages=0, x_cap=0.0, dt=0.0, opt=None, lp_mode=0):
+    def make_device_batch(self, inputs, G, outputs=ALL_OUTPUTS, S_cap=0, stages=0, x_cap=0.0, dt=0.0, opt=None, lp_mode=0,
+                          omega_max=0.0, acc_lat_max=0.0):
         """inputs: dict name -> torch CUDA tensor (dtype = ctx precision, contiguous).  Allocates
         the output tensors once and returns (batch_in, batch_out, result_tensors): the structs can be
         passed to run_device() any number of times without further allocation."""
@@ -189,6 +191,7 @@ class BatchPlanner:
                 assert t.is_cuda and t.dtype == tdt and t.is_contiguous(), name
                 setattr(bi, name, t.data_ptr())
         bi.stages, bi.x_cap, bi.dt, bi.lp_mode = stages, x_cap, dt, lp_mode
+        bi.omega_max, bi.acc_lat_max = omega_max, acc_lat_max
         bi.opt = opt if opt is not None else default_opt()
         res = {"status": torch.empty(P, dtype=torch.int32, device=dev),
                "fail_stage": torch.empty(P, dtype=torch.int32, device=dev)}
