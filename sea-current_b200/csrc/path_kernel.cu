@@ -124,8 +124,8 @@ static bool use_lane_kernel() {  // SCB_PATH_TEAM=cta forces the CTA-team kernel
   return !(e && e[0] == 'c');
 }
 
-// Launch geometry of the path stage: the lane-per-waypoint kernel (threads = 128) for W <= 32, else the
-// CTA-team kernel: PB paths per CTA so that two CTAs fit one SM when possible.  False = the path is too
+// Launch geometry of the path stage: the lane-per-waypoint kernels (threads = 128 as the marker) for W <= 512,
+// else the CTA-team kernel: PB paths per CTA so that two CTAs fit one SM when possible.  False = the path is too
 // long for the CTA kernel or for arc_kernel's shared-memory power bases.  `real_size` is the STORAGE size
 // (arc kernel); the path kernels compute in FP64 in both modes.  The arc-length tables always live in
 // global memory (table_in_smem is kept for the ABI of this helper only).

@@ -39,9 +39,6 @@ constexpr int kLaneWarps = 4;     // warps per CTA
 constexpr int kLaneSlots = 15;    // private FP64 slots per lane in shared memory:
 enum { kSe, kPe, kSwx, kSwy, kPwx, kPwy, kW0x, kW0y, kMag, kBe, kBwx, kBwy, kAlpha, kAnPrev, kApNext };
 
-__device__ __forceinline__ double up1(double v) { return __shfl_up_sync(kAll, v, 1); }
-__device__ __forceinline__ double dn1(double v) { return __shfl_down_sync(kAll, v, 1); }
-__device__ __forceinline__ double from(double v, int src) { return __shfl_sync(kAll, v, src & 31); }
 
 // What one cost node contributes, given B' = (x1, y1) and B'' = (x2, y2) there: the weighted integrand (returned)
 // and, if GRAD, the weighted forces f1 = dJ/dB', f2 = dJ/dB''.
@@ -137,31 +134,125 @@ __device__ __forceinline__ void hodograph_power_T(const double (&g)[5], double (
 
 }  // namespace
 
-template <class S, int DEG>
-__global__ void __launch_bounds__(kLaneWarps * 32, 4) path_lane_kernel(PathArgs g) {
-  extern __shared__ __align__(16) unsigned char lane_smem_raw[];
+
+// ---- how a lane talks to the other lanes of its path -------------------------------------------------
+// WarpComm: the path lives inside one warp (W <= 32, several paths per warp): shuffles only.
+// CtaComm:  one path per CTA (33 <= W <= 512 waypoints, C5's long-horizon paths): neighbours through a
+//           double-buffered exchange area in shared memory, ONE __syncthreads per exchange (a thread can be
+//           at most one exchange ahead of the slowest, and the buffer it then writes is not the one being read).
+struct WarpComm {
+  int base, W;        // first lane and length of this lane's path
+  double* st;         // private slots: st[k * sstride]
+  int sstride;
+  template <int N> __device__ __forceinline__ void prev(const double (&v)[N], double (&pv)[N]) {
+#pragma unroll
+    for (int k = 0; k < N; ++k) pv[k] = __shfl_up_sync(kAll, v[k], 1);
+  }
+  template <int N> __device__ __forceinline__ void next(const double (&v)[N], double (&nx)[N]) {
+#pragma unroll
+    for (int k = 0; k < N; ++k) nx[k] = __shfl_down_sync(kAll, v[k], 1);
+  }
+  template <int N> __device__ __forceinline__ void both(const double (&v)[N], double (&pv)[N], double (&nx)[N]) { prev(v, pv); next(v, nx); }
+  // sum over the path's first n lanes, in lane order (DESIGN.md "New stages", A6: segments in order)
+  __device__ __forceinline__ double path_sum(double v, int n) {
+    double acc = 0;
+    for (int s = 0; s < n; ++s) acc += __shfl_sync(kAll, v, (base + s) & 31);
+    return acc;
+  }
+  __device__ __forceinline__ void path_max2(double& a, double& b) {
+    double ma = 0, mb = 0;
+    for (int k = 0; k < W; ++k) { ma = fmax(ma, __shfl_sync(kAll, a, (base + k) & 31)); mb = fmax(mb, __shfl_sync(kAll, b, (base + k) & 31)); }
+    a = ma; b = mb;
+  }
+  __device__ __forceinline__ bool path_any(bool f) {
+    const unsigned m = __ballot_sync(kAll, f);
+    const unsigned pm = (W >= 32 ? kAll : ((1u << W) - 1u)) << (base & 31);
+    return (m & pm) != 0;
+  }
+};
+
+struct CtaComm {
+  static constexpr int kMaxVals = 6;
+  int T, tid;          // threads of the CTA (a multiple of 32), this thread
+  double* xbuf;        // [2][kMaxVals][T] exchange area
+  double* red;         // [2][2][32] per-warp partials
+  double* st;          // private slots: st[k * sstride]
+  int sstride;
+  int flip = 0, rflip = 0;
+  template <int N> __device__ __forceinline__ double* stage(const double (&v)[N]) {
+    static_assert(N <= kMaxVals, "exchange area too small");
+    double* b = xbuf + (size_t)flip * kMaxVals * T;
+    flip ^= 1;
+#pragma unroll
+    for (int k = 0; k < N; ++k) b[k * T + tid] = v[k];
+    __syncthreads();
+    return b;
+  }
+  template <int N> __device__ __forceinline__ void prev(const double (&v)[N], double (&pv)[N]) {
+    const double* b = stage(v);
+    const int j = max(tid - 1, 0);
+#pragma unroll
+    for (int k = 0; k < N; ++k) pv[k] = b[k * T + j];
+  }
+  template <int N> __device__ __forceinline__ void next(const double (&v)[N], double (&nx)[N]) {
+    const double* b = stage(v);
+    const int j = min(tid + 1, T - 1);
+#pragma unroll
+    for (int k = 0; k < N; ++k) nx[k] = b[k * T + j];
+  }
+  template <int N> __device__ __forceinline__ void both(const double (&v)[N], double (&pv)[N], double (&nx)[N]) {
+    const double* b = stage(v);
+    const int jm = max(tid - 1, 0), jp = min(tid + 1, T - 1);
+#pragma unroll
+    for (int k = 0; k < N; ++k) { pv[k] = b[k * T + jm]; nx[k] = b[k * T + jp]; }
+  }
+  // deterministic tree sum: xor butterfly inside each warp, warp partials added in warp order by every thread
+  __device__ __forceinline__ double path_sum(double v, int n) {
+    if (tid >= n) v = 0;
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(kAll, v, off);
+    double* r = red + (size_t)rflip * 64; rflip ^= 1;
+    if ((tid & 31) == 0) r[tid >> 5] = v;
+    __syncthreads();
+    double acc = 0;
+    for (int w = 0; w < (T >> 5); ++w) acc += r[w];
+    return acc;
+  }
+  __device__ __forceinline__ void path_max2(double& a, double& b) {
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) { a = fmax(a, __shfl_xor_sync(kAll, a, off)); b = fmax(b, __shfl_xor_sync(kAll, b, off)); }
+    double* r = red + (size_t)rflip * 64; rflip ^= 1;
+    if ((tid & 31) == 0) { r[tid >> 5] = a; r[32 + (tid >> 5)] = b; }
+    __syncthreads();
+    double ma = 0, mb = 0;
+    for (int w = 0; w < (T >> 5); ++w) { ma = fmax(ma, r[w]); mb = fmax(mb, r[32 + w]); }
+    a = ma; b = mb;
+  }
+  __device__ __forceinline__ bool path_any(bool f) { return __syncthreads_or(f ? 1 : 0) != 0; }
+};
+
+// One waypoint lane from the waypoints to the control points of its segment.  p: problem, i: waypoint index,
+// own: the lane has a waypoint.  Every lane of the warp / CTA runs this to the end (collectives inside).
+template <class S, int DEG, class Comm>
+__device__ __forceinline__ void lane_path(const PathArgs& g, Comm& cm, int p, int i, bool own) {
   constexpr int NC = DEG + 1;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int W = g.W, nseg = W - 1, PB = g.PB, P = g.P;
-  const int team = blockIdx.x * kLaneWarps + warp;
-  const int p0 = team * PB;
-  if (p0 >= P) return;  // the whole warp leaves together
-  const int pl = lane / W, i = lane - pl * W;
-  const int p = p0 + pl, base = pl * W;
-  const bool own = pl < PB && p < P;
+  const int W = g.W, nseg = W - 1, ss = cm.sstride;
+  double* st = cm.st;
   const bool first = i == 0, last = i == nseg;
   const bool seg = own && !last;          // this lane also owns segment i
   const bool inner = own && !first && !last;
 
-  // ---- waypoints in (a warp's slice of [P][W] is contiguous), neighbours, validation
-  double wx = own ? (double)((const S*)g.wx)[(size_t)p * W + i] : (double)lane;
+  // ---- waypoints in (consecutive lanes read consecutive addresses), neighbours, validation
+  double wx = own ? (double)((const S*)g.wx)[(size_t)p * W + i] : (double)i;
   double wy = own ? (double)((const S*)g.wy)[(size_t)p * W + i] : 0.0;
-  const double xm = up1(wx), ym = up1(wy), xp = dn1(wx), yp = dn1(wy);
+  double xm, ym, xp, yp;
+  {
+    const double v[2] = {wx, wy}; double a[2], b[2];
+    cm.both(v, a, b);
+    xm = a[0]; ym = a[1]; xp = b[0]; yp = b[1];
+  }
   const double dprev = dist2<double>(xm, ym, wx, wy), dnext = dist2<double>(wx, wy, xp, yp);
-  const bool lane_bad = own && (!isfinite(wx) || !isfinite(wy) || (seg && !(dnext > 0)));
-  const unsigned bad_mask = __ballot_sync(kAll, lane_bad);
-  const unsigned path_mask = (W >= 32 ? kAll : ((1u << W) - 1u)) << (base & 31);
-  const bool bad = (bad_mask & path_mask) != 0;
+  const bool bad = cm.path_any(own && (!isfinite(wx) || !isfinite(wy) || (seg && !(dnext > 0))));
 
   // ---- tangents (sc:343-377, 606-638)
   double btx, bty;
@@ -177,37 +268,51 @@ __global__ void __launch_bounds__(kLaneWarps * 32, 4) path_lane_kernel(PathArgs 
     calc_tangent<double>(xm, ym, wx, wy, xp, yp, btx, bty);
   }
 
+  // T and A of this waypoint and the next one: what both the optimiser and the final control points need
+  double alpha = 0;
+  auto waypoint_TA = [&](double e, double& Tx, double& Ty, double& Txp, double& Typ, double& wxp, double& wyp,
+                         double& Ax, double& Ay, double& Axp, double& Ayp) {
+    Tx = e * btx; Ty = e * bty;
+    const double v[4] = {Tx, Ty, wx, wy}; double pv[4], nx[4];
+    cm.both(v, pv, nx);
+    Txp = nx[0]; Typ = nx[1]; wxp = nx[2]; wyp = nx[3];
+    const double pvx = 6.0 * (pv[2] - wx) + 4.0 * Tx + 2.0 * pv[0], pvy = 6.0 * (pv[3] - wy) + 4.0 * Ty + 2.0 * pv[1];
+    const double nxx = 6.0 * (wxp - wx) - 4.0 * Tx - 2.0 * Txp, nxy = 6.0 * (wyp - wy) - 4.0 * Ty - 2.0 * Typ;
+    Ax = first ? nxx : (last ? pvx : alpha * pvx + (1.0 - alpha) * nxx);
+    Ay = first ? nxy : (last ? pvy : alpha * pvy + (1.0 - alpha) * nxy);
+    const double a2[2] = {Ax, Ay}; double an2[2];
+    cm.next(a2, an2);
+    Axp = an2[0]; Ayp = an2[1];
+  };
+
   double cost = 0;
   double e = 1.0;
   if constexpr (DEG == 5) {
     // ================= Lau09 quintic builder (A5), cost + gradient (A6), iRPROP- (A7) =================
-    double* st = (double*)lane_smem_raw + (size_t)warp * kLaneSlots * 32 + lane;  // st[k * 32]: private slot k
     const scb_opt& o = g.opt;
     const double lambda = o.lambda;
+    double an_prev, ap_next;
     {
       const double mag = sqrt(btx * btx + bty * bty);
-      const double alpha = inner ? dnext / (dprev + dnext) : 0.0;
+      alpha = inner ? dnext / (dprev + dnext) : 0.0;
       // weights of the "previous" / "next" cubic in A_i (one-sided at the ends)
       const double ap = first ? 0.0 : (last ? 1.0 : alpha), an = last ? 0.0 : (first ? 1.0 : 1.0 - alpha);
-      st[kSe * 32] = o.step_e; st[kPe * 32] = 0;
-      st[kSwx * 32] = o.step_w * mag; st[kSwy * 32] = o.step_w * mag; st[kPwx * 32] = 0; st[kPwy * 32] = 0;
-      st[kW0x * 32] = wx; st[kW0y * 32] = wy; st[kMag * 32] = mag;
-      st[kBe * 32] = o.e_init; st[kBwx * 32] = wx; st[kBwy * 32] = wy;
-      st[kAlpha * 32] = alpha; st[kAnPrev * 32] = up1(an); st[kApNext * 32] = dn1(ap);
+      st[kSe * ss] = o.step_e; st[kPe * ss] = 0;
+      st[kSwx * ss] = o.step_w * mag; st[kSwy * ss] = o.step_w * mag; st[kPwx * ss] = 0; st[kPwy * ss] = 0;
+      st[kW0x * ss] = wx; st[kW0y * ss] = wy; st[kMag * ss] = mag;
+      st[kBe * ss] = o.e_init; st[kBwx * ss] = wx; st[kBwy * ss] = wy;
+      const double v[2] = {ap, an}; double pv[2], nx[2];
+      cm.both(v, pv, nx);
+      an_prev = pv[1]; ap_next = nx[0];
+      st[kAlpha * ss] = alpha; st[kAnPrev * ss] = an_prev; st[kApNext * ss] = ap_next;
       e = o.e_init;
     }
     const int K = o.iters;
     for (int iter = 0; iter <= K; ++iter) {
       // ---- A5: T, A per waypoint; hodograph control points D of the lane's segment
-      const double alpha = st[kAlpha * 32];
-      const double Tx = e * btx, Ty = e * bty;
-      const double Txm = up1(Tx), Tym = up1(Ty), Txp = dn1(Tx), Typ = dn1(Ty);
-      const double wxm = up1(wx), wym = up1(wy), wxp = dn1(wx), wyp = dn1(wy);
-      const double pvx = 6.0 * (wxm - wx) + 4.0 * Tx + 2.0 * Txm, pvy = 6.0 * (wym - wy) + 4.0 * Ty + 2.0 * Tym;
-      const double nxx = 6.0 * (wxp - wx) - 4.0 * Tx - 2.0 * Txp, nxy = 6.0 * (wyp - wy) - 4.0 * Ty - 2.0 * Typ;
-      const double Ax = first ? nxx : (last ? pvx : alpha * pvx + (1.0 - alpha) * nxx);
-      const double Ay = first ? nxy : (last ? pvy : alpha * pvy + (1.0 - alpha) * nxy);
-      const double Axp = dn1(Ax), Ayp = dn1(Ay);
+      alpha = st[kAlpha * ss];
+      double Tx, Ty, Txp, Typ, wxp, wyp, Ax, Ay, Axp, Ayp;
+      waypoint_TA(e, Tx, Ty, Txp, Typ, wxp, wyp, Ax, Ay, Axp, Ayp);
       double cx[5], cy[5];
       hodograph_power(Tx, fma(0.25, Ax, Tx), fma(0.25, Axp - Ax, fma(5.0, wxp - wx, -2.0 * (Tx + Txp))), fma(-0.25, Axp, Txp), Txp, cx);
       hodograph_power(Ty, fma(0.25, Ay, Ty), fma(0.25, Ayp - Ay, fma(5.0, wyp - wy, -2.0 * (Ty + Typ))), fma(-0.25, Ayp, Typ), Typ, cy);
@@ -216,11 +321,9 @@ __global__ void __launch_bounds__(kLaneWarps * 32, 4) path_lane_kernel(PathArgs 
       if (iter < K) Js = segment_cost<true>(cx, cy, lambda, gcx, gcy);
       else Js = segment_cost<false>(cx, cy, lambda, gcx, gcy);
       if (!seg) Js = 0;
-      // J of the path: segments in order (DESIGN.md "New stages", A6)
-      double J = 0;
-      for (int s = 0; s < nseg; ++s) J += from(Js, base + s);
+      const double J = cm.path_sum(Js, nseg);
       const bool better = iter == 0 || J < cost;
-      if (better) { cost = J; st[kBe * 32] = e; st[kBwx * 32] = wx; st[kBwy * 32] = wy; }
+      if (better) { cost = J; st[kBe * ss] = e; st[kBwx * ss] = wx; st[kBwy * ss] = wy; }
       if (iter == K) break;
       // ---- chain rule: D -> (T, A, W) of the segment's two waypoints, then A -> (T, W) of the neighbours
       double gdx[5], gdy[5];
@@ -230,74 +333,72 @@ __global__ void __launch_bounds__(kLaneWarps * 32, 4) path_lane_kernel(PathArgs 
         for (int m = 0; m < 5; ++m) { gdx[m] = 0; gdy[m] = 0; }
       }
       // end side of the segment (waypoint i+1) is picked up by the next lane
-      const double eTx = up1(gdx[3] + gdx[4] - 2.0 * gdx[2]), eTy = up1(gdy[3] + gdy[4] - 2.0 * gdy[2]);
-      const double eAx = up1(0.25 * (gdx[2] - gdx[3])), eAy = up1(0.25 * (gdy[2] - gdy[3]));
-      const double eWx = up1(5.0 * gdx[2]), eWy = up1(5.0 * gdy[2]);
+      double ein[6];
+      {
+        const double eout[6] = {gdx[3] + gdx[4] - 2.0 * gdx[2], gdy[3] + gdy[4] - 2.0 * gdy[2], 0.25 * (gdx[2] - gdx[3]),
+                                0.25 * (gdy[2] - gdy[3]), 5.0 * gdx[2], 5.0 * gdy[2]};
+        cm.prev(eout, ein);
+      }
       double gTx = gdx[0] + gdx[1] - 2.0 * gdx[2], gTy = gdy[0] + gdy[1] - 2.0 * gdy[2];
       double gAx = 0.25 * (gdx[1] - gdx[2]), gAy = 0.25 * (gdy[1] - gdy[2]);
       double gWx = -5.0 * gdx[2], gWy = -5.0 * gdy[2];
-      if (!first) { gTx += eTx; gTy += eTy; gAx += eAx; gAy += eAy; gWx += eWx; gWy += eWy; }
+      if (!first) { gTx += ein[0]; gTy += ein[1]; gAx += ein[2]; gAy += ein[3]; gWx += ein[4]; gWy += ein[5]; }
       {
         const double ap = first ? 0.0 : (last ? 1.0 : alpha), an = last ? 0.0 : (first ? 1.0 : 1.0 - alpha);
-        const double gAxm = up1(gAx), gAym = up1(gAy), gAxp = dn1(gAx), gAyp = dn1(gAy);
+        const double v[2] = {gAx, gAy}; double gm[2], gp[2];
+        cm.both(v, gm, gp);
         const double k6 = 6.0 * (ap + an), k4 = 4.0 * (ap - an);
         gWx = fma(-k6, gAx, gWx); gWy = fma(-k6, gAy, gWy); gTx = fma(k4, gAx, gTx); gTy = fma(k4, gAy, gTy);
         if (!first) {  // waypoint i is the "next" of i-1
-          const double a = st[kAnPrev * 32];
-          gWx = fma(6.0 * a, gAxm, gWx); gWy = fma(6.0 * a, gAym, gWy); gTx = fma(-2.0 * a, gAxm, gTx); gTy = fma(-2.0 * a, gAym, gTy);
+          const double a = st[kAnPrev * ss];
+          gWx = fma(6.0 * a, gm[0], gWx); gWy = fma(6.0 * a, gm[1], gWy); gTx = fma(-2.0 * a, gm[0], gTx); gTy = fma(-2.0 * a, gm[1], gTy);
         }
         if (!last) {   // waypoint i is the "previous" of i+1
-          const double a = st[kApNext * 32];
-          gWx = fma(6.0 * a, gAxp, gWx); gWy = fma(6.0 * a, gAyp, gWy); gTx = fma(2.0 * a, gAxp, gTx); gTy = fma(2.0 * a, gAyp, gTy);
+          const double a = st[kApNext * ss];
+          gWx = fma(6.0 * a, gp[0], gWx); gWy = fma(6.0 * a, gp[1], gWy); gTx = fma(2.0 * a, gp[0], gTx); gTy = fma(2.0 * a, gp[1], gTy);
         }
       }
       const double ge = gTx * btx + gTy * bty;
       // largest gradient component of each class over the path (components below 1e-9 of it count as zero)
-      double gemax = 0, gwmax = 0;
-      {
-        const double mine = own ? fabs(ge) : 0.0, minw = inner ? fmax(fabs(gWx), fabs(gWy)) : 0.0;
-        for (int k = 0; k < W; ++k) { gemax = fmax(gemax, from(mine, base + k)); gwmax = fmax(gwmax, from(minw, base + k)); }
-      }
+      double gemax = own ? fabs(ge) : 0.0, gwmax = inner ? fmax(fabs(gWx), fabs(gWy)) : 0.0;
+      cm.path_max2(gemax, gwmax);
       // ---- A7: iRPROP-
       {
         const double te = 1e-9 * gemax, tw = 1e-9 * gwmax;
-        double se = st[kSe * 32], pe = st[kPe * 32];
+        double se = st[kSe * ss], pe = st[kPe * ss];
         const double gi = fabs(ge) <= te ? 0.0 : ge;
         const double ei = e + rprop_step<double>(gi, pe, se, 1e-6, 1.0);
         e = fmin((double)o.e_max, fmax((double)o.e_min, ei));
-        st[kSe * 32] = se; st[kPe * 32] = pe;
+        st[kSe * ss] = se; st[kPe * ss] = pe;
         if (o.move_waypoints && inner) {
-          const double mag = st[kMag * 32], w0x = st[kW0x * 32], w0y = st[kW0y * 32];
-          double swx = st[kSwx * 32], swy = st[kSwy * 32], pwx = st[kPwx * 32], pwy = st[kPwy * 32];
+          const double mag = st[kMag * ss], w0x = st[kW0x * ss], w0y = st[kW0y * ss];
+          double swx = st[kSwx * ss], swy = st[kSwy * ss], pwx = st[kPwx * ss], pwy = st[kPwy * ss];
           const double gvx = fabs(gWx) <= tw ? 0.0 : gWx, gvy = fabs(gWy) <= tw ? 0.0 : gWy;
           const double smin = 1e-6 * mag, smax = 0.5 * mag, rr = o.w_radius;
           const double nx = wx + rprop_step<double>(gvx, pwx, swx, smin, smax);
           const double ny = wy + rprop_step<double>(gvy, pwy, swy, smin, smax);
           wx = fmin(w0x + rr, fmax(w0x - rr, nx));
           wy = fmin(w0y + rr, fmax(w0y - rr, ny));
-          st[kSwx * 32] = swx; st[kSwy * 32] = swy; st[kPwx * 32] = pwx; st[kPwy * 32] = pwy;
+          st[kSwx * ss] = swx; st[kSwy * ss] = swy; st[kPwx * ss] = pwx; st[kPwy * ss] = pwy;
         }
       }
     }
-    e = st[kBe * 32]; wx = st[kBwx * 32]; wy = st[kBwy * 32];
+    e = st[kBe * ss]; wx = st[kBwx * ss]; wy = st[kBwy * ss];
+    alpha = st[kAlpha * ss];
   }
 
   // ---- control points of the lane's segment (the frozen construction), cost and the path verdict -> global
   {
-    const double Tx = e * btx, Ty = e * bty;
-    const double Txp = dn1(Tx), Typ = dn1(Ty), wxp = dn1(wx), wyp = dn1(wy);
     double ox[NC], oy[NC];
     if constexpr (DEG == 3) {  // sc:661-681
+      const double Tx = e * btx, Ty = e * bty;
+      const double v[4] = {Tx, Ty, wx, wy}; double nx[4];
+      cm.next(v, nx);
       ox[0] = wx; oy[0] = wy; ox[1] = wx + Tx; oy[1] = wy + Ty;
-      ox[2] = wxp - Txp; oy[2] = wyp - Typ; ox[3] = wxp; oy[3] = wyp;
+      ox[2] = nx[2] - nx[0]; oy[2] = nx[3] - nx[1]; ox[3] = nx[2]; oy[3] = nx[3];
     } else {
-      const double alpha = ((double*)lane_smem_raw + (size_t)warp * kLaneSlots * 32 + lane)[kAlpha * 32];
-      const double Txm = up1(Tx), Tym = up1(Ty), wxm = up1(wx), wym = up1(wy);
-      const double pvx = 6.0 * (wxm - wx) + 4.0 * Tx + 2.0 * Txm, pvy = 6.0 * (wym - wy) + 4.0 * Ty + 2.0 * Tym;
-      const double nxx = 6.0 * (wxp - wx) - 4.0 * Tx - 2.0 * Txp, nxy = 6.0 * (wyp - wy) - 4.0 * Ty - 2.0 * Typ;
-      const double Ax = first ? nxx : (last ? pvx : alpha * pvx + (1.0 - alpha) * nxx);
-      const double Ay = first ? nxy : (last ? pvy : alpha * pvy + (1.0 - alpha) * nxy);
-      const double Axp = dn1(Ax), Ayp = dn1(Ay);
+      double Tx, Ty, Txp, Typ, wxp, wyp, Ax, Ay, Axp, Ayp;
+      waypoint_TA(e, Tx, Ty, Txp, Typ, wxp, wyp, Ax, Ay, Axp, Ayp);
       const double fifth = 1.0 / 5.0, twentieth = 1.0 / 20.0;
       const double p1x = wx + fifth * Tx, p1y = wy + fifth * Ty, p4x = wxp - fifth * Txp, p4y = wyp - fifth * Typ;
       ox[0] = wx; oy[0] = wy; ox[1] = p1x; oy[1] = p1y;
@@ -317,19 +418,64 @@ __global__ void __launch_bounds__(kLaneWarps * 32, 4) path_lane_kernel(PathArgs 
   }
 }
 
+// W <= 32: a warp owns PB = floor(32 / W) consecutive paths
+template <class S, int DEG>
+__global__ void __launch_bounds__(kLaneWarps * 32, 4) path_lane_kernel(PathArgs g) {
+  extern __shared__ __align__(16) unsigned char lane_smem_raw[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int W = g.W, PB = g.PB, P = g.P;
+  const int p0 = (blockIdx.x * kLaneWarps + warp) * PB;
+  if (p0 >= P) return;  // the whole warp leaves together
+  const int pl = lane / W, i = lane - pl * W, p = p0 + pl;
+  WarpComm cm;
+  cm.base = pl * W; cm.W = W; cm.sstride = 32;
+  cm.st = (double*)lane_smem_raw + (size_t)warp * kLaneSlots * 32 + lane;
+  lane_path<S, DEG, WarpComm>(g, cm, p, i, pl < PB && p < P);
+}
+
+// 33 <= W <= 512: one path per CTA of ceil(W / 32) warps (128 registers per thread: 512 threads at most)
+template <class S, int DEG>
+__global__ void __launch_bounds__(512, 1) path_lane_cta_kernel(PathArgs g) {
+  extern __shared__ __align__(16) unsigned char lane_smem_raw[];
+  const int T = blockDim.x, tid = threadIdx.x;
+  CtaComm cm;
+  cm.T = T; cm.tid = tid; cm.sstride = T;
+  cm.xbuf = (double*)lane_smem_raw;
+  cm.red = cm.xbuf + (size_t)2 * CtaComm::kMaxVals * T;
+  cm.st = cm.red + 128 + tid;
+  lane_path<S, DEG, CtaComm>(g, cm, blockIdx.x, tid, tid < g.W);
+}
+
 bool path_lane_shape(int W, int& PB, size_t& smem, int spline_mode) {
-  if (W < 2 || W > 32) return false;
-  PB = 32 / W;
-  smem = spline_mode == SCB_REF_CUBIC ? 0 : (size_t)kLaneWarps * kLaneSlots * 32 * sizeof(double);
+  if (W < 2 || W > 512) return false;
+  if (W <= 32) {
+    PB = 32 / W;
+    smem = spline_mode == SCB_REF_CUBIC ? 0 : (size_t)kLaneWarps * kLaneSlots * 32 * sizeof(double);
+  } else {
+    PB = 1;
+    const size_t T = (size_t)(W + 31) / 32 * 32;
+    smem = ((size_t)2 * CtaComm::kMaxVals * T + 128 + (size_t)kLaneSlots * T) * sizeof(double);
+  }
   return true;
 }
 
 template <class S> void launch_path_lane(const PathArgs& a0, int spline_mode, int PB, size_t smem, cudaStream_t st) {
   PathArgs a = a0;
   a.PB = PB; a.table_in_smem = 0;
-  const int per_cta = PB * kLaneWarps, grid = (a.P + per_cta - 1) / per_cta;
-  if (spline_mode == SCB_REF_CUBIC) path_lane_kernel<S, 3><<<grid, kLaneWarps * 32, smem, st>>>(a);
-  else path_lane_kernel<S, 5><<<grid, kLaneWarps * 32, smem, st>>>(a);
+  if (a.W <= 32) {
+    const int per_cta = PB * kLaneWarps, grid = (a.P + per_cta - 1) / per_cta;
+    if (spline_mode == SCB_REF_CUBIC) path_lane_kernel<S, 3><<<grid, kLaneWarps * 32, smem, st>>>(a);
+    else path_lane_kernel<S, 5><<<grid, kLaneWarps * 32, smem, st>>>(a);
+  } else {
+    const int T = (a.W + 31) / 32 * 32;
+    if (spline_mode == SCB_REF_CUBIC) {
+      cudaFuncSetAttribute(path_lane_cta_kernel<S, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      path_lane_cta_kernel<S, 3><<<a.P, T, smem, st>>>(a);
+    } else {
+      cudaFuncSetAttribute(path_lane_cta_kernel<S, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      path_lane_cta_kernel<S, 5><<<a.P, T, smem, st>>>(a);
+    }
+  }
 }
 template void launch_path_lane<double>(const PathArgs&, int, int, size_t, cudaStream_t);
 template void launch_path_lane<float>(const PathArgs&, int, int, size_t, cudaStream_t);

@@ -199,11 +199,13 @@ def test_batch_matches_oracle_fp64(planners, oracle, mode, W, G, P, lp_mode):
     _check(res, ref, RTOL64, ("ctrl_x", "ctrl_y", "arclen_total", "arclen_table", "T_total", "cost") + GRID)
 
 
-def test_cta_team_kernel_matches_lane_kernel(oracle, monkeypatch):
-    """SCB_PATH_TEAM=cta forces the CTA-team path kernel on short paths: same control points and cost as the
-    lane-per-waypoint kernel (1e-9: the two evaluate the cost in different polynomial bases) and as the oracle."""
+@pytest.mark.parametrize("W", [10, 40])
+def test_cta_team_kernel_matches_lane_kernel(oracle, monkeypatch, W):
+    """SCB_PATH_TEAM=cta forces the CTA-team path kernel (shared-memory phases, Bernstein-form cost): same control
+    points and cost as the lane-per-waypoint kernels (W = 10: paths inside a warp; W = 40: one path per CTA, neighbours
+    through shared memory) to 1e-9 -- they evaluate the cost in different polynomial bases -- and as the oracle."""
     rng = np.random.default_rng(5)
-    P, W, G = 96, 10, 64
+    P, G = 96, 64
     wx, wy = scb.workloads.random_walk_paths(rng, P, W)
     lim = scb.workloads.random_limits(rng, P, slow_fraction=0.0)
     out = {}
