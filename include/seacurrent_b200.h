@@ -132,11 +132,16 @@ typedef struct scb_batch_in {
   const void* vel_start;    /* real [P] or NULL (= 0): q'(0) of the Hermite path (sc:1213-1222) */
   const void* vel_end;      /* real [P] or NULL (= 0) */
   const void* path_len;     /* real [P]: pos_end - pos_start, read only when SCB_STAGE_SPLINE is off */
+  const void* obstacle_edges; /* real [n_obstacle_edges][4] = (x0, y0, x1, y1) or NULL: the obstacle.lines of the
+                               planning_space (sc:193-284, 298-319), obstacle after obstacle, shared by every problem
+                               of the batch.  from_path cuts every tangent back where W -> W +- T crosses an edge
+                               (shrink_tangent, sc:575-596).  SCB_REF_CUBIC only: the convex-hull argument behind
+                               the clipping is the cubic's. */
   int32_t stages;           /* SCB_STAGE_* bitmask; 0 = all */
   int32_t lp_mode;          /* SCB_LP_*: how the stage LPs of toppra are solved; 0 = default */
   int32_t nudge_positions;  /* geometry-only calls: 1 = repair the caller's s_pos in place before resampling
                                (ends pinned to 0 / L, non-monotone entries averaged, clamp; sc:902-912) */
-  int32_t reserved0;
+  int32_t n_obstacle_edges; /* 0 = no obstacles */
   double x_cap;             /* upper bound of sdot^2 in the backward pass; 0 = reference's 100
                                (tp:algorithm.hpp:152 m_initXBound) */
   double dt;                /* uniform-dt stream period; 0 = reference's 0.02 (sc:1199) */

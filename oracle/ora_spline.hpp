@@ -193,6 +193,39 @@ inline void eval_curve(const std::vector<V2<R>>& ctrl, const std::vector<R>& pos
   }
 }
 
+// ---------------------------------------------------------------- N3: tangent clipping against obstacle edges
+// One obstacle edge (x0, y0) -> (x1, y1).  The reference keeps them as obstacle.lines of every obstacle of the
+// planning_space (sc:193-284); shrink_tangent visits obstacles and their lines in order (sc:580-581), which is the
+// order of this flat list.
+template <class R> struct Edge { V2<R> a, b; };
+
+// sc:137-178: intersection of segment l = (l0, l1) with segment k = (k0, k1); collinear and parallel cases are
+// "no intersection" exactly as in the reference.
+template <class R> inline bool seg_intersects(V2<R> l0, V2<R> l1, V2<R> k0, V2<R> k1, V2<R>& pt) {
+  auto cross = [](V2<R> u, V2<R> v) { return u.x * v.y - u.y * v.x; };  // sc:137-139
+  const R a = cross(k0 - l0, l1 - l0);
+  const R b = cross(l1 - l0, k1 - k0);
+  if (b == 0) return false;  // sc:145-162: a == 0 (collinear) and a != 0 (parallel) both return false
+  const R u = a / b;
+  const R c = cross(k0 - l0, k1 - k0);
+  const R t = c / b;         // sc:166-169: d = b
+  if (0 <= u && u <= 1 && 0 <= t && t <= 1) { pt = t * (l1 - l0) + l0; return true; }
+  return false;
+}
+
+// sc:575-596 with k = 1 (sc:612): the tangent is cut back, edge after edge, where the segments W -> W + T or
+// W -> W - T cross an edge, so that both control points W + T (this segment) and W - T (the previous one) stay on
+// W's side of every edge.
+template <class R> inline V2<R> shrink_tangent(V2<R> T, V2<R> Wp, const std::vector<Edge<R>>& edges) {
+  V2<R> ret = T;
+  for (const Edge<R>& e : edges) {
+    V2<R> pt;
+    if (seg_intersects(Wp + ret, Wp, e.a, e.b, pt)) ret = pt - Wp;
+    if (seg_intersects(Wp - ret, Wp, e.a, e.b, pt)) ret = Wp - pt;
+  }
+  return ret;
+}
+
 // ---------------------------------------------------------------- A2: from_path
 // sc:599-683 (obstacle list empty => shrink_tangent, sc:575-596, returns k*T with k = 1).
 // `preview` reproduces the 10,001-point dense sampling of every segment (sc:679, 750-763)
@@ -201,7 +234,7 @@ inline void eval_curve(const std::vector<V2<R>>& ctrl, const std::vector<R>& pos
 template <class R>
 inline Spline<R> from_path(const std::vector<V2<R>>& path, R start_angle, bool preview = false,
                            int eval_mode = EVAL_BF, std::vector<V2<R>>* preview_pts = nullptr,
-                           std::vector<V2<R>>* tangents_out = nullptr) {
+                           std::vector<V2<R>>* tangents_out = nullptr, const std::vector<Edge<R>>* edges = nullptr) {
   if (path.size() < 2) throw std::invalid_argument("Not enough points for a path");
   const size_t W = path.size();
   std::vector<V2<R>> tang; tang.reserve(W);
@@ -213,6 +246,8 @@ inline Spline<R> from_path(const std::vector<V2<R>>& path, R start_angle, bool p
   V2<R> Te = calc_end_tangent(path[W - 2], path[W - 1]);
   for (size_t i = 1; i + 1 < W; ++i) tang.push_back(calc_tangent(path[i - 1], path[i], path[i + 1]));
   tang.push_back(Te);
+  if (edges && !edges->empty())  // sc:615, 620, 637
+    for (size_t i = 0; i < W; ++i) tang[i] = shrink_tangent(tang[i], path[i], *edges);
   Spline<R> sp;
   sp.ctrl.resize(W - 1);
   for (size_t i = 0; i + 1 < W; ++i)
