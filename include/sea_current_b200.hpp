@@ -128,7 +128,27 @@ struct bounding_rect {  // sc:61-84
   float x_max, x_min, y_max, y_min;
   bounding_rect(float x_max, float x_min, float y_max, float y_min) : x_max(x_max), x_min(x_min), y_max(y_max), y_min(y_min) {}
 };
-struct obstacle {};  // sc:193-284: the path reads ps.obstacles only when it is non-empty (shrink_tangent, sc:575-596)
+// sc:193-284: the path reads only obstacle.lines (shrink_tangent, sc:575-596); `contains`, the bounding box and
+// the id serve the global planner, which is not part of this library.
+struct obstacle {
+  std::vector<std::tuple<Vector2f, Vector2f>> lines;
+  std::vector<Vector2f> vertices;
+  obstacle() = default;
+  // sc:251-267: a polyline through the vertices.  Quirk kept: with an EVEN vertex count the reference appends the
+  // first vertex to its constructor argument (not to the member), i.e. the edge list is closed, `vertices` is not.
+  explicit obstacle(std::vector<Vector2f> vs) : vertices(vs) {
+    if (vs.size() % 2 == 0 && !vs.empty()) vs.push_back(vs[0]);
+    for (size_t i = 0; i + 1 < vs.size(); ++i) lines.emplace_back(vs[i], vs[i + 1]);
+  }
+  // sc:269-281: explicit edge list over the vertices
+  obstacle(std::vector<Vector2f> vs, const std::vector<std::tuple<int, int>>& edges) : vertices(std::move(vs)) {
+    for (const auto& e : edges) {
+      if (std::get<0>(e) < 0 || std::get<1>(e) < 0 || (size_t)std::get<0>(e) >= vertices.size() || (size_t)std::get<1>(e) >= vertices.size())
+        throw std::invalid_argument("edge must reference indices within the vertex list");
+      lines.emplace_back(vertices[(size_t)std::get<0>(e)], vertices[(size_t)std::get<1>(e)]);
+    }
+  }
+};
 struct planning_space {  // sc:298-319; only what from_path touches
   std::vector<obstacle> obstacles;
   bounding_rect bound_rect;
@@ -210,15 +230,21 @@ class bezier_spline {  // sc:388-431
   inline int n_segments() const { return (int)ctrl_pts.size(); }
   inline int degree() const { return ctrl_pts.empty() ? 0 : (int)ctrl_pts[0].size() - 1; }
 
-  // sc:599-683 (tangent heuristics sc:343-377).  ps.obstacles must be empty.
+  // sc:599-683 (tangent heuristics sc:343-377, tangent clipping against ps.obstacles sc:575-596).
   static bezier_spline from_path(const std::vector<Vector2f>& path, const planning_space& ps,
                                  float start_angle = std::numeric_limits<float>::quiet_NaN()) {
-    if (!ps.obstacles.empty()) throw std::invalid_argument("sea_current_b200: obstacle-aware tangent clipping is not built yet");
+    if (!ps.obstacles.empty() && b200::spline_mode() != SCB_REF_CUBIC)
+      throw std::invalid_argument("sea_current_b200: obstacle clipping is defined for the reference's cubic spline only");
     if (path.size() < 2) throw std::invalid_argument("sea_current_b200: a path needs at least two waypoints");
     bezier_spline s;
     s.wx_.resize(path.size()); s.wy_.resize(path.size());
     for (size_t i = 0; i < path.size(); ++i) { s.wx_[i] = path[i].x(); s.wy_[i] = path[i].y(); }
     s.start_angle_ = start_angle;
+    for (const obstacle& ob : ps.obstacles)
+      for (const auto& ln : ob.lines) {
+        s.edges_.push_back(std::get<0>(ln).x()); s.edges_.push_back(std::get<0>(ln).y());
+        s.edges_.push_back(std::get<1>(ln).x()); s.edges_.push_back(std::get<1>(ln).y());
+      }
     s.build();
     return s;
   }
@@ -254,7 +280,7 @@ class bezier_spline {  // sc:388-431
   }
 
  private:
-  std::vector<double> wx_, wy_, arc_, kappa_;
+  std::vector<double> wx_, wy_, arc_, kappa_, edges_;  // edges_: [n][4] obstacle edges of the planning_space
   float start_angle_ = std::numeric_limits<float>::quiet_NaN();
   arclength_data ad_;
 
@@ -266,6 +292,7 @@ class bezier_spline {  // sc:388-431
     int32_t status = 0;
     scb_batch_in in{};
     in.P = 1; in.W = W; in.G = b200::kDropInGrid; in.wx = wx_.data(); in.wy = wy_.data(); in.start_angle = &sa;
+    in.obstacle_edges = edges_.empty() ? nullptr : edges_.data(); in.n_obstacle_edges = (int32_t)(edges_.size() / 4);
     in.stages = SCB_STAGE_SPLINE;
     scb_default_opt(&in.opt);
     scb_batch_out out{};
@@ -292,6 +319,7 @@ class bezier_spline {  // sc:388-431
     int32_t status = 0, ns = S;
     scb_batch_in in{};
     in.P = 1; in.W = (int)wx_.size(); in.G = b200::kDropInGrid; in.wx = wx_.data(); in.wy = wy_.data(); in.start_angle = &sa;
+    in.obstacle_edges = edges_.empty() ? nullptr : edges_.data(); in.n_obstacle_edges = (int32_t)(edges_.size() / 4);
     in.stages = SCB_STAGE_SPLINE | SCB_STAGE_GEOMETRY; in.nudge_positions = nudge ? 1 : 0;
     scb_default_opt(&in.opt);
     scb_batch_out out{};

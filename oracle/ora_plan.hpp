@@ -39,6 +39,7 @@ struct PlanIn {
   double x_cap = 100.0;
   double dt = (double)0.02f;
   double omega_max = 0, acc_lat_max = 0;  // curvature-aware velocity caps (0 = off), see scb_batch_in
+  std::vector<Edge<double>> edges;        // obstacle edges for the tangent clipping (REF_CUBIC), see scb_batch_in
   int spline_mode = 0;  // 0 REF_CUBIC, 1 LAU_QUINTIC
   LauOpt opt;
   int solve_mode = tp::SOLVE_THOMAS;
@@ -115,7 +116,7 @@ inline PlanOut plan_one(const PlanIn& in) {
   for (int i = 0; i + 1 < W && !bad; ++i) bad = !(pt_dist(in.path[i], in.path[i + 1]) > 0.0);
   if (bad) { o.status = ST_BAD_PATH; return o; }
   if (in.spline_mode == 0) {
-    sp = from_path(in.path, in.start_angle);
+    sp = from_path(in.path, in.start_angle, false, EVAL_BF, (std::vector<V2<double>>*)nullptr, (std::vector<V2<double>>*)nullptr, &in.edges);
     o.cost = 0;
   } else {
     LauModel<double> m = lau_model(in.path, in.start_angle);

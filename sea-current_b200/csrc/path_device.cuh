@@ -51,6 +51,32 @@ __device__ __forceinline__ void waypoint_tangent(const R* x, const R* y, int W, 
   }
 }
 
+// sc:137-178: does segment l0 -> l1 cross segment k0 -> k1, and where (collinear / parallel: no, as the reference)
+template <class R>
+__device__ __forceinline__ bool seg_intersects(R l0x, R l0y, R l1x, R l1y, R k0x, R k0y, R k1x, R k1y, R& px, R& py) {
+  const R dlx = l1x - l0x, dly = l1y - l0y, dkx = k1x - k0x, dky = k1y - k0y, ex = k0x - l0x, ey = k0y - l0y;
+  const R a = ex * dly - ey * dlx;    // cross(k0 - l0, l1 - l0)
+  const R b = dlx * dky - dly * dkx;  // cross(l1 - l0, k1 - k0)
+  if (b == 0) return false;
+  const R u = a / b;
+  const R c = ex * dky - ey * dkx;    // cross(k0 - l0, k1 - k0)
+  const R t = c / b;
+  if (0 <= u && u <= 1 && 0 <= t && t <= 1) { px = t * dlx + l0x; py = t * dly + l0y; return true; }
+  return false;
+}
+
+// sc:575-596 (k = 1, sc:612): cut the tangent T of waypoint W back, edge after edge, where W -> W + T or W -> W - T
+// crosses an obstacle edge.  edges: [n][4] = (x0, y0, x1, y1) in the storage type S.
+template <class R, class S>
+__device__ __forceinline__ void shrink_tangent(R wx, R wy, const S* edges, int n, R& tx, R& ty) {
+  for (int k = 0; k < n; ++k) {
+    const R ax = (R)edges[4 * k], ay = (R)edges[4 * k + 1], bx = (R)edges[4 * k + 2], by = (R)edges[4 * k + 3];
+    R px, py;
+    if (seg_intersects<R>(wx + tx, wy + ty, wx, wy, ax, ay, bx, by, px, py)) { tx = px - wx; ty = py - wy; }
+    if (seg_intersects<R>(wx - tx, wy - ty, wx, wy, ax, ay, bx, by, px, py)) { tx = wx - px; ty = wy - py; }
+  }
+}
+
 template <class R> struct Carve {
   R* base; size_t off;
   __device__ __forceinline__ Carve(R* b) : base(b), off(0) {}

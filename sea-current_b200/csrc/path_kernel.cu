@@ -80,6 +80,7 @@ __global__ void __launch_bounds__(512, 1) path_kernel(PathArgs g) {
     } else {
       calc_tangent<R>(x[i - 1], y[i - 1], x[i], y[i], x[i + 1], y[i + 1], ox, oy);
     }
+    if (g.n_edges > 0) shrink_tangent<R, S>(x[i], y[i], (const S*)g.edges, g.n_edges, ox, oy);  // sc:615, 620, 637
     tx[it] = ox; ty[it] = oy;
   }
   __syncthreads();

@@ -267,6 +267,7 @@ __device__ __forceinline__ void lane_path(const PathArgs& g, Comm& cm, int p, in
   } else {
     calc_tangent<double>(xm, ym, wx, wy, xp, yp, btx, bty);
   }
+  if (g.n_edges > 0) shrink_tangent<double, S>(wx, wy, (const S*)g.edges, g.n_edges, btx, bty);  // sc:615, 620, 637
 
   // T and A of this waypoint and the next one: what both the optimiser and the final control points need
   double alpha = 0;

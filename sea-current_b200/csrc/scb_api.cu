@@ -24,7 +24,7 @@ enum SlotId {
   SL_L, SL_TABLE, SL_CTRL_X, SL_CTRL_Y, SL_K_LO, SL_K_HI, SL_X, SL_T, SL_XB, SL_CP, SL_KAPPA, SL_STATUS, SL_FAIL, SL_NS,
   // device mirrors of host inputs
   SL_IN_WX, SL_IN_WY, SL_IN_SA, SL_IN_VLO, SL_IN_VHI, SL_IN_VLG, SL_IN_VHG, SL_IN_ALO, SL_IN_AHI, SL_IN_VS,
-  SL_IN_VE, SL_IN_PL,
+  SL_IN_VE, SL_IN_PL, SL_IN_EDGES,
   // device mirrors of host outputs
   SL_O_STATUS, SL_O_FAIL, SL_O_CTRL_X, SL_O_CTRL_Y, SL_O_L, SL_O_TABLE, SL_O_T_TOTAL, SL_O_COST, SL_O_K_LO,
   SL_O_K_HI, SL_O_X, SL_O_T, SL_O_PX, SL_O_PY, SL_O_V, SL_O_A, SL_O_OMEGA, SL_O_NS, SL_O_STIME, SL_O_SPOS,
@@ -87,6 +87,8 @@ int validate(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, int
   if ((stages & SCB_STAGE_TIMING) && !(stages & SCB_STAGE_SPLINE) && !in->path_len) return SCB_E_INVALID;
   if ((stages & SCB_STAGE_GEOMETRY) && !(stages & SCB_STAGE_SPLINE)) return SCB_E_INVALID;
   if (!(in->omega_max >= 0) || !(in->acc_lat_max >= 0)) return SCB_E_INVALID;
+  if (in->n_obstacle_edges < 0 || (in->n_obstacle_edges > 0 && !in->obstacle_edges)) return SCB_E_INVALID;
+  if (in->n_obstacle_edges > 0 && (stages & SCB_STAGE_SPLINE) && ctx->cfg.spline_mode != SCB_REF_CUBIC) return SCB_E_INVALID;
   if ((in->omega_max > 0 || in->acc_lat_max > 0) &&
       (stages & (SCB_STAGE_SPLINE | SCB_STAGE_TIMING | SCB_STAGE_GEOMETRY)) != (SCB_STAGE_SPLINE | SCB_STAGE_TIMING | SCB_STAGE_GEOMETRY))
     return SCB_E_INVALID;  // the caps need the curvature at the gridpoints
@@ -131,6 +133,7 @@ int run_device(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, i
     PathArgs a{};
     a.P = P; a.W = W; a.G = G; a.wx = in->wx; a.wy = in->wy; a.start_angle = in->start_angle;
     a.vel_start = in->vel_start; a.vel_end = in->vel_end;
+    a.edges = in->obstacle_edges; a.n_edges = in->obstacle_edges ? in->n_obstacle_edges : 0;
     a.ctrl_x = dCx; a.ctrl_y = dCy; a.table = dTab; a.L = dL; a.cost = out->cost; a.status = out->status;
     if (do_geo && do_timing) {
       a.px = out->px; a.py = out->py;
@@ -343,6 +346,7 @@ int scb_plan_batch(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* ou
     if ((rc = up(SL_IN_WX, in->wx, (size_t)P * W * rs, &din.wx))) return rc;
     if ((rc = up(SL_IN_WY, in->wy, (size_t)P * W * rs, &din.wy))) return rc;
     if ((rc = up(SL_IN_SA, in->start_angle, P * rs, &din.start_angle))) return rc;
+    if (in->n_obstacle_edges > 0 && (rc = up(SL_IN_EDGES, in->obstacle_edges, (size_t)in->n_obstacle_edges * 4 * rs, &din.obstacle_edges))) return rc;
   }
   if (do_timing) {
     if ((rc = up(SL_IN_VLO, in->vel_lo, P * rs, &din.vel_lo))) return rc;

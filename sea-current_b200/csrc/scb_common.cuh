@@ -77,6 +77,7 @@ struct PathArgs {
   int P, W, G, PB;                    // PB (paths per CTA) and table_in_smem are filled in by launch_path
   const void *wx, *wy, *start_angle;  // [P][W], [P][W], [P] or null
   const void *vel_start, *vel_end;    // [P] or null: end slopes of the Hermite path q(s)
+  const void *edges; int n_edges;     // [n_edges][4] obstacle edges (x0, y0, x1, y1) or null: tangent clipping
   void *ctrl_x, *ctrl_y;              // [P][(W-1)*(d+1)] or null
   void *table;                        // [P][(W-1)*101]; may be null only when the table fits in shared memory
   void *L, *cost;                     // [P]

@@ -35,8 +35,8 @@ class ScbBatchIn(C.Structure):
                 ("vel_lo_grid", C.c_void_p), ("vel_hi_grid", C.c_void_p),
                 ("acc_lo", C.c_void_p), ("acc_hi", C.c_void_p),
                 ("vel_start", C.c_void_p), ("vel_end", C.c_void_p),
-                ("path_len", C.c_void_p), ("stages", C.c_int32), ("lp_mode", C.c_int32),
-                ("nudge_positions", C.c_int32), ("reserved0", C.c_int32),
+                ("path_len", C.c_void_p), ("obstacle_edges", C.c_void_p), ("stages", C.c_int32), ("lp_mode", C.c_int32),
+                ("nudge_positions", C.c_int32), ("n_obstacle_edges", C.c_int32),
                 ("x_cap", C.c_double), ("dt", C.c_double), ("omega_max", C.c_double), ("acc_lat_max", C.c_double),
                 ("opt", ScbOpt)]
 

@@ -100,7 +100,7 @@ class BatchPlanner:
     def plan(self, wx=None, wy=None, vel_lo=None, vel_hi=None, acc_lo=None, acc_hi=None, G=101, start_angle=None,
              vel_lo_grid=None, vel_hi_grid=None, vel_start=None, vel_end=None, path_len=None, stages=0,
              outputs=ALL_OUTPUTS, S_cap=0, x_cap=0.0, dt=0.0, opt=None, out_buffers=None, resample_at=None, lp_mode=0,
-             nudge=False, omega_max=0.0, acc_lat_max=0.0):
+             nudge=False, omega_max=0.0, acc_lat_max=0.0, obstacle_edges=None):
         """Host arrays in, host arrays out (scb_plan_batch).  `out_buffers` lets a caller pass
         preallocated (e.g. pinned) numpy arrays keyed by output name."""
         R = self.real
@@ -132,6 +132,10 @@ class BatchPlanner:
         bi.stages, bi.x_cap, bi.dt, bi.lp_mode = stages, x_cap, dt, lp_mode
         bi.omega_max, bi.acc_lat_max = omega_max, acc_lat_max
         bi.nudge_positions = 1 if nudge else 0
+        if obstacle_edges is not None and len(obstacle_edges):
+            ed = np.ascontiguousarray(obstacle_edges, dtype=R).reshape(-1, 4)
+            keep.append(ed)
+            bi.obstacle_edges, bi.n_obstacle_edges = ed.ctypes.data, ed.shape[0]
         bi.opt = opt if opt is not None else default_opt()
         res = BatchResult()
         bo = abi.ScbBatchOut()
