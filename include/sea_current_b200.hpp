@@ -136,7 +136,7 @@ struct obstacle {
   obstacle() = default;
   // sc:251-267: a polyline through the vertices.  Quirk kept: with an EVEN vertex count the reference appends the
   // first vertex to its constructor argument (not to the member), i.e. the edge list is closed, `vertices` is not.
-  explicit obstacle(std::vector<Vector2f> vs) : vertices(vs) {
+  obstacle(std::vector<Vector2f> vs) : vertices(vs) {
     if (vs.size() % 2 == 0 && !vs.empty()) vs.push_back(vs[0]);
     for (size_t i = 0; i + 1 < vs.size(); ++i) lines.emplace_back(vs[i], vs[i + 1]);
   }

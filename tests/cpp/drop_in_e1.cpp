@@ -5,6 +5,8 @@
 //
 //   drop_in_e1 json <out.json>      the six-waypoint case of examples/json_test.cpp
 //   drop_in_e1 text <out.json>      the request of examples/zmq_test.py:7-10 through handle_text_request
+//   drop_in_e1 lines <unused>       edge lists of the two obstacle constructors (host only, sc:251-281)
+//   drop_in_e1 obst <unused>        from_path over a planning_space with obstacles (shrink_tangent, sc:575-596)
 #include <cstring>
 #include <fstream>
 #include <iomanip>
@@ -40,10 +42,48 @@ static int run_json_case(const char* out_path) {
   return 0;
 }
 
+// Two obstacles near the corner (10, 0) of an L-shaped path: a 4-vertex one (even count: the reference closes its edge
+// list) and a 3-vertex polyline (open).
+static std::vector<obstacle> corner_obstacles() {
+  obstacle a(std::vector<Vector2f>{Vector2f(8, -2.5f), Vector2f(8, -0.5f), Vector2f(9, -0.5f), Vector2f(9, -2.5f)});
+  obstacle b(std::vector<Vector2f>{Vector2f(11, 2), Vector2f(13, 2), Vector2f(13, 3)});
+  obstacle c(std::vector<Vector2f>{Vector2f(20, 20), Vector2f(21, 20), Vector2f(21, 21)}, std::vector<std::tuple<int, int>>{{0, 2}, {2, 1}});
+  return {a, b, c};
+}
+
+static void print_lines(const std::vector<obstacle>& obs) {
+  std::cout << "{\"lines\": [";
+  bool first = true;
+  for (const auto& o : obs)
+    for (const auto& l : o.lines) {
+      std::cout << (first ? "" : ", ") << "[" << std::get<0>(l).x() << ", " << std::get<0>(l).y() << ", " << std::get<1>(l).x() << ", " << std::get<1>(l).y() << "]";
+      first = false;
+    }
+  std::cout << "], \"n_vertices\": [";
+  for (size_t i = 0; i < obs.size(); ++i) std::cout << (i ? ", " : "") << obs[i].vertices.size();
+  std::cout << "]";
+}
+
+static int run_obstacle_case() {
+  planning_space space(bounding_rect{30, -30, 30, -30});
+  space.obstacles = corner_obstacles();
+  const std::vector<Vector2f> path = {Vector2f(0, 0), Vector2f(10, 0), Vector2f(10, 10), Vector2f(0, 10)};
+  bezier_spline sp = bezier_spline::from_path(path, space);
+  const arclength_data ad = sp.arclength();
+  print_lines(space.obstacles);
+  std::cout << std::setprecision(9) << ", \"arclength\": " << ad.arclength << ", \"ctrl\": [";
+  for (int s = 0; s < sp.n_segments(); ++s)
+    for (int k = 0; k < 4; ++k) std::cout << (s + k ? ", " : "") << "[" << sp.ctrl_pts[s][k].x() << ", " << sp.ctrl_pts[s][k].y() << "]";
+  std::cout << "]}" << std::endl;
+  return 0;
+}
+
 int main(int argc, char** argv) {
   if (argc < 3) { std::cerr << "usage: drop_in_e1 json|text <out.json>" << std::endl; return 2; }
   try {
     if (!std::strcmp(argv[1], "json")) return run_json_case(argv[2]);
+    if (!std::strcmp(argv[1], "lines")) { print_lines(corner_obstacles()); std::cout << "}" << std::endl; return 0; }
+    if (!std::strcmp(argv[1], "obst")) return run_obstacle_case();
     const std::string req = "-0.5 0.5 -0.25 0.25\n0 0\n10 0\n10 10";
     std::ofstream o(argv[2]);
     o << b200::handle_text_request(req);

@@ -63,6 +63,34 @@ def test_fails_loudly_without_a_device(built, tmp_path):
     assert r.returncode == 3 and b"no CPU fallback" in r.stderr
 
 
+CORNER_LINES = [[8, -2.5, 8, -0.5], [8, -0.5, 9, -0.5], [9, -0.5, 9, -2.5], [9, -2.5, 8, -2.5],  # 4 vertices: closed by the ctor
+                [11, 2, 13, 2], [13, 2, 13, 3],  # 3 vertices: open polyline
+                [20, 20, 21, 21], [21, 21, 21, 20]]  # explicit edge list
+
+
+def test_obstacle_constructors_build_the_reference_edge_lists(built):
+    """sea_current.hpp:251-281: an even vertex count closes the edge list (the first vertex is appended to the
+    constructor's local copy, `vertices` keeps its size); an odd one stays an open polyline; runs without a GPU."""
+    doc = json.loads(subprocess.check_output([built, "lines", "-"]).decode())
+    assert doc["lines"] == CORNER_LINES and doc["n_vertices"] == [4, 3, 3]
+
+
+@pytest.mark.gpu
+def test_from_path_clips_tangents_at_obstacles(built, oracle):
+    """from_path over a planning_space with obstacles (shrink_tangent, sc:575-596) vs the oracle on the same edges."""
+    doc = json.loads(subprocess.check_output([built, "obst", "-"]).decode())
+    assert doc["lines"] == CORNER_LINES
+    wx = np.array([[0.0, 10.0, 10.0, 0.0]]); wy = np.array([[0.0, 0.0, 10.0, 10.0]])
+    lim = dict(vel_lo=[-1.0], vel_hi=[1.0], acc_lo=[-0.5], acc_hi=[0.5])
+    ref, _ = oracle.plan_batch(wx=wx, wy=wy, G=21, spline_mode=0, obstacle_edges=np.array(CORNER_LINES, dtype=np.float64), **lim)
+    free, _ = oracle.plan_batch(wx=wx, wy=wy, G=21, spline_mode=0, **lim)
+    assert np.abs(ref["ctrl_x"][0] - free["ctrl_x"][0]).max() > 0.5  # the obstacles do cut a tangent back
+    ctrl = np.array(doc["ctrl"])
+    np.testing.assert_allclose(ctrl[:, 0], ref["ctrl_x"][0], atol=2e-6)  # the drop-in holds control points as float32
+    np.testing.assert_allclose(ctrl[:, 1], ref["ctrl_y"][0], atol=2e-6)
+    assert abs(doc["arclength"] / ref["arclen_total"][0] - 1) <= 1e-6
+
+
 @pytest.mark.gpu
 def test_json_case_matches_oracle(built, tmp_path, oracle):
     """examples/json_test.cpp's body through the shim vs the oracle's FP64 plan of the same problem."""
