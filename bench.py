@@ -18,6 +18,7 @@ roofline   dominant kernel (by duration): algorithmic flops (or bytes) / its mea
 cpu_baseline  the oracle's reference-faithful port of the E1 body timed on this box's host cores
 """
 import argparse
+import contextlib
 import json
 import os
 import subprocess
@@ -43,6 +44,8 @@ def parse():
     ap.add_argument("--config", default="C3", choices=["C2", "C3", "C4", "C5"])
     ap.add_argument("--precision", default="fp64", choices=["fp64", "fp32"])
     ap.add_argument("--problems", type=int, default=0, help="override the per-rank batch size")
+    ap.add_argument("--parametrizer", default="spline", choices=["spline", "const_accel"],
+                    help="spline = what the reference's gen_vel_prof builds (the headline); const_accel = toppra's ConstAccel")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
@@ -191,7 +194,8 @@ def main():
     tdt = torch.float64 if a.precision == "fp64" else torch.float32
     opt = scb.default_opt(move_waypoints=1)
     inputs = {k: torch.from_numpy(np.ascontiguousarray(v)).to(dev, dtype=tdt) for k, v in w.items() if k != "G"}
-    bi, bo, res = pl.make_device_batch(inputs, G=G, opt=opt)
+    pm = 1 if a.parametrizer == "const_accel" else 0
+    bi, bo, res = pl.make_device_batch(inputs, G=G, opt=opt, param_mode=pm)
     stream = torch.cuda.ExternalStream(pl.stream(), device=dev)
     nrec = P * 32
 
@@ -248,7 +252,7 @@ def main():
         "path_ms": ("path_lane_kernel" if W <= 32 else "path_kernel", P * rs * (2 * W + 1 + 2 * (d + 1) * (W - 1) + 1), P * K_it * (W - 1) * Q * 120.0),
         "arc_ms": ("arc_kernel", P * rs * (2 * (d + 1) * (W - 1) + 1 + 3 * G), P * ((W - 1) * 3200 * 24.0 + 100.0 * G)),
         "toppra_ms": ("toppra_fast_kernel", P * (rs * (1 + 6 + 3 * G) + 8), P * 640.0 * G),
-        "param_ms": ("param_kernel", P * rs * (2 * G + 3 + 4 * G + 1), P * 60.0 * G),
+        "param_ms": ("param_ca_kernel" if pm else "param_kernel", P * rs * (2 * G + 3 + 4 * G + 1), P * 60.0 * G),
     }
     peaks = {}
     try:
@@ -296,6 +300,7 @@ def main():
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": scaling, "vs_baseline": None,
             "dtype": "f64" if a.precision == "fp64" else "f32", "data": "synthetic",
             "config": dict(cfg, P_per_rank=P, spline="lau_quintic, optimiser K=%d move_waypoints=1" % opt.iters,
+                           parametrizer=a.parametrizer,
                            l2="outputs streamed per step (%.2f GB) exceed the 126 MB L2; no flush" % (path_bytes / 1e9),
                            ok_fraction=ok_frac),
             "stage_ms": stage_ms, "roofline": roof, "clocks": clocks, "gpu_launches": launches_per_step * a.steps}
@@ -303,30 +308,35 @@ def main():
     # ---- e2e: host buffers in pinned memory through scb_plan_batch
     if not a.no_e2e:
         names = scb.TRAJECTORY_OUTPUTS
-        host_in = {k: torch.from_numpy(np.ascontiguousarray(v, dtype=pl.real)).pin_memory().numpy() for k, v in w.items() if k != "G"}
-        bufs = {"status": torch.empty(P, dtype=torch.int32).pin_memory().numpy(),
-                "fail_stage": torch.empty(P, dtype=torch.int32).pin_memory().numpy()}
-        for n in names:
-            bufs[n] = torch.empty(pl.out_shape(n, P, W, G, 0), dtype=tdt).pin_memory().numpy()
-        h2d = sum(v.nbytes for v in host_in.values()); d2h = sum(v.nbytes for v in bufs.values())
-        k2 = max(2, min(a.steps, 5))
-        for _ in range(2):
-            pl.plan(G=G, outputs=names, out_buffers=bufs, opt=opt, **host_in)
-        if world > 1:
-            dist.barrier()
-        t0 = time.perf_counter()
-        for _ in range(k2):
-            pl.plan(G=G, outputs=names, out_buffers=bufs, opt=opt, **host_in)
-        dt = time.perf_counter() - t0
-        if world > 1:
-            t = torch.tensor([dt], device=dev, dtype=torch.float64)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            dt = float(t.item())
+        # host buffers are pinned (and the calls made) from the GPU's own NUMA node: with several ranks on a
+        # two-socket box the scheduler otherwise puts some of them on the far socket and their D2H runs ~3x slower
+        numa = scb.near_gpu(local) if os.environ.get("SCB_BENCH_NUMA", "1") != "0" else contextlib.nullcontext()
+        with numa:
+            host_in = {k: torch.from_numpy(np.ascontiguousarray(v, dtype=pl.real)).pin_memory().numpy() for k, v in w.items() if k != "G"}
+            bufs = {"status": torch.empty(P, dtype=torch.int32).pin_memory().numpy(),
+                    "fail_stage": torch.empty(P, dtype=torch.int32).pin_memory().numpy()}
+            for n in names:
+                bufs[n] = torch.empty(pl.out_shape(n, P, W, G, 0), dtype=tdt).pin_memory().numpy()
+            h2d = sum(v.nbytes for v in host_in.values()); d2h = sum(v.nbytes for v in bufs.values())
+            k2 = max(2, min(a.steps, 5))
+            for _ in range(2):
+                pl.plan(G=G, outputs=names, out_buffers=bufs, opt=opt, param_mode=pm, **host_in)
+            if world > 1:
+                dist.barrier()
+            t0 = time.perf_counter()
+            for _ in range(k2):
+                pl.plan(G=G, outputs=names, out_buffers=bufs, opt=opt, param_mode=pm, **host_in)
+            dt = time.perf_counter() - t0
+            if world > 1:
+                t = torch.tensor([dt], device=dev, dtype=torch.float64)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                dt = float(t.item())
         tm = pl.timing()
         line["e2e"] = {"value": cfg["P_global"] * k2 / dt if scaling == "weak" else cfg["P_global"] * k2 / dt, "unit": UNIT,
                        "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": k2,
                        "last_step_ms": {k: tm[k] for k in ("h2d_ms", "d2h_ms", "total_ms")},
-                       "outputs": list(names)}
+                       "outputs": list(names),
+                       "numa_bound_cpus": len(getattr(numa, "bound", None) or ())}
     if rank == 0 and world == 1 and not a.no_cpu:  # N=1 only (torchrun pins OMP_NUM_THREADS=1 per rank)
         line["cpu_baseline"] = cpu_baseline_run(w, G, a.cpu_seconds, 0)
     if rank == 0:

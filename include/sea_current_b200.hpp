@@ -178,6 +178,12 @@ inline int& spline_mode() {
   static int m = [] { const char* e = std::getenv("SEA_CURRENT_B200_SPLINE"); return (e && (e[0] == 'l' || e[0] == 'L')) ? SCB_LAU_QUINTIC : SCB_REF_CUBIC; }();
   return m;
 }
+// Parametrizer gen_vel_prof builds: toppra::parametrizer::Spline as in the reference (sc:1231), or ConstAccel
+// (tp:parametrizer/const_accel.cpp).  Also settable with SEA_CURRENT_B200_PARAM=const_accel in the environment.
+inline int& param_mode() {
+  static int m = [] { const char* e = std::getenv("SEA_CURRENT_B200_PARAM"); return (e && (e[0] == 'c' || e[0] == 'C')) ? SCB_PARAM_CONST_ACCEL : SCB_PARAM_SPLINE; }();
+  return m;
+}
 inline int& device() { static int d = 0; return d; }
 
 inline void check(int rc, scb_ctx* ctx, const char* what) {
@@ -355,7 +361,7 @@ inline velocity_profile gen_vel_prof(const Eigen::Vector<value_type, N>& pos_end
   scb_batch_in in{};
   in.P = 1; in.W = 2; in.G = G; in.path_len = &L; in.vel_lo_grid = vlo.data(); in.vel_hi_grid = vhi.data();
   in.acc_lo = &alo; in.acc_hi = &ahi; in.vel_start = &vs; in.vel_end = &ve;
-  in.stages = SCB_STAGE_TIMING; in.lp_mode = SCB_LP_SEIDEL; in.dt = (double)dt;
+  in.stages = SCB_STAGE_TIMING; in.lp_mode = SCB_LP_SEIDEL; in.dt = (double)dt; in.param_mode = b200::param_mode();
   scb_default_opt(&in.opt);
   scb_batch_out out{};
   out.status = &status; out.fail_stage = &fail; out.S_cap = S_cap; out.n_samples = &ns;

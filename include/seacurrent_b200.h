@@ -117,6 +117,15 @@ enum {
   SCB_LP_CLOSED_FORM = 2   /* eliminate u: three determinants and six quotients per stage */
 };
 
+/* Parametrizer of the timing stage: how sdot^2 at the gridpoints becomes a function of time. */
+enum {
+  SCB_PARAM_SPLINE = 0,      /* toppra::parametrizer::Spline, what gen_vel_prof builds (sc:1231): trapezoid knot times,
+                                clamped cubic spline q(t) through (t_i, q(s_i))  (tp:parametrizer/spline.cpp:10-45) */
+  SCB_PARAM_CONST_ACCEL = 1  /* toppra::parametrizer::ConstAccel (tp:parametrizer/const_accel.cpp:19-115): constant path
+                                acceleration on every grid interval, s(t) a quadratic per interval, nothing solved;
+                                t, v, a, omega, T_total and the uniform-dt stream are then its values */
+};
+
 typedef struct scb_batch_in {
   int32_t P, W, G;          /* problems, waypoints per problem (>= 2), toppra gridpoints (>= 2;
                                the reference's default is 101, tp:algorithm.hpp:140) */
@@ -142,6 +151,8 @@ typedef struct scb_batch_in {
   int32_t nudge_positions;  /* geometry-only calls: 1 = repair the caller's s_pos in place before resampling
                                (ends pinned to 0 / L, non-monotone entries averaged, clamp; sc:902-912) */
   int32_t n_obstacle_edges; /* 0 = no obstacles */
+  int32_t param_mode;       /* SCB_PARAM_*; 0 = the reference's Spline parametrizer */
+  int32_t reserved0;        /* 0 */
   double x_cap;             /* upper bound of sdot^2 in the backward pass; 0 = reference's 100
                                (tp:algorithm.hpp:152 m_initXBound) */
   double dt;                /* uniform-dt stream period; 0 = reference's 0.02 (sc:1199) */

@@ -227,6 +227,44 @@ inline SplineParam spline_parametrizer(const PPoly& path, const Vec& gridpoints,
   return sp;
 }
 
+// ---------------------------------------------------------------- parametrizer::ConstAccel
+// tp:parametrizer/const_accel.cpp:19-33 (process_internals), 35-58 (evalParams), 60-115 (eval_impl): the path
+// acceleration is constant on every grid interval, so s(t) is a quadratic per interval and nothing is solved.
+struct ConstAccelParam {
+  PPoly path;
+  Vec gridpoints, vs, ts, us;
+  Vec eval_single(double t, int order) const {
+    // first knot of m_ts[1 .. G-2] that is >= t; clamps to the first / last interval (const_accel.cpp:42-48)
+    const int G = (int)ts.size();
+    const int k = (int)(std::lower_bound(ts.begin() + 1, ts.begin() + (G - 1), t) - ts.begin()) - 1;
+    const double dt = t - ts[k];
+    const double u = us[k];
+    const double v = vs[k] + dt * u;
+    double ss = gridpoints[k] + dt * vs[k] + 0.5 * dt * dt * us[k];
+    auto I = path.interval();
+    ss = std::min(std::max(ss, I[0]), I[1]);  // const_accel.cpp:80-81
+    if (order == 0) return path.eval_single(ss, 0);
+    Vec ps = path.eval_single(ss, 1);
+    if (order == 1) { for (double& x : ps) x *= v; return ps; }
+    Vec pss = path.eval_single(ss, 2);
+    for (size_t j = 0; j < ps.size(); ++j) pss[j] = pss[j] * v * v + ps[j] * u;
+    return pss;
+  }
+};
+
+inline ConstAccelParam const_accel_parametrizer(const PPoly& path, const Vec& gridpoints, const Vec& vsquared) {
+  const int G = (int)gridpoints.size();
+  ConstAccelParam c;
+  c.path = path; c.gridpoints = gridpoints;
+  c.vs.resize(G); c.ts.assign(G, 0.0); c.us.assign(G - 1, 0.0);
+  for (int i = 0; i < G; ++i) c.vs[i] = std::sqrt(vsquared[i]);
+  for (int i = 0; i + 1 < G; ++i) {
+    c.us[i] = 0.5 * (c.vs[i + 1] * c.vs[i + 1] - c.vs[i] * c.vs[i]) / (gridpoints[i + 1] - gridpoints[i]);
+    c.ts[i + 1] = c.ts[i] + 2 * (gridpoints[i + 1] - gridpoints[i]) / (c.vs[i + 1] + c.vs[i]);
+  }
+  return c;
+}
+
 // ---------------------------------------------------------------- sc:1191-1265 gen_vel_prof<1>
 struct VelocityProfile {
   std::vector<float> pos, vel, acc;  // sc:1245-1262 (double -> float)

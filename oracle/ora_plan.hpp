@@ -43,6 +43,7 @@ struct PlanIn {
   int spline_mode = 0;  // 0 REF_CUBIC, 1 LAU_QUINTIC
   LauOpt opt;
   int solve_mode = tp::SOLVE_THOMAS;
+  int param_mode = 0;   // 0 parametrizer::Spline (sc:1231), 1 parametrizer::ConstAccel (tp:parametrizer/const_accel.cpp)
   int S_cap = 0;
 };
 
@@ -185,15 +186,26 @@ inline PlanOut plan_one(const PlanIn& in) {
   for (size_t i = 0; i < pd.controllable_sets.size(); ++i) { o.K_lo[i] = pd.controllable_sets[i][0]; o.K_hi[i] = pd.controllable_sets[i][1]; }
   for (size_t i = 0; i < pd.parametrization.size(); ++i) o.x[i] = pd.parametrization[i];
   if (pd.ret_code != tp::OK) return o;
-  // ---- parametrizer
-  tp::SplineParam spp = tp::spline_parametrizer(pb.path, pd.gridpoints, pd.parametrization, in.solve_mode);
-  if ((int)spp.ts.size() != G) { o.status = ST_TIME_KNOTS; return o; }
-  o.T = spp.ts.back() - spp.ts.front();
-  o.t = spp.ts;
+  // ---- parametrizer: traj(t, order) is Spline::eval_impl (tp:parametrizer/spline.cpp:47-49) or ConstAccel::eval_impl
+  tp::SplineParam spp;
+  tp::ConstAccelParam cap;
+  std::function<double(double, int)> traj;
+  if (in.param_mode == 1) {
+    cap = tp::const_accel_parametrizer(pb.path, pd.gridpoints, pd.parametrization);
+    if (!std::isfinite(cap.ts.back())) { o.status = ST_TIME_KNOTS; return o; }  // two neighbouring gridpoints at rest
+    o.t = cap.ts;
+    traj = [&cap](double t, int order) { return cap.eval_single(t, order)[0]; };
+  } else {
+    spp = tp::spline_parametrizer(pb.path, pd.gridpoints, pd.parametrization, in.solve_mode);
+    if ((int)spp.ts.size() != G) { o.status = ST_TIME_KNOTS; return o; }
+    o.t = spp.ts;
+    traj = [&spp](double t, int order) { return spp.traj.eval_single(t, order)[0]; };
+  }
+  o.T = o.t.back() - o.t.front();
   o.px.resize(G); o.py.resize(G); o.v.resize(G); o.a.resize(G); o.omega.resize(G);
   for (int i = 0; i < G; ++i) {
-    o.v[i] = spp.traj.eval_single(spp.ts[i], 1)[0];
-    o.a[i] = spp.traj.eval_single(spp.ts[i], 2)[0];
+    o.v[i] = traj(o.t[i], 1);
+    o.a[i] = traj(o.t[i], 2);
     const double q = pb.path.eval_single(gp[i], 0)[0];
     int seg; double u, kap;
     arclen_invert(polys, o.table, seg_end, q, seg, u);
@@ -205,14 +217,14 @@ inline PlanOut plan_one(const PlanIn& in) {
     const int S = (int)std::ceil(o.T / in.dt);
     o.n_samples = S;
     const int n = std::min(S, in.S_cap);
-    tp::Vec times = tp::linspaced(S, spp.ts.front(), spp.ts.back());
+    tp::Vec times = tp::linspaced(S, o.t.front(), o.t.back());
     o.s_time.resize(n); o.s_pos.resize(n); o.s_vel.resize(n); o.s_acc.resize(n);
     o.s_px.resize(n); o.s_py.resize(n); o.s_omega.resize(n);
     for (int i = 0; i < n; ++i) {
       o.s_time[i] = times[i];
-      o.s_pos[i] = spp.traj.eval_single(times[i], 0)[0];
-      o.s_vel[i] = spp.traj.eval_single(times[i], 1)[0];
-      o.s_acc[i] = spp.traj.eval_single(times[i], 2)[0];
+      o.s_pos[i] = traj(times[i], 0);
+      o.s_vel[i] = traj(times[i], 1);
+      o.s_acc[i] = traj(times[i], 2);
       int seg; double u, kap;
       arclen_invert(polys, o.table, seg_end, o.s_pos[i], seg, u);
       curve_at(polys[seg], u, o.s_px[i], o.s_py[i], kap);

@@ -9,4 +9,4 @@ sea_current.hpp callers is include/sea_current_b200.hpp.
 """
 from .scb import abi, workloads  # noqa: F401
 from .scb.planner import (ALL_OUTPUTS, TRAJECTORY_OUTPUTS, SUMMARY_DTYPE, BatchPlanner, BatchResult, ScbError,  # noqa: F401
-                          default_opt, gather_summaries, shard_range)
+                          default_opt, gather_summaries, gpu_local_cpus, near_gpu, shard_range)

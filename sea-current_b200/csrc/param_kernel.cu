@@ -7,6 +7,7 @@
 //                then the per-gridpoint record: v, a (spline derivatives at the knots) and
 //                omega = v * kappa (sea_current.hpp:1055-1067) with kappa at arc length q(s_i) as
 //                written by path_kernel.
+// param_ca_kernel  parametrizer::ConstAccel (tp:parametrizer/const_accel.cpp), scb_batch_in.param_mode = 1.
 // sample_kernel  the uniform-dt stream of gen_vel_prof (sea_current.hpp:1235-1262), resample
 //                (sc:898-1005) and angular_velocity (sc:1055-1067).
 //
@@ -104,15 +105,18 @@ template <class R, int DEG> struct ArcWalker {
     const R ck = c[k], target = r - ck;
     R du = h * target / (c[k + 1] - ck);
     du = fmin(fmax(du, (R)0), h);
+    // Newton to convergence (linear, not quadratic, next to a cusp of the curve: a fixed count is not enough there)
+    const R tol = (sizeof(R) == 8 ? (R)1e-12 : (R)1e-6) * h;
 #pragma unroll 1
-    for (int it = 0; it < kInvNewton; ++it) {
+    for (int it = 0; it < kInvNewtonMax; ++it) {
       const R half = (R)0.5 * du, mid = a + half;
       R F = 0;
 #pragma unroll
       for (int gq = 0; gq < 4; ++gq) F += (R)kGL4W[gq] * poly.speed(mid + half * (R)kGL4X[gq]);
       F *= half;
-      du = du - (F - target) / poly.speed(a + du);
-      du = fmin(fmax(du, (R)0), h);
+      const R delta = (F - target) / poly.speed(a + du);
+      du = fmin(fmax(du - delta, (R)0), h);
+      if (fabs(delta) <= tol) break;
     }
     poly.eval(fmin(a + du, (R)1), px, py, kappa);
   }
@@ -126,6 +130,7 @@ struct Hermite1 {  // FP64 in both precision modes, like the toppra kernel
   __device__ __forceinline__ double s_at(int i) const { return i == N ? 1.0 : (double)i * step; }
   __device__ __forceinline__ double q(double s) const { return c0 * (s * s * s) + c1 * (s * s) + c2 * s; }
   __device__ __forceinline__ double qd(double s) const { return (3.0 * c0) * (s * s) + (2.0 * c1) * s + c2; }
+  __device__ __forceinline__ double qdd(double s) const { return (6.0 * c0) * s + 2.0 * c1; }
 };
 
 // `S` is the storage type of the caller's arrays; the recurrences (knot times, Thomas) run in FP64
@@ -247,6 +252,81 @@ __global__ void __launch_bounds__(32) param_kernel(ParamArgs g) {
   }
 }
 
+// parametrizer::ConstAccel (tp:parametrizer/const_accel.cpp:19-33 process_internals, 35-58 evalParams, 60-115
+// eval_impl): constant path acceleration u_k on every grid interval, so one forward sweep gives the knot times and the
+// record of every gridpoint, with no system to solve and no scratch besides the knot times the sampler reads.
+// Knot i >= 1 is evaluated the way evalParams finds it: on interval k = i - 1 at dt = t_i - t_{i-1} (lower_bound over
+// m_ts[1 .. G-2]); knot 0 on interval 0 at dt = 0.
+template <class S>
+__global__ void __launch_bounds__(32) param_ca_kernel(ParamArgs g) {
+  typedef double R;
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= g.P) return;
+  const int P = g.P, G = g.G, N = G - 1;
+  const S* __restrict__ X2 = (const S*)g.x;
+  R* __restrict__ tb = (R*)g.t_buf;
+  S* __restrict__ o_t = (S*)g.t; S* __restrict__ o_v = (S*)g.v; S* __restrict__ o_a = (S*)g.a; S* __restrict__ o_om = (S*)g.omega;
+  const S* __restrict__ kap = (const S*)g.kappa;
+  int status = g.status[p];
+  if (status == SCB_ST_OK) {
+    Hermite1 hp;
+    hp.init((R)((const S*)g.L)[p], g.vel_start ? (R)((const S*)g.vel_start)[p] : 0.0,
+            g.vel_end ? (R)((const S*)g.vel_end)[p] : 0.0, N);
+    R v_prev = sqrt((R)X2[p]), t_prev = 0, s_prev = hp.s_at(0);
+    const R kap0 = kap ? (R)kap[p] : 0.0;
+    tb[p] = 0;
+    for (int i0 = 1; i0 <= N; i0 += kPU) {
+      R xs[kPU], kk[kPU];
+#pragma unroll
+      for (int u = 0; u < kPU; ++u) {
+        const size_t o = (size_t)min(i0 + u, N) * P + p;
+        xs[u] = (R)X2[o]; kk[u] = kap ? (R)kap[o] : 0.0;
+      }
+#pragma unroll
+      for (int u = 0; u < kPU; ++u) {
+        const int i = i0 + u;
+        if (i <= N) {
+          const size_t o = (size_t)i * P + p;
+          const R s = hp.s_at(i), v = sqrt(xs[u]), ds = s - s_prev;
+          const R acc_k = 0.5 * (v * v - v_prev * v_prev) / ds;  // m_us[i-1]
+          const R t = t_prev + 2 * ds / (v + v_prev);             // m_ts[i]
+          tb[o] = t;
+          if (i == 1) {  // knot 0: interval 0, dt = 0
+            const R q1 = hp.qd(s_prev);
+            const R vel = q1 * v_prev, acc = hp.qdd(s_prev) * v_prev * v_prev + q1 * acc_k;
+            if (o_t) o_t[p] = (S)0;
+            if (o_v) o_v[p] = (S)vel;
+            if (o_a) o_a[p] = (S)acc;
+            if (o_om) o_om[p] = (S)(vel * kap0);
+          }
+          const R dk = t - t_prev;
+          const R vs = v_prev + dk * acc_k;
+          const R ss = fmin(fmax(s_prev + dk * v_prev + 0.5 * dk * dk * acc_k, 0.0), 1.0);  // const_accel.cpp:80-81
+          const R q1 = hp.qd(ss);
+          const R vel = q1 * vs, acc = hp.qdd(ss) * vs * vs + q1 * acc_k;
+          if (o_t) o_t[o] = (S)t;
+          if (o_v) o_v[o] = (S)vel;
+          if (o_a) o_a[o] = (S)acc;
+          if (o_om) o_om[o] = (S)(vel * kk[u]);
+          t_prev = t; s_prev = s; v_prev = v;
+        }
+      }
+    }
+    // two neighbouring gridpoints at rest: the reference divides by zero (const_accel.cpp:28); reported here
+    if (!(t_prev < 1.0e300)) status = SCB_ST_ERR_TIME_KNOTS;
+    else if (g.T_total) ((S*)g.T_total)[p] = (S)t_prev;
+  }
+  if (status != SCB_ST_OK) {
+    if (g.status[p] == SCB_ST_OK) g.status[p] = status;
+    for (int i = 0; i < G; ++i) {
+      const size_t o = (size_t)i * P + p;
+      tb[o] = 0;
+      if (o_t) o_t[o] = 0; if (o_v) o_v[o] = 0; if (o_a) o_a[o] = 0; if (o_om) o_om[o] = 0;
+    }
+    if (g.T_total) ((S*)g.T_total)[p] = 0;
+  }
+}
+
 template <class R, int DEG>
 __global__ void __launch_bounds__(64) sample_kernel(SampleArgs g) {
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
@@ -274,23 +354,42 @@ __global__ void __launch_bounds__(64) sample_kernel(SampleArgs g) {
       g.n_samples[p] = S;
       n = S < S_cap ? S : S_cap;
       const double stp = S > 1 ? (T - t0) / (double)(S - 1) : 0.0;
+      const bool ca = g.param_mode == SCB_PARAM_CONST_ACCEL;
+      const R* X2 = (const R*)g.x;
       int j = -1;
       double tj = 0, k0 = 0, k1 = 0, k2 = 0, k3 = 0, t_up = t0;
       for (int i = 0; i < n; ++i) {
         const double time = (i == S - 1) ? T : t0 + (double)i * stp;  // Eigen LinSpaced
-        if (j < 0 || (j < N - 1 && t_up <= time)) {
-          if (j < 0) j = 0;
-          while (j < N - 1 && tb[(size_t)(j + 1) * P + p] <= time) ++j;
-          tj = tb[(size_t)j * P + p]; t_up = tb[(size_t)(j + 1) * P + p];
-          const double Xj = Xb[(size_t)j * P + p], Xn = Xb[(size_t)(j + 1) * P + p];
-          const double qj = hp.q(hp.s_at(j)), qn = hp.q(hp.s_at(j + 1));
-          const double h = t_up - tj;
-          k0 = (Xn - Xj) / (3 * h); k1 = Xj; k2 = (qn - qj) / h - h / 3 * (2 * Xj + Xn); k3 = qj;
+        double pos, vel, acc;
+        if (ca) {
+          // evalParams (const_accel.cpp:42-57): interval k with m_ts[k] < time <= m_ts[k+1]; k0 = u_k, k1 = v_k, k2 = s_k
+          if (j < 0 || (j < N - 1 && t_up < time)) {
+            if (j < 0) j = 0;
+            while (j < N - 1 && tb[(size_t)(j + 1) * P + p] < time) ++j;
+            tj = tb[(size_t)j * P + p]; t_up = tb[(size_t)(j + 1) * P + p];
+            const double vj = sqrt((double)X2[(size_t)j * P + p]), vn = sqrt((double)X2[(size_t)(j + 1) * P + p]);
+            k2 = hp.s_at(j); k1 = vj;
+            k0 = 0.5 * (vn * vn - vj * vj) / (hp.s_at(j + 1) - k2);
+          }
+          const double d = time - tj, vs = k1 + d * k0;
+          const double ss = fmin(fmax(k2 + d * k1 + 0.5 * d * d * k0, 0.0), 1.0);
+          const double q1 = hp.qd(ss);
+          pos = hp.q(ss); vel = q1 * vs; acc = hp.qdd(ss) * vs * vs + q1 * k0;
+        } else {
+          if (j < 0 || (j < N - 1 && t_up <= time)) {
+            if (j < 0) j = 0;
+            while (j < N - 1 && tb[(size_t)(j + 1) * P + p] <= time) ++j;
+            tj = tb[(size_t)j * P + p]; t_up = tb[(size_t)(j + 1) * P + p];
+            const double Xj = Xb[(size_t)j * P + p], Xn = Xb[(size_t)(j + 1) * P + p];
+            const double qj = hp.q(hp.s_at(j)), qn = hp.q(hp.s_at(j + 1));
+            const double h = t_up - tj;
+            k0 = (Xn - Xj) / (3 * h); k1 = Xj; k2 = (qn - qj) / h - h / 3 * (2 * Xj + Xn); k3 = qj;
+          }
+          const double ds = time - tj;
+          pos = k0 * (ds * ds * ds) + k1 * (ds * ds) + k2 * ds + k3;
+          vel = (k0 * 3) * (ds * ds) + (k1 * 2) * ds + k2;
+          acc = ((k0 * 3) * 2) * ds + k1 * 2;
         }
-        const double ds = time - tj;
-        const double pos = k0 * (ds * ds * ds) + k1 * (ds * ds) + k2 * ds + k3;
-        const double vel = (k0 * 3) * (ds * ds) + (k1 * 2) * ds + k2;
-        const double acc = ((k0 * 3) * 2) * ds + k1 * 2;
         const size_t o = (size_t)i * P + p;
         if (o_time) o_time[o] = (R)time;
         if (o_pos) o_pos[o] = (R)pos;
@@ -344,7 +443,8 @@ __global__ void __launch_bounds__(64) sample_kernel(SampleArgs g) {
 
 template <class R> void launch_param(const ParamArgs& a, cudaStream_t st) {
   const int block = 32, grid = (a.P + block - 1) / block;
-  param_kernel<R><<<grid, block, 0, st>>>(a);  // R = storage type
+  if (a.param_mode == SCB_PARAM_CONST_ACCEL) param_ca_kernel<R><<<grid, block, 0, st>>>(a);
+  else param_kernel<R><<<grid, block, 0, st>>>(a);  // R = storage type
 }
 template <class R> void launch_sample(const SampleArgs& a, cudaStream_t st) {
   const int block = 64, grid = (a.P + block - 1) / block;

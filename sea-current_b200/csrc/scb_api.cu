@@ -80,6 +80,7 @@ int validate(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, int
   stages = in->stages ? in->stages : (SCB_STAGE_SPLINE | SCB_STAGE_TIMING | SCB_STAGE_GEOMETRY);
   if (in->P < 0 || in->P > ctx->cfg.max_problems) return SCB_E_INVALID;
   if (in->lp_mode < SCB_LP_DEFAULT || in->lp_mode > SCB_LP_CLOSED_FORM) return SCB_E_INVALID;
+  if (in->param_mode != SCB_PARAM_SPLINE && in->param_mode != SCB_PARAM_CONST_ACCEL) return SCB_E_INVALID;
   if ((stages & SCB_STAGE_SPLINE) && (in->W < 2 || in->W > ctx->cfg.max_waypoints || !in->wx || !in->wy)) return SCB_E_INVALID;
   if ((stages & SCB_STAGE_TIMING) && (in->G < 2 || in->G > ctx->cfg.max_gridpoints)) return SCB_E_INVALID;
   if ((stages & SCB_STAGE_TIMING) && (!in->acc_lo || !in->acc_hi)) return SCB_E_INVALID;
@@ -152,16 +153,19 @@ int run_device(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, i
   // internal state of the recurrences is FP64 in both precision modes: in FP64 mode the caller's
   // K_lo / K_hi / t arrays double as that state, in FP32 mode it lives in scratch
   const bool f64 = sizeof(R) == 8;
-  void *dT = f64 ? out->t : nullptr, *dXb = nullptr, *dCp = nullptr;
+  void *dT = f64 ? out->t : nullptr, *dXb = nullptr, *dCp = nullptr, *dXsq = nullptr;
   if (do_timing) {
     void *dKlo = f64 ? out->K_lo : nullptr, *dKhi = f64 ? out->K_hi : nullptr, *dX = out->x;
     const size_t gp = (size_t)G * P * rs, gp8 = (size_t)G * P * 8;
     if (!dKlo && (rc = ensure(ctx, SL_K_LO, gp8, &dKlo))) return rc;
     if (!dKhi && (rc = ensure(ctx, SL_K_HI, gp8, &dKhi))) return rc;
     if (!dX && (rc = ensure(ctx, SL_X, gp, &dX))) return rc;
+    dXsq = dX;
     if (!dT && (rc = ensure(ctx, SL_T, gp8, &dT))) return rc;
-    if ((rc = ensure(ctx, SL_XB, gp8, &dXb))) return rc;
-    if ((rc = ensure(ctx, SL_CP, gp8, &dCp))) return rc;
+    if (in->param_mode == SCB_PARAM_SPLINE) {  // Thomas scratch; the const-accel parametrizer solves nothing
+      if ((rc = ensure(ctx, SL_XB, gp8, &dXb))) return rc;
+      if ((rc = ensure(ctx, SL_CP, gp8, &dCp))) return rc;
+    }
     ToppraArgs t{};
     t.P = P; t.G = G; t.L = dL; t.vel_lo = in->vel_lo; t.vel_hi = in->vel_hi;
     t.vel_lo_grid = in->vel_lo_grid; t.vel_hi_grid = in->vel_hi_grid;
@@ -180,6 +184,7 @@ int run_device(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, i
     q.t = f64 ? nullptr : out->t; q.v = out->v; q.a = out->a; q.omega = out->omega;
     q.t_buf = dT; q.X_buf = dXb; q.cp_buf = dCp; q.T_total = out->T_total; q.status = out->status;
     q.keep_X = want_stream ? 1 : 0;
+    q.param_mode = in->param_mode;
     launch_param<R>(q, st);
     ++launches;
   } else {
@@ -194,6 +199,7 @@ int run_device(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, i
     s.P = P; s.G = G; s.W = W; s.deg = deg; s.S_cap = out->S_cap;
     s.dt = in->dt > 0 ? in->dt : (double)0.02f;
     s.L = dL; s.vel_start = in->vel_start; s.vel_end = in->vel_end; s.t_buf = dT; s.X_buf = dXb;
+    s.x = dXsq; s.param_mode = in->param_mode;
     s.ctrl_x = dCx; s.ctrl_y = dCy; s.table = dTab; s.n_samples = dNs;
     s.s_time = out->s_time; s.s_pos = out->s_pos; s.s_vel = out->s_vel; s.s_acc = out->s_acc;
     s.s_px = out->s_px; s.s_py = out->s_py; s.s_omega = out->s_omega; s.status = out->status;

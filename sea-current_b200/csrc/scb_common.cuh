@@ -113,6 +113,7 @@ struct ParamArgs {
   void *T_total;                       // [P]
   int32_t* status;
   int keep_X;                          // 1: X_buf must hold the solved unknowns afterwards (the uniform-dt sampler reads them)
+  int param_mode;                      // SCB_PARAM_*
 };
 
 struct SampleArgs {
@@ -120,6 +121,8 @@ struct SampleArgs {
   double dt;
   const void *L, *vel_start, *vel_end;
   const void *t_buf, *X_buf;           // [G][P]
+  const void *x;                       // [G][P] sdot^2 (const-accel sampling)
+  int param_mode;                      // SCB_PARAM_*
   const void *ctrl_x, *ctrl_y, *table;
   int32_t* n_samples;                  // [P]
   void *s_time, *s_pos, *s_vel, *s_acc, *s_px, *s_py, *s_omega;  // [S_cap][P]

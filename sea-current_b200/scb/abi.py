@@ -10,6 +10,7 @@ SCB_REF_CUBIC, SCB_LAU_QUINTIC = 0, 1
 ARCLEN_TABLE = 101
 STAGE_SPLINE, STAGE_TIMING, STAGE_GEOMETRY = 1, 2, 4
 LP_DEFAULT, LP_SEIDEL, LP_CLOSED_FORM = 0, 1, 2
+PARAM_SPLINE, PARAM_CONST_ACCEL = 0, 1
 
 ST_OK, ST_ERR_UNKNOWN, ST_ERR_FAIL_CONTROLLABLE, ST_ERR_FAIL_FORWARD_PASS = 0, 1, 2, 3
 ST_ERR_UNINITIALIZED, ST_ERR_FAIL_FEASIBLE = 4, 5
@@ -37,6 +38,7 @@ class ScbBatchIn(C.Structure):
                 ("vel_start", C.c_void_p), ("vel_end", C.c_void_p),
                 ("path_len", C.c_void_p), ("obstacle_edges", C.c_void_p), ("stages", C.c_int32), ("lp_mode", C.c_int32),
                 ("nudge_positions", C.c_int32), ("n_obstacle_edges", C.c_int32),
+                ("param_mode", C.c_int32), ("reserved0", C.c_int32),
                 ("x_cap", C.c_double), ("dt", C.c_double), ("omega_max", C.c_double), ("acc_lat_max", C.c_double),
                 ("opt", ScbOpt)]
 

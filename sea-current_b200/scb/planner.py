@@ -8,6 +8,7 @@ no planning arithmetic here and no fallback: if the library cannot be loaded or 
 device exists, construction raises.
 """
 import ctypes as C
+import os
 
 import numpy as np
 
@@ -100,7 +101,7 @@ class BatchPlanner:
     def plan(self, wx=None, wy=None, vel_lo=None, vel_hi=None, acc_lo=None, acc_hi=None, G=101, start_angle=None,
              vel_lo_grid=None, vel_hi_grid=None, vel_start=None, vel_end=None, path_len=None, stages=0,
              outputs=ALL_OUTPUTS, S_cap=0, x_cap=0.0, dt=0.0, opt=None, out_buffers=None, resample_at=None, lp_mode=0,
-             nudge=False, omega_max=0.0, acc_lat_max=0.0, obstacle_edges=None):
+             nudge=False, omega_max=0.0, acc_lat_max=0.0, obstacle_edges=None, param_mode=0):
         """Host arrays in, host arrays out (scb_plan_batch).  `out_buffers` lets a caller pass
         preallocated (e.g. pinned) numpy arrays keyed by output name."""
         R = self.real
@@ -132,6 +133,7 @@ class BatchPlanner:
         bi.stages, bi.x_cap, bi.dt, bi.lp_mode = stages, x_cap, dt, lp_mode
         bi.omega_max, bi.acc_lat_max = omega_max, acc_lat_max
         bi.nudge_positions = 1 if nudge else 0
+        bi.param_mode = param_mode
         if obstacle_edges is not None and len(obstacle_edges):
             ed = np.ascontiguousarray(obstacle_edges, dtype=R).reshape(-1, 4)
             keep.append(ed)
@@ -174,7 +176,7 @@ class BatchPlanner:
 
     # ------------------------------------------------------------------ HBM-resident buffers
     def make_device_batch(self, inputs, G, outputs=ALL_OUTPUTS, S_cap=0, stages=0, x_cap=0.0, dt=0.0, opt=None, lp_mode=0,
-                          omega_max=0.0, acc_lat_max=0.0):
+                          omega_max=0.0, acc_lat_max=0.0, param_mode=0):
         """inputs: dict name -> torch CUDA tensor (dtype = ctx precision, contiguous).  Allocates
         the output tensors once and returns (batch_in, batch_out, result_tensors): the structs can be
         passed to run_device() any number of times without further allocation."""
@@ -196,6 +198,7 @@ class BatchPlanner:
                 setattr(bi, name, t.data_ptr())
         bi.stages, bi.x_cap, bi.dt, bi.lp_mode = stages, x_cap, dt, lp_mode
         bi.omega_max, bi.acc_lat_max = omega_max, acc_lat_max
+        bi.param_mode = param_mode
         bi.opt = opt if opt is not None else default_opt()
         res = {"status": torch.empty(P, dtype=torch.int32, device=dev),
                "fail_stage": torch.empty(P, dtype=torch.int32, device=dev)}
@@ -247,3 +250,63 @@ def gather_summaries(local_bytes, world, group=None):
     out = torch.empty(world * local_bytes.numel(), dtype=torch.uint8, device=local_bytes.device)
     dist.all_gather_into_tensor(out, local_bytes, group=group)
     return out
+
+
+def _parse_cpulist(text):
+    cpus = set()
+    for part in text.strip().split(","):
+        if not part:
+            continue
+        lo, _, hi = part.partition("-")
+        cpus.update(range(int(lo), int(hi or lo) + 1))
+    return cpus
+
+
+def gpu_local_cpus(device=0):
+    """CPUs of the NUMA node the GPU's PCIe root hangs off (sysfs; NVML when sysfs has no node), or None
+    when the platform exposes no locality (single node, VM without topology)."""
+    import torch
+    pr = torch.cuda.get_device_properties(device)
+    try:
+        bdf = "%04x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+        node = int(open("/sys/bus/pci/devices/%s/numa_node" % bdf).read())
+        if node >= 0:
+            return _parse_cpulist(open("/sys/devices/system/node/node%d/cpulist" % node).read()) or None
+    except (OSError, ValueError, AttributeError):
+        pass
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + str(pr.uuid)).encode())
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        cpus = {64 * w + b for w, m in enumerate(words) for b in range(64) if (int(m) >> b) & 1}
+        return cpus if cpus and len(cpus) < os.cpu_count() else None
+    except Exception:
+        return None
+
+
+class near_gpu:
+    """Context manager: run the enclosed host code on the GPU's own NUMA node.  Host buffers pinned inside
+    it are first-touched there, so the H2D / D2H DMA of scb_plan_batch never crosses the socket interconnect
+    (which on a two-socket box costs about 3x in D2H bandwidth).  The previous affinity mask is restored on
+    exit; pages stay where they were allocated.  A no-op when the platform shows no locality."""
+
+    def __init__(self, device=0):
+        self.device, self.prev, self.bound = device, None, None
+
+    def __enter__(self):
+        try:
+            cpus = gpu_local_cpus(self.device)
+            self.prev = os.sched_getaffinity(0)
+            want = (cpus or set()) & self.prev
+            if want and want != self.prev:
+                os.sched_setaffinity(0, want)
+                self.bound = want
+        except (OSError, AttributeError):
+            self.prev = None
+        return self
+
+    def __exit__(self, *exc):
+        if self.bound and self.prev:
+            os.sched_setaffinity(0, self.prev)
+        return False
