@@ -98,6 +98,18 @@ int ora_spline_param(int nseg, int dof, const double* coeffs, const double* brea
   return (int)sp.ts.size();
 }
 
+// ConstAccel parametrizer over the 1-DOF Hermite path of gen_vel_prof (0 -> L on s in [0, 1], end slopes vs / ve):
+// knot times ts [G] and q, q', q'' at `n_eval` times (tp:parametrizer/const_accel.cpp).
+void ora_const_accel_param(double L, double vs, double ve, int G, const double* gridpoints, const double* vsq, double* ts,
+                           int n_eval, const double* t_eval, double* q, double* qd, double* qdd) {
+  tp::PPoly path = tp::PPoly::hermite({{0.0}, {L}}, {{vs}, {ve}}, {0, 1});
+  tp::ConstAccelParam c = tp::const_accel_parametrizer(path, tp::Vec(gridpoints, gridpoints + G), tp::Vec(vsq, vsq + G));
+  for (int i = 0; i < G; ++i) ts[i] = c.ts[i];
+  for (int i = 0; i < n_eval; ++i) {
+    q[i] = c.eval_single(t_eval[i], 0)[0]; qd[i] = c.eval_single(t_eval[i], 1)[0]; qdd[i] = c.eval_single(t_eval[i], 2)[0];
+  }
+}
+
 // Clamped cubic spline through (t_i, y_i) with end slopes (test_cubic_spline*.cpp vs scipy).
 void ora_cubic_spline(int n, const double* t, const double* y, double bc0, double bc1, int solve_mode, int n_eval,
                       const double* t_eval, double* out) {

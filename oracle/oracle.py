@@ -97,6 +97,15 @@ def spline_param(coeffs, breaks, gridpoints, vsq, t_eval_fn=None, solve_mode=0, 
     return ts[:n], q, qd, qdd
 
 
+def const_accel_param(L, vel_start, vel_end, gridpoints, vsq, t_eval):
+    """parametrizer::ConstAccel over gen_vel_prof's Hermite path: (ts, q, qd, qdd at t_eval)."""
+    gp = _d(gridpoints); G = len(gp); te = _d(t_eval)
+    ts = np.zeros(G); q = np.zeros(len(te)); qd = np.zeros(len(te)); qdd = np.zeros(len(te))
+    lib().ora_const_accel_param(C.c_double(L), C.c_double(vel_start), C.c_double(vel_end), G, _p(gp), _p(_d(vsq)), _p(ts),
+                                len(te), _p(te), _p(q), _p(qd), _p(qdd))
+    return ts, q, qd, qdd
+
+
 def cubic_spline(t, y, bc0, bc1, t_eval, solve_mode=0):
     t = _d(t); y = _d(y); te = _d(t_eval)
     out = np.zeros(len(te))

@@ -108,3 +108,25 @@ def test_gpu_const_accel_fp32_storage_and_bad_mode(oracle):
     with pytest.raises(scb.ScbError):
         pl.plan(wx=wx, wy=wy, G=G, param_mode=7, **lim)
     pl.close()
+
+
+def test_oracle_matches_python_toppra_const_accel(oracle, golden_dir):
+    """The oracle's ConstAccel against the reference's own Python ParametrizeConstAccel on the pinned
+    parametrizations (tests/golden/gen_pytoppra_const_accel.py).  Knot accelerations are not compared: the two
+    siblings pick different intervals exactly at a knot (see the generator's docstring)."""
+    import json
+    import os
+    gold = json.load(open(os.path.join(golden_dir, "pytoppra_const_accel_golden.json")))
+    G = gold["G"]
+    assert len(gold["cases"]) == 4
+    for c in gold["cases"]:
+        ts_w = np.array(c["ts"])
+        t_all = np.concatenate([ts_w, c["t_eval"]])
+        ts, q, qd, qdd = oracle.const_accel_param(c["L"], c["vel_start"], c["vel_end"], np.linspace(0, 1, G), c["x"], t_all)
+        np.testing.assert_allclose(ts, ts_w, rtol=1e-13, err_msg=c["name"])
+        L = c["L"]
+        np.testing.assert_allclose(q[:G], c["q_knots"], rtol=1e-12, atol=1e-13 * L, err_msg=c["name"])
+        np.testing.assert_allclose(qd[:G], c["qd_knots"], rtol=1e-10, atol=1e-12 * L, err_msg=c["name"])
+        np.testing.assert_allclose(q[G:], c["q"], rtol=1e-12, atol=1e-13 * L, err_msg=c["name"])
+        np.testing.assert_allclose(qd[G:], c["qd"], rtol=1e-11, atol=1e-13 * L, err_msg=c["name"])
+        np.testing.assert_allclose(qdd[G:], c["qdd"], rtol=1e-10, atol=1e-12 * np.abs(c["qdd"]).max(), err_msg=c["name"])
