@@ -10,8 +10,10 @@ rollouts, 1,000 gridpoints"), the batch the north_star's roofline target is quot
 same batch per rank (weak scaling), per-problem summary records all-gathered over NCCL.
 
 value      whole-job trajectories/s, inputs and outputs resident in HBM (CUDA events on the ctx stream,
-           max over ranks)
-e2e        same metric through scb_plan_batch with pinned HOST buffers (H2D + kernels + D2H timed)
+           max over ranks); batches are independent, so two are kept in flight on two contexts
+           (config.in_flight; step i runs on context i % 2) -- every step is still one full pass over one batch
+e2e        same metric through scb_plan_batch with pinned HOST buffers (H2D + kernels + D2H timed), one host
+           thread per context
 roofline   dominant kernel (by duration): algorithmic flops (or bytes) / its mean launch duration against the pipe
            that binds it -- the FP64/FP32 vector pipe (measured FMA peak, profiles/r1_fp_peak.json) or HBM
            (MEASURED_PEAKS.json); `kernels` lists every kernel of the step against both, `path` the whole step
@@ -46,6 +48,8 @@ def parse():
     ap.add_argument("--problems", type=int, default=0, help="override the per-rank batch size")
     ap.add_argument("--parametrizer", default="spline", choices=["spline", "const_accel"],
                     help="spline = what the reference's gen_vel_prof builds (the headline); const_accel = toppra's ConstAccel")
+    ap.add_argument("--in-flight", type=int, default=0,
+                    help="independent contexts (streams) the batches alternate over; 0 = 2 (1 for C4, whose outputs are 50 GB)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
@@ -190,26 +194,38 @@ def main():
     P, W = w["wx"].shape
     G = w["G"]
     mode = "lau_quintic"
-    pl = scb.BatchPlanner(local, a.precision, mode, max_problems=P, max_waypoints=W, max_gridpoints=G)
+    # Batches are independent, so a planner keeps `nfl` of them in flight, each on its own context (= stream + scratch,
+    # the C ABI's unit of concurrency: one scb_ctx per host thread): the tail of one batch's FP64-bound path / arc
+    # kernels overlaps the HBM- and latency-bound toppra / param kernels of the other.  Step i runs on context i % nfl.
+    nfl = a.in_flight if a.in_flight > 0 else (1 if a.config == "C4" else 2)
+    pls = [scb.BatchPlanner(local, a.precision, mode, max_problems=P, max_waypoints=W, max_gridpoints=G) for _ in range(nfl)]
+    pl = pls[0]
     tdt = torch.float64 if a.precision == "fp64" else torch.float32
     opt = scb.default_opt(move_waypoints=1)
     inputs = {k: torch.from_numpy(np.ascontiguousarray(v)).to(dev, dtype=tdt) for k, v in w.items() if k != "G"}
     pm = 1 if a.parametrizer == "const_accel" else 0
-    bi, bo, res = pl.make_device_batch(inputs, G=G, opt=opt, param_mode=pm)
-    stream = torch.cuda.ExternalStream(pl.stream(), device=dev)
+    batches = [q.make_device_batch(inputs, G=G, opt=opt, param_mode=pm) for q in pls]
+    bi, bo, res = batches[0]
+    streams = [torch.cuda.ExternalStream(q.stream(), device=dev) for q in pls]
+    stream = streams[0]
     nrec = P * 32
+    nstep = [0]
 
     def step():
-        pl.run_device(bi, bo, sync=False)
-        rec = pl.pack_summary(P, res)
+        c = nstep[0] % nfl
+        nstep[0] += 1
+        pls[c].run_device(batches[c][0], batches[c][1], sync=False)
+        rec = pls[c].pack_summary(P, batches[c][2])
         if world > 1:
-            with torch.cuda.stream(stream):
+            with torch.cuda.stream(streams[c]):
                 rec = scb.gather_summaries(rec, world)
         return rec
 
-    for _ in range(max(a.warmup, 3)):
+    for _ in range(max(a.warmup, 3) + (max(a.warmup, 3) % nfl)):
         rec = step()
-    pl.synchronize(); torch.cuda.synchronize()
+    for q in pls:
+        q.synchronize()
+    torch.cuda.synchronize()
     ok_frac = float((res["status"] == 0).float().mean().item())
     # ---- device-resident timing: K steps, one event pair on the ctx stream
     sampler = ClockSampler(local)
@@ -218,9 +234,13 @@ def main():
     torch.cuda.synchronize()
     sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record(stream)
+    e0.record(stream)  # every context is idle here (synchronize above), so stream 0's clock starts the region
     for _ in range(a.steps):
         rec = step()
+    for sx in streams[1:]:  # the region ends when the last context has finished: stream 0 waits for the others
+        ev = torch.cuda.Event()
+        ev.record(sx)
+        stream.wait_event(ev)
     e1.record(stream)
     if world > 1:
         dist.barrier()
@@ -300,7 +320,7 @@ def main():
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": scaling, "vs_baseline": None,
             "dtype": "f64" if a.precision == "fp64" else "f32", "data": "synthetic",
             "config": dict(cfg, P_per_rank=P, spline="lau_quintic, optimiser K=%d move_waypoints=1" % opt.iters,
-                           parametrizer=a.parametrizer,
+                           parametrizer=a.parametrizer, in_flight=nfl,
                            l2="outputs streamed per step (%.2f GB) exceed the 126 MB L2; no flush" % (path_bytes / 1e9),
                            ok_fraction=ok_frac),
             "stage_ms": stage_ms, "roofline": roof, "clocks": clocks, "gpu_launches": launches_per_step * a.steps}
@@ -313,19 +333,33 @@ def main():
         numa = scb.near_gpu(local) if os.environ.get("SCB_BENCH_NUMA", "1") != "0" else contextlib.nullcontext()
         with numa:
             host_in = {k: torch.from_numpy(np.ascontiguousarray(v, dtype=pl.real)).pin_memory().numpy() for k, v in w.items() if k != "G"}
-            bufs = {"status": torch.empty(P, dtype=torch.int32).pin_memory().numpy(),
-                    "fail_stage": torch.empty(P, dtype=torch.int32).pin_memory().numpy()}
-            for n in names:
-                bufs[n] = torch.empty(pl.out_shape(n, P, W, G, 0), dtype=tdt).pin_memory().numpy()
-            h2d = sum(v.nbytes for v in host_in.values()); d2h = sum(v.nbytes for v in bufs.values())
-            k2 = max(2, min(a.steps, 5))
-            for _ in range(2):
-                pl.plan(G=G, outputs=names, out_buffers=bufs, opt=opt, param_mode=pm, **host_in)
+            hbufs = []
+            for _ in range(nfl):
+                bufs = {"status": torch.empty(P, dtype=torch.int32).pin_memory().numpy(),
+                        "fail_stage": torch.empty(P, dtype=torch.int32).pin_memory().numpy()}
+                for n in names:
+                    bufs[n] = torch.empty(pl.out_shape(n, P, W, G, 0), dtype=tdt).pin_memory().numpy()
+                hbufs.append(bufs)
+            h2d = sum(v.nbytes for v in host_in.values()); d2h = sum(v.nbytes for v in hbufs[0].values())
+            k2 = max(2, min(a.steps, 10))
+            k2 += (-k2) % nfl  # the same number of calls on every context
+
+            def calls(c, n):  # one host thread per context, as the C ABI prescribes; ctypes drops the GIL inside the call
+                for _ in range(n):
+                    pls[c].plan(G=G, outputs=names, out_buffers=hbufs[c], opt=opt, param_mode=pm, **host_in)
+
+            def run(n_each):
+                th = [threading.Thread(target=calls, args=(c, n_each)) for c in range(nfl)]
+                for t_ in th:
+                    t_.start()
+                for t_ in th:
+                    t_.join()
+
+            run(2)
             if world > 1:
                 dist.barrier()
             t0 = time.perf_counter()
-            for _ in range(k2):
-                pl.plan(G=G, outputs=names, out_buffers=bufs, opt=opt, param_mode=pm, **host_in)
+            run(k2 // nfl)
             dt = time.perf_counter() - t0
             if world > 1:
                 t = torch.tensor([dt], device=dev, dtype=torch.float64)
@@ -335,13 +369,14 @@ def main():
         line["e2e"] = {"value": cfg["P_global"] * k2 / dt if scaling == "weak" else cfg["P_global"] * k2 / dt, "unit": UNIT,
                        "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": k2,
                        "last_step_ms": {k: tm[k] for k in ("h2d_ms", "d2h_ms", "total_ms")},
-                       "outputs": list(names),
+                       "outputs": list(names), "host_threads": nfl,
                        "numa_bound_cpus": len(getattr(numa, "bound", None) or ())}
     if rank == 0 and world == 1 and not a.no_cpu:  # N=1 only (torchrun pins OMP_NUM_THREADS=1 per rank)
         line["cpu_baseline"] = cpu_baseline_run(w, G, a.cpu_seconds, 0)
     if rank == 0:
         print(json.dumps(line))
-    pl.close()
+    for q in pls:
+        q.close()
     if world > 1:
         dist.destroy_process_group()
 
