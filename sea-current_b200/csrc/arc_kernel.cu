@@ -81,8 +81,10 @@ __global__ void __launch_bounds__(kArcThreads, 3) arc_kernel(PathArgs g) {
       R dx = kx[DEG - 1], dy = ky[DEG - 1];
 #pragma unroll
       for (int j = DEG - 2; j >= 0; --j) { dx = dx * u + kx[j]; dy = dy * u + ky[j]; }
-      const R n2 = dx * dx + dy * dy;
-      return n2 > 0 ? n2 * fast_rsqrt<R>(n2) : (R)0;
+      // full-precision rsqrt here: a one-sided 1e-13 error in every sample would bias the path length, and the
+      // timing stage differentiates what it derives from it (see rsqrt_n1 in scb_common.cuh)
+      const R n2 = fma(dy, dy, fma(dx, dx, speed_floor<R>()));  // > 0 also at a cusp: no guard around the rsqrt
+      return n2 * fast_rsqrt<R>(n2);
     };
     const R a = fmin((R)k * (R)0.01, (R)1), b = fmin((R)(k + 1) * (R)0.01, (R)1);  // sc:851
     const R half = (b - a) / 2, mid = (b + a) / 2;

@@ -207,10 +207,10 @@ __device__ __forceinline__ void gridpoint_geometry(int i, int N, double step, co
     R dx = kx[DEG - 1], dy = ky[DEG - 1];
 #pragma unroll
     for (int j = DEG - 2; j >= 0; --j) { dx = dx * u + kx[j]; dy = dy * u + ky[j]; }
-    return dx * dx + dy * dy;
+    return fma(dy, dy, fma(dx, dx, speed_floor<R>()));  // > 0 also at a cusp: no guard around the rsqrt
   };
-  auto speed = [&](R u) { const R n2 = speed2(u); return n2 > 0 ? n2 * fast_rsqrt<R>(n2) : (R)0; };
-  auto inv_speed = [&](R u) { const R n2 = speed2(u); return n2 > 0 ? fast_rsqrt<R>(n2) : (R)0; };
+  auto speed = [&](R u) { const R n2 = speed2(u); return n2 * rsqrt_n1<R>(n2); };
+  auto inv_speed = [&](R u) { return rsqrt_n1<R>(speed2(u)); };
   // Start: the cubic Hermite inverse u(s) on [c_k, c_k+1] (end values 0 and h, end slopes 1/|B'|): its error
   // is ~ds^4 |d4u/ds4| / 384, i.e. ~1e-8 h for a smooth piece against ~1e-3 h for linear interpolation, so
   // that ONE Newton step on the quadrature normally reaches the root; near a cusp the clamps keep the
@@ -248,7 +248,7 @@ __device__ __forceinline__ void gridpoint_geometry(int i, int N, double step, co
     R x2 = (R)(DEG - 1) * kx[DEG - 1], y2 = (R)(DEG - 1) * ky[DEG - 1];
 #pragma unroll
     for (int j = DEG - 3; j >= 0; --j) { x2 = x2 * ue + (R)(j + 1) * kx[j + 1]; y2 = y2 * ue + (R)(j + 1) * ky[j + 1]; }
-    const R n2 = x1 * x1 + y1 * y1, rn = n2 > 0 ? fast_rsqrt<R>(n2) : (R)0;
+    const R rn = rsqrt_n1<R>(fma(y1, y1, fma(x1, x1, speed_floor<R>())));
     const R delta = (F - target) * rn;
     du = fmin(fmax(du - delta, (R)0), h);
     const R ad = fabs(delta);
@@ -266,7 +266,7 @@ __device__ __forceinline__ void gridpoint_geometry(int i, int N, double step, co
   R x2 = (R)(DEG - 1) * kx[DEG - 1], y2 = (R)(DEG - 1) * ky[DEG - 1];
 #pragma unroll
   for (int j = DEG - 3; j >= 0; --j) { x2 = x2 * u + (R)(j + 1) * kx[j + 1]; y2 = y2 * u + (R)(j + 1) * ky[j + 1]; }
-  const R n2 = x1 * x1 + y1 * y1, rn = fast_rsqrt<R>(n2);
+  const R rn = fast_rsqrt<R>(fma(y1, y1, fma(x1, x1, speed_floor<R>())));  // cubed below: full precision
   kap = (x1 * y2 - y1 * x2) * (rn * rn * rn);
 }
 

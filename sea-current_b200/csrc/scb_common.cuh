@@ -43,6 +43,25 @@ template <> __device__ __forceinline__ double fast_rsqrt<double>(double x) {
   return fma(y * e, p, y);
 }
 
+// 1/sqrt(x) to ~1e-13 relative: the same seed and ONE second-order step y (1 + e/2), error 3/8 e^2 <= 8.5e-14
+// (|e| <= 2^-21).  4 FP64 instructions and no constant to materialise (the 0.5 is an immediate operand); for
+// the iterates of the arc-length inversion (a root's error is the quadrature's error over the speed: 1e-13 h), not
+// for the table itself -- the error is one-sided (always low), so summed over a path it biases the length by ~3e-14,
+// which the timing stage's difference quotients amplify past 1e-9 -- and not for anything a sign decision hangs on.
+template <class R> __device__ __forceinline__ R rsqrt_n1(R x);
+template <> __device__ __forceinline__ float rsqrt_n1<float>(float x) { return rsqrtf(x); }
+template <> __device__ __forceinline__ double rsqrt_n1<double>(double x) {
+  double y;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+  const double e = fma(-x * y, y, 1.0);
+  return fma(y * e, 0.5, y);
+}
+// Smallest addend that keeps |B'|^2 a positive normal number (a cusp gives exactly 0): added inside the FMA that
+// forms dx^2 + dy^2, it replaces the compare-and-select guard around the reciprocal square root.
+template <class R> __device__ __forceinline__ R speed_floor();
+template <> __device__ __forceinline__ double speed_floor<double>() { return 1e-300; }
+template <> __device__ __forceinline__ float speed_floor<float>() { return 1e-30f; }
+
 // 1/x for a normal x.  FP64: MUFU.RCP64H seed and two Newton steps (4 FMAs) instead of the ~20-instruction
 // IEEE division sequence; relative error <= ~1 ulp.  Used where the result feeds a 1e-9 tolerance, never in the
 // bit-exact Seidel kernel.

@@ -27,5 +27,5 @@ def run(n_ctx, steps):
     return (time.perf_counter() - t0) / steps * 1e3
 
 for rep in range(2):
-    for n in (1, 2, 3, 4):
+    for n in (1, 2):
         print("%d ctx   %.3f ms/step" % (n, run(n, 48)))
