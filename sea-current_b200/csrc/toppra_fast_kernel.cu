@@ -46,9 +46,14 @@ struct Slab { double al, be, lo, hi; };
 
 __device__ __forceinline__ Slab orient(double al, double be, double lo, double hi, double nlo, double nhi) {
   // nlo = -lo, nhi = -hi (constants of the problem)
-  const bool neg = al < 0;
+  // the sign of al is read and applied as a bit (integer compare, one XOR into be's high word): no FP64-pipe
+  // compare and no negate-then-select; al = -0.0 mirrors a slab that has no u in it, which is the same slab
+  const int sgn = __double2hiint(al) & 0x80000000;
+  const bool neg = sgn != 0;
   Slab s;
-  s.al = fabs(al); s.be = neg ? -be : be; s.lo = neg ? nhi : lo; s.hi = neg ? nlo : hi;
+  s.al = fabs(al);
+  s.be = __hiloint2double(__double2hiint(be) ^ sgn, __double2loint(be));
+  s.lo = neg ? nhi : lo; s.hi = neg ? nlo : hi;
   return s;
 }
 
@@ -57,7 +62,7 @@ __device__ __forceinline__ Slab orient(double al, double be, double lo, double h
 // (off the serial chain).
 __device__ __forceinline__ bool pair_apply(double D, double rD, double E1, double E2, double& xl, double& xh) {
   const double q1 = E1 * rD, q2 = E2 * rD;
-  const bool pos = D > 0, zero = D == 0;
+  const bool pos = __double2hiint(D) >= 0, zero = D == 0;  // pos only matters when D != 0 (integer compare on the sign)
   const double hc = pos ? q1 : q2, lc = pos ? q2 : q1;
   xh = dmin(xh, zero ? CUDART_INF : hc);
   xl = dmax(xl, zero ? -CUDART_INF : lc);
@@ -176,6 +181,20 @@ __global__ void __launch_bounds__(64) toppra_fast_kernel(ToppraArgs g) {
     double s = 0.0, a = qd(s), b = qdd(s);
     bool go = true;
     size_t ox = p;  // position of gridpoint i in the [G][P] arrays
+    // The velocity box of gridpoint i can only bite at i = 0: for i >= 1 the pinned x_i was clamped into K_i, and the
+    // backward pass built K_i inside that very box (exact selects, no rounding), so max(xlo, x_i) = min(xhi, x_i) = x_i.
+    // Stage 0 starts from x_0 = vel_start^2 = 0, which a positive lower velocity limit excludes (seidel.cpp:73-76).
+    bool ok0;
+    double xf0;
+    {
+      double lo = vlo, hi = vhi, xlo, xhi;
+      if (GRID) { lo = (double)vlg[ox]; hi = (double)vhg[ox]; }
+      if (CURV) curvature_cap((double)kap[ox], om_max, al_max, lo, hi);
+      vel_xbound(a, lo, hi, xlo, xhi);  // validated by the backward pass
+      const double lo1 = dmax(xlo, xi), hi1 = dmin(xhi, xi);
+      ok0 = !(lo1 > hi1 && (lo1 - hi1 > dmax(fabs(lo1), fabs(hi1)) * ftol::rel_tol));
+      xf0 = lo1 > hi1 ? (lo1 + hi1) / 2 : xi;
+    }
 #pragma unroll 1
     for (int i0 = 0; i0 < N && go; i0 += kTU) {
       double kl[kTU], kh[kTU];
@@ -190,19 +209,13 @@ __global__ void __launch_bounds__(64) toppra_fast_kernel(ToppraArgs g) {
         if (go && i < N) {
           const double sn2 = i + 1 == N ? 1.0 : (double)(i + 1) * step, delta = sn2 - s, twod = 2.0 * delta;
           const double an2 = qd(sn2), bn2 = qdd(sn2);
-          double lo = vlo, hi = vhi, xlo, xhi;
-          if (GRID) { lo = (double)vlg[ox]; hi = (double)vhg[ox]; }
-          if (CURV) curvature_cap((double)kap[ox], om_max, al_max, lo, hi);
-          vel_xbound(a, lo, hi, xlo, xhi);  // validated by the backward pass
           const Slab s1 = orient(a, b, Al, Ah, nAl, nAh);
           const Slab s2 = orient(fma(twod, bn2, an2), bn2, Al, Ah, nAl, nAh);
           a = an2; b = bn2; s = sn2;
           const double r0 = fast_rcp<double>(twod), r1 = fast_rcp<double>(s1.al), r2 = fast_rcp<double>(s2.al);
           const double klo = kl[u], khi = kh[u];
-          // a box that misses x_i by more than the tolerance is infeasible (seidel.cpp:73-76)
-          const double lo1 = dmax(xlo, xi), hi1 = dmin(xhi, xi);
-          bool ok = !(lo1 > hi1 && (lo1 - hi1 > dmax(fabs(lo1), fabs(hi1)) * ftol::rel_tol));
-          const double xf = lo1 > hi1 ? (lo1 + hi1) / 2 : xi;
+          bool ok = i == 0 ? ok0 : true;
+          const double xf = i == 0 ? xf0 : xi;
           // slabs without u (al = 0) only constrain x
           const double u0 = (khi - xf) * r0;
           const double u1 = s1.al > 0 ? fma(-s1.be, xf, s1.hi) * r1 : CUDART_INF;

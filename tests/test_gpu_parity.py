@@ -166,13 +166,21 @@ def test_infeasible_and_bad_inputs_verdicts(planners, oracle, lp_mode):
     vel_hi[8] = 1e-6; vel_lo[8] = -1e-6
     acc_lo[9] = 0.0                              # cannot brake: infeasible near the end
     acc_hi[10] = 0.0                             # cannot accelerate from rest
-    res = pl.plan(wx=wx, wy=wy, vel_lo=vel_lo, vel_hi=vel_hi, acc_lo=acc_lo, acc_hi=acc_hi, G=G, lp_mode=lp_mode)
-    ref, _ = oracle.plan_batch(wx=wx, wy=wy, vel_lo=vel_lo, vel_hi=vel_hi, acc_lo=acc_lo, acc_hi=acc_hi, G=G)
+    # q'(0) = 0.3 > 0 and a positive lower velocity limit: the box of gridpoint 0 excludes the start state x_0 = 0,
+    # the one stage of the forward pass where the box (and not the controllable set) decides
+    vel_start = np.zeros(P); vel_end = np.zeros(P)
+    vel_start[11] = 0.3; vel_end[11] = 0.3; vel_lo[11] = 0.01
+    vel_start[12] = 0.3; vel_end[12] = 0.2       # non-zero end slopes, feasible
+    res = pl.plan(wx=wx, wy=wy, vel_lo=vel_lo, vel_hi=vel_hi, acc_lo=acc_lo, acc_hi=acc_hi, G=G, lp_mode=lp_mode,
+                  vel_start=vel_start, vel_end=vel_end)
+    ref, _ = oracle.plan_batch(wx=wx, wy=wy, vel_lo=vel_lo, vel_hi=vel_hi, acc_lo=acc_lo, acc_hi=acc_hi, G=G,
+                               vel_start=vel_start, vel_end=vel_end)
+    assert ref["status"][11] == 3 and ref["fail_stage"][11] == 0 and ref["status"][12] == 0  # FAIL_FORWARD_PASS at stage 0
     np.testing.assert_array_equal(res["status"], ref["status"])
     ok = ref["status"] == 0
     np.testing.assert_array_equal(res["fail_stage"][ref["status"] < 16], ref["fail_stage"][ref["status"] < 16])
     assert res["status"][4] == 16 and res["status"][5] == 16 and res["status"][3] == 17
-    assert res["status"][1] in (2, 3) and ok.sum() >= P - 8
+    assert res["status"][1] in (2, 3) and ok.sum() >= P - 9
     # problem 7 (|acc| <= 1e-9) has sdot^2 ~ 1e-11: the solvers' absolute row tolerance of 1e-13
     # (seidel-internal.hpp:57) is 1 % of it, so only the bit-exact Seidel back end can track the oracle to 1e-9
     normal = ok.copy(); normal[7] = False
