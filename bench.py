@@ -51,6 +51,9 @@ def parse():
     ap.add_argument("--in-flight", type=int, default=0,
                     help="independent contexts (streams) the batches alternate over; 0 = 2 (1 for C4, whose outputs are 50 GB)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--host-chunk", type=int, default=0,
+                    help="e2e leg: problems per pipelined chunk of scb_plan_batch (0 = the library's default, -1 = one chunk)")
+    ap.add_argument("--e2e-threads", type=int, default=0, help="e2e leg: host threads (= contexts) calling at once; 0 = in-flight")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
     return ap.parse_args()
@@ -341,15 +344,18 @@ def main():
                     bufs[n] = torch.empty(pl.out_shape(n, P, W, G, 0), dtype=tdt).pin_memory().numpy()
                 hbufs.append(bufs)
             h2d = sum(v.nbytes for v in host_in.values()); d2h = sum(v.nbytes for v in hbufs[0].values())
+            nth = min(nfl, a.e2e_threads) if a.e2e_threads > 0 else nfl
             k2 = max(2, min(a.steps, 10))
-            k2 += (-k2) % nfl  # the same number of calls on every context
+            k2 += (-k2) % nth  # the same number of calls on every context
+            for q in pls:
+                q.set_host_chunk(a.host_chunk)
 
             def calls(c, n):  # one host thread per context, as the C ABI prescribes; ctypes drops the GIL inside the call
                 for _ in range(n):
                     pls[c].plan(G=G, outputs=names, out_buffers=hbufs[c], opt=opt, param_mode=pm, **host_in)
 
             def run(n_each):
-                th = [threading.Thread(target=calls, args=(c, n_each)) for c in range(nfl)]
+                th = [threading.Thread(target=calls, args=(c, n_each)) for c in range(nth)]
                 for t_ in th:
                     t_.start()
                 for t_ in th:
@@ -359,7 +365,7 @@ def main():
             if world > 1:
                 dist.barrier()
             t0 = time.perf_counter()
-            run(k2 // nfl)
+            run(k2 // nth)
             dt = time.perf_counter() - t0
             if world > 1:
                 t = torch.tensor([dt], device=dev, dtype=torch.float64)
@@ -369,7 +375,8 @@ def main():
         line["e2e"] = {"value": cfg["P_global"] * k2 / dt if scaling == "weak" else cfg["P_global"] * k2 / dt, "unit": UNIT,
                        "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": k2,
                        "last_step_ms": {k: tm[k] for k in ("h2d_ms", "d2h_ms", "total_ms")},
-                       "outputs": list(names), "host_threads": nfl,
+                       "outputs": list(names), "host_threads": nth,
+                       "host_chunk": a.host_chunk if a.host_chunk else "auto (8192 problems: kernels of chunk c+1 over the D2H of chunk c)",
                        "numa_bound_cpus": len(getattr(numa, "bound", None) or ())}
     if rank == 0 and world == 1 and not a.no_cpu:  # N=1 only (torchrun pins OMP_NUM_THREADS=1 per rank)
         line["cpu_baseline"] = cpu_baseline_run(w, G, a.cpu_seconds, 0)

@@ -202,8 +202,14 @@ void scb_default_opt(scb_opt* opt);
 int scb_create(scb_ctx** out, const scb_config* cfg);
 int scb_destroy(scb_ctx* ctx);
 
-/* Host buffers in, host buffers out: H2D copy, kernels, D2H copy, synchronous. */
+/* Host buffers in, host buffers out: H2D copy, kernels, D2H copy, synchronous.  A batch of more than one chunk of
+ * problems is pipelined: the kernels of chunk c+1 overlap the D2H of chunk c (second stream, two sets of device
+ * mirrors), so device memory is sized by the chunk, not by P.  scb_timing of such a call: total_ms = the call,
+ * d2h_ms = first D2H byte to last, h2d_ms = 0 (folded into the chunks), stage times = the last chunk's. */
 int scb_plan_batch(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out);
+/* problems per chunk of scb_plan_batch: 0 = automatic (8,192 once P >= 16,384, else one chunk), < 0 = never chunk.
+ * Results do not depend on it (problems are independent). */
+int scb_set_host_chunk(scb_ctx* ctx, int32_t problems);
 
 /* Device buffers in and out (already resident in HBM); enqueued on the ctx stream and
  * synchronised before returning unless `async` is non-zero. */

@@ -18,6 +18,7 @@
 namespace {
 
 struct Slot { void* p = nullptr; size_t bytes = 0; };
+constexpr int kAutoHostChunk = 8192;  // scb_plan_batch: problems per chunk when the caller set none
 
 enum SlotId {
   // scratch used when the caller did not ask for the corresponding output
@@ -37,8 +38,11 @@ enum SlotId {
 struct scb_ctx {
   scb_config cfg;
   cudaStream_t stream = nullptr;
-  cudaEvent_t ev[8] = {};
-  Slot slot[SL_COUNT];
+  cudaStream_t copy_stream = nullptr;   // D2H of chunk c while chunk c+1 computes (scb_plan_batch)
+  cudaEvent_t ev[9] = {}, ev_done[2] = {}, ev_copied[2] = {};
+  Slot slot[2 * SL_COUNT];              // second half: mirror set 1 of the chunked host call
+  int host_chunk = 0;                   // scb_set_host_chunk
+  bool piped = false;
   scb_timing timing = {};
   bool timing_pending = false, host_call = false, split_spline = false;
   char err[256] = {0};
@@ -235,7 +239,8 @@ void collect_timing(scb_ctx* ctx) {
   auto el = [&](int a, int b) { float ms = 0; cudaEventElapsedTime(&ms, ctx->ev[a], ctx->ev[b]); return ms; };
   t.spline_ms = el(1, 2); t.toppra_ms = el(2, 3); t.param_ms = el(3, 4); t.sample_ms = el(4, 5);
   t.path_ms = ctx->split_spline ? el(1, 7) : 0; t.arc_ms = ctx->split_spline ? el(7, 2) : 0;
-  if (ctx->host_call) { t.h2d_ms = el(0, 1); t.d2h_ms = el(5, 6); t.total_ms = el(0, 6); }
+  if (ctx->host_call && ctx->piped) { t.h2d_ms = 0; t.d2h_ms = el(8, 6); t.total_ms = el(0, 6); }  // stages: last chunk
+  else if (ctx->host_call) { t.h2d_ms = el(0, 1); t.d2h_ms = el(5, 6); t.total_ms = el(0, 6); }
   else { t.h2d_ms = 0; t.d2h_ms = 0; t.total_ms = el(1, 5); }
   ctx->timing_pending = false;
 }
@@ -299,6 +304,9 @@ int scb_destroy(scb_ctx* ctx) {
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
   for (auto& s : ctx->slot) if (s.p) cudaFree(s.p);
   for (auto& e : ctx->ev) if (e) cudaEventDestroy(e);
+  for (auto& e : ctx->ev_done) if (e) cudaEventDestroy(e);
+  for (auto& e : ctx->ev_copied) if (e) cudaEventDestroy(e);
+  if (ctx->copy_stream) { cudaStreamSynchronize(ctx->copy_stream); cudaStreamDestroy(ctx->copy_stream); }
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
   return SCB_OK;
@@ -324,6 +332,12 @@ int scb_synchronize(scb_ctx* ctx) {
   return SCB_OK;
 }
 
+// Host buffers in, host buffers out.  A large batch is planned in chunks of `chunk` problems: the kernels of
+// chunk c+1 run on the ctx stream while the trajectory records of chunk c travel to the host on a second
+// stream (two sets of device mirrors, ping-pong), so the call costs the D2H time plus ONE chunk of kernels
+// instead of their sum.  Chunks are compact on the device ([G][Pc]); the caller's [G][P] arrays are filled by
+// pitched copies.  Problems are independent, so the results do not depend on the chunking
+// (tests/test_gpu_parity.py::test_host_chunks_bit_identical).
 int scb_plan_batch(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out) {
   int stages;
   int rc = validate(ctx, in, out, stages);
@@ -333,85 +347,133 @@ int scb_plan_batch(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* ou
   if (P == 0) return SCB_OK;
   const size_t rs = real_size(ctx);
   cudaStream_t st = ctx->stream;
-  scb_batch_in din = *in;
-  scb_batch_out dout = *out;
-  SCB_CUDA(cudaEventRecord(ctx->ev[0], st));
-  // ---- H2D: one cudaMemcpyAsync per input array (full speed when the caller's memory is pinned)
-  auto up = [&](int id, const void* src, size_t bytes, const void** dst) -> int {
-    if (!src) { *dst = nullptr; return SCB_OK; }
-    void* d;
-    int r = ensure(ctx, id, bytes, &d);
-    if (r) return r;
-    cudaError_t e = cudaMemcpyAsync(d, src, bytes, cudaMemcpyHostToDevice, st);
-    if (e != cudaSuccess) return fail_cuda(ctx, e, "cudaMemcpyAsync H2D");
-    *dst = d;
-    return SCB_OK;
-  };
+  int chunk = P;
+  if (ctx->host_chunk > 0) chunk = ctx->host_chunk < P ? ctx->host_chunk : P;
+  else if (ctx->host_chunk == 0 && P >= 2 * kAutoHostChunk) chunk = kAutoHostChunk;
+  const int nchunks = (P + chunk - 1) / chunk;
+  const bool piped = nchunks > 1;
+  if (piped && !ctx->copy_stream) {
+    SCB_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+    for (auto& e : ctx->ev_done) SCB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    for (auto& e : ctx->ev_copied) SCB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  }
+  cudaStream_t cs = piped ? ctx->copy_stream : st;
   const bool do_spline = stages & SCB_STAGE_SPLINE, do_timing = stages & SCB_STAGE_TIMING;
-  if (do_spline) {
-    if ((rc = up(SL_IN_WX, in->wx, (size_t)P * W * rs, &din.wx))) return rc;
-    if ((rc = up(SL_IN_WY, in->wy, (size_t)P * W * rs, &din.wy))) return rc;
-    if ((rc = up(SL_IN_SA, in->start_angle, P * rs, &din.start_angle))) return rc;
-    if (in->n_obstacle_edges > 0 && (rc = up(SL_IN_EDGES, in->obstacle_edges, (size_t)in->n_obstacle_edges * 4 * rs, &din.obstacle_edges))) return rc;
-  }
-  if (do_timing) {
-    if ((rc = up(SL_IN_VLO, in->vel_lo, P * rs, &din.vel_lo))) return rc;
-    if ((rc = up(SL_IN_VHI, in->vel_hi, P * rs, &din.vel_hi))) return rc;
-    if ((rc = up(SL_IN_VLG, in->vel_lo_grid, (size_t)G * P * rs, &din.vel_lo_grid))) return rc;
-    if ((rc = up(SL_IN_VHG, in->vel_hi_grid, (size_t)G * P * rs, &din.vel_hi_grid))) return rc;
-    if ((rc = up(SL_IN_ALO, in->acc_lo, P * rs, &din.acc_lo))) return rc;
-    if ((rc = up(SL_IN_AHI, in->acc_hi, P * rs, &din.acc_hi))) return rc;
-    if ((rc = up(SL_IN_VS, in->vel_start, P * rs, &din.vel_start))) return rc;
-    if ((rc = up(SL_IN_VE, in->vel_end, P * rs, &din.vel_end))) return rc;
-    if (!do_spline && (rc = up(SL_IN_PL, in->path_len, P * rs, &din.path_len))) return rc;
-  }
-  // ---- device mirrors of the requested outputs
-  struct Down { void* host; void* dev; size_t bytes; };
-  Down downs[32];
-  int nd = 0;
-  auto mirror = [&](int id, void* host, size_t bytes, void** dev) -> int {
-    if (!host) { *dev = nullptr; return SCB_OK; }
-    void* d;
-    int r = ensure(ctx, id, bytes, &d);
-    if (r) return r;
-    *dev = d;
-    downs[nd++] = {host, d, bytes};
-    return SCB_OK;
-  };
   const size_t nc = (size_t)(W > 1 ? W - 1 : 0) * (deg + 1), nt = (size_t)(W > 1 ? W - 1 : 0) * kTable;
-  const size_t gp = (size_t)G * P * rs, sp = (size_t)S * P * rs;
-#define MIR(id, field, bytes) if ((rc = mirror(id, out->field, bytes, (void**)&dout.field))) return rc
-  MIR(SL_O_STATUS, status, (size_t)P * 4); MIR(SL_O_FAIL, fail_stage, (size_t)P * 4);
-  if (do_spline) {
-    MIR(SL_O_CTRL_X, ctrl_x, P * nc * rs); MIR(SL_O_CTRL_Y, ctrl_y, P * nc * rs);
-    MIR(SL_O_L, arclen_total, P * rs); MIR(SL_O_TABLE, arclen_table, P * nt * rs); MIR(SL_O_COST, cost, P * rs);
-  } else { dout.ctrl_x = dout.ctrl_y = dout.arclen_total = dout.arclen_table = dout.cost = nullptr; }
-  if (do_timing) {
-    MIR(SL_O_T_TOTAL, T_total, P * rs);
-    MIR(SL_O_K_LO, K_lo, gp); MIR(SL_O_K_HI, K_hi, gp); MIR(SL_O_X, x, gp); MIR(SL_O_T, t, gp);
-    MIR(SL_O_V, v, gp); MIR(SL_O_A, a, gp);
-    if (stages & SCB_STAGE_GEOMETRY) { MIR(SL_O_PX, px, gp); MIR(SL_O_PY, py, gp); MIR(SL_O_OMEGA, omega, gp); }
-    else { dout.px = dout.py = dout.omega = nullptr; }
-  } else { dout.T_total = dout.K_lo = dout.K_hi = dout.x = dout.t = dout.v = dout.a = dout.px = dout.py = dout.omega = nullptr; }
-  if (S > 0) {
-    MIR(SL_O_NS, n_samples, (size_t)P * 4);
-    MIR(SL_O_STIME, s_time, sp); MIR(SL_O_SPOS, s_pos, sp); MIR(SL_O_SVEL, s_vel, sp); MIR(SL_O_SACC, s_acc, sp);
-    MIR(SL_O_SPX, s_px, sp); MIR(SL_O_SPY, s_py, sp); MIR(SL_O_SOMEGA, s_omega, sp);
-    if (!do_timing) {  // positions (and velocities) to resample at are inputs
-      SCB_CUDA(cudaMemcpyAsync(dout.n_samples, out->n_samples, (size_t)P * 4, cudaMemcpyHostToDevice, st));
-      SCB_CUDA(cudaMemcpyAsync(dout.s_pos, out->s_pos, sp, cudaMemcpyHostToDevice, st));
-      if (out->s_vel) SCB_CUDA(cudaMemcpyAsync(dout.s_vel, out->s_vel, sp, cudaMemcpyHostToDevice, st));
+  SCB_CUDA(cudaEventRecord(ctx->ev[0], st));
+  const void* dEdges = nullptr;
+  for (int c = 0; c < nchunks; ++c) {
+    const int p0 = c * chunk, Pc = (P - p0 < chunk) ? P - p0 : chunk, b = c & 1;
+    if (c >= 2) SCB_CUDA(cudaStreamWaitEvent(st, ctx->ev_copied[b], 0));  // mirror set b is free again
+    scb_batch_in din = *in;
+    scb_batch_out dout = *out;
+    din.P = Pc;
+    // rows x [P] host array <-> rows x [Pc] device array (rows = 1 and a wider element for the [P][n] arrays)
+    auto copy = [&](void* dst, const void* src, size_t rows, size_t elem, bool to_host, cudaStream_t s) -> cudaError_t {
+      const size_t w = (size_t)Pc * elem, hp = (size_t)P * elem;
+      const cudaMemcpyKind k = to_host ? cudaMemcpyDeviceToHost : cudaMemcpyHostToDevice;
+      if (rows == 1 || Pc == P) return cudaMemcpyAsync(dst, src, w * rows, k, s);
+      return to_host ? cudaMemcpy2DAsync(dst, hp, src, w, w, rows, k, s) : cudaMemcpy2DAsync(dst, w, src, hp, w, rows, k, s);
+    };
+    // ---- H2D of this chunk's inputs, on the compute stream (full speed when the caller's memory is pinned)
+    auto up = [&](int id, const void* src, size_t rows, size_t elem, const void** dst) -> int {
+      if (!src) { *dst = nullptr; return SCB_OK; }
+      void* d;
+      int r = ensure(ctx, id, rows * Pc * elem, &d);
+      if (r) return r;
+      cudaError_t e = copy(d, (const char*)src + (size_t)p0 * elem, rows, elem, false, st);
+      if (e != cudaSuccess) return fail_cuda(ctx, e, "cudaMemcpyAsync H2D");
+      *dst = d;
+      return SCB_OK;
+    };
+    if (do_spline) {
+      if ((rc = up(SL_IN_WX, in->wx, 1, W * rs, &din.wx))) return rc;
+      if ((rc = up(SL_IN_WY, in->wy, 1, W * rs, &din.wy))) return rc;
+      if ((rc = up(SL_IN_SA, in->start_angle, 1, rs, &din.start_angle))) return rc;
+      if (in->n_obstacle_edges > 0) {  // shared by every problem: uploaded once
+        if (c == 0) {
+          void* d;
+          if ((rc = ensure(ctx, SL_IN_EDGES, (size_t)in->n_obstacle_edges * 4 * rs, &d))) return rc;
+          SCB_CUDA(cudaMemcpyAsync(d, in->obstacle_edges, (size_t)in->n_obstacle_edges * 4 * rs, cudaMemcpyHostToDevice, st));
+          dEdges = d;
+        }
+        din.obstacle_edges = dEdges;
+      }
     }
-  }
+    if (do_timing) {
+      if ((rc = up(SL_IN_VLO, in->vel_lo, 1, rs, &din.vel_lo))) return rc;
+      if ((rc = up(SL_IN_VHI, in->vel_hi, 1, rs, &din.vel_hi))) return rc;
+      if ((rc = up(SL_IN_VLG, in->vel_lo_grid, G, rs, &din.vel_lo_grid))) return rc;
+      if ((rc = up(SL_IN_VHG, in->vel_hi_grid, G, rs, &din.vel_hi_grid))) return rc;
+      if ((rc = up(SL_IN_ALO, in->acc_lo, 1, rs, &din.acc_lo))) return rc;
+      if ((rc = up(SL_IN_AHI, in->acc_hi, 1, rs, &din.acc_hi))) return rc;
+      if ((rc = up(SL_IN_VS, in->vel_start, 1, rs, &din.vel_start))) return rc;
+      if ((rc = up(SL_IN_VE, in->vel_end, 1, rs, &din.vel_end))) return rc;
+      if (!do_spline && (rc = up(SL_IN_PL, in->path_len, 1, rs, &din.path_len))) return rc;
+    }
+    // ---- device mirrors (set b) of the requested outputs
+    struct Down { void* host; void* dev; size_t rows, elem; };
+    Down downs[32];
+    int nd = 0;
+    auto mirror = [&](int id, void* host, size_t rows, size_t elem, void** dev) -> int {
+      if (!host) { *dev = nullptr; return SCB_OK; }
+      void* d;
+      int r = ensure(ctx, id + b * SL_COUNT, rows * Pc * elem, &d);
+      if (r) return r;
+      *dev = d;
+      downs[nd++] = {(char*)host + (size_t)p0 * elem, d, rows, elem};
+      return SCB_OK;
+    };
+#define MIR(id, field, rows, elem) if ((rc = mirror(id, out->field, rows, elem, (void**)&dout.field))) return rc
+    MIR(SL_O_STATUS, status, 1, 4); MIR(SL_O_FAIL, fail_stage, 1, 4);
+    if (do_spline) {
+      MIR(SL_O_CTRL_X, ctrl_x, 1, nc * rs); MIR(SL_O_CTRL_Y, ctrl_y, 1, nc * rs);
+      MIR(SL_O_L, arclen_total, 1, rs); MIR(SL_O_TABLE, arclen_table, 1, nt * rs); MIR(SL_O_COST, cost, 1, rs);
+    } else { dout.ctrl_x = dout.ctrl_y = dout.arclen_total = dout.arclen_table = dout.cost = nullptr; }
+    if (do_timing) {
+      MIR(SL_O_T_TOTAL, T_total, 1, rs);
+      MIR(SL_O_K_LO, K_lo, G, rs); MIR(SL_O_K_HI, K_hi, G, rs); MIR(SL_O_X, x, G, rs); MIR(SL_O_T, t, G, rs);
+      MIR(SL_O_V, v, G, rs); MIR(SL_O_A, a, G, rs);
+      if (stages & SCB_STAGE_GEOMETRY) { MIR(SL_O_PX, px, G, rs); MIR(SL_O_PY, py, G, rs); MIR(SL_O_OMEGA, omega, G, rs); }
+      else { dout.px = dout.py = dout.omega = nullptr; }
+    } else { dout.T_total = dout.K_lo = dout.K_hi = dout.x = dout.t = dout.v = dout.a = dout.px = dout.py = dout.omega = nullptr; }
+    if (S > 0) {
+      MIR(SL_O_NS, n_samples, 1, 4);
+      MIR(SL_O_STIME, s_time, S, rs); MIR(SL_O_SPOS, s_pos, S, rs); MIR(SL_O_SVEL, s_vel, S, rs); MIR(SL_O_SACC, s_acc, S, rs);
+      MIR(SL_O_SPX, s_px, S, rs); MIR(SL_O_SPY, s_py, S, rs); MIR(SL_O_SOMEGA, s_omega, S, rs);
+      if (!do_timing) {  // positions (and velocities) to resample at are inputs
+        SCB_CUDA(copy(dout.n_samples, (const char*)out->n_samples + (size_t)p0 * 4, 1, 4, false, st));
+        SCB_CUDA(copy(dout.s_pos, (const char*)out->s_pos + (size_t)p0 * rs, S, rs, false, st));
+        if (out->s_vel) SCB_CUDA(copy(dout.s_vel, (const char*)out->s_vel + (size_t)p0 * rs, S, rs, false, st));
+      }
+    }
 #undef MIR
-  ctx->host_call = true;
-  rc = run_device_any(ctx, &din, &dout, stages);
-  if (rc) return rc;
-  for (int i = 0; i < nd; ++i)
-    SCB_CUDA(cudaMemcpyAsync(downs[i].host, downs[i].dev, downs[i].bytes, cudaMemcpyDeviceToHost, st));
+    ctx->host_call = true;
+    rc = run_device_any(ctx, &din, &dout, stages);
+    if (rc) return rc;
+    if (piped) {
+      SCB_CUDA(cudaEventRecord(ctx->ev_done[b], st));
+      SCB_CUDA(cudaStreamWaitEvent(cs, ctx->ev_done[b], 0));
+      if (c == 0) SCB_CUDA(cudaEventRecord(ctx->ev[8], cs));
+    }
+    for (int i = 0; i < nd; ++i) SCB_CUDA(copy(downs[i].host, downs[i].dev, downs[i].rows, downs[i].elem, true, cs));
+    if (piped) SCB_CUDA(cudaEventRecord(ctx->ev_copied[b], cs));
+  }
+  if (piped) {
+    SCB_CUDA(cudaStreamWaitEvent(st, ctx->ev_copied[0], 0));
+    SCB_CUDA(cudaStreamWaitEvent(st, ctx->ev_copied[1], 0));
+  }
+  ctx->piped = piped;
+  ctx->timing.launches *= nchunks;
   SCB_CUDA(cudaEventRecord(ctx->ev[6], st));
   SCB_CUDA(cudaStreamSynchronize(st));
   collect_timing(ctx);
+  return SCB_OK;
+}
+
+int scb_set_host_chunk(scb_ctx* ctx, int32_t problems) {
+  if (!ctx) return SCB_E_INVALID;
+  ctx->host_chunk = problems;
   return SCB_OK;
 }
 

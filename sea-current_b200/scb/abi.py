@@ -77,6 +77,7 @@ SYMBOLS = {
     "scb_plan_batch": (C.c_int, [C.c_void_p, C.POINTER(ScbBatchIn), C.POINTER(ScbBatchOut)]),
     "scb_plan_batch_device": (C.c_int, [C.c_void_p, C.POINTER(ScbBatchIn), C.POINTER(ScbBatchOut), C.c_int]),
     "scb_synchronize": (C.c_int, [C.c_void_p]),
+    "scb_set_host_chunk": (C.c_int, [C.c_void_p, C.c_int32]),
     "scb_get_timing": (C.c_int, [C.c_void_p, C.POINTER(ScbTiming)]),
     "scb_last_cuda_error": (C.c_char_p, [C.c_void_p]),
     "scb_stream": (C.c_void_p, [C.c_void_p]),

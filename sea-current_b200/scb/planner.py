@@ -80,6 +80,10 @@ class BatchPlanner:
     def synchronize(self):
         self._check(self.lib.scb_synchronize(self.ctx), "scb_synchronize")
 
+    def set_host_chunk(self, problems):
+        """Problems per pipelined chunk of plan() (scb_set_host_chunk): 0 = automatic, < 0 = one chunk."""
+        self._check(self.lib.scb_set_host_chunk(self.ctx, int(problems)), "scb_set_host_chunk")
+
     def algorithmic_bytes(self, P, W, G):
         return self.lib.scb_algorithmic_bytes(self.precision, self.spline_mode, P, W, G)
 

@@ -441,3 +441,55 @@ def test_python_toppra_fixture(planners, golden_dir):
             np.testing.assert_allclose(res["K_hi"][:, p], c["K_hi"], rtol=3e-7, atol=3e-10 * max(c["x"]), err_msg=c["name"])
             np.testing.assert_allclose(res["K_lo"][:, p], c["K_lo"], rtol=3e-7, atol=3e-10 * max(c["x"]), err_msg=c["name"])
             assert abs(res["T_total"][p] - c["T"]) <= 1e-6 * c["T"]
+
+
+@pytest.mark.parametrize("mode", ["ref_cubic", "lau_quintic"])
+def test_host_chunks_bit_identical(planners, mode):
+    """scb_plan_batch pipelines a large batch in chunks (kernels of chunk c+1 over the D2H of chunk c, pitched
+    copies into the caller's [G][P] arrays).  Problems are independent, so every output is bit-identical to the
+    one-chunk call: ragged last chunk, uniform-dt stream, per-gridpoint limits, more than two chunks (mirror
+    sets are reused)."""
+    P, G, S = 1000, 120, 256
+    w = scb.workloads.config_c3(P=P, G=G)
+    rng = np.random.default_rng(5)
+    w["vel_lo_grid"] = np.ascontiguousarray(np.broadcast_to(w["vel_lo"], (G, P)) * rng.uniform(0.5, 1.0, (G, P)))
+    w["vel_hi_grid"] = np.ascontiguousarray(np.broadcast_to(w["vel_hi"], (G, P)) * rng.uniform(0.5, 1.0, (G, P)))
+    pl = planners("fp64", mode)
+    try:
+        pl.set_host_chunk(-1)
+        one = pl.plan(S_cap=S, **w)
+        assert pl.timing()["launches"] == 5
+        for chunk in (384, 96):
+            pl.set_host_chunk(chunk)
+            got = pl.plan(S_cap=S, **w)
+            assert pl.timing()["launches"] == 5 * -(-P // chunk)
+            assert set(got) == set(one)
+            written = np.arange(S)[:, None] < np.where(one["status"] == 0, one["n_samples"], 0)[None, :]
+            for k in one:
+                if k.startswith("s_"):  # rows beyond n_samples[p] are not written
+                    np.testing.assert_array_equal(got[k][written], one[k][written], err_msg="%s chunk=%d" % (k, chunk))
+                else:
+                    np.testing.assert_array_equal(got[k], one[k], err_msg="%s chunk=%d" % (k, chunk))
+    finally:
+        pl.set_host_chunk(0)
+    assert (one["status"] == 0).mean() > 0.9 and written.any()
+
+
+def test_host_chunks_resample_inputs(planners):
+    """Geometry-only calls read n_samples / s_pos from the caller: chunked, they travel by pitched H2D copies."""
+    rng = np.random.default_rng(17)
+    P, W, S = 300, 6, 64
+    wx, wy = scb.workloads.random_walk_paths(rng, P, W)
+    pl = planners("fp64", "ref_cubic")
+    L = pl.plan(wx=wx, wy=wy, stages=scb.abi.STAGE_SPLINE, outputs=("arclen_total",))["arclen_total"]
+    pos = np.linspace(0, 1, S)[:, None] * L[None, :]
+    kw = dict(wx=wx, wy=wy, stages=scb.abi.STAGE_SPLINE | scb.abi.STAGE_GEOMETRY, outputs=("arclen_total", "ctrl_x", "ctrl_y"), S_cap=S)
+    try:
+        pl.set_host_chunk(-1)
+        one = pl.plan(resample_at=(pos.copy(), None, S), **kw)
+        pl.set_host_chunk(128)
+        got = pl.plan(resample_at=(pos.copy(), None, S), **kw)
+    finally:
+        pl.set_host_chunk(0)
+    for k in ("status", "n_samples", "arclen_total", "ctrl_x", "ctrl_y", "s_pos", "s_px", "s_py"):  # what such a call writes
+        np.testing.assert_array_equal(got[k], one[k], err_msg=k)
