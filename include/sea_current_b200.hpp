@@ -40,14 +40,17 @@
 #include <cmath>
 #include <cstdint>
 #include <cstdlib>
+#include <cstring>
 #include <functional>
 #include <initializer_list>
 #include <limits>
+#include <optional>
 #include <ostream>
 #include <sstream>
 #include <stdexcept>
 #include <string>
 #include <tuple>
+#include <unordered_set>
 #include <vector>
 
 #include "seacurrent_b200.h"
@@ -64,6 +67,8 @@ struct Vector2f {
   float operator()(int i) const { return v[i]; }
   float& operator[](int i) { return v[i]; }
   float operator[](int i) const { return v[i]; }
+  bool operator==(const Vector2f& o) const { return v[0] == o.v[0] && v[1] == o.v[1]; }
+  bool operator!=(const Vector2f& o) const { return !(*this == o); }
 };
 template <class T> struct VectorX {
   std::vector<T> d;
@@ -127,32 +132,191 @@ struct planning_error : std::runtime_error {
 struct bounding_rect {  // sc:61-84
   float x_max, x_min, y_max, y_min;
   bounding_rect(float x_max, float x_min, float y_max, float y_min) : x_max(x_max), x_min(x_min), y_max(y_max), y_min(y_min) {}
+  inline bool contains(const Vector2f& p) const { return p.x() <= x_max && p.x() >= x_min && p.y() <= y_max && p.y() >= y_min; }
+  inline void enclose_point(const Vector2f& p) {
+    if (p.x() > x_max) x_max = p.x();
+    if (p.x() < x_min) x_min = p.x();
+    if (p.y() > y_max) y_max = p.y();
+    if (p.y() < y_min) y_min = p.y();
+  }
 };
-// sc:193-284: the path reads only obstacle.lines (shrink_tangent, sc:575-596); `contains`, the bounding box and
-// the id serve the global planner, which is not part of this library.
+
+// sc:87-89: std::pow(float, int) promotes to double, so the distance is formed in double and rounded on return
+inline float pt_dist(const Vector2f& u, const Vector2f& v = Vector2f(0, 0)) {
+  const double dx = (double)(v.x() - u.x()), dy = (double)(v.y() - u.y());
+  return (float)std::sqrt(dx * dx + dy * dy);
+}
+
+struct halton_state {  // sc:93-97
+  int f = 0, i = 0;
+  halton_state(int f, int i) : f(f), i(i) {}
+  halton_state() = default;
+};
+// sc:100-132: the next n elements of the base-b Halton (van der Corput) sequence; advances `state`
+inline std::vector<float> halton(const int b, const int n, halton_state& state) {
+  std::vector<float> nums((size_t)(n > 0 ? n : 0));
+  int f = 0, i = 1;
+  if (state.i != 0 && state.f != 0) { i = state.i; f = state.f; }
+  for (int j = 0; j < n; ++j) {
+    const int x = i - f;
+    if (x == 1) { f = 1; i *= b; }
+    else {
+      int y = i / b;
+      while (x <= y) y = y / b;
+      f = (b + 1) * y - x;
+    }
+    nums[(size_t)j] = static_cast<float>(f) / i;
+  }
+  state.f = f; state.i = i;
+  return nums;
+}
+
+inline float cross2d(const Vector2f& u, const Vector2f& v) { return u.x() * v.y() - u.y() * v.x(); }  // sc:137-139
+// sc:142-178: do segments l and k cross, and where.  Colinear and parallel segments answer "no", as in the reference.
+inline std::tuple<bool, Vector2f> intersects(const std::tuple<Vector2f, Vector2f>& l, const std::tuple<Vector2f, Vector2f>& k) {
+  const Vector2f &l0 = std::get<0>(l), &l1 = std::get<1>(l), &k0 = std::get<0>(k), &k1 = std::get<1>(k);
+  const Vector2f e(k0.x() - l0.x(), k0.y() - l0.y()), dl(l1.x() - l0.x(), l1.y() - l0.y()), dk(k1.x() - k0.x(), k1.y() - k0.y());
+  const float a = cross2d(e, dl), b = cross2d(dl, dk);
+  if (b == 0) return {false, Vector2f(0, 0)};
+  const float u = a / b, c = cross2d(e, dk), t = c / b;
+  if (0 <= u && u <= 1 && 0 <= t && t <= 1) return {true, Vector2f(t * dl.x() + l0.x(), t * dl.y() + l0.y())};
+  return {false, Vector2f(0, 0)};
+}
+inline float dist_pt_line(const Vector2f& p1, const Vector2f& p2, const Vector2f a) {  // sc:181-190 (the infinite line)
+  const float x0 = a.x(), y0 = a.y(), x1 = p1.x(), y1 = p1.y(), x2 = p2.x(), y2 = p2.y();
+  return std::abs((x2 - x1) * (y1 - y0) - (x1 - x0) * (y2 - y1)) / std::sqrt((x2 - x1) * (x2 - x1) + (y2 - y1) * (y2 - y1));
+}
+
+// sc:193-284.  The path reads obstacle.lines (shrink_tangent, sc:575-596); `contains` and the bounding box serve
+// sample_free.  `closed` is never set by the reference's constructors (an uninitialised read in contains); here it
+// defaults to true (the even-odd test) and the caller clears it for a polyline obstacle.
 struct obstacle {
   std::vector<std::tuple<Vector2f, Vector2f>> lines;
   std::vector<Vector2f> vertices;
+  bounding_rect bound_rect = {0, 0, 0, 0};
+  bool closed = true;
+  int64_t id = 0;
   obstacle() = default;
-  // sc:251-267: a polyline through the vertices.  Quirk kept: with an EVEN vertex count the reference appends the
-  // first vertex to its constructor argument (not to the member), i.e. the edge list is closed, `vertices` is not.
+  // sc:251-267: a polyline through the vertices.  Quirks kept: with an EVEN vertex count the reference appends the
+  // first vertex to its constructor argument (not to the member), i.e. the edge list is closed, `vertices` is not;
+  // the bounding box encloses every vertex of that local list but the last.
   obstacle(std::vector<Vector2f> vs) : vertices(vs) {
-    if (vs.size() % 2 == 0 && !vs.empty()) vs.push_back(vs[0]);
-    for (size_t i = 0; i + 1 < vs.size(); ++i) lines.emplace_back(vs[i], vs[i + 1]);
+    if (vs.empty()) return;
+    bound_rect = {vs[0].x(), vs[0].x(), vs[0].y(), vs[0].y()};
+    if (vs.size() % 2 == 0) vs.push_back(vs[0]);
+    for (size_t i = 0; i + 1 < vs.size(); ++i) { lines.emplace_back(vs[i], vs[i + 1]); bound_rect.enclose_point(vs[i]); }
   }
   // sc:269-281: explicit edge list over the vertices
   obstacle(std::vector<Vector2f> vs, const std::vector<std::tuple<int, int>>& edges) : vertices(std::move(vs)) {
+    if (!vertices.empty()) bound_rect = {vertices[0].x(), vertices[0].x(), vertices[0].y(), vertices[0].y()};
     for (const auto& e : edges) {
       if (std::get<0>(e) < 0 || std::get<1>(e) < 0 || (size_t)std::get<0>(e) >= vertices.size() || (size_t)std::get<1>(e) >= vertices.size())
         throw std::invalid_argument("edge must reference indices within the vertex list");
       lines.emplace_back(vertices[(size_t)std::get<0>(e)], vertices[(size_t)std::get<1>(e)]);
+      bound_rect.enclose_point(vertices[(size_t)std::get<0>(e)]);
+      bound_rect.enclose_point(vertices[(size_t)std::get<1>(e)]);
     }
   }
+  // sc:200-250: even-odd crossing count of the segment from outside the bounding box (a crossing that lands on a
+  // vertex counts once per vertex), or, for an open obstacle, "within 0.01 of one of its lines"
+  inline bool contains(const Vector2f& point) const {
+    if (!bound_rect.contains(point)) return false;
+    if (closed) {
+      const Vector2f outside_pt(bound_rect.x_max + 1, bound_rect.y_max + 1);
+      int count = 0;
+      std::vector<bool> corners(vertices.size());
+      for (const auto& line : lines) {
+        const auto [ints, int_pt] = intersects({outside_pt, point}, line);
+        if (!ints) continue;
+        bool counted = false;
+        for (size_t i = 0; i < vertices.size(); ++i) {
+          if (std::abs(int_pt.x() - vertices[i].x()) <= 0.00001 && std::abs(int_pt.y() - vertices[i].y()) <= 0.00001) {
+            if (corners[i]) { counted = true; continue; }
+            corners[i] = true; count++; counted = true;
+            break;
+          }
+        }
+        if (!counted) count++;
+      }
+      return count % 2 == 1;
+    }
+    for (const auto& line : lines)
+      if (dist_pt_line(std::get<0>(line), std::get<1>(line), point) < 0.01f) return true;
+    return false;
+  }
 };
-struct planning_space {  // sc:298-319; only what from_path touches
+
+struct hash_vector2f {  // sc:286-295
+  size_t operator()(const Vector2f v) const {
+    float fa = v.x(), fb = v.y();
+    int32_t a, b;
+    std::memcpy(&a, &fa, 4); std::memcpy(&b, &fb, 4);
+    return std::hash<int32_t>()(a) ^ std::hash<int32_t>()(b);
+  }
+};
+using point_set = std::unordered_set<Vector2f, hash_vector2f>;
+
+// sc:298-319.  from_path reads `.obstacles`; sample_free / fast_marching_trees are the global planner front end
+// (SURVEY 8f N4): sampling stays on the host (the free-space allocations are std::function callbacks), the tree
+// search runs on the GPU (scb_fmt_batch), one query per call here, many per call through b200::fmt_batch.
+struct planning_space {
   std::vector<obstacle> obstacles;
+  std::vector<std::function<bool(Vector2f)>> free_space_allocations;
   bounding_rect bound_rect;
+  halton_state x_state, y_state;
   planning_space(const bounding_rect& br) : bound_rect(br) {}
+
+  inline std::tuple<bool, obstacle> is_obstacle(const Vector2f& p) const {  // sc:1270-1276
+    for (const auto& o : obstacles) if (o.contains(p)) return {true, o};
+    return {false, obstacle()};
+  }
+  inline bool is_free_space_allocated(const Vector2f& p) const {  // sc:1278-1283
+    for (const auto& f : free_space_allocations) if (f(p)) return true;
+    return false;
+  }
+  inline bool is_free(const Vector2f& p) const {  // sc:1285-1292
+    for (const auto& o : obstacles) if (o.contains(p)) return false;
+    return is_free_space_allocated(p);
+  }
+  // sc:1294-1313 in insertion order ((0, 0) first, as the reference's set starts).  The reference's
+  // `while (n > pts.size())` never ends when no candidate is free (e.g. nothing allocated); this one throws after
+  // 64 rounds that added nothing.  It does not print (sc:1306).
+  inline std::vector<Vector2f> sample_free_ordered(const int n) {
+    std::vector<Vector2f> pts{Vector2f(0, 0)};
+    point_set seen(pts.begin(), pts.end());
+    int idle = 0;
+    while (n > (int)pts.size()) {
+      const int m = n - (int)pts.size();
+      const std::vector<float> x_test = halton(2, m, x_state), y_test = halton(3, m, y_state);
+      bool grew = false;
+      for (int i = 0; i < m; ++i) {
+        const Vector2f test((bound_rect.x_max - bound_rect.x_min) * x_test[(size_t)i] + bound_rect.x_min,
+                            (bound_rect.y_max - bound_rect.y_min) * y_test[(size_t)i] + bound_rect.y_min);
+        if (is_free(test) && seen.insert(test).second) { pts.push_back(test); grew = true; }
+      }
+      idle = grew ? 0 : idle + 1;
+      if (idle >= 64) throw std::runtime_error("sample_free: no free point found (is any free space allocated?)");
+    }
+    return pts;
+  }
+  inline point_set sample_free(const int n) {
+    const std::vector<Vector2f> pts = sample_free_ordered(n);
+    return point_set(pts.begin(), pts.end());
+  }
+  inline float cost(const Vector2f a, const Vector2f b) const {  // sc:1315-1326
+    for (const auto& o : obstacles)
+      for (const auto& l : o.lines)
+        if (std::get<0>(intersects({a, b}, l))) return std::numeric_limits<float>::max();
+    return pt_dist(a, b);
+  }
+  inline point_set near(const Vector2f b, const point_set& nodes, const float dist) const {  // sc:1328-1337
+    point_set out;
+    for (const auto& a : nodes)
+      if (pt_dist(a, b) <= std::pow(dist, 2) && a != b) out.insert(a);
+    return out;
+  }
+  // sc:1339-1407: samples n free points (advancing the Halton states, like the reference) and searches on the GPU
+  inline std::optional<std::vector<Vector2f>> fast_marching_trees(const Vector2f& x_init, const Vector2f& x_goal, const int n, const float rn);
 };
 
 struct arclength_data {  // sc:322-326
@@ -222,7 +386,49 @@ inline batch_planner& drop_in_planner() {  // batch-of-1 context behind the refe
   return pl;
 }
 
+// FMT* for many (x_init, x_goal) queries over ONE sampled map (scb_fmt_batch: one CTA per query).  An empty
+// optional = the reference's std::nullopt (the open set ran empty).
+inline std::vector<std::optional<std::vector<Vector2f>>> fmt_batch(const planning_space& space, const std::vector<Vector2f>& samples,
+                                                                   const std::vector<std::tuple<Vector2f, Vector2f>>& queries, const float rn,
+                                                                   std::vector<float>* costs = nullptr) {
+  const int Q = (int)queries.size(), n = (int)samples.size();
+  std::vector<float> nx((size_t)n), ny((size_t)n), edges, ix((size_t)Q), iy((size_t)Q), gx((size_t)Q), gy((size_t)Q);
+  for (int i = 0; i < n; ++i) { nx[(size_t)i] = samples[(size_t)i].x(); ny[(size_t)i] = samples[(size_t)i].y(); }
+  for (const auto& o : space.obstacles)
+    for (const auto& l : o.lines) { edges.push_back(std::get<0>(l).x()); edges.push_back(std::get<0>(l).y()); edges.push_back(std::get<1>(l).x()); edges.push_back(std::get<1>(l).y()); }
+  for (int q = 0; q < Q; ++q) {
+    ix[(size_t)q] = std::get<0>(queries[(size_t)q]).x(); iy[(size_t)q] = std::get<0>(queries[(size_t)q]).y();
+    gx[(size_t)q] = std::get<1>(queries[(size_t)q]).x(); gy[(size_t)q] = std::get<1>(queries[(size_t)q]).y();
+  }
+  const int M = n + 2;  // a path visits a node at most once
+  std::vector<int32_t> status((size_t)Q), len((size_t)Q);
+  std::vector<float> px((size_t)Q * M), py((size_t)Q * M), cost((size_t)Q);
+  scb_fmt_in in{};
+  in.Q = Q; in.n_nodes = n; in.n_edges = (int)(edges.size() / 4); in.max_path = M;
+  in.node_x = nx.data(); in.node_y = ny.data(); in.edges = edges.empty() ? nullptr : edges.data();
+  in.init_x = ix.data(); in.init_y = iy.data(); in.goal_x = gx.data(); in.goal_y = gy.data(); in.rn = rn;
+  scb_fmt_out out{};
+  out.status = status.data(); out.path_len = len.data(); out.path_x = px.data(); out.path_y = py.data(); out.cost = cost.data();
+  batch_planner& pl = drop_in_planner();
+  check(scb_fmt_batch(pl.ctx(), &in, &out), pl.ctx(), "scb_fmt_batch");
+  std::vector<std::optional<std::vector<Vector2f>>> paths((size_t)Q);
+  for (int q = 0; q < Q; ++q) {
+    if (status[(size_t)q] != SCB_FMT_OK) continue;
+    std::vector<Vector2f> p;
+    for (int k = 0; k < len[(size_t)q]; ++k) p.emplace_back(px[(size_t)q * M + k], py[(size_t)q * M + k]);
+    paths[(size_t)q] = std::move(p);
+  }
+  if (costs) *costs = cost;
+  return paths;
+}
+
 }  // namespace b200
+
+inline std::optional<std::vector<Vector2f>> planning_space::fast_marching_trees(const Vector2f& x_init, const Vector2f& x_goal, const int n,
+                                                                                  const float rn) {
+  const std::vector<Vector2f> samples = sample_free_ordered(n);
+  return b200::fmt_batch(*this, samples, {{x_init, x_goal}}, rn)[0];
+}
 
 class bezier_spline {  // sc:388-431
  public:

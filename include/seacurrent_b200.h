@@ -236,6 +236,44 @@ typedef struct scb_summary {
 int scb_pack_summary_device(scb_ctx* ctx, int32_t P, const int32_t* status, const int32_t* fail_stage,
                             const void* T_total, const void* arclen_total, const void* cost, scb_summary* dst);
 
+/* ---- Global planner front end: FMT* over a shared set of sampled nodes, one CTA per query.
+ * Replaces planning_space::fast_marching_trees (sc:1339-1407) with cost (sc:1315-1326), near (sc:1328-1337),
+ * intersects (sc:142-178), for Q (x_init, x_goal) pairs over ONE map: the free-space samples
+ * (planning_space::sample_free, sc:1294-1313 - host side, include/sea_current_b200.hpp) and the obstacle edge list.
+ * Always float, whatever the ctx precision (the reference's planner is float32).  Host pointers.
+ * A node is "near" another when their distance is <= rn * rn (the reference compares pt_dist with pow(rn, 2),
+ * sc:1331), and an edge's cost is the Euclidean distance, FLT_MAX when it crosses an obstacle edge. */
+typedef struct scb_fmt_in {
+  int32_t Q;                /* queries */
+  int32_t n_nodes;          /* shared sample nodes, <= 8192; distinct (a point set) */
+  int32_t n_edges;          /* obstacle edges */
+  int32_t max_path;         /* capacity of one row of path_x / path_y */
+  const float* node_x;      /* [n_nodes] */
+  const float* node_y;
+  const float* edges;       /* [n_edges][4] = (x0, y0, x1, y1), or NULL */
+  const float* init_x;      /* [Q] */
+  const float* init_y;
+  const float* goal_x;      /* [Q] */
+  const float* goal_y;
+  float rn;                 /* connection radius parameter */
+  int32_t reserved0;
+} scb_fmt_in;
+
+enum { SCB_FMT_OK = 0,        /* path found */
+       SCB_FMT_NO_PATH = 1,   /* the open set ran empty: the reference returns std::nullopt */
+       SCB_FMT_PATH_CAP = 2 };/* found, but longer than max_path: path_len and cost are set, the row is not written */
+
+typedef struct scb_fmt_out {
+  int32_t* status;          /* [Q] SCB_FMT_* */
+  int32_t* path_len;        /* [Q] nodes on the path, x_init and x_goal included */
+  int32_t* closed;          /* [Q] or NULL: nodes expanded (size of V_closed) */
+  float* path_x;            /* [Q][max_path] or NULL: x_init ... x_goal */
+  float* path_y;
+  float* cost;              /* [Q] cost-to-come of x_goal (FLT_MAX when there is no path) */
+} scb_fmt_out;
+
+int scb_fmt_batch(scb_ctx* ctx, const scb_fmt_in* in, const scb_fmt_out* out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -8,6 +8,7 @@
 #endif
 #include "../include/seacurrent_b200.h"
 #include "ora_plan.hpp"
+#include "ora_fmt.hpp"
 
 using namespace ora;
 
@@ -301,6 +302,67 @@ int ora_plan_batch(const scb_batch_in* in, const scb_batch_out* out, int spline_
   auto t1 = std::chrono::steady_clock::now();
   if (seconds) *seconds = std::chrono::duration<double>(t1 - t0).count();
   return 0;
+}
+
+// ---- global planner front end (ora_fmt.hpp)
+void ora_halton(int b, int n, int* state_fi, float* out) {
+  ora::HaltonState st; st.f = state_fi[0]; st.i = state_fi[1];
+  const std::vector<float> v = ora::halton(b, n, st);
+  for (int j = 0; j < n; ++j) out[j] = v[j];
+  state_fi[0] = st.f; state_fi[1] = st.i;
+}
+
+static std::vector<ora::FmtObstacle> unpack_obstacles(int n_obs, const int* nv, const float* verts, const int* nl, const float* lines,
+                                                      const float* rects, const int* closed) {
+  std::vector<ora::FmtObstacle> obs(n_obs);
+  size_t vo = 0, lo = 0;
+  for (int k = 0; k < n_obs; ++k) {
+    for (int i = 0; i < nv[k]; ++i, ++vo) obs[k].vertices.push_back(ora::P2{verts[2 * vo], verts[2 * vo + 1]});
+    obs[k].lines.assign(lines + 4 * lo, lines + 4 * (lo + nl[k])); lo += nl[k];
+    obs[k].x_max = rects[4 * k]; obs[k].x_min = rects[4 * k + 1]; obs[k].y_max = rects[4 * k + 2]; obs[k].y_min = rects[4 * k + 3];
+    obs[k].closed = closed[k] != 0;
+  }
+  return obs;
+}
+
+int ora_obstacle_contains(int nv, const float* verts, int nl, const float* lines, const float* rect, int closed, float px, float py) {
+  const std::vector<ora::FmtObstacle> o = unpack_obstacles(1, &nv, verts, &nl, lines, rect, &closed);
+  return ora::obstacle_contains(o[0], ora::P2{px, py}) ? 1 : 0;
+}
+
+// rect = (x_min, x_max, y_min, y_max) of the planning space; state = (x.f, x.i, y.f, y.i); returns the point count
+int ora_sample_free(int n, const float* rect, int n_obs, const int* nv, const float* verts, const int* nl, const float* lines,
+                    const float* obs_rects, const int* closed, int n_free, const float* free_rects, int* state, float* out_xy,
+                    int max_rounds) {
+  const std::vector<ora::FmtObstacle> obs = unpack_obstacles(n_obs, nv, verts, nl, lines, obs_rects, closed);
+  ora::HaltonState xs, ys; xs.f = state[0]; xs.i = state[1]; ys.f = state[2]; ys.i = state[3];
+  const std::vector<float> fr(free_rects, free_rects + 4 * (size_t)n_free);
+  const std::vector<ora::P2> pts = ora::sample_free(n, rect, obs, fr, xs, ys, max_rounds);
+  for (size_t i = 0; i < pts.size(); ++i) { out_xy[2 * i] = pts[i].x; out_xy[2 * i + 1] = pts[i].y; }
+  state[0] = xs.f; state[1] = xs.i; state[2] = ys.f; state[3] = ys.i;
+  return (int)pts.size();
+}
+
+// Q queries over one node set; path_idx [Q][max_path] node indices (0 = init, 1..n samples, n+1 = goal)
+void ora_fmt_batch(int Q, int n, const float* nx, const float* ny, int E, const float* edges, const float* ix, const float* iy,
+                   const float* gx, const float* gy, float rn, int max_path, int* status, int* path_len, int* closed,
+                   int* path_idx, float* path_x, float* path_y, float* cost) {
+  std::vector<ora::P2> samples(n);
+  for (int i = 0; i < n; ++i) samples[i] = ora::P2{nx[i], ny[i]};
+  const std::vector<float> ed(edges, edges + 4 * (size_t)E);
+#pragma omp parallel for schedule(dynamic)
+  for (int q = 0; q < Q; ++q) {
+    const ora::P2 a{ix[q], iy[q]}, b{gx[q], gy[q]};
+    const ora::FmtResult r = ora::fmt_star(samples, ed, a, b, rn);
+    status[q] = r.status; closed[q] = r.closed; path_len[q] = (int)r.path.size(); cost[q] = r.status == 0 ? r.cost : FLT_MAX;
+    if (r.status == 0 && (int)r.path.size() > max_path) { status[q] = 2; continue; }
+    for (size_t k = 0; k < r.path.size(); ++k) {
+      const int id = r.path[k];
+      const ora::P2 p = id == 0 ? a : (id == n + 1 ? b : samples[id - 1]);
+      if (path_idx) path_idx[(size_t)q * max_path + k] = id;
+      path_x[(size_t)q * max_path + k] = p.x; path_y[(size_t)q * max_path + k] = p.y;
+    }
+  }
 }
 
 }  // extern "C"

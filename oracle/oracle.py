@@ -220,3 +220,83 @@ def plan_batch(wx=None, wy=None, vel_lo=None, vel_hi=None, acc_lo=None, acc_hi=N
     sec = C.c_double()
     lib().ora_plan_batch(C.byref(bi), C.byref(bo), spline_mode, solve_mode, nthreads, C.byref(sec))
     return res, sec.value
+
+
+# ---------------------------------------------------------------- global planner front end (ora_fmt.hpp)
+def _f(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def halton(b, n, state=None):
+    """sea_current.hpp:100-132.  state = [f, i] (mutated), None = a fresh sequence."""
+    st = np.asarray(state if state is not None else [0, 0], dtype=np.int32)
+    out = np.empty(n, dtype=np.float32)
+    lib().ora_halton(int(b), int(n), _p(st), _p(out))
+    if state is not None:
+        state[0], state[1] = int(st[0]), int(st[1])
+    return out
+
+
+def make_obstacle(vertices, edges=None, closed=True):
+    """The two obstacle constructors (sc:251-283): vertex loop (an even count appends the first vertex to the local
+    copy the lines are built from) or explicit (i, j) edges.  `closed` is never set by the reference's constructors."""
+    v = [tuple(map(np.float32, p)) for p in vertices]
+    xmax = xmin = v[0][0]; ymax = ymin = v[0][1]
+    lines = []
+
+    def enclose(p):
+        nonlocal xmax, xmin, ymax, ymin
+        xmax = max(xmax, p[0]); xmin = min(xmin, p[0]); ymax = max(ymax, p[1]); ymin = min(ymin, p[1])
+    if edges is None:
+        loc = list(v) + ([v[0]] if len(v) % 2 == 0 else [])
+        for i in range(len(loc) - 1):
+            lines.append(loc[i] + loc[i + 1]); enclose(loc[i])
+    else:
+        for i, j in edges:
+            lines.append(v[i] + v[j]); enclose(v[i]); enclose(v[j])
+    return {"vertices": _f(v).reshape(-1, 2), "lines": _f(lines).reshape(-1, 4), "rect": _f([xmax, xmin, ymax, ymin]),
+            "closed": bool(closed)}
+
+
+def _pack_obstacles(obstacles):
+    nv = np.asarray([len(o["vertices"]) for o in obstacles], dtype=np.int32)
+    nl = np.asarray([len(o["lines"]) for o in obstacles], dtype=np.int32)
+    verts = _f(np.concatenate([o["vertices"] for o in obstacles]) if obstacles else np.zeros((0, 2)))
+    lines = _f(np.concatenate([o["lines"] for o in obstacles]) if obstacles else np.zeros((0, 4)))
+    rects = _f(np.concatenate([o["rect"] for o in obstacles]) if obstacles else np.zeros(0))
+    closed = np.asarray([1 if o["closed"] else 0 for o in obstacles], dtype=np.int32)
+    return nv, verts, nl, lines, rects, closed
+
+
+def obstacle_contains(o, p):
+    return bool(lib().ora_obstacle_contains(len(o["vertices"]), _p(o["vertices"]), len(o["lines"]), _p(o["lines"]), _p(o["rect"]),
+                                            int(o["closed"]), C.c_float(p[0]), C.c_float(p[1])))
+
+
+def sample_free(n, rect, obstacles=(), free_rects=((-1e30, 1e30, -1e30, 1e30),), state=None, max_rounds=64):
+    """planning_space::sample_free (sc:1294-1313).  rect = (x_min, x_max, y_min, y_max); free_rects = the free-space
+    allocations as rectangles; state = [x.f, x.i, y.f, y.i] (mutated).  Returns float32 [m][2], (0, 0) first."""
+    st = np.asarray(state if state is not None else [0, 0, 0, 0], dtype=np.int32)
+    nv, verts, nl, lines, rects, closed = _pack_obstacles(list(obstacles))
+    fr = _f(free_rects).reshape(-1, 4)
+    out = np.empty((max(n, 1) + 1, 2), dtype=np.float32)
+    m = lib().ora_sample_free(int(n), _p(_f(rect)), len(nv), _p(nv), _p(verts), _p(nl), _p(lines), _p(rects), _p(closed), len(fr),
+                              _p(fr), _p(st), _p(out), int(max_rounds))
+    if state is not None:
+        state[:] = [int(x) for x in st]
+    return out[:m].copy()
+
+
+def fmt_batch(nodes, edges, init, goal, rn, max_path=256):
+    """fast_marching_trees (sc:1339-1407) for Q queries over one node set.  nodes [n][2], edges [E][4], init/goal [Q][2]."""
+    nodes = _f(nodes).reshape(-1, 2); init = _f(init).reshape(-1, 2); goal = _f(goal).reshape(-1, 2)
+    ed = _f(edges).reshape(-1, 4) if edges is not None else np.zeros((0, 4), np.float32)
+    Q, n = len(init), len(nodes)
+    nx, ny = _f(nodes[:, 0]), _f(nodes[:, 1])
+    res = {"status": np.empty(Q, np.int32), "path_len": np.empty(Q, np.int32), "closed": np.empty(Q, np.int32),
+           "path_idx": np.full((Q, max_path), -1, np.int32), "path_x": np.zeros((Q, max_path), np.float32),
+           "path_y": np.zeros((Q, max_path), np.float32), "cost": np.empty(Q, np.float32)}
+    lib().ora_fmt_batch(Q, n, _p(nx), _p(ny), len(ed), _p(ed), _p(_f(init[:, 0])), _p(_f(init[:, 1])), _p(_f(goal[:, 0])),
+                        _p(_f(goal[:, 1])), C.c_float(rn), max_path, _p(res["status"]), _p(res["path_len"]), _p(res["closed"]),
+                        _p(res["path_idx"]), _p(res["path_x"]), _p(res["path_y"]), _p(res["cost"]))
+    return res

@@ -1,0 +1,183 @@
+// FMT* over a shared set of sampled nodes, one CTA per planning query (sm_100a).  SURVEY 8f N4.
+//
+// Reference: planning_space::fast_marching_trees (sea_current.hpp:1339-1407) with cost (sc:1315-1326), near
+// (sc:1328-1337), intersects (sc:142-178) and pt_dist (sc:87-89).  The reference keeps V_open / V_unvisited /
+// V_closed as std::unordered_set<Vector2f> and the costs and parents in hash maps keyed by the point; here a
+// node is an index (0 = x_init, 1..n = the shared samples, n+1 = x_goal) and the three sets are one byte of state
+// per node in shared memory, next to the node's coordinates, cost-to-come and parent, so one query's whole
+// search state lives in one SM (21 bytes per node, up to 8,192 samples) and a batch of queries over the same
+// map (MPC goals, multi-robot, replans) fills the GPU with one CTA per query.
+//
+// One expansion of the lowest-cost open node z:
+//   (1) X_near = unvisited nodes within the radius of z         -> compacted into a list (block-wide)
+//   (2) per x in X_near, ONE WARP scans the open nodes within the radius of x, lanes striding over the
+//       node array, each lane keeping the cheapest collision-free cost[y] + |xy| it saw; a candidate is tested
+//       against the obstacle edges only if it beats the lane's best so far (the reference costs every
+//       candidate, collision test included: a colliding one evaluates to FLT_MAX and can never win, so the
+//       argmin is the same); warp min-reduction (cost, then lowest index) -> parent[x], cost[x]
+//   (3) the newly connected nodes become open only after the sweep (V_open.merge, sc:1381), z is closed,
+//       block-wide argmin over the open set picks the next z.
+// Float arithmetic is the reference's, operation for operation: this file is compiled with --fmad=false
+// (Makefile) so the cross products and the double-precision distance are not contracted, and results are
+// bit-identical to the CPU restatement the tests hold.  Exact cost ties go to the lowest node index (the reference: hash order).
+#include <cfloat>
+
+#include "scb_common.cuh"
+
+namespace scb {
+
+namespace {
+
+constexpr int kFmtThreads = 256;
+enum : unsigned char { FMT_UNVISITED = 0, FMT_OPEN = 1, FMT_CLOSED = 2, FMT_OPEN_NEW = 3, FMT_ABSENT = 4 };
+
+__device__ __forceinline__ float fmt_dist(float ax, float ay, float bx, float by) {  // sc:87-89 (pow(float, int) is double)
+  const double dx = (double)(bx - ax), dy = (double)(by - ay);
+  return (float)sqrt(dx * dx + dy * dy);
+}
+
+// sc:142-178 with l = (x, y) and k = the obstacle edge; colinear / parallel -> false
+__device__ __forceinline__ bool fmt_hits(float l0x, float l0y, float l1x, float l1y, const float* __restrict__ e) {
+  const float k0x = e[0], k0y = e[1], k1x = e[2], k1y = e[3];
+  const float ex = k0x - l0x, ey = k0y - l0y, dlx = l1x - l0x, dly = l1y - l0y, dkx = k1x - k0x, dky = k1y - k0y;
+  const float a = ex * dly - ey * dlx;
+  const float b = dlx * dky - dly * dkx;
+  if (b == 0) return false;
+  const float u = a / b;
+  const float c = ex * dky - ey * dkx;
+  const float t = c / b;
+  return 0 <= u && u <= 1 && 0 <= t && t <= 1;
+}
+
+__global__ void __launch_bounds__(kFmtThreads) fmt_kernel(FmtArgs g) {
+  extern __shared__ unsigned char smem_raw[];
+  const int n = g.n, nn = n + 2, GOAL = n + 1, q = blockIdx.x;
+  float* X = (float*)smem_raw;
+  float* Y = X + nn;
+  float* cost = Y + nn;
+  int* parent = (int*)(cost + nn);
+  int* list = parent + nn;
+  unsigned char* state = (unsigned char*)(list + nn);
+  __shared__ int s_count, s_z;
+  __shared__ float s_red_c[kFmtThreads / 32];
+  __shared__ int s_red_i[kFmtThreads / 32];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = kFmtThreads / 32;
+  const float ix = g.ix[q], iy = g.iy[q], gx = g.gx[q], gy = g.gy[q];
+  for (int i = tid; i < nn; i += kFmtThreads) {
+    float x, y;
+    if (i == 0) { x = ix; y = iy; } else if (i == GOAL) { x = gx; y = gy; } else { x = g.nx[i - 1]; y = g.ny[i - 1]; }
+    X[i] = x; Y[i] = y; cost[i] = FLT_MAX; parent[i] = -1;
+    unsigned char s = FMT_UNVISITED;
+    if (i == 0) s = FMT_OPEN;
+    else if (i != GOAL && ((x == gx && y == gy) || (x == ix && y == iy))) s = FMT_ABSENT;  // set semantics
+    state[i] = s;
+  }
+  if (tid == 0) { s_z = 0; s_count = 0; }
+  __syncthreads();
+  if (tid == 0) { cost[0] = 0.f; parent[0] = 0; }
+  const double rn2 = (double)g.rn * (double)g.rn;  // near(): pt_dist <= std::pow(dist, 2), sc:1331
+  int closed = 0, status = 1;
+  if (ix == gx && iy == gy) {  // while (z != x_goal) never runs: the path is {x_init}
+    if (tid == 0) {
+      g.status[q] = 0; g.path_len[q] = 1; g.cost[q] = 0.f;
+      if (g.closed) g.closed[q] = 0;
+      if (g.max_path >= 1 && g.path_x && g.path_y) { g.path_x[(size_t)q * g.max_path] = ix; g.path_y[(size_t)q * g.max_path] = iy; }
+    }
+    return;
+  }
+  __syncthreads();
+  int z = 0;
+  while (true) {
+    // (1) X_near
+    const float zx = X[z], zy = Y[z];
+    for (int i = tid; i < nn; i += kFmtThreads)
+      if (state[i] == FMT_UNVISITED && (double)fmt_dist(X[i], Y[i], zx, zy) <= rn2) list[atomicAdd(&s_count, 1)] = i;
+    __syncthreads();
+    const int count = s_count;
+    // (2) one warp per x
+    for (int li = warp; li < count; li += nwarps) {
+      const int x = list[li];
+      const float xx = X[x], xy = Y[x];
+      float best = FLT_MAX;
+      int besty = -1;
+      for (int y = lane; y < nn; y += 32) {
+        if (state[y] != FMT_OPEN) continue;
+        const float yx = X[y], yy = Y[y];
+        const float d = fmt_dist(xx, xy, yx, yy);  // pt_dist is symmetric bit for bit ((-d)^2 == d^2)
+        if (!((double)d <= rn2)) continue;
+        const float c = cost[y] + d;
+        if (!(c < best)) continue;
+        bool hit = false;
+        for (int k = 0; k < g.E && !hit; ++k) hit = fmt_hits(xx, xy, yx, yy, g.edges + 4 * k);
+        if (!hit) { best = c; besty = y; }
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+        const int oy = __shfl_xor_sync(0xffffffffu, besty, o);
+        if (oy >= 0 && (besty < 0 || ob < best || (ob == best && oy < besty))) { best = ob; besty = oy; }
+      }
+      if (lane == 0 && besty >= 0) { parent[x] = besty; cost[x] = best; state[x] = FMT_OPEN_NEW; }
+    }
+    __syncthreads();
+    // (3) merge, close z, next z = argmin cost over the open set
+    float bc = FLT_MAX;
+    int bi = -1;
+    for (int i = tid; i < nn; i += kFmtThreads) {
+      unsigned char s = state[i];
+      if (s == FMT_OPEN_NEW) { s = FMT_OPEN; state[i] = s; }
+      if (i == z) { s = FMT_CLOSED; state[i] = s; }
+      if (s == FMT_OPEN) { const float c = cost[i]; if (bi < 0 || c < bc) { bc = c; bi = i; } }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float oc = __shfl_xor_sync(0xffffffffu, bc, o);
+      const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+      if (oi >= 0 && (bi < 0 || oc < bc || (oc == bc && oi < bi))) { bc = oc; bi = oi; }
+    }
+    if (lane == 0) { s_red_c[warp] = bc; s_red_i[warp] = bi; }
+    __syncthreads();
+    if (tid == 0) {
+      float c = s_red_c[0]; int i = s_red_i[0];
+      for (int w = 1; w < nwarps; ++w) {
+        const float oc = s_red_c[w]; const int oi = s_red_i[w];
+        if (oi >= 0 && (i < 0 || oc < c || (oc == c && oi < i))) { c = oc; i = oi; }
+      }
+      s_z = i; s_count = 0;
+    }
+    __syncthreads();
+    ++closed;
+    z = s_z;
+    if (z < 0) break;                      // V_open is empty: std::nullopt
+    if (z == GOAL) { status = 0; break; }
+  }
+  if (tid != 0) return;
+  if (g.closed) g.closed[q] = closed;
+  if (status != 0) { g.status[q] = 1; g.path_len[q] = 0; g.cost[q] = FLT_MAX; return; }
+  int len = 1;
+  for (int p = GOAL; p != 0; p = parent[p]) ++len;
+  g.path_len[q] = len; g.cost[q] = cost[GOAL];
+  if (len > g.max_path) { g.status[q] = 2; return; }  // the caller's path buffer is too short; nothing written
+  g.status[q] = 0;
+  if (!g.path_x || !g.path_y) return;
+  float* px = g.path_x + (size_t)q * g.max_path; float* py = g.path_y + (size_t)q * g.max_path;
+  int k = len - 1;
+  for (int p = GOAL; p != 0; p = parent[p], --k) { px[k] = X[p]; py[k] = Y[p]; }
+  px[0] = X[0]; py[0] = Y[0];
+}
+
+}  // namespace
+
+size_t fmt_smem_bytes(int n) { return (size_t)(n + 2) * 21 + 16; }
+
+cudaError_t launch_fmt(const FmtArgs& a, cudaStream_t st) {
+  const size_t smem = fmt_smem_bytes(a.n);
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(fmt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+  }
+  fmt_kernel<<<a.Q, kFmtThreads, smem, st>>>(a);
+  return cudaGetLastError();
+}
+
+}  // namespace scb

@@ -30,6 +30,8 @@ enum SlotId {
   SL_O_STATUS, SL_O_FAIL, SL_O_CTRL_X, SL_O_CTRL_Y, SL_O_L, SL_O_TABLE, SL_O_T_TOTAL, SL_O_COST, SL_O_K_LO,
   SL_O_K_HI, SL_O_X, SL_O_T, SL_O_PX, SL_O_PY, SL_O_V, SL_O_A, SL_O_OMEGA, SL_O_NS, SL_O_STIME, SL_O_SPOS,
   SL_O_SVEL, SL_O_SACC, SL_O_SPX, SL_O_SPY, SL_O_SOMEGA,
+  // FMT* (scb_fmt_batch): one float block of inputs, one of outputs
+  SL_FMT_IN, SL_FMT_OUT,
   SL_COUNT
 };
 
@@ -490,6 +492,66 @@ int scb_pack_summary_device(scb_ctx* ctx, int32_t P, const int32_t* status, cons
     pack_summary_kernel<float><<<grid, block, 0, ctx->stream>>>(P, status, fail_stage, (const float*)T_total,
                                                                 (const float*)arclen_total, (const float*)cost, dst);
   SCB_CUDA(cudaGetLastError());
+  return SCB_OK;
+}
+
+// FMT* over a shared node set, one CTA per query (fmt_kernel.cu).  Inputs are packed into one device block
+// (nodes, edges, queries), outputs into another; both are a few hundred KB, so the call is one H2D, one launch,
+// one D2H per output array.  total_ms of scb_timing = the call, spline_ms = the kernel.
+int scb_fmt_batch(scb_ctx* ctx, const scb_fmt_in* in, const scb_fmt_out* out) {
+  if (!ctx || !in || !out) return SCB_E_INVALID;
+  const int Q = in->Q, n = in->n_nodes, E = in->n_edges, M = in->max_path;
+  if (Q < 0 || n < 0 || n > 8192 || E < 0 || M < 0) return SCB_E_INVALID;
+  if (n > 0 && (!in->node_x || !in->node_y)) return SCB_E_INVALID;
+  if (E > 0 && !in->edges) return SCB_E_INVALID;
+  if (!(in->rn >= 0)) return SCB_E_INVALID;
+  if (Q == 0) return SCB_OK;
+  if (!in->init_x || !in->init_y || !in->goal_x || !in->goal_y || !out->status || !out->path_len || !out->cost) return SCB_E_INVALID;
+  if ((out->path_x == nullptr) != (out->path_y == nullptr) || (out->path_x && M < 1)) return SCB_E_INVALID;
+  SCB_CUDA(cudaSetDevice(ctx->cfg.device));
+  cudaStream_t st = ctx->stream;
+  const size_t n_in = 2 * (size_t)n + 4 * (size_t)E + 4 * (size_t)Q;
+  const size_t n_out = 4 * (size_t)Q + (out->path_x ? 2 * (size_t)Q * M : 0);
+  float *din, *dout;
+  int rc;
+  if ((rc = ensure(ctx, SL_FMT_IN, n_in * 4, (void**)&din))) return rc;
+  if ((rc = ensure(ctx, SL_FMT_OUT, n_out * 4, (void**)&dout))) return rc;
+  scb::FmtArgs a{};
+  a.Q = Q; a.n = n; a.E = E; a.max_path = M; a.rn = in->rn;
+  float* p = din;
+  auto up = [&](const float* src, size_t cnt, const float** dst) -> cudaError_t {
+    *dst = p;
+    cudaError_t e = cnt ? cudaMemcpyAsync(p, src, cnt * 4, cudaMemcpyHostToDevice, st) : cudaSuccess;
+    p += cnt;
+    return e;
+  };
+  SCB_CUDA(cudaEventRecord(ctx->ev[0], st));
+  SCB_CUDA(up(in->node_x, n, &a.nx)); SCB_CUDA(up(in->node_y, n, &a.ny)); SCB_CUDA(up(in->edges, 4 * (size_t)E, &a.edges));
+  SCB_CUDA(up(in->init_x, Q, &a.ix)); SCB_CUDA(up(in->init_y, Q, &a.iy));
+  SCB_CUDA(up(in->goal_x, Q, &a.gx)); SCB_CUDA(up(in->goal_y, Q, &a.gy));
+  a.status = (int32_t*)dout; a.path_len = a.status + Q; a.closed = a.path_len + Q; a.cost = dout + 3 * (size_t)Q;
+  if (out->path_x) { a.path_x = dout + 4 * (size_t)Q; a.path_y = a.path_x + (size_t)Q * M; }
+  SCB_CUDA(cudaEventRecord(ctx->ev[1], st));
+  SCB_CUDA(scb::launch_fmt(a, st));
+  SCB_CUDA(cudaEventRecord(ctx->ev[2], st));
+  SCB_CUDA(cudaMemcpyAsync(out->status, a.status, (size_t)Q * 4, cudaMemcpyDeviceToHost, st));
+  SCB_CUDA(cudaMemcpyAsync(out->path_len, a.path_len, (size_t)Q * 4, cudaMemcpyDeviceToHost, st));
+  if (out->closed) SCB_CUDA(cudaMemcpyAsync(out->closed, a.closed, (size_t)Q * 4, cudaMemcpyDeviceToHost, st));
+  SCB_CUDA(cudaMemcpyAsync(out->cost, a.cost, (size_t)Q * 4, cudaMemcpyDeviceToHost, st));
+  if (out->path_x) {
+    SCB_CUDA(cudaMemcpyAsync(out->path_x, a.path_x, (size_t)Q * M * 4, cudaMemcpyDeviceToHost, st));
+    SCB_CUDA(cudaMemcpyAsync(out->path_y, a.path_y, (size_t)Q * M * 4, cudaMemcpyDeviceToHost, st));
+  }
+  SCB_CUDA(cudaEventRecord(ctx->ev[6], st));
+  SCB_CUDA(cudaStreamSynchronize(st));
+  scb_timing& t = ctx->timing;
+  t = scb_timing{};
+  cudaEventElapsedTime(&t.h2d_ms, ctx->ev[0], ctx->ev[1]);
+  cudaEventElapsedTime(&t.spline_ms, ctx->ev[1], ctx->ev[2]);
+  cudaEventElapsedTime(&t.d2h_ms, ctx->ev[2], ctx->ev[6]);
+  cudaEventElapsedTime(&t.total_ms, ctx->ev[0], ctx->ev[6]);
+  t.launches = 1;
+  ctx->timing_pending = false;
   return SCB_OK;
 }
 

@@ -150,6 +150,19 @@ struct SampleArgs {
   int nudge;                           // geometry-only: repair s_pos in place first (sc:902-912)
 };
 
+struct FmtArgs {                       // fmt_kernel.cu; float whatever the ctx precision (the reference's planner is float)
+  int Q, n, E, max_path;               // queries, shared sample nodes, obstacle edges, capacity of a path row
+  const float *nx, *ny;                // [n]
+  const float* edges;                  // [E][4]
+  const float *ix, *iy, *gx, *gy;      // [Q] x_init, x_goal
+  float rn;
+  int32_t *status, *path_len, *closed; // [Q]; closed may be null
+  float *path_x, *path_y;              // [Q][max_path] or null
+  float* cost;                         // [Q]
+};
+size_t fmt_smem_bytes(int n);
+cudaError_t launch_fmt(const FmtArgs& a, cudaStream_t st);
+
 template <class R> void launch_path(const PathArgs& a, int spline_mode, cudaStream_t st, cudaEvent_t between = nullptr);
 template <class R> void launch_toppra(const ToppraArgs& a, cudaStream_t st);
 template <class R> void launch_toppra_fast(const ToppraArgs& a, cudaStream_t st);

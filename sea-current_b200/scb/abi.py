@@ -67,6 +67,20 @@ class ScbTiming(C.Structure):
                 ("total_ms", C.c_float), ("launches", C.c_int32), ("path_ms", C.c_float), ("arc_ms", C.c_float)]
 
 
+class ScbFmtIn(C.Structure):
+    _fields_ = [("Q", C.c_int32), ("n_nodes", C.c_int32), ("n_edges", C.c_int32), ("max_path", C.c_int32),
+                ("node_x", C.c_void_p), ("node_y", C.c_void_p), ("edges", C.c_void_p),
+                ("init_x", C.c_void_p), ("init_y", C.c_void_p), ("goal_x", C.c_void_p), ("goal_y", C.c_void_p),
+                ("rn", C.c_float), ("reserved0", C.c_int32)]
+
+
+class ScbFmtOut(C.Structure):
+    _fields_ = [("status", C.c_void_p), ("path_len", C.c_void_p), ("closed", C.c_void_p),
+                ("path_x", C.c_void_p), ("path_y", C.c_void_p), ("cost", C.c_void_p)]
+
+
+FMT_OK, FMT_NO_PATH, FMT_PATH_CAP = 0, 1, 2
+
 # every symbol include/seacurrent_b200.h declares: (restype, argtypes)
 SYMBOLS = {
     "scb_version": (C.c_int, []),
@@ -78,6 +92,7 @@ SYMBOLS = {
     "scb_plan_batch_device": (C.c_int, [C.c_void_p, C.POINTER(ScbBatchIn), C.POINTER(ScbBatchOut), C.c_int]),
     "scb_synchronize": (C.c_int, [C.c_void_p]),
     "scb_set_host_chunk": (C.c_int, [C.c_void_p, C.c_int32]),
+    "scb_fmt_batch": (C.c_int, [C.c_void_p, C.POINTER(ScbFmtIn), C.POINTER(ScbFmtOut)]),
     "scb_get_timing": (C.c_int, [C.c_void_p, C.POINTER(ScbTiming)]),
     "scb_last_cuda_error": (C.c_char_p, [C.c_void_p]),
     "scb_stream": (C.c_void_p, [C.c_void_p]),

@@ -101,6 +101,27 @@ class BatchPlanner:
             return (S_cap, P)
         raise KeyError(name)
 
+    # ------------------------------------------------------------------ global planner front end
+    def fmt_batch(self, nodes, edges, init, goal, rn, max_path=256):
+        """FMT* for Q (init, goal) queries over one shared node set and obstacle edge list (scb_fmt_batch; replaces
+        planning_space::fast_marching_trees, sea_current.hpp:1339-1407).  nodes [n][2], edges [E][4] or None,
+        init / goal [Q][2]; float32 whatever the planner's precision."""
+        f32 = lambda a: np.ascontiguousarray(a, dtype=np.float32)
+        nodes = f32(nodes).reshape(-1, 2); init = f32(init).reshape(-1, 2); goal = f32(goal).reshape(-1, 2)
+        ed = f32(edges).reshape(-1, 4) if edges is not None and len(edges) else None
+        Q = len(init)
+        keep = [f32(nodes[:, 0]), f32(nodes[:, 1]), f32(init[:, 0]), f32(init[:, 1]), f32(goal[:, 0]), f32(goal[:, 1])]
+        fi = abi.ScbFmtIn()
+        fi.Q, fi.n_nodes, fi.n_edges, fi.max_path, fi.rn = Q, len(nodes), 0 if ed is None else len(ed), max_path, rn
+        fi.node_x, fi.node_y, fi.init_x, fi.init_y, fi.goal_x, fi.goal_y = (a.ctypes.data for a in keep)
+        fi.edges = None if ed is None else ed.ctypes.data
+        res = BatchResult(status=np.empty(Q, np.int32), path_len=np.empty(Q, np.int32), closed=np.empty(Q, np.int32),
+                          path_x=np.zeros((Q, max_path), np.float32), path_y=np.zeros((Q, max_path), np.float32),
+                          cost=np.empty(Q, np.float32))
+        fo = abi.ScbFmtOut(*(res[k].ctypes.data for k in ("status", "path_len", "closed", "path_x", "path_y", "cost")))
+        self._check(self.lib.scb_fmt_batch(self.ctx, C.byref(fi), C.byref(fo)), "scb_fmt_batch")
+        return res
+
     # ------------------------------------------------------------------ host buffers
     def plan(self, wx=None, wy=None, vel_lo=None, vel_hi=None, acc_lo=None, acc_hi=None, G=101, start_angle=None,
              vel_lo_grid=None, vel_hi_grid=None, vel_start=None, vel_end=None, path_len=None, stages=0,
