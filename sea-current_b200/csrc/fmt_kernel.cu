@@ -4,14 +4,14 @@
 // (sc:1328-1337), intersects (sc:142-178) and pt_dist (sc:87-89).  The reference keeps V_open / V_unvisited /
 // V_closed as std::unordered_set<Vector2f> and the costs and parents in hash maps keyed by the point; here a
 // node is an index (0 = x_init, 1..n = the shared samples, n+1 = x_goal) and the three sets are one byte of state
-// per node in shared memory, next to the node's coordinates, cost-to-come and parent, so one query's whole
-// search state lives in one SM (21 bytes per node, up to 8,192 samples) and a batch of queries over the same
-// map (MPC goals, multi-robot, replans) fills the GPU with one CTA per query.
+// per node in shared memory, next to the node's coordinates, cost-to-come and parent, plus V_open as a compact
+// index list, so one query's whole search state lives in one SM (21 bytes per node, up to 8,192 samples) and a
+// batch of queries over the same map (MPC goals, multi-robot, replans) fills the GPU with one CTA per query.
 //
 // One expansion of the lowest-cost open node z:
 //   (1) X_near = unvisited nodes within the radius of z         -> compacted into a list (block-wide)
 //   (2) per x in X_near, ONE WARP scans the open nodes within the radius of x, lanes striding over the
-//       node array, each lane keeping the cheapest collision-free cost[y] + |xy| it saw; a candidate is tested
+//       open list (the frontier: far fewer entries than nodes), each lane keeping the cheapest collision-free cost[y] + |xy| it saw; a candidate is tested
 //       against the obstacle edges only if it beats the lane's best so far (the reference costs every
 //       candidate, collision test included: a colliding one evaluates to FLT_MAX and can never win, so the
 //       argmin is the same); warp min-reduction (cost, then lowest index) -> parent[x], cost[x]
@@ -55,10 +55,13 @@ __global__ void __launch_bounds__(kFmtThreads) fmt_kernel(FmtArgs g) {
   float* X = (float*)smem_raw;
   float* Y = X + nn;
   float* cost = Y + nn;
-  int* parent = (int*)(cost + nn);
-  int* list = parent + nn;
-  unsigned char* state = (unsigned char*)(list + nn);
-  __shared__ int s_count, s_z;
+  typedef unsigned short idx_t;  // nn <= 8,194
+  idx_t* parent = (idx_t*)(cost + nn);
+  idx_t* xlist = parent + nn;    // X_near of this expansion
+  idx_t* ol = xlist + nn;        // V_open as a compact list (ping-pong with nl)
+  idx_t* nl = ol + nn;
+  unsigned char* state = (unsigned char*)(nl + nn);
+  __shared__ int s_count, s_ocount, s_ncount, s_z;
   __shared__ float s_red_c[kFmtThreads / 32];
   __shared__ int s_red_i[kFmtThreads / 32];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = kFmtThreads / 32;
@@ -66,15 +69,15 @@ __global__ void __launch_bounds__(kFmtThreads) fmt_kernel(FmtArgs g) {
   for (int i = tid; i < nn; i += kFmtThreads) {
     float x, y;
     if (i == 0) { x = ix; y = iy; } else if (i == GOAL) { x = gx; y = gy; } else { x = g.nx[i - 1]; y = g.ny[i - 1]; }
-    X[i] = x; Y[i] = y; cost[i] = FLT_MAX; parent[i] = -1;
+    X[i] = x; Y[i] = y; cost[i] = FLT_MAX; parent[i] = 0;
     unsigned char s = FMT_UNVISITED;
     if (i == 0) s = FMT_OPEN;
     else if (i != GOAL && ((x == gx && y == gy) || (x == ix && y == iy))) s = FMT_ABSENT;  // set semantics
     state[i] = s;
   }
-  if (tid == 0) { s_z = 0; s_count = 0; }
+  if (tid == 0) { s_z = 0; s_count = 0; s_ocount = 1; s_ncount = 0; ol[0] = 0; }
   __syncthreads();
-  if (tid == 0) { cost[0] = 0.f; parent[0] = 0; }
+  if (tid == 0) cost[0] = 0.f;
   const double rn2 = (double)g.rn * (double)g.rn;  // near(): pt_dist <= std::pow(dist, 2), sc:1331
   int closed = 0, status = 1;
   if (ix == gx && iy == gy) {  // while (z != x_goal) never runs: the path is {x_init}
@@ -86,29 +89,29 @@ __global__ void __launch_bounds__(kFmtThreads) fmt_kernel(FmtArgs g) {
     return;
   }
   __syncthreads();
-  int z = 0;
+  int z = 0, ocount = 1;
   while (true) {
     // (1) X_near
     const float zx = X[z], zy = Y[z];
     for (int i = tid; i < nn; i += kFmtThreads)
-      if (state[i] == FMT_UNVISITED && (double)fmt_dist(X[i], Y[i], zx, zy) <= rn2) list[atomicAdd(&s_count, 1)] = i;
+      if (state[i] == FMT_UNVISITED && (double)fmt_dist(X[i], Y[i], zx, zy) <= rn2) xlist[atomicAdd(&s_count, 1)] = (idx_t)i;
     __syncthreads();
     const int count = s_count;
-    // (2) one warp per x
+    // (2) one warp per x, lanes over the open list (its order is arbitrary: ties are resolved by index explicitly)
     for (int li = warp; li < count; li += nwarps) {
-      const int x = list[li];
+      const int x = xlist[li];
       const float xx = X[x], xy = Y[x];
       float best = FLT_MAX;
       int besty = -1;
-      for (int y = lane; y < nn; y += 32) {
-        if (state[y] != FMT_OPEN) continue;
+      for (int k = lane; k < ocount; k += 32) {
+        const int y = ol[k];
         const float yx = X[y], yy = Y[y];
         const float d = fmt_dist(xx, xy, yx, yy);  // pt_dist is symmetric bit for bit ((-d)^2 == d^2)
         if (!((double)d <= rn2)) continue;
         const float c = cost[y] + d;
-        if (!(c < best)) continue;
+        if (!(c < best || (c == best && y < besty))) continue;
         bool hit = false;
-        for (int k = 0; k < g.E && !hit; ++k) hit = fmt_hits(xx, xy, yx, yy, g.edges + 4 * k);
+        for (int e = 0; e < g.E && !hit; ++e) hit = fmt_hits(xx, xy, yx, yy, g.edges + 4 * e);
         if (!hit) { best = c; besty = y; }
       }
 #pragma unroll
@@ -117,18 +120,28 @@ __global__ void __launch_bounds__(kFmtThreads) fmt_kernel(FmtArgs g) {
         const int oy = __shfl_xor_sync(0xffffffffu, besty, o);
         if (oy >= 0 && (besty < 0 || ob < best || (ob == best && oy < besty))) { best = ob; besty = oy; }
       }
-      if (lane == 0 && besty >= 0) { parent[x] = besty; cost[x] = best; state[x] = FMT_OPEN_NEW; }
+      if (lane == 0 && besty >= 0) { parent[x] = (idx_t)besty; cost[x] = best; state[x] = FMT_OPEN_NEW; }
     }
     __syncthreads();
-    // (3) merge, close z, next z = argmin cost over the open set
+    // (3) V_open <- V_open + newly connected - z (rebuilt into the other list), next z = argmin cost over it
     float bc = FLT_MAX;
     int bi = -1;
-    for (int i = tid; i < nn; i += kFmtThreads) {
-      unsigned char s = state[i];
-      if (s == FMT_OPEN_NEW) { s = FMT_OPEN; state[i] = s; }
-      if (i == z) { s = FMT_CLOSED; state[i] = s; }
-      if (s == FMT_OPEN) { const float c = cost[i]; if (bi < 0 || c < bc) { bc = c; bi = i; } }
+    for (int k = tid; k < ocount; k += kFmtThreads) {
+      const int y = ol[k];
+      if (y == z) continue;
+      nl[atomicAdd(&s_ncount, 1)] = (idx_t)y;
+      const float c = cost[y];
+      if (bi < 0 || c < bc || (c == bc && y < bi)) { bc = c; bi = y; }
     }
+    for (int k = tid; k < count; k += kFmtThreads) {
+      const int x = xlist[k];
+      if (state[x] != FMT_OPEN_NEW) continue;
+      state[x] = FMT_OPEN;
+      nl[atomicAdd(&s_ncount, 1)] = (idx_t)x;
+      const float c = cost[x];
+      if (bi < 0 || c < bc || (c == bc && x < bi)) { bc = c; bi = x; }
+    }
+    if (tid == 0) state[z] = FMT_CLOSED;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
       const float oc = __shfl_xor_sync(0xffffffffu, bc, o);
@@ -143,11 +156,12 @@ __global__ void __launch_bounds__(kFmtThreads) fmt_kernel(FmtArgs g) {
         const float oc = s_red_c[w]; const int oi = s_red_i[w];
         if (oi >= 0 && (i < 0 || oc < c || (oc == c && oi < i))) { c = oc; i = oi; }
       }
-      s_z = i; s_count = 0;
+      s_z = i; s_count = 0; s_ocount = s_ncount; s_ncount = 0;
     }
     __syncthreads();
     ++closed;
-    z = s_z;
+    z = s_z; ocount = s_ocount;
+    { idx_t* t = ol; ol = nl; nl = t; }
     if (z < 0) break;                      // V_open is empty: std::nullopt
     if (z == GOAL) { status = 0; break; }
   }
@@ -168,7 +182,7 @@ __global__ void __launch_bounds__(kFmtThreads) fmt_kernel(FmtArgs g) {
 
 }  // namespace
 
-size_t fmt_smem_bytes(int n) { return (size_t)(n + 2) * 21 + 16; }
+size_t fmt_smem_bytes(int n) { return (size_t)(n + 2) * 21 + 16; }  // 3 floats, 4 16-bit indices, 1 state byte per node
 
 cudaError_t launch_fmt(const FmtArgs& a, cudaStream_t st) {
   const size_t smem = fmt_smem_bytes(a.n);

@@ -7,6 +7,9 @@
 //   drop_in_e1 text <out.json>      the request of examples/zmq_test.py:7-10 through handle_text_request
 //   drop_in_e1 lines <unused>       edge lists of the two obstacle constructors (host only, sc:251-281)
 //   drop_in_e1 obst <unused>        from_path over a planning_space with obstacles (shrink_tangent, sc:575-596)
+//   drop_in_e1 sample <n>           planning_space::sample_free over the map of examples/test.cpp:250-259 (host only)
+//   drop_in_e1 fmt <n>              fast_marching_trees(( -0.5, 1), (1, -1), n, 1) as examples/test.cpp:284 calls it, then
+//                                   b200::fmt_batch with three queries over a fresh sample set
 #include <cstring>
 #include <fstream>
 #include <iomanip>
@@ -78,12 +81,67 @@ static int run_obstacle_case() {
   return 0;
 }
 
+// examples/test.cpp:250-259, with all of the rectangle allocated as free space (the example allocates none, so its
+// sample_free cannot return)
+static planning_space example_space() {
+  planning_space space(bounding_rect{1, -1, 1, -1});
+  space.obstacles.push_back(obstacle({Vector2f(-0.5, 0), Vector2f(1, 0), Vector2f(1, 1), Vector2f(0, 1)}));
+  space.obstacles.push_back(obstacle({Vector2f(0, -0.5), Vector2f(1, 0), Vector2f(1, 1), Vector2f(0, 1)}));
+  space.obstacles.push_back(obstacle({Vector2f(-0.6f, 0.148f), Vector2f(-1, 0.148f), Vector2f(-1, 0), Vector2f(-0.6f, 0)}));
+  space.free_space_allocations.push_back([](Vector2f) { return true; });
+  return space;
+}
+
+static void print_pts(const char* key, const std::vector<Vector2f>& pts) {
+  std::cout << "\"" << key << "\": [";
+  for (size_t i = 0; i < pts.size(); ++i) std::cout << (i ? ", " : "") << "[" << pts[i].x() << ", " << pts[i].y() << "]";
+  std::cout << "]";
+}
+
+static int run_sample_case(int n) {
+  planning_space space = example_space();
+  const std::vector<Vector2f> pts = space.sample_free_ordered(n);
+  std::cout << std::setprecision(9) << "{";
+  print_pts("pts", pts);
+  const point_set again = space.sample_free(n);  // the Halton states carry on (sc:1302-1303)
+  std::cout << ", \"state\": [" << space.x_state.f << ", " << space.x_state.i << ", " << space.y_state.f << ", " << space.y_state.i << "]"
+            << ", \"second_set_size\": " << again.size() << ", \"contains\": [" << space.obstacles[0].contains(Vector2f(0.5, 0.5)) << ", "
+            << space.obstacles[0].contains(Vector2f(-0.4f, 0.9f)) << ", " << space.is_free(Vector2f(0.5, 0.5)) << ", " << space.is_free(Vector2f(-0.9f, -0.9f))
+            << "], \"cost\": [" << space.cost(Vector2f(-0.9f, -0.9f), Vector2f(-0.5f, -0.6f)) << ", "
+            << (space.cost(Vector2f(0.5f, -0.9f), Vector2f(0.5f, 0.9f)) == std::numeric_limits<float>::max()) << "]"
+            << ", \"near\": " << space.near(Vector2f(0, 0), point_set(pts.begin(), pts.end()), 0.5f).size() << "}" << std::endl;
+  return 0;
+}
+
+static int run_fmt_case(int n) {
+  planning_space space = example_space();
+  const auto path = space.fast_marching_trees(Vector2f(-0.5, 1), Vector2f(1, -1), n, 1);
+  std::cout << std::setprecision(9) << "{\"found\": " << path.has_value() << ", ";
+  print_pts("path", path.value_or(std::vector<Vector2f>{}));
+  const std::vector<Vector2f> samples = space.sample_free_ordered(n);  // second draw: the states have advanced
+  std::vector<float> costs;
+  const auto paths = b200::fmt_batch(space, samples, {{Vector2f(-0.9f, -0.9f), Vector2f(-0.9f, 0.9f)}, {Vector2f(-0.5, 1), Vector2f(1, -1)},
+                                                       {Vector2f(0.5f, 0.5f), Vector2f(-0.9f, -0.9f)}}, 0.6f, &costs);
+  std::cout << ", ";
+  print_pts("samples", samples);
+  std::cout << ", \"batch\": [";
+  for (size_t q = 0; q < paths.size(); ++q) {
+    std::cout << (q ? ", " : "") << "{\"found\": " << paths[q].has_value() << ", \"cost\": " << (paths[q] ? costs[q] : -1.f) << ", ";
+    print_pts("path", paths[q].value_or(std::vector<Vector2f>{}));
+    std::cout << "}";
+  }
+  std::cout << "]}" << std::endl;
+  return 0;
+}
+
 int main(int argc, char** argv) {
   if (argc < 3) { std::cerr << "usage: drop_in_e1 json|text <out.json>" << std::endl; return 2; }
   try {
     if (!std::strcmp(argv[1], "json")) return run_json_case(argv[2]);
     if (!std::strcmp(argv[1], "lines")) { print_lines(corner_obstacles()); std::cout << "}" << std::endl; return 0; }
     if (!std::strcmp(argv[1], "obst")) return run_obstacle_case();
+    if (!std::strcmp(argv[1], "sample")) return run_sample_case(std::atoi(argv[2]));
+    if (!std::strcmp(argv[1], "fmt")) return run_fmt_case(std::atoi(argv[2]));
     const std::string req = "-0.5 0.5 -0.25 0.25\n0 0\n10 0\n10 10";
     std::ofstream o(argv[2]);
     o << b200::handle_text_request(req);

@@ -142,3 +142,52 @@ def test_text_request_matches_reference_fixture(built, tmp_path, golden_dir):
     m = len(fix["pos_x"])
     np.testing.assert_allclose(x[::st][:m], fix["pos_x"], atol=5e-3)
     np.testing.assert_allclose(y[::st][:m], fix["pos_y"], atol=5e-3)
+
+
+def _example_map(oracle):
+    """examples/test.cpp:250-259"""
+    return [oracle.make_obstacle([(-0.5, 0), (1, 0), (1, 1), (0, 1)]), oracle.make_obstacle([(0, -0.5), (1, 0), (1, 1), (0, 1)]),
+            oracle.make_obstacle([(np.float32(-0.6), np.float32(0.148)), (-1, np.float32(0.148)), (-1, 0), (np.float32(-0.6), 0)])]
+
+
+def test_sample_free_matches_oracle(built, oracle):
+    """planning_space::sample_free / halton / obstacle::contains / cost / near of the drop-in header (host code,
+    sea_current.hpp:100-132, 200-250, 1294-1337) against the oracle: the same points in the same order, the Halton
+    states after two draws; runs without a GPU."""
+    doc = json.loads(subprocess.check_output([built, "sample", "200"]).decode())
+    obs = _example_map(oracle)
+    st = [0, 0, 0, 0]
+    want = oracle.sample_free(200, (-1, 1, -1, 1), obs, state=st)
+    np.testing.assert_array_equal(np.float32(doc["pts"]), want)
+    oracle.sample_free(200, (-1, 1, -1, 1), obs, state=st)
+    assert doc["state"] == st and doc["second_set_size"] == 200
+    assert doc["contains"] == [1, 0, 0, 1]
+    assert doc["cost"][0] == pytest.approx(0.5, rel=1e-6) and doc["cost"][1] == 1
+    pts = np.float32(doc["pts"])
+    d = np.sqrt(pts[:, 0].astype(np.float64) ** 2 + pts[:, 1].astype(np.float64) ** 2).astype(np.float32)
+    assert doc["near"] == int(((d <= 0.25) & (d > 0)).sum())  # near(): pt_dist <= dist^2, the point itself excluded
+
+
+@pytest.mark.gpu
+def test_fast_marching_trees_matches_oracle(built, oracle):
+    """planning_space::fast_marching_trees as examples/test.cpp:284 calls it, and b200::fmt_batch, vs the oracle."""
+    doc = json.loads(subprocess.check_output([built, "fmt", "200"]).decode())
+    obs = _example_map(oracle)
+    edges = np.concatenate([o["lines"] for o in obs])
+    st = [0, 0, 0, 0]
+    first = oracle.sample_free(200, (-1, 1, -1, 1), obs, state=st)
+    want = oracle.fmt_batch(first, edges, [(-0.5, 1)], [(1, -1)], 1.0)
+    assert doc["found"] == 1 and want["status"][0] == 0
+    n = want["path_len"][0]
+    np.testing.assert_array_equal(np.float32(doc["path"]), np.stack([want["path_x"][0, :n], want["path_y"][0, :n]], 1))
+    second = oracle.sample_free(200, (-1, 1, -1, 1), obs, state=st)
+    np.testing.assert_array_equal(np.float32(doc["samples"]), second)
+    q = np.float32([[-0.9, -0.9, -0.9, 0.9], [-0.5, 1, 1, -1], [0.5, 0.5, -0.9, -0.9]])
+    want = oracle.fmt_batch(second, edges, q[:, :2], q[:, 2:], np.float32(0.6))
+    for k, got in enumerate(doc["batch"]):
+        assert got["found"] == int(want["status"][k] == 0)
+        if got["found"]:
+            n = want["path_len"][k]
+            np.testing.assert_array_equal(np.float32(got["path"]), np.stack([want["path_x"][k, :n], want["path_y"][k, :n]], 1))
+            assert np.float32(got["cost"]) == want["cost"][k]
+    assert sum(g["found"] for g in doc["batch"]) >= 2
