@@ -36,6 +36,15 @@ __device__ __forceinline__ float fmt_dist(float ax, float ay, float bx, float by
   return (float)sqrt(dx * dx + dy * dy);
 }
 
+// Float screen in front of the exact test `(float)sqrt(dx^2 + dy^2 in double) <= rn^2`: with s = fl(dx^2 + dy^2)
+// (relative error <= 2.4e-7) and r = rn^2, s > r^2 (1 + 1e-5) is certainly far and s < r^2 (1 - 1e-5) certainly
+// near; only the sliver between goes through the double-precision square root, so the decision is the exact one.
+// 0 = far, 2 = near, 1 = undecided.
+__device__ __forceinline__ int fmt_near_screen(float ax, float ay, float bx, float by, float lo, float hi) {
+  const float dx = bx - ax, dy = by - ay, s = dx * dx + dy * dy;
+  return s > hi ? 0 : (s < lo ? 2 : 1);
+}
+
 // sc:142-178 with l = (x, y) and k = the obstacle edge; colinear / parallel -> false
 __device__ __forceinline__ bool fmt_hits(float l0x, float l0y, float l1x, float l1y, const float* __restrict__ e) {
   const float k0x = e[0], k0y = e[1], k1x = e[2], k1y = e[3];
@@ -79,6 +88,7 @@ __global__ void __launch_bounds__(kFmtThreads) fmt_kernel(FmtArgs g) {
   __syncthreads();
   if (tid == 0) cost[0] = 0.f;
   const double rn2 = (double)g.rn * (double)g.rn;  // near(): pt_dist <= std::pow(dist, 2), sc:1331
+  const float near_lo = (float)(rn2 * rn2 * (1.0 - 1e-5)), near_hi = (float)(rn2 * rn2 * (1.0 + 1e-5));
   int closed = 0, status = 1;
   if (ix == gx && iy == gy) {  // while (z != x_goal) never runs: the path is {x_init}
     if (tid == 0) {
@@ -93,8 +103,11 @@ __global__ void __launch_bounds__(kFmtThreads) fmt_kernel(FmtArgs g) {
   while (true) {
     // (1) X_near
     const float zx = X[z], zy = Y[z];
-    for (int i = tid; i < nn; i += kFmtThreads)
-      if (state[i] == FMT_UNVISITED && (double)fmt_dist(X[i], Y[i], zx, zy) <= rn2) xlist[atomicAdd(&s_count, 1)] = (idx_t)i;
+    for (int i = tid; i < nn; i += kFmtThreads) {
+      if (state[i] != FMT_UNVISITED) continue;
+      const int cls = fmt_near_screen(X[i], Y[i], zx, zy, near_lo, near_hi);
+      if (cls == 2 || (cls == 1 && (double)fmt_dist(X[i], Y[i], zx, zy) <= rn2)) xlist[atomicAdd(&s_count, 1)] = (idx_t)i;
+    }
     __syncthreads();
     const int count = s_count;
     // (2) one warp per x, lanes over the open list (its order is arbitrary: ties are resolved by index explicitly)
@@ -106,8 +119,10 @@ __global__ void __launch_bounds__(kFmtThreads) fmt_kernel(FmtArgs g) {
       for (int k = lane; k < ocount; k += 32) {
         const int y = ol[k];
         const float yx = X[y], yy = Y[y];
+        const int cls = fmt_near_screen(xx, xy, yx, yy, near_lo, near_hi);
+        if (cls == 0) continue;
         const float d = fmt_dist(xx, xy, yx, yy);  // pt_dist is symmetric bit for bit ((-d)^2 == d^2)
-        if (!((double)d <= rn2)) continue;
+        if (cls == 1 && !((double)d <= rn2)) continue;
         const float c = cost[y] + d;
         if (!(c < best || (c == best && y < besty))) continue;
         bool hit = false;

@@ -245,6 +245,16 @@ def test_gpu_fmt_edge_cases(planner, oracle):
         want = oracle.fmt_batch(nodes, edges, [a], [b], 0.8)
         got = planner.fmt_batch(nodes, edges, [a], [b], 0.8)
         _same(got, want)
+    # hops of exactly 0.5 against rn^2 a hair below / above 0.5: the kernel's float screen cannot decide these, the
+    # exact double-precision test does (one radius connects the corridor, the other does not)
+    r_lo = np.float32(np.sqrt(0.5)); r_hi = np.nextafter(r_lo, np.float32(1))
+    verdicts = []
+    for rn in (r_lo, r_hi):
+        want = oracle.fmt_batch(nodes, None, [(0, 0)], [(3, 0)], rn)
+        got = planner.fmt_batch(nodes, None, [(0, 0)], [(3, 0)], rn)
+        _same(got, want)
+        verdicts.append(int(got["status"][0]))
+    assert verdicts == [1, 0], (verdicts, float(r_lo) ** 2, float(r_hi) ** 2)
     want = oracle.fmt_batch(nodes, None, [(0, 0)], [(3, 0)], 0.8, max_path=3)
     got = planner.fmt_batch(nodes, None, [(0, 0)], [(3, 0)], 0.8, max_path=3)
     assert got["status"][0] == want["status"][0] == 2 and got["path_len"][0] == want["path_len"][0] == 7
