@@ -29,6 +29,7 @@ namespace scb {
 namespace {
 
 constexpr int kFmtThreads = 256;
+constexpr int kFmtCoopMax = 4;  // up to this many candidates per 32 open nodes are collision-tested cooperatively, cheapest first
 enum : unsigned char { FMT_UNVISITED = 0, FMT_OPEN = 1, FMT_CLOSED = 2, FMT_OPEN_NEW = 3, FMT_ABSENT = 4 };
 
 __device__ __forceinline__ float fmt_dist(float ax, float ay, float bx, float by) {  // sc:87-89 (pow(float, int) is double)
@@ -70,6 +71,12 @@ __global__ void __launch_bounds__(kFmtThreads) fmt_kernel(FmtArgs g) {
   idx_t* ol = xlist + nn;        // V_open as a compact list (ping-pong with nl)
   idx_t* nl = ol + nn;
   unsigned char* state = (unsigned char*)(nl + nn);
+  const float* edges = g.edges;  // the obstacle edge list: shared memory when it fits (launch_fmt), else global / L1
+  if (g.edges_in_smem) {
+    float* se = (float*)(smem_raw + (((size_t)nn * 21 + 15) & ~(size_t)15));
+    for (int i = threadIdx.x; i < 4 * g.E; i += kFmtThreads) se[i] = g.edges[i];
+    edges = se;
+  }
   __shared__ int s_count, s_ocount, s_ncount, s_z;
   __shared__ float s_red_c[kFmtThreads / 32];
   __shared__ int s_red_i[kFmtThreads / 32];
@@ -110,32 +117,68 @@ __global__ void __launch_bounds__(kFmtThreads) fmt_kernel(FmtArgs g) {
     }
     __syncthreads();
     const int count = s_count;
-    // (2) one warp per x, lanes over the open list (its order is arbitrary: ties are resolved by index explicitly)
+    // (2) one warp per x, lanes over the open list (its order is arbitrary: ties are resolved by index explicitly).
+    //     (wbest, wy) = the cheapest collision-free candidate so far, warp-uniform.  Per 32 list entries the lanes
+    //     cost their own entry, then the warp tests the candidates that would beat (wbest, wy) cheapest first,
+    //     the obstacle edges spread over the lanes; the first free one ends the round (the rest are dearer).
+    //     With more than kFmtCoopMax candidates the lanes test their own edges in parallel instead.
     for (int li = warp; li < count; li += nwarps) {
       const int x = xlist[li];
       const float xx = X[x], xy = Y[x];
-      float best = FLT_MAX;
-      int besty = -1;
-      for (int k = lane; k < ocount; k += 32) {
-        const int y = ol[k];
-        const float yx = X[y], yy = Y[y];
-        const int cls = fmt_near_screen(xx, xy, yx, yy, near_lo, near_hi);
-        if (cls == 0) continue;
-        const float d = fmt_dist(xx, xy, yx, yy);  // pt_dist is symmetric bit for bit ((-d)^2 == d^2)
-        if (cls == 1 && !((double)d <= rn2)) continue;
-        const float c = cost[y] + d;
-        if (!(c < best || (c == best && y < besty))) continue;
-        bool hit = false;
-        for (int e = 0; e < g.E && !hit; ++e) hit = fmt_hits(xx, xy, yx, yy, g.edges + 4 * e);
-        if (!hit) { best = c; besty = y; }
-      }
+      float wbest = FLT_MAX;
+      int wy = -1;
+      for (int k0 = 0; k0 < ocount; k0 += 32) {
+        const int k = k0 + lane;
+        float c = FLT_MAX, yx = 0.f, yy = 0.f;
+        int y = -1;
+        if (k < ocount) {
+          y = ol[k]; yx = X[y]; yy = Y[y];
+          const int cls = fmt_near_screen(xx, xy, yx, yy, near_lo, near_hi);
+          if (cls == 0) y = -1;
+          else {
+            const float d = fmt_dist(xx, xy, yx, yy);  // pt_dist is symmetric bit for bit ((-d)^2 == d^2)
+            if (cls == 1 && !((double)d <= rn2)) y = -1; else c = cost[y] + d;
+          }
+        }
+        bool cand = y >= 0 && (c < wbest || (c == wbest && y < wy));
+        if (__popc(__ballot_sync(0xffffffffu, cand)) > kFmtCoopMax) {
+          // many candidates (a dense neighbourhood): every lane tests its own edge against the obstacles, then one
+          // argmin over the free ones
+          if (cand) {
+            bool hit = false;
+            for (int e = 0; e < g.E && !hit; ++e) hit = fmt_hits(xx, xy, yx, yy, edges + 4 * e);
+            cand = !hit;
+          }
+          float mc = cand ? c : FLT_MAX;
+          int my = cand ? y : 0x7fffffff;
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        const float ob = __shfl_xor_sync(0xffffffffu, best, o);
-        const int oy = __shfl_xor_sync(0xffffffffu, besty, o);
-        if (oy >= 0 && (besty < 0 || ob < best || (ob == best && oy < besty))) { best = ob; besty = oy; }
+          for (int o = 16; o > 0; o >>= 1) {
+            const float oc = __shfl_xor_sync(0xffffffffu, mc, o);
+            const int oy = __shfl_xor_sync(0xffffffffu, my, o);
+            if (oc < mc || (oc == mc && oy < my)) { mc = oc; my = oy; }
+          }
+          if (my != 0x7fffffff) { wbest = mc; wy = my; }
+          continue;
+        }
+        while (__any_sync(0xffffffffu, cand)) {
+          float mc = cand ? c : FLT_MAX;
+          int my = cand ? y : 0x7fffffff;
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) {
+            const float oc = __shfl_xor_sync(0xffffffffu, mc, o);
+            const int oy = __shfl_xor_sync(0xffffffffu, my, o);
+            if (oc < mc || (oc == mc && oy < my)) { mc = oc; my = oy; }
+          }
+          const int src = __ffs(__ballot_sync(0xffffffffu, cand && y == my)) - 1;
+          const float tx = __shfl_sync(0xffffffffu, yx, src), ty = __shfl_sync(0xffffffffu, yy, src);
+          bool hit = false;
+          for (int e = lane; e < g.E; e += 32) hit = hit || fmt_hits(xx, xy, tx, ty, edges + 4 * e);
+          hit = __any_sync(0xffffffffu, hit);
+          if (lane == src) cand = false;
+          if (!hit) { wbest = mc; wy = my; break; }
+        }
       }
-      if (lane == 0 && besty >= 0) { parent[x] = (idx_t)besty; cost[x] = best; state[x] = FMT_OPEN_NEW; }
+      if (lane == 0 && wy >= 0) { parent[x] = (idx_t)wy; cost[x] = wbest; state[x] = FMT_OPEN_NEW; }
     }
     __syncthreads();
     // (3) V_open <- V_open + newly connected - z (rebuilt into the other list), next z = argmin cost over it
@@ -197,10 +240,13 @@ __global__ void __launch_bounds__(kFmtThreads) fmt_kernel(FmtArgs g) {
 
 }  // namespace
 
-size_t fmt_smem_bytes(int n) { return (size_t)(n + 2) * 21 + 16; }  // 3 floats, 4 16-bit indices, 1 state byte per node
+size_t fmt_smem_bytes(int n) { return (((size_t)(n + 2) * 21 + 15) & ~(size_t)15); }  // 3 floats, 4 16-bit indices, 1 state byte per node
 
-cudaError_t launch_fmt(const FmtArgs& a, cudaStream_t st) {
-  const size_t smem = fmt_smem_bytes(a.n);
+cudaError_t launch_fmt(const FmtArgs& a_, cudaStream_t st) {
+  FmtArgs a = a_;
+  size_t smem = fmt_smem_bytes(a.n);
+  a.edges_in_smem = a.E > 0 && smem + (size_t)a.E * 16 <= 200 * 1024;
+  if (a.edges_in_smem) smem += (size_t)a.E * 16;
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(fmt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;

@@ -156,6 +156,7 @@ struct FmtArgs {                       // fmt_kernel.cu; float whatever the ctx 
   const float* edges;                  // [E][4]
   const float *ix, *iy, *gx, *gy;      // [Q] x_init, x_goal
   float rn;
+  int edges_in_smem;                   // set by launch_fmt
   int32_t *status, *path_len, *closed; // [Q]; closed may be null
   float *path_x, *path_y;              // [Q][max_path] or null
   float* cost;                         // [Q]
