@@ -35,6 +35,7 @@
 #ifndef SEA_CURRENT_B200_HPP
 #define SEA_CURRENT_B200_HPP
 
+#include <algorithm>
 #include <array>
 #include <charconv>
 #include <cmath>
@@ -690,6 +691,125 @@ inline std::string handle_text_request(const std::string& req) {
   bezier_spline re = pad.resample(prof.pos[0], ad, true);
   const std::vector<float> ang_vel = re.angular_velocity(prof);
   return serialize_path_to_json(re, prof, ad, ang_vel).dump(4) + "\n";
+}
+
+// Batched variant of the request above: several requests in one message, separated by blank lines;
+// the response is a JSON array with one element per request, in order: the array handle_text_request would return
+// for it, or {"error": ..., "status": toppra ReturnCode / SCB_ST_*, "fail_stage": gridpoint} where that call would
+// throw.  Requests with the same waypoint count are planned together: three scb_plan_batch calls per group
+// (from_path + arclength; gen_vel_prof; resample + angular_velocity) in place of four per request, with the same
+// float hand-overs between them as the one-request sequence, so every element is identical to the one-request
+// response.
+inline std::string handle_text_request_batch(const std::string& req) {
+  struct request { float amin, amax, vmin, vmax; std::vector<double> x, y; std::string error; int status = 0, fail = -1; json out; };
+  std::vector<request> rq;
+  {  // split at blank lines
+    std::istringstream all(req);
+    std::string line, block;
+    auto flush = [&] {
+      if (block.find_first_not_of(" \t\r\n") == std::string::npos) { block.clear(); return; }
+      request r{};
+      std::istringstream ss(block);
+      if (!(ss >> r.amin >> r.amax >> r.vmin >> r.vmax)) r.error = "request: four limits expected";
+      float px, py;
+      while (ss >> px >> py) { r.x.push_back(px); r.y.push_back(py); }
+      if (r.error.empty() && r.x.size() < 2) r.error = "sea_current_b200: a path needs at least two waypoints";
+      rq.push_back(std::move(r));
+      block.clear();
+    };
+    while (std::getline(all, line)) {
+      if (line.find_first_not_of(" \t\r") == std::string::npos) flush(); else { block += line; block += '\n'; }
+    }
+    flush();
+  }
+  static thread_local batch_planner pl(device(), SCB_FP64, spline_mode(), 1 << 16, kDropInMaxWaypoints, kDropInGrid, kDropInMaxSamples);
+  const int G = kDropInGrid;
+  const double dt = (double)0.02f, nan = std::numeric_limits<double>::quiet_NaN();
+  std::vector<int> order;  // requests grouped by waypoint count
+  for (size_t i = 0; i < rq.size(); ++i) if (rq[i].error.empty()) order.push_back((int)i);
+  std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return rq[(size_t)a].x.size() < rq[(size_t)b].x.size(); });
+  for (size_t g0 = 0; g0 < order.size();) {
+    size_t g1 = g0;
+    const int W = (int)rq[(size_t)order[g0]].x.size();
+    while (g1 < order.size() && (int)rq[(size_t)order[g1]].x.size() == W && g1 - g0 < (size_t)(1 << 16)) ++g1;
+    const int P = (int)(g1 - g0);
+    auto R = [&](int p) -> request& { return rq[(size_t)order[g0 + (size_t)p]]; };
+    // (1) from_path + arclength
+    std::vector<double> wx((size_t)P * W), wy((size_t)P * W), sa((size_t)P, nan), L((size_t)P);
+    std::vector<int32_t> st1((size_t)P), st2((size_t)P), fail((size_t)P), ns((size_t)P);
+    for (int p = 0; p < P; ++p)
+      for (int w = 0; w < W; ++w) { wx[(size_t)p * W + w] = R(p).x[(size_t)w]; wy[(size_t)p * W + w] = R(p).y[(size_t)w]; }
+    scb_batch_in in{};
+    in.P = P; in.W = W; in.G = G; in.wx = wx.data(); in.wy = wy.data(); in.start_angle = sa.data(); in.stages = SCB_STAGE_SPLINE;
+    scb_default_opt(&in.opt);
+    scb_batch_out out{};
+    out.status = st1.data(); out.arclen_total = L.data();
+    pl.plan(in, out);
+    // (2) gen_vel_prof on the float arc length (arclength_data holds a float), limits tabulated per gridpoint
+    std::vector<double> Lf((size_t)P), vlo((size_t)G * P), vhi((size_t)G * P), alo((size_t)P), ahi((size_t)P), zero((size_t)P, 0.0), T((size_t)P);
+    for (int p = 0; p < P; ++p) {
+      Lf[(size_t)p] = st1[(size_t)p] == SCB_ST_OK ? (double)(float)L[(size_t)p] : 1.0;
+      alo[(size_t)p] = R(p).amin; ahi[(size_t)p] = R(p).amax;
+      for (int i = 0; i < G; ++i) { vlo[(size_t)i * P + p] = R(p).vmin; vhi[(size_t)i * P + p] = R(p).vmax; }
+    }
+    scb_batch_in tin{};
+    tin.P = P; tin.W = 2; tin.G = G; tin.path_len = Lf.data(); tin.vel_lo_grid = vlo.data(); tin.vel_hi_grid = vhi.data();
+    tin.acc_lo = alo.data(); tin.acc_hi = ahi.data(); tin.vel_start = zero.data(); tin.vel_end = zero.data();
+    tin.stages = SCB_STAGE_TIMING; tin.lp_mode = SCB_LP_SEIDEL; tin.dt = dt; tin.param_mode = param_mode();
+    scb_default_opt(&tin.opt);
+    scb_batch_out tout{};
+    tout.status = st2.data(); tout.fail_stage = fail.data(); tout.T_total = T.data();
+    pl.plan(tin, tout);  // durations first: they size the sample arrays
+    int S = 1;
+    for (int p = 0; p < P; ++p)
+      if (st1[(size_t)p] == SCB_ST_OK && st2[(size_t)p] == SCB_ST_OK) S = std::max(S, (int)std::ceil(T[(size_t)p] / dt) + 2);
+    if (S > kDropInMaxSamples) throw std::runtime_error("sea_current_b200: trajectory longer than the drop-in sample capacity");
+    const size_t SP = (size_t)S * P;
+    std::vector<double> s_t(SP), s_p(SP), s_v(SP), s_a(SP), s_x(SP), s_y(SP), s_o(SP);
+    tout.S_cap = S; tout.n_samples = ns.data(); tout.T_total = nullptr;
+    tout.s_time = s_t.data(); tout.s_pos = s_p.data(); tout.s_vel = s_v.data(); tout.s_acc = s_a.data();
+    pl.plan(tin, tout);
+    // (3) resample (nudged) + angular_velocity at the float positions / velocities of the profile
+    for (int p = 0; p < P; ++p) {
+      const bool ok = st1[(size_t)p] == SCB_ST_OK && st2[(size_t)p] == SCB_ST_OK && ns[(size_t)p] <= S;
+      if (!ok) ns[(size_t)p] = 0;
+      for (int i = 0; i < ns[(size_t)p]; ++i) {
+        const size_t o = (size_t)i * P + p;
+        s_p[o] = (double)(float)s_p[o]; s_v[o] = (double)(float)s_v[o];
+      }
+    }
+    std::vector<int32_t> st3((size_t)P);
+    in.stages = SCB_STAGE_SPLINE | SCB_STAGE_GEOMETRY; in.nudge_positions = 1;
+    scb_batch_out gout{};
+    gout.status = st3.data(); gout.S_cap = S; gout.n_samples = ns.data(); gout.s_pos = s_p.data(); gout.s_vel = s_v.data();
+    gout.s_px = s_x.data(); gout.s_py = s_y.data(); gout.s_omega = s_o.data();
+    pl.plan(in, gout);
+    for (int p = 0; p < P; ++p) {
+      request& r = R(p);
+      if (st1[(size_t)p] != SCB_ST_OK) { r.status = st1[(size_t)p]; r.error = "sea_current_b200: bad path (non-finite waypoint or zero-length leg)"; continue; }
+      if (st2[(size_t)p] != SCB_ST_OK) {
+        r.status = st2[(size_t)p]; r.fail = fail[(size_t)p];
+        r.error = "sea_current_b200: toppra verdict " + std::to_string(r.status) + " at gridpoint " + std::to_string(r.fail);
+        continue;
+      }
+      r.out.samples.resize((size_t)ns[(size_t)p]);
+      for (int i = 0; i < ns[(size_t)p]; ++i) {
+        const size_t o = (size_t)i * P + p;
+        r.out.samples[(size_t)i] = {(double)(float)s_t[o], (double)(float)s_v[o], (double)(float)s_a[o], (double)(float)s_o[o],
+                                    (double)(float)s_x[o], (double)(float)s_y[o]};
+      }
+    }
+    g0 = g1;
+  }
+  std::string resp = "[";
+  for (size_t i = 0; i < rq.size(); ++i) {
+    if (i) resp += ",";
+    if (rq[i].error.empty()) { resp += rq[i].out.dump(-1); continue; }
+    std::string msg;
+    for (char c : rq[i].error) { if (c == '"' || c == '\\') msg += '\\'; msg += c; }
+    resp += "{\"error\":\"" + msg + "\",\"fail_stage\":" + std::to_string(rq[i].fail) + ",\"status\":" + std::to_string(rq[i].status) + "}";
+  }
+  return resp + "]\n";
 }
 
 }  // namespace b200

@@ -7,6 +7,8 @@
 //   drop_in_e1 text <out.json>      the request of examples/zmq_test.py:7-10 through handle_text_request
 //   drop_in_e1 lines <unused>       edge lists of the two obstacle constructors (host only, sc:251-281)
 //   drop_in_e1 obst <unused>        from_path over a planning_space with obstacles (shrink_tangent, sc:575-596)
+//   drop_in_e1 textbatch <out.json> five requests in one message through handle_text_request_batch; each one also through
+//                                   handle_text_request into <out.json>.<k> (or its exception text)
 //   drop_in_e1 sample <n>           planning_space::sample_free over the map of examples/test.cpp:250-259 (host only)
 //   drop_in_e1 fmt <n>              fast_marching_trees(( -0.5, 1), (1, -1), n, 1) as examples/test.cpp:284 calls it, then
 //                                   b200::fmt_batch with three queries over a fresh sample set
@@ -134,12 +136,32 @@ static int run_fmt_case(int n) {
   return 0;
 }
 
+static int run_text_batch(const char* out_path) {
+  const std::vector<std::string> reqs = {
+      "-0.5 0.5 -0.25 0.25\n0 0\n10 0\n10 10",                          // examples/zmq_test.py:7-10
+      "-0.25 0.25 0 1\n0 0\n10 0\n10 10\n10 20\n30 50\n0 0",            // examples/json_test.cpp:19-26
+      "-1.5 1.5 -2 2\n0 0\n4 1\n6 5",                                    // same waypoint count as the first: one group
+      "-0.5 0.5 -0.25 0.25\n0 0\n10 0\n10 0\n20 5",                      // zero-length leg: bad path
+      "-0.5 0.5 0.1 0.25\n0 0\n10 0\n10 10"};                            // velocity box excludes rest: toppra refuses
+  std::string all;
+  for (size_t k = 0; k < reqs.size(); ++k) all += reqs[k] + (k + 1 < reqs.size() ? "\n\n" : "\n");
+  { std::ofstream o(out_path); o << b200::handle_text_request_batch(all); }
+  for (size_t k = 0; k < reqs.size(); ++k) {
+    std::ofstream o(std::string(out_path) + "." + std::to_string(k));
+    try { o << b200::handle_text_request(reqs[k]); }
+    catch (const std::exception& e) { o << "\"" << e.what() << "\"" << std::endl; }
+  }
+  std::cout << "{\"ok\": true, \"n\": " << reqs.size() << "}" << std::endl;
+  return 0;
+}
+
 int main(int argc, char** argv) {
   if (argc < 3) { std::cerr << "usage: drop_in_e1 json|text <out.json>" << std::endl; return 2; }
   try {
     if (!std::strcmp(argv[1], "json")) return run_json_case(argv[2]);
     if (!std::strcmp(argv[1], "lines")) { print_lines(corner_obstacles()); std::cout << "}" << std::endl; return 0; }
     if (!std::strcmp(argv[1], "obst")) return run_obstacle_case();
+    if (!std::strcmp(argv[1], "textbatch")) return run_text_batch(argv[2]);
     if (!std::strcmp(argv[1], "sample")) return run_sample_case(std::atoi(argv[2]));
     if (!std::strcmp(argv[1], "fmt")) return run_fmt_case(std::atoi(argv[2]));
     const std::string req = "-0.5 0.5 -0.25 0.25\n0 0\n10 0\n10 10";

@@ -191,3 +191,25 @@ def test_fast_marching_trees_matches_oracle(built, oracle):
             np.testing.assert_array_equal(np.float32(got["path"]), np.stack([want["path_x"][k, :n], want["path_y"][k, :n]], 1))
             assert np.float32(got["cost"]) == want["cost"][k]
     assert sum(g["found"] for g in doc["batch"]) >= 2
+
+
+@pytest.mark.gpu
+def test_batched_text_request_equals_single_requests(built, tmp_path):
+    """handle_text_request_batch (batched variant): five requests in one message, grouped by waypoint
+    count into three scb_plan_batch calls per group; every element equals the response of the one-request handler
+    (examples/zmq_test.cpp:26-101), value for value, and a request that handler throws for becomes an error object."""
+    out = tmp_path / "batch.json"
+    doc = json.loads(subprocess.check_output([built, "textbatch", str(out)]).decode())
+    batch = json.loads(out.read_text())
+    assert doc["n"] == len(batch) == 5
+    for k in range(3):
+        single = json.loads((tmp_path / ("batch.json.%d" % k)).read_text())
+        assert len(single) > 50 and batch[k] == single, k
+    for k, status in ((3, 16), (4, None)):
+        single = json.loads((tmp_path / ("batch.json.%d" % k)).read_text())
+        assert isinstance(single, str)  # the one-request handler threw
+        assert set(batch[k]) == {"error", "status", "fail_stage"} and batch[k]["status"] != 0
+        if status is not None:
+            assert batch[k]["status"] == status
+        else:
+            assert str(batch[k]["status"]) in single and batch[k]["error"] == single
