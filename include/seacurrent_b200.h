@@ -163,6 +163,13 @@ typedef struct scb_batch_in {
    * Needs SCB_STAGE_SPLINE | SCB_STAGE_TIMING | SCB_STAGE_GEOMETRY in the same call. */
   double omega_max;         /* |angular velocity| <= omega_max  */
   double acc_lat_max;       /* centripetal acceleration v^2 |kappa| <= acc_lat_max */
+  /* Obstacle-distance speed limit (Lau09 III-B eq. 2, the third "isolated constraint"): braking distance plus the
+   * distance travelled during the reaction time must stay below the distance d_i from the curve point of gridpoint i
+   * to the closest obstacle edge (point-to-segment distance over obstacle_edges):
+   *   |v_i| <= -a_brake t_react + sqrt(a_brake^2 t_react^2 + 2 a_brake d_i).
+   * a_brake = 0 switches it off.  Needs all three stages and n_obstacle_edges > 0 in the same call. */
+  double a_brake;           /* maximum deceleration when braking, > 0 */
+  double t_react;           /* reaction time of the system, >= 0 */
   scb_opt opt;
 } scb_batch_in;
 

@@ -39,6 +39,7 @@ struct PlanIn {
   double x_cap = 100.0;
   double dt = (double)0.02f;
   double omega_max = 0, acc_lat_max = 0;  // curvature-aware velocity caps (0 = off), see scb_batch_in
+  double a_brake = 0, t_react = 0;        // obstacle-distance speed limit, Lau09 III-B eq. 2 (a_brake = 0: off)
   std::vector<Edge<double>> edges;        // obstacle edges for the tangent clipping (REF_CUBIC), see scb_batch_in
   int spline_mode = 0;  // 0 REF_CUBIC, 1 LAU_QUINTIC
   LauOpt opt;
@@ -147,8 +148,11 @@ inline PlanOut plan_one(const PlanIn& in) {
   // Curvature-aware limits (Lau09 III-B; the reference's hook is the position-dependent vel_lim_func,
   // sc:1175-1188): the box of gridpoint i is intersected with [-c_i, c_i],
   // c_i = min(omega_max / |kappa_i|, sqrt(acc_lat_max / |kappa_i|)), kappa_i = curvature at arc length q(s_i).
+  // Obstacle-distance limit (Lau09 III-B eq. 2): c_i = -a_brake t_react + sqrt(a_brake^2 t_react^2 + 2 a_brake d_i),
+  // d_i = distance from the curve point of gridpoint i to the closest obstacle edge (point to segment).
+  const bool obst = in.a_brake > 0 && !in.edges.empty();
   std::vector<double> cl, ch;
-  if (in.omega_max > 0 || in.acc_lat_max > 0) {
+  if (in.omega_max > 0 || in.acc_lat_max > 0 || obst) {
     cl.resize(G); ch.resize(G);
     for (int i = 0; i < G; ++i) {
       const double q = pb.path.eval_single(gp[i], 0)[0];
@@ -161,6 +165,18 @@ inline PlanOut plan_one(const PlanIn& in) {
         double c = INFINITY;
         if (in.omega_max > 0) c = in.omega_max / k;
         if (in.acc_lat_max > 0) c = std::min(c, std::sqrt(in.acc_lat_max / k));
+        hi = std::min(hi, c); lo = std::max(lo, -c);
+      }
+      if (obst) {
+        double d2 = INFINITY;
+        for (const auto& e : in.edges) {
+          const double ex = e.b.x - e.a.x, ey = e.b.y - e.a.y, rx = bx - e.a.x, ry = by - e.a.y, ee = ex * ex + ey * ey;
+          double t = ee > 0 ? (rx * ex + ry * ey) / ee : 0.0;
+          t = std::min(std::max(t, 0.0), 1.0);
+          const double qx = rx - t * ex, qy = ry - t * ey;
+          d2 = std::min(d2, qx * qx + qy * qy);
+        }
+        const double at = in.a_brake * in.t_react, c = -at + std::sqrt(at * at + 2.0 * in.a_brake * std::sqrt(d2));
         hi = std::min(hi, c); lo = std::max(lo, -c);
       }
       cl[i] = lo; ch[i] = hi;

@@ -1,0 +1,59 @@
+// Obstacle-distance speed limit (Lau09 III-B eq. 2; scb_batch_in.a_brake / t_react), one thread per (gridpoint,
+// problem) element (sm_100a).  Reads the curve points px, py [G][P] the arc kernel wrote, finds the distance d to the
+// closest obstacle edge (point to segment; the edge list is staged in shared memory and every thread walks it),
+// and writes the velocity box of the gridpoint intersected with [-c, c],
+//   c = -a_brake t_react + sqrt(a_brake^2 t_react^2 + 2 a_brake d),
+// into the per-gridpoint limit arrays the toppra kernels read (vel_lo_grid / vel_hi_grid; the curvature caps, if any,
+// are applied on top by those kernels).  Elementwise and coalesced: 2 reads + 2 writes of a real per element.
+// The reference's hook for a position-dependent limit is vel_lim_func (sea_current.hpp:1175-1188).
+#include "scb_common.cuh"
+
+namespace scb {
+
+namespace {
+
+constexpr int kObstThreads = 256, kObstEdgesSmem = 1024;
+
+template <class S>
+__global__ void __launch_bounds__(kObstThreads) obst_cap_kernel(ObstArgs g) {
+  __shared__ double se[kObstEdgesSmem * 4];
+  const int ns = g.E < kObstEdgesSmem ? g.E : kObstEdgesSmem;
+  const S* __restrict__ ge = (const S*)g.edges;
+  for (int i = threadIdx.x; i < 4 * ns; i += kObstThreads) se[i] = (double)ge[i];
+  __syncthreads();
+  const size_t n = (size_t)g.G * g.P;
+  const double ab = g.a_brake, at = g.a_brake * g.t_react, at2 = at * at;
+  for (size_t o = (size_t)blockIdx.x * kObstThreads + threadIdx.x; o < n; o += (size_t)gridDim.x * kObstThreads) {
+    const int p = (int)(o % (size_t)g.P);
+    const double bx = (double)((const S*)g.px)[o], by = (double)((const S*)g.py)[o];
+    double d2 = CUDART_INF;
+    for (int k = 0; k < g.E; ++k) {
+      double ax, ay, ex, ey;
+      if (k < ns) { ax = se[4 * k]; ay = se[4 * k + 1]; ex = se[4 * k + 2] - ax; ey = se[4 * k + 3] - ay; }
+      else { ax = (double)ge[4 * k]; ay = (double)ge[4 * k + 1]; ex = (double)ge[4 * k + 2] - ax; ey = (double)ge[4 * k + 3] - ay; }
+      const double rx = bx - ax, ry = by - ay, ee = ex * ex + ey * ey;
+      double t = ee > 0 ? (rx * ex + ry * ey) / ee : 0.0;
+      t = fmin(fmax(t, 0.0), 1.0);
+      const double qx = rx - t * ex, qy = ry - t * ey;
+      d2 = fmin(d2, qx * qx + qy * qy);
+    }
+    const double c = -at + sqrt(at2 + 2.0 * ab * sqrt(d2));
+    double lo, hi;
+    if (g.vel_lo_grid && g.vel_hi_grid) { lo = (double)((const S*)g.vel_lo_grid)[o]; hi = (double)((const S*)g.vel_hi_grid)[o]; }
+    else { lo = (double)((const S*)g.vel_lo)[p]; hi = (double)((const S*)g.vel_hi)[p]; }
+    ((S*)g.out_lo)[o] = (S)fmax(lo, -c);
+    ((S*)g.out_hi)[o] = (S)fmin(hi, c);
+  }
+}
+
+}  // namespace
+
+template <class R> void launch_obst_cap(const ObstArgs& a, cudaStream_t st) {
+  const size_t n = (size_t)a.G * a.P;
+  const int grid = (int)((n + kObstThreads - 1) / kObstThreads < (size_t)148 * 16 ? (n + kObstThreads - 1) / kObstThreads : (size_t)148 * 16);
+  obst_cap_kernel<R><<<grid, kObstThreads, 0, st>>>(a);
+}
+template void launch_obst_cap<double>(const ObstArgs&, cudaStream_t);
+template void launch_obst_cap<float>(const ObstArgs&, cudaStream_t);
+
+}  // namespace scb

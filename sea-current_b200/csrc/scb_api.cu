@@ -32,6 +32,8 @@ enum SlotId {
   SL_O_SVEL, SL_O_SACC, SL_O_SPX, SL_O_SPY, SL_O_SOMEGA,
   // FMT* (scb_fmt_batch): one float block of inputs, one of outputs
   SL_FMT_IN, SL_FMT_OUT,
+  // obstacle-distance speed limit: curve points when the caller did not ask for them, capped per-gridpoint boxes
+  SL_PX, SL_PY, SL_CAP_LO, SL_CAP_HI,
   SL_COUNT
 };
 
@@ -99,6 +101,10 @@ int validate(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, int
   if ((in->omega_max > 0 || in->acc_lat_max > 0) &&
       (stages & (SCB_STAGE_SPLINE | SCB_STAGE_TIMING | SCB_STAGE_GEOMETRY)) != (SCB_STAGE_SPLINE | SCB_STAGE_TIMING | SCB_STAGE_GEOMETRY))
     return SCB_E_INVALID;  // the caps need the curvature at the gridpoints
+  if (!(in->a_brake >= 0) || !(in->t_react >= 0)) return SCB_E_INVALID;
+  if (in->a_brake > 0 && in->n_obstacle_edges > 0 &&
+      (stages & (SCB_STAGE_SPLINE | SCB_STAGE_TIMING | SCB_STAGE_GEOMETRY)) != (SCB_STAGE_SPLINE | SCB_STAGE_TIMING | SCB_STAGE_GEOMETRY))
+    return SCB_E_INVALID;  // the limit needs the curve points of the gridpoints
   if (out->S_cap < 0 || out->S_cap > ctx->cfg.max_samples) return SCB_E_INVALID;
   if ((stages & SCB_STAGE_GEOMETRY) && !(stages & SCB_STAGE_TIMING) && (out->S_cap <= 0 || !out->n_samples || !out->s_pos)) return SCB_E_INVALID;
   if (!out->status) return SCB_E_INVALID;
@@ -129,6 +135,8 @@ int run_device(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, i
                                               out->s_py || out->s_omega || out->n_samples);
   void* dKappa = nullptr;
   const bool curv = in->omega_max > 0 || in->acc_lat_max > 0;  // validate(): needs all three stages
+  const bool obst = in->a_brake > 0 && in->n_obstacle_edges > 0 && in->obstacle_edges;  // ditto
+  void *dPx = out->px, *dPy = out->py;
   if (do_spline) {
     const size_t nseg = W - 1;
     // the control points and the arc-length tables are the hand-over between the path kernel and the
@@ -143,7 +151,11 @@ int run_device(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, i
     a.edges = in->obstacle_edges; a.n_edges = in->obstacle_edges ? in->n_obstacle_edges : 0;
     a.ctrl_x = dCx; a.ctrl_y = dCy; a.table = dTab; a.L = dL; a.cost = out->cost; a.status = out->status;
     if (do_geo && do_timing) {
-      a.px = out->px; a.py = out->py;
+      if (obst) {
+        if (!dPx && (rc = ensure(ctx, SL_PX, (size_t)G * P * rs, &dPx))) return rc;
+        if (!dPy && (rc = ensure(ctx, SL_PY, (size_t)G * P * rs, &dPy))) return rc;
+      }
+      a.px = dPx; a.py = dPy;
       if (out->omega || curv) { if ((rc = ensure(ctx, SL_KAPPA, (size_t)G * P * rs, &dKappa))) return rc; a.kappa = dKappa; }
     }
     a.opt = in->opt;
@@ -178,6 +190,17 @@ int run_device(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, i
     t.acc_lo = in->acc_lo; t.acc_hi = in->acc_hi; t.vel_start = in->vel_start; t.vel_end = in->vel_end;
     t.x_cap = in->x_cap > 0 ? in->x_cap : 100.0;
     if (curv) { t.kappa = dKappa; t.omega_max = in->omega_max; t.acc_lat_max = in->acc_lat_max; }
+    if (obst) {  // Lau09 III-B eq. 2: the per-gridpoint boxes under the obstacle-distance limit replace the caller's
+      void *dLo, *dHi;
+      if ((rc = ensure(ctx, SL_CAP_LO, gp, &dLo)) || (rc = ensure(ctx, SL_CAP_HI, gp, &dHi))) return rc;
+      ObstArgs oa{};
+      oa.P = P; oa.G = G; oa.E = in->n_obstacle_edges; oa.px = dPx; oa.py = dPy; oa.edges = in->obstacle_edges;
+      oa.vel_lo = in->vel_lo; oa.vel_hi = in->vel_hi; oa.vel_lo_grid = in->vel_lo_grid; oa.vel_hi_grid = in->vel_hi_grid;
+      oa.a_brake = in->a_brake; oa.t_react = in->t_react; oa.out_lo = dLo; oa.out_hi = dHi;
+      launch_obst_cap<R>(oa, st);
+      ++launches;
+      t.vel_lo_grid = dLo; t.vel_hi_grid = dHi;
+    }
     t.K_lo = dKlo; t.K_hi = dKhi; t.x = dX; t.status = out->status; t.fail_stage = dFail;
     if (!f64) { t.K_lo_out = out->K_lo; t.K_hi_out = out->K_hi; }
     if (in->lp_mode == SCB_LP_SEIDEL) launch_toppra<R>(t, st);

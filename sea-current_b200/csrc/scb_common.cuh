@@ -150,6 +150,17 @@ struct SampleArgs {
   int nudge;                           // geometry-only: repair s_pos in place first (sc:902-912)
 };
 
+struct ObstArgs {                      // obst_kernel.cu: per-gridpoint velocity box under the obstacle-distance limit
+  int P, G, E;
+  const void *px, *py;                 // [G][P] curve points of the gridpoints
+  const void* edges;                   // [E][4]
+  const void *vel_lo, *vel_hi;         // [P] ...
+  const void *vel_lo_grid, *vel_hi_grid;  // ... or [G][P] (then these are the box)
+  double a_brake, t_react;
+  void *out_lo, *out_hi;               // [G][P]
+};
+template <class R> void launch_obst_cap(const ObstArgs& a, cudaStream_t st);
+
 struct FmtArgs {                       // fmt_kernel.cu; float whatever the ctx precision (the reference's planner is float)
   int Q, n, E, max_path;               // queries, shared sample nodes, obstacle edges, capacity of a path row
   const float *nx, *ny;                // [n]

@@ -40,6 +40,7 @@ class ScbBatchIn(C.Structure):
                 ("nudge_positions", C.c_int32), ("n_obstacle_edges", C.c_int32),
                 ("param_mode", C.c_int32), ("reserved0", C.c_int32),
                 ("x_cap", C.c_double), ("dt", C.c_double), ("omega_max", C.c_double), ("acc_lat_max", C.c_double),
+                ("a_brake", C.c_double), ("t_react", C.c_double),
                 ("opt", ScbOpt)]
 
 
