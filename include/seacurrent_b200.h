@@ -63,8 +63,9 @@ enum {
    * linear_joint_velocity.cpp:54; tp:solver.cpp:36-37) */
   SCB_ST_ERR_BAD_PATH = 16,     /* non-finite waypoint, zero-length leg, or arclength <= 0 */
   SCB_ST_ERR_BAD_LIMITS = 17,   /* velocity box excludes 0 where q'(s) = 0, or lo > hi */
-  SCB_ST_ERR_TIME_KNOTS = 18    /* a knot interval < 1e-8 s (the reference drops such knots,
+  SCB_ST_ERR_TIME_KNOTS = 18,   /* a knot interval < 1e-8 s (the reference drops such knots,
                                    tp:parametrizer/spline.cpp:25-33; unreachable for x_cap = 100) */
+  SCB_ST_ERR_COLLISION = 19     /* the finished spline crosses an obstacle edge (scb_batch_in.collision_chords) */
 };
 
 enum { SCB_FP64 = 0, SCB_FP32 = 1 };
@@ -144,15 +145,20 @@ typedef struct scb_batch_in {
   const void* obstacle_edges; /* real [n_obstacle_edges][4] = (x0, y0, x1, y1) or NULL: the obstacle.lines of the
                                planning_space (sc:193-284, 298-319), obstacle after obstacle, shared by every problem
                                of the batch.  from_path cuts every tangent back where W -> W +- T crosses an edge
-                               (shrink_tangent, sc:575-596).  SCB_REF_CUBIC only: the convex-hull argument behind
-                               the clipping is the cubic's. */
+                               (shrink_tangent, sc:575-596).  The clipping is SCB_REF_CUBIC only (the convex-hull
+                               argument behind it is the cubic's); SCB_LAU_QUINTIC takes an edge list only together
+                               with collision_chords > 0. */
   int32_t stages;           /* SCB_STAGE_* bitmask; 0 = all */
   int32_t lp_mode;          /* SCB_LP_*: how the stage LPs of toppra are solved; 0 = default */
   int32_t nudge_positions;  /* geometry-only calls: 1 = repair the caller's s_pos in place before resampling
                                (ends pinned to 0 / L, non-monotone entries averaged, clamp; sc:902-912) */
   int32_t n_obstacle_edges; /* 0 = no obstacles */
   int32_t param_mode;       /* SCB_PARAM_*; 0 = the reference's Spline parametrizer */
-  int32_t reserved0;        /* 0 */
+  int32_t collision_chords; /* M > 0: collision verdict of the finished spline (Lau09 IV-B: a trajectory that is not
+                               collision-free has infinite cost): every segment is cut into M chords and each chord
+                               tested against obstacle_edges with the reference's segment test (sc:142-178); a hit
+                               gives status SCB_ST_ERR_COLLISION and cost = +inf, and the problem is not timed.
+                               With it, SCB_LAU_QUINTIC accepts an edge list too (no tangent clipping there).  0 = off */
   double x_cap;             /* upper bound of sdot^2 in the backward pass; 0 = reference's 100
                                (tp:algorithm.hpp:152 m_initXBound) */
   double dt;                /* uniform-dt stream period; 0 = reference's 0.02 (sc:1199) */

@@ -268,6 +268,7 @@ int ora_plan_batch(const scb_batch_in* in, const scb_batch_out* out, int spline_
     pi.dt = in->dt > 0 ? in->dt : (double)0.02f;
     pi.omega_max = in->omega_max; pi.acc_lat_max = in->acc_lat_max;
     pi.a_brake = in->a_brake; pi.t_react = in->t_react;
+    pi.collision_chords = in->collision_chords;
     pi.param_mode = in->param_mode;
     if (in->obstacle_edges && in->n_obstacle_edges > 0) {
       const double* ed = (const double*)in->obstacle_edges;

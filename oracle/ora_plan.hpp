@@ -22,7 +22,7 @@
 
 namespace ora {
 
-enum { ST_BAD_PATH = 16, ST_BAD_LIMITS = 17, ST_TIME_KNOTS = 18 };
+enum { ST_BAD_PATH = 16, ST_BAD_LIMITS = 17, ST_TIME_KNOTS = 18, ST_COLLISION = 19 };
 static const int INV_NEWTON_ITERS = 40;       // cap; the iteration stops when it has converged (|step| <= 1e-12 h)
 static const double GL4_X[4] = {-0.8611363115940525752, -0.3399810435848562648, 0.3399810435848562648, 0.8611363115940525752};
 static const double GL4_W[4] = {0.3478548451374538574, 0.6521451548625461426, 0.6521451548625461426, 0.3478548451374538574};
@@ -40,6 +40,7 @@ struct PlanIn {
   double dt = (double)0.02f;
   double omega_max = 0, acc_lat_max = 0;  // curvature-aware velocity caps (0 = off), see scb_batch_in
   double a_brake = 0, t_react = 0;        // obstacle-distance speed limit, Lau09 III-B eq. 2 (a_brake = 0: off)
+  int collision_chords = 0;               // M > 0: collision verdict of the finished spline (Lau09 IV-B), see scb_batch_in
   std::vector<Edge<double>> edges;        // obstacle edges for the tangent clipping (REF_CUBIC), see scb_batch_in
   int spline_mode = 0;  // 0 REF_CUBIC, 1 LAU_QUINTIC
   LauOpt opt;
@@ -133,6 +134,24 @@ inline PlanOut plan_one(const PlanIn& in) {
   for (auto& seg : ad.segments) o.table.insert(o.table.end(), seg.begin(), seg.end());
   if (!(o.L > 0) || !std::isfinite(o.L)) { o.status = ST_BAD_PATH; return o; }
   const int nseg = sp.n_segments();
+  // ---- collision verdict (Lau09 IV-B: a trajectory that is not collision-free has infinite cost): every segment cut
+  //      into M chords (de Casteljau), every chord against every obstacle edge with intersects (sc:142-178)
+  if (in.collision_chords > 0 && !in.edges.empty()) {
+    const int M = in.collision_chords;
+    for (int j = 0; j < nseg; ++j) {
+      V2<double> a = sp.ctrl[j][0];
+      for (int k = 1; k <= M; ++k) {
+        const double u = k == M ? 1.0 : (double)k / (double)M;
+        std::vector<V2<double>> t = sp.ctrl[j];
+        for (size_t r = 1; r < t.size(); ++r)
+          for (size_t i = 0; i + r < t.size(); ++i) t[i] = {(1.0 - u) * t[i].x + u * t[i + 1].x, (1.0 - u) * t[i].y + u * t[i + 1].y};
+        V2<double> pt;
+        for (const auto& e : in.edges)
+          if (seg_intersects(a, t[0], e.a, e.b, pt)) { o.status = ST_COLLISION; o.cost = INFINITY; return o; }
+        a = t[0];
+      }
+    }
+  }
   std::vector<double> seg_end(nseg);
   double acc = 0;
   for (int j = 0; j < nseg; ++j) { acc += ad.segments[j].back(); seg_end[j] = acc; }

@@ -167,7 +167,7 @@ def lau_optimise(path_xy, opt, start_angle=float("nan")):
 
 def plan_batch(wx=None, wy=None, vel_lo=None, vel_hi=None, acc_lo=None, acc_hi=None, G=101, start_angle=None,
                vel_lo_grid=None, vel_hi_grid=None, vel_start=None, vel_end=None, spline_mode=0, solve_mode=1,
-               S_cap=0, x_cap=0.0, dt=0.0, opt=None, nthreads=0, outputs=None, omega_max=0.0, acc_lat_max=0.0, obstacle_edges=None, param_mode=0, a_brake=0.0, t_react=0.0):
+               S_cap=0, x_cap=0.0, dt=0.0, opt=None, nthreads=0, outputs=None, omega_max=0.0, acc_lat_max=0.0, obstacle_edges=None, param_mode=0, a_brake=0.0, t_react=0.0, collision_chords=0):
     """The product's batch on the CPU (FP64), same layouts as scb_plan_batch.  Returns (dict, seconds)."""
     abi = _abi()
     keep = []
@@ -191,6 +191,7 @@ def plan_batch(wx=None, wy=None, vel_lo=None, vel_hi=None, acc_lo=None, acc_hi=N
     bi.x_cap, bi.dt = x_cap, dt
     bi.omega_max, bi.acc_lat_max = omega_max, acc_lat_max
     bi.a_brake, bi.t_react = a_brake, t_react
+    bi.collision_chords = collision_chords
     bi.param_mode = param_mode
     if obstacle_edges is not None and len(obstacle_edges):
         ed = np.ascontiguousarray(_d(obstacle_edges)).reshape(-1, 4)

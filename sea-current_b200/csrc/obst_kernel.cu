@@ -6,11 +6,61 @@
 // into the per-gridpoint limit arrays the toppra kernels read (vel_lo_grid / vel_hi_grid; the curvature caps, if any,
 // are applied on top by those kernels).  Elementwise and coalesced: 2 reads + 2 writes of a real per element.
 // The reference's hook for a position-dependent limit is vel_lim_func (sea_current.hpp:1175-1188).
+//
+// collide_kernel: collision verdict of the finished spline (Lau09 IV-B: "if the trajectory is not collision-free
+// according to the obstacle map, its cost is set to infinity"; scb_batch_in.collision_chords).  One thread per
+// (problem, segment): the segment is cut into M chords B(k/M) -> B((k+1)/M) (de Casteljau in FP64) and every chord is
+// tested against every obstacle edge with the reference's segment test (intersects, sea_current.hpp:142-178).  A hit
+// turns status[p] from OK into SCB_ST_ERR_COLLISION and cost[p] into +inf; the timing kernels skip such a problem.
 #include "scb_common.cuh"
+#include "path_device.cuh"
 
 namespace scb {
 
 namespace {
+
+template <class S, int DEG>
+__global__ void __launch_bounds__(256) collide_kernel(CollideArgs g) {
+  __shared__ double se[1024 * 4];
+  const int ns = g.E < 1024 ? g.E : 1024;
+  const S* __restrict__ ge = (const S*)g.edges;
+  for (int i = threadIdx.x; i < 4 * ns; i += 256) se[i] = (double)ge[i];
+  __syncthreads();
+  const int nseg = g.W - 1;
+  const size_t item = (size_t)blockIdx.x * 256 + threadIdx.x;
+  if (item >= (size_t)g.P * nseg) return;
+  const int p = (int)(item / nseg);
+  if (g.status[p] != SCB_ST_OK) return;
+  const S* __restrict__ cx = (const S*)g.ctrl_x + item * (DEG + 1);
+  const S* __restrict__ cy = (const S*)g.ctrl_y + item * (DEG + 1);
+  double bx[DEG + 1], by[DEG + 1];
+#pragma unroll
+  for (int j = 0; j <= DEG; ++j) { bx[j] = (double)cx[j]; by[j] = (double)cy[j]; }
+  double ax = bx[0], ay = by[0];
+  bool hit = false;
+  for (int k = 1; k <= g.M && !hit; ++k) {
+    const double u = k == g.M ? 1.0 : (double)k / (double)g.M;
+    double tx[DEG + 1], ty[DEG + 1];
+#pragma unroll
+    for (int j = 0; j <= DEG; ++j) { tx[j] = bx[j]; ty[j] = by[j]; }
+#pragma unroll
+    for (int r = 1; r <= DEG; ++r)
+#pragma unroll
+      for (int j = 0; j <= DEG - r; ++j) { tx[j] = (1.0 - u) * tx[j] + u * tx[j + 1]; ty[j] = (1.0 - u) * ty[j] + u * ty[j + 1]; }
+    const double qx = tx[0], qy = ty[0];
+    for (int e = 0; e < g.E && !hit; ++e) {
+      double e0x, e0y, e1x, e1y, ix, iy;
+      if (e < ns) { e0x = se[4 * e]; e0y = se[4 * e + 1]; e1x = se[4 * e + 2]; e1y = se[4 * e + 3]; }
+      else { e0x = (double)ge[4 * e]; e0y = (double)ge[4 * e + 1]; e1x = (double)ge[4 * e + 2]; e1y = (double)ge[4 * e + 3]; }
+      hit = seg_intersects<double>(ax, ay, qx, qy, e0x, e0y, e1x, e1y, ix, iy);
+    }
+    ax = qx; ay = qy;
+  }
+  if (hit) {  // several segments of one problem may write: the same values
+    g.status[p] = SCB_ST_ERR_COLLISION;
+    if (g.cost) ((S*)g.cost)[p] = (S)CUDART_INF;
+  }
+}
 
 constexpr int kObstThreads = 256, kObstEdgesSmem = 1024;
 
@@ -55,5 +105,14 @@ template <class R> void launch_obst_cap(const ObstArgs& a, cudaStream_t st) {
 }
 template void launch_obst_cap<double>(const ObstArgs&, cudaStream_t);
 template void launch_obst_cap<float>(const ObstArgs&, cudaStream_t);
+
+template <class R> void launch_collide(const CollideArgs& a, int degree, cudaStream_t st) {
+  const size_t n = (size_t)a.P * (a.W - 1);
+  const int grid = (int)((n + 255) / 256);
+  if (degree == 3) collide_kernel<R, 3><<<grid, 256, 0, st>>>(a);
+  else collide_kernel<R, 5><<<grid, 256, 0, st>>>(a);
+}
+template void launch_collide<double>(const CollideArgs&, int, cudaStream_t);
+template void launch_collide<float>(const CollideArgs&, int, cudaStream_t);
 
 }  // namespace scb

@@ -97,7 +97,9 @@ int validate(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, int
   if ((stages & SCB_STAGE_GEOMETRY) && !(stages & SCB_STAGE_SPLINE)) return SCB_E_INVALID;
   if (!(in->omega_max >= 0) || !(in->acc_lat_max >= 0)) return SCB_E_INVALID;
   if (in->n_obstacle_edges < 0 || (in->n_obstacle_edges > 0 && !in->obstacle_edges)) return SCB_E_INVALID;
-  if (in->n_obstacle_edges > 0 && (stages & SCB_STAGE_SPLINE) && ctx->cfg.spline_mode != SCB_REF_CUBIC) return SCB_E_INVALID;
+  if (in->collision_chords < 0 || in->collision_chords > 4096) return SCB_E_INVALID;
+  if (in->n_obstacle_edges > 0 && (stages & SCB_STAGE_SPLINE) && ctx->cfg.spline_mode != SCB_REF_CUBIC && in->collision_chords == 0)
+    return SCB_E_INVALID;  // the tangent clipping is the cubic's; the quintic takes edges for the collision verdict only
   if ((in->omega_max > 0 || in->acc_lat_max > 0) &&
       (stages & (SCB_STAGE_SPLINE | SCB_STAGE_TIMING | SCB_STAGE_GEOMETRY)) != (SCB_STAGE_SPLINE | SCB_STAGE_TIMING | SCB_STAGE_GEOMETRY))
     return SCB_E_INVALID;  // the caps need the curvature at the gridpoints
@@ -148,7 +150,8 @@ int run_device(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, i
     PathArgs a{};
     a.P = P; a.W = W; a.G = G; a.wx = in->wx; a.wy = in->wy; a.start_angle = in->start_angle;
     a.vel_start = in->vel_start; a.vel_end = in->vel_end;
-    a.edges = in->obstacle_edges; a.n_edges = in->obstacle_edges ? in->n_obstacle_edges : 0;
+    const bool clip = ctx->cfg.spline_mode == SCB_REF_CUBIC && in->obstacle_edges;  // shrink_tangent: cubic only
+    a.edges = clip ? in->obstacle_edges : nullptr; a.n_edges = clip ? in->n_obstacle_edges : 0;
     a.ctrl_x = dCx; a.ctrl_y = dCy; a.table = dTab; a.L = dL; a.cost = out->cost; a.status = out->status;
     if (do_geo && do_timing) {
       if (obst) {
@@ -161,6 +164,13 @@ int run_device(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, i
     a.opt = in->opt;
     launch_path<R>(a, ctx->cfg.spline_mode, st, ctx->ev[7]);
     launches += 2;  // path kernel + arc kernel
+    if (in->collision_chords > 0 && in->obstacle_edges && in->n_obstacle_edges > 0) {
+      CollideArgs ca{};
+      ca.P = P; ca.W = W; ca.E = in->n_obstacle_edges; ca.M = in->collision_chords;
+      ca.ctrl_x = dCx; ca.ctrl_y = dCy; ca.edges = in->obstacle_edges; ca.status = out->status; ca.cost = out->cost;
+      launch_collide<R>(ca, deg, st);
+      ++launches;
+    }
     ctx->split_spline = true;
   } else {
     SCB_CUDA(cudaMemsetAsync(out->status, 0, (size_t)P * 4, st));

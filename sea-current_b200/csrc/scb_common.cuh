@@ -161,6 +161,15 @@ struct ObstArgs {                      // obst_kernel.cu: per-gridpoint velocity
 };
 template <class R> void launch_obst_cap(const ObstArgs& a, cudaStream_t st);
 
+struct CollideArgs {                   // obst_kernel.cu: collision verdict of the finished spline
+  int P, W, E, M;                      // problems, waypoints, obstacle edges, chords per segment
+  const void *ctrl_x, *ctrl_y;         // [P][(W-1)(d+1)]
+  const void* edges;                   // [E][4]
+  int32_t* status;                     // [P]: OK -> SCB_ST_ERR_COLLISION on a hit
+  void* cost;                          // [P] or null: +inf on a hit
+};
+template <class R> void launch_collide(const CollideArgs& a, int degree, cudaStream_t st);
+
 struct FmtArgs {                       // fmt_kernel.cu; float whatever the ctx precision (the reference's planner is float)
   int Q, n, E, max_path;               // queries, shared sample nodes, obstacle edges, capacity of a path row
   const float *nx, *ny;                // [n]

@@ -14,7 +14,7 @@ PARAM_SPLINE, PARAM_CONST_ACCEL = 0, 1
 
 ST_OK, ST_ERR_UNKNOWN, ST_ERR_FAIL_CONTROLLABLE, ST_ERR_FAIL_FORWARD_PASS = 0, 1, 2, 3
 ST_ERR_UNINITIALIZED, ST_ERR_FAIL_FEASIBLE = 4, 5
-ST_ERR_BAD_PATH, ST_ERR_BAD_LIMITS, ST_ERR_TIME_KNOTS = 16, 17, 18
+ST_ERR_BAD_PATH, ST_ERR_BAD_LIMITS, ST_ERR_TIME_KNOTS, ST_ERR_COLLISION = 16, 17, 18, 19
 
 
 class ScbConfig(C.Structure):
@@ -38,7 +38,7 @@ class ScbBatchIn(C.Structure):
                 ("vel_start", C.c_void_p), ("vel_end", C.c_void_p),
                 ("path_len", C.c_void_p), ("obstacle_edges", C.c_void_p), ("stages", C.c_int32), ("lp_mode", C.c_int32),
                 ("nudge_positions", C.c_int32), ("n_obstacle_edges", C.c_int32),
-                ("param_mode", C.c_int32), ("reserved0", C.c_int32),
+                ("param_mode", C.c_int32), ("collision_chords", C.c_int32),
                 ("x_cap", C.c_double), ("dt", C.c_double), ("omega_max", C.c_double), ("acc_lat_max", C.c_double),
                 ("a_brake", C.c_double), ("t_react", C.c_double),
                 ("opt", ScbOpt)]

@@ -126,7 +126,7 @@ class BatchPlanner:
     def plan(self, wx=None, wy=None, vel_lo=None, vel_hi=None, acc_lo=None, acc_hi=None, G=101, start_angle=None,
              vel_lo_grid=None, vel_hi_grid=None, vel_start=None, vel_end=None, path_len=None, stages=0,
              outputs=ALL_OUTPUTS, S_cap=0, x_cap=0.0, dt=0.0, opt=None, out_buffers=None, resample_at=None, lp_mode=0,
-             nudge=False, omega_max=0.0, acc_lat_max=0.0, obstacle_edges=None, param_mode=0, a_brake=0.0, t_react=0.0):
+             nudge=False, omega_max=0.0, acc_lat_max=0.0, obstacle_edges=None, param_mode=0, a_brake=0.0, t_react=0.0, collision_chords=0):
         """Host arrays in, host arrays out (scb_plan_batch).  `out_buffers` lets a caller pass
         preallocated (e.g. pinned) numpy arrays keyed by output name."""
         R = self.real
@@ -158,6 +158,7 @@ class BatchPlanner:
         bi.stages, bi.x_cap, bi.dt, bi.lp_mode = stages, x_cap, dt, lp_mode
         bi.omega_max, bi.acc_lat_max = omega_max, acc_lat_max
         bi.a_brake, bi.t_react = a_brake, t_react
+        bi.collision_chords = collision_chords
         bi.nudge_positions = 1 if nudge else 0
         bi.param_mode = param_mode
         if obstacle_edges is not None and len(obstacle_edges):
