@@ -50,6 +50,9 @@ def parse():
                     help="spline = what the reference's gen_vel_prof builds (the headline); const_accel = toppra's ConstAccel")
     ap.add_argument("--in-flight", type=int, default=0,
                     help="independent contexts (streams) the batches alternate over; 0 = 2 (1 for C4, whose outputs are 50 GB)")
+    ap.add_argument("--obstacles", type=int, default=0,
+                    help="E > 0: E wall pieces beside the nominal path, collision verdict (16 chords per segment) and the obstacle-"
+                         "distance speed limit (a_brake 1.0, t_react 0.2) switched on (SURVEY 8f N2 / N3); not the headline")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--host-chunk", type=int, default=0,
                     help="e2e leg: problems per pipelined chunk of scb_plan_batch (0 = the library's default, -1 = one chunk)")
@@ -207,7 +210,19 @@ def main():
     opt = scb.default_opt(move_waypoints=1)
     inputs = {k: torch.from_numpy(np.ascontiguousarray(v)).to(dev, dtype=tdt) for k, v in w.items() if k != "G"}
     pm = 1 if a.parametrizer == "const_accel" else 0
-    batches = [q.make_device_batch(inputs, G=G, opt=opt, param_mode=pm) for q in pls]
+    extra, extra_host = {}, {}
+    if a.obstacles > 0:  # wall pieces scattered 1-3 m beside the first path's legs
+        rng = np.random.default_rng(7)
+        k = rng.integers(0, W - 1, a.obstacles)
+        mid = np.stack([(w["wx"][0, k] + w["wx"][0, k + 1]) / 2, (w["wy"][0, k] + w["wy"][0, k + 1]) / 2], 1)
+        leg = np.stack([w["wx"][0, k + 1] - w["wx"][0, k], w["wy"][0, k + 1] - w["wy"][0, k]], 1)
+        nrm = np.stack([-leg[:, 1], leg[:, 0]], 1) / np.linalg.norm(leg, axis=1, keepdims=True)
+        c = mid + nrm * (rng.uniform(1.0, 3.0, (a.obstacles, 1)) * rng.choice([-1.0, 1.0], (a.obstacles, 1)))
+        d = leg / np.linalg.norm(leg, axis=1, keepdims=True) * rng.uniform(0.3, 1.0, (a.obstacles, 1))
+        edges = np.ascontiguousarray(np.concatenate([c - d, c + d], 1))
+        extra_host = dict(obstacle_edges=edges, a_brake=1.0, t_react=0.2, collision_chords=16)
+        extra = dict(extra_host, obstacle_edges=torch.from_numpy(edges).to(dev, dtype=tdt))
+    batches = [q.make_device_batch(inputs, G=G, opt=opt, param_mode=pm, **extra) for q in pls]
     bi, bo, res = batches[0]
     streams = [torch.cuda.ExternalStream(q.stream(), device=dev) for q in pls]
     stream = streams[0]
@@ -325,7 +340,9 @@ def main():
             "config": dict(cfg, P_per_rank=P, spline="lau_quintic, optimiser K=%d move_waypoints=1" % opt.iters,
                            parametrizer=a.parametrizer, in_flight=nfl,
                            l2="outputs streamed per step (%.2f GB) exceed the 126 MB L2; no flush" % (path_bytes / 1e9),
-                           ok_fraction=ok_frac),
+                           ok_fraction=ok_frac,
+                           **({"obstacles": "%d wall pieces, collision_chords 16, a_brake 1.0, t_react 0.2 (arc_ms includes the collision "
+                                            "kernel, toppra_ms the obstacle-distance kernel)" % a.obstacles} if a.obstacles > 0 else {})),
             "stage_ms": stage_ms, "roofline": roof, "clocks": clocks, "gpu_launches": launches_per_step * a.steps}
 
     # ---- e2e: host buffers in pinned memory through scb_plan_batch
@@ -352,7 +369,7 @@ def main():
 
             def calls(c, n):  # one host thread per context, as the C ABI prescribes; ctypes drops the GIL inside the call
                 for _ in range(n):
-                    pls[c].plan(G=G, outputs=names, out_buffers=hbufs[c], opt=opt, param_mode=pm, **host_in)
+                    pls[c].plan(G=G, outputs=names, out_buffers=hbufs[c], opt=opt, param_mode=pm, **extra_host, **host_in)
 
             def run(n_each):
                 th = [threading.Thread(target=calls, args=(c, n_each)) for c in range(nth)]

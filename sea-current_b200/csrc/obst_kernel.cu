@@ -48,10 +48,14 @@ __global__ void __launch_bounds__(256) collide_kernel(CollideArgs g) {
 #pragma unroll
       for (int j = 0; j <= DEG - r; ++j) { tx[j] = (1.0 - u) * tx[j] + u * tx[j + 1]; ty[j] = (1.0 - u) * ty[j] + u * ty[j + 1]; }
     const double qx = tx[0], qy = ty[0];
+    // chord and edge with disjoint bounding boxes cannot cross (the segment test's u and t are then outside [0, 1] by
+    // far more than its rounding): four compares skip the two divisions for almost every pair
+    const double cxl = fmin(ax, qx), cxh = fmax(ax, qx), cyl = fmin(ay, qy), cyh = fmax(ay, qy);
     for (int e = 0; e < g.E && !hit; ++e) {
       double e0x, e0y, e1x, e1y, ix, iy;
       if (e < ns) { e0x = se[4 * e]; e0y = se[4 * e + 1]; e1x = se[4 * e + 2]; e1y = se[4 * e + 3]; }
       else { e0x = (double)ge[4 * e]; e0y = (double)ge[4 * e + 1]; e1x = (double)ge[4 * e + 2]; e1y = (double)ge[4 * e + 3]; }
+      if (fmin(e0x, e1x) > cxh || fmax(e0x, e1x) < cxl || fmin(e0y, e1y) > cyh || fmax(e0y, e1y) < cyl) continue;
       hit = seg_intersects<double>(ax, ay, qx, qy, e0x, e0y, e1x, e1y, ix, iy);
     }
     ax = qx; ay = qy;
@@ -62,37 +66,66 @@ __global__ void __launch_bounds__(256) collide_kernel(CollideArgs g) {
   }
 }
 
-constexpr int kObstThreads = 256, kObstEdgesSmem = 1024;
+constexpr int kObstThreads = 256, kObstEdgesSmem = 768, kObstPer = 4;
 
 template <class S>
 __global__ void __launch_bounds__(kObstThreads) obst_cap_kernel(ObstArgs g) {
-  __shared__ double se[kObstEdgesSmem * 4];
+  // per edge: start point, direction, 1 / |direction|^2 (0 for a degenerate edge: the distance to its point)
+  __shared__ double se[kObstEdgesSmem * 5];
   const int ns = g.E < kObstEdgesSmem ? g.E : kObstEdgesSmem;
   const S* __restrict__ ge = (const S*)g.edges;
-  for (int i = threadIdx.x; i < 4 * ns; i += kObstThreads) se[i] = (double)ge[i];
+  for (int k = threadIdx.x; k < ns; k += kObstThreads) {
+    const double ax = (double)ge[4 * k], ay = (double)ge[4 * k + 1], ex = (double)ge[4 * k + 2] - ax, ey = (double)ge[4 * k + 3] - ay;
+    const double ee = ex * ex + ey * ey;
+    se[5 * k] = ax; se[5 * k + 1] = ay; se[5 * k + 2] = ex; se[5 * k + 3] = ey; se[5 * k + 4] = ee > 0 ? 1.0 / ee : 0.0;
+  }
   __syncthreads();
   const size_t n = (size_t)g.G * g.P;
   const double ab = g.a_brake, at = g.a_brake * g.t_react, at2 = at * at;
-  for (size_t o = (size_t)blockIdx.x * kObstThreads + threadIdx.x; o < n; o += (size_t)gridDim.x * kObstThreads) {
-    const int p = (int)(o % (size_t)g.P);
-    const double bx = (double)((const S*)g.px)[o], by = (double)((const S*)g.py)[o];
-    double d2 = CUDART_INF;
-    for (int k = 0; k < g.E; ++k) {
-      double ax, ay, ex, ey;
-      if (k < ns) { ax = se[4 * k]; ay = se[4 * k + 1]; ex = se[4 * k + 2] - ax; ey = se[4 * k + 3] - ay; }
-      else { ax = (double)ge[4 * k]; ay = (double)ge[4 * k + 1]; ex = (double)ge[4 * k + 2] - ax; ey = (double)ge[4 * k + 3] - ay; }
-      const double rx = bx - ax, ry = by - ay, ee = ex * ex + ey * ey;
-      double t = ee > 0 ? (rx * ex + ry * ey) / ee : 0.0;
-      t = fmin(fmax(t, 0.0), 1.0);
-      const double qx = rx - t * ex, qy = ry - t * ey;
-      d2 = fmin(d2, qx * qx + qy * qy);
+  // kObstPer elements per thread, a grid stride apart (coalesced): one broadcast read of an edge serves all of them --
+  // with one element per thread the kernel was bound by the shared-memory reads of the edge list, not by the FP64 pipe
+  const size_t stride = (size_t)gridDim.x * kObstThreads;
+  for (size_t o0 = (size_t)blockIdx.x * kObstThreads + threadIdx.x; o0 < n; o0 += stride * kObstPer) {
+    double bx[kObstPer], by[kObstPer], d2[kObstPer];
+#pragma unroll
+    for (int j = 0; j < kObstPer; ++j) {
+      const size_t o = o0 + j * stride;
+      const bool in = o < n;
+      bx[j] = in ? (double)((const S*)g.px)[o] : 0.0; by[j] = in ? (double)((const S*)g.py)[o] : 0.0; d2[j] = CUDART_INF;
     }
-    const double c = -at + sqrt(at2 + 2.0 * ab * sqrt(d2));
-    double lo, hi;
-    if (g.vel_lo_grid && g.vel_hi_grid) { lo = (double)((const S*)g.vel_lo_grid)[o]; hi = (double)((const S*)g.vel_hi_grid)[o]; }
-    else { lo = (double)((const S*)g.vel_lo)[p]; hi = (double)((const S*)g.vel_hi)[p]; }
-    ((S*)g.out_lo)[o] = (S)fmax(lo, -c);
-    ((S*)g.out_hi)[o] = (S)fmin(hi, c);
+    for (int k = 0; k < ns; ++k) {
+      const double ax = se[5 * k], ay = se[5 * k + 1], ex = se[5 * k + 2], ey = se[5 * k + 3], ie = se[5 * k + 4];
+#pragma unroll
+      for (int j = 0; j < kObstPer; ++j) {
+        const double rx = bx[j] - ax, ry = by[j] - ay;
+        const double t = fmin(fmax((rx * ex + ry * ey) * ie, 0.0), 1.0);
+        const double qx = fma(-t, ex, rx), qy = fma(-t, ey, ry);
+        d2[j] = fmin(d2[j], fma(qx, qx, qy * qy));
+      }
+    }
+    for (int k = ns; k < g.E; ++k) {  // an edge list longer than the shared-memory stage: the rest from global memory
+      const double ax = (double)ge[4 * k], ay = (double)ge[4 * k + 1], ex = (double)ge[4 * k + 2] - ax, ey = (double)ge[4 * k + 3] - ay;
+      const double ee = ex * ex + ey * ey;
+#pragma unroll
+      for (int j = 0; j < kObstPer; ++j) {
+        const double rx = bx[j] - ax, ry = by[j] - ay;
+        const double t = fmin(fmax(ee > 0 ? (rx * ex + ry * ey) / ee : 0.0, 0.0), 1.0);
+        const double qx = rx - t * ex, qy = ry - t * ey;
+        d2[j] = fmin(d2[j], qx * qx + qy * qy);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < kObstPer; ++j) {
+      const size_t o = o0 + j * stride;
+      if (o >= n) break;
+      const int p = (int)(o % (size_t)g.P);
+      const double c = -at + sqrt(at2 + 2.0 * ab * sqrt(d2[j]));
+      double lo, hi;
+      if (g.vel_lo_grid && g.vel_hi_grid) { lo = (double)((const S*)g.vel_lo_grid)[o]; hi = (double)((const S*)g.vel_hi_grid)[o]; }
+      else { lo = (double)((const S*)g.vel_lo)[p]; hi = (double)((const S*)g.vel_hi)[p]; }
+      ((S*)g.out_lo)[o] = (S)fmax(lo, -c);
+      ((S*)g.out_hi)[o] = (S)fmin(hi, c);
+    }
   }
 }
 
@@ -100,7 +133,8 @@ __global__ void __launch_bounds__(kObstThreads) obst_cap_kernel(ObstArgs g) {
 
 template <class R> void launch_obst_cap(const ObstArgs& a, cudaStream_t st) {
   const size_t n = (size_t)a.G * a.P;
-  const int grid = (int)((n + kObstThreads - 1) / kObstThreads < (size_t)148 * 16 ? (n + kObstThreads - 1) / kObstThreads : (size_t)148 * 16);
+  const size_t want = (n + (size_t)kObstThreads * kObstPer - 1) / ((size_t)kObstThreads * kObstPer);
+  const int grid = (int)(want < (size_t)148 * 16 ? (want ? want : 1) : (size_t)148 * 16);
   obst_cap_kernel<R><<<grid, kObstThreads, 0, st>>>(a);
 }
 template void launch_obst_cap<double>(const ObstArgs&, cudaStream_t);

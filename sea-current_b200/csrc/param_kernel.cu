@@ -151,10 +151,15 @@ __global__ void __launch_bounds__(32) param_kernel(ParamArgs g) {
   S* __restrict__ o_t = (S*)g.t; S* __restrict__ o_v = (S*)g.v; S* __restrict__ o_a = (S*)g.a; S* __restrict__ o_om = (S*)g.omega;
   const S* __restrict__ kap = (const S*)g.kappa;
   int status = g.status[p];
+  // A problem that arrives failed (bad path, collision verdict, toppra's verdict) gets an all-zero record.  Its thread
+  // walks both sweeps WITH its warp and stores zeros through the same store instructions as its healthy neighbours
+  // (`live` selects the value): no divergent zero-fill loop, and no 32-byte sector written in two partial pieces at
+  // different times (measured with 7 % of C3 colliding: a separate zero-fill loop doubled the kernel's time).
+  const bool live = status == SCB_ST_OK;
   Hermite1 hp;
-  if (status == SCB_ST_OK) {
-    hp.init((R)((const S*)g.L)[p], g.vel_start ? (R)((const S*)g.vel_start)[p] : 0.0,
-            g.vel_end ? (R)((const S*)g.vel_end)[p] : 0.0, N);
+  hp.init(live ? (R)((const S*)g.L)[p] : 1.0, g.vel_start ? (R)((const S*)g.vel_start)[p] : 0.0,
+          g.vel_end ? (R)((const S*)g.vel_end)[p] : 0.0, N);
+  {
     // ---- pass 1: knot times (trapezoid rule, spline.cpp:14-24) + Thomas forward elimination of the
     //      clamped cubic spline through (t_i, q(s_i))  (piecewise_poly_path.cpp:102-176)
     const R sd0 = fast_sqrt((R)X2[p]);
@@ -174,9 +179,9 @@ __global__ void __launch_bounds__(32) param_kernel(ParamArgs g) {
           const R s = hp.s_at(i), sd = fast_sqrt(xs[u]);
           const R avg = (sd_prev + sd) * 0.5;
           const R dt = avg > 1e-8 ? (s - s_prev) * fast_rcp<R>(avg) : 5.0;
-          if (dt < 1e-8) status = SCB_ST_ERR_TIME_KNOTS;
+          if (live && dt < 1e-8) status = SCB_ST_ERR_TIME_KNOTS;
           const R t = t_prev + dt;
-          tb[(size_t)i * P + p] = t;
+          tb[(size_t)i * P + p] = live ? t : 0.0;
           const R qi = hp.q(s);
           const R h = t - t_prev;                          // h_{i-1}
           const R slope = (qi - q_prev) * fast_rcp<R>(h);  // (q_i - q_{i-1}) / h_{i-1}
@@ -198,21 +203,16 @@ __global__ void __launch_bounds__(32) param_kernel(ParamArgs g) {
       }
     }
   }
-  if (status != SCB_ST_OK) {
-    if (g.status[p] == SCB_ST_OK) g.status[p] = status;
-    for (int i = 0; i < G; ++i) {
-      const size_t o = (size_t)i * P + p;
-      tb[o] = 0; Xb[o] = 0;
-      if (o_t) o_t[o] = 0; if (o_v) o_v[o] = 0; if (o_a) o_a[o] = 0; if (o_om) o_om[o] = 0;
-    }
-    if (g.T_total) ((S*)g.T_total)[p] = 0;
-    return;
+  if (live && status != SCB_ST_OK) {  // failed in pass 1 (knot times; rare): its knot times are already stored
+    g.status[p] = status;
+    for (int i = 0; i < G; ++i) tb[(size_t)i * P + p] = 0;
   }
+  const bool good = status == SCB_ST_OK;
   // ---- pass 2 (backward): back substitution, knot derivatives, angular velocity
   R X_next = Xb[(size_t)N * P + p];
   R t_next = tb[(size_t)N * P + p];
   R q_next = hp.q(hp.s_at(N));
-  if (g.T_total) ((S*)g.T_total)[p] = (S)(t_next - tb[p]);
+  if (g.T_total) ((S*)g.T_total)[p] = good ? (S)(t_next - tb[p]) : (S)0;
   const R kapN = kap ? (R)kap[(size_t)N * P + p] : 0.0;
   const R X_N = X_next, t_N = t_next;
   for (int i0 = N - 1; i0 >= 0; i0 -= kPU) {
@@ -228,7 +228,7 @@ __global__ void __launch_bounds__(32) param_kernel(ParamArgs g) {
       if (i >= 0) {
         const size_t o = (size_t)i * P + p;
         const R Xi = xb[u] - cb[u] * X_next;
-        if (g.keep_X) Xb[o] = Xi;
+        if (g.keep_X) Xb[o] = good ? Xi : 0.0;
         const R ti = tt[u], qv = hp.q(hp.s_at(i));
         const R h = t_next - ti;
         const R vi = (q_next - qv) * fast_rcp<R>(h) - h * (1.0 / 3.0) * (2 * Xi + X_next);
@@ -237,15 +237,16 @@ __global__ void __launch_bounds__(32) param_kernel(ParamArgs g) {
           const R k0 = (X_N - Xi) * fast_rcp<R>(3 * h), k1 = Xi;
           const R vN = (k0 * 3) * (h * h) + (k1 * 2) * h + vi, aN = ((k0 * 3) * 2) * h + k1 * 2;
           const size_t oN = (size_t)N * P + p;
-          if (o_t) o_t[oN] = (S)t_N;
-          if (o_v) o_v[oN] = (S)vN;
-          if (o_a) o_a[oN] = (S)aN;
-          if (o_om) o_om[oN] = (S)(vN * kapN);
+          if (g.keep_X && !good) Xb[oN] = 0.0;
+          if (o_t) o_t[oN] = good ? (S)t_N : (S)0;
+          if (o_v) o_v[oN] = good ? (S)vN : (S)0;
+          if (o_a) o_a[oN] = good ? (S)aN : (S)0;
+          if (o_om) o_om[oN] = good ? (S)(vN * kapN) : (S)0;
         }
-        if (o_t) o_t[o] = (S)ti;
-        if (o_v) o_v[o] = (S)vi;
-        if (o_a) o_a[o] = (S)(Xi * 2);
-        if (o_om) o_om[o] = (S)(vi * kk[u]);
+        if (o_t) o_t[o] = good ? (S)ti : (S)0;
+        if (o_v) o_v[o] = good ? (S)vi : (S)0;
+        if (o_a) o_a[o] = good ? (S)(Xi * 2) : (S)0;
+        if (o_om) o_om[o] = good ? (S)(vi * kk[u]) : (S)0;
         X_next = Xi; t_next = ti; q_next = qv;
       }
     }

@@ -203,7 +203,8 @@ class BatchPlanner:
 
     # ------------------------------------------------------------------ HBM-resident buffers
     def make_device_batch(self, inputs, G, outputs=ALL_OUTPUTS, S_cap=0, stages=0, x_cap=0.0, dt=0.0, opt=None, lp_mode=0,
-                          omega_max=0.0, acc_lat_max=0.0, param_mode=0):
+                          omega_max=0.0, acc_lat_max=0.0, param_mode=0, obstacle_edges=None, a_brake=0.0, t_react=0.0,
+                          collision_chords=0):
         """inputs: dict name -> torch CUDA tensor (dtype = ctx precision, contiguous).  Allocates
         the output tensors once and returns (batch_in, batch_out, result_tensors): the structs can be
         passed to run_device() any number of times without further allocation."""
@@ -226,6 +227,10 @@ class BatchPlanner:
         bi.stages, bi.x_cap, bi.dt, bi.lp_mode = stages, x_cap, dt, lp_mode
         bi.omega_max, bi.acc_lat_max = omega_max, acc_lat_max
         bi.param_mode = param_mode
+        bi.a_brake, bi.t_react, bi.collision_chords = a_brake, t_react, collision_chords
+        if obstacle_edges is not None:  # [E][4] CUDA tensor; the caller keeps it alive
+            assert obstacle_edges.is_cuda and obstacle_edges.dtype == tdt and obstacle_edges.is_contiguous()
+            bi.obstacle_edges, bi.n_obstacle_edges = obstacle_edges.data_ptr(), obstacle_edges.shape[0]
         bi.opt = opt if opt is not None else default_opt()
         res = {"status": torch.empty(P, dtype=torch.int32, device=dev),
                "fail_stage": torch.empty(P, dtype=torch.int32, device=dev)}
