@@ -10,11 +10,12 @@
 //
 // One expansion of the lowest-cost open node z:
 //   (1) X_near = unvisited nodes within the radius of z         -> compacted into a list (block-wide)
-//   (2) per x in X_near, ONE WARP scans the open nodes within the radius of x, lanes striding over the
-//       open list (the frontier: far fewer entries than nodes), each lane keeping the cheapest collision-free cost[y] + |xy| it saw; a candidate is tested
-//       against the obstacle edges only if it beats the lane's best so far (the reference costs every
-//       candidate, collision test included: a colliding one evaluates to FLT_MAX and can never win, so the
-//       argmin is the same); warp min-reduction (cost, then lowest index) -> parent[x], cost[x]
+//   (2) per x in X_near, ONE WARP scans the open nodes within the radius of x, lanes striding over the open list
+//       (the frontier: far fewer entries than nodes).  Per 32 entries the lanes cost their own candidate
+//       cost[y] + |xy|, then the warp tests the candidates that would beat its best so far cheapest first, one
+//       obstacle edge per lane; the first collision-free one ends the round (the reference costs every candidate,
+//       collision test included: a colliding one evaluates to FLT_MAX and can never win, so the argmin is the
+//       same).  Ties: lowest index -> parent[x], cost[x]
 //   (3) the newly connected nodes become open only after the sweep (V_open.merge, sc:1381), z is closed,
 //       block-wide argmin over the open set picks the next z.
 // Float arithmetic is the reference's, operation for operation: this file is compiled with --fmad=false
