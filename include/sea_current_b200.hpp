@@ -45,6 +45,7 @@
 #include <functional>
 #include <initializer_list>
 #include <limits>
+#include <memory>
 #include <optional>
 #include <ostream>
 #include <sstream>
@@ -370,6 +371,7 @@ class batch_planner {
   batch_planner(const batch_planner&) = delete;
   batch_planner& operator=(const batch_planner&) = delete;
   scb_ctx* ctx() const { return ctx_; }
+  int mode() const { return mode_; }
   int degree() const { return mode_ == SCB_REF_CUBIC ? 3 : 5; }
   // host buffers in, host buffers out; see seacurrent_b200.h for the layouts
   void plan(const scb_batch_in& in, const scb_batch_out& out) { check(scb_plan_batch(ctx_, &in, &out), ctx_, "scb_plan_batch"); }
@@ -382,9 +384,20 @@ class batch_planner {
 
 constexpr int kDropInMaxWaypoints = 4096, kDropInGrid = 101 /* tp:algorithm.hpp:140 */, kDropInMaxSamples = 1 << 17;
 
-inline batch_planner& drop_in_planner() {  // batch-of-1 context behind the reference-shaped calls
-  static thread_local batch_planner pl(device(), SCB_FP64, spline_mode(), 1, kDropInMaxWaypoints, kDropInGrid, kDropInMaxSamples);
-  return pl;
+// Per-thread context behind the reference-shaped calls.  spline_mode() and device() are mutable globals: the context
+// is rebuilt when either differs from what it was created with, so the mode a call checks is the mode its kernels run.
+inline batch_planner& context_for(std::unique_ptr<batch_planner>& slot, int& dev_of_slot, int max_problems) {
+  if (!slot || slot->mode() != spline_mode() || dev_of_slot != device()) {
+    slot.reset();
+    slot = std::make_unique<batch_planner>(device(), SCB_FP64, spline_mode(), max_problems, kDropInMaxWaypoints, kDropInGrid, kDropInMaxSamples);
+    dev_of_slot = device();
+  }
+  return *slot;
+}
+inline batch_planner& drop_in_planner() {  // batch-of-1
+  static thread_local std::unique_ptr<batch_planner> pl;
+  static thread_local int dev = -1;
+  return context_for(pl, dev, 1);
 }
 
 // FMT* for many (x_init, x_goal) queries over ONE sampled map (scb_fmt_batch: one CTA per query).  An empty
@@ -446,7 +459,7 @@ class bezier_spline {  // sc:388-431
   // sc:599-683 (tangent heuristics sc:343-377, tangent clipping against ps.obstacles sc:575-596).
   static bezier_spline from_path(const std::vector<Vector2f>& path, const planning_space& ps,
                                  float start_angle = std::numeric_limits<float>::quiet_NaN()) {
-    if (!ps.obstacles.empty() && b200::spline_mode() != SCB_REF_CUBIC)
+    if (!ps.obstacles.empty() && b200::drop_in_planner().mode() != SCB_REF_CUBIC)
       throw std::invalid_argument("sea_current_b200: obstacle clipping is defined for the reference's cubic spline only");
     if (path.size() < 2) throw std::invalid_argument("sea_current_b200: a path needs at least two waypoints");
     bezier_spline s;
@@ -494,6 +507,8 @@ class bezier_spline {  // sc:388-431
 
  private:
   std::vector<double> wx_, wy_, arc_, kappa_, edges_;  // edges_: [n][4] obstacle edges of the planning_space
+  std::vector<double> cx_, cy_, tab_;                  // FP64 control points and arc-length tables of build(): what
+                                                       // resample / angular_velocity evaluate (no second from_path)
   float start_angle_ = std::numeric_limits<float>::quiet_NaN();
   arclength_data ad_;
 
@@ -513,6 +528,7 @@ class bezier_spline {  // sc:388-431
     pl.plan(in, out);
     if (status != SCB_ST_OK) throw planning_error(status, -1, "sea_current_b200: bad path (non-finite waypoint or zero-length leg)");
     ctrl_pts.assign((size_t)nseg, std::vector<Vector2f>((size_t)nc));
+    cx_ = cx; cy_ = cy; tab_ = tab;
     ad_ = arclength_data();
     ad_.arclength = (float)L;
     for (int s = 0; s < nseg; ++s) {
@@ -523,19 +539,20 @@ class bezier_spline {  // sc:388-431
     }
   }
 
-  void geometry(const double* vel, bool nudge) {  // SCB_STAGE_SPLINE | SCB_STAGE_GEOMETRY at arc_
+  void geometry(const double* vel, bool nudge) {  // SCB_STAGE_GEOMETRY alone at arc_: the spline of build() is an input
     b200::batch_planner& pl = b200::drop_in_planner();
     const int S = (int)arc_.size();
     if (S > b200::kDropInMaxSamples) throw std::invalid_argument("sea_current_b200: too many samples for the drop-in context");
+    if ((int)cx_.size() != (int)(wx_.size() - 1) * (pl.degree() + 1))
+      throw std::logic_error("sea_current_b200: b200::spline_mode() changed between from_path and resample / angular_velocity");
     std::vector<double> px((size_t)S), py((size_t)S), om((size_t)S), vv;
-    double sa = start_angle_;
     int32_t status = 0, ns = S;
     scb_batch_in in{};
-    in.P = 1; in.W = (int)wx_.size(); in.G = b200::kDropInGrid; in.wx = wx_.data(); in.wy = wy_.data(); in.start_angle = &sa;
-    in.obstacle_edges = edges_.empty() ? nullptr : edges_.data(); in.n_obstacle_edges = (int32_t)(edges_.size() / 4);
-    in.stages = SCB_STAGE_SPLINE | SCB_STAGE_GEOMETRY; in.nudge_positions = nudge ? 1 : 0;
+    in.P = 1; in.W = (int)wx_.size(); in.G = b200::kDropInGrid;
+    in.stages = SCB_STAGE_GEOMETRY; in.nudge_positions = nudge ? 1 : 0;
     scb_default_opt(&in.opt);
     scb_batch_out out{};
+    out.ctrl_x = cx_.data(); out.ctrl_y = cy_.data(); out.arclen_table = tab_.data();
     out.status = &status; out.S_cap = S; out.n_samples = &ns; out.s_pos = arc_.data();
     if (vel) { vv.assign(vel, vel + S); out.s_vel = vv.data(); }
     out.s_px = px.data(); out.s_py = py.data(); out.s_omega = om.data();
@@ -722,7 +739,9 @@ inline std::string handle_text_request_batch(const std::string& req) {
     }
     flush();
   }
-  static thread_local batch_planner pl(device(), SCB_FP64, spline_mode(), 1 << 16, kDropInMaxWaypoints, kDropInGrid, kDropInMaxSamples);
+  static thread_local std::unique_ptr<batch_planner> pl_slot;
+  static thread_local int pl_dev = -1;
+  batch_planner& pl = context_for(pl_slot, pl_dev, 1 << 16);
   const int G = kDropInGrid;
   const double dt = (double)0.02f, nan = std::numeric_limits<double>::quiet_NaN();
   std::vector<int> order;  // requests grouped by waypoint count

@@ -62,7 +62,12 @@ enum {
   /* conditions the reference asserts on or throws for (sc:34-52 SC_ASSERT; tp:constraint/
    * linear_joint_velocity.cpp:54; tp:solver.cpp:36-37) */
   SCB_ST_ERR_BAD_PATH = 16,     /* non-finite waypoint, zero-length leg, or arclength <= 0 */
-  SCB_ST_ERR_BAD_LIMITS = 17,   /* velocity box excludes 0 where q'(s) = 0, or lo > hi */
+  SCB_ST_ERR_BAD_LIMITS = 17,   /* velocity box excludes 0 where q'(s) = 0 (tp:constraint/linear_joint_velocity.cpp:54),
+                                   acc_lo > acc_hi (LinearJointAcceleration::check, tp:constraint/
+                                   linear_joint_acceleration.cpp:18-22), or any limit (scalar or per gridpoint) is NaN.
+                                   Infinite limits are legal ("no limit").  A per-gridpoint velocity box with
+                                   lo > hi is NOT rejected here: like the reference's LinearJointVelocityVarying
+                                   (sc:1177-1188, no check) it makes the stage LP infeasible */
   SCB_ST_ERR_TIME_KNOTS = 18,   /* a knot interval < 1e-8 s (the reference drops such knots,
                                    tp:parametrizer/spline.cpp:25-33; unreachable for x_cap = 100) */
   SCB_ST_ERR_COLLISION = 19     /* the finished spline crosses an obstacle edge (scb_batch_in.collision_chords) */
@@ -104,9 +109,13 @@ enum {
   SCB_STAGE_TIMING = 2,   /* gen_vel_prof: L -> status, K, x, t, v, a, T_total, s_time/pos/vel/acc.
                              Without SCB_STAGE_SPLINE the path length is read from path_len. */
   SCB_STAGE_GEOMETRY = 4  /* resample + angular_velocity: arc length -> px, py, omega and
-                             s_px, s_py, s_omega.  Needs SCB_STAGE_SPLINE in the same call.
+                             s_px, s_py, s_omega.
                              Without SCB_STAGE_TIMING, out->n_samples / s_pos (and s_vel, if
-                             s_omega is wanted) are INPUTS: the positions to resample at. */
+                             s_omega is wanted) are INPUTS: the positions to resample at.
+                             Without SCB_STAGE_SPLINE (and then without SCB_STAGE_TIMING), out->ctrl_x /
+                             ctrl_y / arclen_table are INPUTS too: the spline of an earlier
+                             SCB_STAGE_SPLINE call (the reference's bezier_spline carries its control
+                             points into resample / angular_velocity the same way, sc:898, sc:1055). */
 };
 
 /* Stage-LP back ends of the toppra passes (tp:solver/seidel.cpp:265-347).  Both return the same

@@ -252,8 +252,11 @@ int ora_plan_batch(const scb_batch_in* in, const scb_batch_out* out, int spline_
 #pragma omp parallel for schedule(dynamic)
   for (int p = 0; p < P; ++p) {
     PlanIn pi;
-    pi.path.resize(W);
-    for (int i = 0; i < W; ++i) pi.path[i] = {wx[(size_t)p * W + i], wy[(size_t)p * W + i]};
+    if (in->stages == SCB_STAGE_TIMING) { pi.timing_only = true; pi.path_len = ((const double*)in->path_len)[p]; }
+    else {
+      pi.path.resize(W);
+      for (int i = 0; i < W; ++i) pi.path[i] = {wx[(size_t)p * W + i], wy[(size_t)p * W + i]};
+    }
     pi.start_angle = sa ? sa[p] : NAN;
     std::vector<double> gl, gh;
     if (vlg && vhg) {

@@ -47,6 +47,8 @@ struct PlanIn {
   int solve_mode = tp::SOLVE_THOMAS;
   int param_mode = 0;   // 0 parametrizer::Spline (sc:1231), 1 parametrizer::ConstAccel (tp:parametrizer/const_accel.cpp)
   int S_cap = 0;
+  bool timing_only = false;  // SCB_STAGE_TIMING alone: gen_vel_prof on a path of length path_len, no curve
+  double path_len = 0;
 };
 
 struct PlanOut {
@@ -115,6 +117,10 @@ inline PlanOut plan_one(const PlanIn& in) {
   // ---- spline
   Spline<double> sp;
   bool bad = false;
+  int nseg = 0;
+  std::vector<double> seg_end;
+  std::vector<SegPoly> polys;
+  if (in.timing_only) { o.L = in.path_len; } else {
   for (int i = 0; i < W; ++i) bad = bad || !std::isfinite(in.path[i].x) || !std::isfinite(in.path[i].y);
   for (int i = 0; i + 1 < W && !bad; ++i) bad = !(pt_dist(in.path[i], in.path[i + 1]) > 0.0);
   if (bad) { o.status = ST_BAD_PATH; return o; }
@@ -133,7 +139,7 @@ inline PlanOut plan_one(const PlanIn& in) {
   o.L = ad.arclength;
   for (auto& seg : ad.segments) o.table.insert(o.table.end(), seg.begin(), seg.end());
   if (!(o.L > 0) || !std::isfinite(o.L)) { o.status = ST_BAD_PATH; return o; }
-  const int nseg = sp.n_segments();
+  nseg = sp.n_segments();
   // ---- collision verdict (Lau09 IV-B: a trajectory that is not collision-free has infinite cost): every segment cut
   //      into M chords (de Casteljau), every chord against every obstacle edge with intersects (sc:142-178)
   if (in.collision_chords > 0 && !in.edges.empty()) {
@@ -152,11 +158,12 @@ inline PlanOut plan_one(const PlanIn& in) {
       }
     }
   }
-  std::vector<double> seg_end(nseg);
+  seg_end.resize(nseg);
   double acc = 0;
   for (int j = 0; j < nseg; ++j) { acc += ad.segments[j].back(); seg_end[j] = acc; }
-  std::vector<SegPoly> polys(nseg);
+  polys.resize(nseg);
   for (int j = 0; j < nseg; ++j) polys[j].set(sp.ctrl[j]);
+  }
   // ---- toppra (sc:1191-1233)
   tp::Problem pb;
   pb.path = tp::PPoly::hermite({{0.0}, {o.L}}, {{in.vel_start}, {in.vel_end}}, {0, 1});
@@ -169,9 +176,15 @@ inline PlanOut plan_one(const PlanIn& in) {
   // c_i = min(omega_max / |kappa_i|, sqrt(acc_lat_max / |kappa_i|)), kappa_i = curvature at arc length q(s_i).
   // Obstacle-distance limit (Lau09 III-B eq. 2): c_i = -a_brake t_react + sqrt(a_brake^2 t_react^2 + 2 a_brake d_i),
   // d_i = distance from the curve point of gridpoint i to the closest obstacle edge (point to segment).
+  // LinearJointAcceleration::check throws when lower > upper (tp:constraint/linear_joint_acceleration.cpp:18-22);
+  // a NaN limit, which every comparison of the reference lets through, is reported the same way
+  if (!(in.acc_lo <= in.acc_hi)) { o.status = ST_BAD_LIMITS; return o; }
+  if (vlg && vhg) {
+    for (int i = 0; i < G; ++i) if (std::isnan(vlg[i]) || std::isnan(vhg[i])) { o.status = ST_BAD_LIMITS; return o; }
+  } else if (std::isnan(vlo) || std::isnan(vhi)) { o.status = ST_BAD_LIMITS; return o; }
   const bool obst = in.a_brake > 0 && !in.edges.empty();
   std::vector<double> cl, ch;
-  if (in.omega_max > 0 || in.acc_lat_max > 0 || obst) {
+  if (!in.timing_only && (in.omega_max > 0 || in.acc_lat_max > 0 || obst)) {
     cl.resize(G); ch.resize(G);
     for (int i = 0; i < G; ++i) {
       const double q = pb.path.eval_single(gp[i], 0)[0];
@@ -241,6 +254,7 @@ inline PlanOut plan_one(const PlanIn& in) {
   for (int i = 0; i < G; ++i) {
     o.v[i] = traj(o.t[i], 1);
     o.a[i] = traj(o.t[i], 2);
+    if (in.timing_only) continue;
     const double q = pb.path.eval_single(gp[i], 0)[0];
     int seg; double u, kap;
     arclen_invert(polys, o.table, seg_end, q, seg, u);
@@ -260,6 +274,7 @@ inline PlanOut plan_one(const PlanIn& in) {
       o.s_pos[i] = traj(times[i], 0);
       o.s_vel[i] = traj(times[i], 1);
       o.s_acc[i] = traj(times[i], 2);
+      if (in.timing_only) continue;
       int seg; double u, kap;
       arclen_invert(polys, o.table, seg_end, o.s_pos[i], seg, u);
       curve_at(polys[seg], u, o.s_px[i], o.s_py[i], kap);

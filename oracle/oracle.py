@@ -167,8 +167,10 @@ def lau_optimise(path_xy, opt, start_angle=float("nan")):
 
 def plan_batch(wx=None, wy=None, vel_lo=None, vel_hi=None, acc_lo=None, acc_hi=None, G=101, start_angle=None,
                vel_lo_grid=None, vel_hi_grid=None, vel_start=None, vel_end=None, spline_mode=0, solve_mode=1,
-               S_cap=0, x_cap=0.0, dt=0.0, opt=None, nthreads=0, outputs=None, omega_max=0.0, acc_lat_max=0.0, obstacle_edges=None, param_mode=0, a_brake=0.0, t_react=0.0, collision_chords=0):
-    """The product's batch on the CPU (FP64), same layouts as scb_plan_batch.  Returns (dict, seconds)."""
+               S_cap=0, x_cap=0.0, dt=0.0, opt=None, nthreads=0, outputs=None, omega_max=0.0, acc_lat_max=0.0, obstacle_edges=None, param_mode=0, a_brake=0.0, t_react=0.0, collision_chords=0,
+               path_len=None):
+    """The product's batch on the CPU (FP64), same layouts as scb_plan_batch.  Returns (dict, seconds).
+    path_len (and no waypoints) = SCB_STAGE_TIMING alone: gen_vel_prof on paths of those lengths."""
     abi = _abi()
     keep = []
 
@@ -179,10 +181,14 @@ def plan_batch(wx=None, wy=None, vel_lo=None, vel_hi=None, acc_lo=None, acc_hi=N
         keep.append(a)
         return a.ctypes.data
 
-    wx = _d(wx); P, W = wx.shape
     bi = abi.ScbBatchIn()
+    if wx is None:
+        path_len = _d(np.atleast_1d(path_len)); P, W = len(path_len), 2
+        bi.path_len, bi.stages = arr(path_len, (P,)), abi.STAGE_TIMING
+    else:
+        wx = _d(wx); P, W = wx.shape
+        bi.wx, bi.wy = arr(wx, (P, W)), arr(wy, (P, W))
     bi.P, bi.W, bi.G = P, W, G
-    bi.wx, bi.wy = arr(wx, (P, W)), arr(wy, (P, W))
     bi.start_angle = arr(start_angle, (P,))
     bi.vel_lo, bi.vel_hi = arr(vel_lo, (P,)), arr(vel_hi, (P,))
     bi.vel_lo_grid, bi.vel_hi_grid = arr(vel_lo_grid, (G, P)), arr(vel_hi_grid, (G, P))

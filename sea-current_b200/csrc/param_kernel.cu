@@ -405,8 +405,9 @@ __global__ void __launch_bounds__(64) sample_kernel(SampleArgs g) {
         }
       }
     } else if (geo) {  // resample / angular_velocity of caller-supplied positions
-      const int S = g.n_samples[p];
+      const int S = g.n_samples[p];      // caller-supplied: clamp to [0, S_cap]
       n = S < S_cap ? S : S_cap;
+      if (n < 0) n = 0;
       if (g.nudge && n > 0) {  // sc:902-912, in place like the reference (it takes profile_pos by reference)
         const R Ltot = walk.total;
         o_pos[p] = 0;

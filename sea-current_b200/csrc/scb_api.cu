@@ -25,7 +25,7 @@ enum SlotId {
   SL_L, SL_TABLE, SL_CTRL_X, SL_CTRL_Y, SL_K_LO, SL_K_HI, SL_X, SL_T, SL_XB, SL_CP, SL_KAPPA, SL_STATUS, SL_FAIL, SL_NS,
   // device mirrors of host inputs
   SL_IN_WX, SL_IN_WY, SL_IN_SA, SL_IN_VLO, SL_IN_VHI, SL_IN_VLG, SL_IN_VHG, SL_IN_ALO, SL_IN_AHI, SL_IN_VS,
-  SL_IN_VE, SL_IN_PL, SL_IN_EDGES,
+  SL_IN_VE, SL_IN_PL, SL_IN_EDGES, SL_IN_CX, SL_IN_CY, SL_IN_TAB,
   // device mirrors of host outputs
   SL_O_STATUS, SL_O_FAIL, SL_O_CTRL_X, SL_O_CTRL_Y, SL_O_L, SL_O_TABLE, SL_O_T_TOTAL, SL_O_COST, SL_O_K_LO,
   SL_O_K_HI, SL_O_X, SL_O_T, SL_O_PX, SL_O_PY, SL_O_V, SL_O_A, SL_O_OMEGA, SL_O_NS, SL_O_STIME, SL_O_SPOS,
@@ -94,7 +94,11 @@ int validate(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, int
   if ((stages & SCB_STAGE_TIMING) && (!in->acc_lo || !in->acc_hi)) return SCB_E_INVALID;
   if ((stages & SCB_STAGE_TIMING) && !((in->vel_lo && in->vel_hi) || (in->vel_lo_grid && in->vel_hi_grid))) return SCB_E_INVALID;
   if ((stages & SCB_STAGE_TIMING) && !(stages & SCB_STAGE_SPLINE) && !in->path_len) return SCB_E_INVALID;
-  if ((stages & SCB_STAGE_GEOMETRY) && !(stages & SCB_STAGE_SPLINE)) return SCB_E_INVALID;
+  if ((stages & SCB_STAGE_GEOMETRY) && !(stages & SCB_STAGE_SPLINE)) {
+    // geometry of an EXISTING spline: control points and tables of an earlier SCB_STAGE_SPLINE call are inputs
+    if ((stages & SCB_STAGE_TIMING) || !out->ctrl_x || !out->ctrl_y || !out->arclen_table) return SCB_E_INVALID;
+    if (in->W < 2 || in->W > ctx->cfg.max_waypoints) return SCB_E_INVALID;
+  }
   if (!(in->omega_max >= 0) || !(in->acc_lat_max >= 0)) return SCB_E_INVALID;
   if (in->n_obstacle_edges < 0 || (in->n_obstacle_edges > 0 && !in->obstacle_edges)) return SCB_E_INVALID;
   if (in->collision_chords < 0 || in->collision_chords > 4096) return SCB_E_INVALID;
@@ -442,10 +446,12 @@ int scb_plan_batch(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* ou
       if ((rc = up(SL_IN_VHG, in->vel_hi_grid, G, rs, &din.vel_hi_grid))) return rc;
       if ((rc = up(SL_IN_ALO, in->acc_lo, 1, rs, &din.acc_lo))) return rc;
       if ((rc = up(SL_IN_AHI, in->acc_hi, 1, rs, &din.acc_hi))) return rc;
-      if ((rc = up(SL_IN_VS, in->vel_start, 1, rs, &din.vel_start))) return rc;
-      if ((rc = up(SL_IN_VE, in->vel_end, 1, rs, &din.vel_end))) return rc;
       if (!do_spline && (rc = up(SL_IN_PL, in->path_len, 1, rs, &din.path_len))) return rc;
     }
+    // the end slopes of q(s) are read by the arc kernel (gridpoint geometry) as well as by the timing stage:
+    // mirrored whenever the caller passes them, whatever the stages
+    if ((rc = up(SL_IN_VS, in->vel_start, 1, rs, &din.vel_start))) return rc;
+    if ((rc = up(SL_IN_VE, in->vel_end, 1, rs, &din.vel_end))) return rc;
     // ---- device mirrors (set b) of the requested outputs
     struct Down { void* host; void* dev; size_t rows, elem; };
     Down downs[32];
@@ -464,6 +470,11 @@ int scb_plan_batch(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* ou
     if (do_spline) {
       MIR(SL_O_CTRL_X, ctrl_x, 1, nc * rs); MIR(SL_O_CTRL_Y, ctrl_y, 1, nc * rs);
       MIR(SL_O_L, arclen_total, 1, rs); MIR(SL_O_TABLE, arclen_table, 1, nt * rs); MIR(SL_O_COST, cost, 1, rs);
+    } else if (stages & SCB_STAGE_GEOMETRY) {  // the spline is an input
+      dout.arclen_total = dout.cost = nullptr;
+      if ((rc = up(SL_IN_CX, out->ctrl_x, 1, nc * rs, (const void**)&dout.ctrl_x))) return rc;
+      if ((rc = up(SL_IN_CY, out->ctrl_y, 1, nc * rs, (const void**)&dout.ctrl_y))) return rc;
+      if ((rc = up(SL_IN_TAB, out->arclen_table, 1, nt * rs, (const void**)&dout.arclen_table))) return rc;
     } else { dout.ctrl_x = dout.ctrl_y = dout.arclen_total = dout.arclen_table = dout.cost = nullptr; }
     if (do_timing) {
       MIR(SL_O_T_TOTAL, T_total, 1, rs);

@@ -85,6 +85,11 @@ __device__ __forceinline__ bool vel_xbound(double v, double lo, double hi, doubl
   return !(zero && (hi < 0 || lo > 0));
 }
 
+// A NaN limit must not be dropped by the compare-and-select min / max above (it would read as "unlimited"):
+// SCB_ST_ERR_BAD_LIMITS, like a lower acceleration limit above the upper one, which the reference rejects when it
+// constructs the constraint (LinearJointAcceleration::check, tp:constraint/linear_joint_acceleration.cpp:18-22).
+__device__ __forceinline__ bool both_numbers(double a, double b) { return a == a && b == b; }
+
 constexpr int kTU = 8;  // forward pass: controllable sets of kTU stages are fetched ahead of the dependent chain
 
 }  // namespace
@@ -115,6 +120,10 @@ __global__ void __launch_bounds__(64) toppra_fast_kernel(ToppraArgs g) {
     Al = (double)((const S*)g.acc_lo)[p]; Ah = (double)((const S*)g.acc_hi)[p];
     vlo = g.vel_lo ? (double)((const S*)g.vel_lo)[p] : 0.0; vhi = g.vel_hi ? (double)((const S*)g.vel_hi)[p] : 0.0;
   }
+  if (!pre_failed && (!(Al <= Ah) || (!GRID && !both_numbers(vlo, vhi)))) status = SCB_ST_ERR_BAD_LIMITS;
+  // an infinite acceleration limit is "no limit" (the reference's rows with an infinite constant): the slab algebra
+  // below multiplies limits by u-coefficients that are exactly 0 at the path ends (0 * inf), so it sees +-1e100
+  Al = dmax(Al, -1e100); Ah = dmin(Ah, 1e100);
   const double nAl = -Al, nAh = -Ah, step = 1.0 / (double)N, x_cap = g.x_cap;
   const double c0_3 = 3.0 * c0, c1_2 = 2.0 * c1, c0_6 = 6.0 * c0;
   auto qd = [&](double s) { return c0_3 * (s * s) + c1_2 * s + c2; };
@@ -133,20 +142,21 @@ __global__ void __launch_bounds__(64) toppra_fast_kernel(ToppraArgs g) {
   if (!pre_failed) {
     double lo = vlo, hi = vhi, xl, xh;
     if (GRID) { lo = (double)vlg[o]; hi = (double)vhg[o]; }
+    const bool nums = !GRID || both_numbers(lo, hi);
     if (CURV) curvature_cap((double)kap[o], om_max, al_max, lo, hi);
-    if (!vel_xbound(an, lo, hi, xl, xh)) status = SCB_ST_ERR_BAD_LIMITS;
+    if (!vel_xbound(an, lo, hi, xl, xh) || !nums) status = SCB_ST_ERR_BAD_LIMITS;
   }
   bool alive = status == SCB_ST_OK;
   int first_fail = -1;
-  const bool acc_ok = Al <= Ah + ftol::abs_tol;
 #pragma unroll 1
   for (int i = N - 1; i >= 0; --i) {
     o -= P;
     const double s = (double)i * step, delta = sn - s, twod = 2.0 * delta, a = qd(s), b = qdd(s);
     double lo = vlo, hi = vhi, xlo, xhi;
     if (GRID) { lo = (double)vlg[o]; hi = (double)vhg[o]; }
+    const bool nums = !GRID || both_numbers(lo, hi);
     if (CURV) curvature_cap((double)kap[o], om_max, al_max, lo, hi);
-    const bool vel_ok = vel_xbound(a, lo, hi, xlo, xhi);
+    const bool vel_ok = vel_xbound(a, lo, hi, xlo, xhi) && nums;
     // rows of the stage (tp:constraint.cpp:100-162): acceleration at s_i and, interpolated, at s_{i+1}
     const Slab s1 = orient(a, b, Al, Ah, nAl, nAh);
     const Slab s2 = orient(fma(twod, bn, an), bn, Al, Ah, nAl, nAh);
@@ -161,7 +171,7 @@ __global__ void __launch_bounds__(64) toppra_fast_kernel(ToppraArgs g) {
     ok = pair_apply(D12, r12, fma(s1.hi, s2.al, -(s2.lo * s1.al)), fma(s1.lo, s2.al, -(s2.hi * s1.al)), xl, xh) && ok;
     ok = pair_apply(D01, r01, fma(nhi, s1.al, -(s1.lo * twod)), fma(nlo, s1.al, -(s1.hi * twod)), xl, xh) && ok;
     ok = pair_apply(D02, r02, fma(nhi, s2.al, -(s2.lo * twod)), fma(nlo, s2.al, -(s2.hi * twod)), xl, xh) && ok;
-    ok = ok && !incoherent(xl, xh) && acc_ok;
+    ok = ok && !incoherent(xl, xh);
     if (!ok) { first_fail = i; alive = false; put_K(o, 0.0, 0.0); continue; }
     nhi = xh; nlo = dmax(0.0, xl);
     put_K(o, nlo, nhi);

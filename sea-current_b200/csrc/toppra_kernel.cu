@@ -210,13 +210,18 @@ __global__ void __launch_bounds__(64) toppra_kernel(ToppraArgs g) {
 
   // the reference evaluates every gridpoint's velocity box before the passes
   // (solver.cpp:26-63) and throws on the first bad one: same verdict here.
+  // A lower acceleration limit above the upper one is rejected when the reference constructs the constraint
+  // (LinearJointAcceleration::check, tp:constraint/linear_joint_acceleration.cpp:18-22); a NaN limit, which every
+  // comparison of the reference lets through, is reported the same way (SCB_ST_ERR_BAD_LIMITS).
   if (!pre_failed) {
     double xl, xh;
+    if (!(pk.acc_lo <= pk.acc_hi)) status = SCB_ST_ERR_BAD_LIMITS;
     for (int i = 0; i < G && status == SCB_ST_OK; ++i) {
       double lo = pk.vlo, hi = pk.vhi;
       if (grid_lim) { lo = (double)vlg[(size_t)i * P + p]; hi = (double)vhg[(size_t)i * P + p]; }
-    if (curv) curvature_cap((double)kap[(size_t)i * P + p], g.omega_max, g.acc_lat_max, lo, hi);
-      if (!vel_xbound(pk.qd(pk.s_at(i)), lo, hi, xl, xh)) status = SCB_ST_ERR_BAD_LIMITS;
+      const bool nums = lo == lo && hi == hi;
+      if (curv) curvature_cap((double)kap[(size_t)i * P + p], g.omega_max, g.acc_lat_max, lo, hi);
+      if (!vel_xbound(pk.qd(pk.s_at(i)), lo, hi, xl, xh) || !nums) status = SCB_ST_ERR_BAD_LIMITS;
     }
   }
 

@@ -336,7 +336,7 @@ def test_full_size_properties_c2(planners):
     pl = planners("fp64", "lau_quintic")
     res = pl.plan(**w)
     ok = res["status"] == 0
-    assert ok.mean() > 0.98
+    assert 0.97 < ok.mean() < 0.995   # scb.workloads.hard_cases: about 1 % of the batch fails
     G, P = res["x"].shape
     # forward parametrization lies inside the controllable sets, which lie inside [0, x_cap]
     assert np.all(res["x"][:, ok] <= res["K_hi"][:, ok] * (1 + 1e-12) + 1e-300)
@@ -352,11 +352,13 @@ def test_full_size_properties_c2(planners):
     # toppra's guarantee: q'(s_i) * sdot_i inside the velocity box (q = L (3 s^2 - 2 s^3))
     sg = np.linspace(0.0, 1.0, G)[:, None]
     qd = 6.0 * res["arclen_total"][None, ok] * sg * (1.0 - sg)
-    assert np.all(qd * np.sqrt(res["x"][:, ok]) <= w["vel_hi"][None, ok] * (1 + 1e-9))
+    assert np.all(qd * np.sqrt(res["x"][:, ok]) <= w["vel_hi_grid"][:, ok] * (1 + 1e-9))
+    assert np.all(qd * np.sqrt(res["x"][:, ok]) >= w["vel_lo_grid"][:, ok] * (1 + 1e-9) - 1e-12)
     # the interpolating spline of the parametrizer overshoots a little at the knots (the reference
     # fixture itself shows 0.2531 against a limit of 0.25)
-    over = np.abs(res["v"][:, ok]) / w["vel_hi"][None, ok]
-    assert np.quantile(over, 0.999) <= 1.02 and over.max() <= 1.5
+    over = np.abs(res["v"][:, ok]) / w["vel_hi_grid"][:, ok]
+    plain = (w["vel_hi_grid"].min(axis=0) == w["vel_hi_grid"].max(axis=0))[ok]   # no 10x drop of the limit inside the path
+    assert np.quantile(over, 0.999) <= 1.02 and over[:, plain].max() <= 1.5
     # arc length dominates the chord polygon
     chord = np.sum(np.hypot(np.diff(w["wx"], axis=1), np.diff(w["wy"], axis=1)), axis=1)
     assert np.all(res["arclen_total"][ok] >= chord[ok] * (1 - 1e-12))

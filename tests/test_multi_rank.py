@@ -26,8 +26,11 @@ def test_c4_shards_reproduce_the_global_problem_set():
     whole = scb.workloads.config_c4(P=P)
     for world in (2, 4):
         parts = [scb.workloads.config_c4(P=P, lo=lo, hi=hi) for lo, hi in (scb.shard_range(P, r, world) for r in range(world))]
-        for k in ("wx", "wy", "vel_hi", "acc_hi"):
+        for k in ("wx", "wy", "vel_hi", "acc_hi", "acc_lo"):
             np.testing.assert_array_equal(np.concatenate([p[k] for p in parts], axis=0), whole[k])
+        for k in ("vel_lo_grid", "vel_hi_grid"):  # [G][P]: shards are column blocks
+            np.testing.assert_array_equal(np.concatenate([p[k] for p in parts], axis=1), whole[k])
+            assert all(p[k].flags.c_contiguous for p in parts)
 
 
 def test_summary_record_layout():
