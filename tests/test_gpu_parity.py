@@ -495,3 +495,48 @@ def test_host_chunks_resample_inputs(planners):
         pl.set_host_chunk(0)
     for k in ("status", "n_samples", "arclen_total", "ctrl_x", "ctrl_y", "s_pos", "s_px", "s_py"):  # what such a call writes
         np.testing.assert_array_equal(got[k], one[k], err_msg=k)
+
+
+def test_spline_only_stages_with_end_slopes(planners):
+    """Host entry without SCB_STAGE_TIMING but WITH vel_start / vel_end (valid per seacurrent_b200.h): the arc kernel
+    reads the end slopes whenever they are passed, so their device mirrors must exist whatever the stages (r1 advisor
+    finding: a host pointer reached the kernel).  The spline does not depend on them."""
+    rng = np.random.default_rng(31)
+    P, W = 40, 7
+    wx, wy = scb.workloads.random_walk_paths(rng, P, W)
+    pl = planners("fp64", "ref_cubic")
+    outs = ("arclen_total", "ctrl_x", "ctrl_y", "arclen_table")
+    a = pl.plan(wx=wx, wy=wy, stages=scb.abi.STAGE_SPLINE, outputs=outs)
+    b = pl.plan(wx=wx, wy=wy, stages=scb.abi.STAGE_SPLINE, outputs=outs, vel_start=np.full(P, 0.3), vel_end=np.full(P, 0.1))
+    for k in outs:
+        np.testing.assert_array_equal(a[k], b[k])
+    S = 16
+    pos = np.linspace(0, 1, S)[:, None] * a["arclen_total"][None, :]
+    c = pl.plan(wx=wx, wy=wy, stages=scb.abi.STAGE_SPLINE | scb.abi.STAGE_GEOMETRY, outputs=outs, S_cap=S,
+                resample_at=(pos, None, S), vel_start=np.full(P, 0.3), vel_end=np.full(P, 0.1))
+    assert np.all(c["status"] == 0)
+    np.testing.assert_allclose(c["s_px"][0], wx[:, 0], atol=1e-9)
+
+
+@pytest.mark.parametrize("mode", ["ref_cubic", "lau_quintic"])
+def test_geometry_of_an_existing_spline(planners, mode):
+    """SCB_STAGE_GEOMETRY alone: control points and tables of an earlier SCB_STAGE_SPLINE call are inputs (what the
+    C++ drop-in's resample / angular_velocity do instead of rebuilding the spline): same bits as the merged call.
+    A negative n_samples entry (caller's array) is clamped, not trusted."""
+    rng = np.random.default_rng(41)
+    P, W, S = 24, 9, 48
+    wx, wy = scb.workloads.random_walk_paths(rng, P, W)
+    pl = planners("fp64", mode)
+    outs = ("arclen_total", "ctrl_x", "ctrl_y", "arclen_table")
+    first = pl.plan(wx=wx, wy=wy, stages=scb.abi.STAGE_SPLINE, outputs=outs)
+    pos = np.linspace(0, 1, S)[:, None] * first["arclen_total"][None, :]
+    vel = rng.uniform(0.1, 2.0, (S, P))
+    merged = pl.plan(wx=wx, wy=wy, stages=scb.abi.STAGE_SPLINE | scb.abi.STAGE_GEOMETRY, outputs=outs, S_cap=S,
+                     resample_at=(pos.copy(), vel.copy(), S))
+    ns = np.full(P, S, dtype=np.int32); ns[3] = -7; ns[5] = 0
+    alone = pl.plan(wx=np.zeros((P, W)), stages=scb.abi.STAGE_GEOMETRY, outputs=(), S_cap=S, resample_at=(pos.copy(), vel.copy(), ns),
+                    out_buffers={k: first[k] for k in ("ctrl_x", "ctrl_y", "arclen_table")}, spline_inputs=True)
+    live = np.ones(P, bool); live[[3, 5]] = False
+    for k in ("s_px", "s_py", "s_omega"):
+        np.testing.assert_array_equal(alone[k][:, live], merged[k][:, live], err_msg=k)
+        assert np.all(alone[k][:, ~live] == 0)
