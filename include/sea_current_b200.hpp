@@ -375,11 +375,42 @@ class batch_planner {
   int degree() const { return mode_ == SCB_REF_CUBIC ? 3 : 5; }
   // host buffers in, host buffers out; see seacurrent_b200.h for the layouts
   void plan(const scb_batch_in& in, const scb_batch_out& out) { check(scb_plan_batch(ctx_, &in, &out), ctx_, "scb_plan_batch"); }
+  // rank, then fetch: the batch stays in HBM, the 32-byte summaries come back; fetch() then reads the
+  // records of the few problems the caller keeps (host arrays laid out as scb_batch_out with P := n)
+  void plan_summary(const scb_batch_in& in, bool record_f32, scb_summary* summaries) {
+    check(scb_plan_batch_summary(ctx_, &in, record_f32 ? 1 : 0, summaries), ctx_, "scb_plan_batch_summary");
+  }
+  void fetch(int n, const int32_t* problem_ids, const scb_batch_out& out) { check(scb_fetch(ctx_, n, problem_ids, &out), ctx_, "scb_fetch"); }
   scb_timing timing() const { scb_timing t{}; scb_get_timing(ctx_, &t); return t; }
 
  private:
   scb_ctx* ctx_ = nullptr;
   int precision_, mode_;
+};
+
+// One process, several GPUs: contiguous blocks of ceil(P / R) problems, block r on device r with its own scb_ctx and
+// host thread (scb_multi_*).  Problems share nothing, so there is no collective; the summaries land in the caller's
+// array in problem order.  max_problems is the capacity PER DEVICE.
+class multi_gpu_planner {
+ public:
+  multi_gpu_planner(int n_devices, int precision, int spline_mode, int max_problems, int max_waypoints, int max_gridpoints,
+                    const int32_t* devices = nullptr) {
+    scb_config cfg{0, precision, spline_mode, max_problems, max_waypoints, max_gridpoints, 0};
+    check(scb_multi_create(&m_, &cfg, n_devices, devices), nullptr, "scb_multi_create");
+  }
+  ~multi_gpu_planner() { if (m_) scb_multi_destroy(m_); }
+  multi_gpu_planner(const multi_gpu_planner&) = delete;
+  multi_gpu_planner& operator=(const multi_gpu_planner&) = delete;
+  int devices() const { return scb_multi_devices(m_); }
+  void plan(const scb_batch_in& in, const scb_batch_out& out) { check(scb_multi_plan_batch(m_, &in, &out), nullptr, "scb_multi_plan_batch"); }
+  void plan_summary(const scb_batch_in& in, bool record_f32, scb_summary* summaries) {
+    check(scb_multi_plan_summary(m_, &in, record_f32 ? 1 : 0, summaries), nullptr, "scb_multi_plan_summary");
+  }
+  void fetch(int n, const int32_t* problem_ids, const scb_batch_out& out) { check(scb_multi_fetch(m_, n, problem_ids, &out), nullptr, "scb_multi_fetch"); }
+  scb_timing timing(int r) const { scb_timing t{}; scb_multi_get_timing(m_, r, &t); return t; }
+
+ private:
+  scb_multi* m_ = nullptr;
 };
 
 constexpr int kDropInMaxWaypoints = 4096, kDropInGrid = 101 /* tp:algorithm.hpp:140 */, kDropInMaxSamples = 1 << 17;

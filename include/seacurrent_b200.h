@@ -34,13 +34,14 @@
 #ifndef SEACURRENT_B200_H
 #define SEACURRENT_B200_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
 extern "C" {
 #endif
 
-#define SCB_VERSION 100 /* 0.1.0 */
+#define SCB_VERSION 200 /* 0.2.0 */
 
 /* API-level error codes (function return values) */
 enum {
@@ -206,6 +207,13 @@ typedef struct scb_batch_out {
   void* omega;              /* v * curvature */
   /* uniform-dt stream (what gen_vel_prof + resample + angular_velocity return), [S_cap][P] */
   int32_t S_cap;
+  int32_t record_f32;       /* 1: the trajectory RECORD - t, px, py, v, a, omega and the s_* stream - is float whatever the
+                               ctx precision: what the reference hands its caller (velocity_profile holds VectorXf
+                               pos / vel / acc, sc:379-386, 1245-1262; resample and angular_velocity return float).
+                               Arithmetic is unchanged (FP64 in SCB_FP64); values are rounded once, in the kernels'
+                               stores, so a host call moves half the bytes.  K_lo / K_hi / x, control points, tables
+                               and the [P] scalars stay `real`.  In a geometry-only call the s_pos / s_vel INPUTS are
+                               float too.  0: everything is `real`. */
   int32_t* n_samples;       /* [P]  ceil(T/dt) (sc:1237); entries beyond S_cap are not written */
   void* s_time; void* s_pos; void* s_vel; void* s_acc; void* s_px; void* s_py; void* s_omega;
 } scb_batch_out;
@@ -236,7 +244,18 @@ int scb_set_host_chunk(scb_ctx* ctx, int32_t problems);
 /* Device buffers in and out (already resident in HBM); enqueued on the ctx stream and
  * synchronised before returning unless `async` is non-zero. */
 int scb_plan_batch_device(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, int async);
+/* The same, enqueued on the CALLER's stream (a cudaStream_t, passed as void* so that this header needs no CUDA
+ * header) and never synchronised: an MPC loop overlaps its own kernels and copies with the planning of the next
+ * batch and orders them with its own events.  The ctx's scratch is shared by all calls on the ctx, so a call on a
+ * different stream than the previous one first makes that stream wait (device side, cudaStreamWaitEvent) for the
+ * previous call's kernels.  scb_get_timing after such a call needs the caller to have synchronised `stream`. */
+int scb_plan_batch_async(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, void* stream);
 int scb_synchronize(scb_ctx* ctx);
+
+/* Page-locked host memory for the host-buffer entry points (their copies run at PCIe speed only from / to pinned
+ * memory), so that a caller needs no CUDA toolkit of its own.  NULL on failure. */
+void* scb_alloc_pinned(size_t bytes);
+void scb_free_pinned(void* p);
 
 int scb_get_timing(scb_ctx* ctx, scb_timing* out);
 const char* scb_last_cuda_error(scb_ctx* ctx);
@@ -257,6 +276,35 @@ typedef struct scb_summary {
  * stream; not synchronised. */
 int scb_pack_summary_device(scb_ctx* ctx, int32_t P, const int32_t* status, const int32_t* fail_stage,
                             const void* T_total, const void* arclen_total, const void* cost, scb_summary* dst);
+
+/* ---- Rank, then fetch: what an MPC outer loop does with 65,536 candidate rollouts is rank them by
+ * the 32-byte summaries and read the trajectories of the few it keeps.  scb_plan_batch_summary plans a batch of HOST
+ * inputs, keeps every output of scb_batch_out (except the uniform-dt stream) resident in HBM inside the ctx, and
+ * copies back only summaries[P]; scb_fetch then gathers the records of the n problems the caller names (device-side
+ * gather into compact [G][n] / [n][..] arrays, one small D2H per array) into host arrays laid out as scb_batch_out
+ * with P := n (record arrays float if the plan was made with record_f32).  The retained results stay valid until
+ * the next scb_plan_batch_summary on the ctx. */
+int scb_plan_batch_summary(scb_ctx* ctx, const scb_batch_in* in, int32_t record_f32, scb_summary* summaries);
+int scb_fetch(scb_ctx* ctx, int32_t n, const int32_t* problem_ids, const scb_batch_out* out);
+
+/* ---- One process, several GPUs: problems share nothing, so a batch is cut into contiguous blocks of
+ * ceil(P / R) problems, block r planned on device r by its own scb_ctx and host thread; there is no data-path
+ * collective, and since the summaries land in the caller's host array no gather either (a multi-PROCESS job
+ * all-gathers the same 32-byte records over NCCL: bench.py).  All pointers are HOST pointers. */
+typedef struct scb_multi scb_multi;
+/* cfg->device is ignored; devices = NULL means 0 .. n_devices-1; cfg->max_problems is the capacity PER DEVICE */
+int scb_multi_create(scb_multi** out, const scb_config* cfg, int32_t n_devices, const int32_t* devices);
+int scb_multi_destroy(scb_multi* m);
+int32_t scb_multi_devices(const scb_multi* m);
+/* full records: every device writes its block of columns of the caller's [G][P] arrays (scb_plan_batch per block) */
+int scb_multi_plan_batch(scb_multi* m, const scb_batch_in* in, const scb_batch_out* out);
+/* rank-then-fetch over all devices: summaries[P] in problem order; fetch routes every id to the device that owns it */
+int scb_multi_plan_summary(scb_multi* m, const scb_batch_in* in, int32_t record_f32, scb_summary* summaries);
+int scb_multi_fetch(scb_multi* m, int32_t n, const int32_t* problem_ids, const scb_batch_out* out);
+/* [lo, hi) of the block device r plans out of P problems on R devices */
+void scb_shard_range(int32_t P, int32_t r, int32_t R, int32_t* lo, int32_t* hi);
+/* timing of the last call on device r's ctx */
+int scb_multi_get_timing(scb_multi* m, int32_t r, scb_timing* out);
 
 /* ---- Global planner front end: FMT* over a shared set of sampled nodes, one CTA per query.
  * Replaces planning_space::fast_marching_trees (sc:1339-1407) with cost (sc:1315-1326), near (sc:1328-1337),

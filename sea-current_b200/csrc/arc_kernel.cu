@@ -168,16 +168,18 @@ __global__ void __launch_bounds__(kArcThreads, 3) arc_kernel(PathArgs g) {
   __syncthreads();  // the tables written above are read below by other threads of this CTA
 
   // ---- geometry at the toppra gridpoints: q(s_i) -> (segment, u) -> point, curvature
-  if (g.px || g.py || g.kappa) {
+  if (g.px || g.py || g.kappa || g.px32 || g.py32) {
     const int G = g.G, N = G - 1;
     const double step = 1.0 / (double)N;
     R* o_px = (R*)g.px; R* o_py = (R*)g.py; R* o_k = (R*)g.kappa;
+    float* o_px32 = g.px32; float* o_py32 = g.py32;  // float records beside (or instead of) the R arrays
     int sg = 0;
     for (int it = tid; it < PBa * G; it += T) {
       const int i = it / PBa, pl = it - i * PBa;
       const size_t oo = (size_t)i * P + p0 + pl;
       if (bad[pl]) {
         if (o_px) o_px[oo] = 0; if (o_py) o_py[oo] = 0; if (o_k) o_k[oo] = 0;
+        if (o_px32) o_px32[oo] = 0; if (o_py32) o_py32[oo] = 0;
         continue;
       }
       R bx, by, kap;
@@ -187,6 +189,8 @@ __global__ void __launch_bounds__(kArcThreads, 3) arc_kernel(PathArgs g) {
       if (o_px) o_px[oo] = bx;
       if (o_py) o_py[oo] = by;
       if (o_k) o_k[oo] = kap;
+      if (o_px32) o_px32[oo] = (float)bx;
+      if (o_py32) o_py32[oo] = (float)by;
     }
   }
 }

@@ -140,7 +140,8 @@ struct Hermite1 {  // FP64 in both precision modes, like the toppra kernel
 // gridpoint), and quotients go through fast_rcp / fast_sqrt (no IEEE division sequences).
 constexpr int kPU = 8;
 
-template <class S>
+// O: type of the record arrays t, v, a, omega (= S, or float when scb_batch_out.record_f32 asks for float records)
+template <class S, class O>
 __global__ void __launch_bounds__(32) param_kernel(ParamArgs g) {
   typedef double R;
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
@@ -148,7 +149,7 @@ __global__ void __launch_bounds__(32) param_kernel(ParamArgs g) {
   const int P = g.P, G = g.G, N = G - 1;
   const S* __restrict__ X2 = (const S*)g.x;  // sdot^2
   R* __restrict__ tb = (R*)g.t_buf; R* __restrict__ Xb = (R*)g.X_buf; R* __restrict__ cpb = (R*)g.cp_buf;
-  S* __restrict__ o_t = (S*)g.t; S* __restrict__ o_v = (S*)g.v; S* __restrict__ o_a = (S*)g.a; S* __restrict__ o_om = (S*)g.omega;
+  O* __restrict__ o_t = (O*)g.t; O* __restrict__ o_v = (O*)g.v; O* __restrict__ o_a = (O*)g.a; O* __restrict__ o_om = (O*)g.omega;
   const S* __restrict__ kap = (const S*)g.kappa;
   int status = g.status[p];
   // A problem that arrives failed (bad path, collision verdict, toppra's verdict) gets an all-zero record.  Its thread
@@ -238,15 +239,15 @@ __global__ void __launch_bounds__(32) param_kernel(ParamArgs g) {
           const R vN = (k0 * 3) * (h * h) + (k1 * 2) * h + vi, aN = ((k0 * 3) * 2) * h + k1 * 2;
           const size_t oN = (size_t)N * P + p;
           if (g.keep_X && !good) Xb[oN] = 0.0;
-          if (o_t) o_t[oN] = good ? (S)t_N : (S)0;
-          if (o_v) o_v[oN] = good ? (S)vN : (S)0;
-          if (o_a) o_a[oN] = good ? (S)aN : (S)0;
-          if (o_om) o_om[oN] = good ? (S)(vN * kapN) : (S)0;
+          if (o_t) o_t[oN] = good ? (O)t_N : (O)0;
+          if (o_v) o_v[oN] = good ? (O)vN : (O)0;
+          if (o_a) o_a[oN] = good ? (O)aN : (O)0;
+          if (o_om) o_om[oN] = good ? (O)(vN * kapN) : (O)0;
         }
-        if (o_t) o_t[o] = good ? (S)ti : (S)0;
-        if (o_v) o_v[o] = good ? (S)vi : (S)0;
-        if (o_a) o_a[o] = good ? (S)(Xi * 2) : (S)0;
-        if (o_om) o_om[o] = good ? (S)(vi * kk[u]) : (S)0;
+        if (o_t) o_t[o] = good ? (O)ti : (O)0;
+        if (o_v) o_v[o] = good ? (O)vi : (O)0;
+        if (o_a) o_a[o] = good ? (O)(Xi * 2) : (O)0;
+        if (o_om) o_om[o] = good ? (O)(vi * kk[u]) : (O)0;
         X_next = Xi; t_next = ti; q_next = qv;
       }
     }
@@ -258,7 +259,7 @@ __global__ void __launch_bounds__(32) param_kernel(ParamArgs g) {
 // record of every gridpoint, with no system to solve and no scratch besides the knot times the sampler reads.
 // Knot i >= 1 is evaluated the way evalParams finds it: on interval k = i - 1 at dt = t_i - t_{i-1} (lower_bound over
 // m_ts[1 .. G-2]); knot 0 on interval 0 at dt = 0.
-template <class S>
+template <class S, class O>
 __global__ void __launch_bounds__(32) param_ca_kernel(ParamArgs g) {
   typedef double R;
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
@@ -266,7 +267,7 @@ __global__ void __launch_bounds__(32) param_ca_kernel(ParamArgs g) {
   const int P = g.P, G = g.G, N = G - 1;
   const S* __restrict__ X2 = (const S*)g.x;
   R* __restrict__ tb = (R*)g.t_buf;
-  S* __restrict__ o_t = (S*)g.t; S* __restrict__ o_v = (S*)g.v; S* __restrict__ o_a = (S*)g.a; S* __restrict__ o_om = (S*)g.omega;
+  O* __restrict__ o_t = (O*)g.t; O* __restrict__ o_v = (O*)g.v; O* __restrict__ o_a = (O*)g.a; O* __restrict__ o_om = (O*)g.omega;
   const S* __restrict__ kap = (const S*)g.kappa;
   int status = g.status[p];
   if (status == SCB_ST_OK) {
@@ -295,20 +296,20 @@ __global__ void __launch_bounds__(32) param_ca_kernel(ParamArgs g) {
           if (i == 1) {  // knot 0: interval 0, dt = 0
             const R q1 = hp.qd(s_prev);
             const R vel = q1 * v_prev, acc = hp.qdd(s_prev) * v_prev * v_prev + q1 * acc_k;
-            if (o_t) o_t[p] = (S)0;
-            if (o_v) o_v[p] = (S)vel;
-            if (o_a) o_a[p] = (S)acc;
-            if (o_om) o_om[p] = (S)(vel * kap0);
+            if (o_t) o_t[p] = (O)0;
+            if (o_v) o_v[p] = (O)vel;
+            if (o_a) o_a[p] = (O)acc;
+            if (o_om) o_om[p] = (O)(vel * kap0);
           }
           const R dk = t - t_prev;
           const R vs = v_prev + dk * acc_k;
           const R ss = fmin(fmax(s_prev + dk * v_prev + 0.5 * dk * dk * acc_k, 0.0), 1.0);  // const_accel.cpp:80-81
           const R q1 = hp.qd(ss);
           const R vel = q1 * vs, acc = hp.qdd(ss) * vs * vs + q1 * acc_k;
-          if (o_t) o_t[o] = (S)t;
-          if (o_v) o_v[o] = (S)vel;
-          if (o_a) o_a[o] = (S)acc;
-          if (o_om) o_om[o] = (S)(vel * kk[u]);
+          if (o_t) o_t[o] = (O)t;
+          if (o_v) o_v[o] = (O)vel;
+          if (o_a) o_a[o] = (O)acc;
+          if (o_om) o_om[o] = (O)(vel * kk[u]);
           t_prev = t; s_prev = s; v_prev = v;
         }
       }
@@ -328,13 +329,15 @@ __global__ void __launch_bounds__(32) param_ca_kernel(ParamArgs g) {
   }
 }
 
-template <class R, int DEG>
+// O: type of the stream arrays s_* (= R, or float when scb_batch_out.record_f32 asks for float records; in a
+// geometry-only call the caller's s_pos / s_vel inputs have that type too)
+template <class R, int DEG, class O>
 __global__ void __launch_bounds__(64) sample_kernel(SampleArgs g) {
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
   if (p >= g.P) return;
   const int P = g.P, N = g.G - 1, S_cap = g.S_cap;
-  R* o_time = (R*)g.s_time; R* o_pos = (R*)g.s_pos; R* o_vel = (R*)g.s_vel; R* o_acc = (R*)g.s_acc;
-  R* o_px = (R*)g.s_px; R* o_py = (R*)g.s_py; R* o_om = (R*)g.s_omega;
+  O* o_time = (O*)g.s_time; O* o_pos = (O*)g.s_pos; O* o_vel = (O*)g.s_vel; O* o_acc = (O*)g.s_acc;
+  O* o_px = (O*)g.s_px; O* o_py = (O*)g.s_py; O* o_om = (O*)g.s_omega;
   const bool ok = g.status[p] == SCB_ST_OK;
   int n = 0;
   if (ok) {
@@ -392,16 +395,16 @@ __global__ void __launch_bounds__(64) sample_kernel(SampleArgs g) {
           acc = ((k0 * 3) * 2) * ds + k1 * 2;
         }
         const size_t o = (size_t)i * P + p;
-        if (o_time) o_time[o] = (R)time;
-        if (o_pos) o_pos[o] = (R)pos;
-        if (o_vel) o_vel[o] = (R)vel;
-        if (o_acc) o_acc[o] = (R)acc;
+        if (o_time) o_time[o] = (O)time;
+        if (o_pos) o_pos[o] = (O)pos;
+        if (o_vel) o_vel[o] = (O)vel;
+        if (o_acc) o_acc[o] = (O)acc;
         if (geo) {
           R px, py, kap;
           walk.locate((R)pos, px, py, kap);
-          if (o_px) o_px[o] = px;
-          if (o_py) o_py[o] = py;
-          if (o_om) o_om[o] = (R)(vel * (double)kap);
+          if (o_px) o_px[o] = (O)px;
+          if (o_py) o_py[o] = (O)py;
+          if (o_om) o_om[o] = (O)(vel * (double)kap);
         }
       }
     } else if (geo) {  // resample / angular_velocity of caller-supplied positions
@@ -409,14 +412,14 @@ __global__ void __launch_bounds__(64) sample_kernel(SampleArgs g) {
       n = S < S_cap ? S : S_cap;
       if (n < 0) n = 0;
       if (g.nudge && n > 0) {  // sc:902-912, in place like the reference (it takes profile_pos by reference)
-        const R Ltot = walk.total;
+        const O Ltot = (O)walk.total;
         o_pos[p] = 0;
         o_pos[(size_t)(n - 1) * P + p] = Ltot;
-        R prev = 0;
+        O prev = 0;
         for (int i = 1; i + 1 < n; ++i) {
           const size_t o = (size_t)i * P + p;
-          R cur = o_pos[o];
-          const R nxt = o_pos[o + P];
+          O cur = o_pos[o];
+          const O nxt = o_pos[o + P];
           if (cur < prev || cur > nxt) cur = (prev + nxt) / 2;
           if (cur < 0) cur = 0;
           if (cur > Ltot) cur = Ltot;
@@ -427,10 +430,10 @@ __global__ void __launch_bounds__(64) sample_kernel(SampleArgs g) {
       for (int i = 0; i < n; ++i) {
         const size_t o = (size_t)i * P + p;
         R px, py, kap;
-        walk.locate(o_pos[o], px, py, kap);
-        if (o_px) o_px[o] = px;
-        if (o_py) o_py[o] = py;
-        if (o_om) o_om[o] = (o_vel ? o_vel[o] : (R)1) * kap;
+        walk.locate((R)o_pos[o], px, py, kap);
+        if (o_px) o_px[o] = (O)px;
+        if (o_py) o_py[o] = (O)py;
+        if (o_om) o_om[o] = (O)((o_vel ? (R)o_vel[o] : (R)1) * kap);
       }
     }
   } else if (g.timing) {
@@ -445,13 +448,18 @@ __global__ void __launch_bounds__(64) sample_kernel(SampleArgs g) {
 
 template <class R> void launch_param(const ParamArgs& a, cudaStream_t st) {
   const int block = 32, grid = (a.P + block - 1) / block;
-  if (a.param_mode == SCB_PARAM_CONST_ACCEL) param_ca_kernel<R><<<grid, block, 0, st>>>(a);
-  else param_kernel<R><<<grid, block, 0, st>>>(a);  // R = storage type
+  const bool f32 = a.rec_f32 && sizeof(R) == 8;  // R = storage type
+  if (a.param_mode == SCB_PARAM_CONST_ACCEL) {
+    if (f32) param_ca_kernel<R, float><<<grid, block, 0, st>>>(a); else param_ca_kernel<R, R><<<grid, block, 0, st>>>(a);
+  } else {
+    if (f32) param_kernel<R, float><<<grid, block, 0, st>>>(a); else param_kernel<R, R><<<grid, block, 0, st>>>(a);
+  }
 }
 template <class R> void launch_sample(const SampleArgs& a, cudaStream_t st) {
   const int block = 64, grid = (a.P + block - 1) / block;
-  if (a.deg == 3) sample_kernel<R, 3><<<grid, block, 0, st>>>(a);
-  else sample_kernel<R, 5><<<grid, block, 0, st>>>(a);
+  const bool f32 = a.rec_f32 && sizeof(R) == 8;
+  if (a.deg == 3) { if (f32) sample_kernel<R, 3, float><<<grid, block, 0, st>>>(a); else sample_kernel<R, 3, R><<<grid, block, 0, st>>>(a); }
+  else { if (f32) sample_kernel<R, 5, float><<<grid, block, 0, st>>>(a); else sample_kernel<R, 5, R><<<grid, block, 0, st>>>(a); }
 }
 template void launch_param<double>(const ParamArgs&, cudaStream_t);
 template void launch_param<float>(const ParamArgs&, cudaStream_t);

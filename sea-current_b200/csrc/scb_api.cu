@@ -12,6 +12,8 @@
 #include <cstdio>
 #include <cstring>
 #include <new>
+#include <thread>
+#include <vector>
 
 #include "scb_common.cuh"
 
@@ -34,6 +36,9 @@ enum SlotId {
   SL_FMT_IN, SL_FMT_OUT,
   // obstacle-distance speed limit: curve points when the caller did not ask for them, capped per-gridpoint boxes
   SL_PX, SL_PY, SL_CAP_LO, SL_CAP_HI,
+  // scb_plan_batch_summary: every output stays resident in HBM until the next such call; scb_fetch gathers from it
+  SL_R_STATUS, SL_R_FAIL, SL_R_CTRL_X, SL_R_CTRL_Y, SL_R_L, SL_R_TABLE, SL_R_T_TOTAL, SL_R_COST, SL_R_K_LO, SL_R_K_HI,
+  SL_R_X, SL_R_T, SL_R_PX, SL_R_PY, SL_R_V, SL_R_A, SL_R_OMEGA, SL_R_SUMMARY, SL_F_IDS, SL_F_STAGE,
   SL_COUNT
 };
 
@@ -41,7 +46,14 @@ enum SlotId {
 
 struct scb_ctx {
   scb_config cfg;
-  cudaStream_t stream = nullptr;
+  cudaStream_t stream = nullptr;        // the ctx's own stream
+  cudaStream_t run = nullptr;           // stream the current call launches on (= stream, or the caller's: scb_plan_batch_async)
+  cudaStream_t last = nullptr;          // stream of the previous call; ev_last marks its end
+  cudaEvent_t ev_last = nullptr;
+  std::vector<void*> retired;           // scratch buffers replaced by larger ones: freed when the ctx is idle
+  // results retained by scb_plan_batch_summary
+  scb_batch_out kept = {};
+  int kept_P = 0, kept_W = 0, kept_G = 0, kept_rec32 = 0;
   cudaStream_t copy_stream = nullptr;   // D2H of chunk c while chunk c+1 computes (scb_plan_batch)
   cudaEvent_t ev[9] = {}, ev_done[2] = {}, ev_copied[2] = {};
   Slot slot[2 * SL_COUNT];              // second half: mirror set 1 of the chunked host call
@@ -66,18 +78,25 @@ int fail_cuda(scb_ctx* c, cudaError_t e, const char* where) {
     if (e_ != cudaSuccess) return fail_cuda(ctx, e_, #call);   \
   } while (0)
 
-// grow-only device buffer
+// grow-only device buffer.  A buffer that has to grow may still be read by kernels in flight (an asynchronous call, or
+// the other half of the chunk pipeline): it is retired, not freed - cudaFree would have to wait for the device.
 int ensure(scb_ctx* ctx, int id, size_t bytes, void** out) {
   Slot& s = ctx->slot[id];
   if (bytes == 0) bytes = 16;
   if (s.bytes < bytes) {
-    if (s.p) { cudaFree(s.p); s.p = nullptr; s.bytes = 0; }
+    if (s.p) { ctx->retired.push_back(s.p); s.p = nullptr; s.bytes = 0; }
     cudaError_t e = cudaMalloc(&s.p, bytes);
     if (e != cudaSuccess) { fail_cuda(ctx, e, "cudaMalloc"); return e == cudaErrorMemoryAllocation ? SCB_E_NOMEM : SCB_E_CUDA; }
     s.bytes = bytes;
   }
   *out = s.p;
   return SCB_OK;
+}
+
+// free the scratch buffers that were replaced by larger ones; called only when the ctx's streams are idle
+void release_retired(scb_ctx* ctx) {
+  for (void* p : ctx->retired) cudaFree(p);
+  ctx->retired.clear();
 }
 
 size_t real_size(const scb_ctx* c) { return c->cfg.precision == SCB_FP64 ? 8 : 4; }
@@ -127,9 +146,13 @@ template <class R>
 int run_device(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, int stages) {
   const int P = in->P, W = in->W, G = in->G, deg = degree_of(ctx);
   const size_t rs = sizeof(R);
-  cudaStream_t st = ctx->stream;
+  cudaStream_t st = ctx->run ? ctx->run : ctx->stream;
   int launches = 0;
   if (P == 0) return SCB_OK;
+  // scratch is shared by every call on the ctx: a call on another stream than the previous one waits for it
+  if (ctx->last && ctx->last != st) SCB_CUDA(cudaStreamWaitEvent(st, ctx->ev_last, 0));
+  // float records (scb_batch_out.record_f32): only a conversion in the stores of the FP64 kernels
+  const bool rec32 = out->record_f32 != 0 && sizeof(R) == 8;
   const bool do_spline = stages & SCB_STAGE_SPLINE, do_timing = stages & SCB_STAGE_TIMING,
              do_geo = stages & SCB_STAGE_GEOMETRY;
   int rc;
@@ -142,7 +165,7 @@ int run_device(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, i
   void* dKappa = nullptr;
   const bool curv = in->omega_max > 0 || in->acc_lat_max > 0;  // validate(): needs all three stages
   const bool obst = in->a_brake > 0 && in->n_obstacle_edges > 0 && in->obstacle_edges;  // ditto
-  void *dPx = out->px, *dPy = out->py;
+  void *dPx = rec32 ? nullptr : out->px, *dPy = rec32 ? nullptr : out->py;  // R-typed curve points (the obstacle kernel's input)
   if (do_spline) {
     const size_t nseg = W - 1;
     // the control points and the arc-length tables are the hand-over between the path kernel and the
@@ -163,6 +186,7 @@ int run_device(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, i
         if (!dPy && (rc = ensure(ctx, SL_PY, (size_t)G * P * rs, &dPy))) return rc;
       }
       a.px = dPx; a.py = dPy;
+      if (rec32) { a.px32 = (float*)out->px; a.py32 = (float*)out->py; }
       if (out->omega || curv) { if ((rc = ensure(ctx, SL_KAPPA, (size_t)G * P * rs, &dKappa))) return rc; a.kappa = dKappa; }
     }
     a.opt = in->opt;
@@ -184,8 +208,8 @@ int run_device(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, i
   SCB_CUDA(cudaEventRecord(ctx->ev[2], st));
   // internal state of the recurrences is FP64 in both precision modes: in FP64 mode the caller's
   // K_lo / K_hi / t arrays double as that state, in FP32 mode it lives in scratch
-  const bool f64 = sizeof(R) == 8;
-  void *dT = f64 ? out->t : nullptr, *dXb = nullptr, *dCp = nullptr, *dXsq = nullptr;
+  const bool f64 = sizeof(R) == 8, t_is_state = f64 && !rec32;  // the caller's FP64 t array doubles as the knot-time state
+  void *dT = t_is_state ? out->t : nullptr, *dXb = nullptr, *dCp = nullptr, *dXsq = nullptr;
   if (do_timing) {
     void *dKlo = f64 ? out->K_lo : nullptr, *dKhi = f64 ? out->K_hi : nullptr, *dX = out->x;
     const size_t gp = (size_t)G * P * rs, gp8 = (size_t)G * P * 8;
@@ -224,7 +248,8 @@ int run_device(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, i
     ParamArgs q{};
     q.P = P; q.G = G; q.L = dL; q.vel_start = in->vel_start; q.vel_end = in->vel_end;
     q.x = dX; q.kappa = dKappa;
-    q.t = f64 ? nullptr : out->t; q.v = out->v; q.a = out->a; q.omega = out->omega;
+    q.t = t_is_state ? nullptr : out->t; q.v = out->v; q.a = out->a; q.omega = out->omega;
+    q.rec_f32 = rec32 ? 1 : 0;
     q.t_buf = dT; q.X_buf = dXb; q.cp_buf = dCp; q.T_total = out->T_total; q.status = out->status;
     q.keep_X = want_stream ? 1 : 0;
     q.param_mode = in->param_mode;
@@ -247,10 +272,13 @@ int run_device(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, i
     s.s_time = out->s_time; s.s_pos = out->s_pos; s.s_vel = out->s_vel; s.s_acc = out->s_acc;
     s.s_px = out->s_px; s.s_py = out->s_py; s.s_omega = out->s_omega; s.status = out->status;
     s.timing = do_timing ? 1 : 0; s.geometry = do_geo ? 1 : 0; s.nudge = in->nudge_positions ? 1 : 0;
+    s.rec_f32 = rec32 ? 1 : 0;
     launch_sample<R>(s, st);
     ++launches;
   }
   SCB_CUDA(cudaEventRecord(ctx->ev[5], st));
+  SCB_CUDA(cudaEventRecord(ctx->ev_last, st));
+  ctx->last = st;
   SCB_CUDA(cudaGetLastError());
   ctx->timing.launches = launches;
   ctx->timing_pending = true;
@@ -333,6 +361,7 @@ int scb_create(scb_ctx** out, const scb_config* cfg) {
     delete ctx; return SCB_E_CUDA;
   }
   for (auto& e : ctx->ev) if (cudaEventCreate(&e) != cudaSuccess) { scb_destroy(ctx); return SCB_E_CUDA; }
+  if (cudaEventCreateWithFlags(&ctx->ev_last, cudaEventDisableTiming) != cudaSuccess) { scb_destroy(ctx); return SCB_E_CUDA; }
   *out = ctx;
   return SCB_OK;
 }
@@ -341,6 +370,9 @@ int scb_destroy(scb_ctx* ctx) {
   if (!ctx) return SCB_E_INVALID;
   cudaSetDevice(ctx->cfg.device);
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+  if (ctx->last && ctx->last != ctx->stream && ctx->ev_last) cudaEventSynchronize(ctx->ev_last);  // a caller's stream
+  release_retired(ctx);
+  if (ctx->ev_last) cudaEventDestroy(ctx->ev_last);
   for (auto& s : ctx->slot) if (s.p) cudaFree(s.p);
   for (auto& e : ctx->ev) if (e) cudaEventDestroy(e);
   for (auto& e : ctx->ev_done) if (e) cudaEventDestroy(e);
@@ -357,39 +389,112 @@ int scb_plan_batch_device(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_
   if (rc) return rc;
   SCB_CUDA(cudaSetDevice(ctx->cfg.device));
   ctx->host_call = false;
+  ctx->run = nullptr;
   rc = run_device_any(ctx, in, out, stages);
   if (rc) return rc;
-  if (!async) { SCB_CUDA(cudaStreamSynchronize(ctx->stream)); collect_timing(ctx); }
+  if (!async) { SCB_CUDA(cudaStreamSynchronize(ctx->stream)); collect_timing(ctx); release_retired(ctx); }
   return SCB_OK;
+}
+
+int scb_plan_batch_async(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, void* stream) {
+  int stages;
+  int rc = validate(ctx, in, out, stages);
+  if (rc) return rc;
+  SCB_CUDA(cudaSetDevice(ctx->cfg.device));
+  ctx->host_call = false;
+  ctx->run = stream ? (cudaStream_t)stream : ctx->stream;
+  rc = run_device_any(ctx, in, out, stages);
+  ctx->run = nullptr;
+  return rc;
 }
 
 int scb_synchronize(scb_ctx* ctx) {
   if (!ctx) return SCB_E_INVALID;
   SCB_CUDA(cudaSetDevice(ctx->cfg.device));
   SCB_CUDA(cudaStreamSynchronize(ctx->stream));
+  if (ctx->last && ctx->last != ctx->stream) SCB_CUDA(cudaEventSynchronize(ctx->ev_last));  // a caller's stream
   collect_timing(ctx);
+  release_retired(ctx);
   return SCB_OK;
 }
 
-// Host buffers in, host buffers out.  A large batch is planned in chunks of `chunk` problems: the kernels of
-// chunk c+1 run on the ctx stream while the trajectory records of chunk c travel to the host on a second
-// stream (two sets of device mirrors, ping-pong), so the call costs the D2H time plus ONE chunk of kernels
-// instead of their sum.  Chunks are compact on the device ([G][Pc]); the caller's [G][P] arrays are filled by
-// pitched copies.  Problems are independent, so the results do not depend on the chunking
-// (tests/test_gpu_parity.py::test_host_chunks_bit_identical).
-int scb_plan_batch(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out) {
-  int stages;
-  int rc = validate(ctx, in, out, stages);
-  if (rc) return rc;
+// Host buffers in, host buffers out, for problems [base, base + Pn) of the caller's arrays (leading dimension
+// in->P): scb_plan_batch is the whole range, scb_multi_plan_batch gives every device its block.  A large range is
+// planned in chunks of `chunk` problems: the kernels of chunk c+1 run on the ctx stream while the trajectory records
+// of chunk c travel to the host on a second stream (two sets of device mirrors, ping-pong), so the call costs the
+// D2H time plus ONE chunk of kernels instead of their sum.  Chunks are compact on the device ([G][Pc]); the
+// caller's [G][P] arrays are filled by pitched copies.  Problems are independent, so the results do not depend on
+// the chunking (tests/test_gpu_parity.py::test_host_chunks_bit_identical).
+}  // extern "C"
+
+namespace {
+
+// H2D of the inputs of problems [p0, p0 + Pc) (host arrays of leading dimension P) into the ctx's input mirrors,
+// on stream st; din receives the device pointers.  The obstacle edge list is shared: uploaded when `edges_too`.
+int upload_inputs(scb_ctx* ctx, const scb_batch_in* in, int stages, int p0, int Pc, cudaStream_t st, bool edges_too,
+                  const void** dEdges, scb_batch_in& din) {
+  const int P = in->P, W = in->W, G = in->G;
+  const size_t rs = real_size(ctx);
+  const bool do_spline = stages & SCB_STAGE_SPLINE, do_timing = stages & SCB_STAGE_TIMING;
+  int rc;
+  din = *in;
+  din.P = Pc;
+  auto up = [&](int id, const void* src, size_t rows, size_t elem, const void** dst) -> int {
+    if (!src) { *dst = nullptr; return SCB_OK; }
+    void* d;
+    int r = ensure(ctx, id, rows * Pc * elem, &d);
+    if (r) return r;
+    const size_t w = (size_t)Pc * elem, hp = (size_t)P * elem;
+    const char* h = (const char*)src + (size_t)p0 * elem;
+    cudaError_t e = (rows == 1 || Pc == P) ? cudaMemcpyAsync(d, h, w * rows, cudaMemcpyHostToDevice, st)
+                                           : cudaMemcpy2DAsync(d, w, h, hp, w, rows, cudaMemcpyHostToDevice, st);
+    if (e != cudaSuccess) return fail_cuda(ctx, e, "cudaMemcpyAsync H2D");
+    *dst = d;
+    return SCB_OK;
+  };
+  if (do_spline) {
+    if ((rc = up(SL_IN_WX, in->wx, 1, W * rs, &din.wx))) return rc;
+    if ((rc = up(SL_IN_WY, in->wy, 1, W * rs, &din.wy))) return rc;
+    if ((rc = up(SL_IN_SA, in->start_angle, 1, rs, &din.start_angle))) return rc;
+    if (in->n_obstacle_edges > 0) {  // shared by every problem: uploaded once
+      if (edges_too) {
+        void* d;
+        if ((rc = ensure(ctx, SL_IN_EDGES, (size_t)in->n_obstacle_edges * 4 * rs, &d))) return rc;
+        SCB_CUDA(cudaMemcpyAsync(d, in->obstacle_edges, (size_t)in->n_obstacle_edges * 4 * rs, cudaMemcpyHostToDevice, st));
+        *dEdges = d;
+      }
+      din.obstacle_edges = *dEdges;
+    }
+  }
+  if (do_timing) {
+    if ((rc = up(SL_IN_VLO, in->vel_lo, 1, rs, &din.vel_lo))) return rc;
+    if ((rc = up(SL_IN_VHI, in->vel_hi, 1, rs, &din.vel_hi))) return rc;
+    if ((rc = up(SL_IN_VLG, in->vel_lo_grid, G, rs, &din.vel_lo_grid))) return rc;
+    if ((rc = up(SL_IN_VHG, in->vel_hi_grid, G, rs, &din.vel_hi_grid))) return rc;
+    if ((rc = up(SL_IN_ALO, in->acc_lo, 1, rs, &din.acc_lo))) return rc;
+    if ((rc = up(SL_IN_AHI, in->acc_hi, 1, rs, &din.acc_hi))) return rc;
+    if (!do_spline && (rc = up(SL_IN_PL, in->path_len, 1, rs, &din.path_len))) return rc;
+  }
+  // the end slopes of q(s) are read by the arc kernel (gridpoint geometry) as well as by the timing stage:
+  // mirrored whenever the caller passes them, whatever the stages
+  if ((rc = up(SL_IN_VS, in->vel_start, 1, rs, &din.vel_start))) return rc;
+  if ((rc = up(SL_IN_VE, in->vel_end, 1, rs, &din.vel_end))) return rc;
+  return SCB_OK;
+}
+
+int plan_host_range(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, int stages, int base, int Pn) {
   SCB_CUDA(cudaSetDevice(ctx->cfg.device));
   const int P = in->P, W = in->W, G = in->G, deg = degree_of(ctx), S = out->S_cap;
-  if (P == 0) return SCB_OK;
+  if (Pn == 0) return SCB_OK;
   const size_t rs = real_size(ctx);
+  const size_t rr = out->record_f32 ? 4 : rs;  // element size of the record arrays
+  ctx->run = nullptr;
   cudaStream_t st = ctx->stream;
-  int chunk = P;
-  if (ctx->host_chunk > 0) chunk = ctx->host_chunk < P ? ctx->host_chunk : P;
-  else if (ctx->host_chunk == 0 && P >= 2 * kAutoHostChunk) chunk = kAutoHostChunk;
-  const int nchunks = (P + chunk - 1) / chunk;
+  int rc;
+  int chunk = Pn;
+  if (ctx->host_chunk > 0) chunk = ctx->host_chunk < Pn ? ctx->host_chunk : Pn;
+  else if (ctx->host_chunk == 0 && Pn >= 2 * kAutoHostChunk) chunk = kAutoHostChunk;
+  const int nchunks = (Pn + chunk - 1) / chunk;
   const bool piped = nchunks > 1;
   if (piped && !ctx->copy_stream) {
     SCB_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
@@ -402,11 +507,10 @@ int scb_plan_batch(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* ou
   SCB_CUDA(cudaEventRecord(ctx->ev[0], st));
   const void* dEdges = nullptr;
   for (int c = 0; c < nchunks; ++c) {
-    const int p0 = c * chunk, Pc = (P - p0 < chunk) ? P - p0 : chunk, b = c & 1;
+    const int p0 = base + c * chunk, Pc = (Pn - c * chunk < chunk) ? Pn - c * chunk : chunk, b = c & 1;
     if (c >= 2) SCB_CUDA(cudaStreamWaitEvent(st, ctx->ev_copied[b], 0));  // mirror set b is free again
-    scb_batch_in din = *in;
+    scb_batch_in din;
     scb_batch_out dout = *out;
-    din.P = Pc;
     // rows x [P] host array <-> rows x [Pc] device array (rows = 1 and a wider element for the [P][n] arrays)
     auto copy = [&](void* dst, const void* src, size_t rows, size_t elem, bool to_host, cudaStream_t s) -> cudaError_t {
       const size_t w = (size_t)Pc * elem, hp = (size_t)P * elem;
@@ -415,6 +519,7 @@ int scb_plan_batch(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* ou
       return to_host ? cudaMemcpy2DAsync(dst, hp, src, w, w, rows, k, s) : cudaMemcpy2DAsync(dst, w, src, hp, w, rows, k, s);
     };
     // ---- H2D of this chunk's inputs, on the compute stream (full speed when the caller's memory is pinned)
+    if ((rc = upload_inputs(ctx, in, stages, p0, Pc, st, c == 0, &dEdges, din))) return rc;
     auto up = [&](int id, const void* src, size_t rows, size_t elem, const void** dst) -> int {
       if (!src) { *dst = nullptr; return SCB_OK; }
       void* d;
@@ -425,33 +530,6 @@ int scb_plan_batch(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* ou
       *dst = d;
       return SCB_OK;
     };
-    if (do_spline) {
-      if ((rc = up(SL_IN_WX, in->wx, 1, W * rs, &din.wx))) return rc;
-      if ((rc = up(SL_IN_WY, in->wy, 1, W * rs, &din.wy))) return rc;
-      if ((rc = up(SL_IN_SA, in->start_angle, 1, rs, &din.start_angle))) return rc;
-      if (in->n_obstacle_edges > 0) {  // shared by every problem: uploaded once
-        if (c == 0) {
-          void* d;
-          if ((rc = ensure(ctx, SL_IN_EDGES, (size_t)in->n_obstacle_edges * 4 * rs, &d))) return rc;
-          SCB_CUDA(cudaMemcpyAsync(d, in->obstacle_edges, (size_t)in->n_obstacle_edges * 4 * rs, cudaMemcpyHostToDevice, st));
-          dEdges = d;
-        }
-        din.obstacle_edges = dEdges;
-      }
-    }
-    if (do_timing) {
-      if ((rc = up(SL_IN_VLO, in->vel_lo, 1, rs, &din.vel_lo))) return rc;
-      if ((rc = up(SL_IN_VHI, in->vel_hi, 1, rs, &din.vel_hi))) return rc;
-      if ((rc = up(SL_IN_VLG, in->vel_lo_grid, G, rs, &din.vel_lo_grid))) return rc;
-      if ((rc = up(SL_IN_VHG, in->vel_hi_grid, G, rs, &din.vel_hi_grid))) return rc;
-      if ((rc = up(SL_IN_ALO, in->acc_lo, 1, rs, &din.acc_lo))) return rc;
-      if ((rc = up(SL_IN_AHI, in->acc_hi, 1, rs, &din.acc_hi))) return rc;
-      if (!do_spline && (rc = up(SL_IN_PL, in->path_len, 1, rs, &din.path_len))) return rc;
-    }
-    // the end slopes of q(s) are read by the arc kernel (gridpoint geometry) as well as by the timing stage:
-    // mirrored whenever the caller passes them, whatever the stages
-    if ((rc = up(SL_IN_VS, in->vel_start, 1, rs, &din.vel_start))) return rc;
-    if ((rc = up(SL_IN_VE, in->vel_end, 1, rs, &din.vel_end))) return rc;
     // ---- device mirrors (set b) of the requested outputs
     struct Down { void* host; void* dev; size_t rows, elem; };
     Down downs[32];
@@ -478,19 +556,19 @@ int scb_plan_batch(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* ou
     } else { dout.ctrl_x = dout.ctrl_y = dout.arclen_total = dout.arclen_table = dout.cost = nullptr; }
     if (do_timing) {
       MIR(SL_O_T_TOTAL, T_total, 1, rs);
-      MIR(SL_O_K_LO, K_lo, G, rs); MIR(SL_O_K_HI, K_hi, G, rs); MIR(SL_O_X, x, G, rs); MIR(SL_O_T, t, G, rs);
-      MIR(SL_O_V, v, G, rs); MIR(SL_O_A, a, G, rs);
-      if (stages & SCB_STAGE_GEOMETRY) { MIR(SL_O_PX, px, G, rs); MIR(SL_O_PY, py, G, rs); MIR(SL_O_OMEGA, omega, G, rs); }
+      MIR(SL_O_K_LO, K_lo, G, rs); MIR(SL_O_K_HI, K_hi, G, rs); MIR(SL_O_X, x, G, rs); MIR(SL_O_T, t, G, rr);
+      MIR(SL_O_V, v, G, rr); MIR(SL_O_A, a, G, rr);
+      if (stages & SCB_STAGE_GEOMETRY) { MIR(SL_O_PX, px, G, rr); MIR(SL_O_PY, py, G, rr); MIR(SL_O_OMEGA, omega, G, rr); }
       else { dout.px = dout.py = dout.omega = nullptr; }
     } else { dout.T_total = dout.K_lo = dout.K_hi = dout.x = dout.t = dout.v = dout.a = dout.px = dout.py = dout.omega = nullptr; }
     if (S > 0) {
       MIR(SL_O_NS, n_samples, 1, 4);
-      MIR(SL_O_STIME, s_time, S, rs); MIR(SL_O_SPOS, s_pos, S, rs); MIR(SL_O_SVEL, s_vel, S, rs); MIR(SL_O_SACC, s_acc, S, rs);
-      MIR(SL_O_SPX, s_px, S, rs); MIR(SL_O_SPY, s_py, S, rs); MIR(SL_O_SOMEGA, s_omega, S, rs);
+      MIR(SL_O_STIME, s_time, S, rr); MIR(SL_O_SPOS, s_pos, S, rr); MIR(SL_O_SVEL, s_vel, S, rr); MIR(SL_O_SACC, s_acc, S, rr);
+      MIR(SL_O_SPX, s_px, S, rr); MIR(SL_O_SPY, s_py, S, rr); MIR(SL_O_SOMEGA, s_omega, S, rr);
       if (!do_timing) {  // positions (and velocities) to resample at are inputs
         SCB_CUDA(copy(dout.n_samples, (const char*)out->n_samples + (size_t)p0 * 4, 1, 4, false, st));
-        SCB_CUDA(copy(dout.s_pos, (const char*)out->s_pos + (size_t)p0 * rs, S, rs, false, st));
-        if (out->s_vel) SCB_CUDA(copy(dout.s_vel, (const char*)out->s_vel + (size_t)p0 * rs, S, rs, false, st));
+        SCB_CUDA(copy(dout.s_pos, (const char*)out->s_pos + (size_t)p0 * rr, S, rr, false, st));
+        if (out->s_vel) SCB_CUDA(copy(dout.s_vel, (const char*)out->s_vel + (size_t)p0 * rr, S, rr, false, st));
       }
     }
 #undef MIR
@@ -512,8 +590,302 @@ int scb_plan_batch(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* ou
   ctx->piped = piped;
   ctx->timing.launches *= nchunks;
   SCB_CUDA(cudaEventRecord(ctx->ev[6], st));
+  SCB_CUDA(cudaEventRecord(ctx->ev_last, st));
   SCB_CUDA(cudaStreamSynchronize(st));
   collect_timing(ctx);
+  release_retired(ctx);
+  return SCB_OK;
+}
+
+// ---- rank, then fetch -------------------------------------------------------------------------------------------
+struct GatherJob { const void* src; void* dst; int rows, per, words; };  // rows > 0: [rows][P] columns; else [P][per] rows
+struct GatherArgs { GatherJob job[20]; int njobs, P, n; const int32_t* ids; };
+
+// dst[i][j] = src[i][ids[j]]  (column gather of a [rows][P] array)  or  dst[j][:] = src[ids[j]][:]  (row gather of a
+// [P][per] array); elements are `words` 32-bit words.  blockIdx.y = job.
+__global__ void gather_kernel(GatherArgs a) {
+  const GatherJob jb = a.job[blockIdx.y];
+  const uint32_t* __restrict__ src = (const uint32_t*)jb.src;
+  uint32_t* __restrict__ dst = (uint32_t*)jb.dst;
+  const size_t w = (size_t)jb.words;
+  if (jb.rows > 0) {
+    const size_t total = (size_t)jb.rows * a.n * w;
+    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+      const size_t k = e % w, ij = e / w, j = ij % a.n, i = ij / a.n;
+      dst[e] = src[((size_t)i * a.P + a.ids[j]) * w + k];
+    }
+  } else {
+    const size_t row = (size_t)jb.per * w, total = row * a.n;
+    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+      const size_t j = e / row, k = e % row;
+      dst[e] = src[(size_t)a.ids[j] * row + k];
+    }
+  }
+}
+
+// Plan problems [base, base + Pn) of the caller's host inputs, keep every output in the ctx, copy the summaries back.
+int plan_summary_range(scb_ctx* ctx, const scb_batch_in* in, int rec32, int base, int Pn, scb_summary* summaries) {
+  SCB_CUDA(cudaSetDevice(ctx->cfg.device));
+  ctx->kept_P = 0;
+  if (Pn == 0) return SCB_OK;
+  const int W = in->W, G = in->G, deg = degree_of(ctx);
+  const size_t rs = real_size(ctx), rr = rec32 ? 4 : rs;
+  const int stages = SCB_STAGE_SPLINE | SCB_STAGE_TIMING | SCB_STAGE_GEOMETRY;
+  ctx->run = nullptr;
+  cudaStream_t st = ctx->stream;
+  int rc;
+  SCB_CUDA(cudaEventRecord(ctx->ev[0], st));
+  scb_batch_in din;
+  const void* dEdges = nullptr;
+  if ((rc = upload_inputs(ctx, in, stages, base, Pn, st, true, &dEdges, din))) return rc;
+  scb_batch_out k = {};
+  const size_t nc = (size_t)(W - 1) * (deg + 1), nt = (size_t)(W - 1) * kTable, gp = (size_t)G * Pn;
+#define KEEP(id, field, bytes) if ((rc = ensure(ctx, id, (bytes), (void**)&k.field))) return rc
+  KEEP(SL_R_STATUS, status, (size_t)Pn * 4); KEEP(SL_R_FAIL, fail_stage, (size_t)Pn * 4);
+  KEEP(SL_R_CTRL_X, ctrl_x, Pn * nc * rs); KEEP(SL_R_CTRL_Y, ctrl_y, Pn * nc * rs);
+  KEEP(SL_R_L, arclen_total, Pn * rs); KEEP(SL_R_TABLE, arclen_table, Pn * nt * rs);
+  KEEP(SL_R_T_TOTAL, T_total, Pn * rs); KEEP(SL_R_COST, cost, Pn * rs);
+  KEEP(SL_R_K_LO, K_lo, gp * rs); KEEP(SL_R_K_HI, K_hi, gp * rs); KEEP(SL_R_X, x, gp * rs);
+  KEEP(SL_R_T, t, gp * rr); KEEP(SL_R_PX, px, gp * rr); KEEP(SL_R_PY, py, gp * rr);
+  KEEP(SL_R_V, v, gp * rr); KEEP(SL_R_A, a, gp * rr); KEEP(SL_R_OMEGA, omega, gp * rr);
+#undef KEEP
+  k.record_f32 = rec32 ? 1 : 0;
+  ctx->host_call = true;
+  if ((rc = run_device_any(ctx, &din, &k, stages))) return rc;
+  scb_summary* dsum;
+  if ((rc = ensure(ctx, SL_R_SUMMARY, (size_t)Pn * sizeof(scb_summary), (void**)&dsum))) return rc;
+  if ((rc = scb_pack_summary_device(ctx, Pn, k.status, k.fail_stage, k.T_total, k.arclen_total, k.cost, dsum))) return rc;
+  SCB_CUDA(cudaMemcpyAsync(summaries, dsum, (size_t)Pn * sizeof(scb_summary), cudaMemcpyDeviceToHost, st));
+  ctx->piped = false;
+  ctx->timing.launches += 1;
+  SCB_CUDA(cudaEventRecord(ctx->ev[6], st));
+  SCB_CUDA(cudaEventRecord(ctx->ev_last, st));
+  SCB_CUDA(cudaStreamSynchronize(st));
+  collect_timing(ctx);
+  release_retired(ctx);
+  ctx->kept = k; ctx->kept_P = Pn; ctx->kept_W = W; ctx->kept_G = G; ctx->kept_rec32 = rec32 ? 1 : 0;
+  return SCB_OK;
+}
+
+// Gather problems ids[0..n) of the retained results into host arrays of leading dimension ld, columns [col0, col0 + n).
+int fetch_cols(scb_ctx* ctx, int n, const int32_t* ids, const scb_batch_out* out, int col0, int ld) {
+  if (n == 0) return SCB_OK;
+  SCB_CUDA(cudaSetDevice(ctx->cfg.device));
+  const int P = ctx->kept_P, W = ctx->kept_W, G = ctx->kept_G, deg = degree_of(ctx);
+  if (P <= 0) return SCB_E_INVALID;
+  for (int j = 0; j < n; ++j) if (ids[j] < 0 || ids[j] >= P) return SCB_E_INVALID;
+  const size_t rs = real_size(ctx), rr = ctx->kept_rec32 ? 4 : rs;
+  const size_t nc = (size_t)(W - 1) * (deg + 1), nt = (size_t)(W - 1) * kTable;
+  cudaStream_t st = ctx->stream;
+  int rc;
+  int32_t* dIds;
+  if ((rc = ensure(ctx, SL_F_IDS, (size_t)n * 4, (void**)&dIds))) return rc;
+  SCB_CUDA(cudaMemcpyAsync(dIds, ids, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+  const scb_batch_out& k = ctx->kept;
+  struct Item { void* host; const void* dev; int rows, per; size_t elem; };
+  const Item items[] = {
+      {out->status, k.status, 0, 1, 4}, {out->fail_stage, k.fail_stage, 0, 1, 4},
+      {out->ctrl_x, k.ctrl_x, 0, (int)nc, rs}, {out->ctrl_y, k.ctrl_y, 0, (int)nc, rs},
+      {out->arclen_total, k.arclen_total, 0, 1, rs}, {out->arclen_table, k.arclen_table, 0, (int)nt, rs},
+      {out->T_total, k.T_total, 0, 1, rs}, {out->cost, k.cost, 0, 1, rs},
+      {out->K_lo, k.K_lo, G, 1, rs}, {out->K_hi, k.K_hi, G, 1, rs}, {out->x, k.x, G, 1, rs},
+      {out->t, k.t, G, 1, rr}, {out->px, k.px, G, 1, rr}, {out->py, k.py, G, 1, rr},
+      {out->v, k.v, G, 1, rr}, {out->a, k.a, G, 1, rr}, {out->omega, k.omega, G, 1, rr}};
+  size_t total = 0;
+  for (const Item& it : items) if (it.host) total += ((size_t)(it.rows > 0 ? it.rows : it.per) * n * it.elem + 15) / 16 * 16;
+  char* stage;
+  if ((rc = ensure(ctx, SL_F_STAGE, total, (void**)&stage))) return rc;
+  GatherArgs ga{};
+  ga.P = P; ga.n = n; ga.ids = dIds;
+  size_t off = 0, offs[20];
+  size_t most = 0;
+  for (const Item& it : items) {
+    if (!it.host) continue;
+    const size_t bytes = (size_t)(it.rows > 0 ? it.rows : it.per) * n * it.elem;
+    offs[ga.njobs] = off;
+    ga.job[ga.njobs++] = {it.dev, stage + off, it.rows, it.per, (int)(it.elem / 4)};
+    off += (bytes + 15) / 16 * 16;
+    most = bytes / 4 > most ? bytes / 4 : most;
+  }
+  if (ga.njobs == 0) return SCB_OK;
+  SCB_CUDA(cudaEventRecord(ctx->ev[0], st));
+  const int gx = (int)((most + 255) / 256 < 296 ? (most + 255) / 256 : 296);
+  gather_kernel<<<dim3(gx ? gx : 1, ga.njobs), 256, 0, st>>>(ga);
+  SCB_CUDA(cudaGetLastError());
+  int j = 0;
+  for (const Item& it : items) {
+    if (!it.host) continue;
+    const char* src = stage + offs[j++];
+    if (it.rows > 0) {  // [rows][n] -> columns [col0, col0 + n) of [rows][ld]
+      const size_t w = (size_t)n * it.elem;
+      if (ld == n) SCB_CUDA(cudaMemcpyAsync(it.host, src, w * it.rows, cudaMemcpyDeviceToHost, st));
+      else SCB_CUDA(cudaMemcpy2DAsync((char*)it.host + (size_t)col0 * it.elem, (size_t)ld * it.elem, src, w, w, it.rows, cudaMemcpyDeviceToHost, st));
+    } else {
+      const size_t row = (size_t)it.per * it.elem;
+      SCB_CUDA(cudaMemcpyAsync((char*)it.host + (size_t)col0 * row, src, row * n, cudaMemcpyDeviceToHost, st));
+    }
+  }
+  SCB_CUDA(cudaEventRecord(ctx->ev[6], st));
+  SCB_CUDA(cudaStreamSynchronize(st));
+  scb_timing& t = ctx->timing;
+  float ms = 0;
+  cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[6]);
+  t.d2h_ms = ms;  // the plan's stage times stay; d2h_ms = this fetch
+  return SCB_OK;
+}
+
+int validate_summary(scb_ctx* ctx, const scb_batch_in* in) {
+  if (!ctx || !in) return SCB_E_INVALID;
+  int32_t dummy = 0;
+  scb_batch_out o{};
+  o.status = &dummy;
+  int stages;
+  if (in->stages != 0 && in->stages != (SCB_STAGE_SPLINE | SCB_STAGE_TIMING | SCB_STAGE_GEOMETRY)) return SCB_E_INVALID;
+  return validate(ctx, in, &o, stages);
+}
+
+}  // namespace
+
+struct scb_multi {
+  std::vector<scb_ctx*> ctx;
+  int kept_P = 0;  // problems of the last scb_multi_plan_summary
+};
+
+namespace {
+// one host thread per device, as one scb_ctx per host thread is the ABI's rule
+template <class F> int on_every_device(scb_multi* m, F&& body) {
+  const int R = (int)m->ctx.size();
+  std::vector<int> rcs((size_t)R, SCB_OK);
+  std::vector<std::thread> th;
+  for (int r = 1; r < R; ++r) th.emplace_back([&, r] { rcs[(size_t)r] = body(r); });
+  rcs[0] = body(0);
+  for (auto& t : th) t.join();
+  for (int rc : rcs) if (rc) return rc;
+  return SCB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int scb_plan_batch(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out) {
+  int stages;
+  int rc = validate(ctx, in, out, stages);
+  if (rc) return rc;
+  return plan_host_range(ctx, in, out, stages, 0, in->P);
+}
+
+int scb_plan_batch_summary(scb_ctx* ctx, const scb_batch_in* in, int32_t record_f32, scb_summary* summaries) {
+  int rc = validate_summary(ctx, in);
+  if (rc) return rc;
+  if (!summaries) return SCB_E_INVALID;
+  return plan_summary_range(ctx, in, record_f32, 0, in->P, summaries);
+}
+
+int scb_fetch(scb_ctx* ctx, int32_t n, const int32_t* problem_ids, const scb_batch_out* out) {
+  if (!ctx || n < 0 || (n > 0 && !problem_ids) || !out) return SCB_E_INVALID;
+  return fetch_cols(ctx, n, problem_ids, out, 0, n);
+}
+
+void scb_shard_range(int32_t P, int32_t r, int32_t R, int32_t* lo, int32_t* hi) {
+  const int64_t per = R > 0 ? ((int64_t)P + R - 1) / R : P;
+  int64_t a = (int64_t)r * per, b;
+  if (a > P) a = P;
+  b = a + per;
+  if (b > P) b = P;
+  if (lo) *lo = (int32_t)a;
+  if (hi) *hi = (int32_t)b;
+}
+
+int scb_multi_create(scb_multi** out, const scb_config* cfg, int32_t n_devices, const int32_t* devices) {
+  if (!out || !cfg || n_devices < 1) return SCB_E_INVALID;
+  *out = nullptr;
+  scb_multi* m = new (std::nothrow) scb_multi();
+  if (!m) return SCB_E_NOMEM;
+  for (int r = 0; r < n_devices; ++r) {
+    scb_config c = *cfg;
+    c.device = devices ? devices[r] : r;
+    scb_ctx* x = nullptr;
+    const int rc = scb_create(&x, &c);
+    if (rc) { scb_multi_destroy(m); return rc; }
+    m->ctx.push_back(x);
+  }
+  *out = m;
+  return SCB_OK;
+}
+
+int scb_multi_destroy(scb_multi* m) {
+  if (!m) return SCB_E_INVALID;
+  for (scb_ctx* x : m->ctx) scb_destroy(x);
+  delete m;
+  return SCB_OK;
+}
+
+int32_t scb_multi_devices(const scb_multi* m) { return m ? (int32_t)m->ctx.size() : 0; }
+
+int scb_multi_get_timing(scb_multi* m, int32_t r, scb_timing* out) {
+  if (!m || r < 0 || r >= (int32_t)m->ctx.size()) return SCB_E_INVALID;
+  return scb_get_timing(m->ctx[(size_t)r], out);
+}
+
+int scb_multi_plan_batch(scb_multi* m, const scb_batch_in* in, const scb_batch_out* out) {
+  if (!m || m->ctx.empty() || !in || !out) return SCB_E_INVALID;
+  const int R = (int)m->ctx.size();
+  int stages = 0;
+  for (int r = 0; r < R; ++r) {  // every block must fit its device's capacity
+    int32_t lo, hi;
+    scb_shard_range(in->P, r, R, &lo, &hi);
+    scb_batch_in probe = *in;
+    probe.P = hi - lo;
+    const int rc = validate(m->ctx[(size_t)r], &probe, out, stages);
+    if (rc) return rc;
+  }
+  return on_every_device(m, [&](int r) {
+    int32_t lo, hi;
+    scb_shard_range(in->P, r, R, &lo, &hi);
+    return plan_host_range(m->ctx[(size_t)r], in, out, stages, lo, hi - lo);
+  });
+}
+
+int scb_multi_plan_summary(scb_multi* m, const scb_batch_in* in, int32_t record_f32, scb_summary* summaries) {
+  if (!m || m->ctx.empty() || !in || !summaries) return SCB_E_INVALID;
+  const int R = (int)m->ctx.size();
+  m->kept_P = 0;
+  for (int r = 0; r < R; ++r) {
+    int32_t lo, hi;
+    scb_shard_range(in->P, r, R, &lo, &hi);
+    scb_batch_in probe = *in;
+    probe.P = hi - lo;
+    const int rc = validate_summary(m->ctx[(size_t)r], &probe);
+    if (rc) return rc;
+  }
+  const int rc = on_every_device(m, [&](int r) {
+    int32_t lo, hi;
+    scb_shard_range(in->P, r, R, &lo, &hi);
+    return plan_summary_range(m->ctx[(size_t)r], in, record_f32, lo, hi - lo, summaries + lo);
+  });
+  if (rc == SCB_OK) m->kept_P = in->P;
+  return rc;
+}
+
+int scb_multi_fetch(scb_multi* m, int32_t n, const int32_t* problem_ids, const scb_batch_out* out) {
+  if (!m || m->ctx.empty() || n < 0 || (n > 0 && !problem_ids) || !out || m->kept_P <= 0) return SCB_E_INVALID;
+  const int R = (int)m->ctx.size(), P = m->kept_P;
+  // ids of one device are fetched into consecutive columns: the caller's order is restored by asking for them in
+  // runs; an MPC loop asks for a handful of ids, so every run of consecutive same-owner ids is one small fetch
+  for (int j = 0; j < n; ++j) if (problem_ids[j] < 0 || problem_ids[j] >= P) return SCB_E_INVALID;
+  int j0 = 0;
+  while (j0 < n) {
+    int32_t lo = 0, hi = 0;
+    int owner = 0;
+    for (owner = 0; owner < R; ++owner) { scb_shard_range(P, owner, R, &lo, &hi); if (problem_ids[j0] < hi) break; }
+    int j1 = j0;
+    std::vector<int32_t> local;
+    while (j1 < n && problem_ids[j1] >= lo && problem_ids[j1] < hi) local.push_back(problem_ids[j1++] - lo);
+    const int rc = fetch_cols(m->ctx[(size_t)owner], j1 - j0, local.data(), out, j0, n);
+    if (rc) return rc;
+    j0 = j1;
+  }
   return SCB_OK;
 }
 
@@ -598,6 +970,13 @@ int scb_fmt_batch(scb_ctx* ctx, const scb_fmt_in* in, const scb_fmt_out* out) {
   ctx->timing_pending = false;
   return SCB_OK;
 }
+
+void* scb_alloc_pinned(size_t bytes) {
+  void* p = nullptr;
+  if (cudaMallocHost(&p, bytes ? bytes : 1) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+  return p;
+}
+void scb_free_pinned(void* p) { if (p) cudaFreeHost(p); }
 
 int scb_get_timing(scb_ctx* ctx, scb_timing* out) {
   if (!ctx || !out) return SCB_E_INVALID;

@@ -101,6 +101,7 @@ struct PathArgs {
   void *table;                        // [P][(W-1)*101]; may be null only when the table fits in shared memory
   void *L, *cost;                     // [P]
   void *px, *py, *kappa;              // [G][P] or null: curve point / curvature at arc length q(s_i)
+  float *px32, *py32;                 // [G][P] or null: the same curve points as float records (scb_batch_out.record_f32)
   int32_t* status;                    // [P]  written: SCB_ST_OK or SCB_ST_ERR_BAD_PATH
   int table_in_smem;
   scb_opt opt;
@@ -127,7 +128,8 @@ struct ParamArgs {
   const void *L, *vel_start, *vel_end; // [P]
   const void *x;                       // [G][P]
   const void *kappa;                   // [G][P] or null
-  void *t, *v, *a, *omega;             // [G][P] outputs (any may be null)
+  void *t, *v, *a, *omega;             // [G][P] outputs (any may be null); float when rec_f32
+  int rec_f32;                         // scb_batch_out.record_f32: the record arrays above are float whatever S
   void *t_buf, *X_buf, *cp_buf;        // [G][P] scratch: knot times, spline unknowns, Thomas c'
   void *T_total;                       // [P]
   int32_t* status;
@@ -144,7 +146,8 @@ struct SampleArgs {
   int param_mode;                      // SCB_PARAM_*
   const void *ctrl_x, *ctrl_y, *table;
   int32_t* n_samples;                  // [P]
-  void *s_time, *s_pos, *s_vel, *s_acc, *s_px, *s_py, *s_omega;  // [S_cap][P]
+  void *s_time, *s_pos, *s_vel, *s_acc, *s_px, *s_py, *s_omega;  // [S_cap][P]; float when rec_f32
+  int rec_f32;
   const int32_t* status;
   int timing, geometry;                // timing off: s_pos / s_vel / n_samples are inputs
   int nudge;                           // geometry-only: repair s_pos in place first (sc:902-912)

@@ -52,7 +52,7 @@ class ScbBatchOut(C.Structure):
                 ("K_lo", C.c_void_p), ("K_hi", C.c_void_p), ("x", C.c_void_p), ("t", C.c_void_p),
                 ("px", C.c_void_p), ("py", C.c_void_p), ("v", C.c_void_p), ("a", C.c_void_p),
                 ("omega", C.c_void_p),
-                ("S_cap", C.c_int32), ("n_samples", C.c_void_p),
+                ("S_cap", C.c_int32), ("record_f32", C.c_int32), ("n_samples", C.c_void_p),
                 ("s_time", C.c_void_p), ("s_pos", C.c_void_p), ("s_vel", C.c_void_p), ("s_acc", C.c_void_p),
                 ("s_px", C.c_void_p), ("s_py", C.c_void_p), ("s_omega", C.c_void_p)]
 
@@ -91,9 +91,22 @@ SYMBOLS = {
     "scb_destroy": (C.c_int, [C.c_void_p]),
     "scb_plan_batch": (C.c_int, [C.c_void_p, C.POINTER(ScbBatchIn), C.POINTER(ScbBatchOut)]),
     "scb_plan_batch_device": (C.c_int, [C.c_void_p, C.POINTER(ScbBatchIn), C.POINTER(ScbBatchOut), C.c_int]),
+    "scb_plan_batch_async": (C.c_int, [C.c_void_p, C.POINTER(ScbBatchIn), C.POINTER(ScbBatchOut), C.c_void_p]),
     "scb_synchronize": (C.c_int, [C.c_void_p]),
+    "scb_plan_batch_summary": (C.c_int, [C.c_void_p, C.POINTER(ScbBatchIn), C.c_int32, C.c_void_p]),
+    "scb_fetch": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.POINTER(ScbBatchOut)]),
+    "scb_multi_create": (C.c_int, [C.POINTER(C.c_void_p), C.POINTER(ScbConfig), C.c_int32, C.c_void_p]),
+    "scb_multi_destroy": (C.c_int, [C.c_void_p]),
+    "scb_multi_devices": (C.c_int32, [C.c_void_p]),
+    "scb_multi_plan_batch": (C.c_int, [C.c_void_p, C.POINTER(ScbBatchIn), C.POINTER(ScbBatchOut)]),
+    "scb_multi_plan_summary": (C.c_int, [C.c_void_p, C.POINTER(ScbBatchIn), C.c_int32, C.c_void_p]),
+    "scb_multi_fetch": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.POINTER(ScbBatchOut)]),
+    "scb_shard_range": (None, [C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
+    "scb_multi_get_timing": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(ScbTiming)]),
     "scb_set_host_chunk": (C.c_int, [C.c_void_p, C.c_int32]),
     "scb_fmt_batch": (C.c_int, [C.c_void_p, C.POINTER(ScbFmtIn), C.POINTER(ScbFmtOut)]),
+    "scb_alloc_pinned": (C.c_void_p, [C.c_size_t]),
+    "scb_free_pinned": (None, [C.c_void_p]),
     "scb_get_timing": (C.c_int, [C.c_void_p, C.POINTER(ScbTiming)]),
     "scb_last_cuda_error": (C.c_char_p, [C.c_void_p]),
     "scb_stream": (C.c_void_p, [C.c_void_p]),

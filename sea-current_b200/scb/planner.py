@@ -21,6 +21,9 @@ ALL_OUTPUTS = ("ctrl_x", "ctrl_y", "arclen_table") + PER_PROBLEM + PER_GRID
 # what the reference's E1 call sequence hands back to its caller (gen_vel_prof + resample +
 # angular_velocity, examples/json_test.cpp:28-58), one record per toppra gridpoint
 TRAJECTORY_OUTPUTS = ("arclen_total", "T_total", "t", "px", "py", "v", "a", "omega")
+# the arrays scb_batch_out.record_f32 turns into float32 whatever the ctx precision (the reference's velocity_profile,
+# resample and angular_velocity hand their caller float32: sea_current.hpp:379-386, 1245-1262)
+RECORD = ("t", "px", "py", "v", "a", "omega") + PER_SAMPLE
 
 
 class ScbError(RuntimeError):
@@ -126,9 +129,11 @@ class BatchPlanner:
     def plan(self, wx=None, wy=None, vel_lo=None, vel_hi=None, acc_lo=None, acc_hi=None, G=101, start_angle=None,
              vel_lo_grid=None, vel_hi_grid=None, vel_start=None, vel_end=None, path_len=None, stages=0,
              outputs=ALL_OUTPUTS, S_cap=0, x_cap=0.0, dt=0.0, opt=None, out_buffers=None, resample_at=None, lp_mode=0,
-             nudge=False, omega_max=0.0, acc_lat_max=0.0, obstacle_edges=None, param_mode=0, a_brake=0.0, t_react=0.0, collision_chords=0):
+             nudge=False, omega_max=0.0, acc_lat_max=0.0, obstacle_edges=None, param_mode=0, a_brake=0.0, t_react=0.0, collision_chords=0,
+             spline=None, record_f32=False):
         """Host arrays in, host arrays out (scb_plan_batch).  `out_buffers` lets a caller pass
-        preallocated (e.g. pinned) numpy arrays keyed by output name."""
+        preallocated (e.g. pinned) numpy arrays keyed by output name.  `spline` = dict(ctrl_x, ctrl_y, arclen_table) of an
+        earlier SCB_STAGE_SPLINE call: inputs of a SCB_STAGE_GEOMETRY-only call (no waypoints then)."""
         R = self.real
         keep = []
 
@@ -144,6 +149,9 @@ class BatchPlanner:
         if wx is not None:
             wx = np.ascontiguousarray(wx, dtype=R)
             P, W = wx.shape
+        elif spline is not None:
+            P = spline["ctrl_x"].shape[0]
+            W = spline["ctrl_x"].shape[1] // (self.degree + 1) + 1
         else:
             P, W = len(np.atleast_1d(path_len)), 2
         bi = abi.ScbBatchIn()
@@ -181,14 +189,16 @@ class BatchPlanner:
         bo.status = outbuf("status", (P,), np.int32)
         bo.fail_stage = outbuf("fail_stage", (P,), np.int32)
         bo.S_cap = S_cap
+        bo.record_f32 = 1 if record_f32 else 0
+        rec = np.float32 if record_f32 else R
         names = list(outputs)
         if S_cap > 0:
             names += [n for n in PER_SAMPLE if n not in names]
             bo.n_samples = outbuf("n_samples", (P,), np.int32)
             if resample_at is not None:  # geometry only: positions (and velocities) are inputs
                 pos, vel, ns = resample_at
-                res["s_pos"] = np.ascontiguousarray(pos, dtype=R)
-                res["s_vel"] = np.ascontiguousarray(vel, dtype=R) if vel is not None else None
+                res["s_pos"] = np.ascontiguousarray(pos, dtype=rec)
+                res["s_vel"] = np.ascontiguousarray(vel, dtype=rec) if vel is not None else None
                 res["n_samples"][:] = ns
                 ob = dict(ob, s_pos=res["s_pos"])
                 if res["s_vel"] is not None:
@@ -197,14 +207,81 @@ class BatchPlanner:
                     names.remove("s_vel")
                     del res["s_vel"]
         for n in names:
-            setattr(bo, n, outbuf(n, self.out_shape(n, P, W, G, S_cap), R))
+            setattr(bo, n, outbuf(n, self.out_shape(n, P, W, G, S_cap), rec if n in RECORD else R))
+        if spline is not None:
+            for n in ("ctrl_x", "ctrl_y", "arclen_table"):
+                setattr(bo, n, arr(spline[n], self.out_shape(n, P, W, G, S_cap)))
         self._check(self.lib.scb_plan_batch(self.ctx, C.byref(bi), C.byref(bo)), "scb_plan_batch")
+        return res
+
+    # ------------------------------------------------------------------ rank, then fetch
+    def _batch_in(self, keep, wx, wy, vel_lo, vel_hi, acc_lo, acc_hi, G, opt=None, **kw):
+        R = self.real
+
+        def arr(a, shape):
+            if a is None:
+                return None
+            a = np.ascontiguousarray(a, dtype=R)
+            if a.shape != shape:
+                a = np.ascontiguousarray(np.broadcast_to(a, shape))
+            keep.append(a)
+            return a.ctypes.data
+        wx = np.ascontiguousarray(wx, dtype=R)
+        P, W = wx.shape
+        bi = abi.ScbBatchIn()
+        bi.P, bi.W, bi.G = P, W, G
+        bi.wx, bi.wy = arr(wx, (P, W)), arr(wy, (P, W))
+        bi.vel_lo, bi.vel_hi, bi.acc_lo, bi.acc_hi = arr(vel_lo, (P,)), arr(vel_hi, (P,)), arr(acc_lo, (P,)), arr(acc_hi, (P,))
+        for n in ("start_angle", "vel_start", "vel_end"):
+            setattr(bi, n, arr(kw.pop(n, None), (P,)))
+        for n in ("vel_lo_grid", "vel_hi_grid"):
+            setattr(bi, n, arr(kw.pop(n, None), (G, P)))
+        ed = kw.pop("obstacle_edges", None)
+        if ed is not None and len(ed):
+            ed = np.ascontiguousarray(ed, dtype=R).reshape(-1, 4)
+            keep.append(ed)
+            bi.obstacle_edges, bi.n_obstacle_edges = ed.ctypes.data, ed.shape[0]
+        for n, v in kw.items():  # scalars: x_cap, dt, lp_mode, omega_max, acc_lat_max, a_brake, t_react, collision_chords, param_mode
+            setattr(bi, n, v)
+        bi.opt = opt if opt is not None else default_opt()
+        return bi, P, W
+
+    def plan_summary(self, wx, wy, vel_lo, vel_hi, acc_lo, acc_hi, G=101, record_f32=True, opt=None, summaries=None, **kw):
+        """scb_plan_batch_summary: host inputs in, the batch stays in HBM, only the 32-byte summaries come back
+        (numpy structured array SUMMARY_DTYPE [P]; `summaries` = a preallocated, e.g. pinned, one)."""
+        keep = []
+        bi, P, W = self._batch_in(keep, wx, wy, vel_lo, vel_hi, acc_lo, acc_hi, G, opt, **kw)
+        out = summaries if summaries is not None else np.empty(P, dtype=SUMMARY_DTYPE)
+        assert out.shape == (P,) and out.dtype == SUMMARY_DTYPE and out.flags.c_contiguous
+        self._check(self.lib.scb_plan_batch_summary(self.ctx, C.byref(bi), 1 if record_f32 else 0, out.ctypes.data),
+                    "scb_plan_batch_summary")
+        self._kept = (P, W, G, bool(record_f32))
+        return out
+
+    def fetch(self, ids, outputs=TRAJECTORY_OUTPUTS, out_buffers=None):
+        """scb_fetch: the records of problems `ids` of the last plan_summary, as arrays laid out like plan()'s with P := len(ids)."""
+        P, W, G, rec32 = self._kept
+        ids = np.ascontiguousarray(ids, dtype=np.int32)
+        n = len(ids)
+        res = BatchResult()
+        bo = abi.ScbBatchOut()
+        ob = out_buffers or {}
+        for name in ("status", "fail_stage") + tuple(outputs):
+            dt = np.int32 if name in ("status", "fail_stage") else (np.float32 if rec32 and name in RECORD else self.real)
+            shape = (n,) if name in ("status", "fail_stage") else self.out_shape(name, n, W, G, 0)
+            a = ob.get(name)
+            if a is None:
+                a = np.empty(shape, dtype=dt)
+            assert a.shape == tuple(shape) and a.dtype == dt and a.flags.c_contiguous, name
+            res[name] = a
+            setattr(bo, name, a.ctypes.data)
+        self._check(self.lib.scb_fetch(self.ctx, n, ids.ctypes.data, C.byref(bo)), "scb_fetch")
         return res
 
     # ------------------------------------------------------------------ HBM-resident buffers
     def make_device_batch(self, inputs, G, outputs=ALL_OUTPUTS, S_cap=0, stages=0, x_cap=0.0, dt=0.0, opt=None, lp_mode=0,
                           omega_max=0.0, acc_lat_max=0.0, param_mode=0, obstacle_edges=None, a_brake=0.0, t_react=0.0,
-                          collision_chords=0):
+                          collision_chords=0, record_f32=False):
         """inputs: dict name -> torch CUDA tensor (dtype = ctx precision, contiguous).  Allocates
         the output tensors once and returns (batch_in, batch_out, result_tensors): the structs can be
         passed to run_device() any number of times without further allocation."""
@@ -236,13 +313,14 @@ class BatchPlanner:
                "fail_stage": torch.empty(P, dtype=torch.int32, device=dev)}
         bo = abi.ScbBatchOut()
         bo.status, bo.fail_stage, bo.S_cap = res["status"].data_ptr(), res["fail_stage"].data_ptr(), S_cap
+        bo.record_f32 = 1 if record_f32 else 0
         names = list(outputs)
         if S_cap > 0:
             names += [n for n in PER_SAMPLE if n not in names]
             res["n_samples"] = torch.empty(P, dtype=torch.int32, device=dev)
             bo.n_samples = res["n_samples"].data_ptr()
         for n in names:
-            res[n] = torch.empty(self.out_shape(n, P, W, G, S_cap), dtype=tdt, device=dev)
+            res[n] = torch.empty(self.out_shape(n, P, W, G, S_cap), dtype=torch.float32 if record_f32 and n in RECORD else tdt, device=dev)
             setattr(bo, n, res[n].data_ptr())
         return bi, bo, res
 
@@ -250,10 +328,19 @@ class BatchPlanner:
         self._check(self.lib.scb_plan_batch_device(self.ctx, C.byref(bi), C.byref(bo), 0 if sync else 1),
                     "scb_plan_batch_device")
 
+    def run_async(self, bi, bo, stream):
+        """scb_plan_batch_async: enqueue on the caller's stream (a torch.cuda.Stream or a raw cudaStream_t), never synchronise."""
+        raw = getattr(stream, "cuda_stream", stream)
+        self._check(self.lib.scb_plan_batch_async(self.ctx, C.byref(bi), C.byref(bo), C.c_void_p(raw)), "scb_plan_batch_async")
+
     def pack_summary(self, P, res):
-        """Device-side pack of the 32-byte per-problem summary records (what the multi-GPU path gathers)."""
+        """Device-side pack of the 32-byte per-problem summary records (what the multi-GPU path gathers).  The record
+        buffer belongs to the result set (allocated once, inside torch's allocator but never returned to it while the
+        batch lives), so the kernel that fills it on the ctx stream never races a reuse of the block by torch."""
         import torch
-        dst = torch.empty(P * C.sizeof(abi.ScbSummary), dtype=torch.uint8, device=res["status"].device)
+        dst = res.get("_summary")
+        if dst is None or dst.numel() != P * C.sizeof(abi.ScbSummary):
+            dst = res["_summary"] = torch.empty(P * C.sizeof(abi.ScbSummary), dtype=torch.uint8, device=res["status"].device)
         ptr = lambda n: res[n].data_ptr() if n in res else None
         self._check(self.lib.scb_pack_summary_device(self.ctx, P, ptr("status"), ptr("fail_stage"), ptr("T_total"),
                                                      ptr("arclen_total"), ptr("cost"), dst.data_ptr()),
@@ -266,10 +353,94 @@ SUMMARY_DTYPE = np.dtype([("status", np.int32), ("fail_stage", np.int32), ("T_to
 
 
 def shard_range(P, rank, world):
-    """Contiguous block of problems owned by `rank`: [lo, hi)."""
+    """Contiguous block of problems owned by `rank`: [lo, hi).  Same rule as scb_shard_range."""
     per = (P + world - 1) // world
     lo = min(P, rank * per)
     return lo, min(P, lo + per)
+
+
+class MultiPlanner:
+    """scb_multi_*: one process, one scb_ctx + host thread per GPU, contiguous blocks of problems per device."""
+
+    def __init__(self, n_devices, precision="fp64", spline_mode="lau_quintic", max_problems=65536, max_waypoints=32,
+                 max_gridpoints=1001, devices=None):
+        self.lib = abi.load_library()
+        self.precision = {"fp64": abi.SCB_FP64, "fp32": abi.SCB_FP32}[precision]
+        self.spline_mode = {"ref_cubic": abi.SCB_REF_CUBIC, "lau_quintic": abi.SCB_LAU_QUINTIC}[spline_mode]
+        self.real = np.float64 if self.precision == abi.SCB_FP64 else np.float32
+        self.degree = 3 if self.spline_mode == abi.SCB_REF_CUBIC else 5
+        cfg = abi.ScbConfig(0, self.precision, self.spline_mode, max_problems, max_waypoints, max_gridpoints, 0)
+        dv = None
+        if devices is not None:
+            dv = np.ascontiguousarray(devices, dtype=np.int32)
+            n_devices = len(dv)
+        h = C.c_void_p()
+        rc = self.lib.scb_multi_create(C.byref(h), C.byref(cfg), n_devices, None if dv is None else dv.ctypes.data)
+        if rc != 0:
+            raise ScbError("scb_multi_create: %s" % self.lib.scb_strerror(rc).decode())
+        self.m = h
+        self.n_devices = n_devices
+
+    def close(self):
+        if getattr(self, "m", None):
+            self.lib.scb_multi_destroy(self.m)
+            self.m = None
+
+    __del__ = close
+    out_shape = BatchPlanner.out_shape
+    _batch_in = BatchPlanner._batch_in
+
+    def _check(self, rc, what):
+        if rc != 0:
+            raise ScbError("%s: %s" % (what, self.lib.scb_strerror(rc).decode()))
+
+    def timing(self, r):
+        t = abi.ScbTiming()
+        self.lib.scb_multi_get_timing(self.m, r, C.byref(t))
+        return {k: getattr(t, k) for k, _ in abi.ScbTiming._fields_}
+
+    def plan(self, wx, wy, vel_lo, vel_hi, acc_lo, acc_hi, G=101, outputs=TRAJECTORY_OUTPUTS, record_f32=False, opt=None,
+             out_buffers=None, **kw):
+        keep = []
+        bi, P, W = self._batch_in(keep, wx, wy, vel_lo, vel_hi, acc_lo, acc_hi, G, opt, **kw)
+        res = BatchResult()
+        bo = abi.ScbBatchOut()
+        bo.record_f32 = 1 if record_f32 else 0
+        ob = out_buffers or {}
+        for name in ("status", "fail_stage") + tuple(outputs):
+            dt = np.int32 if name in ("status", "fail_stage") else (np.float32 if record_f32 and name in RECORD else self.real)
+            shape = (P,) if name in ("status", "fail_stage") else self.out_shape(name, P, W, G, 0)
+            a = ob.get(name)
+            if a is None:
+                a = np.empty(shape, dtype=dt)
+            assert a.shape == tuple(shape) and a.dtype == dt and a.flags.c_contiguous, name
+            res[name] = a
+            setattr(bo, name, a.ctypes.data)
+        self._check(self.lib.scb_multi_plan_batch(self.m, C.byref(bi), C.byref(bo)), "scb_multi_plan_batch")
+        return res
+
+    def plan_summary(self, wx, wy, vel_lo, vel_hi, acc_lo, acc_hi, G=101, record_f32=True, opt=None, summaries=None, **kw):
+        keep = []
+        bi, P, W = self._batch_in(keep, wx, wy, vel_lo, vel_hi, acc_lo, acc_hi, G, opt, **kw)
+        out = summaries if summaries is not None else np.empty(P, dtype=SUMMARY_DTYPE)
+        self._check(self.lib.scb_multi_plan_summary(self.m, C.byref(bi), 1 if record_f32 else 0, out.ctypes.data),
+                    "scb_multi_plan_summary")
+        self._kept = (P, W, G, bool(record_f32))
+        return out
+
+    def fetch(self, ids, outputs=TRAJECTORY_OUTPUTS):
+        P, W, G, rec32 = self._kept
+        ids = np.ascontiguousarray(ids, dtype=np.int32)
+        n = len(ids)
+        res = BatchResult()
+        bo = abi.ScbBatchOut()
+        for name in ("status", "fail_stage") + tuple(outputs):
+            dt = np.int32 if name in ("status", "fail_stage") else (np.float32 if rec32 and name in RECORD else self.real)
+            shape = (n,) if name in ("status", "fail_stage") else self.out_shape(name, n, W, G, 0)
+            res[name] = np.empty(shape, dtype=dt)
+            setattr(bo, name, res[name].ctypes.data)
+        self._check(self.lib.scb_multi_fetch(self.m, n, ids.ctypes.data, C.byref(bo)), "scb_multi_fetch")
+        return res
 
 
 def gather_summaries(local_bytes, world, group=None):

@@ -26,20 +26,21 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(lib, n), n
     assert sorted(abi.SYMBOLS) == names
-    assert lib.scb_version() == 100
+    assert lib.scb_version() == 200
 
 
 def test_struct_layouts_match_header(tmp_path):
     src = tmp_path / "sz.c"
     src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "seacurrent_b200.h"\nint main(){printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu\\n",'
                    "sizeof(scb_config),sizeof(scb_opt),sizeof(scb_batch_in),sizeof(scb_batch_out),sizeof(scb_timing),"
-                   "sizeof(scb_summary),offsetof(scb_batch_in,opt),offsetof(scb_batch_out,S_cap),offsetof(scb_batch_in,x_cap));return 0;}\n")
+                   "sizeof(scb_summary),offsetof(scb_batch_in,opt),offsetof(scb_batch_out,S_cap),offsetof(scb_batch_in,x_cap));\n"
+                   'printf("%zu %zu\\n",offsetof(scb_batch_out,record_f32),offsetof(scb_batch_out,n_samples));return 0;}\n')
     exe = tmp_path / "sz"
     subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)])
     got = [int(x) for x in subprocess.check_output([str(exe)]).split()]
     want = [C.sizeof(abi.ScbConfig), C.sizeof(abi.ScbOpt), C.sizeof(abi.ScbBatchIn), C.sizeof(abi.ScbBatchOut),
             C.sizeof(abi.ScbTiming), C.sizeof(abi.ScbSummary), abi.ScbBatchIn.opt.offset, abi.ScbBatchOut.S_cap.offset,
-            abi.ScbBatchIn.x_cap.offset]
+            abi.ScbBatchIn.x_cap.offset, abi.ScbBatchOut.record_f32.offset, abi.ScbBatchOut.n_samples.offset]
     assert got == want
 
 

@@ -213,3 +213,20 @@ def test_batched_text_request_equals_single_requests(built, tmp_path):
             assert batch[k]["status"] == status
         else:
             assert str(batch[k]["status"]) in single and batch[k]["error"] == single
+
+
+@pytest.mark.gpu
+def test_cpp_multi_gpu_program(tmp_path):
+    """tests/cpp/multi_gpu_c4.cpp: BASELINE config 4's shape planned from C++ through b200::multi_gpu_planner on every GPU
+    of the box (summaries of all problems, then the records of the 16 fastest), no CUDA toolkit on the caller's side."""
+    import torch
+    exe = _build(tmp_path, "multi_gpu_c4.cpp")
+    n = torch.cuda.device_count()
+    doc = json.loads(subprocess.check_output([exe, str(n), "30000", "2"]).decode())
+    assert doc["devices"] == n and doc["P"] == 30000 and doc["fetched_consistent"] is True
+    assert 100 < doc["failed"] < 600          # ~1 % of the problems cannot brake
+    assert doc["trajectories_per_s"] > 1e5
+    if n == 1:  # the same batch cut into three blocks on one device: same verdict counts, same winner
+        exe3 = exe  # blocks are a property of the call, not of the binary
+        doc3 = json.loads(subprocess.check_output([exe3, "1", "30000", "1"]).decode())
+        assert doc3["failed"] == doc["failed"] and doc3["best_T"] == doc["best_T"]

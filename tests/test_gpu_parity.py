@@ -534,8 +534,8 @@ def test_geometry_of_an_existing_spline(planners, mode):
     merged = pl.plan(wx=wx, wy=wy, stages=scb.abi.STAGE_SPLINE | scb.abi.STAGE_GEOMETRY, outputs=outs, S_cap=S,
                      resample_at=(pos.copy(), vel.copy(), S))
     ns = np.full(P, S, dtype=np.int32); ns[3] = -7; ns[5] = 0
-    alone = pl.plan(wx=np.zeros((P, W)), stages=scb.abi.STAGE_GEOMETRY, outputs=(), S_cap=S, resample_at=(pos.copy(), vel.copy(), ns),
-                    out_buffers={k: first[k] for k in ("ctrl_x", "ctrl_y", "arclen_table")}, spline_inputs=True)
+    alone = pl.plan(stages=scb.abi.STAGE_GEOMETRY, outputs=(), S_cap=S, resample_at=(pos.copy(), vel.copy(), ns),
+                    spline={k: first[k] for k in ("ctrl_x", "ctrl_y", "arclen_table")})
     live = np.ones(P, bool); live[[3, 5]] = False
     for k in ("s_px", "s_py", "s_omega"):
         np.testing.assert_array_equal(alone[k][:, live], merged[k][:, live], err_msg=k)
