@@ -51,7 +51,15 @@ def parse(path):
 
 if __name__ == "__main__":
     res = parse(sys.argv[1])
-    if len(sys.argv) > 2:
+    if len(sys.argv) > 2 and sys.argv[2] == "--merge":  # ncu_ops.py ops.csv --merge profiles/ncu_ops.json TAG "source description"
+        path, tag, src = sys.argv[3], sys.argv[4], sys.argv[5]
+        try:
+            db = json.load(open(path))
+        except Exception:
+            db = {}
+        db[tag] = {"source": src, "kernels": {k: v for k, v in res.items() if not k.startswith("at::")}}
+        json.dump(db, open(path, "w"), indent=1, sort_keys=True)
+    elif len(sys.argv) > 2:
         json.dump(res, open(sys.argv[2], "w"), indent=1, sort_keys=True)
     for k, m in res.items():
         print("%-46s n=%d  %.3f ms  dfma %.3e dmul %.3e dadd %.3e  -> %.2f GFLOP fp64 (%.1f TF/s)  ffma %.2e  thr/inst %.1f  fp64 pipe %.0f%%  issue %.0f%%  dram %.2f GB"
