@@ -496,7 +496,7 @@ def main():
             if not a.no_extras:
                 line["e2e_fp64_records"] = record_leg(False, max(2, n_each // 2))
             # rank, then fetch: summaries of all P rollouts, then the records of the TOPK fastest feasible ones
-            summ = [pin(np.empty(P, dtype=scb.SUMMARY_DTYPE)) for _ in range(nth)]
+            summ = [torch.empty(P * scb.SUMMARY_DTYPE.itemsize, dtype=torch.uint8).pin_memory().numpy().view(scb.SUMMARY_DTYPE) for _ in range(nth)]
             fetched = [None] * nth
 
             def topk(c):

@@ -139,7 +139,9 @@ enum {
 
 typedef struct scb_batch_in {
   int32_t P, W, G;          /* problems, waypoints per problem (>= 2), toppra gridpoints (>= 2;
-                               the reference's default is 101, tp:algorithm.hpp:140) */
+                               the reference's default is 101, tp:algorithm.hpp:140).  W <= 522 in SCB_LAU_QUINTIC
+                               (beyond 512 waypoints the optimiser state of one path lives in one SM's shared
+                               memory), a few thousand in SCB_REF_CUBIC; a longer path is SCB_E_INVALID */
   const void* wx;           /* real [P][W]  waypoint x */
   const void* wy;           /* real [P][W]  waypoint y */
   const void* start_angle;  /* real [P] or NULL; NaN = atan2 of the first leg (sc:606-609) */

@@ -8,5 +8,5 @@ and scb/ (ctypes marshalling for tests and bench, synthetic workloads).  The C++
 sea_current.hpp callers is include/sea_current_b200.hpp.
 """
 from .scb import abi, workloads  # noqa: F401
-from .scb.planner import (ALL_OUTPUTS, RECORD, TRAJECTORY_OUTPUTS, SUMMARY_DTYPE, BatchPlanner, BatchResult, MultiPlanner,  # noqa: F401
+from .scb.planner import (ALL_OUTPUTS, PER_GRID, PER_PROBLEM, PER_SAMPLE, RECORD, TRAJECTORY_OUTPUTS, SUMMARY_DTYPE, BatchPlanner, BatchResult, MultiPlanner,  # noqa: F401
                           ScbError, default_opt, gather_summaries, gpu_local_cpus, near_gpu, shard_range)

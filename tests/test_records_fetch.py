@@ -101,7 +101,7 @@ def test_rank_then_fetch(record_f32):
         np.testing.assert_array_equal(got["status"], full["status"][ids])
         np.testing.assert_array_equal(got["fail_stage"], full["fail_stage"][ids])
         for k in scb.ALL_OUTPUTS:
-            want = full[k][:, ids] if k in scb.planner.PER_GRID else full[k][ids]
+            want = full[k][:, ids] if k in scb.PER_GRID else full[k][ids]
             if record_f32 and k in scb.RECORD:
                 want = want.astype(np.float32)
             assert got[k].dtype == want.dtype, k

@@ -201,10 +201,11 @@ def test_degenerate_stage_lps_gridpoint_boxes(oracle, lp_mode):
 
 
 # ------------------------------------------------------------------ the CTA-team path kernel beyond the lane kernels
-@pytest.mark.parametrize("mode", ["ref_cubic", "lau_quintic"])
-def test_path_kernel_beyond_512_waypoints(oracle, mode):
-    """W > 512: path_kernel.cu (CTA team, Bernstein-form cost in shared memory) is the only path kernel."""
-    P, W, G = 4, 600, 400
+@pytest.mark.parametrize("mode,W", [("ref_cubic", 600), ("lau_quintic", 520)])
+def test_path_kernel_beyond_512_waypoints(oracle, mode, W):
+    """W > 512: path_kernel.cu (CTA team, Bernstein-form cost in shared memory) is the only path kernel.  Its optimiser
+    state lives in one SM's shared memory, which bounds the quintic mode at 522 waypoints (seacurrent_b200.h)."""
+    P, G = 4, 400
     rng = np.random.default_rng(600)
     wx, wy = scb.workloads.random_walk_paths(rng, P, W)
     lim = scb.workloads.random_limits(rng, P, slow_fraction=0.0)
@@ -214,3 +215,9 @@ def test_path_kernel_beyond_512_waypoints(oracle, mode):
     ref, _ = oracle.plan_batch(wx=wx, wy=wy, G=G, spline_mode=0 if mode == "ref_cubic" else 1, **lim)
     assert np.all(ref["status"] == 0)
     _check(res, ref, RTOL64, ("ctrl_x", "ctrl_y", "arclen_total", "arclen_table", "T_total", "cost") + GRID)
+    if mode == "lau_quintic":  # one more waypoint than fits: refused, not truncated
+        pl = scb.BatchPlanner(0, "fp64", mode, max_problems=P, max_waypoints=600, max_gridpoints=G)
+        wx2, wy2 = scb.workloads.random_walk_paths(rng, P, 523)
+        with pytest.raises(scb.ScbError):
+            pl.plan(wx=wx2, wy=wy2, G=G, **lim)
+        pl.close()
