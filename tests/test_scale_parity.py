@@ -15,6 +15,7 @@ import pytest
 
 import seacurrent_b200 as scb
 from test_gpu_parity import GRID, RTOL32, RTOL64, _check, rel_err
+from tolerances import conditioning
 
 pytestmark = pytest.mark.gpu
 
@@ -32,9 +33,9 @@ def c5_case(oracle):
     lim = scb.workloads.random_limits(rng, P, slow_fraction=0.05)
     refs = {}
 
-    def ref(mode):
+    def ref(mode):  # (oracle result, its measured own spread under 8-ulp input perturbations: tests/tolerances.py)
         if mode not in refs:
-            refs[mode] = oracle.plan_batch(wx=wx, wy=wy, G=G, spline_mode=0 if mode == "ref_cubic" else 1, solve_mode=1, **lim)[0]
+            refs[mode] = conditioning(oracle, wx=wx, wy=wy, G=G, spline_mode=0 if mode == "ref_cubic" else 1, solve_mode=1, **lim)
         return refs[mode]
     return dict(P=P, W=W, G=G, wx=wx, wy=wy, lim=lim, ref=ref)
 
@@ -45,9 +46,9 @@ def test_c5_shape_fp64(c5_case, mode):
     pl = scb.BatchPlanner(0, "fp64", mode, max_problems=c["P"], max_waypoints=c["W"], max_gridpoints=c["G"])
     res = pl.plan(wx=c["wx"], wy=c["wy"], G=c["G"], **c["lim"])
     pl.close()
-    ref = c["ref"](mode)
+    ref, spread = c["ref"](mode)
     assert (ref["status"] == 0).sum() >= c["P"] - 2
-    _check(res, ref, RTOL64, ("ctrl_x", "ctrl_y", "arclen_total", "arclen_table", "T_total", "cost") + GRID)
+    _check(res, ref, RTOL64, ("ctrl_x", "ctrl_y", "arclen_total", "arclen_table", "T_total", "cost") + GRID, spread)
 
 
 @pytest.mark.parametrize("mode", ["ref_cubic", "lau_quintic"])
@@ -58,7 +59,7 @@ def test_c5_shape_fp32(c5_case, mode):
     pl = scb.BatchPlanner(0, "fp32", mode, max_problems=c["P"], max_waypoints=c["W"], max_gridpoints=c["G"])
     res = pl.plan(wx=c["wx"], wy=c["wy"], G=c["G"], **c["lim"])
     pl.close()
-    ref = c["ref"](mode)
+    ref, _ = c["ref"](mode)
     np.testing.assert_array_equal(res["status"], ref["status"])
     np.testing.assert_array_equal(res["fail_stage"], ref["fail_stage"])
     ok = ref["status"] == 0
@@ -212,9 +213,9 @@ def test_path_kernel_beyond_512_waypoints(oracle, mode, W):
     pl = scb.BatchPlanner(0, "fp64", mode, max_problems=P, max_waypoints=W, max_gridpoints=G)
     res = pl.plan(wx=wx, wy=wy, G=G, **lim)
     pl.close()
-    ref, _ = oracle.plan_batch(wx=wx, wy=wy, G=G, spline_mode=0 if mode == "ref_cubic" else 1, **lim)
+    ref, spread = conditioning(oracle, wx=wx, wy=wy, G=G, spline_mode=0 if mode == "ref_cubic" else 1, **lim)
     assert np.all(ref["status"] == 0)
-    _check(res, ref, RTOL64, ("ctrl_x", "ctrl_y", "arclen_total", "arclen_table", "T_total", "cost") + GRID)
+    _check(res, ref, RTOL64, ("ctrl_x", "ctrl_y", "arclen_total", "arclen_table", "T_total", "cost") + GRID, spread)
     if mode == "lau_quintic":  # one more waypoint than fits: refused, not truncated
         pl = scb.BatchPlanner(0, "fp64", mode, max_problems=P, max_waypoints=600, max_gridpoints=G)
         wx2, wy2 = scb.workloads.random_walk_paths(rng, P, 523)
