@@ -189,15 +189,44 @@ template <class R> struct LauResult {
   std::vector<V2<R>> Wp;
   std::vector<R> e;
   R cost;
-  std::vector<R> history;  // J at every evaluation (K+1 entries)
+  std::vector<R> history;  // J at every evaluation (K+1 entries); +inf where the iterate collides
+  bool collision_free = true;  // false: every iterate crossed an obstacle edge (cost = +inf)
 };
+
+// Collision test of one spline (Lau09 IV-B): every segment cut into M chords B(k/M) -> B((k+1)/M), every chord
+// against every obstacle edge with the reference's segment test (intersects, sc:142-178).
+template <class R> inline bool lau_collides(const Spline<R>& sp, const std::vector<Edge<R>>& edges, int M) {
+  for (const auto& seg : sp.ctrl) {
+    V2<R> a = seg[0];
+    for (int k = 1; k <= M; ++k) {
+      const R u = k == M ? (R)1 : (R)k / (R)M;
+      std::vector<V2<R>> t = seg;
+      for (size_t r = 1; r < t.size(); ++r)
+        for (size_t i = 0; i + r < t.size(); ++i) t[i] = {((R)1 - u) * t[i].x + u * t[i + 1].x, ((R)1 - u) * t[i].y + u * t[i + 1].y};
+      V2<R> pt;
+      for (const auto& e : edges)
+        if (seg_intersects(a, t[0], e.a, e.b, pt)) return true;
+      a = t[0];
+    }
+  }
+  return false;
+}
 
 // A7.  iRPROP- with a fixed budget of K gradient iterations (Lau09 Alg. 1 adapted to use the
 // sign of the analytic gradient): step *1.2 while the sign holds, *0.5 and skip the move on
 // a sign change; parameters clamped to their boxes; best-so-far parameters are returned.
 // A gradient component within 1e-9 of the largest one of its class counts as zero (so that
 // rounding noise on exactly-stationary parameters cannot decide a move).
-template <class R> inline LauResult<R> lau_optimise(const LauModel<R>& m, const LauOpt& o) {
+//
+// Collision term (Lau09 IV-B: "if the trajectory is not collision-free according to the obstacle map, its cost is set to
+// infinity"; there the optimiser is derivative-free and simply rejects such a trial step).  With an edge list and
+// M = collision_chords > 0, every iterate is tested (lau_collides) and a colliding iterate has J = +inf: it can never
+// become the best-so-far, and it is REJECTED - the parameters return to the best collision-free iterate found so far,
+// every step size is halved and the gradient memory cleared, so the next trial is a shorter step from there.  While no
+// collision-free iterate exists yet (the initial spline collides) the gradient steps go on.  The returned spline is the
+// best collision-free iterate; if there is none, collision_free = false and cost = +inf.
+template <class R> inline LauResult<R> lau_optimise(const LauModel<R>& m, const LauOpt& o,
+                                                    const std::vector<Edge<R>>* edges = nullptr, int chords = 0) {
   const int W = (int)m.W0.size();
   std::vector<V2<R>> Wp = m.W0;
   std::vector<R> e(W, (R)o.e_init);
@@ -216,10 +245,21 @@ template <class R> inline LauResult<R> lau_optimise(const LauModel<R>& m, const 
   std::vector<V2<R>> gW; std::vector<R> ge;
   for (int it = 0; it <= o.iters; ++it) {
     Spline<R> sp = lau_build(m, Wp, e);
-    const R J = lau_cost_grad(sp, (R)o.lambda, &g);
+    R J = lau_cost_grad(sp, (R)o.lambda, &g);
+    const bool hit = edges && chords > 0 && !edges->empty() && lau_collides(sp, *edges, chords);
+    if (hit) J = (R)INFINITY;
     best.history.push_back(J);
     if (it == 0 || J < best.cost) { best.cost = J; best.spline = sp; best.Wp = Wp; best.e = e; }
     if (it == o.iters) break;
+    if (hit && best.cost < (R)INFINITY) {  // rejected trial: back to the best collision-free iterate, shorter steps
+      Wp = best.Wp; e = best.e;
+      for (int i = 0; i < W; ++i) {
+        se[i] = std::max(se[i] * (R)0.5, (R)1e-6); pe[i] = 0;
+        const R smin = (R)1e-6 * m.mag[i];
+        sw[i] = {std::max(sw[i].x * (R)0.5, smin), std::max(sw[i].y * (R)0.5, smin)}; pw[i] = {0, 0};
+      }
+      continue;
+    }
     lau_backprop(m, g, gW, ge);
     R gemax = 0, gwmax = 0;
     for (int i = 0; i < W; ++i) gemax = std::max(gemax, std::fabs(ge[i]));
@@ -242,6 +282,7 @@ template <class R> inline LauResult<R> lau_optimise(const LauModel<R>& m, const 
       }
     }
   }
+  best.collision_free = best.cost < (R)INFINITY;
   return best;
 }
 

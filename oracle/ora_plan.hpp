@@ -129,7 +129,9 @@ inline PlanOut plan_one(const PlanIn& in) {
     o.cost = 0;
   } else {
     LauModel<double> m = lau_model(in.path, in.start_angle);
-    LauResult<double> r = lau_optimise(m, in.opt);
+    // the collision term lives INSIDE the optimiser loop in quintic mode (ora_lau.hpp: rejected trials, best
+    // collision-free iterate); the verdict on the finished spline below is then the same test on that iterate
+    LauResult<double> r = lau_optimise(m, in.opt, &in.edges, in.collision_chords);
     sp = r.spline; o.cost = r.cost;
   }
   o.degree = sp.degree();

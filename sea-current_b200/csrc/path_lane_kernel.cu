@@ -132,6 +132,83 @@ __device__ __forceinline__ void hodograph_power_T(const double (&g)[5], double (
   gd[4] = g[4];
 }
 
+// ---- collision term inside the optimiser loop (Lau09 IV-B; DESIGN.md "New stages", A7) ------------------------------
+// Does the lane's segment, cut into M chords B(k/M) -> B((k+1)/M), cross an obstacle edge (the reference's segment
+// test, sc:142-178)?  The segment is given by its start point and hodograph control points D_0..D_4 (control points
+// P_0 = W, P_{j+1} = P_j + D_j / 5).  Two culls keep the common case cheap: the float bounding box of the control
+// polygon (the curve lies in its convex hull) against the float bounding box of every edge - rounded outwards, so a
+// cull never hides a crossing - and, for the few edges that survive, the chord's box against the edge's.  Edge data
+// of the first kCollSmem edges sits in shared memory (one broadcast read per edge), the rest comes from global memory.
+constexpr int kCollSmem = 128;
+struct CollEdges {
+  const double* e;   // [n][4] in shared memory (first kCollSmem edges)
+  const float* box;  // [n][4] = (xlo, xhi, ylo, yhi), rounded outwards
+  int ns, n;         // staged / all
+  const void* g;     // all edges in global memory, storage type S
+};
+
+template <class S>
+__device__ __forceinline__ void stage_coll_edges(const PathArgs& g, double* se, float* sb, int tid, int T) {
+  const int ns = g.n_coll_edges < kCollSmem ? g.n_coll_edges : kCollSmem;
+  const S* ge = (const S*)g.coll_edges;
+  for (int k = tid; k < ns; k += T) {
+    const double x0 = (double)ge[4 * k], y0 = (double)ge[4 * k + 1], x1 = (double)ge[4 * k + 2], y1 = (double)ge[4 * k + 3];
+    se[4 * k] = x0; se[4 * k + 1] = y0; se[4 * k + 2] = x1; se[4 * k + 3] = y1;
+    sb[4 * k] = __double2float_rd(fmin(x0, x1)); sb[4 * k + 1] = __double2float_ru(fmax(x0, x1));
+    sb[4 * k + 2] = __double2float_rd(fmin(y0, y1)); sb[4 * k + 3] = __double2float_ru(fmax(y0, y1));
+  }
+}
+
+template <class S>
+__device__ __noinline__ bool segment_hits(double wx, double wy, const double (&dx)[5], const double (&dy)[5], const CollEdges& ce, int M) {
+  // control polygon -> float box of the hull
+  float xlo, xhi, ylo, yhi;
+  {
+    double px = wx, py = wy, ax = wx, bx = wx, ay = wy, by = wy;
+#pragma unroll
+    for (int j = 0; j < 5; ++j) {
+      px = fma(0.2, dx[j], px); py = fma(0.2, dy[j], py);
+      ax = fmin(ax, px); bx = fmax(bx, px); ay = fmin(ay, py); by = fmax(by, py);
+    }
+    // the chord points below come from the power basis: a hair outside the hull by rounding; widen by 1e-6 of its size
+    const float mx = 1e-6f * (float)(bx - ax) + 1e-30f, my = 1e-6f * (float)(by - ay) + 1e-30f;
+    xlo = __double2float_rd(ax) - mx; xhi = __double2float_ru(bx) + mx; ylo = __double2float_rd(ay) - my; yhi = __double2float_ru(by) + my;
+  }
+  // power basis of the segment: B(u) = W + u (c0 + u (c1/2 + u (c2/3 + u (c3/4 + u c4/5))))
+  double cx[5], cy[5];
+  hodograph_power(dx[0], dx[1], dx[2], dx[3], dx[4], cx);
+  hodograph_power(dy[0], dy[1], dy[2], dy[3], dy[4], cy);
+  const double qx1 = 0.5 * cx[1], qx2 = cx[2] * (1.0 / 3.0), qx3 = 0.25 * cx[3], qx4 = 0.2 * cx[4];
+  const double qy1 = 0.5 * cy[1], qy2 = cy[2] * (1.0 / 3.0), qy3 = 0.25 * cy[3], qy4 = 0.2 * cy[4];
+  const double invM = 1.0 / (double)M;
+  const S* ge = (const S*)ce.g;
+  for (int e = 0; e < ce.n; ++e) {
+    double e0x, e0y, e1x, e1y;
+    float bxl, bxh, byl, byh;
+    if (e < ce.ns) {
+      bxl = ce.box[4 * e]; bxh = ce.box[4 * e + 1]; byl = ce.box[4 * e + 2]; byh = ce.box[4 * e + 3];
+      if (bxl > xhi || bxh < xlo || byl > yhi || byh < ylo) continue;
+      e0x = ce.e[4 * e]; e0y = ce.e[4 * e + 1]; e1x = ce.e[4 * e + 2]; e1y = ce.e[4 * e + 3];
+    } else {
+      e0x = (double)ge[4 * e]; e0y = (double)ge[4 * e + 1]; e1x = (double)ge[4 * e + 2]; e1y = (double)ge[4 * e + 3];
+      if (fmin(e0x, e1x) > (double)xhi || fmax(e0x, e1x) < (double)xlo || fmin(e0y, e1y) > (double)yhi || fmax(e0y, e1y) < (double)ylo) continue;
+    }
+    const double exl = fmin(e0x, e1x), exh = fmax(e0x, e1x), eyl = fmin(e0y, e1y), eyh = fmax(e0y, e1y);
+    double ax = wx, ay = wy;
+    for (int k = 1; k <= M; ++k) {
+      const double u = k == M ? 1.0 : (double)k * invM;
+      const double qx = fma(u, fma(u, fma(u, fma(u, fma(u, qx4, qx3), qx2), qx1), cx[0]), wx);
+      const double qy = fma(u, fma(u, fma(u, fma(u, fma(u, qy4, qy3), qy2), qy1), cy[0]), wy);
+      if (!(exl > fmax(ax, qx) || exh < fmin(ax, qx) || eyl > fmax(ay, qy) || eyh < fmin(ay, qy))) {
+        double ix, iy;
+        if (seg_intersects<double>(ax, ay, qx, qy, e0x, e0y, e1x, e1y, ix, iy)) return true;
+      }
+      ax = qx; ay = qy;
+    }
+  }
+  return false;
+}
+
 }  // namespace
 
 
@@ -233,8 +310,10 @@ struct CtaComm {
 
 // One waypoint lane from the waypoints to the control points of its segment.  p: problem, i: waypoint index,
 // own: the lane has a waypoint.  Every lane of the warp / CTA runs this to the end (collectives inside).
-template <class S, int DEG, class Comm>
-__device__ __forceinline__ void lane_path(const PathArgs& g, Comm& cm, int p, int i, bool own) {
+// COLL: the collision term inside the optimiser loop is compiled in (a separate instantiation, so that the default
+// kernel stays the register-exact code it was: 127 registers, no stack traffic in the loop)
+template <class S, int DEG, class Comm, bool COLL>
+__device__ __forceinline__ void lane_path(const PathArgs& g, Comm& cm, int p, int i, bool own, const CollEdges& ce) {
   constexpr int NC = DEG + 1;
   const int W = g.W, nseg = W - 1, ss = cm.sstride;
   double* st = cm.st;
@@ -315,14 +394,22 @@ __device__ __forceinline__ void lane_path(const PathArgs& g, Comm& cm, int p, in
       double Tx, Ty, Txp, Typ, wxp, wyp, Ax, Ay, Axp, Ayp;
       waypoint_TA(e, Tx, Ty, Txp, Typ, wxp, wyp, Ax, Ay, Axp, Ayp);
       double cx[5], cy[5];
-      hodograph_power(Tx, fma(0.25, Ax, Tx), fma(0.25, Axp - Ax, fma(5.0, wxp - wx, -2.0 * (Tx + Txp))), fma(-0.25, Axp, Txp), Txp, cx);
-      hodograph_power(Ty, fma(0.25, Ay, Ty), fma(0.25, Ayp - Ay, fma(5.0, wyp - wy, -2.0 * (Ty + Typ))), fma(-0.25, Ayp, Typ), Typ, cy);
+      const double hdx[5] = {Tx, fma(0.25, Ax, Tx), fma(0.25, Axp - Ax, fma(5.0, wxp - wx, -2.0 * (Tx + Txp))), fma(-0.25, Axp, Txp), Txp};
+      const double hdy[5] = {Ty, fma(0.25, Ay, Ty), fma(0.25, Ayp - Ay, fma(5.0, wyp - wy, -2.0 * (Ty + Typ))), fma(-0.25, Ayp, Typ), Typ};
+      hodograph_power(hdx[0], hdx[1], hdx[2], hdx[3], hdx[4], cx);
+      hodograph_power(hdy[0], hdy[1], hdy[2], hdy[3], hdy[4], cy);
       // ---- A6
       double gcx[5], gcy[5], Js;
       if (iter < K) Js = segment_cost<true>(cx, cy, lambda, gcx, gcy);
       else Js = segment_cost<false>(cx, cy, lambda, gcx, gcy);
       if (!seg) Js = 0;
-      const double J = cm.path_sum(Js, nseg);
+      double J = cm.path_sum(Js, nseg);
+      // collision term (Lau09 IV-B): a colliding iterate has infinite cost; it is rejected below
+      bool hit = false;
+      if constexpr (COLL) {
+        hit = cm.path_any(seg && segment_hits<S>(wx, wy, hdx, hdy, ce, g.coll_chords));
+        if (hit) J = CUDART_INF;
+      }
       const bool better = iter == 0 || J < cost;
       if (better) { cost = J; st[kBe * ss] = e; st[kBwx * ss] = wx; st[kBwy * ss] = wy; }
       if (iter == K) break;
@@ -363,24 +450,30 @@ __device__ __forceinline__ void lane_path(const PathArgs& g, Comm& cm, int p, in
       // largest gradient component of each class over the path (components below 1e-9 of it count as zero)
       double gemax = own ? fabs(ge) : 0.0, gwmax = inner ? fmax(fabs(gWx), fabs(gWy)) : 0.0;
       cm.path_max2(gemax, gwmax);
-      // ---- A7: iRPROP-
+      // ---- A7: iRPROP-.  A rejected (colliding) trial, once a collision-free iterate exists: back to the best such
+      // iterate, every step halved, gradient memory cleared.  The lanes of a rejected path still walked the chain rule
+      // above with their warp (its shuffles need every lane); only what they keep differs.
       {
+        const bool reject = COLL && hit && cost < CUDART_INF;
         const double te = 1e-9 * gemax, tw = 1e-9 * gwmax;
-        double se = st[kSe * ss], pe = st[kPe * ss];
+        const double se0 = st[kSe * ss];
+        double se = se0, pe = st[kPe * ss];
         const double gi = fabs(ge) <= te ? 0.0 : ge;
         const double ei = e + rprop_step<double>(gi, pe, se, 1e-6, 1.0);
-        e = fmin((double)o.e_max, fmax((double)o.e_min, ei));
-        st[kSe * ss] = se; st[kPe * ss] = pe;
+        e = reject ? st[kBe * ss] : fmin((double)o.e_max, fmax((double)o.e_min, ei));
+        st[kSe * ss] = reject ? fmax(0.5 * se0, 1e-6) : se; st[kPe * ss] = reject ? 0.0 : pe;
         if (o.move_waypoints && inner) {
           const double mag = st[kMag * ss], w0x = st[kW0x * ss], w0y = st[kW0y * ss];
-          double swx = st[kSwx * ss], swy = st[kSwy * ss], pwx = st[kPwx * ss], pwy = st[kPwy * ss];
+          const double swx0 = st[kSwx * ss], swy0 = st[kSwy * ss];
+          double swx = swx0, swy = swy0, pwx = st[kPwx * ss], pwy = st[kPwy * ss];
           const double gvx = fabs(gWx) <= tw ? 0.0 : gWx, gvy = fabs(gWy) <= tw ? 0.0 : gWy;
           const double smin = 1e-6 * mag, smax = 0.5 * mag, rr = o.w_radius;
           const double nx = wx + rprop_step<double>(gvx, pwx, swx, smin, smax);
           const double ny = wy + rprop_step<double>(gvy, pwy, swy, smin, smax);
-          wx = fmin(w0x + rr, fmax(w0x - rr, nx));
-          wy = fmin(w0y + rr, fmax(w0y - rr, ny));
-          st[kSwx * ss] = swx; st[kSwy * ss] = swy; st[kPwx * ss] = pwx; st[kPwy * ss] = pwy;
+          wx = reject ? st[kBwx * ss] : fmin(w0x + rr, fmax(w0x - rr, nx));
+          wy = reject ? st[kBwy * ss] : fmin(w0y + rr, fmax(w0y - rr, ny));
+          st[kSwx * ss] = reject ? fmax(0.5 * swx0, smin) : swx; st[kSwy * ss] = reject ? fmax(0.5 * swy0, smin) : swy;
+          st[kPwx * ss] = reject ? 0.0 : pwx; st[kPwy * ss] = reject ? 0.0 : pwy;
         }
       }
     }
@@ -420,22 +513,30 @@ __device__ __forceinline__ void lane_path(const PathArgs& g, Comm& cm, int p, in
 }
 
 // W <= 32: a warp owns PB = floor(32 / W) consecutive paths
-template <class S, int DEG>
+template <class S, int DEG, bool COLL>
 __global__ void __launch_bounds__(kLaneWarps * 32, 4) path_lane_kernel(PathArgs g) {
   extern __shared__ __align__(16) unsigned char lane_smem_raw[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int W = g.W, PB = g.PB, P = g.P;
   const int p0 = (blockIdx.x * kLaneWarps + warp) * PB;
-  if (p0 >= P) return;  // the whole warp leaves together
   const int pl = lane / W, i = lane - pl * W, p = p0 + pl;
   WarpComm cm;
   cm.base = pl * W; cm.W = W; cm.sstride = 32;
   cm.st = (double*)lane_smem_raw + (size_t)warp * kLaneSlots * 32 + lane;
-  lane_path<S, DEG, WarpComm>(g, cm, p, i, pl < PB && p < P);
+  CollEdges ce{nullptr, nullptr, 0, 0, nullptr};
+  if constexpr (COLL) {  // every thread reaches the barrier (no early return above)
+    double* se = (double*)lane_smem_raw + (size_t)kLaneWarps * kLaneSlots * 32;
+    float* sb = (float*)(se + 4 * kCollSmem);
+    stage_coll_edges<S>(g, se, sb, threadIdx.x, kLaneWarps * 32);
+    __syncthreads();
+    ce = CollEdges{se, sb, g.n_coll_edges < kCollSmem ? g.n_coll_edges : kCollSmem, g.n_coll_edges, g.coll_edges};
+  }
+  if (p0 >= P) return;  // the whole warp leaves together
+  lane_path<S, DEG, WarpComm, COLL>(g, cm, p, i, pl < PB && p < P, ce);
 }
 
 // 33 <= W <= 512: one path per CTA of ceil(W / 32) warps (128 registers per thread: 512 threads at most)
-template <class S, int DEG>
+template <class S, int DEG, bool COLL>
 __global__ void __launch_bounds__(512, 1) path_lane_cta_kernel(PathArgs g) {
   extern __shared__ __align__(16) unsigned char lane_smem_raw[];
   const int T = blockDim.x, tid = threadIdx.x;
@@ -444,18 +545,27 @@ __global__ void __launch_bounds__(512, 1) path_lane_cta_kernel(PathArgs g) {
   cm.xbuf = (double*)lane_smem_raw;
   cm.red = cm.xbuf + (size_t)2 * CtaComm::kMaxVals * T;
   cm.st = cm.red + 128 + tid;
-  lane_path<S, DEG, CtaComm>(g, cm, blockIdx.x, tid, tid < g.W);
+  CollEdges ce{nullptr, nullptr, 0, 0, nullptr};
+  if constexpr (COLL) {
+    double* se = cm.red + 128 + (size_t)kLaneSlots * T;
+    float* sb = (float*)(se + 4 * kCollSmem);
+    stage_coll_edges<S>(g, se, sb, tid, T);
+    __syncthreads();
+    ce = CollEdges{se, sb, g.n_coll_edges < kCollSmem ? g.n_coll_edges : kCollSmem, g.n_coll_edges, g.coll_edges};
+  }
+  lane_path<S, DEG, CtaComm, COLL>(g, cm, blockIdx.x, tid, tid < g.W, ce);
 }
 
 bool path_lane_shape(int W, int& PB, size_t& smem, int spline_mode) {
   if (W < 2 || W > 512) return false;
+  const size_t coll = spline_mode == SCB_REF_CUBIC ? 0 : (size_t)kCollSmem * (4 * sizeof(double) + 4 * sizeof(float));  // staged edges
   if (W <= 32) {
     PB = 32 / W;
-    smem = spline_mode == SCB_REF_CUBIC ? 0 : (size_t)kLaneWarps * kLaneSlots * 32 * sizeof(double);
+    smem = spline_mode == SCB_REF_CUBIC ? 0 : (size_t)kLaneWarps * kLaneSlots * 32 * sizeof(double) + coll;
   } else {
     PB = 1;
     const size_t T = (size_t)(W + 31) / 32 * 32;
-    smem = ((size_t)2 * CtaComm::kMaxVals * T + 128 + (size_t)kLaneSlots * T) * sizeof(double);
+    smem = ((size_t)2 * CtaComm::kMaxVals * T + 128 + (size_t)kLaneSlots * T) * sizeof(double) + coll;
   }
   return true;
 }
@@ -465,16 +575,20 @@ template <class S> void launch_path_lane(const PathArgs& a0, int spline_mode, in
   a.PB = PB; a.table_in_smem = 0;
   if (a.W <= 32) {
     const int per_cta = PB * kLaneWarps, grid = (a.P + per_cta - 1) / per_cta;
-    if (spline_mode == SCB_REF_CUBIC) path_lane_kernel<S, 3><<<grid, kLaneWarps * 32, smem, st>>>(a);
-    else path_lane_kernel<S, 5><<<grid, kLaneWarps * 32, smem, st>>>(a);
+    if (spline_mode == SCB_REF_CUBIC) path_lane_kernel<S, 3, false><<<grid, kLaneWarps * 32, smem, st>>>(a);
+    else if (a.n_coll_edges > 0) path_lane_kernel<S, 5, true><<<grid, kLaneWarps * 32, smem, st>>>(a);
+    else path_lane_kernel<S, 5, false><<<grid, kLaneWarps * 32, smem, st>>>(a);
   } else {
     const int T = (a.W + 31) / 32 * 32;
     if (spline_mode == SCB_REF_CUBIC) {
-      cudaFuncSetAttribute(path_lane_cta_kernel<S, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      path_lane_cta_kernel<S, 3><<<a.P, T, smem, st>>>(a);
+      cudaFuncSetAttribute(path_lane_cta_kernel<S, 3, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      path_lane_cta_kernel<S, 3, false><<<a.P, T, smem, st>>>(a);
+    } else if (a.n_coll_edges > 0) {
+      cudaFuncSetAttribute(path_lane_cta_kernel<S, 5, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      path_lane_cta_kernel<S, 5, true><<<a.P, T, smem, st>>>(a);
     } else {
-      cudaFuncSetAttribute(path_lane_cta_kernel<S, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      path_lane_cta_kernel<S, 5><<<a.P, T, smem, st>>>(a);
+      cudaFuncSetAttribute(path_lane_cta_kernel<S, 5, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      path_lane_cta_kernel<S, 5, false><<<a.P, T, smem, st>>>(a);
     }
   }
 }

@@ -122,7 +122,9 @@ int validate(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, int
   if (in->n_obstacle_edges < 0 || (in->n_obstacle_edges > 0 && !in->obstacle_edges)) return SCB_E_INVALID;
   if (in->collision_chords < 0 || in->collision_chords > 4096) return SCB_E_INVALID;
   if (in->n_obstacle_edges > 0 && (stages & SCB_STAGE_SPLINE) && ctx->cfg.spline_mode != SCB_REF_CUBIC && in->collision_chords == 0)
-    return SCB_E_INVALID;  // the tangent clipping is the cubic's; the quintic takes edges for the collision verdict only
+    return SCB_E_INVALID;  // the tangent clipping is the cubic's; the quintic takes edges for the collision term only
+  if (in->n_obstacle_edges > 0 && (stages & SCB_STAGE_SPLINE) && ctx->cfg.spline_mode != SCB_REF_CUBIC && in->W > 512)
+    return SCB_E_INVALID;  // the collision term lives in the lane kernels' optimiser loop (W <= 512)
   if ((in->omega_max > 0 || in->acc_lat_max > 0) &&
       (stages & (SCB_STAGE_SPLINE | SCB_STAGE_TIMING | SCB_STAGE_GEOMETRY)) != (SCB_STAGE_SPLINE | SCB_STAGE_TIMING | SCB_STAGE_GEOMETRY))
     return SCB_E_INVALID;  // the caps need the curvature at the gridpoints
@@ -179,6 +181,10 @@ int run_device(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, i
     a.vel_start = in->vel_start; a.vel_end = in->vel_end;
     const bool clip = ctx->cfg.spline_mode == SCB_REF_CUBIC && in->obstacle_edges;  // shrink_tangent: cubic only
     a.edges = clip ? in->obstacle_edges : nullptr; a.n_edges = clip ? in->n_obstacle_edges : 0;
+    if (ctx->cfg.spline_mode == SCB_LAU_QUINTIC && in->collision_chords > 0 && in->obstacle_edges && in->n_obstacle_edges > 0) {
+      // Lau09 IV-B inside the optimiser loop: colliding trial iterates are rejected (path_lane_kernel.cu)
+      a.coll_edges = in->obstacle_edges; a.n_coll_edges = in->n_obstacle_edges; a.coll_chords = in->collision_chords;
+    }
     a.ctrl_x = dCx; a.ctrl_y = dCy; a.table = dTab; a.L = dL; a.cost = out->cost; a.status = out->status;
     if (do_geo && do_timing) {
       if (obst) {

@@ -97,6 +97,7 @@ struct PathArgs {
   const void *wx, *wy, *start_angle;  // [P][W], [P][W], [P] or null
   const void *vel_start, *vel_end;    // [P] or null: end slopes of the Hermite path q(s)
   const void *edges; int n_edges;     // [n_edges][4] obstacle edges (x0, y0, x1, y1) or null: tangent clipping
+  const void *coll_edges; int n_coll_edges, coll_chords;  // quintic optimiser: collision term inside the loop (Lau09 IV-B)
   void *ctrl_x, *ctrl_y;              // [P][(W-1)*(d+1)] or null
   void *table;                        // [P][(W-1)*101]; may be null only when the table fits in shared memory
   void *L, *cost;                     // [P]

@@ -1,9 +1,13 @@
-"""Collision verdict of the finished spline (SURVEY 8f N3, Lau09 IV-B: "if the trajectory is not collision-free
-according to the obstacle map, its cost is set to infinity"): scb_batch_in.collision_chords = M cuts every segment into
-M chords and tests each against the obstacle edges with the reference's segment test (intersects,
-sea_current.hpp:142-178).  A hit -> status SCB_ST_ERR_COLLISION (19), cost = +inf, the problem is not timed.
-CPU: the oracle against a numpy restatement.  GPU: verdicts identical to the oracle's, timing of the free problems
-at 1e-9, both spline constructions."""
+"""Collision term (SURVEY 8f N3, Lau09 IV-B: "if the trajectory is not collision-free according to the obstacle map, its
+cost is set to infinity"): scb_batch_in.collision_chords = M cuts every segment into M chords and tests each against
+the obstacle edges with the reference's segment test (intersects, sea_current.hpp:142-178).
+  * verdict on the finished spline (both constructions): a hit -> status SCB_ST_ERR_COLLISION (19), cost = +inf, the
+    problem is not timed;
+  * inside the quintic optimiser's loop: a colliding trial iterate has infinite cost and is REJECTED (back to the best
+    collision-free iterate, steps halved), so the optimiser keeps its best collision-free iterate instead of walking
+    through a wall.
+CPU: the oracle against a numpy restatement, and what the in-loop term buys.  GPU: verdicts identical to the oracle's,
+control points and timing of the free problems at 1e-9, both spline constructions."""
 import numpy as np
 import pytest
 
@@ -58,7 +62,9 @@ def test_oracle_hand_case(oracle):
         wall = np.array([[3.0, -1.0, 3.0, 1.0]])  # across the first leg
         hit, _ = oracle.plan_batch(wx=wx, wy=wy, G=51, spline_mode=mode, obstacle_edges=wall, collision_chords=16, **lim)
         assert hit["status"][0] == COLLISION and np.isinf(hit["cost"][0]) and hit["T_total"][0] == 0
-        np.testing.assert_array_equal(hit["ctrl_x"], free["ctrl_x"])
+        # the wall cuts the leg in two: every iterate collides, the best-so-far stays the initial spline
+        start, _ = oracle.plan_batch(wx=wx, wy=wy, G=51, spline_mode=mode, opt=scb.default_opt(iters=0), **lim)
+        np.testing.assert_array_equal(hit["ctrl_x"], start["ctrl_x"])
         away = np.array([[3.0, 5.0, 3.0, 7.0]])
         ok, _ = oracle.plan_batch(wx=wx, wy=wy, G=51, spline_mode=mode, obstacle_edges=away, collision_chords=16, **lim)
         assert ok["status"][0] == 0 and ok["T_total"][0] == free["T_total"][0] and ok["cost"][0] == free["cost"][0]
@@ -79,6 +85,44 @@ def test_oracle_vs_numpy_restatement(oracle, mode, nc):
     np.testing.assert_array_equal(got["status"] == COLLISION, want)
     assert 4 <= want.sum() <= 36
     assert np.all(np.isinf(got["cost"][want])) and np.all(got["T_total"][want] == 0) and np.all(got["T_total"][~want] > 0)
+
+
+def test_optimiser_keeps_its_best_collision_free_iterate(oracle):
+    """What the term inside the loop buys (Lau09 IV-B): walls beside the legs, close enough that the unconstrained
+    optimiser swings some splines through them.  With the term, a problem whose INITIAL spline is collision-free can no
+    longer end in a collision, so the colliding fraction drops to the problems that collide from the start."""
+    P, W, M = 160, 8, 12
+    rng = np.random.default_rng(77)
+    wx, wy = scb.workloads.random_walk_paths(rng, P, W)
+    # E wall pieces, each 0.2 .. 1.2 m beside the middle of a random leg of a random problem and parallel to it (the paths
+    # all leave the origin, so every piece lies near many of them); one list shared by the batch
+    E = 14
+    k = rng.integers(1, W - 2, E); p = rng.integers(0, P, E)
+    mid = np.stack([(wx[p, k] + wx[p, k + 1]) / 2, (wy[p, k] + wy[p, k + 1]) / 2], 1)
+    leg = np.stack([wx[p, k + 1] - wx[p, k], wy[p, k + 1] - wy[p, k]], 1)
+    leg /= np.linalg.norm(leg, axis=1, keepdims=True)
+    nrm = np.stack([-leg[:, 1], leg[:, 0]], 1)
+    c = mid + nrm * (rng.uniform(0.2, 1.2, (E, 1)) * rng.choice([-1.0, 1.0], (E, 1)))
+    edges = np.concatenate([c - 0.6 * leg, c + 0.6 * leg], 1)
+    lim = dict(vel_lo=np.full(P, -2.0), vel_hi=np.full(P, 2.0), acc_lo=np.full(P, -1.0), acc_hi=np.full(P, 1.0))
+    opt = scb.default_opt(move_waypoints=1)
+    kw = dict(wx=wx, wy=wy, G=51, spline_mode=1, **lim)
+    start, _ = oracle.plan_batch(opt=scb.default_opt(iters=0), **kw)           # the initial splines
+    blind, _ = oracle.plan_batch(opt=opt, **kw)                                 # optimiser that knows no obstacles
+    aware, _ = oracle.plan_batch(opt=opt, obstacle_edges=edges, collision_chords=M, **kw)
+    hits = lambda r: np.array([_spline_hits(r["ctrl_x"][q], r["ctrl_y"][q], 6, edges, M) for q in range(P)])
+    h0, hb, ha = hits(start), hits(blind), hits(aware)
+    np.testing.assert_array_equal(aware["status"] == COLLISION, ha)      # the verdict is the finished spline's
+    assert not np.any(ha & ~h0)                                          # free at the start -> free at the end
+    assert (hb & ~h0).sum() >= 3                                         # ... which the blind optimiser does not give
+    assert ha.sum() < hb.sum()
+    # where neither run ever met a wall the term changes nothing; elsewhere the kept iterate costs at least the blind optimum's
+    same = ~hb & ~ha & (aware["cost"] == blind["cost"])
+    print("colliding: initial %d, blind optimiser %d, with the term %d of %d; untouched by the term: %d" % (h0.sum(), hb.sum(), ha.sum(), P, same.sum()))
+    assert same.sum() >= P // 4
+    np.testing.assert_array_equal(aware["ctrl_x"][same], blind["ctrl_x"][same])
+    free = ~ha
+    assert np.all(aware["cost"][free] <= start["cost"][free] * (1 + 1e-12))    # best-so-far never worse than the start
 
 
 @pytest.fixture(scope="module")
@@ -108,6 +152,10 @@ def test_gpu_verdicts_match_oracle(planners, oracle, mode, W, P):
     assert np.all(np.isinf(got["cost"][hit])) and np.all(got["T_total"][hit] == 0)
     np.testing.assert_allclose(got["T_total"][ok], ref["T_total"][ok], rtol=1e-9)
     np.testing.assert_allclose(got["arclen_total"][ok], ref["arclen_total"][ok], rtol=1e-9)
+    np.testing.assert_allclose(got["cost"][ok], ref["cost"][ok], rtol=1e-9)
+    for k in ("ctrl_x", "ctrl_y"):  # in quintic mode the rejected trials steer the optimiser: same iterates, same control points
+        sc = np.abs(ref[k][ok]).max(axis=1, keepdims=True)
+        assert np.max(np.abs(got[k][ok] - ref[k][ok]) / np.maximum(np.abs(ref[k][ok]), 1e-3 * sc)) <= 1e-9, k
     # a summary-ranking outer loop sees the colliding candidates as infinitely dear
     assert np.all(got["cost"][ok] < np.inf)
     off = planners("fp64", mode).plan(**dict(kw, collision_chords=0)) if mode == "ref_cubic" else None
