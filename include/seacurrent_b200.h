@@ -308,6 +308,38 @@ void scb_shard_range(int32_t P, int32_t r, int32_t R, int32_t* lo, int32_t* hi);
 /* timing of the last call on device r's ctx */
 int scb_multi_get_timing(scb_multi* m, int32_t r, scb_timing* out);
 
+/* ---- toppra on a caller-supplied path (what the reference's toppra does beyond the one configuration gen_vel_prof<1>
+ * uses, as far as the six-row stage LP of the kernels reaches): a piecewise-cubic path of one or two degrees of freedom
+ * (PiecewisePolyPath, tp:geometric_path/piecewise_poly_path.cpp:215-252), box limits per degree of freedom, N + 1 =
+ * G gridpoints LinSpaced over the path interval, collocation or interpolation discretisation
+ * (tp:constraint.hpp:13-14), the reference's Seidel sequence operation for operation; controllable sets, forward
+ * pass (tp:algorithm.cpp:14-68, tp:algorithm/toppra.cpp:15-46) and feasible sets (computeFeasibleSets,
+ * tp:algorithm.cpp:70-103).  dof = 2 needs collocation, dof = 1 takes both (2 + 2 dof or 2 + 4 dof rows <= 6).
+ * This is the entry the reference's own known-answer vectors (cpp/tests/test_algorithm.cpp:64-165: 2-DOF, 3 segments,
+ * N = 50, collocation) reach a KERNEL through.  Always FP64; host pointers; outputs [G][P]. */
+typedef struct scb_ppoly_in {
+  int32_t P, n_seg, dof, G;
+  const double* coeffs;     /* [P][n_seg][4][dof]: row 0 multiplies (s - s_seg)^3, row 3 is the value */
+  const double* breaks;     /* [n_seg + 1], strictly increasing, shared by the batch */
+  const double* vel_lo;     /* [P][dof] */
+  const double* vel_hi;
+  const double* acc_lo;     /* [P][dof] */
+  const double* acc_hi;
+  int32_t interpolation;    /* 0: collocation, 1: interpolation (dof = 1 only) */
+  int32_t reserved0;
+  double sd_start, sd_end;  /* computePathParametrization(vel_start, vel_end) */
+  double x_cap;             /* 0 = the reference's 100 */
+} scb_ppoly_in;
+typedef struct scb_ppoly_out {
+  int32_t* status;          /* [P] toppra ReturnCode numbering (+ SCB_ST_ERR_BAD_LIMITS) */
+  int32_t* fail_stage;      /* [P] or NULL */
+  int32_t* feas_status;     /* [P] or NULL: SCB_ST_OK / SCB_ST_ERR_FAIL_FEASIBLE */
+  double* K_lo; double* K_hi;       /* [G][P] controllable sets */
+  double* x;                        /* [G][P] parametrization */
+  double* feas_lo; double* feas_hi; /* [G][P] or NULL: feasible sets */
+} scb_ppoly_out;
+int scb_toppra_ppoly(scb_ctx* ctx, const scb_ppoly_in* in, const scb_ppoly_out* out);
+
 /* ---- Global planner front end: FMT* over a shared set of sampled nodes, one CTA per query.
  * Replaces planning_space::fast_marching_trees (sc:1339-1407) with cost (sc:1315-1326), near (sc:1328-1337),
  * intersects (sc:142-178), for Q (x_init, x_goal) pairs over ONE map: the free-space samples

@@ -36,6 +36,7 @@ enum SlotId {
   SL_FMT_IN, SL_FMT_OUT,
   // obstacle-distance speed limit: curve points when the caller did not ask for them, capped per-gridpoint boxes
   SL_PX, SL_PY, SL_CAP_LO, SL_CAP_HI,
+  SL_PP_IN, SL_PP_OUT,  // scb_toppra_ppoly: one block of inputs, one of outputs
   // scb_plan_batch_summary: every output stays resident in HBM until the next such call; scb_fetch gathers from it
   SL_R_STATUS, SL_R_FAIL, SL_R_CTRL_X, SL_R_CTRL_Y, SL_R_L, SL_R_TABLE, SL_R_T_TOTAL, SL_R_COST, SL_R_K_LO, SL_R_K_HI,
   SL_R_X, SL_R_T, SL_R_PX, SL_R_PY, SL_R_V, SL_R_A, SL_R_OMEGA, SL_R_SUMMARY, SL_F_IDS, SL_F_STAGE,
@@ -974,6 +975,49 @@ int scb_fmt_batch(scb_ctx* ctx, const scb_fmt_in* in, const scb_fmt_out* out) {
   cudaEventElapsedTime(&t.total_ms, ctx->ev[0], ctx->ev[6]);
   t.launches = 1;
   ctx->timing_pending = false;
+  return SCB_OK;
+}
+
+// toppra on a caller-supplied piecewise-cubic path (toppra_kernel.cu: toppra_ppoly_kernel).  One H2D block, one launch,
+// one D2H block.
+int scb_toppra_ppoly(scb_ctx* ctx, const scb_ppoly_in* in, const scb_ppoly_out* out) {
+  if (!ctx || !in || !out) return SCB_E_INVALID;
+  const int P = in->P, ns = in->n_seg, m = in->dof, G = in->G;
+  if (P < 0 || ns < 1 || ns > 64 || G < 2 || (m != 1 && m != 2) || (m == 2 && in->interpolation)) return SCB_E_INVALID;
+  if (P == 0) return SCB_OK;
+  if (!in->coeffs || !in->breaks || !in->vel_lo || !in->vel_hi || !in->acc_lo || !in->acc_hi || !out->status || !out->K_lo || !out->K_hi)
+    return SCB_E_INVALID;
+  for (int k = 0; k < ns; ++k) if (!(in->breaks[k] < in->breaks[k + 1])) return SCB_E_INVALID;
+  SCB_CUDA(cudaSetDevice(ctx->cfg.device));
+  cudaStream_t st = ctx->stream;
+  const size_t nco = (size_t)P * ns * 4 * m, nl = (size_t)P * m, gp = (size_t)G * P;
+  const size_t n_in = nco + (ns + 1) + 4 * nl;
+  double* din; char* dout;
+  int rc;
+  if ((rc = ensure(ctx, SL_PP_IN, n_in * 8, (void**)&din))) return rc;
+  if ((rc = ensure(ctx, SL_PP_OUT, 5 * gp * 8 + 3 * (size_t)P * 4 + 64, (void**)&dout))) return rc;
+  scb::PpolyArgs a{};
+  a.P = P; a.n_seg = ns; a.dof = m; a.G = G; a.interpolation = in->interpolation;
+  a.sd_start = in->sd_start; a.sd_end = in->sd_end; a.x_cap = in->x_cap > 0 ? in->x_cap : 100.0;
+  double* q = din;
+  auto up = [&](const double* src, size_t n, const double** dst) -> cudaError_t { *dst = q; cudaError_t e = cudaMemcpyAsync(q, src, n * 8, cudaMemcpyHostToDevice, st); q += n; return e; };
+  SCB_CUDA(up(in->coeffs, nco, &a.coeffs)); SCB_CUDA(up(in->breaks, ns + 1, &a.breaks));
+  SCB_CUDA(up(in->vel_lo, nl, &a.vel_lo)); SCB_CUDA(up(in->vel_hi, nl, &a.vel_hi));
+  SCB_CUDA(up(in->acc_lo, nl, &a.acc_lo)); SCB_CUDA(up(in->acc_hi, nl, &a.acc_hi));
+  double* o = (double*)dout;
+  a.K_lo = o; a.K_hi = o + gp; a.x = o + 2 * gp;
+  a.feas_lo = (out->feas_lo || out->feas_hi) ? o + 3 * gp : nullptr; a.feas_hi = a.feas_lo ? o + 4 * gp : nullptr;
+  int32_t* oi = (int32_t*)(o + 5 * gp);
+  a.status = oi; a.fail_stage = oi + P; a.feas_status = oi + 2 * (size_t)P;
+  scb::launch_toppra_ppoly(a, st);
+  SCB_CUDA(cudaGetLastError());
+  auto down = [&](void* dst, const void* src, size_t bytes) -> cudaError_t { return dst ? cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, st) : cudaSuccess; };
+  SCB_CUDA(down(out->status, a.status, (size_t)P * 4)); SCB_CUDA(down(out->fail_stage, a.fail_stage, (size_t)P * 4));
+  SCB_CUDA(down(out->feas_status, a.feas_status, (size_t)P * 4));
+  SCB_CUDA(down(out->K_lo, a.K_lo, gp * 8)); SCB_CUDA(down(out->K_hi, a.K_hi, gp * 8)); SCB_CUDA(down(out->x, a.x, gp * 8));
+  if (a.feas_lo) { SCB_CUDA(down(out->feas_lo, a.feas_lo, gp * 8)); SCB_CUDA(down(out->feas_hi, a.feas_hi, gp * 8)); }
+  SCB_CUDA(cudaStreamSynchronize(st));
+  release_retired(ctx);
   return SCB_OK;
 }
 

@@ -188,6 +188,16 @@ struct FmtArgs {                       // fmt_kernel.cu; float whatever the ctx 
 size_t fmt_smem_bytes(int n);
 cudaError_t launch_fmt(const FmtArgs& a, cudaStream_t st);
 
+struct PpolyArgs {                     // toppra_kernel.cu: toppra on a caller-supplied piecewise-cubic path, FP64
+  int P, n_seg, dof, G, interpolation;
+  const double *coeffs, *breaks;       // [P][n_seg][4][dof], [n_seg + 1]
+  const double *vel_lo, *vel_hi, *acc_lo, *acc_hi;  // [P][dof]
+  double sd_start, sd_end, x_cap;
+  int32_t *status, *fail_stage, *feas_status;       // [P]
+  double *K_lo, *K_hi, *x, *feas_lo, *feas_hi;      // [G][P]; K_lo / K_hi are required (state of the forward pass)
+};
+void launch_toppra_ppoly(const PpolyArgs& a, cudaStream_t st);
+
 template <class R> void launch_path(const PathArgs& a, int spline_mode, cudaStream_t st, cudaEvent_t between = nullptr);
 template <class R> void launch_toppra(const ToppraArgs& a, cudaStream_t st);
 template <class R> void launch_toppra_fast(const ToppraArgs& a, cudaStream_t st);

@@ -273,6 +273,173 @@ __global__ void __launch_bounds__(64) toppra_kernel(ToppraArgs g) {
   g.fail_stage[p] = fail_stage;
 }
 
+// ---- toppra on a caller-supplied piecewise-cubic path with one or two degrees of freedom ------------------------------
+// (scb_toppra_ppoly).  The stage LP of toppra has 2 + 2 m rows with collocation and 2 + 4 m with interpolation
+// (tp:solver/seidel.cpp:204-263): six rows - the LP solve_lp2d6 above unrolls - for m = 2 with collocation, which is
+// the configuration of the reference's own known-answer test (cpp/tests/test_algorithm.cpp:64-165: 2-DOF, three cubic
+// segments, N = 50, Seidel), and for m = 1 with interpolation, gen_vel_prof's.  m = 1 with collocation has four rows
+// and is padded with the always-satisfied row (0, 0, -1) the reference itself uses for an absent coupling row
+// (seidel.cpp:298-303): such a row is skipped by the incremental loop and projects to a constant <= 0 in every 1-D
+// LP, so the optimum is that of the four-row problem bit for bit.  Besides the controllable sets and the forward pass
+// the kernel computes the feasible sets (computeFeasibleSets, tp:algorithm.cpp:70-103).  One thread per problem.
+struct PpolyPath {
+  const double* c;       // this problem's [nseg][4][dof]; row 0 multiplies ds^3 (piecewise_poly_path.cpp:215-226)
+  const double* breaks;  // [nseg + 1]
+  int nseg, dof;
+  // findSegmentIndex (piecewise_poly_path.cpp:240-252): upper_bound - 1, clamped
+  __device__ __forceinline__ int segment(double pos) const {
+    int idx = -1;
+    for (int k = 0; k <= nseg; ++k) if (breaks[k] <= pos) idx = k;  // last break <= pos  ==  upper_bound - 1
+    return idx < 0 ? 0 : (idx > nseg - 1 ? nseg - 1 : idx);
+  }
+  // first and second derivative of dof k at pos, in the reference's order of operations: coefficients differentiated
+  // row by row (computeDerivativesCoefficients, piecewise_poly_path.cpp:190-198), power form summed from the highest
+  // power down starting at 0 (eval_single; pow(ds, 2) == ds * ds, pow(ds, 1) == ds, pow(ds, 0) == 1 exactly)
+  __device__ __forceinline__ void d12(double pos, int k, double& q1, double& q2) const {
+    const int seg = segment(pos);
+    const double ds = pos - breaks[seg];
+    const double* cs = c + ((size_t)seg * 4) * dof + k;
+    const double c0 = cs[0], c1 = cs[dof], c2 = cs[2 * dof];
+    const double d1 = c0 * 3.0, d2 = c1 * 2.0, d3 = c2 * 1.0;
+    q1 = ((0.0 + d1 * (ds * ds)) + d2 * ds) + d3;
+    const double e2 = d1 * 2.0, e3 = d2 * 1.0;
+    q2 = (0.0 + e2 * ds) + e3;
+  }
+};
+
+__global__ void __launch_bounds__(64) toppra_ppoly_kernel(PpolyArgs g) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= g.P) return;
+  const int P = g.P, G = g.G, N = G - 1, m = g.dof;
+  PpolyPath path{g.coeffs + (size_t)p * g.n_seg * 4 * m, g.breaks, g.n_seg, m};
+  const double s0 = g.breaks[0], s1 = g.breaks[g.n_seg];
+  // Eigen's LinSpaced(G, s0, s1): low + i * step, the last point exactly high
+  const double step = (s1 - s0) / (double)N;
+  auto s_at = [&](int i) { return i >= N ? s1 : s0 + (double)i * step; };
+  double vlo[2], vhi[2], alo[2], ahi[2];
+  for (int k = 0; k < m; ++k) {
+    vlo[k] = g.vel_lo[(size_t)p * m + k]; vhi[k] = g.vel_hi[(size_t)p * m + k];
+    alo[k] = g.acc_lo[(size_t)p * m + k]; ahi[k] = g.acc_hi[(size_t)p * m + k];
+  }
+  const bool interp = g.interpolation != 0;
+  int status = SCB_ST_OK, fail_stage = -1;
+  // x-box of gridpoint i from the velocity limits (linear_joint_velocity.cpp:24-61, all dofs)
+  auto xbox = [&](int i, double& xlo, double& xhi) -> bool {
+    const double s = s_at(i);
+    double sdmin = -tol::maxsd, sdmax = tol::maxsd;
+    bool ok = true;
+    for (int k = 0; k < m; ++k) {
+      double v, vv;
+      path.d12(s, k, v, vv);
+      const double vinv = 1.0 / v;
+      if (v > 0) { sdmax = fmin(vhi[k] * vinv, sdmax); sdmin = fmax(vlo[k] * vinv, sdmin); }
+      else if (v < 0) { sdmax = fmin(vlo[k] * vinv, sdmax); sdmin = fmax(vhi[k] * vinv, sdmin); }
+      else if (vhi[k] < 0 || vlo[k] > 0) ok = false;
+    }
+    xlo = sdmin > 0 ? sdmin * sdmin : 0.0;
+    xhi = sdmax * sdmax;
+    return ok;
+  };
+  // rows 2..5 of stage i (constraint.cpp:100-162, 185-204; linear_joint_acceleration.cpp:22-49; seidel.cpp:228-239):
+  // F = [I; -I] per block, g = [acc_hi; -acc_lo]; interpolation appends the block of gridpoint i + 1
+  auto rows = [&](int i, double (&A)[6][3], double& delta) {
+    const double s = s_at(i), sn = s_at(i + 1 > N ? N : i + 1);
+    delta = sn - s;
+    int r = 2;
+    double a[2], b[2];
+    for (int k = 0; k < m; ++k) path.d12(s, k, a[k], b[k]);
+    for (int k = 0; k < m; ++k) { A[r][0] = a[k]; A[r][1] = b[k]; A[r][2] = -ahi[k]; ++r; }
+    for (int k = 0; k < m; ++k) { A[r][0] = -a[k]; A[r][1] = -b[k]; A[r][2] = alo[k]; ++r; }
+    if (interp) {  // m == 1
+      double an, bn, a2, b2;
+      if (i < N) { path.d12(sn, 0, an, bn); a2 = an + 2 * delta * bn; b2 = bn; }
+      else { a2 = a[0]; b2 = b[0]; }
+      A[r][0] = a2; A[r][1] = b2; A[r][2] = -ahi[0]; ++r;
+      A[r][0] = -a2; A[r][1] = -b2; A[r][2] = alo[0]; ++r;
+    }
+    for (; r < 6; ++r) { A[r][0] = 0; A[r][1] = 0; A[r][2] = -1; }  // m = 1 with collocation: padding
+  };
+  auto couple = [&](double (&A)[6][3], int i, double delta, double nlo, double nhi) {
+    if (i >= N || nlo <= -kInf) { A[0][0] = 0; A[0][1] = 0; A[0][2] = -1; }
+    else { A[0][0] = -2.0 * delta; A[0][1] = -1; A[0][2] = nlo; }
+    if (i >= N || nhi >= kInf) { A[1][0] = 0; A[1][1] = 0; A[1][2] = -1; }
+    else { A[1][0] = 2.0 * delta; A[1][1] = 1; A[1][2] = -nhi; }
+  };
+  auto put = [&](double* lo, double* hi, int i, double a, double b) {
+    if (lo) lo[(size_t)i * P + p] = a;
+    if (hi) hi[(size_t)i * P + p] = b;
+  };
+  for (int i = 0; i < G && status == SCB_ST_OK; ++i) {
+    double xl, xh;
+    if (!xbox(i, xl, xh)) status = SCB_ST_ERR_BAD_LIMITS;
+  }
+  for (int k = 0; k < m; ++k) if (!(alo[k] <= ahi[k]) || vlo[k] != vlo[k] || vhi[k] != vhi[k]) status = SCB_ST_ERR_BAD_LIMITS;
+  // ---- controllable sets (algorithm.cpp:28-68)
+  const double xe = g.sd_end * g.sd_end;
+  double nlo = xe, nhi = xe;
+  put(g.K_lo, g.K_hi, N, nlo, nhi);
+  int i = N - 1;
+  if (status == SCB_ST_OK) {
+    for (; i >= 0; --i) {
+      double A[6][3], xlo, xhi, delta;
+      rows(i, A, delta);
+      xbox(i, xlo, xhi);
+      couple(A, i, delta, nlo, nhi);
+      const double lo1 = fmax(xlo, 0.0), hi1 = fmin(xhi, g.x_cap);
+      double u, xu, xl;
+      if (!solve_lp2d6(-tol::tie, 1.0, A, lo1, hi1, u, xu)) { status = SCB_ST_ERR_FAIL_CONTROLLABLE; fail_stage = i; break; }
+      if (!solve_lp2d6(tol::tie, -1.0, A, lo1, hi1, u, xl)) { status = SCB_ST_ERR_FAIL_CONTROLLABLE; fail_stage = i; put(g.K_lo, g.K_hi, i, 0.0, xu); --i; break; }
+      nhi = xu; nlo = fmax(0.0, xl);
+      put(g.K_lo, g.K_hi, i, nlo, nhi);
+    }
+  }
+  for (; i >= 0; --i) put(g.K_lo, g.K_hi, i, 0.0, 0.0);
+  // ---- forward pass (toppra.cpp:15-46); parametrization(0) = sd_start, not squared (l.23)
+  double xi = g.sd_start;
+  if (g.x) g.x[p] = xi;
+  i = 0;
+  if (status == SCB_ST_OK) {
+    for (; i < N; ++i) {
+      double A[6][3], xlo, xhi, delta;
+      rows(i, A, delta);
+      xbox(i, xlo, xhi);
+      const double klo = g.K_lo[(size_t)(i + 1) * P + p], khi = g.K_hi[(size_t)(i + 1) * P + p];
+      couple(A, i, delta, klo, khi);
+      const double lo1 = fmax(xlo, xi), hi1 = fmin(xhi, xi);
+      double u, xx;
+      if (!solve_lp2d6(2.0 * delta, 1.0, A, lo1, hi1, u, xx)) { status = SCB_ST_ERR_FAIL_FORWARD_PASS; fail_stage = i; break; }
+      xi = fmin(khi, fmax(klo, xi + 2.0 * delta * u));
+      if (g.x) g.x[(size_t)(i + 1) * P + p] = xi;
+    }
+  }
+  if (g.x) for (++i; i <= N; ++i) g.x[(size_t)i * P + p] = 0;
+  // ---- feasible sets (algorithm.cpp:70-103): every stage against the whole box [0, 100] on both sides
+  int feas_status = SCB_ST_OK;
+  if (g.feas_lo || g.feas_hi) {
+    for (int j = 0; j <= N; ++j) {
+      double A[6][3], xlo, xhi, delta, u, xu = 0, xl = 0;
+      bool ok = status != SCB_ST_ERR_BAD_LIMITS && feas_status == SCB_ST_OK;
+      if (ok) {
+        rows(j, A, delta);
+        xbox(j, xlo, xhi);
+        couple(A, j, delta, 0.0, 100.0);
+        const double lo1 = fmax(xlo, 0.0), hi1 = fmin(xhi, 100.0);
+        ok = solve_lp2d6(-tol::tie, 1.0, A, lo1, hi1, u, xu) && solve_lp2d6(tol::tie, -1.0, A, lo1, hi1, u, xl);
+        if (!ok) feas_status = SCB_ST_ERR_FAIL_FEASIBLE;
+      }
+      put(g.feas_lo, g.feas_hi, j, ok ? xl : 0.0, ok ? xu : 0.0);
+    }
+  }
+  g.status[p] = status;
+  if (g.fail_stage) g.fail_stage[p] = fail_stage;
+  if (g.feas_status) g.feas_status[p] = feas_status;
+}
+
+void launch_toppra_ppoly(const PpolyArgs& a, cudaStream_t st) {
+  const int block = 64;
+  toppra_ppoly_kernel<<<(a.P + block - 1) / block, block, 0, st>>>(a);
+}
+
 template <class S> void launch_toppra(const ToppraArgs& a, cudaStream_t st) {
   const int block = 64;
   toppra_kernel<S><<<(a.P + block - 1) / block, block, 0, st>>>(a);

@@ -75,6 +75,18 @@ class ScbFmtIn(C.Structure):
                 ("rn", C.c_float), ("reserved0", C.c_int32)]
 
 
+class ScbPpolyIn(C.Structure):
+    _fields_ = [("P", C.c_int32), ("n_seg", C.c_int32), ("dof", C.c_int32), ("G", C.c_int32),
+                ("coeffs", C.c_void_p), ("breaks", C.c_void_p), ("vel_lo", C.c_void_p), ("vel_hi", C.c_void_p),
+                ("acc_lo", C.c_void_p), ("acc_hi", C.c_void_p), ("interpolation", C.c_int32), ("reserved0", C.c_int32),
+                ("sd_start", C.c_double), ("sd_end", C.c_double), ("x_cap", C.c_double)]
+
+
+class ScbPpolyOut(C.Structure):
+    _fields_ = [("status", C.c_void_p), ("fail_stage", C.c_void_p), ("feas_status", C.c_void_p),
+                ("K_lo", C.c_void_p), ("K_hi", C.c_void_p), ("x", C.c_void_p), ("feas_lo", C.c_void_p), ("feas_hi", C.c_void_p)]
+
+
 class ScbFmtOut(C.Structure):
     _fields_ = [("status", C.c_void_p), ("path_len", C.c_void_p), ("closed", C.c_void_p),
                 ("path_x", C.c_void_p), ("path_y", C.c_void_p), ("cost", C.c_void_p)]
@@ -105,6 +117,7 @@ SYMBOLS = {
     "scb_multi_get_timing": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(ScbTiming)]),
     "scb_set_host_chunk": (C.c_int, [C.c_void_p, C.c_int32]),
     "scb_fmt_batch": (C.c_int, [C.c_void_p, C.POINTER(ScbFmtIn), C.POINTER(ScbFmtOut)]),
+    "scb_toppra_ppoly": (C.c_int, [C.c_void_p, C.POINTER(ScbPpolyIn), C.POINTER(ScbPpolyOut)]),
     "scb_alloc_pinned": (C.c_void_p, [C.c_size_t]),
     "scb_free_pinned": (None, [C.c_void_p]),
     "scb_get_timing": (C.c_int, [C.c_void_p, C.POINTER(ScbTiming)]),

@@ -125,6 +125,27 @@ class BatchPlanner:
         self._check(self.lib.scb_fmt_batch(self.ctx, C.byref(fi), C.byref(fo)), "scb_fmt_batch")
         return res
 
+    # ------------------------------------------------------------------ toppra on a caller-supplied path
+    def toppra_ppoly(self, coeffs, breaks, G, vel_lo, vel_hi, acc_lo, acc_hi, interpolation=0, sd_start=0.0, sd_end=0.0, x_cap=0.0,
+                     feasible=True):
+        """scb_toppra_ppoly: coeffs [P][n_seg][4][dof] (row 0 multiplies ds^3), breaks [n_seg + 1], limits [P][dof]."""
+        d = lambda a: np.ascontiguousarray(a, dtype=np.float64)
+        coeffs = d(coeffs); P, ns, _, m = coeffs.shape
+        keep = [coeffs, d(breaks)] + [d(np.broadcast_to(d(a), (P, m))) for a in (vel_lo, vel_hi, acc_lo, acc_hi)]
+        pi = abi.ScbPpolyIn()
+        pi.P, pi.n_seg, pi.dof, pi.G = P, ns, m, G
+        pi.coeffs, pi.breaks, pi.vel_lo, pi.vel_hi, pi.acc_lo, pi.acc_hi = (a.ctypes.data for a in keep)
+        pi.interpolation, pi.sd_start, pi.sd_end, pi.x_cap = int(interpolation), sd_start, sd_end, x_cap
+        res = BatchResult(status=np.empty(P, np.int32), fail_stage=np.empty(P, np.int32), feas_status=np.empty(P, np.int32),
+                          K_lo=np.empty((G, P)), K_hi=np.empty((G, P)), x=np.empty((G, P)))
+        if feasible:
+            res["feas_lo"] = np.empty((G, P)); res["feas_hi"] = np.empty((G, P))
+        po = abi.ScbPpolyOut()
+        for k, v in res.items():
+            setattr(po, k, v.ctypes.data)
+        self._check(self.lib.scb_toppra_ppoly(self.ctx, C.byref(pi), C.byref(po)), "scb_toppra_ppoly")
+        return res
+
     # ------------------------------------------------------------------ host buffers
     def plan(self, wx=None, wy=None, vel_lo=None, vel_hi=None, acc_lo=None, acc_hi=None, G=101, start_angle=None,
              vel_lo_grid=None, vel_hi_grid=None, vel_start=None, vel_end=None, path_len=None, stages=0,
