@@ -174,6 +174,21 @@ __device__ __noinline__ bool segment_hits(double wx, double wy, const double (&d
     const float mx = 1e-6f * (float)(bx - ax) + 1e-30f, my = 1e-6f * (float)(by - ay) + 1e-30f;
     xlo = __double2float_rd(ax) - mx; xhi = __double2float_ru(bx) + mx; ylo = __double2float_rd(ay) - my; yhi = __double2float_ru(by) + my;
   }
+  // candidate edges: those whose box meets the hull's (bit mask over the staged edges)
+  unsigned cand[kCollSmem / 32];
+  unsigned any = 0;
+#pragma unroll
+  for (int w = 0; w < kCollSmem / 32; ++w) {
+    unsigned m = 0;
+    const int e0 = 32 * w, e1 = ce.ns < e0 + 32 ? ce.ns : e0 + 32;
+    for (int e = e0; e < e1; ++e) {
+      const float4 b = ((const float4*)ce.box)[e];
+      if (!(b.x > xhi || b.y < xlo || b.z > yhi || b.w < ylo)) m |= 1u << (e - e0);
+    }
+    cand[w] = m; any |= m;
+  }
+  const bool tail = ce.n > ce.ns;  // an edge list longer than the stage: the rest is walked from global memory
+  if (!any && !tail) return false;
   // power basis of the segment: B(u) = W + u (c0 + u (c1/2 + u (c2/3 + u (c3/4 + u c4/5))))
   double cx[5], cy[5];
   hodograph_power(dx[0], dx[1], dx[2], dx[3], dx[4], cx);
@@ -182,29 +197,37 @@ __device__ __noinline__ bool segment_hits(double wx, double wy, const double (&d
   const double qy1 = 0.5 * cy[1], qy2 = cy[2] * (1.0 / 3.0), qy3 = 0.25 * cy[3], qy4 = 0.2 * cy[4];
   const double invM = 1.0 / (double)M;
   const S* ge = (const S*)ce.g;
-  for (int e = 0; e < ce.n; ++e) {
-    double e0x, e0y, e1x, e1y;
-    float bxl, bxh, byl, byh;
-    if (e < ce.ns) {
-      bxl = ce.box[4 * e]; bxh = ce.box[4 * e + 1]; byl = ce.box[4 * e + 2]; byh = ce.box[4 * e + 3];
-      if (bxl > xhi || bxh < xlo || byl > yhi || byh < ylo) continue;
-      e0x = ce.e[4 * e]; e0y = ce.e[4 * e + 1]; e1x = ce.e[4 * e + 2]; e1y = ce.e[4 * e + 3];
-    } else {
-      e0x = (double)ge[4 * e]; e0y = (double)ge[4 * e + 1]; e1x = (double)ge[4 * e + 2]; e1y = (double)ge[4 * e + 3];
-      if (fmin(e0x, e1x) > (double)xhi || fmax(e0x, e1x) < (double)xlo || fmin(e0y, e1y) > (double)yhi || fmax(e0y, e1y) < (double)ylo) continue;
+  double ax = wx, ay = wy;
+  float fax = (float)wx, fay = (float)wy;
+  for (int k = 1; k <= M; ++k) {  // every chord point is formed once; the candidates are tested chord by chord
+    const double u = k == M ? 1.0 : (double)k * invM;
+    const double qx = fma(u, fma(u, fma(u, fma(u, fma(u, qx4, qx3), qx2), qx1), cx[0]), wx);
+    const double qy = fma(u, fma(u, fma(u, fma(u, fma(u, qy4, qy3), qy2), qy1), cy[0]), wy);
+    const float fqx = (float)qx, fqy = (float)qy;
+    // float box of the chord, widened by two float ulps of its coordinates (the conversions round to nearest)
+    const float gx = 2.4e-7f * fmaxf(fabsf(fax), fabsf(fqx)) + 1e-30f, gy = 2.4e-7f * fmaxf(fabsf(fay), fabsf(fqy)) + 1e-30f;
+    const float cxl = fminf(fax, fqx) - gx, cxh = fmaxf(fax, fqx) + gx, cyl = fminf(fay, fqy) - gy, cyh = fmaxf(fay, fqy) + gy;
+#pragma unroll
+    for (int w = 0; w < kCollSmem / 32; ++w) {
+      unsigned m = cand[w];
+      while (m) {
+        const int e = 32 * w + __ffs(m) - 1;
+        m &= m - 1;
+        const float4 b = ((const float4*)ce.box)[e];
+        if (b.x > cxh || b.y < cxl || b.z > cyh || b.w < cyl) continue;
+        double ix, iy;
+        if (seg_intersects<double>(ax, ay, qx, qy, ce.e[4 * e], ce.e[4 * e + 1], ce.e[4 * e + 2], ce.e[4 * e + 3], ix, iy)) return true;
+      }
     }
-    const double exl = fmin(e0x, e1x), exh = fmax(e0x, e1x), eyl = fmin(e0y, e1y), eyh = fmax(e0y, e1y);
-    double ax = wx, ay = wy;
-    for (int k = 1; k <= M; ++k) {
-      const double u = k == M ? 1.0 : (double)k * invM;
-      const double qx = fma(u, fma(u, fma(u, fma(u, fma(u, qx4, qx3), qx2), qx1), cx[0]), wx);
-      const double qy = fma(u, fma(u, fma(u, fma(u, fma(u, qy4, qy3), qy2), qy1), cy[0]), wy);
-      if (!(exl > fmax(ax, qx) || exh < fmin(ax, qx) || eyl > fmax(ay, qy) || eyh < fmin(ay, qy))) {
+    if (tail) {
+      for (int e = ce.ns; e < ce.n; ++e) {
+        const double e0x = (double)ge[4 * e], e0y = (double)ge[4 * e + 1], e1x = (double)ge[4 * e + 2], e1y = (double)ge[4 * e + 3];
+        if (fmin(e0x, e1x) > fmax(ax, qx) || fmax(e0x, e1x) < fmin(ax, qx) || fmin(e0y, e1y) > fmax(ay, qy) || fmax(e0y, e1y) < fmin(ay, qy)) continue;
         double ix, iy;
         if (seg_intersects<double>(ax, ay, qx, qy, e0x, e0y, e1x, e1y, ix, iy)) return true;
       }
-      ax = qx; ay = qy;
     }
+    ax = qx; ay = qy; fax = fqx; fay = fqy;
   }
   return false;
 }

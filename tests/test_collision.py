@@ -148,7 +148,8 @@ def test_gpu_verdicts_match_oracle(planners, oracle, mode, W, P):
     np.testing.assert_array_equal(got["status"], ref["status"])
     hit = ref["status"] == COLLISION
     ok = ref["status"] == 0
-    assert hit.sum() >= P // 8 and ok.sum() >= P // 2
+    # the cubic has no optimiser: what collides stays colliding; the quintic's optimiser steers most candidates clear
+    assert hit.sum() >= (P // 8 if mode == "ref_cubic" else 2) and ok.sum() >= P // 2
     assert np.all(np.isinf(got["cost"][hit])) and np.all(got["T_total"][hit] == 0)
     np.testing.assert_allclose(got["T_total"][ok], ref["T_total"][ok], rtol=1e-9)
     np.testing.assert_allclose(got["arclen_total"][ok], ref["arclen_total"][ok], rtol=1e-9)
