@@ -18,7 +18,8 @@ No modelled slack is used for them:
     scheme: the end-to-end difference in a was 40x what 32-ulp input perturbations explain, all of it inherited from x).
     param_stage_check() therefore feeds the KERNEL's own x and L to the oracle's parametrizer (tp:parametrizer/
     spline.cpp:10-45 restated) and compares t, v, a with rtol * max(|want|, 1e-3 scale) + SPREAD_FACTOR * the
-    parametrizer's measured spread under PROBE_ULPS-ulp perturbations of x (per problem, its maximum over the knots).
+    parametrizer's measured spread under PROBE_ULPS-ulp perturbations of its data - x and the gridpoints s_i, whose
+    knot values q(s_i) enter through differences that cancel ~L / dq digits (per problem, the maximum over the knots).
 Everything else (x, K, t, px, py, control points, tables,
 L, T, J) gets NO such term: tests/test_tolerances.py shows on the CPU that they move by < 1e-10 relative.
 """
@@ -87,11 +88,11 @@ def param_stage_check(oracle, res, ref, rtol, kw, names=("t", "v", "a"), max_pro
         c0 = ve - 2.0 * L + vs
         coeffs = np.array([c0, (ve - vs - 3.0 * c0) / 2.0, vs, 0.0]).reshape(1, 4, 1)
 
-        def param(x):
-            ts, _, _, _ = oracle.spline_param(coeffs, [0.0, 1.0], gp, x, solve_mode=1)
+        def param(x, g=gp):
+            ts, _, _, _ = oracle.spline_param(coeffs, [0.0, 1.0], g, x, solve_mode=1)
             if len(ts) != G:
                 return None
-            _, _, qd, qdd = oracle.spline_param(coeffs, [0.0, 1.0], gp, x, solve_mode=1, t_eval=ts)
+            _, _, qd, qdd = oracle.spline_param(coeffs, [0.0, 1.0], g, x, solve_mode=1, t_eval=ts)
             return {"t": ts, "v": qd[:, 0], "a": qdd[:, 0]}
         x = np.ascontiguousarray(res["x"][:, p], dtype=np.float64)
         want = param(x)
@@ -99,7 +100,11 @@ def param_stage_check(oracle, res, ref, rtol, kw, names=("t", "v", "a"), max_pro
             continue
         spread = {n: 0.0 for n in names}
         for _ in range(2):
-            pr = param(x * (1.0 + d * rng.choice([-1.0, 1.0], size=G)))
+            # the stage's data are x AND the gridpoints s_i = i / N (whose last bit depends on how LinSpaced is rounded,
+            # SURVEY 8-C5): the knot values q(s_i) enter through differences q_i - q_{i-1} that cancel ~L/dq digits
+            gpp = gp * (1.0 + d * rng.choice([-1.0, 1.0], size=G))
+            gpp[0], gpp[-1] = 0.0, 1.0
+            pr = param(x * (1.0 + d * rng.choice([-1.0, 1.0], size=G)), gpp)
             if pr is not None:
                 for n in names:
                     spread[n] = max(spread[n], float(np.max(np.abs(pr[n] - want[n]))))
