@@ -143,12 +143,13 @@ constexpr int kCollSmem = 128;
 struct CollEdges {
   const double* e;   // [n][4] in shared memory (first kCollSmem edges)
   const float* box;  // [n][4] = (xlo, xhi, ylo, yhi), rounded outwards
+  const float* ef;   // [n][4] = the end points as floats (oriented-box cull)
   int ns, n;         // staged / all
   const void* g;     // all edges in global memory, storage type S
 };
 
 template <class S>
-__device__ __forceinline__ void stage_coll_edges(const PathArgs& g, double* se, float* sb, int tid, int T) {
+__device__ __forceinline__ void stage_coll_edges(const PathArgs& g, double* se, float* sb, float* sf, int tid, int T) {
   const int ns = g.n_coll_edges < kCollSmem ? g.n_coll_edges : kCollSmem;
   const S* ge = (const S*)g.coll_edges;
   for (int k = tid; k < ns; k += T) {
@@ -156,23 +157,44 @@ __device__ __forceinline__ void stage_coll_edges(const PathArgs& g, double* se, 
     se[4 * k] = x0; se[4 * k + 1] = y0; se[4 * k + 2] = x1; se[4 * k + 3] = y1;
     sb[4 * k] = __double2float_rd(fmin(x0, x1)); sb[4 * k + 1] = __double2float_ru(fmax(x0, x1));
     sb[4 * k + 2] = __double2float_rd(fmin(y0, y1)); sb[4 * k + 3] = __double2float_ru(fmax(y0, y1));
+    sf[4 * k] = (float)x0; sf[4 * k + 1] = (float)y0; sf[4 * k + 2] = (float)x1; sf[4 * k + 3] = (float)y1;
   }
 }
 
 template <class S>
 __device__ __noinline__ bool segment_hits(double wx, double wy, const double (&dx)[5], const double (&dy)[5], const CollEdges& ce, int M) {
-  // control polygon -> float box of the hull
-  float xlo, xhi, ylo, yhi;
+  // control polygon -> float box of the hull, and the hull's box in the frame of the segment's chord W_i -> W_i+1:
+  // s = n . (P - W) across the chord (n = the chord turned by 90 degrees, not normalised), a = d . (P - W) along it.
+  // A wall beside a diagonal leg lies inside the axis-aligned box but outside the oriented one.
+  float xlo, xhi, ylo, yhi, slo, shi, alo, ahi;
+  float fwx, fwy, fdx, fdy;
   {
-    double px = wx, py = wy, ax = wx, bx = wx, ay = wy, by = wy;
+    double rx[5], ry[5];
+    double px = 0, py = 0, ax = 0, bx = 0, ay = 0, by = 0;
 #pragma unroll
     for (int j = 0; j < 5; ++j) {
       px = fma(0.2, dx[j], px); py = fma(0.2, dy[j], py);
+      rx[j] = px; ry[j] = py;
       ax = fmin(ax, px); bx = fmax(bx, px); ay = fmin(ay, py); by = fmax(by, py);
     }
     // the chord points below come from the power basis: a hair outside the hull by rounding; widen by 1e-6 of its size
     const float mx = 1e-6f * (float)(bx - ax) + 1e-30f, my = 1e-6f * (float)(by - ay) + 1e-30f;
-    xlo = __double2float_rd(ax) - mx; xhi = __double2float_ru(bx) + mx; ylo = __double2float_rd(ay) - my; yhi = __double2float_ru(by) + my;
+    xlo = __double2float_rd(wx + ax) - mx; xhi = __double2float_ru(wx + bx) + mx;
+    ylo = __double2float_rd(wy + ay) - my; yhi = __double2float_ru(wy + by) + my;
+    const double cdx = rx[4], cdy = ry[4];  // the chord
+    double s0 = 0, s1 = 0, a0 = 0, a1 = 0;
+#pragma unroll
+    for (int j = 0; j < 5; ++j) {
+      const double sj = fma(cdx, ry[j], -(cdy * rx[j])), aj = fma(cdx, rx[j], cdy * ry[j]);
+      s0 = fmin(s0, sj); s1 = fmax(s1, sj); a0 = fmin(a0, aj); a1 = fmax(a1, aj);
+    }
+    fwx = (float)wx; fwy = (float)wy; fdx = (float)cdx; fdy = (float)cdy;
+    // float evaluation of the edge side: coordinates rounded to float (rel. 6e-8 each), two products summed; the margin
+    // is 16 float ulps of the largest term that can occur, |d| (|W| + |edge|) - far more than the rounding, far less
+    // than a millimetre for paths of a few hundred metres
+    const float big = (fabsf(fdx) + fabsf(fdy)) * (fabsf(fwx) + fabsf(fwy) + (float)(bx - ax) + (float)(by - ay) + 1.0f);
+    const float mg = 1e-6f * big + 1e-30f;
+    slo = __double2float_rd(s0) - mg; shi = __double2float_ru(s1) + mg; alo = __double2float_rd(a0) - mg; ahi = __double2float_ru(a1) + mg;
   }
   // candidate edges: those whose box meets the hull's (bit mask over the staged edges)
   unsigned cand[kCollSmem / 32];
@@ -183,7 +205,15 @@ __device__ __noinline__ bool segment_hits(double wx, double wy, const double (&d
     const int e0 = 32 * w, e1 = ce.ns < e0 + 32 ? ce.ns : e0 + 32;
     for (int e = e0; e < e1; ++e) {
       const float4 b = ((const float4*)ce.box)[e];
-      if (!(b.x > xhi || b.y < xlo || b.z > yhi || b.w < ylo)) m |= 1u << (e - e0);
+      if (b.x > xhi || b.y < xlo || b.z > yhi || b.w < ylo) continue;
+      const float4 q = ((const float4*)ce.ef)[e];
+      const float r0x = q.x - fwx, r0y = q.y - fwy, r1x = q.z - fwx, r1y = q.w - fwy;
+      const float mgs = 1e-6f * (fabsf(fdx) + fabsf(fdy)) * (fabsf(q.x) + fabsf(q.y) + fabsf(q.z) + fabsf(q.w));  // the edge's own size
+      const float n0 = fdx * r0y - fdy * r0x, n1 = fdx * r1y - fdy * r1x;
+      if (fmaxf(n0, n1) < slo - mgs || fminf(n0, n1) > shi + mgs) continue;  // the whole edge on one side of the hull
+      const float t0 = fdx * r0x + fdy * r0y, t1 = fdx * r1x + fdy * r1y;
+      if (fmaxf(t0, t1) < alo - mgs || fminf(t0, t1) > ahi + mgs) continue;  // ... or before / beyond it
+      m |= 1u << (e - e0);
     }
     cand[w] = m; any |= m;
   }
@@ -546,13 +576,14 @@ __global__ void __launch_bounds__(kLaneWarps * 32, 4) path_lane_kernel(PathArgs 
   WarpComm cm;
   cm.base = pl * W; cm.W = W; cm.sstride = 32;
   cm.st = (double*)lane_smem_raw + (size_t)warp * kLaneSlots * 32 + lane;
-  CollEdges ce{nullptr, nullptr, 0, 0, nullptr};
+  CollEdges ce{nullptr, nullptr, nullptr, 0, 0, nullptr};
   if constexpr (COLL) {  // every thread reaches the barrier (no early return above)
     double* se = (double*)lane_smem_raw + (size_t)kLaneWarps * kLaneSlots * 32;
     float* sb = (float*)(se + 4 * kCollSmem);
-    stage_coll_edges<S>(g, se, sb, threadIdx.x, kLaneWarps * 32);
+    float* sf = sb + 4 * kCollSmem;
+    stage_coll_edges<S>(g, se, sb, sf, threadIdx.x, kLaneWarps * 32);
     __syncthreads();
-    ce = CollEdges{se, sb, g.n_coll_edges < kCollSmem ? g.n_coll_edges : kCollSmem, g.n_coll_edges, g.coll_edges};
+    ce = CollEdges{se, sb, sf, g.n_coll_edges < kCollSmem ? g.n_coll_edges : kCollSmem, g.n_coll_edges, g.coll_edges};
   }
   if (p0 >= P) return;  // the whole warp leaves together
   lane_path<S, DEG, WarpComm, COLL>(g, cm, p, i, pl < PB && p < P, ce);
@@ -568,20 +599,21 @@ __global__ void __launch_bounds__(512, 1) path_lane_cta_kernel(PathArgs g) {
   cm.xbuf = (double*)lane_smem_raw;
   cm.red = cm.xbuf + (size_t)2 * CtaComm::kMaxVals * T;
   cm.st = cm.red + 128 + tid;
-  CollEdges ce{nullptr, nullptr, 0, 0, nullptr};
+  CollEdges ce{nullptr, nullptr, nullptr, 0, 0, nullptr};
   if constexpr (COLL) {
     double* se = cm.red + 128 + (size_t)kLaneSlots * T;
     float* sb = (float*)(se + 4 * kCollSmem);
-    stage_coll_edges<S>(g, se, sb, tid, T);
+    float* sf = sb + 4 * kCollSmem;
+    stage_coll_edges<S>(g, se, sb, sf, tid, T);
     __syncthreads();
-    ce = CollEdges{se, sb, g.n_coll_edges < kCollSmem ? g.n_coll_edges : kCollSmem, g.n_coll_edges, g.coll_edges};
+    ce = CollEdges{se, sb, sf, g.n_coll_edges < kCollSmem ? g.n_coll_edges : kCollSmem, g.n_coll_edges, g.coll_edges};
   }
   lane_path<S, DEG, CtaComm, COLL>(g, cm, blockIdx.x, tid, tid < g.W, ce);
 }
 
 bool path_lane_shape(int W, int& PB, size_t& smem, int spline_mode) {
   if (W < 2 || W > 512) return false;
-  const size_t coll = spline_mode == SCB_REF_CUBIC ? 0 : (size_t)kCollSmem * (4 * sizeof(double) + 4 * sizeof(float));  // staged edges
+  const size_t coll = spline_mode == SCB_REF_CUBIC ? 0 : (size_t)kCollSmem * (4 * sizeof(double) + 8 * sizeof(float));  // staged edges
   if (W <= 32) {
     PB = 32 / W;
     smem = spline_mode == SCB_REF_CUBIC ? 0 : (size_t)kLaneWarps * kLaneSlots * 32 * sizeof(double) + coll;
