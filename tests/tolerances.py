@@ -179,4 +179,10 @@ def check(res, ref, rtol, names, spread):
             g, w = res[n][ok], ref[n][ok]
             tol = rtol * np.maximum(np.abs(w), 1e-3 * np.abs(w).max(axis=1, keepdims=True)) + 1e-300
         bad = np.abs(g - w) > tol
-        assert not bad.any(), (n, float(np.max(np.abs(g - w) / tol)), int(bad.sum()))
+        if bad.any():  # say where: the worst offenders with what the tolerance was made of
+            r = np.abs(g - w) / tol
+            worst = [tuple(int(k) for k in np.unravel_index(j, r.shape)) for j in np.argsort(r, axis=None)[::-1][:4]]
+            detail = [(ix, float(g[ix]), float(w[ix]), float(tol[ix]) if np.ndim(tol) else float(tol),
+                       float(spread[n][:, ok][ix]) if n in spread and n in GRID else None,
+                       float(sc[n][ix[-1]]) if n in sc else None) for ix in worst]
+            raise AssertionError((n, float(r.max()), int(bad.sum()), "worst (index, got, want, tol, spread, scale):", detail))
