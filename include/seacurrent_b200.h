@@ -77,7 +77,7 @@ enum {
 /* SCB_FP32 is a STORAGE mode, not a faster compute mode: every `real` buffer (inputs, outputs, tables) is float and the
  * arc-length / geometry kernels compute in float; the stages that take decisions - toppra's passes (tolerances 1e-13 /
  * 1e-10 / 1e-9), the parametrizer recurrences and the sign-driven optimiser - compute in FP64 in both modes.  Parity:
- * 1e-4 of the oracle.  For float RECORDS with FP64 arithmetic use SCB_FP64 + scb_batch_out.record_f32. */
+ * 1e-4 of the FP64 results.  For float RECORDS with FP64 arithmetic use SCB_FP64 + scb_batch_out.record_f32. */
 enum { SCB_FP64 = 0, SCB_FP32 = 1 };
 enum { SCB_REF_CUBIC = 0,    /* the reference's construction, sc:599-683 */
        SCB_LAU_QUINTIC = 1 };/* Lau et al. IROS'09 sec. III-A quintic + optimiser */

@@ -161,8 +161,9 @@ __device__ __forceinline__ void stage_coll_edges(const PathArgs& g, double* se, 
   }
 }
 
-template <class S>
-__device__ __noinline__ bool segment_hits(double wx, double wy, const double (&dx)[5], const double (&dy)[5], const CollEdges& ce, int M) {
+// NW: 32-edge words of the candidate mask (1 when the staged list has at most 32 edges: the common case walks one word)
+template <class S, int NW>
+__device__ __noinline__ bool segment_hits_nw(double wx, double wy, const double (&dx)[5], const double (&dy)[5], const CollEdges& ce, int M) {
   // control polygon -> float box of the hull, and the hull's box in the frame of the segment's chord W_i -> W_i+1:
   // s = n . (P - W) across the chord (n = the chord turned by 90 degrees, not normalised), a = d . (P - W) along it.
   // A wall beside a diagonal leg lies inside the axis-aligned box but outside the oriented one.
@@ -197,10 +198,10 @@ __device__ __noinline__ bool segment_hits(double wx, double wy, const double (&d
     slo = __double2float_rd(s0) - mg; shi = __double2float_ru(s1) + mg; alo = __double2float_rd(a0) - mg; ahi = __double2float_ru(a1) + mg;
   }
   // candidate edges: those whose box meets the hull's (bit mask over the staged edges)
-  unsigned cand[kCollSmem / 32];
+  unsigned cand[NW];
   unsigned any = 0;
 #pragma unroll
-  for (int w = 0; w < kCollSmem / 32; ++w) {
+  for (int w = 0; w < NW; ++w) {
     unsigned m = 0;
     const int e0 = 32 * w, e1 = ce.ns < e0 + 32 ? ce.ns : e0 + 32;
     for (int e = e0; e < e1; ++e) {
@@ -238,7 +239,7 @@ __device__ __noinline__ bool segment_hits(double wx, double wy, const double (&d
     const float gx = 2.4e-7f * fmaxf(fabsf(fax), fabsf(fqx)) + 1e-30f, gy = 2.4e-7f * fmaxf(fabsf(fay), fabsf(fqy)) + 1e-30f;
     const float cxl = fminf(fax, fqx) - gx, cxh = fmaxf(fax, fqx) + gx, cyl = fminf(fay, fqy) - gy, cyh = fmaxf(fay, fqy) + gy;
 #pragma unroll
-    for (int w = 0; w < kCollSmem / 32; ++w) {
+    for (int w = 0; w < NW; ++w) {
       unsigned m = cand[w];
       while (m) {
         const int e = 32 * w + __ffs(m) - 1;
@@ -264,6 +265,11 @@ __device__ __noinline__ bool segment_hits(double wx, double wy, const double (&d
 
 }  // namespace
 
+
+template <class S>
+__device__ __forceinline__ bool segment_hits(double wx, double wy, const double (&dx)[5], const double (&dy)[5], const CollEdges& ce, int M) {
+  return ce.ns <= 32 ? segment_hits_nw<S, 1>(wx, wy, dx, dy, ce, M) : segment_hits_nw<S, kCollSmem / 32>(wx, wy, dx, dy, ce, M);
+}
 
 // ---- how a lane talks to the other lanes of its path -------------------------------------------------
 // WarpComm: the path lives inside one warp (W <= 32, several paths per warp): shuffles only.
