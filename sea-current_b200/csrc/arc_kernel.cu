@@ -30,11 +30,18 @@ namespace scb {
 
 constexpr int kArcThreads = 256;
 constexpr int kPiecesPerLane = 4, kScanLanes = kSub / kPiecesPerLane;  // 25 lanes x 4 pieces = 100
+// Coarse inverse of a segment's table: for the 33 arc lengths j / 32 of the segment's length the piece that holds
+// them (one byte each).  The lookup of a gridpoint starts from the linear interpolation between two entries instead of
+// from the proportional guess r / length, which assumes a constant speed along the segment and was off by more than
+// the 4-wide prefetch window on most gridpoints of a quintic segment: the walk that repaired it was 13 % of this
+// kernel's stall samples and 8.5 % of its instructions (profiles/r2j arc_kernel lines, path_device.cuh:195-196).
+constexpr int kCoarse = 32, kCoarseStride = 36;
 
 __host__ __device__ inline size_t arc_smem_bytes(int W, int deg, int PB, int real_size, bool table_in_smem) {
   const size_t nseg = W - 1;
   const size_t reals = (size_t)PB * nseg * (2 * (deg + 1) + 2 * deg + 2 + (table_in_smem ? kTable : 0));
-  return 64 + sizeof(double) * PB * (nseg + 4) + (reals * real_size + 15) / 16 * 16;
+  const size_t coarse = table_in_smem ? (size_t)PB * nseg * kCoarseStride : 0;  // inverse-table guesses (bytes)
+  return 64 + sizeof(double) * PB * (nseg + 4) + (reals * real_size + 15) / 16 * 16 + coarse;
 }
 
 // TS: the CTA's arc-length tables also live in shared memory (the geometry phase reads them from there; the
@@ -57,6 +64,7 @@ __global__ void __launch_bounds__(kArcThreads, 3) arc_kernel(PathArgs g) {
   R* segtot = sm.take((size_t)PB * nseg);
   R* invlen = sm.take((size_t)PB * nseg);            // 100 / segment length
   R* stab = TS ? sm.take((size_t)PB * nseg * kTable) : nullptr;
+  unsigned char* coarse = TS ? smem_raw + arc_smem_bytes(W, DEG, PB, (int)sizeof(R), true) - (size_t)PB * nseg * kCoarseStride : nullptr;
   const int nS = PBa * nseg, nc = nseg * NC, nt = nseg * kTable;
 
   // ---- status of the path kernel, power basis of every segment
@@ -136,6 +144,16 @@ __global__ void __launch_bounds__(kArcThreads, 3) arc_kernel(PathArgs g) {
     }
     if (lane == 0) { c[0] = 0; if (TS) cs[0] = 0; }
     if (lane == kScanLanes - 1) segtot[sg] = incl;
+    if (TS) {  // coarse inverse: lane j finds the piece that holds the arc length (j / 32) of the segment
+      __syncwarp();
+      const R tot = __shfl_sync(kFullMask, incl, kScanLanes - 1);
+      unsigned char* cz = coarse + (size_t)sg * kCoarseStride;
+      const R target = tot * ((R)lane * (R)(1.0 / kCoarse));
+      int lo = 0, hi = kSub;  // largest k in [0, 99] with cs[k] <= target
+      while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (cs[mid] <= target) lo = mid; else hi = mid; }
+      cz[lane] = (unsigned char)lo;
+      if (lane == 0) cz[kCoarse] = (unsigned char)(kSub - 1);
+    }
   }
   __syncthreads();
 
@@ -183,7 +201,8 @@ __global__ void __launch_bounds__(kArcThreads, 3) arc_kernel(PathArgs g) {
         continue;
       }
       R bx, by, kap;
-      gridpoint_geometry<R, DEG>(i, N, step, segend + pl * nseg, nseg, hqc + pl * 4, invlen + pl * nseg, sg, wtab + (size_t)pl * nt,
+      gridpoint_geometry<R, DEG>(i, N, step, segend + pl * nseg, nseg, hqc + pl * 4, invlen + pl * nseg, sg,
+                                 TS ? coarse + (size_t)pl * nseg * kCoarseStride : nullptr, kCoarseStride, wtab + (size_t)pl * nt,
                                  ax + (size_t)pl * nseg * NC, ay + (size_t)pl * nseg * NC, hx + (size_t)pl * nseg * DEG,
                                  hy + (size_t)pl * nseg * DEG, bx, by, kap);
       if (o_px) o_px[oo] = bx;

@@ -165,7 +165,8 @@ template <class R> __device__ __forceinline__ void lau_node_basis(R* out, int no
 //   ax, ay: its [nseg][DEG+1] power-basis coefficients.
 template <class R, int DEG>
 __device__ __forceinline__ void gridpoint_geometry(int i, int N, double step, const double* segend, int nseg, const double* hqc,
-                                                   const R* inv_len, int& sg, const R* tab, const R* ax, const R* ay,
+                                                   const R* inv_len, int& sg, const unsigned char* coarse, int coarse_stride,
+                                                   const R* tab, const R* ax, const R* ay,
                                                    const R* hx, const R* hy, R& bx, R& by, R& kap) {
   // hqc: {c0, c1, c2} of q(s) = c0 s^3 + c1 s^2 + c2 s; inv_len[j] = 100 / length of segment j; sg: the caller's
   // guess of the segment (its previous gridpoint's), updated
@@ -181,7 +182,16 @@ __device__ __forceinline__ void gridpoint_geometry(int i, int N, double step, co
   const R* c = tab + (size_t)sg * kTable;
   // largest kl in [0, 99] with c[kl] <= r: the table is close to linear, so start from the proportional
   // guess and walk (two independent loads, then rarely more) instead of seven dependent bisection loads
-  int kl = (int)(r * inv_len[sg]);
+  int kl;
+  if (coarse) {  // coarse inverse table (arc_kernel.cu): 32 cells per segment, linear interpolation of the piece index
+    const R pc = r * inv_len[sg] * (R)0.32;  // position in cells: r / length * 32
+    const int j = max(0, min(31, (int)pc));
+    const unsigned char* cz = coarse + (size_t)sg * coarse_stride;
+    const int k0 = cz[j], k1 = cz[j + 1];
+    kl = k0 + (int)((pc - (R)j) * (R)(k1 - k0));
+  } else {
+    kl = (int)(r * inv_len[sg]);
+  }
   kl = max(1, min(kSub - 2, kl));
   // four independent loads around the guess decide almost every gridpoint in one memory round trip
   // (the dependent walk that follows was 21 % of this kernel's stall samples, profiles/r1h_arc_kernel_f64.lines.txt)

@@ -205,13 +205,22 @@ __global__ void __launch_bounds__(64) toppra_fast_kernel(ToppraArgs g) {
       ok0 = !(lo1 > hi1 && (lo1 - hi1 > dmax(fabs(lo1), fabs(hi1)) * ftol::rel_tol));
       xf0 = lo1 > hi1 ? (lo1 + hi1) / 2 : xi;
     }
+    // The controllable sets of the NEXT kTU stages are fetched while this block's dependent chain runs (double
+    // buffer): with the fetch at the top of its own block the first stage of every block waited out a full DRAM round
+    // trip with 3.5 warps per scheduler to hide it - 9.5 % of the kernel's stall samples sat on that one line
+    // (long scoreboard, profiles/r2j per-line profile of toppra_fast_kernel).
+    double kl[kTU], kh[kTU], nl[kTU], nh[kTU];
+#pragma unroll
+    for (int u = 0; u < kTU; ++u) {
+      const size_t ok_ = (size_t)min(u + 1, N) * P + p;
+      kl[u] = K_lo[ok_]; kh[u] = K_hi[ok_];
+    }
 #pragma unroll 1
     for (int i0 = 0; i0 < N && go; i0 += kTU) {
-      double kl[kTU], kh[kTU];
 #pragma unroll
       for (int u = 0; u < kTU; ++u) {
-        const size_t ok_ = (size_t)min(i0 + u + 1, N) * P + p;
-        kl[u] = K_lo[ok_]; kh[u] = K_hi[ok_];
+        const size_t ok_ = (size_t)min(i0 + kTU + u + 1, N) * P + p;
+        nl[u] = K_lo[ok_]; nh[u] = K_hi[ok_];
       }
 #pragma unroll
       for (int u = 0; u < kTU; ++u) {
@@ -246,6 +255,8 @@ __global__ void __launch_bounds__(64) toppra_fast_kernel(ToppraArgs g) {
           }
         }
       }
+#pragma unroll
+      for (int u = 0; u < kTU; ++u) { kl[u] = nl[u]; kh[u] = nh[u]; }
     }
   }
   for (int i = done + 1; i <= N; ++i) X[(size_t)i * P + p] = (S)0;
