@@ -182,7 +182,8 @@ def check(res, ref, rtol, names, spread):
             # rounding noise, which near the path's ends, where v -> 0, is all there is of omega), kappa = omega / v here
             live = np.abs(ref["v"][:, ok]) > 1e-6 * np.max(np.abs(ref["v"][:, ok]), axis=0, keepdims=True)
             g, w = np.where(live, _kappa(res)[:, ok], 0.0), np.where(live, ref["_kappa"][:, ok], 0.0)
-            tol = rtol * np.maximum(np.abs(w), 1e-3 * np.abs(w).max(axis=0, keepdims=True)) + OMEGA_FACTOR * spread["_kappa"][:, ok] + 1e-300
+            ksc = np.maximum(np.abs(w).max(axis=0), 1.0 / ref["arclen_total"][ok])   # a straight path has kappa == 0: its scale is 1 / L
+            tol = rtol * np.maximum(np.abs(w), 1e-3 * ksc[None, :]) + OMEGA_FACTOR * spread["_kappa"][:, ok]
         elif n in GRID:
             g, w = res[n][:, ok], ref[n][:, ok]
             tol = rtol * np.maximum(np.abs(w), 1e-3 * sc[n][None, :])
