@@ -94,7 +94,9 @@ constexpr int kTU = 8;  // forward pass: controllable sets of kTU stages are fet
 
 }  // namespace
 
-template <class S, bool GRID, bool CURV>
+// DB: the forward pass fetches the controllable sets of the NEXT block of stages while the current block's dependent
+// chain runs (see the comment there); chosen by the launcher for batches that leave the SMs short of warps
+template <class S, bool GRID, bool CURV, bool DB>
 __global__ void __launch_bounds__(64) toppra_fast_kernel(ToppraArgs g) {
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
   if (p >= g.P) return;
@@ -205,22 +207,30 @@ __global__ void __launch_bounds__(64) toppra_fast_kernel(ToppraArgs g) {
       ok0 = !(lo1 > hi1 && (lo1 - hi1 > dmax(fabs(lo1), fabs(hi1)) * ftol::rel_tol));
       xf0 = lo1 > hi1 ? (lo1 + hi1) / 2 : xi;
     }
-    // The controllable sets of the NEXT kTU stages are fetched while this block's dependent chain runs (double
-    // buffer): with the fetch at the top of its own block the first stage of every block waited out a full DRAM round
-    // trip with 3.5 warps per scheduler to hide it - 9.5 % of the kernel's stall samples sat on that one line
-    // (long scoreboard, profiles/r2j per-line profile of toppra_fast_kernel).
-    double kl[kTU], kh[kTU], nl[kTU], nh[kTU];
+    // The controllable sets of a block of kTU stages are fetched ahead of the block's dependent chain.  With the fetch
+    // at the top of its own block the first stage waits out a DRAM round trip (9.5 % of the stall samples on C3, long
+    // scoreboard: profiles/r2j per-line profile).  DB fetches the NEXT block while the current one runs: measured, that
+    // wins where the SMs are short of warps (C5, 8,192 problems: 6.15 -> 5.40 ms; C2: 0.558 -> 0.537) and loses on C3
+    // (14 warps per SM already hide most of it; 36 more registers and the copies cost more: 1.23 -> 1.39 ms).
+    double kl[kTU], kh[kTU], nl[DB ? kTU : 1], nh[DB ? kTU : 1];
+    if constexpr (DB) {
 #pragma unroll
-    for (int u = 0; u < kTU; ++u) {
-      const size_t ok_ = (size_t)min(u + 1, N) * P + p;
-      kl[u] = K_lo[ok_]; kh[u] = K_hi[ok_];
+      for (int u = 0; u < kTU; ++u) {
+        const size_t ok_ = (size_t)min(u + 1, N) * P + p;
+        kl[u] = K_lo[ok_]; kh[u] = K_hi[ok_];
+      }
     }
 #pragma unroll 1
     for (int i0 = 0; i0 < N && go; i0 += kTU) {
 #pragma unroll
       for (int u = 0; u < kTU; ++u) {
-        const size_t ok_ = (size_t)min(i0 + kTU + u + 1, N) * P + p;
-        nl[u] = K_lo[ok_]; nh[u] = K_hi[ok_];
+        if constexpr (DB) {
+          const size_t ok_ = (size_t)min(i0 + kTU + u + 1, N) * P + p;
+          nl[u] = K_lo[ok_]; nh[u] = K_hi[ok_];
+        } else {
+          const size_t ok_ = (size_t)min(i0 + u + 1, N) * P + p;
+          kl[u] = K_lo[ok_]; kh[u] = K_hi[ok_];
+        }
       }
 #pragma unroll
       for (int u = 0; u < kTU; ++u) {
@@ -255,8 +265,10 @@ __global__ void __launch_bounds__(64) toppra_fast_kernel(ToppraArgs g) {
           }
         }
       }
+      if constexpr (DB) {
 #pragma unroll
-      for (int u = 0; u < kTU; ++u) { kl[u] = nl[u]; kh[u] = nh[u]; }
+        for (int u = 0; u < kTU; ++u) { kl[u] = nl[u]; kh[u] = nh[u]; }
+      }
     }
   }
   for (int i = done + 1; i <= N; ++i) X[(size_t)i * P + p] = (S)0;
@@ -267,10 +279,18 @@ __global__ void __launch_bounds__(64) toppra_fast_kernel(ToppraArgs g) {
 template <class S> void launch_toppra_fast(const ToppraArgs& a, cudaStream_t st) {
   const int block = 64, grid = (a.P + block - 1) / block;
   const bool gl = a.vel_lo_grid && a.vel_hi_grid, cv = a.kappa && (a.omega_max > 0 || a.acc_lat_max > 0);
-  if (gl && cv) toppra_fast_kernel<S, true, true><<<grid, block, 0, st>>>(a);
-  else if (gl) toppra_fast_kernel<S, true, false><<<grid, block, 0, st>>>(a);
-  else if (cv) toppra_fast_kernel<S, false, true><<<grid, block, 0, st>>>(a);
-  else toppra_fast_kernel<S, false, false><<<grid, block, 0, st>>>(a);
+  const bool db = a.P < 148 * 64 * 4;  // fewer than four CTAs per SM
+  if (db) {
+    if (gl && cv) toppra_fast_kernel<S, true, true, true><<<grid, block, 0, st>>>(a);
+    else if (gl) toppra_fast_kernel<S, true, false, true><<<grid, block, 0, st>>>(a);
+    else if (cv) toppra_fast_kernel<S, false, true, true><<<grid, block, 0, st>>>(a);
+    else toppra_fast_kernel<S, false, false, true><<<grid, block, 0, st>>>(a);
+  } else {
+    if (gl && cv) toppra_fast_kernel<S, true, true, false><<<grid, block, 0, st>>>(a);
+    else if (gl) toppra_fast_kernel<S, true, false, false><<<grid, block, 0, st>>>(a);
+    else if (cv) toppra_fast_kernel<S, false, true, false><<<grid, block, 0, st>>>(a);
+    else toppra_fast_kernel<S, false, false, false><<<grid, block, 0, st>>>(a);
+  }
 }
 template void launch_toppra_fast<double>(const ToppraArgs&, cudaStream_t);
 template void launch_toppra_fast<float>(const ToppraArgs&, cudaStream_t);

@@ -9,7 +9,8 @@ move by a few ulp:
   omega  = v * kappa(u(q)): at a curvature spike (a near-cusp of the spline) kappa changes by orders of magnitude over
          1e-3 of a segment, so the ~eps * L uncertainty of the arc position q is amplified
 No modelled slack is used for them:
-  * omega: conditioning() RE-RUNS THE ORACLE on inputs perturbed by PROBE_ULPS ulp (random signs) and the tolerance is
+  * omega is checked factor by factor - v in the parametrizer stage (below), kappa = omega / v here: conditioning()
+    RE-RUNS THE ORACLE on inputs perturbed by PROBE_ULPS ulp (random signs) and the tolerance is
     rtol * max(|want|, 1e-3 scale) + OMEGA_FACTOR * observed spread, pointwise (running maximum of the spread over
     +-8 gridpoints, so that a handful of random probes (four) leave no accidental zeros).  A backward-error statement: the GPU result
     must be as close to the oracle as the oracle is to itself under input perturbations of PROBE_ULPS * SPREAD_FACTOR ulp.
@@ -52,11 +53,13 @@ def conditioning(oracle, n_probe=4, ulps=PROBE_ULPS, seed=4242, names=ILL_CONDIT
                 pk[key] = arr * (1.0 + d * rng.choice([-1.0, 1.0], size=arr.shape))
         pr, _ = oracle.plan_batch(**pk)
         same = pr["status"] == ref["status"]
-        for n in names:
+        if "omega" in ref and "v" in ref:  # curvature at the gridpoints, the factor of omega the arc kernel owns
+            ref["_kappa"], pr["_kappa"] = _kappa(ref), _kappa(pr)
+        for n in tuple(names) + ("_kappa",):
             if n in ref:
                 diff = np.abs(pr[n] - ref[n])
                 # a verdict that flips under the perturbation is a knife-edge problem, not a spread
-                if diff.ndim == 2 and n in GRID + tuple(k for k in names if k.startswith("s_")):
+                if diff.ndim == 2 and (n in GRID or n.startswith("s_") or n == "_kappa"):
                     diff[:, ~same] = 0.0     # [G][P] / [S][P]
                 else:
                     diff[~same] = 0.0        # [P] / [P][n]
@@ -144,6 +147,13 @@ def param_stage_check(oracle, res, ref, rtol, kw, names=("t", "v", "a"), max_pro
             assert np.all(err <= tol), ("parametrizer stage", n, int(p), float(np.max(err / tol)), own)
 
 
+def _kappa(r):
+    """omega / v where v is not (numerically) zero, else 0."""
+    v = np.asarray(r["v"], dtype=np.float64)
+    live = np.abs(v) > 1e-6 * np.max(np.abs(v), axis=0, keepdims=True)
+    return np.where(live, np.asarray(r["omega"], dtype=np.float64) / np.where(live, v, 1.0), 0.0)
+
+
 def scales(ref, ok):
     """Per-problem magnitude of every physical quantity (the floor of the relative error is 1e-3 of it)."""
     x = ref["x"][:, ok]; v = np.abs(ref["v"][:, ok]); a = np.abs(ref["a"][:, ok])
@@ -167,11 +177,17 @@ def check(res, ref, rtol, names, spread):
     for n in names:
         if n in ("a", "v"):
             continue
-        if n in GRID:
+        if n == "omega":
+            # omega = v * kappa, checked factor by factor: v in the parametrizer stage above (it carries that stage's
+            # rounding noise, which near the path's ends, where v -> 0, is all there is of omega), kappa = omega / v here
+            live = np.abs(ref["v"][:, ok]) > 1e-6 * np.max(np.abs(ref["v"][:, ok]), axis=0, keepdims=True)
+            g, w = np.where(live, _kappa(res)[:, ok], 0.0), np.where(live, ref["_kappa"][:, ok], 0.0)
+            tol = rtol * np.maximum(np.abs(w), 1e-3 * np.abs(w).max(axis=0, keepdims=True)) + OMEGA_FACTOR * spread["_kappa"][:, ok] + 1e-300
+        elif n in GRID:
             g, w = res[n][:, ok], ref[n][:, ok]
             tol = rtol * np.maximum(np.abs(w), 1e-3 * sc[n][None, :])
             if n in ILL_CONDITIONED:
-                tol = tol + (OMEGA_FACTOR if n == "omega" else SPREAD_FACTOR) * spread[n][:, ok]
+                tol = tol + SPREAD_FACTOR * spread[n][:, ok]
         elif n in ("T_total", "cost", "arclen_total"):
             g, w = res[n][ok], ref[n][ok]
             tol = rtol * np.abs(w) + 1e-300
@@ -183,6 +199,6 @@ def check(res, ref, rtol, names, spread):
             r = np.abs(g - w) / tol
             worst = [tuple(int(k) for k in np.unravel_index(j, r.shape)) for j in np.argsort(r, axis=None)[::-1][:4]]
             detail = [(ix, float(g[ix]), float(w[ix]), float(tol[ix]) if np.ndim(tol) else float(tol),
-                       float(spread[n][:, ok][ix]) if n in spread and n in GRID else None,
+                       float(spread["_kappa" if n == "omega" else n][:, ok][ix]) if n in GRID and ("_kappa" if n == "omega" else n) in spread else None,
                        float(sc[n][ix[-1]]) if n in sc else None) for ix in worst]
             raise AssertionError((n, float(r.max()), int(bad.sum()), "worst (index, got, want, tol, spread, scale):", detail))
