@@ -148,6 +148,21 @@ struct CollEdges {
   const void* g;     // all edges in global memory, storage type S
 };
 
+// The staged edge data is read through explicit shared-memory loads: the pointers reach segment_hits through a struct
+// and a call, where the compiler no longer knows their address space and emits generic loads (long-scoreboard stalls on
+// the cull loop's first line were 6 % of the kernel's samples, profiles/r2n per-line profile).
+__device__ __forceinline__ float4 lds_f4(const float* base, int idx) {
+  float4 v;
+  const unsigned a = (unsigned)__cvta_generic_to_shared(base) + 16u * (unsigned)idx;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ void lds_edge(const double* base, int idx, double& x0, double& y0, double& x1, double& y1) {
+  const unsigned a = (unsigned)__cvta_generic_to_shared(base) + 32u * (unsigned)idx;
+  asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(x0), "=d"(y0) : "r"(a));
+  asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(x1), "=d"(y1) : "r"(a + 16u));
+}
+
 template <class S>
 __device__ __forceinline__ void stage_coll_edges(const PathArgs& g, double* se, float* sb, float* sf, int tid, int T) {
   const int ns = g.n_coll_edges < kCollSmem ? g.n_coll_edges : kCollSmem;
@@ -205,9 +220,9 @@ __device__ __noinline__ bool segment_hits_nw(double wx, double wy, const double 
     unsigned m = 0;
     const int e0 = 32 * w, e1 = ce.ns < e0 + 32 ? ce.ns : e0 + 32;
     for (int e = e0; e < e1; ++e) {
-      const float4 b = ((const float4*)ce.box)[e];
+      const float4 b = lds_f4(ce.box, e);
       if (b.x > xhi || b.y < xlo || b.z > yhi || b.w < ylo) continue;
-      const float4 q = ((const float4*)ce.ef)[e];
+      const float4 q = lds_f4(ce.ef, e);
       const float r0x = q.x - fwx, r0y = q.y - fwy, r1x = q.z - fwx, r1y = q.w - fwy;
       const float mgs = 1e-6f * (fabsf(fdx) + fabsf(fdy)) * (fabsf(q.x) + fabsf(q.y) + fabsf(q.z) + fabsf(q.w));  // the edge's own size
       const float n0 = fdx * r0y - fdy * r0x, n1 = fdx * r1y - fdy * r1x;
@@ -244,10 +259,11 @@ __device__ __noinline__ bool segment_hits_nw(double wx, double wy, const double 
       while (m) {
         const int e = 32 * w + __ffs(m) - 1;
         m &= m - 1;
-        const float4 b = ((const float4*)ce.box)[e];
+        const float4 b = lds_f4(ce.box, e);
         if (b.x > cxh || b.y < cxl || b.z > cyh || b.w < cyl) continue;
-        double ix, iy;
-        if (seg_intersects<double>(ax, ay, qx, qy, ce.e[4 * e], ce.e[4 * e + 1], ce.e[4 * e + 2], ce.e[4 * e + 3], ix, iy)) return true;
+        double e0x, e0y, e1x, e1y, ix, iy;
+        lds_edge(ce.e, e, e0x, e0y, e1x, e1y);
+        if (seg_intersects<double>(ax, ay, qx, qy, e0x, e0y, e1x, e1y, ix, iy)) return true;
       }
     }
     if (tail) {
