@@ -141,7 +141,11 @@ struct Hermite1 {  // FP64 in both precision modes, like the toppra kernel
 constexpr int kPU = 8;
 
 // O: type of the record arrays t, v, a, omega (= S, or float when scb_batch_out.record_f32 asks for float records)
-template <class S, class O>
+// DB: both sweeps fetch the NEXT block of gridpoints while the current block's dependent arithmetic runs (57 % of the
+//     kernel's stall samples are long-scoreboard waits on the first use of a block it has just requested, profiles/r2q
+//     per-line profile).  On C3 the kernel already moves its traffic at 84 % of the HBM peak, so the variant is for
+//     batches that leave the SMs short of warps (the launcher picks it below four CTAs of toppra per SM, like toppra's).
+template <class S, class O, bool DB>
 __global__ void __launch_bounds__(32) param_kernel(ParamArgs g) {
   typedef double R;
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
@@ -169,10 +173,17 @@ __global__ void __launch_bounds__(32) param_kernel(ParamArgs g) {
     R cp_prev = 0, b_prev = 0;
     const R bc0 = hp.qd(hp.s_at(0)) * sd0;
     tb[p] = 0;
-    for (int i0 = 1; i0 <= N; i0 += kPU) {
-      R xs[kPU];
+    R xs[kPU], xn[DB ? kPU : 1];
+    if constexpr (DB) {
 #pragma unroll
-      for (int u = 0; u < kPU; ++u) xs[u] = (R)X2[(size_t)min(i0 + u, N) * P + p];
+      for (int u = 0; u < kPU; ++u) xs[u] = (R)X2[(size_t)min(1 + u, N) * P + p];
+    }
+    for (int i0 = 1; i0 <= N; i0 += kPU) {
+#pragma unroll
+      for (int u = 0; u < kPU; ++u) {
+        if constexpr (DB) xn[u] = (R)X2[(size_t)min(i0 + kPU + u, N) * P + p];
+        else xs[u] = (R)X2[(size_t)min(i0 + u, N) * P + p];
+      }
 #pragma unroll
       for (int u = 0; u < kPU; ++u) {
         const int i = i0 + u;
@@ -202,6 +213,10 @@ __global__ void __launch_bounds__(32) param_kernel(ParamArgs g) {
           t_prev = t; h_prev = h; slope_prev = slope; q_prev = qi; s_prev = s; sd_prev = sd;
         }
       }
+      if constexpr (DB) {
+#pragma unroll
+        for (int u = 0; u < kPU; ++u) xs[u] = xn[u];
+      }
     }
   }
   if (live && status != SCB_ST_OK) {  // failed in pass 1 (knot times; rare): its knot times are already stored
@@ -216,12 +231,24 @@ __global__ void __launch_bounds__(32) param_kernel(ParamArgs g) {
   if (g.T_total) ((S*)g.T_total)[p] = good ? (S)(t_next - tb[p]) : (S)0;
   const R kapN = kap ? (R)kap[(size_t)N * P + p] : 0.0;
   const R X_N = X_next, t_N = t_next;
-  for (int i0 = N - 1; i0 >= 0; i0 -= kPU) {
-    R xb[kPU], cb[kPU], tt[kPU], kk[kPU];
+  R xb[kPU], cb[kPU], tt[kPU], kk[kPU], xb2[DB ? kPU : 1], cb2[DB ? kPU : 1], tt2[DB ? kPU : 1], kk2[DB ? kPU : 1];
+  if constexpr (DB) {
 #pragma unroll
     for (int u = 0; u < kPU; ++u) {
-      const size_t o = (size_t)max(i0 - u, 0) * P + p;
+      const size_t o = (size_t)max(N - 1 - u, 0) * P + p;
       xb[u] = Xb[o]; cb[u] = cpb[o]; tt[u] = tb[o]; kk[u] = kap ? (R)kap[o] : 0.0;
+    }
+  }
+  for (int i0 = N - 1; i0 >= 0; i0 -= kPU) {
+#pragma unroll
+    for (int u = 0; u < kPU; ++u) {
+      if constexpr (DB) {
+        const size_t o = (size_t)max(i0 - kPU - u, 0) * P + p;
+        xb2[u] = Xb[o]; cb2[u] = cpb[o]; tt2[u] = tb[o]; kk2[u] = kap ? (R)kap[o] : 0.0;
+      } else {
+        const size_t o = (size_t)max(i0 - u, 0) * P + p;
+        xb[u] = Xb[o]; cb[u] = cpb[o]; tt[u] = tb[o]; kk[u] = kap ? (R)kap[o] : 0.0;
+      }
     }
 #pragma unroll
     for (int u = 0; u < kPU; ++u) {
@@ -250,6 +277,10 @@ __global__ void __launch_bounds__(32) param_kernel(ParamArgs g) {
         if (o_om) o_om[o] = good ? (O)(vi * kk[u]) : (O)0;
         X_next = Xi; t_next = ti; q_next = qv;
       }
+    }
+    if constexpr (DB) {
+#pragma unroll
+      for (int u = 0; u < kPU; ++u) { xb[u] = xb2[u]; cb[u] = cb2[u]; tt[u] = tt2[u]; kk[u] = kk2[u]; }
     }
   }
 }
@@ -452,7 +483,9 @@ template <class R> void launch_param(const ParamArgs& a, cudaStream_t st) {
   if (a.param_mode == SCB_PARAM_CONST_ACCEL) {
     if (f32) param_ca_kernel<R, float><<<grid, block, 0, st>>>(a); else param_ca_kernel<R, R><<<grid, block, 0, st>>>(a);
   } else {
-    if (f32) param_kernel<R, float><<<grid, block, 0, st>>>(a); else param_kernel<R, R><<<grid, block, 0, st>>>(a);
+    const bool db = a.P < 148 * 64 * 4;
+    if (db) { if (f32) param_kernel<R, float, true><<<grid, block, 0, st>>>(a); else param_kernel<R, R, true><<<grid, block, 0, st>>>(a); }
+    else { if (f32) param_kernel<R, float, false><<<grid, block, 0, st>>>(a); else param_kernel<R, R, false><<<grid, block, 0, st>>>(a); }
   }
 }
 template <class R> void launch_sample(const SampleArgs& a, cudaStream_t st) {
