@@ -483,7 +483,7 @@ template <class R> void launch_param(const ParamArgs& a, cudaStream_t st) {
   if (a.param_mode == SCB_PARAM_CONST_ACCEL) {
     if (f32) param_ca_kernel<R, float><<<grid, block, 0, st>>>(a); else param_ca_kernel<R, R><<<grid, block, 0, st>>>(a);
   } else {
-    const bool db = a.P < 148 * 64 * 4;
+    const bool db = a.P < 148 * 64 * 4;  // measured on C3 with the rule overridden: 1.034 ms without, 1.039 ms with (HBM-bound either way)
     if (db) { if (f32) param_kernel<R, float, true><<<grid, block, 0, st>>>(a); else param_kernel<R, R, true><<<grid, block, 0, st>>>(a); }
     else { if (f32) param_kernel<R, float, false><<<grid, block, 0, st>>>(a); else param_kernel<R, R, false><<<grid, block, 0, st>>>(a); }
   }
