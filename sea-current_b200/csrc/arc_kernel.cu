@@ -40,7 +40,7 @@ constexpr int kCoarse = 32, kCoarseStride = 36;
 __host__ __device__ inline size_t arc_smem_bytes(int W, int deg, int PB, int real_size, bool table_in_smem) {
   const size_t nseg = W - 1;
   const size_t reals = (size_t)PB * nseg * (2 * (deg + 1) + 2 * deg + 2 + (table_in_smem ? kTable : 0));
-  const size_t coarse = table_in_smem ? (size_t)PB * nseg * kCoarseStride : 0;  // inverse-table guesses (bytes)
+  const size_t coarse = (size_t)PB * nseg * kCoarseStride;  // inverse-table guesses (bytes), whichever memory the tables are in
   return 64 + sizeof(double) * PB * (nseg + 4) + (reals * real_size + 15) / 16 * 16 + coarse;
 }
 
@@ -64,7 +64,7 @@ __global__ void __launch_bounds__(kArcThreads, 3) arc_kernel(PathArgs g) {
   R* segtot = sm.take((size_t)PB * nseg);
   R* invlen = sm.take((size_t)PB * nseg);            // 100 / segment length
   R* stab = TS ? sm.take((size_t)PB * nseg * kTable) : nullptr;
-  unsigned char* coarse = TS ? smem_raw + arc_smem_bytes(W, DEG, PB, (int)sizeof(R), true) - (size_t)PB * nseg * kCoarseStride : nullptr;
+  unsigned char* coarse = smem_raw + arc_smem_bytes(W, DEG, PB, (int)sizeof(R), TS) - (size_t)PB * nseg * kCoarseStride;
   const int nS = PBa * nseg, nc = nseg * NC, nt = nseg * kTable;
 
   // ---- status of the path kernel, power basis of every segment
@@ -144,8 +144,8 @@ __global__ void __launch_bounds__(kArcThreads, 3) arc_kernel(PathArgs g) {
     }
     if (lane == 0) { c[0] = 0; if (TS) cs[0] = 0; }
     if (lane == kScanLanes - 1) segtot[sg] = incl;
-    if (TS) {  // coarse inverse: lane j finds the piece that holds the arc length (j / 32) of the segment
-      __syncwarp();
+    {  // coarse inverse: lane j finds the piece that holds the arc length (j / 32) of the segment
+      __syncwarp();  // the table entries above were written by other lanes of this warp (shared or global memory)
       const R tot = __shfl_sync(kFullMask, incl, kScanLanes - 1);
       unsigned char* cz = coarse + (size_t)sg * kCoarseStride;
       const R target = tot * ((R)lane * (R)(1.0 / kCoarse));
@@ -202,7 +202,7 @@ __global__ void __launch_bounds__(kArcThreads, 3) arc_kernel(PathArgs g) {
       }
       R bx, by, kap;
       gridpoint_geometry<R, DEG>(i, N, step, segend + pl * nseg, nseg, hqc + pl * 4, invlen + pl * nseg, sg,
-                                 TS ? coarse + (size_t)pl * nseg * kCoarseStride : nullptr, kCoarseStride, wtab + (size_t)pl * nt,
+                                 coarse + (size_t)pl * nseg * kCoarseStride, kCoarseStride, wtab + (size_t)pl * nt,
                                  ax + (size_t)pl * nseg * NC, ay + (size_t)pl * nseg * NC, hx + (size_t)pl * nseg * DEG,
                                  hy + (size_t)pl * nseg * DEG, bx, by, kap);
       if (o_px) o_px[oo] = bx;
