@@ -64,7 +64,9 @@ int main(int argc, char** argv) {
     pl.plan_summary(in, true, summ);
     std::iota(ids.begin(), ids.end(), 0);
     auto key = [&](int32_t i) { return summ[i].status == 0 ? summ[i].T_total : 1e300; };
-    std::partial_sort(ids.begin(), ids.begin() + K, ids.end(), [&](int32_t a, int32_t b) { return key(a) < key(b); });
+    auto less = [&](int32_t a, int32_t b) { return key(a) < key(b); };
+    std::nth_element(ids.begin(), ids.begin() + K, ids.end(), less);   // O(P): the K fastest, then those in order
+    std::sort(ids.begin(), ids.begin() + K, less);
     scb_batch_out out{};
     out.status = st.data(); out.T_total = T.data(); out.t = t.data(); out.px = px.data(); out.py = py.data(); out.v = v.data(); out.omega = om.data();
     pl.fetch(K, ids.data(), out);
