@@ -4,13 +4,16 @@ end slopes, per-gridpoint limits, curvature caps, both parametrizers; random wal
 repeated waypoints, offsets of 1e6, millimetre scale, zigzags).  tools/gpu/fuzz_parity.py runs the same generator against
 the clock (12,000 cases in four minutes on the round-2 build: every failure was one of the two ill-conditioned input
 classes the module's header describes, none a kernel defect)."""
+import os
+
 import numpy as np
 import pytest
 
 import fuzz_cases
 import seacurrent_b200 as scb
 
-SEED, CASES = 20260, 160
+# a longer one-off sweep: SCB_SWEEP_SEED=.. SCB_SWEEP_CASES=.. python -m pytest tests/test_random_sweep.py -m gpu
+SEED, CASES = int(os.environ.get("SCB_SWEEP_SEED", 20260)), int(os.environ.get("SCB_SWEEP_CASES", 160))
 
 
 def _cases():
@@ -32,13 +35,27 @@ def test_harness_on_the_oracle_itself(oracle):
         fuzz_cases.run_case(c, None, oracle)
 
 
+def _ext_cases():
+    rng = np.random.default_rng(SEED + 1)
+    return [fuzz_cases.make_ext_case(rng) for _ in range(CASES // 2)]
+
+
+def test_extended_harness_on_the_oracle_itself(oracle):
+    """Obstacles (tangent clipping, collision term, obstacle-distance limit) and the uniform-dt stream."""
+    cs = _ext_cases()
+    assert any(c["obst"] for c in cs) and any(c["S_cap"] for c in cs)
+    for c in cs[:8]:
+        fuzz_cases.run_case(c, None, oracle)
+
+
 @pytest.mark.gpu
-def test_random_sweep_matches_oracle(oracle):
-    planners = {m: scb.BatchPlanner(0, "fp64", m, max_problems=256, max_waypoints=80, max_gridpoints=512)
+@pytest.mark.parametrize("family", ["plain", "extended"])
+def test_random_sweep_matches_oracle(oracle, family):
+    planners = {m: scb.BatchPlanner(0, "fp64", m, max_problems=256, max_waypoints=80, max_gridpoints=512, max_samples=2048)
                 for m in ("ref_cubic", "lau_quintic")}
     failures = []
     try:
-        for k, c in enumerate(_cases()):
+        for k, c in enumerate(_cases() if family == "plain" else _ext_cases()):
             try:
                 fuzz_cases.run_case(c, planners[c["mode"]], oracle)
             except AssertionError as e:

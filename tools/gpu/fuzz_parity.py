@@ -24,11 +24,12 @@ def main():
     ora.build()
     rng = np.random.default_rng(seed)
     dry = os.environ.get("FUZZ_DRY") == "1"
-    planners = None if dry else {m: scb.BatchPlanner(0, "fp64", m, max_problems=256, max_waypoints=80, max_gridpoints=512) for m in ("ref_cubic", "lau_quintic")}
+    ext = os.environ.get("FUZZ_EXT") == "1"   # obstacles and the sample stream as well
+    planners = None if dry else {m: scb.BatchPlanner(0, "fp64", m, max_problems=256, max_waypoints=80, max_gridpoints=512, max_samples=2048) for m in ("ref_cubic", "lau_quintic")}
     t0 = time.time()
     n = 0; fails = []; okp = 0; totp = 0
     while time.time() - t0 < budget:
-        c = fuzz_cases.make_case(rng)
+        c = (fuzz_cases.make_ext_case if ext else fuzz_cases.make_case)(rng)
         n += 1
         try:
             a, b = fuzz_cases.run_case(c, None if planners is None else planners[c["mode"]], ora)
@@ -41,7 +42,7 @@ def main():
                 break
     out = {"seed": seed, "cases": n, "failures": fails, "problems": totp, "feasible": okp, "seconds": time.time() - t0}
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
-    json.dump(out, open(os.path.join(ROOT, "gpurun_out", f"fuzz_{seed}.json"), "w"), indent=1)
+    json.dump(out, open(os.path.join(ROOT, "gpurun_out", f"fuzz_{'ext_' if ext else ''}{seed}.json"), "w"), indent=1)
     print(f"cases {n}  failures {len(fails)}  problems {totp} feasible {okp}")
 
 
