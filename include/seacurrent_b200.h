@@ -129,7 +129,11 @@ enum {
   SCB_LP_DEFAULT = 0,      /* = SCB_LP_CLOSED_FORM */
   SCB_LP_SEIDEL = 1,       /* the reference's incremental sequence, operation for operation: given the
                               same path length, bit-identical to the reference's FP64 results; ~6x slower */
-  SCB_LP_CLOSED_FORM = 2   /* eliminate u: three determinants and six quotients per stage */
+  SCB_LP_CLOSED_FORM = 2   /* eliminate u: three determinants and six quotients per stage.  Returns the exact
+                              optimum; the reference's Seidel stops at a vertex within its ABSOLUTE row tolerance
+                              (1e-13) of it, so the two agree to ~1e-13 absolute in x = sdot^2: below 1e-9
+                              relative unless x itself is below ~1e-4 (millimetre-scale paths with acceleration
+                              limits ~1e-7: 1.4e-8 measured).  Use SCB_LP_SEIDEL there for 1e-9 agreement. */
 };
 
 /* Parametrizer of the timing stage: how sdot^2 at the gridpoints becomes a function of time. */

@@ -26,9 +26,9 @@ def make_api_case(rng):
     c["G"] = int(rng.choice([2, 3, 17, 64, 101, 130]))
     if c["shape"] in ("line", "far"):
         c["shape"] = "walk"
-    c["S_cap"] = int(rng.choice([0, 0, 64, 300]))
+    c["api_S"] = int(rng.choice([0, 0, 64, 300]))
     c["chunk"] = int(rng.choice([1, 7, 32, 50, 64, 100]))
-    c["obst"] = bool(rng.random() < 0.35) and c["W"] <= 48
+    c["api_obst"] = bool(rng.random() < 0.35) and c["W"] <= 48
     c["rec32"] = bool(rng.random() < 0.5)
     c["multi"] = int(rng.choice([0, 2, 3]))
     return c
@@ -37,7 +37,7 @@ def make_api_case(rng):
 def api_kwargs(c):
     kw = fuzz_cases.build(c)
     rng = np.random.default_rng(c["seed"] + 1)
-    if c["obst"]:
+    if c["api_obst"]:
         wx, wy = kw["wx"], kw["wy"]
         k = rng.integers(0, c["W"] - 1, 10)
         mx, my = (wx[0, k] + wx[0, k + 1]) / 2, (wy[0, k] + wy[0, k + 1]) / 2
@@ -47,8 +47,8 @@ def api_kwargs(c):
         kw["collision_chords"] = 8
         if rng.random() < 0.5:
             kw["a_brake"], kw["t_react"] = 1.0, 0.2
-    if c["S_cap"]:
-        kw["S_cap"] = c["S_cap"]
+    if c["api_S"]:
+        kw["S_cap"] = c["api_S"]
         kw["dt"] = float(rng.choice([0.02, 0.1, 0.5]))
     return kw
 
@@ -67,7 +67,7 @@ def _same(got, one, S, what):
 def run_api_case(c, planner):
     import torch
     kw = api_kwargs(c)
-    P, W, G, S = c["P"], c["W"], c["G"], c["S_cap"]
+    P, W, G, S = c["P"], c["W"], c["G"], c["api_S"]
     lp = c["lp"]
     planner.set_host_chunk(-1)
     one = planner.plan(lp_mode=lp, **kw)
@@ -122,7 +122,7 @@ def _cases():
 def test_api_cases_are_reproducible():
     a, b = _cases(), _cases()
     assert a == b
-    assert any(c["obst"] for c in a) and any(c["S_cap"] for c in a) and any(c["rec32"] for c in a) and any(c["multi"] for c in a)
+    assert any(c["api_obst"] for c in a) and any(c["api_S"] for c in a) and any(c["rec32"] for c in a) and any(c["multi"] for c in a)
     for c in a[:5]:
         kw = api_kwargs(c)
         assert kw["wx"].shape == (c["P"], c["W"])
