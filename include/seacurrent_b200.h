@@ -41,7 +41,7 @@
 extern "C" {
 #endif
 
-#define SCB_VERSION 200 /* 0.2.0 */
+#define SCB_VERSION 201 /* 0.2.1 */
 
 /* API-level error codes (function return values) */
 enum {
@@ -322,21 +322,25 @@ int scb_multi_get_timing(scb_multi* m, int32_t r, scb_timing* out);
  * G gridpoints LinSpaced over the path interval, collocation or interpolation discretisation
  * (tp:constraint.hpp:13-14), the reference's Seidel sequence operation for operation; controllable sets, forward
  * pass (tp:algorithm.cpp:14-68, tp:algorithm/toppra.cpp:15-46) and feasible sets (computeFeasibleSets,
- * tp:algorithm.cpp:70-103).  dof = 2 needs collocation, dof = 1 takes both (2 + 2 dof or 2 + 4 dof rows <= 6).
+ * tp:algorithm.cpp:70-103).  1 <= dof <= SCB_MAX_DOF, both discretisations: a stage LP has 2 + 2 dof rows (collocation)
+ * or 2 + 4 dof (interpolation); six rows run the register-resident solver, more rows a looped one.
  * This is the entry the reference's own known-answer vectors (cpp/tests/test_algorithm.cpp:64-165: 2-DOF, 3 segments,
  * N = 50, collocation) reach a KERNEL through.  Always FP64; host pointers; outputs [G][P]. */
+#define SCB_MAX_DOF 6
 typedef struct scb_ppoly_in {
   int32_t P, n_seg, dof, G;
   const double* coeffs;     /* [P][n_seg][4][dof]: row 0 multiplies (s - s_seg)^3, row 3 is the value */
   const double* breaks;     /* [n_seg + 1], strictly increasing, shared by the batch */
-  const double* vel_lo;     /* [P][dof] */
+  const double* vel_lo;     /* [P][dof]; may be NULL when the grids below are given */
   const double* vel_hi;
   const double* acc_lo;     /* [P][dof] */
   const double* acc_hi;
-  int32_t interpolation;    /* 0: collocation, 1: interpolation (dof = 1 only) */
+  int32_t interpolation;    /* 0: collocation, 1: interpolation */
   int32_t reserved0;
   double sd_start, sd_end;  /* computePathParametrization(vel_start, vel_end) */
   double x_cap;             /* 0 = the reference's 100 */
+  const double* vel_lo_grid;/* [G][dof][P] or NULL: velocity limits that vary along the path (the reference's */
+  const double* vel_hi_grid;/* LinearJointVelocityVarying, sc:1177-1188, tabulated at the gridpoints) */
 } scb_ppoly_in;
 typedef struct scb_ppoly_out {
   int32_t* status;          /* [P] toppra ReturnCode numbering (+ SCB_ST_ERR_BAD_LIMITS) */
@@ -347,6 +351,50 @@ typedef struct scb_ppoly_out {
   double* feas_lo; double* feas_hi; /* [G][P] or NULL: feasible sets */
 } scb_ppoly_out;
 int scb_toppra_ppoly(scb_ctx* ctx, const scb_ppoly_in* in, const scb_ppoly_out* out);
+
+/* ---- gen_vel_prof<N> for N degrees of freedom (sc:1191-1265; `requires (N >= 1)`): the straight Hermite path
+ * pos_start -> pos_end with end slopes vel_start / vel_end over s in [0, 1] (CubicHermiteSpline, sc:1210-1219;
+ * tp:geometric_path/piecewise_poly_path.cpp:352-379), velocity limits per degree of freedom (constant, or tabulated
+ * at the gridpoints for a vel_lim_func), acceleration limits with the interpolation discretisation (sc:1207), toppra,
+ * then the parametrizer and the uniform-dt record of every degree of freedom (sc:1231-1262).  The LP passes are
+ * toppra_ppoly_kernel<N, interpolation>; the parametrizer and sampler are the timing stage's own kernels run once per
+ * degree of freedom on the shared sdot^2 (the spline parametrizer is one cubic spline per degree of freedom over the
+ * same knot times, tp:parametrizer/spline.cpp:10-45).  FP64; host pointers.
+ * With dof = 1 this is scb_plan_batch's SCB_STAGE_TIMING with SCB_LP_SEIDEL. */
+typedef struct scb_ndof_in {
+  int32_t P, dof, G;        /* 1 <= dof <= SCB_MAX_DOF; G gridpoints LinSpaced over [0, 1] */
+  int32_t interpolation;    /* 1 = what gen_vel_prof builds (sc:1207); 0 = collocation */
+  const double* pos_start;  /* [P][dof] */
+  const double* pos_end;
+  const double* vel_start;  /* [P][dof] end slopes dq/ds of the Hermite path, or NULL = 0 */
+  const double* vel_end;
+  const double* vel_lo;     /* [P][dof], or NULL when the grids are given */
+  const double* vel_hi;
+  const double* vel_lo_grid;/* [G][dof][P] or NULL */
+  const double* vel_hi_grid;
+  const double* acc_lo;     /* [P][dof] */
+  const double* acc_hi;
+  double dt;                /* sample period; 0 = the reference's 0.02f */
+  double x_cap;             /* 0 = the reference's 100 */
+  int32_t param_mode;       /* SCB_PARAM_* */
+  int32_t reserved0;
+} scb_ndof_in;
+typedef struct scb_ndof_out {
+  int32_t* status;          /* [P] */
+  int32_t* fail_stage;      /* [P] or NULL */
+  double* K_lo; double* K_hi; /* [G][P] or NULL */
+  double* x;                /* [G][P] or NULL: sdot^2 at the gridpoints */
+  double* t;                /* [G][P] or NULL: knot times */
+  double* T_total;          /* [P] or NULL */
+  int32_t S_cap;            /* rows of the sample arrays (<= the ctx's max_samples); 0 = no record */
+  int32_t reserved0;
+  int32_t* n_samples;       /* [P] or NULL: ceil(T / dt), may exceed S_cap (then the record is truncated) */
+  double* s_time;           /* [S_cap][P] or NULL */
+  double* s_pos;            /* [dof][S_cap][P] or NULL: velocity_profile.pos[k] of problem p = s_pos[k][.][p] */
+  double* s_vel;
+  double* s_acc;
+} scb_ndof_out;
+int scb_gen_vel_prof(scb_ctx* ctx, const scb_ndof_in* in, const scb_ndof_out* out);
 
 /* ---- Global planner front end: FMT* over a shared set of sampled nodes, one CTA per query.
  * Replaces planning_space::fast_marching_trees (sc:1339-1407) with cost (sc:1315-1326), near (sc:1328-1337),

@@ -76,6 +76,39 @@ int ora_toppra_ppoly(int nseg, int dof, const double* coeffs, const double* brea
   return d.ret_code;
 }
 
+// The same with velocity limits that vary along the path (LinearJointVelocityVarying, sc:1177-1188): vel_lo_grid /
+// vel_hi_grid [G][dof] are the limits AT the gridpoints (the constraint evaluates vel_lim_func there and nowhere else).
+int ora_toppra_ppoly_grid(int nseg, int dof, const double* coeffs, const double* breaks, int G, const double* vel_lo_grid,
+                          const double* vel_hi_grid, const double* acc_lo, const double* acc_hi, int interpolation,
+                          double sd_start, double sd_end, double* K, double* x, int* fail_stage) {
+  tp::Problem pb;
+  pb.path.breaks.assign(breaks, breaks + nseg + 1);
+  for (int s = 0; s < nseg; ++s) {
+    std::vector<tp::Vec> c(4, tp::Vec(dof));
+    for (int r = 0; r < 4; ++r) for (int k = 0; k < dof; ++k) c[r][k] = coeffs[((size_t)s * 4 + r) * dof + k];
+    pb.path.c0.push_back(c);
+  }
+  pb.path.finish();
+  pb.gridpoints = tp::linspaced(G, breaks[0], breaks[nseg]);
+  const tp::Vec gp = pb.gridpoints;
+  pb.vel_lim = [=](double s, tp::Vec& lo, tp::Vec& hi) {
+    int i = 0;  // the gridpoint this position is
+    double best = INFINITY;
+    for (int j = 0; j < G; ++j) { const double d = std::fabs(gp[j] - s); if (d < best) { best = d; i = j; } }
+    lo.assign(vel_lo_grid + (size_t)i * dof, vel_lo_grid + (size_t)(i + 1) * dof);
+    hi.assign(vel_hi_grid + (size_t)i * dof, vel_hi_grid + (size_t)(i + 1) * dof);
+  };
+  pb.acc_lo.assign(acc_lo, acc_lo + dof); pb.acc_hi.assign(acc_hi, acc_hi + dof);
+  pb.interpolation = interpolation != 0;
+  tp::ParamData d = tp::compute_path_parametrization(pb, sd_start, sd_end);
+  for (int i = 0; i < G; ++i) {
+    if (K && i < (int)d.controllable_sets.size()) { K[2 * i] = d.controllable_sets[i][0]; K[2 * i + 1] = d.controllable_sets[i][1]; }
+    if (x && i < (int)d.parametrization.size()) x[i] = d.parametrization[i];
+  }
+  if (fail_stage) *fail_stage = d.fail_stage;
+  return d.ret_code;
+}
+
 // Spline parametrizer over a generic ppoly path (test_spline_parametrizer.cpp): returns the
 // knot times ts [G] and evaluates q(t), q'(t) at `n_eval` times.  solve_mode 0 dense QR, 1 Thomas.
 int ora_spline_param(int nseg, int dof, const double* coeffs, const double* breaks, int G, const double* gridpoints,

@@ -86,6 +86,53 @@ def toppra_ppoly(coeffs, breaks, G, vel_lo, vel_hi, acc_lo, acc_hi, interpolatio
     return rc, K, x, feas, frc.value
 
 
+def toppra_ppoly_grid(coeffs, breaks, G, vel_lo_grid, vel_hi_grid, acc_lo, acc_hi, interpolation, sd_start=0.0, sd_end=0.0):
+    """toppra_ppoly with velocity limits tabulated at the gridpoints: vel_*_grid [G][dof].  Returns (rc, K, x, fail_stage)."""
+    coeffs = _d(coeffs); nseg, _, dof = coeffs.shape
+    K = np.zeros((G, 2)); x = np.zeros(G); fs = C.c_int(-1)
+    rc = lib().ora_toppra_ppoly_grid(nseg, dof, _p(coeffs), _p(_d(breaks)), G, _p(_d(vel_lo_grid)), _p(_d(vel_hi_grid)),
+                                     _p(_d(acc_lo)), _p(_d(acc_hi)), int(interpolation), C.c_double(sd_start),
+                                     C.c_double(sd_end), _p(K), _p(x), C.byref(fs))
+    return rc, K, x, fs.value
+
+
+def hermite_coeffs(pos_start, pos_end, vel_start, vel_end):
+    """CubicHermiteSpline over [0, 1] (tp:geometric_path/piecewise_poly_path.cpp:364-375, dt = 1): [1][4][dof]."""
+    p0, p1, v0, v1 = (_d(a) for a in (pos_start, pos_end, vel_start, vel_end))
+    dt = 1.0
+    c3 = p0; c2 = v0
+    c0 = (v1 * dt - 2 * p1 + c2 * dt + 2 * c3) / dt ** 3
+    c1 = (v1 - c2 - 3 * c0 * dt * dt) / (2 * dt)
+    return np.ascontiguousarray(np.stack([c0, c1, c2, c3])[None])
+
+
+def gen_vel_prof_ndof(pos_start, pos_end, vel_start, vel_end, vel_lo, vel_hi, acc_lo, acc_hi, G=101, dt=0.02, interpolation=1,
+                      vel_lo_grid=None, vel_hi_grid=None, solve_mode=1):
+    """gen_vel_prof<N> of ONE problem (sc:1191-1265): Hermite path, toppra with the interpolation discretisation, Spline
+    parametrizer, uniform-dt record.  Limits [dof] (or grids [G][dof]).  Returns dict(status, fail_stage, K, x, t, time,
+    pos, vel, acc) with pos / vel / acc [n][dof]."""
+    dof = len(np.atleast_1d(pos_start))
+    co = hermite_coeffs(pos_start, pos_end, vel_start if vel_start is not None else np.zeros(dof),
+                        vel_end if vel_end is not None else np.zeros(dof))
+    if vel_lo_grid is not None:
+        rc, K, x, fs = toppra_ppoly_grid(co, [0.0, 1.0], G, vel_lo_grid, vel_hi_grid, acc_lo, acc_hi, interpolation)
+    else:
+        g = np.ones((G, 1))
+        rc, K, x, fs = toppra_ppoly_grid(co, [0.0, 1.0], G, g * _d(vel_lo)[None, :], g * _d(vel_hi)[None, :], acc_lo, acc_hi, interpolation)
+    out = dict(status=rc, fail_stage=fs, K=K, x=x)
+    if rc != 0:
+        return out
+    gp = np.linspace(0.0, 1.0, G)
+    ts, _, _, _ = spline_param(co, [0.0, 1.0], gp, x, solve_mode=solve_mode)
+    n = int(np.ceil((ts[-1] - ts[0]) / dt))
+    time = ts[0] + np.arange(n) * ((ts[-1] - ts[0]) / (n - 1)) if n > 1 else np.array([ts[0]])
+    if n > 1:
+        time[-1] = ts[-1]
+    _, q, qd, qdd = spline_param(co, [0.0, 1.0], gp, x, solve_mode=solve_mode, t_eval=time)
+    out.update(t=ts, time=time, pos=q, vel=qd, acc=qdd)
+    return out
+
+
 def spline_param(coeffs, breaks, gridpoints, vsq, t_eval_fn=None, solve_mode=0, t_eval=None):
     coeffs = _d(coeffs); nseg, _, dof = coeffs.shape
     gp = _d(gridpoints); G = len(gp)

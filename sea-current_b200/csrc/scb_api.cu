@@ -983,15 +983,16 @@ int scb_fmt_batch(scb_ctx* ctx, const scb_fmt_in* in, const scb_fmt_out* out) {
 int scb_toppra_ppoly(scb_ctx* ctx, const scb_ppoly_in* in, const scb_ppoly_out* out) {
   if (!ctx || !in || !out) return SCB_E_INVALID;
   const int P = in->P, ns = in->n_seg, m = in->dof, G = in->G;
-  if (P < 0 || ns < 1 || ns > 64 || G < 2 || (m != 1 && m != 2) || (m == 2 && in->interpolation)) return SCB_E_INVALID;
+  if (P < 0 || ns < 1 || ns > 64 || G < 2 || m < 1 || m > SCB_MAX_DOF) return SCB_E_INVALID;
   if (P == 0) return SCB_OK;
-  if (!in->coeffs || !in->breaks || !in->vel_lo || !in->vel_hi || !in->acc_lo || !in->acc_hi || !out->status || !out->K_lo || !out->K_hi)
+  const bool vgrid = in->vel_lo_grid && in->vel_hi_grid;
+  if (!in->coeffs || !in->breaks || !(vgrid || (in->vel_lo && in->vel_hi)) || !in->acc_lo || !in->acc_hi || !out->status || !out->K_lo || !out->K_hi)
     return SCB_E_INVALID;
   for (int k = 0; k < ns; ++k) if (!(in->breaks[k] < in->breaks[k + 1])) return SCB_E_INVALID;
   SCB_CUDA(cudaSetDevice(ctx->cfg.device));
   cudaStream_t st = ctx->stream;
-  const size_t nco = (size_t)P * ns * 4 * m, nl = (size_t)P * m, gp = (size_t)G * P;
-  const size_t n_in = nco + (ns + 1) + 4 * nl;
+  const size_t nco = (size_t)P * ns * 4 * m, nl = (size_t)P * m, gp = (size_t)G * P, ng = vgrid ? gp * m : 0;
+  const size_t n_in = nco + (ns + 1) + 4 * nl + 2 * ng;
   double* din; char* dout;
   int rc;
   if ((rc = ensure(ctx, SL_PP_IN, n_in * 8, (void**)&din))) return rc;
@@ -1002,7 +1003,8 @@ int scb_toppra_ppoly(scb_ctx* ctx, const scb_ppoly_in* in, const scb_ppoly_out* 
   double* q = din;
   auto up = [&](const double* src, size_t n, const double** dst) -> cudaError_t { *dst = q; cudaError_t e = cudaMemcpyAsync(q, src, n * 8, cudaMemcpyHostToDevice, st); q += n; return e; };
   SCB_CUDA(up(in->coeffs, nco, &a.coeffs)); SCB_CUDA(up(in->breaks, ns + 1, &a.breaks));
-  SCB_CUDA(up(in->vel_lo, nl, &a.vel_lo)); SCB_CUDA(up(in->vel_hi, nl, &a.vel_hi));
+  if (vgrid) { SCB_CUDA(up(in->vel_lo_grid, ng, &a.vel_lo_grid)); SCB_CUDA(up(in->vel_hi_grid, ng, &a.vel_hi_grid)); }
+  else { SCB_CUDA(up(in->vel_lo, nl, &a.vel_lo)); SCB_CUDA(up(in->vel_hi, nl, &a.vel_hi)); }
   SCB_CUDA(up(in->acc_lo, nl, &a.acc_lo)); SCB_CUDA(up(in->acc_hi, nl, &a.acc_hi));
   double* o = (double*)dout;
   a.K_lo = o; a.K_hi = o + gp; a.x = o + 2 * gp;
@@ -1017,6 +1019,109 @@ int scb_toppra_ppoly(scb_ctx* ctx, const scb_ppoly_in* in, const scb_ppoly_out* 
   SCB_CUDA(down(out->K_lo, a.K_lo, gp * 8)); SCB_CUDA(down(out->K_hi, a.K_hi, gp * 8)); SCB_CUDA(down(out->x, a.x, gp * 8));
   if (a.feas_lo) { SCB_CUDA(down(out->feas_lo, a.feas_lo, gp * 8)); SCB_CUDA(down(out->feas_hi, a.feas_hi, gp * 8)); }
   SCB_CUDA(cudaStreamSynchronize(st));
+  release_retired(ctx);
+  return SCB_OK;
+}
+
+// gen_vel_prof<N> (sc:1191-1265) for a batch: Hermite coefficients on the host (tp:geometric_path/
+// piecewise_poly_path.cpp:364-375, the reference's order of operations), toppra_ppoly_kernel<N, interpolation> for the
+// LP passes, then the timing stage's parametrizer and sampler once per degree of freedom on the shared sdot^2: degree
+// of freedom k is the 1-DOF Hermite path 0 -> pos_end[k] - pos_start[k] with its own end slopes (the offset
+// pos_start[k] is added to the record on the way out).
+int scb_gen_vel_prof(scb_ctx* ctx, const scb_ndof_in* in, const scb_ndof_out* out) {
+  if (!ctx || !in || !out) return SCB_E_INVALID;
+  const int P = in->P, m = in->dof, G = in->G, S = out->S_cap;
+  if (P < 0 || P > ctx->cfg.max_problems || G < 2 || G > ctx->cfg.max_gridpoints || m < 1 || m > SCB_MAX_DOF) return SCB_E_INVALID;
+  if (S < 0 || S > ctx->cfg.max_samples) return SCB_E_INVALID;
+  if (in->param_mode != SCB_PARAM_SPLINE && in->param_mode != SCB_PARAM_CONST_ACCEL) return SCB_E_INVALID;
+  if (P == 0) return SCB_OK;
+  const bool vgrid = in->vel_lo_grid && in->vel_hi_grid;
+  if (!in->pos_start || !in->pos_end || !(vgrid || (in->vel_lo && in->vel_hi)) || !in->acc_lo || !in->acc_hi || !out->status)
+    return SCB_E_INVALID;
+  SCB_CUDA(cudaSetDevice(ctx->cfg.device));
+  cudaStream_t st = ctx->stream;
+  const size_t nl = (size_t)P * m, gp = (size_t)G * P, ng = vgrid ? gp * m : 0, sp = (size_t)S * P;
+  // ---- host staging: coefficients [P][1][4][m], breaks, and the per-dof arrays of the parametrizer [m][P]
+  std::vector<double> stage(4 * nl + 2 + 3 * nl);
+  double* co = stage.data(); double* br = co + 4 * nl; double* Lk = br + 2; double* vsk = Lk + nl; double* vek = vsk + nl;
+  br[0] = 0.0; br[1] = 1.0;
+  for (int p = 0; p < P; ++p)
+    for (int k = 0; k < m; ++k) {
+      const double p0 = in->pos_start[(size_t)p * m + k], p1 = in->pos_end[(size_t)p * m + k];
+      const double v0 = in->vel_start ? in->vel_start[(size_t)p * m + k] : 0.0, v1 = in->vel_end ? in->vel_end[(size_t)p * m + k] : 0.0;
+      const double dt = 1.0;
+      double* c = co + (size_t)p * 4 * m + k;  // rows 0..3 at stride m
+      c[3 * m] = p0; c[2 * m] = v0;
+      c[0] = (v1 * dt - 2 * p1 + c[2 * m] * dt + 2 * c[3 * m]) / (dt * dt * dt);
+      c[m] = (v1 - c[2 * m] - 3 * c[0] * dt * dt) / (2 * dt);
+      Lk[(size_t)k * P + p] = p1 - p0; vsk[(size_t)k * P + p] = v0; vek[(size_t)k * P + p] = v1;
+    }
+  const size_t n_in = stage.size() + 4 * nl + 2 * ng;
+  double* din; char* dout;
+  int rc;
+  if ((rc = ensure(ctx, SL_PP_IN, n_in * 8, (void**)&din))) return rc;
+  const bool spline = in->param_mode == SCB_PARAM_SPLINE;
+  const size_t n_out = 3 * gp + (spline ? 3 : 1) * gp + (size_t)P + sp + 3 * sp * m;   // K_lo K_hi x | t X c' | T | s_time | s_pos s_vel s_acc
+  if ((rc = ensure(ctx, SL_PP_OUT, n_out * 8 + 3 * (size_t)P * 4 + 64, (void**)&dout))) return rc;
+  scb::PpolyArgs a{};
+  a.P = P; a.n_seg = 1; a.dof = m; a.G = G; a.interpolation = in->interpolation;
+  a.sd_start = 0.0; a.sd_end = 0.0; a.x_cap = in->x_cap > 0 ? in->x_cap : 100.0;
+  SCB_CUDA(cudaMemcpyAsync(din, stage.data(), stage.size() * 8, cudaMemcpyHostToDevice, st));
+  a.coeffs = din; a.breaks = din + 4 * nl;
+  const double *dL = din + 4 * nl + 2, *dVs = dL + nl, *dVe = dVs + nl;
+  double* q = din + stage.size();
+  auto up = [&](const double* src, size_t n, const double** dst) -> cudaError_t { *dst = q; cudaError_t e = cudaMemcpyAsync(q, src, n * 8, cudaMemcpyHostToDevice, st); q += n; return e; };
+  if (vgrid) { SCB_CUDA(up(in->vel_lo_grid, ng, &a.vel_lo_grid)); SCB_CUDA(up(in->vel_hi_grid, ng, &a.vel_hi_grid)); }
+  else { SCB_CUDA(up(in->vel_lo, nl, &a.vel_lo)); SCB_CUDA(up(in->vel_hi, nl, &a.vel_hi)); }
+  SCB_CUDA(up(in->acc_lo, nl, &a.acc_lo)); SCB_CUDA(up(in->acc_hi, nl, &a.acc_hi));
+  double* o = (double*)dout;
+  a.K_lo = o; a.K_hi = o + gp; a.x = o + 2 * gp;
+  double* dT = o + 3 * gp; double* dXb = spline ? dT + gp : nullptr; double* dCp = spline ? dT + 2 * gp : nullptr;
+  double* dTt = dT + (spline ? 3 : 1) * gp; double* dSt = dTt + P; double* dSp = dSt + sp; double* dSv = dSp + sp * m; double* dSa = dSv + sp * m;
+  int32_t* oi = (int32_t*)(dSa + sp * m);
+  a.status = oi; a.fail_stage = oi + P;
+  int32_t* dNs = oi + 2 * (size_t)P;
+  scb::launch_toppra_ppoly(a, st);
+  for (int k = 0; k < m; ++k) {
+    ParamArgs pa{};
+    pa.P = P; pa.G = G; pa.L = dL + (size_t)k * P; pa.vel_start = dVs + (size_t)k * P; pa.vel_end = dVe + (size_t)k * P;
+    pa.x = a.x; pa.t_buf = dT; pa.X_buf = dXb; pa.cp_buf = dCp; pa.T_total = dTt; pa.status = a.status;
+    pa.keep_X = 1; pa.param_mode = in->param_mode;
+    launch_param<double>(pa, st);
+    if (S > 0) {
+      SampleArgs sa{};
+      sa.P = P; sa.G = G; sa.W = 2; sa.deg = 3; sa.S_cap = S; sa.dt = in->dt > 0 ? in->dt : (double)0.02f;
+      sa.L = pa.L; sa.vel_start = pa.vel_start; sa.vel_end = pa.vel_end; sa.t_buf = dT; sa.X_buf = dXb; sa.x = a.x;
+      sa.param_mode = in->param_mode; sa.n_samples = dNs; sa.s_time = dSt;
+      sa.s_pos = dSp + (size_t)k * sp; sa.s_vel = dSv + (size_t)k * sp; sa.s_acc = dSa + (size_t)k * sp;
+      sa.status = a.status; sa.timing = 1;
+      launch_sample<double>(sa, st);
+    }
+  }
+  SCB_CUDA(cudaGetLastError());
+  auto down = [&](void* dst, const void* src, size_t bytes) -> cudaError_t { return dst ? cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, st) : cudaSuccess; };
+  SCB_CUDA(down(out->status, a.status, (size_t)P * 4)); SCB_CUDA(down(out->fail_stage, a.fail_stage, (size_t)P * 4));
+  SCB_CUDA(down(out->K_lo, a.K_lo, gp * 8)); SCB_CUDA(down(out->K_hi, a.K_hi, gp * 8)); SCB_CUDA(down(out->x, a.x, gp * 8));
+  SCB_CUDA(down(out->t, dT, gp * 8)); SCB_CUDA(down(out->T_total, dTt, (size_t)P * 8));
+  std::vector<int32_t> ns_host(S > 0 ? P : 0);
+  if (S > 0) {
+    SCB_CUDA(cudaMemcpyAsync(ns_host.data(), dNs, (size_t)P * 4, cudaMemcpyDeviceToHost, st)); SCB_CUDA(down(out->s_time, dSt, sp * 8));
+    SCB_CUDA(down(out->s_pos, dSp, sp * m * 8)); SCB_CUDA(down(out->s_vel, dSv, sp * m * 8)); SCB_CUDA(down(out->s_acc, dSa, sp * m * 8));
+  }
+  SCB_CUDA(cudaStreamSynchronize(st));
+  // positions are recorded relative to pos_start (the 1-DOF kernels' Hermite path starts at 0): add the offset to the
+  // rows that were written (rows beyond n_samples stay 0, failed problems have none)
+  if (S > 0 && out->n_samples) std::memcpy(out->n_samples, ns_host.data(), (size_t)P * 4);
+  if (S > 0 && out->s_pos) {
+    for (int k = 0; k < m; ++k)
+      for (int p = 0; p < P; ++p) {
+        const double p0 = in->pos_start[(size_t)p * m + k];
+        if (p0 == 0.0 || out->status[p] != SCB_ST_OK) continue;
+        const int n = ns_host[p] < S ? ns_host[p] : S;
+        double* col = out->s_pos + (size_t)k * sp + p;
+        for (int i = 0; i < n; ++i) col[(size_t)i * P] += p0;
+      }
+  }
   release_retired(ctx);
   return SCB_OK;
 }

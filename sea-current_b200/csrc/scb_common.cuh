@@ -192,6 +192,7 @@ struct PpolyArgs {                     // toppra_kernel.cu: toppra on a caller-s
   int P, n_seg, dof, G, interpolation;
   const double *coeffs, *breaks;       // [P][n_seg][4][dof], [n_seg + 1]
   const double *vel_lo, *vel_hi, *acc_lo, *acc_hi;  // [P][dof]
+  const double *vel_lo_grid, *vel_hi_grid;          // [G][dof][P] or null: velocity limits that vary along the path
   double sd_start, sd_end, x_cap;
   int32_t *status, *fail_stage, *feas_status;       // [P]
   double *K_lo, *K_hi, *x, *feas_lo, *feas_hi;      // [G][P]; K_lo / K_hi are required (state of the forward pass)

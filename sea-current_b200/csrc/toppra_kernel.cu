@@ -119,6 +119,54 @@ __device__ __forceinline__ bool solve_lp2d6(double v0, double v1, const double (
   return true;
 }
 
+// The same LP with NR rows (more degrees of freedom than gen_vel_prof<1>: 2 + 2 dof rows, twice the dof part with the
+// interpolation discretisation).  Same operation sequence; six rows go through solve_lp2d6 (registers, fully unrolled),
+// more rows keep the matrix in local memory and loop.
+template <int NR>
+__device__ __noinline__ bool solve_lp2d_n(double v0, double v1, const double (&A)[NR][3], double lo1, double hi1,
+                                          double& u_opt, double& x_opt) {
+  if (lo1 > hi1) {
+    if (lo1 - hi1 > fmax(fabs(lo1), fabs(hi1)) * tol::rel_tol || lo1 == kInf || hi1 == -kInf) return false;
+    const double xf = (lo1 + hi1) / 2;
+    Lp1d lp; lp.init();
+#pragma unroll 1
+    for (int r = 0; r < NR; ++r) lp.row(A[r][0], A[r][2] + xf * A[r][1]);
+    double uo;
+    if (!lp.finish(v0, uo)) return false;
+    u_opt = uo; x_opt = xf;
+    return true;
+  }
+  double cu = v0 > 0 ? kInf : -kInf;
+  double cx = v1 > 0 ? hi1 : lo1;
+#pragma unroll 1
+  for (int i = 0; i < NR; ++i) {
+    const double r0 = A[i][0], r1 = A[i][1], r2 = A[i][2];
+    if (value3(r0, r1, r2, cu, cx) < tol::abs_tol) continue;
+    const double sq = r0 * r0 + r1 * r1;
+    const double f = -r2 / sq;
+    const double zx0 = r0 * f, zx1 = r1 * f;
+    const double d0 = -r1, d1 = r0;
+    const double v1d = v0 * d0 + v1 * d1;
+    Lp1d lp; lp.init();
+#pragma unroll 1
+    for (int j = 0; j < i; ++j) lp.row(A[j][0] * d0 + A[j][1] * d1, value3(A[j][0], A[j][1], A[j][2], zx0, zx1));
+    lp.row(-d1, value3(0.0, -1.0, lo1, zx0, zx1));
+    lp.row(d1, value3(0.0, 1.0, -hi1, zx0, zx1));
+    double t;
+    if (!lp.finish(v1d, t)) return false;
+    cu = zx0 + t * d0;
+    cx = zx1 + t * d1;
+  }
+  u_opt = cu; x_opt = cx;
+  return true;
+}
+template <int NR>
+__device__ __forceinline__ bool solve_lp2d(double v0, double v1, const double (&A)[NR][3], double lo1, double hi1,
+                                           double& u_opt, double& x_opt) {
+  if constexpr (NR == 6) return solve_lp2d6(v0, v1, A, lo1, hi1, u_opt, x_opt);
+  else return solve_lp2d_n<NR>(v0, v1, A, lo1, hi1, u_opt, x_opt);
+}
+
 // Per-problem constants of the Hermite path and its limits.
 struct PathK {
   double c0, c1, c2;       // q(s) = c0 s^3 + c1 s^2 + c2 s   (c3 = pos_start = 0)
@@ -307,59 +355,78 @@ struct PpolyPath {
   }
 };
 
+// M degrees of freedom; INTERP: the interpolation discretisation (every acceleration row a second time, at gridpoint
+// i + 1 seen from i).  Rows: 2 coupling rows + 2 M (+ 2 M).  One degree of freedom with collocation pads its four rows
+// to six so that every six-row problem runs the register-resident solver.
+template <int M, bool INTERP>
 __global__ void __launch_bounds__(64) toppra_ppoly_kernel(PpolyArgs g) {
+  constexpr int NRraw = 2 + 2 * M * (INTERP ? 2 : 1), NR = NRraw < 6 ? 6 : NRraw;
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
   if (p >= g.P) return;
-  const int P = g.P, G = g.G, N = G - 1, m = g.dof;
+  const int P = g.P, G = g.G, N = G - 1;
+  constexpr int m = M;
   PpolyPath path{g.coeffs + (size_t)p * g.n_seg * 4 * m, g.breaks, g.n_seg, m};
   const double s0 = g.breaks[0], s1 = g.breaks[g.n_seg];
   // Eigen's LinSpaced(G, s0, s1): low + i * step, the last point exactly high
   const double step = (s1 - s0) / (double)N;
   auto s_at = [&](int i) { return i >= N ? s1 : s0 + (double)i * step; };
-  double vlo[2], vhi[2], alo[2], ahi[2];
+  double vlo[M], vhi[M], alo[M], ahi[M];
+  const bool vgrid = g.vel_lo_grid && g.vel_hi_grid;  // [G][M][P]: a velocity limit that varies along the path
+#pragma unroll
   for (int k = 0; k < m; ++k) {
-    vlo[k] = g.vel_lo[(size_t)p * m + k]; vhi[k] = g.vel_hi[(size_t)p * m + k];
+    vlo[k] = vgrid ? 0.0 : g.vel_lo[(size_t)p * m + k]; vhi[k] = vgrid ? 0.0 : g.vel_hi[(size_t)p * m + k];
     alo[k] = g.acc_lo[(size_t)p * m + k]; ahi[k] = g.acc_hi[(size_t)p * m + k];
   }
-  const bool interp = g.interpolation != 0;
   int status = SCB_ST_OK, fail_stage = -1;
   // x-box of gridpoint i from the velocity limits (linear_joint_velocity.cpp:24-61, all dofs)
   auto xbox = [&](int i, double& xlo, double& xhi) -> bool {
     const double s = s_at(i);
     double sdmin = -tol::maxsd, sdmax = tol::maxsd;
     bool ok = true;
+#pragma unroll
     for (int k = 0; k < m; ++k) {
       double v, vv;
       path.d12(s, k, v, vv);
+      const double lo = vgrid ? g.vel_lo_grid[((size_t)i * m + k) * P + p] : vlo[k];
+      const double hi = vgrid ? g.vel_hi_grid[((size_t)i * m + k) * P + p] : vhi[k];
+      if (lo != lo || hi != hi) ok = false;
       const double vinv = 1.0 / v;
-      if (v > 0) { sdmax = fmin(vhi[k] * vinv, sdmax); sdmin = fmax(vlo[k] * vinv, sdmin); }
-      else if (v < 0) { sdmax = fmin(vlo[k] * vinv, sdmax); sdmin = fmax(vhi[k] * vinv, sdmin); }
-      else if (vhi[k] < 0 || vlo[k] > 0) ok = false;
+      if (v > 0) { sdmax = fmin(hi * vinv, sdmax); sdmin = fmax(lo * vinv, sdmin); }
+      else if (v < 0) { sdmax = fmin(lo * vinv, sdmax); sdmin = fmax(hi * vinv, sdmin); }
+      else if (hi < 0 || lo > 0) ok = false;
     }
     xlo = sdmin > 0 ? sdmin * sdmin : 0.0;
     xhi = sdmax * sdmax;
     return ok;
   };
-  // rows 2..5 of stage i (constraint.cpp:100-162, 185-204; linear_joint_acceleration.cpp:22-49; seidel.cpp:228-239):
+  // rows 2.. of stage i (constraint.cpp:100-162, 185-204; linear_joint_acceleration.cpp:22-49; seidel.cpp:228-239):
   // F = [I; -I] per block, g = [acc_hi; -acc_lo]; interpolation appends the block of gridpoint i + 1
-  auto rows = [&](int i, double (&A)[6][3], double& delta) {
+  auto rows = [&](int i, double (&A)[NR][3], double& delta) {
     const double s = s_at(i), sn = s_at(i + 1 > N ? N : i + 1);
     delta = sn - s;
     int r = 2;
-    double a[2], b[2];
+    double a[M], b[M];
+#pragma unroll
     for (int k = 0; k < m; ++k) path.d12(s, k, a[k], b[k]);
+#pragma unroll
     for (int k = 0; k < m; ++k) { A[r][0] = a[k]; A[r][1] = b[k]; A[r][2] = -ahi[k]; ++r; }
+#pragma unroll
     for (int k = 0; k < m; ++k) { A[r][0] = -a[k]; A[r][1] = -b[k]; A[r][2] = alo[k]; ++r; }
-    if (interp) {  // m == 1
-      double an, bn, a2, b2;
-      if (i < N) { path.d12(sn, 0, an, bn); a2 = an + 2 * delta * bn; b2 = bn; }
-      else { a2 = a[0]; b2 = b[0]; }
-      A[r][0] = a2; A[r][1] = b2; A[r][2] = -ahi[0]; ++r;
-      A[r][0] = -a2; A[r][1] = -b2; A[r][2] = alo[0]; ++r;
+    if constexpr (INTERP) {
+      double a2[M], b2[M];
+#pragma unroll
+      for (int k = 0; k < m; ++k) {
+        if (i < N) { double an, bn; path.d12(sn, k, an, bn); a2[k] = an + 2 * delta * bn; b2[k] = bn; }
+        else { a2[k] = a[k]; b2[k] = b[k]; }
+      }
+#pragma unroll
+      for (int k = 0; k < m; ++k) { A[r][0] = a2[k]; A[r][1] = b2[k]; A[r][2] = -ahi[k]; ++r; }
+#pragma unroll
+      for (int k = 0; k < m; ++k) { A[r][0] = -a2[k]; A[r][1] = -b2[k]; A[r][2] = alo[k]; ++r; }
     }
-    for (; r < 6; ++r) { A[r][0] = 0; A[r][1] = 0; A[r][2] = -1; }  // m = 1 with collocation: padding
+    for (; r < NR; ++r) { A[r][0] = 0; A[r][1] = 0; A[r][2] = -1; }  // one dof with collocation: padding
   };
-  auto couple = [&](double (&A)[6][3], int i, double delta, double nlo, double nhi) {
+  auto couple = [&](double (&A)[NR][3], int i, double delta, double nlo, double nhi) {
     if (i >= N || nlo <= -kInf) { A[0][0] = 0; A[0][1] = 0; A[0][2] = -1; }
     else { A[0][0] = -2.0 * delta; A[0][1] = -1; A[0][2] = nlo; }
     if (i >= N || nhi >= kInf) { A[1][0] = 0; A[1][1] = 0; A[1][2] = -1; }
@@ -373,6 +440,7 @@ __global__ void __launch_bounds__(64) toppra_ppoly_kernel(PpolyArgs g) {
     double xl, xh;
     if (!xbox(i, xl, xh)) status = SCB_ST_ERR_BAD_LIMITS;
   }
+#pragma unroll
   for (int k = 0; k < m; ++k) if (!(alo[k] <= ahi[k]) || vlo[k] != vlo[k] || vhi[k] != vhi[k]) status = SCB_ST_ERR_BAD_LIMITS;
   // ---- controllable sets (algorithm.cpp:28-68)
   const double xe = g.sd_end * g.sd_end;
@@ -381,14 +449,14 @@ __global__ void __launch_bounds__(64) toppra_ppoly_kernel(PpolyArgs g) {
   int i = N - 1;
   if (status == SCB_ST_OK) {
     for (; i >= 0; --i) {
-      double A[6][3], xlo, xhi, delta;
+      double A[NR][3], xlo, xhi, delta;
       rows(i, A, delta);
       xbox(i, xlo, xhi);
       couple(A, i, delta, nlo, nhi);
       const double lo1 = fmax(xlo, 0.0), hi1 = fmin(xhi, g.x_cap);
       double u, xu, xl;
-      if (!solve_lp2d6(-tol::tie, 1.0, A, lo1, hi1, u, xu)) { status = SCB_ST_ERR_FAIL_CONTROLLABLE; fail_stage = i; break; }
-      if (!solve_lp2d6(tol::tie, -1.0, A, lo1, hi1, u, xl)) { status = SCB_ST_ERR_FAIL_CONTROLLABLE; fail_stage = i; put(g.K_lo, g.K_hi, i, 0.0, xu); --i; break; }
+      if (!solve_lp2d<NR>(-tol::tie, 1.0, A, lo1, hi1, u, xu)) { status = SCB_ST_ERR_FAIL_CONTROLLABLE; fail_stage = i; break; }
+      if (!solve_lp2d<NR>(tol::tie, -1.0, A, lo1, hi1, u, xl)) { status = SCB_ST_ERR_FAIL_CONTROLLABLE; fail_stage = i; put(g.K_lo, g.K_hi, i, 0.0, xu); --i; break; }
       nhi = xu; nlo = fmax(0.0, xl);
       put(g.K_lo, g.K_hi, i, nlo, nhi);
     }
@@ -400,14 +468,14 @@ __global__ void __launch_bounds__(64) toppra_ppoly_kernel(PpolyArgs g) {
   i = 0;
   if (status == SCB_ST_OK) {
     for (; i < N; ++i) {
-      double A[6][3], xlo, xhi, delta;
+      double A[NR][3], xlo, xhi, delta;
       rows(i, A, delta);
       xbox(i, xlo, xhi);
       const double klo = g.K_lo[(size_t)(i + 1) * P + p], khi = g.K_hi[(size_t)(i + 1) * P + p];
       couple(A, i, delta, klo, khi);
       const double lo1 = fmax(xlo, xi), hi1 = fmin(xhi, xi);
       double u, xx;
-      if (!solve_lp2d6(2.0 * delta, 1.0, A, lo1, hi1, u, xx)) { status = SCB_ST_ERR_FAIL_FORWARD_PASS; fail_stage = i; break; }
+      if (!solve_lp2d<NR>(2.0 * delta, 1.0, A, lo1, hi1, u, xx)) { status = SCB_ST_ERR_FAIL_FORWARD_PASS; fail_stage = i; break; }
       xi = fmin(khi, fmax(klo, xi + 2.0 * delta * u));
       if (g.x) g.x[(size_t)(i + 1) * P + p] = xi;
     }
@@ -417,14 +485,14 @@ __global__ void __launch_bounds__(64) toppra_ppoly_kernel(PpolyArgs g) {
   int feas_status = SCB_ST_OK;
   if (g.feas_lo || g.feas_hi) {
     for (int j = 0; j <= N; ++j) {
-      double A[6][3], xlo, xhi, delta, u, xu = 0, xl = 0;
+      double A[NR][3], xlo, xhi, delta, u, xu = 0, xl = 0;
       bool ok = status != SCB_ST_ERR_BAD_LIMITS && feas_status == SCB_ST_OK;
       if (ok) {
         rows(j, A, delta);
         xbox(j, xlo, xhi);
         couple(A, j, delta, 0.0, 100.0);
         const double lo1 = fmax(xlo, 0.0), hi1 = fmin(xhi, 100.0);
-        ok = solve_lp2d6(-tol::tie, 1.0, A, lo1, hi1, u, xu) && solve_lp2d6(tol::tie, -1.0, A, lo1, hi1, u, xl);
+        ok = solve_lp2d<NR>(-tol::tie, 1.0, A, lo1, hi1, u, xu) && solve_lp2d<NR>(tol::tie, -1.0, A, lo1, hi1, u, xl);
         if (!ok) feas_status = SCB_ST_ERR_FAIL_FEASIBLE;
       }
       put(g.feas_lo, g.feas_hi, j, ok ? xl : 0.0, ok ? xu : 0.0);
@@ -435,9 +503,22 @@ __global__ void __launch_bounds__(64) toppra_ppoly_kernel(PpolyArgs g) {
   if (g.feas_status) g.feas_status[p] = feas_status;
 }
 
+template <int M> static void launch_ppoly_m(const PpolyArgs& a, cudaStream_t st) {
+  const int block = 64, grid = (a.P + block - 1) / block;
+  if (a.interpolation) toppra_ppoly_kernel<M, true><<<grid, block, 0, st>>>(a);
+  else toppra_ppoly_kernel<M, false><<<grid, block, 0, st>>>(a);
+}
+
 void launch_toppra_ppoly(const PpolyArgs& a, cudaStream_t st) {
-  const int block = 64;
-  toppra_ppoly_kernel<<<(a.P + block - 1) / block, block, 0, st>>>(a);
+  switch (a.dof) {
+    case 1: launch_ppoly_m<1>(a, st); break;
+    case 2: launch_ppoly_m<2>(a, st); break;
+    case 3: launch_ppoly_m<3>(a, st); break;
+    case 4: launch_ppoly_m<4>(a, st); break;
+    case 5: launch_ppoly_m<5>(a, st); break;
+    case 6: launch_ppoly_m<6>(a, st); break;
+    default: break;  // scb_toppra_ppoly validates 1 <= dof <= SCB_MAX_DOF
+  }
 }
 
 template <class S> void launch_toppra(const ToppraArgs& a, cudaStream_t st) {

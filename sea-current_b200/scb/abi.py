@@ -79,7 +79,26 @@ class ScbPpolyIn(C.Structure):
     _fields_ = [("P", C.c_int32), ("n_seg", C.c_int32), ("dof", C.c_int32), ("G", C.c_int32),
                 ("coeffs", C.c_void_p), ("breaks", C.c_void_p), ("vel_lo", C.c_void_p), ("vel_hi", C.c_void_p),
                 ("acc_lo", C.c_void_p), ("acc_hi", C.c_void_p), ("interpolation", C.c_int32), ("reserved0", C.c_int32),
-                ("sd_start", C.c_double), ("sd_end", C.c_double), ("x_cap", C.c_double)]
+                ("sd_start", C.c_double), ("sd_end", C.c_double), ("x_cap", C.c_double),
+                ("vel_lo_grid", C.c_void_p), ("vel_hi_grid", C.c_void_p)]
+
+
+MAX_DOF = 6
+
+
+class ScbNdofIn(C.Structure):
+    _fields_ = [("P", C.c_int32), ("dof", C.c_int32), ("G", C.c_int32), ("interpolation", C.c_int32),
+                ("pos_start", C.c_void_p), ("pos_end", C.c_void_p), ("vel_start", C.c_void_p), ("vel_end", C.c_void_p),
+                ("vel_lo", C.c_void_p), ("vel_hi", C.c_void_p), ("vel_lo_grid", C.c_void_p), ("vel_hi_grid", C.c_void_p),
+                ("acc_lo", C.c_void_p), ("acc_hi", C.c_void_p), ("dt", C.c_double), ("x_cap", C.c_double),
+                ("param_mode", C.c_int32), ("reserved0", C.c_int32)]
+
+
+class ScbNdofOut(C.Structure):
+    _fields_ = [("status", C.c_void_p), ("fail_stage", C.c_void_p), ("K_lo", C.c_void_p), ("K_hi", C.c_void_p),
+                ("x", C.c_void_p), ("t", C.c_void_p), ("T_total", C.c_void_p), ("S_cap", C.c_int32), ("reserved0", C.c_int32),
+                ("n_samples", C.c_void_p), ("s_time", C.c_void_p), ("s_pos", C.c_void_p), ("s_vel", C.c_void_p),
+                ("s_acc", C.c_void_p)]
 
 
 class ScbPpolyOut(C.Structure):
@@ -118,6 +137,7 @@ SYMBOLS = {
     "scb_set_host_chunk": (C.c_int, [C.c_void_p, C.c_int32]),
     "scb_fmt_batch": (C.c_int, [C.c_void_p, C.POINTER(ScbFmtIn), C.POINTER(ScbFmtOut)]),
     "scb_toppra_ppoly": (C.c_int, [C.c_void_p, C.POINTER(ScbPpolyIn), C.POINTER(ScbPpolyOut)]),
+    "scb_gen_vel_prof": (C.c_int, [C.c_void_p, C.POINTER(ScbNdofIn), C.POINTER(ScbNdofOut)]),
     "scb_alloc_pinned": (C.c_void_p, [C.c_size_t]),
     "scb_free_pinned": (None, [C.c_void_p]),
     "scb_get_timing": (C.c_int, [C.c_void_p, C.POINTER(ScbTiming)]),

@@ -127,14 +127,18 @@ class BatchPlanner:
 
     # ------------------------------------------------------------------ toppra on a caller-supplied path
     def toppra_ppoly(self, coeffs, breaks, G, vel_lo, vel_hi, acc_lo, acc_hi, interpolation=0, sd_start=0.0, sd_end=0.0, x_cap=0.0,
-                     feasible=True):
-        """scb_toppra_ppoly: coeffs [P][n_seg][4][dof] (row 0 multiplies ds^3), breaks [n_seg + 1], limits [P][dof]."""
+                     feasible=True, vel_lo_grid=None, vel_hi_grid=None):
+        """scb_toppra_ppoly: coeffs [P][n_seg][4][dof] (row 0 multiplies ds^3), breaks [n_seg + 1], limits [P][dof];
+        vel_*_grid [G][dof][P] replace the constant velocity limits when given."""
         d = lambda a: np.ascontiguousarray(a, dtype=np.float64)
         coeffs = d(coeffs); P, ns, _, m = coeffs.shape
-        keep = [coeffs, d(breaks)] + [d(np.broadcast_to(d(a), (P, m))) for a in (vel_lo, vel_hi, acc_lo, acc_hi)]
+        keep = [coeffs, d(breaks)] + [None if a is None else d(np.broadcast_to(d(a), (P, m))) for a in (vel_lo, vel_hi, acc_lo, acc_hi)]
         pi = abi.ScbPpolyIn()
         pi.P, pi.n_seg, pi.dof, pi.G = P, ns, m, G
-        pi.coeffs, pi.breaks, pi.vel_lo, pi.vel_hi, pi.acc_lo, pi.acc_hi = (a.ctypes.data for a in keep)
+        pi.coeffs, pi.breaks, pi.vel_lo, pi.vel_hi, pi.acc_lo, pi.acc_hi = (None if a is None else a.ctypes.data for a in keep)
+        if vel_lo_grid is not None:
+            keep += [d(np.broadcast_to(d(vel_lo_grid), (G, m, P))), d(np.broadcast_to(d(vel_hi_grid), (G, m, P)))]
+            pi.vel_lo_grid, pi.vel_hi_grid = keep[-2].ctypes.data, keep[-1].ctypes.data
         pi.interpolation, pi.sd_start, pi.sd_end, pi.x_cap = int(interpolation), sd_start, sd_end, x_cap
         res = BatchResult(status=np.empty(P, np.int32), fail_stage=np.empty(P, np.int32), feas_status=np.empty(P, np.int32),
                           K_lo=np.empty((G, P)), K_hi=np.empty((G, P)), x=np.empty((G, P)))
@@ -144,6 +148,36 @@ class BatchPlanner:
         for k, v in res.items():
             setattr(po, k, v.ctypes.data)
         self._check(self.lib.scb_toppra_ppoly(self.ctx, C.byref(pi), C.byref(po)), "scb_toppra_ppoly")
+        return res
+
+    def gen_vel_prof(self, pos_start, pos_end, vel_lo, vel_hi, acc_lo, acc_hi, G=101, vel_start=None, vel_end=None,
+                     vel_lo_grid=None, vel_hi_grid=None, interpolation=1, dt=0.0, x_cap=0.0, param_mode=0, S_cap=0):
+        """scb_gen_vel_prof: gen_vel_prof<N> (sc:1191-1265) for a batch.  pos_* / vel_* / acc_* [P][dof]; returns status,
+        fail_stage, K_lo, K_hi, x, t [G][P], T_total [P] and, with S_cap > 0, n_samples, s_time [S][P], s_pos / s_vel /
+        s_acc [dof][S][P]."""
+        d = lambda a: np.ascontiguousarray(a, dtype=np.float64)
+        ps = d(np.atleast_2d(pos_start)); P, m = ps.shape
+        bc = lambda a: None if a is None else d(np.broadcast_to(d(a), (P, m)))
+        keep = [ps, bc(pos_end), bc(vel_start), bc(vel_end), bc(vel_lo), bc(vel_hi), bc(acc_lo), bc(acc_hi)]
+        ni = abi.ScbNdofIn()
+        ni.P, ni.dof, ni.G, ni.interpolation = P, m, G, int(interpolation)
+        (ni.pos_start, ni.pos_end, ni.vel_start, ni.vel_end, ni.vel_lo, ni.vel_hi, ni.acc_lo, ni.acc_hi) = (
+            None if a is None else a.ctypes.data for a in keep)
+        if vel_lo_grid is not None:
+            keep += [d(np.broadcast_to(d(vel_lo_grid), (G, m, P))), d(np.broadcast_to(d(vel_hi_grid), (G, m, P)))]
+            ni.vel_lo_grid, ni.vel_hi_grid = keep[-2].ctypes.data, keep[-1].ctypes.data
+        ni.dt, ni.x_cap, ni.param_mode = dt, x_cap, param_mode
+        res = BatchResult(status=np.empty(P, np.int32), fail_stage=np.empty(P, np.int32), K_lo=np.empty((G, P)),
+                          K_hi=np.empty((G, P)), x=np.empty((G, P)), t=np.empty((G, P)), T_total=np.empty(P))
+        no = abi.ScbNdofOut()
+        no.S_cap = S_cap
+        if S_cap > 0:
+            res["n_samples"] = np.empty(P, np.int32); res["s_time"] = np.empty((S_cap, P))
+            for k in ("s_pos", "s_vel", "s_acc"):
+                res[k] = np.empty((m, S_cap, P))
+        for k, v in res.items():
+            setattr(no, k, v.ctypes.data)
+        self._check(self.lib.scb_gen_vel_prof(self.ctx, C.byref(ni), C.byref(no)), "scb_gen_vel_prof")
         return res
 
     # ------------------------------------------------------------------ host buffers

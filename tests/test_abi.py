@@ -26,7 +26,7 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(lib, n), n
     assert sorted(abi.SYMBOLS) == names
-    assert lib.scb_version() == 200
+    assert lib.scb_version() == 201
 
 
 def test_struct_layouts_match_header(tmp_path):
@@ -34,13 +34,17 @@ def test_struct_layouts_match_header(tmp_path):
     src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "seacurrent_b200.h"\nint main(){printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu\\n",'
                    "sizeof(scb_config),sizeof(scb_opt),sizeof(scb_batch_in),sizeof(scb_batch_out),sizeof(scb_timing),"
                    "sizeof(scb_summary),offsetof(scb_batch_in,opt),offsetof(scb_batch_out,S_cap),offsetof(scb_batch_in,x_cap));\n"
-                   'printf("%zu %zu\\n",offsetof(scb_batch_out,record_f32),offsetof(scb_batch_out,n_samples));return 0;}\n')
+                   'printf("%zu %zu\\n",offsetof(scb_batch_out,record_f32),offsetof(scb_batch_out,n_samples));\n'
+                   'printf("%zu %zu %zu %zu %zu %zu\\n",sizeof(scb_ppoly_in),offsetof(scb_ppoly_in,vel_lo_grid),sizeof(scb_ndof_in),'
+                   "sizeof(scb_ndof_out),offsetof(scb_ndof_in,dt),offsetof(scb_ndof_out,n_samples));return 0;}\n")
     exe = tmp_path / "sz"
     subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)])
     got = [int(x) for x in subprocess.check_output([str(exe)]).split()]
     want = [C.sizeof(abi.ScbConfig), C.sizeof(abi.ScbOpt), C.sizeof(abi.ScbBatchIn), C.sizeof(abi.ScbBatchOut),
             C.sizeof(abi.ScbTiming), C.sizeof(abi.ScbSummary), abi.ScbBatchIn.opt.offset, abi.ScbBatchOut.S_cap.offset,
-            abi.ScbBatchIn.x_cap.offset, abi.ScbBatchOut.record_f32.offset, abi.ScbBatchOut.n_samples.offset]
+            abi.ScbBatchIn.x_cap.offset, abi.ScbBatchOut.record_f32.offset, abi.ScbBatchOut.n_samples.offset,
+            C.sizeof(abi.ScbPpolyIn), abi.ScbPpolyIn.vel_lo_grid.offset, C.sizeof(abi.ScbNdofIn), C.sizeof(abi.ScbNdofOut),
+            abi.ScbNdofIn.dt.offset, abi.ScbNdofOut.n_samples.offset]
     assert got == want
 
 
