@@ -594,15 +594,56 @@ class bezier_spline {  // sc:388-431
   }
 };
 
-// sc:1191-1265.  N = 1 is the only instantiation sea-current uses (arc length is the one DOF).
+// sc:1191-1265.  N = 1 is the instantiation sea-current's own call sequence uses (arc length is the one DOF) and runs
+// the timing stage of scb_plan_batch; N = 2 .. SCB_MAX_DOF run scb_gen_vel_prof (the generic-row LP kernel, then the same
+// parametrizer and sampler once per degree of freedom).
 template <int N>
 inline velocity_profile gen_vel_prof(const Eigen::Vector<value_type, N>& pos_end, const Eigen::Vector<value_type, N>& pos_start,
                                      const Eigen::Vector<value_type, N>& vel_end, const Eigen::Vector<value_type, N>& vel_start,
                                      const vel_lim_func& vel_lim, const Eigen::Vector<value_type, N>& acc_min,
                                      const Eigen::Vector<value_type, N>& acc_max, const float dt = 0.02f) {
-  static_assert(N == 1, "sea_current_b200: gen_vel_prof is built for the 1-DOF arc-length path (N = 1)");
+  static_assert(N >= 1 && N <= SCB_MAX_DOF, "sea_current_b200: gen_vel_prof<N> is built for 1 <= N <= SCB_MAX_DOF degrees of freedom");
   b200::batch_planner& pl = b200::drop_in_planner();
   const int G = b200::kDropInGrid, S_cap = b200::kDropInMaxSamples;
+  if constexpr (N > 1) {
+    // vel_lim_func tabulated at toppra's gridpoints, [G][N] (one problem: P = 1)
+    std::vector<double> vlo((size_t)G * N), vhi((size_t)G * N);
+    for (int i = 0; i < G; ++i) {
+      const double s = i == G - 1 ? 1.0 : (double)i * (1.0 / (double)(G - 1));
+      auto lim = vel_lim(s);
+      for (int k = 0; k < N; ++k) { vlo[(size_t)i * N + k] = std::get<0>(lim)(k); vhi[(size_t)i * N + k] = std::get<1>(lim)(k); }
+    }
+    double p0[N], p1[N], v0[N], v1[N], alo[N], ahi[N];
+    for (int k = 0; k < N; ++k) { p0[k] = pos_start(k); p1[k] = pos_end(k); v0[k] = vel_start(k); v1[k] = vel_end(k); alo[k] = acc_min(k); ahi[k] = acc_max(k); }
+    int32_t status = 0, fail = -1, ns = 0;
+    std::vector<double> st((size_t)S_cap), sp((size_t)S_cap * N), sv((size_t)S_cap * N), sa((size_t)S_cap * N);
+    scb_ndof_in in{};
+    in.P = 1; in.dof = N; in.G = G; in.interpolation = 1;
+    in.pos_start = p0; in.pos_end = p1; in.vel_start = v0; in.vel_end = v1;
+    in.vel_lo_grid = vlo.data(); in.vel_hi_grid = vhi.data(); in.acc_lo = alo; in.acc_hi = ahi;
+    in.dt = (double)dt; in.param_mode = b200::param_mode();
+    scb_ndof_out out{};
+    out.status = &status; out.fail_stage = &fail; out.S_cap = S_cap; out.n_samples = &ns;
+    out.s_time = st.data(); out.s_pos = sp.data(); out.s_vel = sv.data(); out.s_acc = sa.data();
+    b200::check(scb_gen_vel_prof(pl.ctx(), &in, &out), pl.ctx(), "scb_gen_vel_prof");
+    if (status != SCB_ST_OK) {
+      std::ostringstream m;
+      m << "sea_current_b200: toppra verdict " << status << " at gridpoint " << fail;
+      throw planning_error(status, fail, m.str());
+    }
+    if (ns > S_cap) throw std::runtime_error("sea_current_b200: trajectory longer than the drop-in sample capacity");
+    std::vector<VectorXf> pos, vel, acc;
+    for (int k = 0; k < N; ++k) {
+      VectorXf a(ns), b(ns), c(ns);
+      for (int i = 0; i < ns; ++i) {
+        a(i) = (float)sp[(size_t)k * S_cap + i]; b(i) = (float)sv[(size_t)k * S_cap + i]; c(i) = (float)sa[(size_t)k * S_cap + i];
+      }
+      pos.push_back(a); vel.push_back(b); acc.push_back(c);
+    }
+    toppra::Vector time(ns);
+    for (int i = 0; i < ns; ++i) time(i) = st[(size_t)i];
+    return velocity_profile(pos, vel, acc, time);
+  }
   // vel_lim_func of the path position s (sc:1177-1188), tabulated at toppra's gridpoints
   std::vector<double> vlo((size_t)G), vhi((size_t)G);
   for (int i = 0; i < G; ++i) {

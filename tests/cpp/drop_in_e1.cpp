@@ -10,6 +10,7 @@
 //   drop_in_e1 textbatch <out.json> five requests in one message through handle_text_request_batch; each one also through
 //                                   handle_text_request into <out.json>.<k> (or its exception text)
 //   drop_in_e1 sample <n>           planning_space::sample_free over the map of examples/test.cpp:250-259 (host only)
+//   drop_in_e1 ndof <unused>        gen_vel_prof<3>: three degrees of freedom, a velocity limit that drops mid-path (sc:1191-1265)
 //   drop_in_e1 fmt <n>              fast_marching_trees(( -0.5, 1), (1, -1), n, 1) as examples/test.cpp:284 calls it, then
 //                                   b200::fmt_batch with three queries over a fresh sample set
 #include <cstring>
@@ -155,6 +156,32 @@ static int run_text_batch(const char* out_path) {
   return 0;
 }
 
+// gen_vel_prof<N> with N = 3 (sc:1191, `requires (N >= 1)`): the reference's signature, end before start
+static int run_ndof_case() {
+  const Eigen::Vector<value_type, 3> pos_end{4.0, -1.5, 2.0}, pos_start{0.5, 1.0, 2.5}, vel_end{0.2, 0.0, 0.0}, vel_start{0.0, -0.1, 0.0},
+      acc_min{-0.5, -0.4, -0.3}, acc_max{0.5, 0.6, 0.3};
+  auto vel_lim = [](toppra::value_type s) {
+    toppra::Vector lower(3), upper(3);
+    const double f = (s > 0.405 && s < 0.595) ? 0.25 : 1.0;
+    for (int k = 0; k < 3; ++k) { upper(k) = f * (1.0 + 0.5 * k); lower(k) = -upper(k); }
+    return std::make_tuple(lower, upper);
+  };
+  velocity_profile prof = gen_vel_prof<3>(pos_end, pos_start, vel_end, vel_start, vel_lim, acc_min, acc_max, 0.05f);
+  std::cout << std::setprecision(9) << "{\"n\": " << prof.time.rows() << ", \"dof\": " << prof.pos.size() << ", \"T\": " << prof.time(prof.time.rows() - 1);
+  for (const char* name : {"pos", "vel", "acc"}) {
+    const std::vector<VectorXf>& v = !std::strcmp(name, "pos") ? prof.pos : (!std::strcmp(name, "vel") ? prof.vel : prof.acc);
+    std::cout << ", \"" << name << "\": [";
+    for (size_t k = 0; k < v.size(); ++k) {
+      std::cout << (k ? ", [" : "[");
+      for (long i = 0; i < v[k].rows(); ++i) std::cout << (i ? ", " : "") << v[k](i);
+      std::cout << "]";
+    }
+    std::cout << "]";
+  }
+  std::cout << "}" << std::endl;
+  return 0;
+}
+
 int main(int argc, char** argv) {
   if (argc < 3) { std::cerr << "usage: drop_in_e1 json|text <out.json>" << std::endl; return 2; }
   try {
@@ -164,6 +191,7 @@ int main(int argc, char** argv) {
     if (!std::strcmp(argv[1], "textbatch")) return run_text_batch(argv[2]);
     if (!std::strcmp(argv[1], "sample")) return run_sample_case(std::atoi(argv[2]));
     if (!std::strcmp(argv[1], "fmt")) return run_fmt_case(std::atoi(argv[2]));
+    if (!std::strcmp(argv[1], "ndof")) return run_ndof_case();
     const std::string req = "-0.5 0.5 -0.25 0.25\n0 0\n10 0\n10 10";
     std::ofstream o(argv[2]);
     o << b200::handle_text_request(req);

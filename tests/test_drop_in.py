@@ -169,6 +169,29 @@ def test_sample_free_matches_oracle(built, oracle):
 
 
 @pytest.mark.gpu
+def test_gen_vel_prof_three_dof(built, oracle):
+    """gen_vel_prof<3> through the reference's signature (sc:1191-1265): the float record of every degree of freedom
+    against the oracle's composition of the same steps."""
+    doc = json.loads(subprocess.check_output([built, "ndof", "-"]).decode())
+    G = 101
+    s = np.linspace(0.0, 1.0, G)
+    f = np.where((s > 0.405) & (s < 0.595), 0.25, 1.0)
+    hi = f[:, None] * (1.0 + 0.5 * np.arange(3))[None, :]
+    r = oracle.gen_vel_prof_ndof([0.5, 1.0, 2.5], [4.0, -1.5, 2.0], [0.0, -0.1, 0.0], [0.2, 0.0, 0.0], None, None, [-0.5, -0.4, -0.3],
+                                 [0.5, 0.6, 0.3], G=G, dt=float(np.float32(0.05)), vel_lo_grid=-hi, vel_hi_grid=hi)
+    assert r["status"] == 0
+    assert doc["dof"] == 3 and doc["n"] == len(r["time"])
+    assert abs(doc["T"] - r["time"][-1]) <= 1e-8 * r["time"][-1]
+    for name, key in (("pos", "pos"), ("vel", "vel"), ("acc", "acc")):
+        got = np.array(doc[name]).T
+        want = r[key].astype(np.float32)
+        scale = np.abs(want).max(axis=0, keepdims=True)
+        assert np.all(np.abs(got - want) <= (2e-6 if name != "acc" else 1e-5) * scale + 1e-9), name
+    # the limit that drops to a quarter between s = 0.405 and 0.595 is obeyed by the record of every degree of freedom
+    assert np.all(np.abs(np.array(doc["vel"])) <= (1.0 + 0.5 * np.arange(3))[:, None] * 1.02)
+
+
+@pytest.mark.gpu
 def test_fast_marching_trees_matches_oracle(built, oracle):
     """planning_space::fast_marching_trees as examples/test.cpp:284 calls it, and b200::fmt_batch, vs the oracle."""
     doc = json.loads(subprocess.check_output([built, "fmt", "200"]).decode())
