@@ -27,6 +27,8 @@
 // with selects (a zero determinant selects infinite bounds and a feasibility flag), array positions are
 // running pointers, and only what depends on the previous stage's result (two FMAs, two products, a few
 // min/max per pair) sits on the serial chain; reciprocals of the determinants do not.
+#include <cstdlib>
+
 #include "scb_common.cuh"
 
 namespace scb {
@@ -292,10 +294,258 @@ __global__ void __launch_bounds__(64) toppra_fast_kernel(ToppraArgs g) {
   g.fail_stage[p] = fail_stage;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Warp-specialised variant for batches that leave the SMs short of warps (C2: 4,096 problems).
+// There the kernel above is bound by ONE warp's instruction stream per scheduler: ~200 instructions per stage-pass, of
+// which about half depend on the previous stage's result (two FMAs, two products and a few min / max per slab pair, the
+// feasibility flags, the store).  Here four warps own 32 problems: warp 0 (the chain) runs exactly that half, warps 1-3
+// (the producers) compute everything that does not depend on the chain - q', q'', the velocity box, the oriented slabs,
+// the determinants and their reciprocals, the whole pair of the two acceleration slabs - for every third stage each, one
+// chunk of stages ahead, and hand it over through a double-buffered shared-memory area ([stage][value][lane]:
+// conflict-free), one __syncthreads per chunk.
+// The arithmetic is the kernel's above operation for operation: results are bit-identical (tests/test_scale_parity.py).
+// NG groups of 32 problems per CTA (four warps each), kWsChunk stages per hand-over.
+constexpr int kWsVals = 13;
+
+template <class S, bool GRID, bool CURV, int NG, int kWsChunk>
+__global__ void __launch_bounds__(NG * 128) toppra_ws_kernel(ToppraArgs g) {
+  __shared__ double bufs[NG][2][kWsChunk][kWsVals][32];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int grp = wid % NG, warp = wid / NG;   // warp: 0 = the chain, 1..3 = the producers of group grp
+  double (*buf)[kWsChunk][kWsVals][32] = bufs[grp];
+  const int p_raw = (blockIdx.x * NG + grp) * 32 + lane;
+  const bool valid = p_raw < g.P;
+  const int p = valid ? p_raw : g.P - 1;   // lanes past the end compute problem P - 1 again and store nothing
+  const size_t P = (size_t)g.P;
+  const int G = g.G, N = G - 1;
+  constexpr bool kNarrow = sizeof(S) != sizeof(double);
+  double* __restrict__ K_lo = (double*)g.K_lo; double* __restrict__ K_hi = (double*)g.K_hi;
+  S* __restrict__ oK_lo = kNarrow ? (S*)g.K_lo_out : nullptr; S* __restrict__ oK_hi = kNarrow ? (S*)g.K_hi_out : nullptr;
+  S* __restrict__ X = (S*)g.x;
+  auto put_K = [&](size_t o, double lo, double hi) {
+    if (!valid) return;
+    K_lo[o] = lo; K_hi[o] = hi;
+    if (kNarrow) { if (oK_lo) oK_lo[o] = (S)lo; if (oK_hi) oK_hi[o] = (S)hi; }
+  };
+  int status = g.status[p], fail_stage = -1;
+  const bool pre_failed = status != SCB_ST_OK;
+  double c0, c1, c2, Al, Ah, vlo, vhi;
+  {
+    const double L = pre_failed ? 1.0 : (double)((const S*)g.L)[p];
+    const double vs = g.vel_start ? (double)((const S*)g.vel_start)[p] : 0.0;
+    const double ve = g.vel_end ? (double)((const S*)g.vel_end)[p] : 0.0;
+    c2 = vs; c0 = (ve - 2.0 * L + vs); c1 = (ve - vs - 3.0 * c0) / 2.0;
+    Al = (double)((const S*)g.acc_lo)[p]; Ah = (double)((const S*)g.acc_hi)[p];
+    vlo = g.vel_lo ? (double)((const S*)g.vel_lo)[p] : 0.0; vhi = g.vel_hi ? (double)((const S*)g.vel_hi)[p] : 0.0;
+  }
+  if (!pre_failed && (!(Al <= Ah) || (!GRID && !both_numbers(vlo, vhi)))) status = SCB_ST_ERR_BAD_LIMITS;
+  Al = dmax(Al, -1e100); Ah = dmin(Ah, 1e100);
+  const double nAl = -Al, nAh = -Ah, step = 1.0 / (double)N, x_cap = g.x_cap;
+  const double c0_3 = 3.0 * c0, c1_2 = 2.0 * c1, c0_6 = 6.0 * c0;
+  auto qd = [&](double s) { return c0_3 * (s * s) + c1_2 * s + c2; };
+  auto qdd = [&](double s) { return c0_6 * s + c1_2; };
+  auto s_of = [&](int i) { return i >= N ? 1.0 : (double)i * step; };
+  const S* __restrict__ vlg = (const S*)g.vel_lo_grid; const S* __restrict__ vhg = (const S*)g.vel_hi_grid;
+  const S* __restrict__ kap = (const S*)g.kappa;
+  const double om_max = g.omega_max, al_max = g.acc_lat_max;
+  const int nchunk = (N + kWsChunk - 1) / kWsChunk;
+
+  // velocity box of gridpoint i (validated): what both passes' producers and the chain's two end points need
+  auto vel_box = [&](int i, double a, double& xlo, double& xhi) -> bool {
+    double lo = vlo, hi = vhi;
+    const size_t o = (size_t)i * P + p;
+    if (GRID) { lo = (double)vlg[o]; hi = (double)vhg[o]; }
+    const bool nums = !GRID || both_numbers(lo, hi);
+    if (CURV) curvature_cap((double)kap[o], om_max, al_max, lo, hi);
+    return vel_xbound(a, lo, hi, xlo, xhi) && nums;
+  };
+
+  // ---- backward pass
+  // producer: stage i -> buf[b][j]: {al1, -(lo1 twod), -(hi1 twod), r01, D01, al2, -(lo2 twod), -(hi2 twod), r02, D02, xl, xh, flags}
+  auto produce_back = [&](int b, int j, int i) {
+    const double s = (double)i * step, sn = s_of(i + 1), delta = sn - s, twod = 2.0 * delta;
+    const double a = qd(s), bq = qdd(s), an = qd(sn), bn = qdd(sn);
+    double xlo, xhi;
+    const bool vel_ok = vel_box(i, a, xlo, xhi);
+    const Slab s1 = orient(a, bq, Al, Ah, nAl, nAh);
+    const Slab s2 = orient(fma(twod, bn, an), bn, Al, Ah, nAl, nAh);
+    const double D01 = fma(-twod, s1.be, s1.al), D02 = fma(-twod, s2.be, s2.al), D12 = fma(s1.be, s2.al, -(s2.be * s1.al));
+    const double r01 = fast_rcp<double>(D01), r02 = fast_rcp<double>(D02), r12 = fast_rcp<double>(D12);
+    double xl = dmax(xlo, 0.0), xh = dmin(xhi, x_cap);
+    bool ok = !incoherent(xl, xh);
+    ok = pair_apply(D12, r12, fma(s1.hi, s2.al, -(s2.lo * s1.al)), fma(s1.lo, s2.al, -(s2.hi * s1.al)), xl, xh) && ok;
+    double (*v)[32] = buf[b][j];
+    v[0][lane] = s1.al; v[1][lane] = -(s1.lo * twod); v[2][lane] = -(s1.hi * twod); v[3][lane] = r01; v[4][lane] = D01;
+    v[5][lane] = s2.al; v[6][lane] = -(s2.lo * twod); v[7][lane] = -(s2.hi * twod); v[8][lane] = r02; v[9][lane] = D02;
+    v[10][lane] = xl; v[11][lane] = xh;
+    v[12][lane] = __longlong_as_double((long long)((vel_ok ? 1 : 0) | (ok ? 2 : 0)));
+  };
+  double nlo = 0, nhi = 0;  // K[N] = (0, 0)  (sc:1225)
+  bool alive;
+  int first_fail = -1;
+  if (warp == 0) {
+    put_K((size_t)N * P + p, nlo, nhi);
+    if (!pre_failed) {
+      double xl, xh;
+      if (!vel_box(N, qd(1.0), xl, xh)) status = SCB_ST_ERR_BAD_LIMITS;
+    }
+  }
+  alive = status == SCB_ST_OK;
+  auto chunk_first = [&](int c) { return N - 1 - c * kWsChunk; };   // stages chunk_first(c) - j, j = 0 .. kWsChunk - 1, while >= 0
+  if (warp > 0) {
+    for (int j = warp - 1; j < kWsChunk; j += 3) { const int i = chunk_first(0) - j; if (i >= 0) produce_back(0, j, i); }
+  }
+  __syncthreads();
+#pragma unroll 1
+  for (int c = 0; c < nchunk; ++c) {
+    const int b = c & 1;
+    if (warp > 0) {
+      if (c + 1 < nchunk)
+        for (int j = warp - 1; j < kWsChunk; j += 3) { const int i = chunk_first(c + 1) - j; if (i >= 0) produce_back(b ^ 1, j, i); }
+    } else {
+#pragma unroll
+      for (int j = 0; j < kWsChunk; ++j) {
+        const int i = chunk_first(c) - j;
+        if (i >= 0) {
+          const size_t o = (size_t)i * P + p;
+          const double (*v)[32] = buf[b][j];
+          const int fl = (int)__double_as_longlong(v[12][lane]);
+          if (!pre_failed && !(fl & 1)) { status = SCB_ST_ERR_BAD_LIMITS; alive = false; }
+          if (!alive) { put_K(o, 0.0, 0.0); continue; }
+          const double al1 = v[0][lane], nlt1 = v[1][lane], nht1 = v[2][lane], r01 = v[3][lane], D01 = v[4][lane];
+          const double al2 = v[5][lane], nlt2 = v[6][lane], nht2 = v[7][lane], r02 = v[8][lane], D02 = v[9][lane];
+          double xl = v[10][lane], xh = v[11][lane];
+          bool ok = (fl & 2) != 0;
+          ok = pair_apply(D01, r01, fma(nhi, al1, nlt1), fma(nlo, al1, nht1), xl, xh) && ok;
+          ok = pair_apply(D02, r02, fma(nhi, al2, nlt2), fma(nlo, al2, nht2), xl, xh) && ok;
+          ok = ok && !incoherent(xl, xh);
+          if (!ok) { first_fail = i; alive = false; put_K(o, 0.0, 0.0); continue; }
+          nhi = xh; nlo = dmax(0.0, xl);
+          put_K(o, nlo, nhi);
+        }
+      }
+    }
+    __syncthreads();
+  }
+  if (warp == 0) {
+    if (status == SCB_ST_ERR_BAD_LIMITS) {
+      for (int i = 0; i < N; ++i) put_K((size_t)i * P + p, 0.0, 0.0);
+    } else if (first_fail >= 0) {
+      status = SCB_ST_ERR_FAIL_CONTROLLABLE; fail_stage = first_fail;
+    }
+  }
+  __syncthreads();   // the producers start on the forward pass's first chunk: the backward pass's last buffer is free
+
+  // ---- forward pass
+  // producer: stage i -> {twod, r0, s1.al, s1.be, s1.hi, s1.lo, r1, s2.al, s2.be, s2.hi, s2.lo, r2}
+  auto produce_fwd = [&](int b, int j, int i) {
+    const double s = (double)i * step, sn2 = s_of(i + 1), delta = sn2 - s, twod = 2.0 * delta;
+    const double a = qd(s), bq = qdd(s), an2 = qd(sn2), bn2 = qdd(sn2);
+    const Slab s1 = orient(a, bq, Al, Ah, nAl, nAh);
+    const Slab s2 = orient(fma(twod, bn2, an2), bn2, Al, Ah, nAl, nAh);
+    double (*v)[32] = buf[b][j];
+    v[0][lane] = twod; v[1][lane] = fast_rcp<double>(twod);
+    v[2][lane] = s1.al; v[3][lane] = s1.be; v[4][lane] = s1.hi; v[5][lane] = s1.lo; v[6][lane] = fast_rcp<double>(s1.al);
+    v[7][lane] = s2.al; v[8][lane] = s2.be; v[9][lane] = s2.hi; v[10][lane] = s2.lo; v[11][lane] = fast_rcp<double>(s2.al);
+  };
+  double xi = 0;
+  int done = 0;
+  bool go = false, ok0 = true;
+  double xf0 = 0;
+  double kl[kWsChunk], kh[kWsChunk], nl[kWsChunk], nh[kWsChunk];
+  if (warp == 0) {
+    if (valid) X[p] = (S)xi;
+    go = status == SCB_ST_OK;
+    if (go) {
+      double xlo, xhi;
+      vel_box(0, qd(0.0), xlo, xhi);  // validated by the backward pass
+      const double lo1 = dmax(xlo, xi), hi1 = dmin(xhi, xi);
+      ok0 = !(lo1 > hi1 && (lo1 - hi1 > dmax(fabs(lo1), fabs(hi1)) * ftol::rel_tol));
+      xf0 = lo1 > hi1 ? (lo1 + hi1) / 2 : xi;
+    }
+#pragma unroll
+    for (int u = 0; u < kWsChunk; ++u) {
+      const size_t ok_ = (size_t)min(u + 1, N) * P + p;
+      kl[u] = K_lo[ok_]; kh[u] = K_hi[ok_];
+    }
+  } else {
+    for (int j = warp - 1; j < kWsChunk; j += 3) { if (j < N) produce_fwd(0, j, j); }
+  }
+  __syncthreads();
+#pragma unroll 1
+  for (int c = 0; c < nchunk; ++c) {
+    const int b = c & 1, i0 = c * kWsChunk;
+    if (warp > 0) {
+      if (c + 1 < nchunk)
+        for (int j = warp - 1; j < kWsChunk; j += 3) { const int i = i0 + kWsChunk + j; if (i < N) produce_fwd(b ^ 1, j, i); }
+    } else {
+#pragma unroll
+      for (int u = 0; u < kWsChunk; ++u) {   // the next chunk's controllable sets, in flight while this chunk's chain runs
+        const size_t ok_ = (size_t)min(i0 + kWsChunk + u + 1, N) * P + p;
+        nl[u] = K_lo[ok_]; nh[u] = K_hi[ok_];
+      }
+#pragma unroll
+      for (int u = 0; u < kWsChunk; ++u) {
+        const int i = i0 + u;
+        if (go && i < N) {
+          const double (*v)[32] = buf[b][u];
+          const double twod = v[0][lane], r0 = v[1][lane];
+          Slab s1, s2;
+          s1.al = v[2][lane]; s1.be = v[3][lane]; s1.hi = v[4][lane]; s1.lo = v[5][lane];
+          const double r1 = v[6][lane];
+          s2.al = v[7][lane]; s2.be = v[8][lane]; s2.hi = v[9][lane]; s2.lo = v[10][lane];
+          const double r2 = v[11][lane];
+          const double klo = kl[u], khi = kh[u];
+          bool ok = i == 0 ? ok0 : true;
+          const double xf = i == 0 ? xf0 : xi;
+          const double u0 = (khi - xf) * r0;
+          const double u1 = s1.al > 0 ? fma(-s1.be, xf, s1.hi) * r1 : CUDART_INF;
+          const double u2 = s2.al > 0 ? fma(-s2.be, xf, s2.hi) * r2 : CUDART_INF;
+          const double uu = dmin(u0, dmin(u1, u2));
+          const double slack = dmax(ftol::abs_tol, fabs(uu) * ftol::rel_tol);
+          ok = ok && (klo - xf - twod * uu) <= twod * slack + ftol::abs_tol;
+          ok = ok && (s1.lo - s1.be * xf - s1.al * uu) <= s1.al * slack + ftol::abs_tol;
+          ok = ok && (s2.lo - s2.be * xf - s2.al * uu) <= s2.al * slack + ftol::abs_tol;
+          ok = ok && (s1.al > 0 || (s1.be * xf - s1.hi) <= ftol::abs_tol);
+          ok = ok && (s2.al > 0 || (s2.be * xf - s2.hi) <= ftol::abs_tol);
+          if (!ok) { status = SCB_ST_ERR_FAIL_FORWARD_PASS; fail_stage = i; go = false; }
+          else {
+            xi = dmin(khi, dmax(klo, fma(twod, uu, xi)));
+            if (valid) X[(size_t)(i + 1) * P + p] = (S)xi;
+            done = i + 1;
+          }
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < kWsChunk; ++u) { kl[u] = nl[u]; kh[u] = nh[u]; }
+    }
+    __syncthreads();
+  }
+  if (warp == 0 && valid) {
+    for (int i = done + 1; i <= N; ++i) X[(size_t)i * P + p] = (S)0;
+    g.status[p] = status;
+    g.fail_stage[p] = fail_stage;
+  }
+}
+
 template <class S> void launch_toppra_fast(const ToppraArgs& a, cudaStream_t st) {
   const int block = 64, grid = (a.P + block - 1) / block;
   const bool gl = a.vel_lo_grid && a.vel_hi_grid, cv = a.kappa && (a.omega_max > 0 || a.acc_lat_max > 0);
   const bool db = a.P < 148 * 64 * 4;  // fewer than four CTAs per SM
+  const char* ws_env = getenv("SCB_TOPPRA_WS");  // A/B switch of the tests: 1 = always, 0 = never
+  const int groups = (a.P + 31) / 32;
+  const bool ws = ws_env ? atoi(ws_env) != 0 : groups <= 148;
+  if (ws) {
+    auto go = [&](auto kern1, auto kern2) {
+      if (groups > 148) kern2<<<(groups + 1) / 2, 256, 0, st>>>(a);
+      else kern1<<<groups, 128, 0, st>>>(a);
+    };
+    if (gl && cv) go(toppra_ws_kernel<S, true, true, 1, 6>, toppra_ws_kernel<S, true, true, 2, 3>);
+    else if (gl) go(toppra_ws_kernel<S, true, false, 1, 6>, toppra_ws_kernel<S, true, false, 2, 3>);
+    else if (cv) go(toppra_ws_kernel<S, false, true, 1, 6>, toppra_ws_kernel<S, false, true, 2, 3>);
+    else go(toppra_ws_kernel<S, false, false, 1, 6>, toppra_ws_kernel<S, false, false, 2, 3>);
+    return;
+  }
   if (db) {
     if (gl && cv) toppra_fast_kernel<S, true, true, true><<<grid, block, 0, st>>>(a);
     else if (gl) toppra_fast_kernel<S, true, false, true><<<grid, block, 0, st>>>(a);

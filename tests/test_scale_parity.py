@@ -222,3 +222,41 @@ def test_path_kernel_beyond_512_waypoints(oracle, mode, W):
         with pytest.raises(scb.ScbError):
             pl.plan(wx=wx2, wy=wy2, G=G, **lim)
         pl.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("precision", ["fp64", "fp32"])
+def test_warp_specialised_toppra_is_bit_identical(monkeypatch, precision):
+    """toppra_ws_kernel (chain warp + three producer warps per 32 problems; what batches below 37,888 problems run) against
+    toppra_fast_kernel (one thread per problem): the same arithmetic operation for operation, so every bit of the verdicts,
+    the controllable sets and the parametrization - with failing problems, per-gridpoint limits, curvature caps, end slopes,
+    ragged CTAs (P = 1, 33, 4096 + 5) and gridpoint counts around the chunk size (N = 1, 2, 6, 7, 12, 13, 499)."""
+    rng = np.random.default_rng(99)
+    cases = []
+    for P, G in ((1, 2), (33, 3), (70, 7), (64, 8), (5, 13), (97, 14), (4101, 500), (300, 101)):
+        w = scb.workloads.config_c2(P=P, G=G, hard_fraction=0.1) if G >= 8 else None
+        if w is None:
+            wx, wy = scb.workloads.random_walk_paths(rng, P, 6)
+            w = dict(wx=wx, wy=wy, G=G, **scb.workloads.random_limits(rng, P, slow_fraction=0.1))
+        w["vel_start"] = rng.uniform(0.0, 0.2, P); w["vel_end"] = rng.uniform(0.0, 0.2, P)
+        cases.append((w, {}))
+        if G >= 13:
+            cases.append((w, dict(omega_max=1.0, acc_lat_max=0.8)))
+    cases.append((dict(path_len=rng.uniform(1.0, 30.0, 500), G=64, **scb.workloads.random_limits(rng, 500, slow_fraction=0.1)),
+                  dict(stages=scb.abi.STAGE_TIMING, outputs=("K_lo", "K_hi", "x", "t", "v", "a", "T_total"))))
+    w = scb.workloads.config_c2(P=4800, G=40, hard_fraction=0.1)   # more than 148 groups: two groups per CTA
+    cases.append((w, {}))
+    got = {}
+    for ws in ("0", "1"):
+        monkeypatch.setenv("SCB_TOPPRA_WS", ws)
+        pl = scb.BatchPlanner(0, precision, "ref_cubic", max_problems=4800, max_waypoints=24, max_gridpoints=512)
+        try:
+            got[ws] = [pl.plan(**w, **kw) for w, kw in cases]
+        finally:
+            pl.close()
+    nfail = 0
+    for a, b in zip(got["0"], got["1"]):
+        nfail += int((a["status"] != 0).sum())
+        for k in ("status", "fail_stage", "K_lo", "K_hi", "x", "t", "T_total", "v", "a"):
+            np.testing.assert_array_equal(a[k], b[k], err_msg=k)
+    assert nfail > 0
