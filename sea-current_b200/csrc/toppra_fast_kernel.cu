@@ -403,26 +403,35 @@ __global__ void __launch_bounds__(NG * 128) toppra_ws_kernel(ToppraArgs g) {
       if (c + 1 < nchunk)
         for (int j = warp - 1; j < kWsChunk; j += 3) { const int i = chunk_first(c + 1) - j; if (i >= 0) produce_back(b ^ 1, j, i); }
     } else {
+      // The chain, branch-free: a failed problem keeps computing (on whatever its registers hold) and stores zeros, so
+      // the only thing between one stage's sdot^2 bounds and the next is the arithmetic that produces them - two FMAs,
+      // two products, the selects and two min / max per slab pair; the feasibility flags ride beside it, and the
+      // shared-memory loads of the stages of a chunk can be issued ahead of the stages before them.
+      auto stage = [&](int j, int i) {
+        const size_t o = (size_t)i * P + p;
+        const double (*v)[32] = buf[b][j];
+        const int fl = (int)__double_as_longlong(v[12][lane]);
+        const double al1 = v[0][lane], nlt1 = v[1][lane], nht1 = v[2][lane], r01 = v[3][lane], D01 = v[4][lane];
+        const double al2 = v[5][lane], nlt2 = v[6][lane], nht2 = v[7][lane], r02 = v[8][lane], D02 = v[9][lane];
+        double xl = v[10][lane], xh = v[11][lane];
+        const bool bad = !pre_failed && !(fl & 1);
+        status = bad ? SCB_ST_ERR_BAD_LIMITS : status;
+        alive = alive && !bad;
+        bool ok = (fl & 2) != 0;
+        ok = pair_apply(D01, r01, fma(nhi, al1, nlt1), fma(nlo, al1, nht1), xl, xh) && ok;
+        ok = pair_apply(D02, r02, fma(nhi, al2, nlt2), fma(nlo, al2, nht2), xl, xh) && ok;
+        ok = ok && !incoherent(xl, xh);
+        first_fail = (alive && !ok) ? i : first_fail;
+        alive = alive && ok;
+        nhi = xh; nlo = dmax(0.0, xl);
+        put_K(o, alive ? nlo : 0.0, alive ? nhi : 0.0);
+      };
+      const int i0 = chunk_first(c);
+      if (i0 >= kWsChunk - 1) {
 #pragma unroll
-      for (int j = 0; j < kWsChunk; ++j) {
-        const int i = chunk_first(c) - j;
-        if (i >= 0) {
-          const size_t o = (size_t)i * P + p;
-          const double (*v)[32] = buf[b][j];
-          const int fl = (int)__double_as_longlong(v[12][lane]);
-          if (!pre_failed && !(fl & 1)) { status = SCB_ST_ERR_BAD_LIMITS; alive = false; }
-          if (!alive) { put_K(o, 0.0, 0.0); continue; }
-          const double al1 = v[0][lane], nlt1 = v[1][lane], nht1 = v[2][lane], r01 = v[3][lane], D01 = v[4][lane];
-          const double al2 = v[5][lane], nlt2 = v[6][lane], nht2 = v[7][lane], r02 = v[8][lane], D02 = v[9][lane];
-          double xl = v[10][lane], xh = v[11][lane];
-          bool ok = (fl & 2) != 0;
-          ok = pair_apply(D01, r01, fma(nhi, al1, nlt1), fma(nlo, al1, nht1), xl, xh) && ok;
-          ok = pair_apply(D02, r02, fma(nhi, al2, nlt2), fma(nlo, al2, nht2), xl, xh) && ok;
-          ok = ok && !incoherent(xl, xh);
-          if (!ok) { first_fail = i; alive = false; put_K(o, 0.0, 0.0); continue; }
-          nhi = xh; nlo = dmax(0.0, xl);
-          put_K(o, nlo, nhi);
-        }
+        for (int j = 0; j < kWsChunk; ++j) stage(j, i0 - j);
+      } else {
+        for (int j = 0; j <= i0; ++j) stage(j, i0 - j);
       }
     }
     __syncthreads();
@@ -484,37 +493,42 @@ __global__ void __launch_bounds__(NG * 128) toppra_ws_kernel(ToppraArgs g) {
         const size_t ok_ = (size_t)min(i0 + kWsChunk + u + 1, N) * P + p;
         nl[u] = K_lo[ok_]; nh[u] = K_hi[ok_];
       }
+      auto stage = [&](int u, int i) {   // branch-free like the backward chain: a stopped problem computes on and stores nothing
+        const double (*v)[32] = buf[b][u];
+        const double twod = v[0][lane], r0 = v[1][lane];
+        Slab s1, s2;
+        s1.al = v[2][lane]; s1.be = v[3][lane]; s1.hi = v[4][lane]; s1.lo = v[5][lane];
+        const double r1 = v[6][lane];
+        s2.al = v[7][lane]; s2.be = v[8][lane]; s2.hi = v[9][lane]; s2.lo = v[10][lane];
+        const double r2 = v[11][lane];
+        const double klo = kl[u], khi = kh[u];
+        bool ok = i == 0 ? ok0 : true;
+        const double xf = i == 0 ? xf0 : xi;
+        const double u0 = (khi - xf) * r0;
+        const double u1 = s1.al > 0 ? fma(-s1.be, xf, s1.hi) * r1 : CUDART_INF;
+        const double u2 = s2.al > 0 ? fma(-s2.be, xf, s2.hi) * r2 : CUDART_INF;
+        const double uu = dmin(u0, dmin(u1, u2));
+        const double slack = dmax(ftol::abs_tol, fabs(uu) * ftol::rel_tol);
+        ok = ok && (klo - xf - twod * uu) <= twod * slack + ftol::abs_tol;
+        ok = ok && (s1.lo - s1.be * xf - s1.al * uu) <= s1.al * slack + ftol::abs_tol;
+        ok = ok && (s2.lo - s2.be * xf - s2.al * uu) <= s2.al * slack + ftol::abs_tol;
+        ok = ok && (s1.al > 0 || (s1.be * xf - s1.hi) <= ftol::abs_tol);
+        ok = ok && (s2.al > 0 || (s2.be * xf - s2.hi) <= ftol::abs_tol);
+        const bool fail_now = go && !ok;
+        status = fail_now ? SCB_ST_ERR_FAIL_FORWARD_PASS : status;
+        fail_stage = fail_now ? i : fail_stage;
+        go = go && ok;
+        const double xn = dmin(khi, dmax(klo, fma(twod, uu, xi)));
+        xi = go ? xn : xi;
+        if (go && valid) X[(size_t)(i + 1) * P + p] = (S)xi;
+        done = go ? i + 1 : done;
+      };
+      if (i0 + kWsChunk <= N) {
 #pragma unroll
-      for (int u = 0; u < kWsChunk; ++u) {
-        const int i = i0 + u;
-        if (go && i < N) {
-          const double (*v)[32] = buf[b][u];
-          const double twod = v[0][lane], r0 = v[1][lane];
-          Slab s1, s2;
-          s1.al = v[2][lane]; s1.be = v[3][lane]; s1.hi = v[4][lane]; s1.lo = v[5][lane];
-          const double r1 = v[6][lane];
-          s2.al = v[7][lane]; s2.be = v[8][lane]; s2.hi = v[9][lane]; s2.lo = v[10][lane];
-          const double r2 = v[11][lane];
-          const double klo = kl[u], khi = kh[u];
-          bool ok = i == 0 ? ok0 : true;
-          const double xf = i == 0 ? xf0 : xi;
-          const double u0 = (khi - xf) * r0;
-          const double u1 = s1.al > 0 ? fma(-s1.be, xf, s1.hi) * r1 : CUDART_INF;
-          const double u2 = s2.al > 0 ? fma(-s2.be, xf, s2.hi) * r2 : CUDART_INF;
-          const double uu = dmin(u0, dmin(u1, u2));
-          const double slack = dmax(ftol::abs_tol, fabs(uu) * ftol::rel_tol);
-          ok = ok && (klo - xf - twod * uu) <= twod * slack + ftol::abs_tol;
-          ok = ok && (s1.lo - s1.be * xf - s1.al * uu) <= s1.al * slack + ftol::abs_tol;
-          ok = ok && (s2.lo - s2.be * xf - s2.al * uu) <= s2.al * slack + ftol::abs_tol;
-          ok = ok && (s1.al > 0 || (s1.be * xf - s1.hi) <= ftol::abs_tol);
-          ok = ok && (s2.al > 0 || (s2.be * xf - s2.hi) <= ftol::abs_tol);
-          if (!ok) { status = SCB_ST_ERR_FAIL_FORWARD_PASS; fail_stage = i; go = false; }
-          else {
-            xi = dmin(khi, dmax(klo, fma(twod, uu, xi)));
-            if (valid) X[(size_t)(i + 1) * P + p] = (S)xi;
-            done = i + 1;
-          }
-        }
+        for (int u = 0; u < kWsChunk; ++u) stage(u, i0 + u);
+      } else {
+#pragma unroll
+        for (int u = 0; u < kWsChunk; ++u) if (i0 + u < N) stage(u, i0 + u);
       }
 #pragma unroll
       for (int u = 0; u < kWsChunk; ++u) { kl[u] = nl[u]; kh[u] = nh[u]; }

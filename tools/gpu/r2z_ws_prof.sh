@@ -1,5 +1,6 @@
 #!/bin/bash
-# per-line profile of the warp-specialised toppra kernel on C2 and C5
+# per-line profile of the warp-specialised toppra kernel on C2 (its default there) and, forced, on C5
+export SCB_TOPPRA_WS=1
 for c in C2 C5; do
 CMD="python bench.py --config $c --steps 2 --warmup 3 --no-e2e --no-cpu --no-extras"
 $CMD > gpurun_out/r2z_plain_$c.log 2>&1 && \
