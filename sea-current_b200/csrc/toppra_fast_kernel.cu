@@ -548,7 +548,9 @@ template <class S> void launch_toppra_fast(const ToppraArgs& a, cudaStream_t st)
   const bool db = a.P < 148 * 64 * 4;  // fewer than four CTAs per SM
   const char* ws_env = getenv("SCB_TOPPRA_WS");  // A/B switch of the tests: 1 = always, 0 = never
   const int groups = (a.P + 31) / 32;
-  const bool ws = ws_env ? atoi(ws_env) != 0 : groups <= 2 * 148;  // at most one CTA per SM (two groups per CTA beyond 148)
+  // at most one CTA per SM (two groups per CTA beyond 148); FP64 storage only: with float storage the chain warp also
+  // converts and writes the caller's float copies of K, and that is slower than the kernel above (C5: 7.27 against 5.64 ms)
+  const bool ws = ws_env ? atoi(ws_env) != 0 : (groups <= 2 * 148 && sizeof(S) == 8);
   if (ws) {
     auto go = [&](auto kern1, auto kern2) {
       if (groups > 148) kern2<<<(groups + 1) / 2, 256, 0, st>>>(a);
