@@ -103,9 +103,10 @@ def run_api_case(c, planner):
     # ---- device entry
     dev = torch.device("cuda", 0)
     dkw = {k: v for k, v in skw.items() if not isinstance(v, np.ndarray)}
-    t = {k: torch.from_numpy(np.ascontiguousarray(v)).to(dev) for k, v in skw.items() if isinstance(v, np.ndarray) and k != "obstacle_edges"}
+    R = planner.real   # the context's storage type: plan() converts host arrays the same way
+    t = {k: torch.from_numpy(np.ascontiguousarray(v, dtype=R)).to(dev) for k, v in skw.items() if isinstance(v, np.ndarray) and k != "obstacle_edges"}
     if "obstacle_edges" in skw:
-        dkw["obstacle_edges"] = torch.from_numpy(skw["obstacle_edges"]).to(dev)
+        dkw["obstacle_edges"] = torch.from_numpy(np.ascontiguousarray(skw["obstacle_edges"], dtype=R)).to(dev)
     bi, bo, res = planner.make_device_batch(t, lp_mode=lp, **dkw)
     planner.run_device(bi, bo)
     for k, v in res.items():
@@ -129,8 +130,9 @@ def test_api_cases_are_reproducible():
 
 
 @pytest.mark.gpu
-def test_entry_points_agree_bit_for_bit():
-    planners = {m: scb.BatchPlanner(0, "fp64", m, max_problems=300, max_waypoints=80, max_gridpoints=160, max_samples=320)
+@pytest.mark.parametrize("precision", ["fp64", "fp32"])
+def test_entry_points_agree_bit_for_bit(precision):
+    planners = {m: scb.BatchPlanner(0, precision, m, max_problems=300, max_waypoints=80, max_gridpoints=160, max_samples=320)
                 for m in ("ref_cubic", "lau_quintic")}
     failures = []
     feasible = total = 0
@@ -142,7 +144,7 @@ def test_entry_points_agree_bit_for_bit():
                 if c["multi"]:
                     kw = api_kwargs(c)
                     skw = {a: v for a, v in kw.items() if a not in ("S_cap", "dt")}
-                    mp = scb.MultiPlanner(c["multi"], "fp64", c["mode"], max_problems=c["P"], max_waypoints=c["W"],
+                    mp = scb.MultiPlanner(c["multi"], precision, c["mode"], max_problems=c["P"], max_waypoints=c["W"],
                                           max_gridpoints=c["G"], devices=[0] * c["multi"])
                     try:
                         names = tuple(n for n in scb.TRAJECTORY_OUTPUTS + ("x", "ctrl_x", "ctrl_y") if n in one)

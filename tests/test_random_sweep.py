@@ -64,3 +64,48 @@ def test_random_sweep_matches_oracle(oracle, family):
         for p in planners.values():
             p.close()
     assert not failures, failures
+
+
+@pytest.mark.gpu
+def test_fp32_storage_mode_sweep():
+    """SCB_FP32 (float storage, float arc length / geometry, FP64 decisions) against SCB_FP64 on the swept shapes in general
+    position, inputs rounded to float first so that both modes plan the same problems: 1e-4 (the north star's FP32
+    tolerance) on control points, length, duration and curve points; 1e-3 on sdot^2, the controllable sets and the knot
+    times, which the toppra passes derive from the float-stored path length with gains of up to 1e4 (tests/tolerances.py:
+    x and K move by 2e-11 under 8-ulp perturbations of the waypoints; float storage of L is a 6e-8 perturbation -
+    measured on this sweep: 2.6e-4 on one case of 60, below 1e-4 on the others); verdicts equal but for knife-edge
+    problems (at most 1 %)."""
+    cases = [c for c in _cases() if c["shape"] in ("walk", "zigzag", "dup") and c["W"] >= 3][:60]
+    assert len(cases) >= 40
+    pl = {(pr, m): scb.BatchPlanner(0, pr, m, max_problems=256, max_waypoints=80, max_gridpoints=512)
+          for pr in ("fp64", "fp32") for m in ("ref_cubic", "lau_quintic")}
+    flips = total = 0
+    failures = []
+    try:
+        for k, c in enumerate(cases):
+            kw = fuzz_cases.build(c)
+            kw = {a: (v.astype(np.float32).astype(np.float64) if isinstance(v, np.ndarray) else v) for a, v in kw.items()}
+            a = pl["fp64", c["mode"]].plan(lp_mode=c["lp"], **kw)
+            b = pl["fp32", c["mode"]].plan(lp_mode=c["lp"], **kw)
+            both = (a["status"] == 0) & (b["status"] == 0)
+            flips += int((a["status"] != b["status"]).sum()); total += c["P"]
+            if not both.any():
+                continue
+            L = a["arclen_total"][both]
+            for n in ("ctrl_x", "ctrl_y", "arclen_total", "T_total", "px", "py", "x", "K_hi", "t"):
+                g, w = (b[n][:, both], a[n][:, both]) if n in fuzz_cases.GRID else (b[n][both], a[n][both])
+                if n in ("ctrl_x", "ctrl_y", "px", "py"):   # positions: against the path's extent
+                    ext = np.maximum(np.abs(a["ctrl_x"][both]).max(axis=1), np.abs(a["ctrl_y"][both]).max(axis=1))
+                    sc = (ext[:, None] if n.startswith("ctrl") else ext[None, :]) * np.ones_like(w)
+                elif n in fuzz_cases.GRID:
+                    sc = np.maximum(np.abs(w), 1e-2 * np.abs(w).max(axis=0, keepdims=True))
+                else:
+                    sc = np.abs(w)
+                err = np.abs(g - w) / np.maximum(sc, 1e-300)
+                if err.max() > (1e-3 if n in ("x", "K_hi", "t") else 1e-4):
+                    failures.append((k, n, float(err.max()), c))
+    finally:
+        for p in pl.values():
+            p.close()
+    assert not failures, failures[:6]
+    assert flips <= 0.01 * total, (flips, total)
