@@ -115,6 +115,8 @@ class ClockSampler:
         self.index, self.rows, self.stop_flag, self.th = index, [], False, None
 
     def _run(self):
+        if self._run_nvml():
+            return
         while not self.stop_flag:
             try:
                 out = subprocess.check_output(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
@@ -123,6 +125,31 @@ class ClockSampler:
             except Exception:
                 pass
             time.sleep(0.05)
+
+    def _run_nvml(self):
+        """The same readings through NVML (what nvidia-smi prints), every 2 ms: a 140 ms timed region gets ~60 samples
+        instead of the two a subprocess per sample manages.  False = NVML unavailable, fall back to nvidia-smi."""
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            h = pynvml.nvmlDeviceGetHandleByIndex(self.index)
+            reasons_fn = getattr(pynvml, "nvmlDeviceGetCurrentClocksEventReasons", None) or pynvml.nvmlDeviceGetCurrentClocksThrottleReasons
+            mx = pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM)
+            pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM); reasons_fn(h)
+        except Exception:
+            return False
+        bits = ((0x8, 2), (0x40, 3), (0x20, 4), (0x4, 5))   # hw_slowdown, hw_thermal_slowdown, sw_thermal_slowdown, sw_power_cap
+        while not self.stop_flag:
+            try:
+                r = reasons_fn(h)
+                row = [str(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)), str(mx), "", "", "", ""]
+                for bit, col in bits:
+                    row[col] = "Active" if r & bit else "Not Active"
+                self.rows.append(row)
+            except Exception:
+                pass
+            time.sleep(0.002)
+        return True
 
     def start(self):
         self.th = threading.Thread(target=self._run, daemon=True)
