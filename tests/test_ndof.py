@@ -71,6 +71,50 @@ def test_oracle_identical_dofs_collapse_to_one(oracle):
     np.testing.assert_allclose(b["pos"][:, 2], a["pos"][:, 0], rtol=1e-12, atol=1e-12)
 
 
+# ------------------------------------------------------------------ the reference's own end-to-end example
+def _approach_case():
+    """third-party/toppra/cpp/tests/test_toppra_approach.cpp:30-152 (the quickstart example): 2 joints, Hermite pieces
+    through (0,0) -> (1,2) -> (2,0) with slopes (0,0), (1,1), (0,0) over s = 0, 1, 2; velocity box [[-1, 1], [-0.5, 0.5]],
+    acceleration box [[-0.05, 0.2], [-0.1, 0.3]] with the INTERPOLATION discretisation; N = 100."""
+    pos = np.array([[0.0, 0.0], [1.0, 2.0], [2.0, 0.0]]); vel = np.array([[0.0, 0.0], [1.0, 1.0], [0.0, 0.0]])
+    breaks = np.array([0.0, 1.0, 2.0])
+    co = np.zeros((2, 4, 2))
+    for k in range(2):
+        dt = breaks[k + 1] - breaks[k]
+        c3 = pos[k]; c2 = vel[k]
+        c0 = (vel[k + 1] * dt - 2 * pos[k + 1] + c2 * dt + 2 * c3) / dt ** 3
+        c1 = (vel[k + 1] - c2 - 3 * c0 * dt * dt) / (2 * dt)
+        co[k] = [c0, c1, c2, c3]
+    return co, breaks, np.array([-1.0, -0.5]), np.array([1.0, 0.5]), np.array([-0.05, -0.1]), np.array([0.2, 0.3])
+
+
+def _approach_check(co, breaks, x, vlo, vhi, alo, ahi):
+    """What the reference's test asserts (l.133-151): ConstAccel parametrizer (tp:parametrizer/const_accel.cpp) evaluated
+    at 11 times LinSpaced over its interval; every joint velocity and acceleration inside its box x (1 + 0.01)."""
+    G = len(x); s = np.linspace(breaks[0], breaks[-1], G); sd = np.sqrt(x)
+    ts = np.concatenate([[0.0], np.cumsum(2 * np.diff(s) / (sd[1:] + sd[:-1]))])
+    us = 0.5 * np.diff(x) / np.diff(s)
+    for t in np.linspace(ts[0], ts[-1], 11):
+        k = min(max(int(np.searchsorted(ts[1:-1], t, side="left")), 0), G - 2)
+        d = t - ts[k]
+        v = sd[k] + d * us[k]
+        ss = min(max(s[k] + d * sd[k] + 0.5 * d * d * us[k], breaks[0]), breaks[-1])
+        seg = min(int(np.searchsorted(breaks, ss, side="right")) - 1, len(breaks) - 2)
+        e = ss - breaks[seg]
+        q1 = 3 * co[seg, 0] * e * e + 2 * co[seg, 1] * e + co[seg, 2]
+        q2 = 6 * co[seg, 0] * e + 2 * co[seg, 1]
+        vel, acc = q1 * v, q2 * v * v + q1 * us[k]
+        assert np.all(vel >= vlo * 1.01) and np.all(vel <= vhi * 1.01), (t, vel)
+        assert np.all(acc >= alo * 1.01) and np.all(acc <= ahi * 1.01), (t, acc)
+
+
+def test_reference_quickstart_example_on_the_oracle(oracle):
+    co, breaks, vlo, vhi, alo, ahi = _approach_case()
+    rc, K, x, _, _ = oracle.toppra_ppoly(co, breaks, 101, vlo, vhi, alo, ahi, 1)
+    assert rc == 0   # ReturnCode::OK (l.79, l.103)
+    _approach_check(co, breaks, x, vlo, vhi, alo, ahi)
+
+
 # ------------------------------------------------------------------ GPU
 @pytest.fixture(scope="module")
 def planner():
@@ -165,6 +209,19 @@ def test_toppra_ppoly_many_dof_matches_oracle(planner, oracle, m, interp):
             np.testing.assert_array_equal(res["K_lo"][:, p], K[:, 0]); np.testing.assert_array_equal(res["K_hi"][:, p], K[:, 1])
             np.testing.assert_array_equal(res["x"][:, p], x)
     assert 0 in seen
+
+
+@pytest.mark.gpu
+def test_reference_quickstart_example_on_the_kernel(planner, oracle):
+    """test_toppra_approach.cpp on toppra_ppoly_kernel<2, true> (ten-row stage LPs): the reference's assertions on the
+    kernel's own parametrization, and the oracle's bits."""
+    co, breaks, vlo, vhi, alo, ahi = _approach_case()
+    res = planner.toppra_ppoly(co[None], breaks, 101, vlo, vhi, alo, ahi, interpolation=1, feasible=False)
+    assert res["status"][0] == 0
+    _approach_check(co, breaks, res["x"][:, 0], vlo, vhi, alo, ahi)
+    rc, K, x, _, _ = oracle.toppra_ppoly(co, breaks, 101, vlo, vhi, alo, ahi, 1)
+    np.testing.assert_array_equal(res["x"][:, 0], x)
+    np.testing.assert_array_equal(res["K_hi"][:, 0], K[:, 1]); np.testing.assert_array_equal(res["K_lo"][:, 0], K[:, 0])
 
 
 @pytest.mark.gpu
