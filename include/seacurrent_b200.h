@@ -11,6 +11,7 @@
  *   bezier_spline::from_path            sc:402, sc:599-683   -> ctrl_x / ctrl_y
  *   bezier_spline::arclength            sc:413, sc:767-896   -> arclen_total / arclen_table
  *   gen_vel_prof<1>                     sc:1191-1265         -> status, K_lo/K_hi, x, t, s_* streams
+ *   gen_vel_prof<N>, N > 1              sc:1191-1265         -> scb_gen_vel_prof (below)
  *     TOPPRA::computePathParametrization tp:algorithm.cpp:14-26 (ReturnCode tp:algorithm.hpp:13-32)
  *     parametrizer::Spline              tp:parametrizer/spline.cpp:10-45
  *   bezier_spline::resample             sc:419, sc:898-1005  -> px / py, s_px / s_py
@@ -317,7 +318,7 @@ void scb_shard_range(int32_t P, int32_t r, int32_t R, int32_t* lo, int32_t* hi);
 int scb_multi_get_timing(scb_multi* m, int32_t r, scb_timing* out);
 
 /* ---- toppra on a caller-supplied path (what the reference's toppra does beyond the one configuration gen_vel_prof<1>
- * uses, as far as the six-row stage LP of the kernels reaches): a piecewise-cubic path of one or two degrees of freedom
+ * uses): a piecewise-cubic path of one to SCB_MAX_DOF degrees of freedom
  * (PiecewisePolyPath, tp:geometric_path/piecewise_poly_path.cpp:215-252), box limits per degree of freedom, N + 1 =
  * G gridpoints LinSpaced over the path interval, collocation or interpolation discretisation
  * (tp:constraint.hpp:13-14), the reference's Seidel sequence operation for operation; controllable sets, forward
