@@ -92,3 +92,9 @@ def test_product_never_imports_oracle():
                 if f.endswith((".py", ".cu", ".cuh", ".inl", ".h", ".hpp")) or f == "Makefile":
                     m = pat.search(open(os.path.join(dp, f)).read())
                     assert m is None, (dp, f, m.group(0))
+
+
+def test_graft_entry_build_agrees_with_the_header():
+    """__graft_entry__.build() (the driver's build check) must not pin a stale ABI version."""
+    import __graft_entry__ as g
+    g.build()
