@@ -10,6 +10,7 @@
 // Reference call sequence replaced (examples/json_test.cpp:28-58):
 //   from_path -> arclength -> gen_vel_prof<1> -> resample -> angular_velocity.
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <thread>
@@ -55,6 +56,8 @@ struct scb_ctx {
   // results retained by scb_plan_batch_summary
   scb_batch_out kept = {};
   int kept_P = 0, kept_W = 0, kept_G = 0, kept_rec32 = 0;
+  cudaStream_t hi = nullptr;            // highest-priority stream: the latency-bound stages (toppra, parametrizer) run here
+  cudaEvent_t ev_hi[2] = {};            // hand-over stream -> hi, hi -> stream
   cudaStream_t copy_stream = nullptr;   // D2H of chunk c while chunk c+1 computes (scb_plan_batch)
   cudaEvent_t ev[9] = {}, ev_done[2] = {}, ev_copied[2] = {};
   Slot slot[2 * SL_COUNT];              // second half: mirror set 1 of the chunked host call
@@ -229,6 +232,14 @@ int run_device(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, i
       if ((rc = ensure(ctx, SL_XB, gp8, &dXb))) return rc;
       if ((rc = ensure(ctx, SL_CP, gp8, &dCp))) return rc;
     }
+    // the latency-bound stages go to the ctx's high-priority stream (own stream only: a caller's stream stays single)
+    const bool use_hi = ctx->hi && st == ctx->stream;
+    cudaStream_t st0 = st;
+    if (use_hi) {
+      SCB_CUDA(cudaEventRecord(ctx->ev_hi[0], st));
+      SCB_CUDA(cudaStreamWaitEvent(ctx->hi, ctx->ev_hi[0], 0));
+      st = ctx->hi;
+    }
     ToppraArgs t{};
     t.P = P; t.G = G; t.L = dL; t.vel_lo = in->vel_lo; t.vel_hi = in->vel_hi;
     t.vel_lo_grid = in->vel_lo_grid; t.vel_hi_grid = in->vel_hi_grid;
@@ -262,6 +273,11 @@ int run_device(scb_ctx* ctx, const scb_batch_in* in, const scb_batch_out* out, i
     q.param_mode = in->param_mode;
     launch_param<R>(q, st);
     ++launches;
+    if (use_hi) {
+      SCB_CUDA(cudaEventRecord(ctx->ev_hi[1], st));
+      st = st0;
+      SCB_CUDA(cudaStreamWaitEvent(st, ctx->ev_hi[1], 0));
+    }
   } else {
     SCB_CUDA(cudaMemsetAsync(dFail, 0xff, (size_t)P * 4, st));
     SCB_CUDA(cudaEventRecord(ctx->ev[3], st));
@@ -369,6 +385,23 @@ int scb_create(scb_ctx** out, const scb_config* cfg) {
   }
   for (auto& e : ctx->ev) if (cudaEventCreate(&e) != cudaSuccess) { scb_destroy(ctx); return SCB_E_CUDA; }
   if (cudaEventCreateWithFlags(&ctx->ev_last, cudaEventDisableTiming) != cudaSuccess) { scb_destroy(ctx); return SCB_E_CUDA; }
+  {
+    // Priority hand-over (SCB_PRIO=0 turns it off): the block scheduler offers a freed SM slot to the highest-priority
+    // pending work, so with several batches in flight the toppra / parametrizer CTAs of one batch start beside the
+    // FP64-bound path / arc kernels of another instead of behind their whole grid.
+    const char* e = getenv("SCB_PRIO");
+    if (!e || atoi(e) != 0) {
+      int least = 0, greatest = 0;
+      if (cudaDeviceGetStreamPriorityRange(&least, &greatest) == cudaSuccess && greatest < least &&
+          cudaStreamCreateWithPriority(&ctx->hi, cudaStreamNonBlocking, greatest) == cudaSuccess) {
+        for (auto& ev : ctx->ev_hi)
+          if (cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) != cudaSuccess) { scb_destroy(ctx); return SCB_E_CUDA; }
+      } else {
+        cudaGetLastError();
+        ctx->hi = nullptr;
+      }
+    }
+  }
   *out = ctx;
   return SCB_OK;
 }
@@ -385,6 +418,8 @@ int scb_destroy(scb_ctx* ctx) {
   for (auto& e : ctx->ev_done) if (e) cudaEventDestroy(e);
   for (auto& e : ctx->ev_copied) if (e) cudaEventDestroy(e);
   if (ctx->copy_stream) { cudaStreamSynchronize(ctx->copy_stream); cudaStreamDestroy(ctx->copy_stream); }
+  if (ctx->hi) { cudaStreamSynchronize(ctx->hi); cudaStreamDestroy(ctx->hi); }
+  for (auto& e : ctx->ev_hi) if (e) cudaEventDestroy(e);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
   return SCB_OK;
