@@ -231,8 +231,6 @@ int arc_paths_per_cta(int W, int spline_mode, int real_size, size_t& smem, bool*
 }
 
 template <class R, int DEG, bool TS> static void launch_arc_t(const PathArgs& a, int grid, size_t smem, cudaStream_t st) {
-  const char* e = getenv("SCB_ARC_SMEM_KB");   // experiment: see SCB_PATH_SMEM_KB in path_lane_kernel.cu
-  if (e && (size_t)atoi(e) * 1024 > smem) smem = (size_t)atoi(e) * 1024;
   cudaFuncSetAttribute(arc_kernel<R, DEG, TS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (TS) cudaFuncSetAttribute(arc_kernel<R, DEG, TS>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
   arc_kernel<R, DEG, TS><<<grid, kArcThreads, smem, st>>>(a);

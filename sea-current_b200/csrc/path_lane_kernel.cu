@@ -654,17 +654,7 @@ template <class S> void launch_path_lane(const PathArgs& a0, int spline_mode, in
     const int per_cta = PB * kLaneWarps, grid = (a.P + per_cta - 1) / per_cta;
     if (spline_mode == SCB_REF_CUBIC) path_lane_kernel<S, 3, false><<<grid, kLaneWarps * 32, smem, st>>>(a);
     else if (a.n_coll_edges > 0) path_lane_kernel<S, 5, true><<<grid, kLaneWarps * 32, smem, st>>>(a);
-    else {
-      // SCB_PATH_SMEM_KB (experiment): dynamic shared memory per CTA, i.e. a cap on the CTAs per SM, so that the other
-      // in-flight batch's latency-bound kernels find registers beside this kernel's
-      const char* e = getenv("SCB_PATH_SMEM_KB");
-      const size_t want = e ? (size_t)atoi(e) * 1024 : 0;
-      if (want > smem) {
-        cudaFuncSetAttribute(path_lane_kernel<S, 5, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)want);
-        smem = want;
-      }
-      path_lane_kernel<S, 5, false><<<grid, kLaneWarps * 32, smem, st>>>(a);
-    }
+    else path_lane_kernel<S, 5, false><<<grid, kLaneWarps * 32, smem, st>>>(a);
   } else {
     const int T = (a.W + 31) / 32 * 32;
     if (spline_mode == SCB_REF_CUBIC) {
