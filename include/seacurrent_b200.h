@@ -42,7 +42,7 @@
 extern "C" {
 #endif
 
-#define SCB_VERSION 201 /* 0.2.1 */
+#define SCB_VERSION 202 /* 0.2.2 */
 
 /* API-level error codes (function return values) */
 enum {
@@ -50,7 +50,8 @@ enum {
   SCB_E_INVALID = -1,   /* bad argument (NULL, P/W/G out of range, capacity exceeded) */
   SCB_E_NO_DEVICE = -2, /* no CUDA device / not an sm_100 part */
   SCB_E_CUDA = -3,      /* CUDA runtime error; see scb_last_cuda_error */
-  SCB_E_NOMEM = -4
+  SCB_E_NOMEM = -4,
+  SCB_E_TOO_LARGE = -5  /* scb_param_static: G * P beyond the static scratch (SCB_STATIC_MAX_GP) */
 };
 
 /* per-problem status[p].  0-5 are toppra's ReturnCode (tp:algorithm.hpp:13-32). */
@@ -396,6 +397,28 @@ typedef struct scb_ndof_out {
   double* s_acc;
 } scb_ndof_out;
 int scb_gen_vel_prof(scb_ctx* ctx, const scb_ndof_in* in, const scb_ndof_out* out);
+
+/* ---- Allocation-free parametrizer.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The spline parametrizer of the timing stage (what scb_plan_batch_device runs after the toppra passes:
+ * tp:parametrizer/spline.cpp:10-45 as a Thomas solve) on the CALLER's device arrays, with its two [G][P] scratch arrays
+ * in one file-scope device array of the library: G * P <= SCB_STATIC_MAX_GP (2^20; 16 MiB that every GPU which loads
+ * the library holds until exit).  The call allocates nothing (no cudaMalloc / cudaFree, no context, no stream or event
+ * creation), enqueues one kernel on `stream` (a cudaStream_t of the CURRENT device; NULL = the default stream) and
+ * does not synchronise.  All pointers are device pointers of the current device, FP64, [G][P] arrays problem-fastest:
+ *   path_len [P], x [G][P] (sdot^2 at the gridpoints), vel_start / vel_end [P] or NULL (= 0): inputs;
+ *   status [P]: in / out - a problem whose status is not SCB_ST_OK on entry gets an all-zero record; the kernel
+ *               sets SCB_ST_ERR_TIME_KNOTS where the knot times do not increase;
+ *   t [G][P] (required: the knot times are the sweep's own state), v, a [G][P] or NULL, T_total [P] or NULL: outputs.
+ * Results are bit-identical to the t / v / a / T_total of scb_plan_batch_device on the same x and path length.
+ * Every call shares the scratch array, which keeps the last call's contents (nothing in it has to start at zero: a
+ * call reads only what it wrote itself): calls that OVERLAP on the GPU race - order them on one stream or with events.
+ * Returns SCB_E_TOO_LARGE beyond the maximum, SCB_E_INVALID for bad arguments, SCB_E_CUDA for a runtime error;
+ * scb_static_last_error() has the text (per host thread). */
+#define SCB_STATIC_MAX_GP (1 << 20)
+int scb_param_static(int32_t P, int32_t G, const double* path_len, const double* x, const double* vel_start,
+                     const double* vel_end, int32_t* status, double* t, double* v, double* a, double* T_total, void* stream);
+const char* scb_static_last_error(void);
 
 /* ---- Global planner front end: FMT* over a shared set of sampled nodes, one CTA per query.
  * Replaces planning_space::fast_marching_trees (sc:1339-1407) with cost (sc:1315-1326), near (sc:1328-1337),

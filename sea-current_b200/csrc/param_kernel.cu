@@ -14,6 +14,8 @@
 // Arc length -> curve parameter is an exact inversion of the arc-length table (search + Newton
 // on a 4-point Gauss-Legendre integral of |B'|), not the reference's float Chebyshev fit
 // (DESIGN.md "Deviations").  All gridpoint / sample arrays are [n][P], problem index fastest.
+#include <cstdio>
+
 #include "scb_common.cuh"
 
 namespace scb {
@@ -500,3 +502,79 @@ template void launch_sample<double>(const SampleArgs&, cudaStream_t);
 template void launch_sample<float>(const SampleArgs&, cudaStream_t);
 
 }  // namespace scb
+
+// ---------------------------------------------------------------------------------------------------------------
+// Allocation-free entry (include/seacurrent_b200.h: scb_param_static).  No counterpart in the reference; added
+// for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops,
+// harnesses that forbid it).  The Thomas scratch of the spline parametrizer (elimination coefficients c' and the
+// right-hand sides / unknowns X, [G][P] doubles each) lives in ONE file-scope device array of fixed size; every GPU
+// that loads the library holds its 16 MiB until exit.  The kernel is param_kernel<double, double, DB> itself: same
+// arithmetic, same bits as the timing stage of scb_plan_batch_device.
+//   * Nothing in the scratch has to start at zero: every element a problem's backward sweep reads (rows 0..N of X,
+//     rows 0..N-1 of c') was written by the same thread's forward sweep of the SAME call, so the previous call's
+//     contents are never observed.
+//   * Every call shares the array: two calls that overlap on the GPU (different streams, or the same stream from two
+//     host threads without ordering) race on it.  Order them on one stream or with events.
+namespace scb {
+namespace {
+__device__ __align__(256) double g_param_static_scratch[2 * (size_t)SCB_STATIC_MAX_GP];
+
+constexpr int kStaticMaxDevices = 64;
+double* g_static_ptr[kStaticMaxDevices] = {};   // device address of the array on each device (set once per device)
+thread_local char g_static_err[256] = {0};
+
+int static_fail(cudaError_t e, const char* where) {
+  snprintf(g_static_err, sizeof g_static_err, "%s: %s", where, cudaGetErrorString(e));
+  cudaGetLastError();
+  return SCB_E_CUDA;
+}
+}  // namespace
+}  // namespace scb
+
+extern "C" {
+
+const char* scb_static_last_error(void) { return scb::g_static_err; }
+
+int scb_param_static(int32_t P, int32_t G, const double* path_len, const double* x, const double* vel_start,
+                     const double* vel_end, int32_t* status, double* t, double* v, double* a, double* T_total, void* stream) {
+  using namespace scb;
+  g_static_err[0] = 0;
+  if (P < 0 || G < 2 || !path_len || !x || !status || !t) {
+    snprintf(g_static_err, sizeof g_static_err, "scb_param_static: bad argument (P >= 0, G >= 2, path_len, x, status and t are required)");
+    return SCB_E_INVALID;
+  }
+  if ((long long)P * (long long)G > (long long)SCB_STATIC_MAX_GP) {
+    snprintf(g_static_err, sizeof g_static_err, "scb_param_static: G * P = %lld exceeds the static scratch (SCB_STATIC_MAX_GP = %d)",
+             (long long)P * (long long)G, (int)SCB_STATIC_MAX_GP);
+    return SCB_E_TOO_LARGE;
+  }
+  if (P == 0) return SCB_OK;
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return static_fail(e, "cudaGetDevice");
+  if (dev < 0 || dev >= kStaticMaxDevices) {
+    snprintf(g_static_err, sizeof g_static_err, "scb_param_static: device ordinal %d beyond %d", dev, kStaticMaxDevices);
+    return SCB_E_INVALID;
+  }
+  // The array's name is a host-side stand-in here, not a device address: ask the runtime for the address on THIS
+  // device (the current one), once per device.  Racing first calls from two host threads store the same value.
+  double* scratch = g_static_ptr[dev];
+  if (!scratch) {
+    e = cudaGetSymbolAddress((void**)&scratch, g_param_static_scratch);
+    if (e != cudaSuccess || !scratch) return static_fail(e, "cudaGetSymbolAddress(g_param_static_scratch)");
+    g_static_ptr[dev] = scratch;
+  }
+  const size_t gp = (size_t)G * (size_t)P;
+  ParamArgs q{};
+  q.P = P; q.G = G; q.L = path_len; q.vel_start = vel_start; q.vel_end = vel_end; q.x = x; q.kappa = nullptr;
+  q.t = nullptr;           // the caller's FP64 t array is the knot-time state itself, as in scb_plan_batch_device
+  q.v = v; q.a = a; q.omega = nullptr; q.rec_f32 = 0;
+  q.t_buf = t; q.X_buf = scratch; q.cp_buf = scratch + gp;
+  q.T_total = T_total; q.status = status; q.keep_X = 0; q.param_mode = SCB_PARAM_SPLINE;
+  launch_param<double>(q, (cudaStream_t)stream);
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return static_fail(e, "param_kernel launch");
+  return SCB_OK;
+}
+
+}  // extern "C"

@@ -348,6 +348,7 @@ const char* scb_strerror(int code) {
     case SCB_E_NO_DEVICE: return "no usable sm_100 CUDA device (there is no CPU fallback)";
     case SCB_E_CUDA: return "CUDA runtime error (see scb_last_cuda_error)";
     case SCB_E_NOMEM: return "out of device memory";
+    case SCB_E_TOO_LARGE: return "G * P exceeds the static scratch of the allocation-free entry (SCB_STATIC_MAX_GP)";
     default: return "unknown error";
   }
 }

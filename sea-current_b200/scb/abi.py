@@ -138,6 +138,8 @@ SYMBOLS = {
     "scb_fmt_batch": (C.c_int, [C.c_void_p, C.POINTER(ScbFmtIn), C.POINTER(ScbFmtOut)]),
     "scb_toppra_ppoly": (C.c_int, [C.c_void_p, C.POINTER(ScbPpolyIn), C.POINTER(ScbPpolyOut)]),
     "scb_gen_vel_prof": (C.c_int, [C.c_void_p, C.POINTER(ScbNdofIn), C.POINTER(ScbNdofOut)]),
+    "scb_param_static": (C.c_int, [C.c_int32, C.c_int32] + [C.c_void_p] * 10),
+    "scb_static_last_error": (C.c_char_p, []),
     "scb_alloc_pinned": (C.c_void_p, [C.c_size_t]),
     "scb_free_pinned": (None, [C.c_void_p]),
     "scb_get_timing": (C.c_int, [C.c_void_p, C.POINTER(ScbTiming)]),

@@ -26,7 +26,7 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(lib, n), n
     assert sorted(abi.SYMBOLS) == names
-    assert lib.scb_version() == 201
+    assert lib.scb_version() == 202
 
 
 def test_struct_layouts_match_header(tmp_path):
