@@ -27,6 +27,8 @@
 // only reproducible where the gradient is resolved far below the decision threshold (1e-9 of the
 // largest component) -- like toppra's feasibility tolerances this does not exist in FP32
 // (DESIGN.md "Precision modes").  S = float only changes what is loaded and stored.
+#include <cstdlib>
+
 #include "lau_nodes_device.h"
 #include "path_device.cuh"
 
@@ -37,7 +39,10 @@ namespace {
 constexpr unsigned kAll = 0xffffffffu;
 constexpr int kLaneWarps = 4;     // warps per CTA
 constexpr int kLaneSlots = 15;    // private FP64 slots per lane in shared memory:
-enum { kSe, kPe, kSwx, kSwy, kPwx, kPwy, kW0x, kW0y, kMag, kBe, kBwx, kBwy, kAlpha, kAnPrev, kApNext };
+enum { kSe, kPe, kSwx, kSwy, kPwx, kPwy, kW0x, kW0y, kMag, kBe, kBwx, kBwy, kAlpha, kAnPrev, kApNext,
+       // SHADOW mapping (path_pair_kernel): state of the path's LAST waypoint, carried by the lane of its last segment
+       kSeS, kPeS, kBeS, kBtSx, kBtSy, kSx, kSy, kAnPrevS };
+constexpr int kPairSlots = 23;
 
 
 // What one cost node contributes, given B' = (x1, y1) and B'' = (x2, y2) there: the weighted integrand (returned)
@@ -383,16 +388,84 @@ struct CtaComm {
   __device__ __forceinline__ bool path_any(bool f) { return __syncthreads_or(f ? 1 : 0) != 0; }
 };
 
+// PairComm: paths packed over a PAIR of warps (64 lanes, one lane per SEGMENT: path_pair_kernel), so a path may straddle
+// the two warps.  Everything goes through a double-buffered exchange area of the pair and ONE named barrier of 64
+// threads per exchange (the same one-exchange-ahead argument as CtaComm).  Sums run over the path's lanes in lane
+// order, like WarpComm's: the bits of the cost do not depend on the mapping.
+struct PairComm {
+  static constexpr int kMaxVals = 6, T = 64;
+  int tid, base, n, bar;  // lane within the pair, first lane and number of lanes of this lane's path, barrier id
+  double* xbuf;           // [2][kMaxVals][64]
+  double* st;
+  int sstride;
+  int flip = 0;
+  template <int N> __device__ __forceinline__ const double* stage(const double (&v)[N]) {
+    static_assert(N <= kMaxVals, "exchange area too small");
+    double* b = xbuf + (size_t)flip * kMaxVals * T;
+    flip ^= 1;
+#pragma unroll
+    for (int k = 0; k < N; ++k) b[k * T + tid] = v[k];
+    asm volatile("bar.sync %0, %1;" ::"r"(bar), "r"(T) : "memory");
+    return b;
+  }
+  template <int N> __device__ __forceinline__ void prev(const double (&v)[N], double (&pv)[N]) {
+    const double* b = stage(v);
+    const int j = max(tid - 1, 0);
+#pragma unroll
+    for (int k = 0; k < N; ++k) pv[k] = b[k * T + j];
+  }
+  template <int N> __device__ __forceinline__ void next(const double (&v)[N], double (&nx)[N]) {
+    const double* b = stage(v);
+    const int j = min(tid + 1, T - 1);
+#pragma unroll
+    for (int k = 0; k < N; ++k) nx[k] = b[k * T + j];
+  }
+  template <int N> __device__ __forceinline__ void both(const double (&v)[N], double (&pv)[N], double (&nx)[N]) {
+    const double* b = stage(v);
+    const int jm = max(tid - 1, 0), jp = min(tid + 1, T - 1);
+#pragma unroll
+    for (int k = 0; k < N; ++k) { pv[k] = b[k * T + jm]; nx[k] = b[k * T + jp]; }
+  }
+  __device__ __forceinline__ double path_sum(double v, int cnt) {
+    const double a[1] = {v};
+    const double* b = stage(a);
+    double acc = 0;
+    for (int s = 0; s < cnt; ++s) acc += b[min(base + s, T - 1)];
+    return acc;
+  }
+  __device__ __forceinline__ void path_max2(double& a, double& c) {
+    const double v[2] = {a, c};
+    const double* b = stage(v);
+    double ma = 0, mb = 0;
+    for (int k = 0; k < n; ++k) { const int j = min(base + k, T - 1); ma = fmax(ma, b[j]); mb = fmax(mb, b[T + j]); }
+    a = ma; c = mb;
+  }
+  __device__ __forceinline__ bool path_any(bool f) {
+    const double v[1] = {f ? 1.0 : 0.0};
+    const double* b = stage(v);
+    double m = 0;
+    for (int k = 0; k < n; ++k) m = fmax(m, b[min(base + k, T - 1)]);
+    return m != 0;
+  }
+};
+
 // One waypoint lane from the waypoints to the control points of its segment.  p: problem, i: waypoint index,
 // own: the lane has a waypoint.  Every lane of the warp / CTA runs this to the end (collectives inside).
 // COLL: the collision term inside the optimiser loop is compiled in (a separate instantiation, so that the default
 // kernel stays the register-exact code it was: 127 registers, no stack traffic in the loop)
-template <class S, int DEG, class Comm, bool COLL>
+// SHADOW (path_pair_kernel): one lane per SEGMENT - waypoint i and segment i for i = 0 .. nseg-1 - and the lane of the
+// last segment also carries the path's last waypoint (its elongation is a parameter of the optimiser like any other):
+// what the lane of waypoint nseg would have computed and handed to its neighbour is computed here, with the same
+// expressions in the same order, and substituted for the neighbour's values.  Every lane executes the shadow code
+// (a handful of instructions per iteration against ~1,600 for the segment's cost); only the last-segment lane keeps it.
+template <class S, int DEG, class Comm, bool COLL, bool SHADOW = false>
 __device__ __forceinline__ void lane_path(const PathArgs& g, Comm& cm, int p, int i, bool own, const CollEdges& ce) {
+  static_assert(!(SHADOW && (COLL || DEG != 5)), "the shadow mapping is built for the plain quintic optimiser");
   constexpr int NC = DEG + 1;
   const int W = g.W, nseg = W - 1, ss = cm.sstride;
   double* st = cm.st;
   const bool first = i == 0, last = i == nseg;
+  const bool hasS = SHADOW && own && i == nseg - 1;
   const bool seg = own && !last;          // this lane also owns segment i
   const bool inner = own && !first && !last;
 
@@ -405,8 +478,13 @@ __device__ __forceinline__ void lane_path(const PathArgs& g, Comm& cm, int p, in
     cm.both(v, a, b);
     xm = a[0]; ym = a[1]; xp = b[0]; yp = b[1];
   }
+  double sx = 0, sy = 0;  // SHADOW: the last waypoint
+  if constexpr (SHADOW) {
+    if (hasS) { sx = (double)((const S*)g.wx)[(size_t)p * W + nseg]; sy = (double)((const S*)g.wy)[(size_t)p * W + nseg]; xp = sx; yp = sy; }
+  }
   const double dprev = dist2<double>(xm, ym, wx, wy), dnext = dist2<double>(wx, wy, xp, yp);
-  const bool bad = cm.path_any(own && (!isfinite(wx) || !isfinite(wy) || (seg && !(dnext > 0))));
+  const bool bad = cm.path_any((own && (!isfinite(wx) || !isfinite(wy) || (seg && !(dnext > 0)))) ||
+                               (hasS && (!isfinite(sx) || !isfinite(sy))));
 
   // ---- tangents (sc:343-377, 606-638)
   double btx, bty;
@@ -422,14 +500,24 @@ __device__ __forceinline__ void lane_path(const PathArgs& g, Comm& cm, int p, in
     calc_tangent<double>(xm, ym, wx, wy, xp, yp, btx, bty);
   }
   if (g.n_edges > 0) shrink_tangent<double, S>(wx, wy, (const S*)g.edges, g.n_edges, btx, bty);  // sc:615, 620, 637
+  double bsx = 0, bsy = 0;  // SHADOW: base tangent of the last waypoint (the `last` branch above, seen from its neighbour)
+  if constexpr (SHADOW) {
+    const double dps = dist2<double>(wx, wy, sx, sy);
+    const double dx = sx - wx, dy = sy - wy, n = sqrt(dx * dx + dy * dy);
+    bsx = (0.5 * dps) * (dx / n); bsy = (0.5 * dps) * (dy / n);
+  }
 
   // T and A of this waypoint and the next one: what both the optimiser and the final control points need
   double alpha = 0;
+  double eS = 1.0;  // SHADOW: elongation of the last waypoint
   auto waypoint_TA = [&](double e, double& Tx, double& Ty, double& Txp, double& Typ, double& wxp, double& wyp,
                          double& Ax, double& Ay, double& Axp, double& Ayp) {
     Tx = e * btx; Ty = e * bty;
     const double v[4] = {Tx, Ty, wx, wy}; double pv[4], nx[4];
     cm.both(v, pv, nx);
+    if constexpr (SHADOW) {
+      if (hasS) { nx[0] = eS * st[kBtSx * ss]; nx[1] = eS * st[kBtSy * ss]; nx[2] = st[kSx * ss]; nx[3] = st[kSy * ss]; }
+    }
     Txp = nx[0]; Typ = nx[1]; wxp = nx[2]; wyp = nx[3];
     const double pvx = 6.0 * (pv[2] - wx) + 4.0 * Tx + 2.0 * pv[0], pvy = 6.0 * (pv[3] - wy) + 4.0 * Ty + 2.0 * pv[1];
     const double nxx = 6.0 * (wxp - wx) - 4.0 * Tx - 2.0 * Txp, nxy = 6.0 * (wyp - wy) - 4.0 * Ty - 2.0 * Typ;
@@ -437,6 +525,11 @@ __device__ __forceinline__ void lane_path(const PathArgs& g, Comm& cm, int p, in
     Ay = first ? nxy : (last ? pvy : alpha * pvy + (1.0 - alpha) * nxy);
     const double a2[2] = {Ax, Ay}; double an2[2];
     cm.next(a2, an2);
+    if constexpr (SHADOW) {
+      if (hasS) {  // A of the last waypoint: the "previous" cubic alone (the `last` case of the lane it replaces)
+        an2[0] = 6.0 * (wx - wxp) + 4.0 * Txp + 2.0 * Tx; an2[1] = 6.0 * (wy - wyp) + 4.0 * Typ + 2.0 * Ty;
+      }
+    }
     Axp = an2[0]; Ayp = an2[1];
   };
 
@@ -459,6 +552,13 @@ __device__ __forceinline__ void lane_path(const PathArgs& g, Comm& cm, int p, in
       const double v[2] = {ap, an}; double pv[2], nx[2];
       cm.both(v, pv, nx);
       an_prev = pv[1]; ap_next = nx[0];
+      if constexpr (SHADOW) {
+        if (hasS) ap_next = 1.0;  // the last waypoint's weight of its "previous" cubic
+        st[kSeS * ss] = o.step_e; st[kPeS * ss] = 0; st[kBeS * ss] = o.e_init;
+        st[kBtSx * ss] = bsx; st[kBtSy * ss] = bsy; st[kSx * ss] = sx; st[kSy * ss] = sy;
+        st[kAnPrevS * ss] = an;   // ... and the weight of this lane's waypoint's "next" cubic, which it sees as an_prev
+        eS = o.e_init;
+      }
       st[kAlpha * ss] = alpha; st[kAnPrev * ss] = an_prev; st[kApNext * ss] = ap_next;
       e = o.e_init;
     }
@@ -487,6 +587,7 @@ __device__ __forceinline__ void lane_path(const PathArgs& g, Comm& cm, int p, in
       }
       const bool better = iter == 0 || J < cost;
       if (better) { cost = J; st[kBe * ss] = e; st[kBwx * ss] = wx; st[kBwy * ss] = wy; }
+      if constexpr (SHADOW) { if (better) st[kBeS * ss] = eS; }
       if (iter == K) break;
       // ---- chain rule: D -> (T, A, W) of the segment's two waypoints, then A -> (T, W) of the neighbours
       double gdx[5], gdy[5];
@@ -497,10 +598,14 @@ __device__ __forceinline__ void lane_path(const PathArgs& g, Comm& cm, int p, in
       }
       // end side of the segment (waypoint i+1) is picked up by the next lane
       double ein[6];
+      double gTSx = 0, gTSy = 0, gASx = 0, gASy = 0;  // SHADOW: gradient w.r.t. T and A of the last waypoint
       {
         const double eout[6] = {gdx[3] + gdx[4] - 2.0 * gdx[2], gdy[3] + gdy[4] - 2.0 * gdy[2], 0.25 * (gdx[2] - gdx[3]),
                                 0.25 * (gdy[2] - gdy[3]), 5.0 * gdx[2], 5.0 * gdy[2]};
         cm.prev(eout, ein);
+        if constexpr (SHADOW) {  // the lane it replaces adds what it receives to its own (zero) segment part
+          gTSx = 0.0 + eout[0]; gTSy = 0.0 + eout[1]; gASx = 0.0 + eout[2]; gASy = 0.0 + eout[3];
+        }
       }
       double gTx = gdx[0] + gdx[1] - 2.0 * gdx[2], gTy = gdy[0] + gdy[1] - 2.0 * gdy[2];
       double gAx = 0.25 * (gdx[1] - gdx[2]), gAy = 0.25 * (gdy[1] - gdy[2]);
@@ -510,6 +615,13 @@ __device__ __forceinline__ void lane_path(const PathArgs& g, Comm& cm, int p, in
         const double ap = first ? 0.0 : (last ? 1.0 : alpha), an = last ? 0.0 : (first ? 1.0 : 1.0 - alpha);
         const double v[2] = {gAx, gAy}; double gm[2], gp[2];
         cm.both(v, gm, gp);
+        if constexpr (SHADOW) {
+          if (hasS) { gp[0] = gASx; gp[1] = gASy; }
+          // the last waypoint: ap = 1, an = 0, so k4 = 4; then its `!first` part with gm = this lane's gA
+          const double aS = st[kAnPrevS * ss];
+          gTSx = fma(4.0, gASx, gTSx); gTSy = fma(4.0, gASy, gTSy);
+          gTSx = fma(-2.0 * aS, gAx, gTSx); gTSy = fma(-2.0 * aS, gAy, gTSy);
+        }
         const double k6 = 6.0 * (ap + an), k4 = 4.0 * (ap - an);
         gWx = fma(-k6, gAx, gWx); gWy = fma(-k6, gAy, gWy); gTx = fma(k4, gAx, gTx); gTy = fma(k4, gAy, gTy);
         if (!first) {  // waypoint i is the "next" of i-1
@@ -524,6 +636,12 @@ __device__ __forceinline__ void lane_path(const PathArgs& g, Comm& cm, int p, in
       const double ge = gTx * btx + gTy * bty;
       // largest gradient component of each class over the path (components below 1e-9 of it count as zero)
       double gemax = own ? fabs(ge) : 0.0, gwmax = inner ? fmax(fabs(gWx), fabs(gWy)) : 0.0;
+      double geS = 0;
+      if constexpr (SHADOW) {
+        const double bx = st[kBtSx * ss], by = st[kBtSy * ss];
+        geS = gTSx * bx + gTSy * by;
+        if (hasS) gemax = fmax(gemax, fabs(geS));
+      }
       cm.path_max2(gemax, gwmax);
       // ---- A7: iRPROP-.  A rejected (colliding) trial, once a collision-free iterate exists: back to the best such
       // iterate, every step halved, gradient memory cleared.  The lanes of a rejected path still walked the chain rule
@@ -537,6 +655,13 @@ __device__ __forceinline__ void lane_path(const PathArgs& g, Comm& cm, int p, in
         const double ei = e + rprop_step<double>(gi, pe, se, 1e-6, 1.0);
         e = reject ? st[kBe * ss] : fmin((double)o.e_max, fmax((double)o.e_min, ei));
         st[kSe * ss] = reject ? fmax(0.5 * se0, 1e-6) : se; st[kPe * ss] = reject ? 0.0 : pe;
+        if constexpr (SHADOW) {  // the same step for the last waypoint's elongation
+          double seS = st[kSeS * ss], peS = st[kPeS * ss];
+          const double giS = fabs(geS) <= te ? 0.0 : geS;
+          const double eiS = eS + rprop_step<double>(giS, peS, seS, 1e-6, 1.0);
+          eS = fmin((double)o.e_max, fmax((double)o.e_min, eiS));
+          st[kSeS * ss] = seS; st[kPeS * ss] = peS;
+        }
         if (o.move_waypoints && inner) {
           const double mag = st[kMag * ss], w0x = st[kW0x * ss], w0y = st[kW0y * ss];
           const double swx0 = st[kSwx * ss], swy0 = st[kSwy * ss];
@@ -553,6 +678,7 @@ __device__ __forceinline__ void lane_path(const PathArgs& g, Comm& cm, int p, in
       }
     }
     e = st[kBe * ss]; wx = st[kBwx * ss]; wy = st[kBwy * ss];
+    if constexpr (SHADOW) eS = st[kBeS * ss];
     alpha = st[kAlpha * ss];
   }
 
@@ -611,6 +737,27 @@ __global__ void __launch_bounds__(kLaneWarps * 32, 4) path_lane_kernel(PathArgs 
   lane_path<S, DEG, WarpComm, COLL>(g, cm, p, i, pl < PB && p < P, ce);
 }
 
+// 3 <= W <= 32, plain quintic optimiser: one lane per SEGMENT, floor(64 / (W - 1)) paths packed over each PAIR of warps
+// (W = 10: 7 paths on 63 of 64 lanes, against 3 paths per warp = 54 of 64 above; W = 20: 3 paths per pair against 2).
+// Same arithmetic, same summation order: bit-identical control points and cost (tests/test_gpu_parity.py).
+template <class S>
+__global__ void __launch_bounds__(kLaneWarps * 32, 4) path_pair_kernel(PathArgs g) {
+  extern __shared__ __align__(16) unsigned char lane_smem_raw[];
+  constexpr int kPairs = kLaneWarps / 2;
+  const int pair = threadIdx.x >> 6, t = threadIdx.x & 63;
+  const int nseg = g.W - 1, PBp = 64 / nseg, P = g.P;
+  const int p0 = (blockIdx.x * kPairs + pair) * PBp;
+  const int pl = t / nseg, i = t - pl * nseg, p = p0 + pl;
+  PairComm cm;
+  cm.tid = t; cm.base = pl * nseg; cm.n = nseg; cm.bar = 1 + pair; cm.sstride = 64;
+  cm.xbuf = (double*)lane_smem_raw + (size_t)pair * 2 * PairComm::kMaxVals * 64;
+  cm.st = (double*)lane_smem_raw + (size_t)kPairs * 2 * PairComm::kMaxVals * 64 + (size_t)pair * kPairSlots * 64 + t;
+  const CollEdges ce{nullptr, nullptr, nullptr, 0, 0, nullptr};
+  if (p0 >= P) return;  // the whole pair leaves together (its barrier is its own)
+  lane_path<S, 5, PairComm, false, true>(g, cm, p, i, pl < PBp && p < P, ce);
+}
+constexpr size_t kPairSmem = ((size_t)(kLaneWarps / 2) * 2 * PairComm::kMaxVals * 64 + (size_t)(kLaneWarps / 2) * kPairSlots * 64) * sizeof(double);
+
 // 33 <= W <= 512: one path per CTA of ceil(W / 32) warps (128 registers per thread: 512 threads at most)
 template <class S, int DEG, bool COLL>
 __global__ void __launch_bounds__(512, 1) path_lane_cta_kernel(PathArgs g) {
@@ -654,7 +801,18 @@ template <class S> void launch_path_lane(const PathArgs& a0, int spline_mode, in
     const int per_cta = PB * kLaneWarps, grid = (a.P + per_cta - 1) / per_cta;
     if (spline_mode == SCB_REF_CUBIC) path_lane_kernel<S, 3, false><<<grid, kLaneWarps * 32, smem, st>>>(a);
     else if (a.n_coll_edges > 0) path_lane_kernel<S, 5, true><<<grid, kLaneWarps * 32, smem, st>>>(a);
-    else path_lane_kernel<S, 5, false><<<grid, kLaneWarps * 32, smem, st>>>(a);
+    else {
+      // the pair mapping where it packs more paths onto the lanes (SCB_PATH_PAIR = 0 / 1: never / wherever it can run)
+      const char* e = getenv("SCB_PATH_PAIR");
+      const int nseg = a.W - 1, per_pair = a.W >= 3 ? 64 / nseg : 0;
+      const bool can = a.W >= 3, wins = can && per_pair > 2 * PB;
+      if (e ? (atoi(e) != 0 && can) : wins) {
+        const int per_cta2 = per_pair * (kLaneWarps / 2), grid2 = (a.P + per_cta2 - 1) / per_cta2;
+        path_pair_kernel<S><<<grid2, kLaneWarps * 32, kPairSmem, st>>>(a);
+      } else {
+        path_lane_kernel<S, 5, false><<<grid, kLaneWarps * 32, smem, st>>>(a);
+      }
+    }
   } else {
     const int T = (a.W + 31) / 32 * 32;
     if (spline_mode == SCB_REF_CUBIC) {

@@ -193,6 +193,32 @@ def test_cta_team_kernel_matches_lane_kernel(oracle, monkeypatch, W):
         assert rel_err(out["cta", "fp32"][n], out["lane", "fp32"][n], floor=float(np.max(np.abs(ref[n])))) <= 1e-6, n
 
 
+@pytest.mark.parametrize("W", [3, 4, 5, 10, 13, 17, 20, 31, 32])
+def test_pair_mapping_is_bit_identical(monkeypatch, W):
+    """path_pair_kernel (one lane per SEGMENT, paths packed over pairs of warps, the last waypoint carried by the lane of
+    the last segment; what W = 10 and W = 20 run by default) against path_lane_kernel / path_lane_cta_kernel (one lane per
+    WAYPOINT): the same expressions in the same order, so every bit of the control points, the cost and everything
+    downstream - with and without moving waypoints, start angles given and not, a bad path, ragged last CTA."""
+    rng = np.random.default_rng(50 + W)
+    P, G = 203, 40
+    wx, wy = scb.workloads.random_walk_paths(rng, P, W)
+    wx[7, W // 2] = np.nan
+    lim = scb.workloads.random_limits(rng, P, slow_fraction=0.0)
+    sa = rng.uniform(-np.pi, np.pi, P); sa[::2] = np.nan
+    out = {}
+    for pair in ("0", "1"):
+        monkeypatch.setenv("SCB_PATH_PAIR", pair)
+        pl = scb.BatchPlanner(0, "fp64", "lau_quintic", max_problems=P, max_waypoints=W, max_gridpoints=G)
+        try:
+            out[pair] = [pl.plan(wx=wx, wy=wy, G=G, start_angle=sa, opt=scb.default_opt(move_waypoints=mv), **lim) for mv in (0, 1)]
+        finally:
+            pl.close()
+    for a, b in zip(out["0"], out["1"]):
+        assert a["status"][7] != 0 and (a["status"] == 0).sum() >= P - 3
+        for k in ("status", "ctrl_x", "ctrl_y", "cost", "arclen_total", "x", "t", "px", "omega", "T_total"):
+            np.testing.assert_array_equal(a[k], b[k], err_msg=k)
+
+
 def test_c3_rollouts_match_oracle(planners, oracle):
     w = scb.workloads.config_c3(P=192)
     pl = planners("fp64", "lau_quintic")
