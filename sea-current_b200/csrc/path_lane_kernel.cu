@@ -519,7 +519,9 @@ __device__ __forceinline__ void lane_path(const PathArgs& g, Comm& cm, int p, in
       if (hasS) { nx[0] = eS * st[kBtSx * ss]; nx[1] = eS * st[kBtSy * ss]; nx[2] = st[kSx * ss]; nx[3] = st[kSy * ss]; }
     }
     Txp = nx[0]; Typ = nx[1]; wxp = nx[2]; wyp = nx[3];
-    const double pvx = 6.0 * (pv[2] - wx) + 4.0 * Tx + 2.0 * pv[0], pvy = 6.0 * (pv[3] - wy) + 4.0 * Ty + 2.0 * pv[1];
+    // (written out with the contraction the compiler chose for `6 (Wp - W) + 4 T + 2 Tp`, so that the SHADOW copy
+    // below is the same arithmetic by construction)
+    const double pvx = fma(2.0, pv[0], fma(6.0, pv[2] - wx, 4.0 * Tx)), pvy = fma(2.0, pv[1], fma(6.0, pv[3] - wy, 4.0 * Ty));
     const double nxx = 6.0 * (wxp - wx) - 4.0 * Tx - 2.0 * Txp, nxy = 6.0 * (wyp - wy) - 4.0 * Ty - 2.0 * Typ;
     Ax = first ? nxx : (last ? pvx : alpha * pvx + (1.0 - alpha) * nxx);
     Ay = first ? nxy : (last ? pvy : alpha * pvy + (1.0 - alpha) * nxy);
@@ -527,7 +529,7 @@ __device__ __forceinline__ void lane_path(const PathArgs& g, Comm& cm, int p, in
     cm.next(a2, an2);
     if constexpr (SHADOW) {
       if (hasS) {  // A of the last waypoint: the "previous" cubic alone (the `last` case of the lane it replaces)
-        an2[0] = 6.0 * (wx - wxp) + 4.0 * Txp + 2.0 * Tx; an2[1] = 6.0 * (wy - wyp) + 4.0 * Typ + 2.0 * Ty;
+        an2[0] = fma(2.0, Tx, fma(6.0, wx - wxp, 4.0 * Txp)); an2[1] = fma(2.0, Ty, fma(6.0, wy - wyp, 4.0 * Typ));
       }
     }
     Axp = an2[0]; Ayp = an2[1];
