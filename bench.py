@@ -167,6 +167,19 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(sm)}
 
 
+def path_kernel_name(W, mode, obstacles):
+    """The kernel launch_path_lane picks (path_lane_kernel.cu): the pair mapping where it packs more paths onto the lanes."""
+    if W > 512:
+        return "path_kernel"
+    if W > 32:
+        return "path_lane_cta_kernel"
+    pair = mode == "lau_quintic" and not obstacles and W >= 3 and 64 // (W - 1) > 2 * (32 // W)
+    env = os.environ.get("SCB_PATH_PAIR")
+    if env is not None:
+        pair = mode == "lau_quintic" and not obstacles and W >= 3 and int(env) != 0
+    return "path_pair_kernel" if pair else "path_lane_kernel"
+
+
 def host_cores():
     """Host threads this process may use (torchrun exports OMP_NUM_THREADS=1; the CPU arm must not inherit that)."""
     try:
@@ -378,7 +391,7 @@ def main():
     # algorithmic bytes of each kernel = its mandatory inputs + outputs; algorithmic flops = SURVEY 8-D5's model,
     # F_par's 160 G split 100 G (arc-length inversion, curve, curvature: arc kernel) + 60 G (parametrizer)
     kern = {
-        "path_ms": ("path_lane_kernel" if W <= 512 else "path_kernel", P * rs * (2 * W + 1 + 2 * (d + 1) * (W - 1) + 1), P * K_it * (W - 1) * Q * 120.0),
+        "path_ms": (path_kernel_name(W, mode, a.obstacles), P * rs * (2 * W + 1 + 2 * (d + 1) * (W - 1) + 1), P * K_it * (W - 1) * Q * 120.0),
         "arc_ms": ("arc_kernel", P * rs * (2 * (d + 1) * (W - 1) + 1 + 3 * G), P * ((W - 1) * 3200 * (4.0 * (d - 1) + 8.0) + 100.0 * G)),
         "toppra_ms": ("toppra_fast_kernel", P * (rs * (1 + 6 + 3 * G + grid_in) + 8), P * 640.0 * G),
         "param_ms": ("param_ca_kernel" if pm else "param_kernel", P * rs * (2 * G + 3 + 4 * G + 1), P * 60.0 * G),

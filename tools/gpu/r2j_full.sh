@@ -15,5 +15,5 @@ M=smsp__sass_thread_inst_executed_op_dfma_pred_on.sum,smsp__sass_thread_inst_exe
 $CMD > gpurun_out/${T}_plain.log 2>&1 && \
 ncu --metrics $M --clock-control none -s 12 -c 10 --csv --log-file gpurun_out/${T}_ops.csv $CMD > gpurun_out/${T}_ncu_ops.log 2>&1
 ncu --metrics gpu__time_duration.sum --clock-control none -s 12 -c 40 --csv --log-file gpurun_out/${T}_launches.csv $CMD > gpurun_out/${T}_ncu_launches.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:"path_lane_kernel|arc_kernel|toppra_fast_kernel|param_kernel" -s 8 -c 4 -o gpurun_out/${T}_full $CMD > gpurun_out/${T}_ncu_full.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:"path_pair_kernel|path_lane_kernel|arc_kernel|toppra_fast_kernel|param_kernel" -s 8 -c 4 -o gpurun_out/${T}_full $CMD > gpurun_out/${T}_ncu_full.log 2>&1
 ls -la gpurun_out | tail -20
