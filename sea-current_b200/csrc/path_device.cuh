@@ -106,9 +106,11 @@ static __constant__ double kPGL4W[4] = {0.3478548451374538574, 0.652145154862546
 
 // iRPROP- update of one parameter (DESIGN.md "New stages")
 template <class R> __device__ __forceinline__ R rprop_step(R gv, R& gprev, R& step, R smin, R smax) {
+  // selects, not branches (the same values: a NaN product fails both comparisons and leaves everything as it is)
   const R s = gv * gprev;
-  if (s > 0) step = fmin(step * (R)1.2, smax);
-  else if (s < 0) { step = fmax(step * (R)0.5, smin); gv = 0; }
+  const R up = fmin(step * (R)1.2, smax), dn = fmax(step * (R)0.5, smin);
+  step = s > 0 ? up : (s < 0 ? dn : step);
+  gv = s < 0 ? (R)0 : gv;
   gprev = gv;
   return gv > 0 ? -step : (gv < 0 ? step : (R)0);
 }

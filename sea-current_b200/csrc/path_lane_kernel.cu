@@ -429,15 +429,19 @@ struct PairComm {
   __device__ __forceinline__ double path_sum(double v, int cnt) {
     const double a[1] = {v};
     const double* b = stage(a);
+    const double* q = b + base;
+    const int m = min(cnt, T - base);  // (lanes without a path may start near the end of the area)
     double acc = 0;
-    for (int s = 0; s < cnt; ++s) acc += b[min(base + s, T - 1)];
+    for (int s = 0; s < m; ++s) acc += q[s];
     return acc;
   }
   __device__ __forceinline__ void path_max2(double& a, double& c) {
     const double v[2] = {a, c};
     const double* b = stage(v);
+    const double* q = b + base;
+    const int m = min(n, T - base);
     double ma = 0, mb = 0;
-    for (int k = 0; k < n; ++k) { const int j = min(base + k, T - 1); ma = fmax(ma, b[j]); mb = fmax(mb, b[T + j]); }
+    for (int k = 0; k < m; ++k) { ma = fmax(ma, q[k]); mb = fmax(mb, q[T + k]); }
     a = ma; c = mb;
   }
   __device__ __forceinline__ bool path_any(bool f) {
